@@ -1,0 +1,228 @@
+/* libcuorb — C ABI of the B200-native ORB front-end (hand-written sm_100a CUDA).
+ *
+ * This is the ONLY boundary between the untouched CPU SLAM code of the reference
+ * (elkuno213/orbslam3_cpp_fork: Tracking / Frame / ORBmatcher callers) and the GPU.
+ * Plain C: opaque handles, POD structs, raw pointers and sizes.  No C++/torch types.
+ *
+ * Every entry point cites the reference interface it replaces (paths relative to the
+ * reference checkout).  Error convention (reference: src/ORBextractor.cc:1060-1062 returns -1
+ * on an empty image; no exceptions on this path): functions return >= 0 on success and a
+ * negative cuorb_status on failure; cuorb_last_error() gives a thread-local message.
+ * There is NO CPU fallback: if no CUDA device / kernel image is usable the call fails.
+ */
+#ifndef CUORB_H
+#define CUORB_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CUORB_VERSION 100
+
+typedef enum cuorb_status {
+  CUORB_OK            = 0,
+  CUORB_E_EMPTY       = -1, /* empty image: same value operator() returns (ORBextractor.cc:1060) */
+  CUORB_E_BADARG      = -2, /* null pointer, bad size, image larger than the handle was built for */
+  CUORB_E_CAPACITY    = -3, /* caller buffers (or an internal candidate list) too small */
+  CUORB_E_CUDA        = -4, /* CUDA runtime error (sticky) — see cuorb_last_error() */
+  CUORB_E_UNSUPPORTED = -5, /* geometry the reference itself has undefined behaviour for */
+  CUORB_E_STATE       = -6  /* call sequence error (e.g. fetch before extract) */
+} cuorb_status;
+
+/* Layout-identical to cv::KeyPoint (7 x 4 bytes, no padding): pt.x, pt.y, size, angle,
+ * response, octave, class_id.  The host shim can memcpy into std::vector<cv::KeyPoint>. */
+typedef struct cuorb_keypoint {
+  float   x, y;
+  float   size;
+  float   angle;    /* degrees in [0,360) (cv::fastAtan2) */
+  float   response; /* FAST score 1..254 */
+  int32_t octave;
+  int32_t class_id; /* always -1 */
+} cuorb_keypoint;
+
+/* ORBextractor::ORBextractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST)
+ * (include/ORBextractor.h:48, src/ORBextractor.cc:403-465) + capacity of the device arena. */
+typedef struct cuorb_config {
+  int32_t nfeatures;
+  float   scale_factor;
+  int32_t nlevels;      /* 1..CUORB_MAX_LEVELS */
+  int32_t ini_th_fast;
+  int32_t min_th_fast;
+  int32_t max_width;    /* largest image the handle will be given */
+  int32_t max_height;
+  int32_t max_batch;    /* images per batched call (1 for the drop-in operator()) */
+  int32_t device;       /* CUDA device ordinal */
+} cuorb_config;
+
+#define CUORB_MAX_LEVELS 16
+#define CUORB_DESC_BYTES 32
+
+typedef struct cuorb_extractor cuorb_extractor;
+
+/* where a caller-supplied image / descriptor buffer lives */
+typedef enum cuorb_mem { CUORB_MEM_HOST = 0, CUORB_MEM_DEVICE = 1 } cuorb_mem;
+
+const char* cuorb_last_error(void);
+int         cuorb_version(void);
+int         cuorb_device_count(void);
+
+/* pinned host memory helpers (so H2D/D2H copies of the batched calls are truly asynchronous) */
+void* cuorb_host_alloc(size_t bytes);
+void  cuorb_host_free(void* p);
+
+/* ---- extractor: replaces class ORB_SLAM3::ORBextractor (include/ORBextractor.h:41-119) ---- */
+
+/* ctor (src/ORBextractor.cc:403-465); allocates every device/pinned buffer up front. */
+cuorb_extractor* cuorb_extractor_create(const cuorb_config* cfg);
+void             cuorb_extractor_destroy(cuorb_extractor* ext);
+
+/* GetScaleFactors / GetInverseScaleFactors / GetScaleSigmaSquares / GetInverseScaleSigmaSquares
+ * (include/ORBextractor.h:63-85) and mnFeaturesPerLevel (src/ORBextractor.cc:427-440).
+ * Each out pointer may be NULL; arrays hold nlevels entries. Returns nlevels. */
+int cuorb_extractor_get_tables(const cuorb_extractor* ext, float* scale, float* inv_scale,
+                               float* sigma2, float* inv_sigma2, int32_t* features_per_level);
+
+/* int ORBextractor::operator()(image, mask, keypoints, descriptors, vLappingArea)
+ * (include/ORBextractor.h:55-61, src/ORBextractor.cc:1052-1138), called by Frame::ExtractORB
+ * (src/Frame.cc:555-562).  img: 8-bit single channel, host memory, row pitch `stride`.
+ * kps/desc: host buffers of `capacity` entries / capacity*32 bytes; *n_out = keypoint count.
+ * Returns monoIndex (>= 0) or a negative cuorb_status (CUORB_E_EMPTY == the reference's -1). */
+int cuorb_extract(cuorb_extractor* ext, const uint8_t* img, int width, int height, size_t stride,
+                  int lap0, int lap1, cuorb_keypoint* kps, uint8_t* desc, int capacity, int* n_out);
+
+/* Batched / asynchronous form of the same operator: n_images images of identical size laid out
+ * `image_stride` bytes apart in host (pinned recommended) or device memory.  Work is enqueued on
+ * the handle's stream and returns immediately; results stay on the device until fetched. */
+int cuorb_extract_batch_async(cuorb_extractor* ext, int n_images, const uint8_t* imgs, int width,
+                              int height, size_t stride, size_t image_stride, cuorb_mem where,
+                              int lap0, int lap1);
+
+/* Copy the results of the last batch to host and wait.  kps: n_images*capacity entries, desc:
+ * n_images*capacity*32 bytes (either may be NULL to skip), n_out/mono_index_out: n_images ints.
+ * Returns the number of images, or a negative status (CUORB_E_CAPACITY if any image has more
+ * keypoints than `capacity`; counts are still written). */
+int cuorb_extract_fetch(cuorb_extractor* ext, cuorb_keypoint* kps, uint8_t* desc, int capacity,
+                        int32_t* n_out, int32_t* mono_index_out);
+/* Asynchronous variant: enqueues D2H into pinned caller buffers; pair with cuorb_sync(). */
+int cuorb_extract_fetch_async(cuorb_extractor* ext, cuorb_keypoint* kps, uint8_t* desc,
+                              int capacity, int32_t* n_out, int32_t* mono_index_out);
+int cuorb_sync(cuorb_extractor* ext);
+
+/* std::vector<cv::Mat> mvImagePyramid (include/ORBextractor.h:87; read by
+ * Frame::ComputeStereoMatches, src/Frame.cc:950,1039,1056).  Device pointer to pixel (0,0) of
+ * `level` of image `image_index` of the last batch (the 19-px REFLECT_101 border lies at negative
+ * offsets, as in the reference's ROI-of-temp layout); valid until the next extract call. */
+int cuorb_extractor_pyramid(const cuorb_extractor* ext, int image_index, int level,
+                            const uint8_t** dev_ptr, int* width, int* height, size_t* stride);
+
+/* Parity/debug downloads (synchronous).  plane: 0 = pyramid level incl. 19-px border
+ * ((w+38)*(h+38) bytes, tightly packed), 1 = pyramid level without border (w*h),
+ * 2 = 7x7 sigma-2 blurred level (w*h) (src/ORBextractor.cc:1103-1104).  Returns bytes written. */
+int64_t cuorb_extractor_download_plane(cuorb_extractor* ext, int image_index, int level, int plane,
+                                       uint8_t* out, size_t out_bytes, int* width, int* height);
+/* Per-level FAST candidates handed to DistributeOctTree (vToDistributeKeys,
+ * src/ORBextractor.cc:766-850): coordinates relative to (minBorderX,minBorderY), FAST response,
+ * sorted into the reference's cell-row-major / row-major order.  Returns the count. */
+int cuorb_extractor_download_candidates(cuorb_extractor* ext, int image_index, int level,
+                                        int32_t* xs, int32_t* ys, int32_t* responses, int capacity);
+
+/* ---- stereo association: replaces void Frame::ComputeStereoMatches()
+ * (include/Frame.h:155, src/Frame.cc:944-1113); BASELINE.json calls it "SearchStereo". ---- */
+
+/* Device-resident form: matches the last batch extracted on `left` against the last batch on
+ * `right` (same n_images, kps/descriptors/pyramids still on the device).  Enqueued on left's
+ * stream after right's work.  mb/mbf: Frame::mb, Frame::mbf (src/Frame.cc:257). */
+int cuorb_stereo_match_batch_async(cuorb_extractor* left, cuorb_extractor* right, float mb,
+                                   float mbf);
+/* mvuRight / mvDepth (src/Frame.cc:945-946) of the last stereo batch: n_images*capacity floats
+ * each, -1 where unmatched.  best_idx_r / best_dist / sad are optional debug outputs (may be
+ * NULL): coarse Hamming winner, its distance (src/Frame.cc:1001-1026), and the SAD pushed to
+ * vDistIdx (src/Frame.cc:1096) or -1. */
+int cuorb_stereo_fetch(cuorb_extractor* left, float* u_right, float* depth, int capacity,
+                       int32_t* best_idx_r, int32_t* best_dist, int32_t* sad);
+int cuorb_stereo_fetch_async(cuorb_extractor* left, float* u_right, float* depth, int capacity);
+
+/* Host-pointer form with the exact member set the reference method reads: left/right keypoints
+ * and descriptors (mvKeys, mvKeysRight, mDescriptors, mDescriptorsRight), mb, mbf; scale tables
+ * and pyramids come from the two extractor handles (image 0 of their last extract). */
+int cuorb_stereo_match(cuorb_extractor* left, cuorb_extractor* right, int n_left,
+                       const cuorb_keypoint* kps_left, const uint8_t* desc_left, int n_right,
+                       const cuorb_keypoint* kps_right, const uint8_t* desc_right, float mb,
+                       float mbf, float* u_right, float* depth);
+
+/* ---- matcher: replaces the tracking-time subset of class ORB_SLAM3::ORBmatcher ---- */
+
+/* static int ORBmatcher::DescriptorDistance(const cv::Mat&, const cv::Mat&)
+ * (include/ORBmatcher.h:40, src/ORBmatcher.cc:2075-2089).  Host-side popcount: one pair is far
+ * too small for a device round trip. */
+int cuorb_hamming256(const void* a, const void* b);
+/* Batched device form: out[i] = Hamming(a[ia[i]], b[ib[i]]) for n_pairs pairs; a, b are host
+ * arrays of 32-byte descriptors, ia/ib may be NULL (then pair i = (i, i)). */
+int cuorb_hamming_batch(int device, const uint8_t* a, int n_a, const uint8_t* b, int n_b,
+                        const int32_t* ia, const int32_t* ib, int n_pairs, int32_t* out);
+
+/* The Frame members the two SearchByProjection overloads read (flattened by the host shim). */
+typedef struct cuorb_frame_view {
+  int32_t               n;             /* Frame::N (Nleft == -1: pinhole, non-fisheye) */
+  const cuorb_keypoint* keys_un;       /* mvKeysUn */
+  const uint8_t*        descriptors;   /* mDescriptors, n x 32 */
+  const float*          u_right;       /* mvuRight (may be NULL = all -1) */
+  const uint8_t*        bound_with_obs;/* per feature: mvpMapPoints[i] && Observations()>0 */
+  float                 min_x, min_y, max_x, max_y; /* mnMinX.. (src/Frame.cc:932-940) */
+  float                 grid_w_inv, grid_h_inv;     /* mfGridElementWidthInv/HeightInv */
+  float                 mb, mbf;
+  int32_t               nlevels;
+  const float*          scale_factors; /* mvScaleFactors */
+} cuorb_frame_view;
+
+/* int ORBmatcher::SearchByProjection(Frame&, const std::vector<MapPoint*>&, th, bFarPoints,
+ * thFarPoints) (include/ORBmatcher.h:44-50, src/ORBmatcher.cc:38-150; pinhole branch).
+ * Per MapPoint SoA: proj_x/proj_y/proj_xr = mTrackProjX/Y/XR, level = mnTrackScaleLevel,
+ * view_cos = mTrackViewCos, depth = mTrackDepth, flags bit0 = mbTrackInView, bit1 = isBad(),
+ * bit2 = Observations() > 0.  best_idx_out[i] = frame feature bound to MapPoint i, or -1; the
+ * caller replays F.mvpMapPoints[best] = pMP in MapPoint order.  Returns nmatches. */
+#define CUORB_MP_IN_VIEW 1u
+#define CUORB_MP_BAD     2u
+#define CUORB_MP_HAS_OBS 4u
+int cuorb_search_by_projection(int device, const cuorb_frame_view* frame, int n_mappoints,
+                               const uint8_t* mp_desc, const float* proj_x, const float* proj_y,
+                               const float* proj_xr, const int32_t* level, const float* view_cos,
+                               const float* depth, const uint8_t* flags, float th, int far_points,
+                               float th_far_points, float nn_ratio, int32_t* best_idx_out);
+
+/* int ORBmatcher::SearchByProjection(Frame& Cur, const Frame& Last, th, bMono)
+ * (include/ORBmatcher.h:54-56, src/ORBmatcher.cc:1684-1811, 1889-1908; pinhole branch).
+ * Per last-frame feature SoA (only features with a non-outlier MapPoint are passed as valid):
+ * u/v = projected pixel, inv_z = 1/zc, last_octave, last_angle = kpLF.angle, flags as above with
+ * bit0 = "has MapPoint and not outlier".  forward/backward = bForward/bBackward (1702-1703).
+ * best_idx_out[i] = current-frame feature or -1 (BEFORE the rotation check); rot_bin_out[i] =
+ * histogram bin or -1; keep_bins_out[3] = ComputeThreeMaxima result (src/ORBmatcher.cc:2038).
+ * Returns nmatches after the rotation-consistency removal, as the reference does. */
+int cuorb_search_by_projection_frame(int device, const cuorb_frame_view* cur, int n_last,
+                                     const uint8_t* last_desc, const float* u, const float* v,
+                                     const float* inv_z, const int32_t* last_octave,
+                                     const float* last_angle, const uint8_t* flags, float th,
+                                     int forward, int backward, int check_orientation,
+                                     int32_t* best_idx_out, int32_t* rot_bin_out,
+                                     int32_t* keep_bins_out);
+
+/* ---- instrumentation ---- */
+
+/* number of libcuorb kernel launches issued by this process so far (bench.py's gpu_launches) */
+uint64_t cuorb_kernel_launch_count(void);
+/* CUDA-event time, in ms, of the stages of the last batch on this handle (requires
+ * cuorb_set_profiling(ext, 1) before the extract call).  stage ids: CUORB_STAGE_*. */
+enum {
+  CUORB_STAGE_H2D = 0, CUORB_STAGE_PYRAMID, CUORB_STAGE_FAST, CUORB_STAGE_OCTREE,
+  CUORB_STAGE_BLUR, CUORB_STAGE_DESCRIBE, CUORB_STAGE_STEREO, CUORB_STAGE_COUNT
+};
+int cuorb_set_profiling(cuorb_extractor* ext, int enabled);
+int cuorb_stage_ms(cuorb_extractor* ext, float* ms_out /* CUORB_STAGE_COUNT floats */);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CUORB_H */

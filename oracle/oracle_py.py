@@ -1,0 +1,288 @@
+"""TEST INFRASTRUCTURE — NOT PRODUCT CODE.
+
+ctypes binding of the CPU oracle (oracle/_build/liborb_oracle.so, built by oracle/Makefile).
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import
+this module; the product package (orbslam3_cpp_fork_b200) never does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "_build", "liborb_oracle.so")
+
+KP_DTYPE = np.dtype(
+    [("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+     ("octave", "<i4"), ("class_id", "<i4")]
+)
+assert KP_DTYPE.itemsize == 28
+
+
+class FrameViewC(C.Structure):
+    """cuorb_frame_view (include/cuorb.h)."""
+
+    _fields_ = [
+        ("n", C.c_int32), ("keys_un", C.c_void_p), ("descriptors", C.c_void_p),
+        ("u_right", C.c_void_p), ("bound_with_obs", C.c_void_p),
+        ("min_x", C.c_float), ("min_y", C.c_float), ("max_x", C.c_float), ("max_y", C.c_float),
+        ("grid_w_inv", C.c_float), ("grid_h_inv", C.c_float), ("mb", C.c_float), ("mbf", C.c_float),
+        ("nlevels", C.c_int32), ("scale_factors", C.c_void_p),
+    ]
+
+
+def build(force: bool = False) -> str:
+    srcs = [os.path.join(_HERE, f) for f in
+            ("orb_oracle.cpp", "orb_oracle_match.cpp", "orb_oracle_capi.cpp", "orb_oracle.hpp")]
+    stale = (not os.path.exists(_LIB_PATH)) or any(
+        os.path.getmtime(s) > os.path.getmtime(_LIB_PATH) for s in srcs)
+    if force or stale:
+        subprocess.check_call(["make", "-C", _HERE, "-s"] + (["-B"] if force else []))
+    return _LIB_PATH
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(_LIB_PATH)
+        L.oo_create.restype = C.c_void_p
+        L.oo_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        L.oo_destroy.argtypes = [C.c_void_p]
+        L.oo_get_tables.argtypes = [C.c_void_p] + [C.c_void_p] * 5
+        L.oo_get_umax.argtypes = [C.c_void_p, C.c_void_p]
+        L.oo_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int,
+                                 C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
+        L.oo_level_size.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.oo_get_plane.restype = C.c_int64
+        L.oo_get_plane.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t]
+        L.oo_get_candidates.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.oo_get_level_keys.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        L.oo_resize.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_void_p, C.c_int, C.c_int]
+        L.oo_border.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_void_p, C.c_int]
+        L.oo_fast.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.oo_blur.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_void_p]
+        L.oo_fast_atan2.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.oo_octree.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                C.c_int, C.c_void_p, C.c_int]
+        L.oo_hamming.argtypes = [C.c_void_p, C.c_void_p]
+        L.oo_stereo.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                C.c_void_p, C.c_void_p, C.c_float, C.c_float] + [C.c_void_p] * 5
+        L.oo_search_by_projection.argtypes = (
+            [C.POINTER(FrameViewC), C.c_int] + [C.c_void_p] * 8 +
+            [C.c_float, C.c_int, C.c_float, C.c_float, C.c_void_p])
+        L.oo_search_by_projection_frame.argtypes = (
+            [C.POINTER(FrameViewC), C.c_int] + [C.c_void_p] * 7 +
+            [C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p])
+        L.oo_bench_stereo.restype = C.c_double
+        L.oo_bench_stereo.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                      C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float,
+                                      C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def make_frame_view(keys_un, desc, u_right, bound, w, h, scale_factors, mb=0.0, mbf=0.0,
+                    min_x=0.0, min_y=0.0, max_x=None, max_y=None):
+    """Build a cuorb_frame_view (+ keepalive list) the way the Frame ctor fills the members
+    (src/Frame.cc:240-257: mfGridElementWidthInv = 64 / (mnMaxX - mnMinX), ...)."""
+    max_x = float(w) if max_x is None else max_x
+    max_y = float(h) if max_y is None else max_y
+    keys_un = np.ascontiguousarray(keys_un, dtype=KP_DTYPE)
+    desc = np.ascontiguousarray(desc, dtype=np.uint8)
+    sf = np.ascontiguousarray(scale_factors, dtype=np.float32)
+    ur = None if u_right is None else np.ascontiguousarray(u_right, dtype=np.float32)
+    bd = None if bound is None else np.ascontiguousarray(bound, dtype=np.uint8)
+    fv = FrameViewC()
+    fv.n = len(keys_un)
+    fv.keys_un = _p(keys_un); fv.descriptors = _p(desc); fv.u_right = _p(ur); fv.bound_with_obs = _p(bd)
+    fv.min_x, fv.min_y, fv.max_x, fv.max_y = min_x, min_y, max_x, max_y
+    fv.grid_w_inv = float(np.float32(64.0) / np.float32(np.float32(max_x) - np.float32(min_x)))
+    fv.grid_h_inv = float(np.float32(48.0) / np.float32(np.float32(max_y) - np.float32(min_y)))
+    fv.mb, fv.mbf = mb, mbf
+    fv.nlevels = len(sf)
+    fv.scale_factors = _p(sf)
+    return fv, [keys_un, desc, sf, ur, bd]
+
+
+class OracleExtractor:
+    """ORBextractor of the oracle (same ctor arguments as include/ORBextractor.h:48)."""
+
+    def __init__(self, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7):
+        self.L = lib()
+        self.nlevels = nlevels
+        self.h = self.L.oo_create(nfeatures, scale_factor, nlevels, ini_th, min_th)
+        self.cap = max(4 * nfeatures, 64)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.oo_destroy(self.h)
+            self.h = None
+
+    def tables(self):
+        n = self.nlevels
+        sf, inv, s2, is2 = (np.zeros(n, np.float32) for _ in range(4))
+        per = np.zeros(n, np.int32)
+        self.L.oo_get_tables(self.h, _p(sf), _p(inv), _p(s2), _p(is2), _p(per))
+        return sf, inv, s2, is2, per
+
+    def umax(self):
+        out = np.zeros(16, np.int32)
+        self.L.oo_get_umax(self.h, _p(out))
+        return out
+
+    def extract(self, img, lap=(0, 0)):
+        """operator(): returns (monoIndex, keypoints[KP_DTYPE], descriptors[n,32])."""
+        if img is None or img.size == 0:
+            return -1, np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8)
+        img = np.ascontiguousarray(img, dtype=np.uint8)
+        h, w = img.shape
+        kps = np.zeros(self.cap, KP_DTYPE)
+        desc = np.zeros((self.cap, 32), np.uint8)
+        n = C.c_int(0)
+        mono = self.L.oo_extract(self.h, _p(img), w, h, img.strides[0], lap[0], lap[1], _p(kps),
+                                 _p(desc), self.cap, C.byref(n))
+        if mono < 0:
+            raise RuntimeError(f"oracle extract failed: {mono}")
+        return mono, kps[: n.value].copy(), desc[: n.value].copy()
+
+    def level_size(self, level):
+        w, h = C.c_int(), C.c_int()
+        self.L.oo_level_size(self.h, level, C.byref(w), C.byref(h))
+        return w.value, h.value
+
+    def plane(self, level, plane):
+        w, h = self.level_size(level)
+        if plane == 0:
+            out = np.zeros((h + 38, w + 38), np.uint8)
+        else:
+            out = np.zeros((h, w), np.uint8)
+        r = self.L.oo_get_plane(self.h, level, plane, _p(out), out.size)
+        if r == 0:
+            return None
+        assert r == out.size, r
+        return out
+
+    def candidates(self, level, cap=200000):
+        xs, ys, rs = (np.zeros(cap, np.int32) for _ in range(3))
+        n = self.L.oo_get_candidates(self.h, level, _p(xs), _p(ys), _p(rs), cap)
+        assert n <= cap
+        return xs[:n].copy(), ys[:n].copy(), rs[:n].copy()
+
+    def level_keys(self, level):
+        out = np.zeros(self.cap, KP_DTYPE)
+        n = self.L.oo_get_level_keys(self.h, level, _p(out), self.cap)
+        return out[:n].copy()
+
+    def octree(self, keys, min_x, max_x, min_y, max_y, n_desired):
+        keys = np.ascontiguousarray(keys, dtype=KP_DTYPE)
+        cap = max(len(keys), 16)
+        out = np.zeros(cap, KP_DTYPE)
+        n = self.L.oo_octree(self.h, _p(keys), len(keys), min_x, max_x, min_y, max_y, n_desired,
+                             _p(out), cap)
+        return out[:n].copy()
+
+
+def resize(src, dw, dh):
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.zeros((dh, dw), np.uint8)
+    lib().oo_resize(_p(src), src.shape[1], src.shape[0], src.strides[0], _p(dst), dw, dh)
+    return dst
+
+
+def border(src, b=19):
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.zeros((src.shape[0] + 2 * b, src.shape[1] + 2 * b), np.uint8)
+    lib().oo_border(_p(src), src.shape[1], src.shape[0], src.strides[0], _p(dst), b)
+    return dst
+
+
+def fast(img, threshold, nonmax=True, cap=400000):
+    img = np.ascontiguousarray(img, np.uint8)
+    out = np.zeros(cap, KP_DTYPE)
+    n = lib().oo_fast(_p(img), img.shape[1], img.shape[0], img.strides[0], threshold, int(nonmax),
+                      _p(out), cap)
+    assert n <= cap
+    return out[:n].copy()
+
+
+def blur(img):
+    img = np.ascontiguousarray(img, np.uint8)
+    dst = np.zeros_like(img)
+    lib().oo_blur(_p(img), img.shape[1], img.shape[0], img.strides[0], _p(dst))
+    return dst
+
+
+def fast_atan2(y, x):
+    y = np.ascontiguousarray(y, np.float32)
+    x = np.ascontiguousarray(x, np.float32)
+    out = np.zeros_like(y)
+    lib().oo_fast_atan2(_p(y), _p(x), _p(out), y.size)
+    return out
+
+
+def hamming(a, b):
+    a = np.ascontiguousarray(a, np.uint8)
+    b = np.ascontiguousarray(b, np.uint8)
+    return lib().oo_hamming(_p(a), _p(b))
+
+
+def stereo(ext_l: OracleExtractor, ext_r: OracleExtractor, kps_l, desc_l, kps_r, desc_r, mb, mbf):
+    """Frame::ComputeStereoMatches on the pyramids of the two extractors' last extract.
+    Returns dict(u_right, depth, best_idx_r, best_dist, sad)."""
+    kps_l = np.ascontiguousarray(kps_l, KP_DTYPE); kps_r = np.ascontiguousarray(kps_r, KP_DTYPE)
+    desc_l = np.ascontiguousarray(desc_l, np.uint8); desc_r = np.ascontiguousarray(desc_r, np.uint8)
+    n = len(kps_l)
+    u = np.zeros(n, np.float32); d = np.zeros(n, np.float32)
+    bi, bd, sad = (np.zeros(n, np.int32) for _ in range(3))
+    lib().oo_stereo(ext_l.h, ext_r.h, n, _p(kps_l), _p(desc_l), len(kps_r), _p(kps_r), _p(desc_r),
+                    mb, mbf, _p(u), _p(d), _p(bi), _p(bd), _p(sad))
+    return dict(u_right=u, depth=d, best_idx_r=bi, best_dist=bd, sad=sad)
+
+
+def search_by_projection(fv, mp_desc, px, py, pxr, level, view_cos, depth, flags, th, far_points,
+                         th_far, nn_ratio):
+    M = len(px)
+    arrs = [np.ascontiguousarray(mp_desc, np.uint8), np.ascontiguousarray(px, np.float32),
+            np.ascontiguousarray(py, np.float32), np.ascontiguousarray(pxr, np.float32),
+            np.ascontiguousarray(level, np.int32), np.ascontiguousarray(view_cos, np.float32),
+            np.ascontiguousarray(depth, np.float32), np.ascontiguousarray(flags, np.uint8)]
+    out = np.zeros(M, np.int32)
+    n = lib().oo_search_by_projection(C.byref(fv), M, *[_p(a) for a in arrs], th, int(far_points),
+                                      th_far, nn_ratio, _p(out))
+    return n, out
+
+
+def search_by_projection_frame(fv, last_desc, u, v, inv_z, last_octave, last_angle, flags, th,
+                               forward, backward, check_ori=True):
+    n_last = len(u)
+    arrs = [np.ascontiguousarray(last_desc, np.uint8), np.ascontiguousarray(u, np.float32),
+            np.ascontiguousarray(v, np.float32), np.ascontiguousarray(inv_z, np.float32),
+            np.ascontiguousarray(last_octave, np.int32), np.ascontiguousarray(last_angle, np.float32),
+            np.ascontiguousarray(flags, np.uint8)]
+    best = np.zeros(n_last, np.int32); rot = np.zeros(n_last, np.int32); keep = np.zeros(3, np.int32)
+    n = lib().oo_search_by_projection_frame(C.byref(fv), n_last, *[_p(a) for a in arrs], th,
+                                            int(forward), int(backward), int(check_ori), _p(best),
+                                            _p(rot), _p(keep))
+    return n, best, rot, keep
+
+
+def bench_stereo(left, right, mb, mbf, n_threads, nfeatures=1000, scale=1.2, nlevels=8, ini=20,
+                 mn=7):
+    """Time the oracle's stereo path over a stack of frames [n,h,w]; returns (seconds, kps, matches)."""
+    left = np.ascontiguousarray(left, np.uint8); right = np.ascontiguousarray(right, np.uint8)
+    n, h, w = left.shape
+    k, m = C.c_int64(0), C.c_int64(0)
+    sec = lib().oo_bench_stereo(nfeatures, scale, nlevels, ini, mn, _p(left), _p(right), n, w, h, mb,
+                                mbf, n_threads, C.byref(k), C.byref(m))
+    return sec, k.value, m.value
