@@ -85,6 +85,10 @@ void             cuorb_extractor_destroy(cuorb_extractor* ext);
 int cuorb_extractor_get_tables(const cuorb_extractor* ext, float* scale, float* inv_scale,
                                float* sigma2, float* inv_sigma2, int32_t* features_per_level);
 
+/* Largest keypoint count one image can produce with this handle's current geometry
+ * (sum over levels of quota + quadtree overshoot slack); device-side result rows are this long. */
+int cuorb_extractor_capacity(const cuorb_extractor* ext);
+
 /* int ORBextractor::operator()(image, mask, keypoints, descriptors, vLappingArea)
  * (include/ORBextractor.h:55-61, src/ORBextractor.cc:1052-1138), called by Frame::ExtractORB
  * (src/Frame.cc:555-562).  img: 8-bit single channel, host memory, row pitch `stride`.

@@ -1,0 +1,8 @@
+"""orbslam3_cpp_fork_b200 — B200-native ORB front-end (libcuorb) behind the reference's operator API.
+
+Only the hot path of SURVEY.md §8 lives here: csrc/ (sm_100a CUDA kernels + the C ABI of
+include/cuorb.h), the ctypes binding, and the host-side mirrors of ORBextractor / ORBmatcher.
+"""
+from ._lib import KP_DTYPE, CuorbError, load  # noqa: F401
+from .extractor import ORBextractor  # noqa: F401
+from .matcher import Frame, MapPointSoA, ORBmatcher  # noqa: F401

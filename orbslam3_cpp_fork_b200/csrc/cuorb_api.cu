@@ -1,0 +1,660 @@
+// libcuorb — C ABI implementation (see include/cuorb.h): extractor handle, geometry tables
+// computed with the reference's float arithmetic, stream-ordered batch pipeline.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <mutex>
+
+#include "common.cuh"
+
+namespace cuorb {
+
+static thread_local std::string t_last_error;
+void set_error(const std::string& msg) { t_last_error = msg; }
+std::atomic<unsigned long long> g_launch_count{0};
+
+static inline int cv_round_f(float v) { return (int)lrintf(v); }
+static inline short sat_short(float v) {
+  int i = cv_round_f(v);
+  return (short)std::min(std::max(i, -32768), 32767);
+}
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+}  // namespace cuorb
+
+using namespace cuorb;
+
+struct cuorb_extractor {
+  cuorb_config  cfg;
+  ExtractorGeom g;  // geometry of the CURRENT image size (rebuilt when the size changes)
+  int           cur_w = 0, cur_h = 0;
+  float scale[MAX_LEVELS], inv_scale[MAX_LEVELS], sigma2[MAX_LEVELS], inv_sigma2[MAX_LEVELS];
+  int   quota[MAX_LEVELS];
+
+  cudaStream_t stream = nullptr;
+  cudaEvent_t  ev_done = nullptr;       // recorded after the last enqueued work
+  cudaEvent_t  ev_stage[CUORB_STAGE_COUNT + 1] = {};
+  bool         profiling = false, have_stage_times = false, stereo_timed = false;
+
+  // device buffers (sized for max_width x max_height x max_batch)
+  ExtractorGeom* d_geom = nullptr;
+  ResizeTap *d_xtab = nullptr, *d_ytab = nullptr;
+  int4*      d_blur_tiles = nullptr;
+  int        n_blur_tiles = 0;
+  uint8_t *  d_input = nullptr, *d_pyr = nullptr, *d_blur = nullptr;
+  unsigned * d_cand = nullptr, *d_cand_scratch = nullptr;
+  int *      d_cand_count = nullptr, *d_key_count = nullptr, *d_flags = nullptr, *d_slot = nullptr;
+  LevelKey*  d_keys = nullptr;
+  cuorb_keypoint* d_out_kps = nullptr;
+  uint8_t*   d_out_desc = nullptr;
+  int *      d_out_n = nullptr, *d_out_mono = nullptr;
+  float *    d_uright = nullptr, *d_depth = nullptr;
+  int *      d_sad = nullptr, *d_best_idx = nullptr, *d_best_dist = nullptr;
+  // pinned host mirrors of the small per-image results
+  int *h_out_n = nullptr, *h_out_mono = nullptr, *h_flags = nullptr;
+  size_t cap_input = 0, cap_pyr = 0, cap_blur = 0, cap_cand = 0, cap_keys = 0, cap_kp = 0;
+  size_t cap_xtab = 0, cap_ytab = 0, cap_tiles = 0;
+  int    n_img = 0;       // images in the last batch
+  bool   have_batch = false, have_stereo = false;
+};
+
+namespace cuorb {
+
+// ctor tables (src/ORBextractor.cc:411-440)
+static void build_tables(cuorb_extractor* e) {
+  const cuorb_config& c = e->cfg;
+  const double scaleFactor = (double)c.scale_factor;  // float ctor arg -> double member
+  e->scale[0] = 1.0f; e->sigma2[0] = 1.0f;
+  for (int i = 1; i < c.nlevels; i++) {
+    e->scale[i]  = (float)(e->scale[i - 1] * scaleFactor);
+    e->sigma2[i] = e->scale[i] * e->scale[i];
+  }
+  for (int i = 0; i < c.nlevels; i++) {
+    e->inv_scale[i]  = 1.0f / e->scale[i];
+    e->inv_sigma2[i] = 1.0f / e->sigma2[i];
+  }
+  float factor = (float)(1.0f / scaleFactor);
+  float nDesired = (float)(c.nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)c.nlevels)));
+  int sum = 0;
+  for (int l = 0; l < c.nlevels - 1; l++) {
+    e->quota[l] = cv_round_f(nDesired);
+    sum += e->quota[l];
+    nDesired *= factor;
+  }
+  e->quota[c.nlevels - 1] = std::max(c.nfeatures - sum, 0);
+}
+
+// Per-size geometry.  Returns CUORB_OK or an error for sizes the reference has UB for.
+static int build_geometry(const cuorb_extractor* e, int w, int h, ExtractorGeom& g,
+                          std::vector<ResizeTap>& xtab, std::vector<ResizeTap>& ytab) {
+  const cuorb_config& c = e->cfg;
+  memset(&g, 0, sizeof(g));
+  g.nlevels = c.nlevels; g.ini_th = c.ini_th_fast; g.min_th = c.min_th_fast;
+  xtab.clear(); ytab.clear();
+  size_t pyr_off = 0, blur_off = 0, cand_off = 0;
+  int key_off = 0, cell_base = 0;
+  for (int l = 0; l < c.nlevels; l++) {
+    LevelGeom& L = g.lv[l];
+    const float s = e->inv_scale[l];
+    L.w = cv_round_f((float)w * s);  // :1143
+    L.h = cv_round_f((float)h * s);
+    L.scale = e->scale[l]; L.inv_scale = s;
+    L.kp_size = (float)(int)(PATCH_SIZE * e->scale[l]);  // :865
+    if (L.w <= 2 * EDGE_THRESHOLD || L.h <= 2 * EDGE_THRESHOLD) {
+      set_error("pyramid level too small for the 19-px border / FAST region");
+      return CUORB_E_UNSUPPORTED;
+    }
+    L.pitch     = (int)align_up((size_t)ROW_LEAD + L.w + EDGE_THRESHOLD, 64);
+    L.plane_off = pyr_off;
+    L.pix_off   = pyr_off + (size_t)EDGE_THRESHOLD * L.pitch + ROW_LEAD;
+    pyr_off += align_up((size_t)L.pitch * (L.h + 2 * EDGE_THRESHOLD), 256);
+    L.bpitch   = (int)align_up((size_t)L.w, 16);
+    L.blur_off = blur_off;
+    blur_off += align_up((size_t)L.bpitch * L.h, 256);
+    // FAST cells (:761-775)
+    L.maxBorderX = L.w - EDGE_THRESHOLD + 3;
+    L.maxBorderY = L.h - EDGE_THRESHOLD + 3;
+    const float width = (float)(L.maxBorderX - FAST_BORDER), height = (float)(L.maxBorderY - FAST_BORDER);
+    L.nCols = (int)(width / 35.f);
+    L.nRows = (int)(height / 35.f);
+    if (L.nCols <= 0 || L.nRows <= 0) {
+      set_error("pyramid level smaller than one 35-px FAST cell (division by zero in the reference)");
+      return CUORB_E_UNSUPPORTED;
+    }
+    L.wCell = (int)std::ceil(width / L.nCols);
+    L.hCell = (int)std::ceil(height / L.nRows);
+    L.cell_base = cell_base;
+    cell_base += L.nCols * L.nRows;
+    g.max_cell_w = std::max(g.max_cell_w, L.wCell);
+    g.max_cell_h = std::max(g.max_cell_h, L.hCell);
+    // octree roots (:566-568)
+    L.quota = e->quota[l];
+    L.nIni  = (int)std::round(width / height);
+    if (L.nIni <= 0) {
+      set_error("portrait image with aspect < 0.5: nIni == 0 (division by zero in the reference)");
+      return CUORB_E_UNSUPPORTED;
+    }
+    L.hX       = width / L.nIni;
+    L.node_cap = std::max(L.quota, 4 * L.nIni) + 8;
+    L.key_cap  = L.node_cap;
+    L.key_off  = key_off;
+    key_off += L.key_cap;
+    // worst case of strict 8-neighbour local maxima: one per 2x2 block of each cell
+    L.cand_cap = L.nCols * L.nRows * ((L.wCell + 1) / 2) * ((L.hCell + 1) / 2);
+    L.cand_off = cand_off;
+    cand_off += align_up((size_t)L.cand_cap, 32);
+    if (L.w + 2 * EDGE_THRESHOLD >= 4096 || L.h + 2 * EDGE_THRESHOLD >= 4096 || L.node_cap >= 32767) {
+      set_error("image or feature count beyond the packed 12-bit coordinate / 15-bit node range");
+      return CUORB_E_UNSUPPORTED;
+    }
+    // resize tables (OpenCV resize.cpp: scale = 1/(dst/src) in double, float fx, 11-bit weights)
+    L.xtab_off = (int)xtab.size();
+    L.ytab_off = (int)ytab.size();
+    if (l > 0) {
+      const LevelGeom& S = g.lv[l - 1];
+      if (S.w == 2 * L.w && S.h == 2 * L.h) {
+        set_error("exact 2x decimation: cv::resize switches INTER_LINEAR to INTER_AREA (not implemented)");
+        return CUORB_E_UNSUPPORTED;
+      }
+      const double scale_x = 1. / ((double)L.w / S.w), scale_y = 1. / ((double)L.h / S.h);
+      for (int dx = 0; dx < L.w; dx++) {
+        float fx = (float)((dx + 0.5) * scale_x - 0.5);
+        int sx = (int)std::floor(fx);
+        fx -= sx;
+        if (sx < 0) { fx = 0; sx = 0; }
+        if (sx >= S.w - 1) { fx = 0; sx = S.w - 1; }
+        xtab.push_back(ResizeTap{(short)sx, sat_short((1.f - fx) * 2048.f), sat_short(fx * 2048.f), 0});
+      }
+      for (int dy = 0; dy < L.h; dy++) {
+        float fy = (float)((dy + 0.5) * scale_y - 0.5);
+        int sy = (int)std::floor(fy);
+        fy -= sy;
+        ytab.push_back(ResizeTap{(short)sy, sat_short((1.f - fy) * 2048.f), sat_short(fy * 2048.f), 0});
+      }
+    }
+  }
+  g.total_cells     = cell_base;
+  g.kp_cap          = key_off;
+  g.key_img_stride  = key_off;
+  g.pyr_img_stride  = pyr_off;
+  g.blur_img_stride = blur_off;
+  g.cand_img_stride = cand_off;
+  if (g.kp_cap >= 65536) { set_error("more than 65535 keypoints per image"); return CUORB_E_UNSUPPORTED; }
+  return CUORB_OK;
+}
+
+}  // namespace cuorb
+
+// ------------------------------------------------------------------------------------------
+// handle lifetime
+// ------------------------------------------------------------------------------------------
+namespace cuorb {
+
+template <typename T>
+static cudaError_t dev_alloc(T** p, size_t count) {
+  return cudaMalloc((void**)p, std::max<size_t>(count, 1) * sizeof(T));
+}
+
+static void free_all(cuorb_extractor* e) {
+  cudaSetDevice(e->cfg.device);
+  void* dev[] = {e->d_geom, e->d_xtab, e->d_ytab, e->d_blur_tiles, e->d_input, e->d_pyr, e->d_blur,
+                 e->d_cand, e->d_cand_scratch, e->d_cand_count, e->d_key_count, e->d_flags, e->d_slot,
+                 e->d_keys, e->d_out_kps, e->d_out_desc, e->d_out_n, e->d_out_mono, e->d_uright,
+                 e->d_depth, e->d_sad, e->d_best_idx, e->d_best_dist};
+  for (void* p : dev) if (p) cudaFree(p);
+  void* host[] = {e->h_out_n, e->h_out_mono, e->h_flags};
+  for (void* p : host) if (p) cudaFreeHost(p);
+  for (auto& ev : e->ev_stage) if (ev) cudaEventDestroy(ev);
+  if (e->ev_done) cudaEventDestroy(e->ev_done);
+  if (e->stream) cudaStreamDestroy(e->stream);
+}
+
+// (re)build geometry for an image size and upload it; buffers were sized for the maximum
+static int set_size(cuorb_extractor* e, int w, int h) {
+  if (w == e->cur_w && h == e->cur_h) return CUORB_OK;
+  if (w > e->cfg.max_width || h > e->cfg.max_height) {
+    set_error("image larger than max_width x max_height given to cuorb_extractor_create");
+    return CUORB_E_BADARG;
+  }
+  ExtractorGeom g;
+  std::vector<ResizeTap> xt, yt;
+  int rc = build_geometry(e, w, h, g, xt, yt);
+  if (rc != CUORB_OK) return rc;
+  std::vector<int4> tiles;
+  build_blur_tiles(g, tiles);
+  const size_t nb = (size_t)e->cfg.max_batch;
+  if (g.pyr_img_stride * nb + 4096 > e->cap_pyr || g.blur_img_stride * nb > e->cap_blur ||
+      g.cand_img_stride * nb > e->cap_cand || (size_t)g.key_img_stride * nb > e->cap_keys ||
+      (size_t)g.kp_cap * nb > e->cap_kp || xt.size() > e->cap_xtab || yt.size() > e->cap_ytab ||
+      tiles.size() > e->cap_tiles) {
+    set_error("internal: geometry of this size exceeds the arena sized for max_width x max_height");
+    return CUORB_E_CAPACITY;
+  }
+  // the previous geometry may still be in use by enqueued work
+  CUORB_CUDA_TRY(cudaStreamSynchronize(e->stream));
+  CUORB_CUDA_TRY(cudaMemcpy(e->d_geom, &g, sizeof(g), cudaMemcpyHostToDevice));
+  if (!xt.empty()) CUORB_CUDA_TRY(cudaMemcpy(e->d_xtab, xt.data(), xt.size() * sizeof(ResizeTap), cudaMemcpyHostToDevice));
+  if (!yt.empty()) CUORB_CUDA_TRY(cudaMemcpy(e->d_ytab, yt.data(), yt.size() * sizeof(ResizeTap), cudaMemcpyHostToDevice));
+  CUORB_CUDA_TRY(cudaMemcpy(e->d_blur_tiles, tiles.data(), tiles.size() * sizeof(int4), cudaMemcpyHostToDevice));
+  e->n_blur_tiles = (int)tiles.size();
+  e->g = g; e->cur_w = w; e->cur_h = h;
+  e->have_batch = false; e->have_stereo = false;
+  return CUORB_OK;
+}
+
+}  // namespace cuorb
+
+extern "C" {
+
+const char* cuorb_last_error(void) { return t_last_error.c_str(); }
+int cuorb_version(void) { return CUORB_VERSION; }
+int cuorb_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { set_error("cudaGetDeviceCount failed (no CUDA device / driver)"); return 0; }
+  return n;
+}
+uint64_t cuorb_kernel_launch_count(void) { return g_launch_count.load(); }
+
+void* cuorb_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (cudaMallocHost(&p, bytes) != cudaSuccess) { set_error("cudaMallocHost failed"); return nullptr; }
+  return p;
+}
+void cuorb_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+cuorb_extractor* cuorb_extractor_create(const cuorb_config* cfg) {
+  if (!cfg || cfg->nlevels < 1 || cfg->nlevels > CUORB_MAX_LEVELS || cfg->nfeatures < 1 ||
+      cfg->scale_factor <= 1.0f || cfg->max_width < 1 || cfg->max_height < 1 || cfg->max_batch < 1 ||
+      cfg->max_batch > 65535) {
+    set_error("cuorb_extractor_create: bad configuration");
+    return nullptr;
+  }
+  if (cudaSetDevice(cfg->device) != cudaSuccess) {
+    set_error("cuorb_extractor_create: cudaSetDevice failed (no usable CUDA device; there is no CPU fallback)");
+    return nullptr;
+  }
+  cuorb_extractor* e = new cuorb_extractor();
+  e->cfg = *cfg;
+  build_tables(e);
+  ExtractorGeom g;
+  std::vector<ResizeTap> xt, yt;
+  if (build_geometry(e, cfg->max_width, cfg->max_height, g, xt, yt) != CUORB_OK) { delete e; return nullptr; }
+  std::vector<int4> tiles;
+  build_blur_tiles(g, tiles);
+  const size_t nb = (size_t)cfg->max_batch;
+  e->cap_input = (size_t)cfg->max_width * cfg->max_height * nb;
+  e->cap_pyr   = g.pyr_img_stride * nb + 4096;  // slack: tile loaders may read a few bytes past a plane
+  e->cap_blur  = g.blur_img_stride * nb + 256;
+  e->cap_cand  = g.cand_img_stride * nb;
+  e->cap_keys  = (size_t)g.key_img_stride * nb;
+  e->cap_kp    = (size_t)g.kp_cap * nb;
+  e->cap_xtab  = xt.size() + 64; e->cap_ytab = yt.size() + 64; e->cap_tiles = tiles.size() + 64;
+  bool ok = true;
+  ok &= cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess;
+  ok &= cudaEventCreateWithFlags(&e->ev_done, cudaEventDisableTiming) == cudaSuccess;
+  for (auto& ev : e->ev_stage) ok &= cudaEventCreate(&ev) == cudaSuccess;
+  ok &= dev_alloc(&e->d_geom, 1) == cudaSuccess;
+  ok &= dev_alloc(&e->d_xtab, e->cap_xtab) == cudaSuccess;
+  ok &= dev_alloc(&e->d_ytab, e->cap_ytab) == cudaSuccess;
+  ok &= dev_alloc(&e->d_blur_tiles, e->cap_tiles) == cudaSuccess;
+  ok &= dev_alloc(&e->d_input, e->cap_input) == cudaSuccess;
+  ok &= dev_alloc(&e->d_pyr, e->cap_pyr) == cudaSuccess;
+  ok &= dev_alloc(&e->d_blur, e->cap_blur) == cudaSuccess;
+  ok &= dev_alloc(&e->d_cand, e->cap_cand) == cudaSuccess;
+  ok &= dev_alloc(&e->d_cand_scratch, 2 * e->cap_cand) == cudaSuccess;
+  ok &= dev_alloc(&e->d_cand_count, nb * MAX_LEVELS) == cudaSuccess;
+  ok &= dev_alloc(&e->d_key_count, nb * MAX_LEVELS) == cudaSuccess;
+  ok &= dev_alloc(&e->d_flags, 1) == cudaSuccess;
+  ok &= dev_alloc(&e->d_slot, e->cap_kp) == cudaSuccess;
+  ok &= dev_alloc(&e->d_keys, e->cap_keys) == cudaSuccess;
+  ok &= dev_alloc(&e->d_out_kps, e->cap_kp) == cudaSuccess;
+  ok &= dev_alloc(&e->d_out_desc, e->cap_kp * 32) == cudaSuccess;
+  ok &= dev_alloc(&e->d_out_n, nb) == cudaSuccess;
+  ok &= dev_alloc(&e->d_out_mono, nb) == cudaSuccess;
+  ok &= dev_alloc(&e->d_uright, e->cap_kp) == cudaSuccess;
+  ok &= dev_alloc(&e->d_depth, e->cap_kp) == cudaSuccess;
+  ok &= dev_alloc(&e->d_sad, e->cap_kp) == cudaSuccess;
+  ok &= dev_alloc(&e->d_best_idx, e->cap_kp) == cudaSuccess;
+  ok &= dev_alloc(&e->d_best_dist, e->cap_kp) == cudaSuccess;
+  ok &= cudaMallocHost((void**)&e->h_out_n, nb * sizeof(int)) == cudaSuccess;
+  ok &= cudaMallocHost((void**)&e->h_out_mono, nb * sizeof(int)) == cudaSuccess;
+  ok &= cudaMallocHost((void**)&e->h_flags, sizeof(int)) == cudaSuccess;
+  ok = ok && init_describe_constants() == 0;
+  if (ok) ok = cudaMemset(e->d_pyr, 0, e->cap_pyr) == cudaSuccess;
+  if (!ok || set_size(e, cfg->max_width, cfg->max_height) != CUORB_OK) {
+    if (!ok) set_error(std::string("cuorb_extractor_create: CUDA allocation/initialisation failed: ") +
+                       cudaGetErrorString(cudaGetLastError()));
+    free_all(e);
+    delete e;
+    return nullptr;
+  }
+  return e;
+}
+
+void cuorb_extractor_destroy(cuorb_extractor* e) {
+  if (!e) return;
+  cudaSetDevice(e->cfg.device);
+  if (e->stream) cudaStreamSynchronize(e->stream);
+  free_all(e);
+  delete e;
+}
+
+int cuorb_extractor_get_tables(const cuorb_extractor* e, float* scale, float* inv_scale, float* sigma2,
+                               float* inv_sigma2, int32_t* per_level) {
+  if (!e) { set_error("null handle"); return CUORB_E_BADARG; }
+  for (int i = 0; i < e->cfg.nlevels; i++) {
+    if (scale) scale[i] = e->scale[i];
+    if (inv_scale) inv_scale[i] = e->inv_scale[i];
+    if (sigma2) sigma2[i] = e->sigma2[i];
+    if (inv_sigma2) inv_sigma2[i] = e->inv_sigma2[i];
+    if (per_level) per_level[i] = e->quota[i];
+  }
+  return e->cfg.nlevels;
+}
+
+int cuorb_extractor_capacity(const cuorb_extractor* e) {
+  if (!e) { set_error("null handle"); return CUORB_E_BADARG; }
+  return e->g.kp_cap;
+}
+
+int cuorb_set_profiling(cuorb_extractor* e, int enabled) {
+  if (!e) { set_error("null handle"); return CUORB_E_BADARG; }
+  e->profiling = enabled != 0;
+  return CUORB_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// extraction
+// ------------------------------------------------------------------------------------------
+namespace cuorb {
+static int check_flags(cuorb_extractor* e) {
+  const int f = *e->h_flags;
+  if (f & FLAG_CAND_OVERFLOW) { set_error("internal FAST candidate list overflow"); return CUORB_E_CAPACITY; }
+  if (f & (FLAG_NODE_OVERFLOW | FLAG_KEY_OVERFLOW)) { set_error("internal quadtree node pool overflow"); return CUORB_E_CAPACITY; }
+  return CUORB_OK;
+}
+}  // namespace cuorb
+
+extern "C" {
+
+int cuorb_extract_batch_async(cuorb_extractor* e, int n_images, const uint8_t* imgs, int width,
+                              int height, size_t stride, size_t image_stride, cuorb_mem where,
+                              int lap0, int lap1) {
+  if (!e) { set_error("null handle"); return CUORB_E_BADARG; }
+  if (!imgs || width <= 0 || height <= 0 || n_images <= 0) { set_error("empty image"); return CUORB_E_EMPTY; }
+  if (n_images > e->cfg.max_batch || stride < (size_t)width) { set_error("batch larger than max_batch or stride < width"); return CUORB_E_BADARG; }
+  CUORB_CUDA_TRY(cudaSetDevice(e->cfg.device));
+  int rc = set_size(e, width, height);
+  if (rc != CUORB_OK) return rc;
+  cudaStream_t st = e->stream;
+  const bool prof = e->profiling;
+  if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_H2D], st);
+  const uint8_t* dimgs = imgs;
+  size_t dstride = stride, dimg_stride = image_stride;
+  if (where == CUORB_MEM_HOST) {
+    if (stride == (size_t)width && (n_images == 1 || image_stride == (size_t)width * height)) {
+      CUORB_CUDA_TRY(cudaMemcpyAsync(e->d_input, imgs, (size_t)width * height * n_images, cudaMemcpyHostToDevice, st));
+    } else {
+      for (int i = 0; i < n_images; i++)
+        CUORB_CUDA_TRY(cudaMemcpy2DAsync(e->d_input + (size_t)i * width * height, width, imgs + (size_t)i * image_stride,
+                                         stride, width, height, cudaMemcpyHostToDevice, st));
+    }
+    dimgs = e->d_input; dstride = width; dimg_stride = (size_t)width * height;
+  }
+  CUORB_CUDA_TRY(cudaMemsetAsync(e->d_cand_count, 0, sizeof(int) * (size_t)n_images * e->g.nlevels, st));
+  CUORB_CUDA_TRY(cudaMemsetAsync(e->d_flags, 0, sizeof(int), st));
+  if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_PYRAMID], st);
+  launch_pyramid(e->g, e->d_geom, dimgs, width, height, dstride, dimg_stride, n_images, e->d_pyr, e->d_xtab, e->d_ytab, st);
+  if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_FAST], st);
+  launch_fast(e->g, e->d_geom, n_images, e->d_pyr, e->d_cand, e->d_cand_count, e->d_flags, st);
+  if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_OCTREE], st);
+  launch_octree(e->g, e->d_geom, n_images, e->d_cand, e->d_cand_scratch, e->d_cand_count, e->d_keys,
+                e->d_key_count, e->d_flags, st);
+  if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_BLUR], st);
+  launch_blur(&e->g, e->d_geom, n_images, e->d_blur_tiles, e->n_blur_tiles, e->d_pyr, e->d_blur, st);
+  if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_DESCRIBE], st);
+  launch_describe(e->g, e->d_geom, n_images, e->d_pyr, e->d_blur, e->d_keys, e->d_key_count, lap0, lap1,
+                  e->d_slot, e->d_out_kps, e->d_out_desc, e->d_out_n, e->d_out_mono, st);
+  if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_STEREO], st);
+  CUORB_CUDA_TRY(cudaGetLastError());
+  CUORB_CUDA_TRY(cudaEventRecord(e->ev_done, st));
+  e->n_img = n_images; e->have_batch = true; e->have_stereo = false;
+  e->have_stage_times = prof; e->stereo_timed = false;
+  return CUORB_OK;
+}
+
+int cuorb_extract_fetch_async(cuorb_extractor* e, cuorb_keypoint* kps, uint8_t* desc, int capacity,
+                              int32_t* n_out, int32_t* mono_out) {
+  if (!e) { set_error("null handle"); return CUORB_E_BADARG; }
+  if (!e->have_batch) { set_error("fetch before extract"); return CUORB_E_STATE; }
+  if ((kps || desc) && capacity <= 0) { set_error("capacity <= 0"); return CUORB_E_BADARG; }
+  CUORB_CUDA_TRY(cudaSetDevice(e->cfg.device));
+  cudaStream_t st = e->stream;
+  const int n = e->n_img, cap = e->g.kp_cap, cw = std::min(capacity, cap);
+  CUORB_CUDA_TRY(cudaMemcpyAsync(e->h_out_n, e->d_out_n, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
+  CUORB_CUDA_TRY(cudaMemcpyAsync(e->h_out_mono, e->d_out_mono, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
+  CUORB_CUDA_TRY(cudaMemcpyAsync(e->h_flags, e->d_flags, sizeof(int), cudaMemcpyDeviceToHost, st));
+  if (n_out) CUORB_CUDA_TRY(cudaMemcpyAsync(n_out, e->d_out_n, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
+  if (mono_out) CUORB_CUDA_TRY(cudaMemcpyAsync(mono_out, e->d_out_mono, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
+  if (kps)
+    CUORB_CUDA_TRY(cudaMemcpy2DAsync(kps, (size_t)capacity * sizeof(cuorb_keypoint), e->d_out_kps,
+                                     (size_t)cap * sizeof(cuorb_keypoint), (size_t)cw * sizeof(cuorb_keypoint), n,
+                                     cudaMemcpyDeviceToHost, st));
+  if (desc)
+    CUORB_CUDA_TRY(cudaMemcpy2DAsync(desc, (size_t)capacity * 32, e->d_out_desc, (size_t)cap * 32, (size_t)cw * 32, n,
+                                     cudaMemcpyDeviceToHost, st));
+  return n;
+}
+
+int cuorb_sync(cuorb_extractor* e) {
+  if (!e) { set_error("null handle"); return CUORB_E_BADARG; }
+  CUORB_CUDA_TRY(cudaSetDevice(e->cfg.device));
+  CUORB_CUDA_TRY(cudaStreamSynchronize(e->stream));
+  return CUORB_OK;
+}
+
+int cuorb_extract_fetch(cuorb_extractor* e, cuorb_keypoint* kps, uint8_t* desc, int capacity,
+                        int32_t* n_out, int32_t* mono_out) {
+  int n = cuorb_extract_fetch_async(e, kps, desc, capacity, n_out, mono_out);
+  if (n < 0) return n;
+  int rc = cuorb_sync(e);
+  if (rc != CUORB_OK) return rc;
+  rc = check_flags(e);
+  if (rc != CUORB_OK) return rc;
+  if (kps || desc)
+    for (int i = 0; i < n; i++)
+      if (e->h_out_n[i] > capacity) { set_error("caller capacity smaller than the keypoint count"); return CUORB_E_CAPACITY; }
+  return n;
+}
+
+int cuorb_extract(cuorb_extractor* e, const uint8_t* img, int width, int height, size_t stride,
+                  int lap0, int lap1, cuorb_keypoint* kps, uint8_t* desc, int capacity, int* n_out) {
+  int rc = cuorb_extract_batch_async(e, 1, img, width, height, stride, stride * (size_t)height, CUORB_MEM_HOST, lap0, lap1);
+  if (rc != CUORB_OK) return rc;
+  int32_t n = 0, mono = 0;
+  rc = cuorb_extract_fetch(e, kps, desc, capacity, &n, &mono);
+  if (n_out) *n_out = n;
+  if (rc < 0) return rc;
+  return mono;
+}
+
+int cuorb_extractor_pyramid(const cuorb_extractor* e, int image_index, int level, const uint8_t** dev_ptr,
+                            int* width, int* height, size_t* stride) {
+  if (!e || !e->have_batch || image_index < 0 || image_index >= e->n_img || level < 0 || level >= e->g.nlevels) {
+    set_error("cuorb_extractor_pyramid: bad handle / index, or no batch extracted yet");
+    return CUORB_E_BADARG;
+  }
+  const LevelGeom& L = e->g.lv[level];
+  if (dev_ptr) *dev_ptr = e->d_pyr + (size_t)image_index * e->g.pyr_img_stride + L.pix_off;
+  if (width) *width = L.w;
+  if (height) *height = L.h;
+  if (stride) *stride = (size_t)L.pitch;
+  return CUORB_OK;
+}
+
+int64_t cuorb_extractor_download_plane(cuorb_extractor* e, int image_index, int level, int plane,
+                                       uint8_t* out, size_t out_bytes, int* width, int* height) {
+  if (!e || !e->have_batch || image_index < 0 || image_index >= e->n_img || level < 0 ||
+      level >= e->g.nlevels || plane < 0 || plane > 2 || !out) {
+    set_error("cuorb_extractor_download_plane: bad argument");
+    return CUORB_E_BADARG;
+  }
+  CUORB_CUDA_TRY(cudaSetDevice(e->cfg.device));
+  const LevelGeom& L = e->g.lv[level];
+  if (width) *width = L.w;
+  if (height) *height = L.h;
+  const int B = EDGE_THRESHOLD;
+  const size_t ow = plane == 0 ? L.w + 2 * B : L.w, oh = plane == 0 ? L.h + 2 * B : L.h;
+  if (out_bytes < ow * oh) { set_error("output buffer too small"); return CUORB_E_CAPACITY; }
+  CUORB_CUDA_TRY(cudaStreamSynchronize(e->stream));
+  const uint8_t* src; size_t spitch;
+  if (plane == 0) { src = e->d_pyr + (size_t)image_index * e->g.pyr_img_stride + L.plane_off + (ROW_LEAD - B); spitch = L.pitch; }
+  else if (plane == 1) { src = e->d_pyr + (size_t)image_index * e->g.pyr_img_stride + L.pix_off; spitch = L.pitch; }
+  else { src = e->d_blur + (size_t)image_index * e->g.blur_img_stride + L.blur_off; spitch = L.bpitch; }
+  CUORB_CUDA_TRY(cudaMemcpy2D(out, ow, src, spitch, ow, oh, cudaMemcpyDeviceToHost));
+  return (int64_t)(ow * oh);
+}
+
+int cuorb_extractor_download_candidates(cuorb_extractor* e, int image_index, int level, int32_t* xs,
+                                        int32_t* ys, int32_t* responses, int capacity) {
+  if (!e || !e->have_batch || image_index < 0 || image_index >= e->n_img || level < 0 || level >= e->g.nlevels) {
+    set_error("cuorb_extractor_download_candidates: bad argument");
+    return CUORB_E_BADARG;
+  }
+  // the device list is unordered (appended with atomics); sorted here into the reference's order
+  CUORB_CUDA_TRY(cudaSetDevice(e->cfg.device));
+  CUORB_CUDA_TRY(cudaStreamSynchronize(e->stream));
+  const LevelGeom& L = e->g.lv[level];
+  int cnt = 0;
+  CUORB_CUDA_TRY(cudaMemcpy(&cnt, e->d_cand_count + image_index * e->g.nlevels + level, sizeof(int), cudaMemcpyDeviceToHost));
+  cnt = std::min(cnt, L.cand_cap);
+  std::vector<unsigned> a(cnt);
+  if (cnt) {
+    CUORB_CUDA_TRY(cudaMemcpy(a.data(), e->d_cand + (size_t)image_index * e->g.cand_img_stride + L.cand_off,
+                              sizeof(unsigned) * cnt, cudaMemcpyDeviceToHost));
+  }
+  std::vector<unsigned long long> ord(cnt);
+  for (int i = 0; i < cnt; i++) {
+    const int x = cand_x(a[i]), y = cand_y(a[i]);
+    const unsigned long long cell = (unsigned long long)((y - 3) / L.hCell) * L.nCols + (x - 3) / L.wCell;
+    ord[i] = (cell << 40) | ((unsigned long long)y << 28) | ((unsigned long long)x << 16) | (unsigned long long)cand_s(a[i]);
+  }
+  std::sort(ord.begin(), ord.end());
+  for (int i = 0; i < cnt && i < capacity; i++) {
+    xs[i] = (int)((ord[i] >> 16) & 0xFFF); ys[i] = (int)((ord[i] >> 28) & 0xFFF); responses[i] = (int)(ord[i] & 0xFF);
+  }
+  return cnt;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// stereo association
+// ------------------------------------------------------------------------------------------
+extern "C" {
+
+int cuorb_stereo_match_batch_async(cuorb_extractor* l, cuorb_extractor* r, float mb, float mbf) {
+  if (!l || !r) { set_error("null handle"); return CUORB_E_BADARG; }
+  if (!l->have_batch || !r->have_batch || l->n_img != r->n_img) { set_error("stereo match needs one extracted batch of equal size on both handles"); return CUORB_E_STATE; }
+  if (l->cfg.device != r->cfg.device || l->cur_w != r->cur_w || l->cur_h != r->cur_h ||
+      l->g.nlevels != r->g.nlevels || l->g.kp_cap != r->g.kp_cap || l->cfg.scale_factor != r->cfg.scale_factor) {
+    set_error("stereo match needs two extractors with identical configuration on one device");
+    return CUORB_E_BADARG;
+  }
+  CUORB_CUDA_TRY(cudaSetDevice(l->cfg.device));
+  CUORB_CUDA_TRY(cudaStreamWaitEvent(l->stream, r->ev_done, 0));
+  StereoArgs a;
+  a.dgL = l->d_geom; a.pyrL = l->d_pyr; a.pyrR = r->d_pyr;
+  a.kpsL = l->d_out_kps; a.kpsR = r->d_out_kps; a.descL = l->d_out_desc; a.descR = r->d_out_desc;
+  a.nL = l->d_out_n; a.nR = r->d_out_n; a.kp_cap = l->g.kp_cap; a.n_img = l->n_img;
+  a.mb = mb; a.mbf = mbf; a.u_right = l->d_uright; a.depth = l->d_depth;
+  a.best_idx_r = l->d_best_idx; a.best_dist = l->d_best_dist; a.sad = l->d_sad;
+  launch_stereo(l->g, a, l->stream);
+  if (l->profiling) { cudaEventRecord(l->ev_stage[CUORB_STAGE_COUNT], l->stream); l->stereo_timed = true; }
+  CUORB_CUDA_TRY(cudaGetLastError());
+  CUORB_CUDA_TRY(cudaEventRecord(l->ev_done, l->stream));
+  l->have_stereo = true;
+  return CUORB_OK;
+}
+
+int cuorb_stereo_fetch_async(cuorb_extractor* l, float* u_right, float* depth, int capacity) {
+  if (!l) { set_error("null handle"); return CUORB_E_BADARG; }
+  if (!l->have_stereo) { set_error("stereo fetch before stereo match"); return CUORB_E_STATE; }
+  CUORB_CUDA_TRY(cudaSetDevice(l->cfg.device));
+  const int n = l->n_img, cap = l->g.kp_cap, cw = std::min(capacity, cap);
+  if (u_right) CUORB_CUDA_TRY(cudaMemcpy2DAsync(u_right, (size_t)capacity * 4, l->d_uright, (size_t)cap * 4, (size_t)cw * 4, n, cudaMemcpyDeviceToHost, l->stream));
+  if (depth) CUORB_CUDA_TRY(cudaMemcpy2DAsync(depth, (size_t)capacity * 4, l->d_depth, (size_t)cap * 4, (size_t)cw * 4, n, cudaMemcpyDeviceToHost, l->stream));
+  return n;
+}
+
+int cuorb_stereo_fetch(cuorb_extractor* l, float* u_right, float* depth, int capacity,
+                       int32_t* best_idx_r, int32_t* best_dist, int32_t* sad) {
+  int n = cuorb_stereo_fetch_async(l, u_right, depth, capacity);
+  if (n < 0) return n;
+  const int cap = l->g.kp_cap, cw = std::min(capacity, cap);
+  int32_t* dst[3] = {best_idx_r, best_dist, sad};
+  int* src[3] = {l->d_best_idx, l->d_best_dist, l->d_sad};
+  for (int k = 0; k < 3; k++)
+    if (dst[k]) CUORB_CUDA_TRY(cudaMemcpy2DAsync(dst[k], (size_t)capacity * 4, src[k], (size_t)cap * 4, (size_t)cw * 4, n, cudaMemcpyDeviceToHost, l->stream));
+  int rc = cuorb_sync(l);
+  return rc != CUORB_OK ? rc : n;
+}
+
+// Host-pointer form: uploads the caller's keypoints/descriptors into the handles' result slots
+// of image 0 (they normally already are there) and runs the same kernels.
+int cuorb_stereo_match(cuorb_extractor* l, cuorb_extractor* r, int n_left, const cuorb_keypoint* kps_left,
+                       const uint8_t* desc_left, int n_right, const cuorb_keypoint* kps_right,
+                       const uint8_t* desc_right, float mb, float mbf, float* u_right, float* depth) {
+  if (!l || !r || !u_right || !depth) { set_error("null argument"); return CUORB_E_BADARG; }
+  if (!l->have_batch || !r->have_batch) { set_error("stereo match needs the pyramids of a previous extract on both handles"); return CUORB_E_STATE; }
+  if (n_left < 0 || n_right < 0 || n_left > l->g.kp_cap || n_right > r->g.kp_cap) { set_error("keypoint count beyond handle capacity"); return CUORB_E_CAPACITY; }
+  CUORB_CUDA_TRY(cudaSetDevice(l->cfg.device));
+  if (n_left) {
+    CUORB_CUDA_TRY(cudaMemcpyAsync(l->d_out_kps, kps_left, sizeof(cuorb_keypoint) * n_left, cudaMemcpyHostToDevice, l->stream));
+    CUORB_CUDA_TRY(cudaMemcpyAsync(l->d_out_desc, desc_left, 32 * (size_t)n_left, cudaMemcpyHostToDevice, l->stream));
+  }
+  CUORB_CUDA_TRY(cudaMemcpyAsync(l->d_out_n, &n_left, sizeof(int), cudaMemcpyHostToDevice, l->stream));
+  if (n_right) {
+    CUORB_CUDA_TRY(cudaMemcpyAsync(r->d_out_kps, kps_right, sizeof(cuorb_keypoint) * n_right, cudaMemcpyHostToDevice, r->stream));
+    CUORB_CUDA_TRY(cudaMemcpyAsync(r->d_out_desc, desc_right, 32 * (size_t)n_right, cudaMemcpyHostToDevice, r->stream));
+  }
+  CUORB_CUDA_TRY(cudaMemcpyAsync(r->d_out_n, &n_right, sizeof(int), cudaMemcpyHostToDevice, r->stream));
+  CUORB_CUDA_TRY(cudaStreamSynchronize(l->stream));  // &n_left / &n_right are stack variables
+  CUORB_CUDA_TRY(cudaStreamSynchronize(r->stream));
+  CUORB_CUDA_TRY(cudaEventRecord(r->ev_done, r->stream));
+  const int saved_l = l->n_img, saved_r = r->n_img;
+  l->n_img = 1; r->n_img = 1;
+  int rc = cuorb_stereo_match_batch_async(l, r, mb, mbf);
+  if (rc == CUORB_OK) {
+    CUORB_CUDA_TRY(cudaMemcpyAsync(u_right, l->d_uright, 4 * (size_t)n_left, cudaMemcpyDeviceToHost, l->stream));
+    CUORB_CUDA_TRY(cudaMemcpyAsync(depth, l->d_depth, 4 * (size_t)n_left, cudaMemcpyDeviceToHost, l->stream));
+    rc = cuorb_sync(l);
+  }
+  l->n_img = saved_l; r->n_img = saved_r;
+  return rc;
+}
+
+int cuorb_stage_ms(cuorb_extractor* e, float* ms_out) {
+  if (!e || !ms_out) { set_error("null argument"); return CUORB_E_BADARG; }
+  if (!e->have_stage_times) { set_error("no profiled batch (call cuorb_set_profiling before extract)"); return CUORB_E_STATE; }
+  CUORB_CUDA_TRY(cudaSetDevice(e->cfg.device));
+  CUORB_CUDA_TRY(cudaStreamSynchronize(e->stream));
+  for (int s = 0; s < CUORB_STAGE_COUNT; s++) {
+    ms_out[s] = 0.f;
+    if (s == CUORB_STAGE_STEREO && !e->stereo_timed) continue;
+    CUORB_CUDA_TRY(cudaEventElapsedTime(&ms_out[s], e->ev_stage[s], e->ev_stage[s + 1]));
+  }
+  return CUORB_OK;
+}
+
+int cuorb_hamming256(const void* a, const void* b) {
+  const uint64_t* pa = (const uint64_t*)a; const uint64_t* pb = (const uint64_t*)b;
+  uint64_t x[4]; memcpy(x, pa, 32);
+  uint64_t y[4]; memcpy(y, pb, 32);
+  return __builtin_popcountll(x[0] ^ y[0]) + __builtin_popcountll(x[1] ^ y[1]) +
+         __builtin_popcountll(x[2] ^ y[2]) + __builtin_popcountll(x[3] ^ y[3]);
+}
+
+}  // extern "C"

@@ -1,0 +1,174 @@
+"""Host-side mirror of the tracking-time subset of class ORB_SLAM3::ORBmatcher (reference
+include/ORBmatcher.h:35-158) and of Frame::ComputeStereoMatches (include/Frame.h:155), over the
+libcuorb C ABI.  `Frame` / `MapPointSoA` are the flattened views of the reference's pointer graph
+that its C++ shim would build.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import _lib
+from ._lib import KP_DTYPE, check, ptr
+
+FRAME_GRID_ROWS, FRAME_GRID_COLS = 48, 64  # include/Frame.h:36-37
+
+
+@dataclass
+class Frame:
+    """The Frame members the matchers read (pinhole / Nleft == -1)."""
+    mvKeysUn: np.ndarray            # KP_DTYPE [N]
+    mDescriptors: np.ndarray        # u8 [N, 32]
+    mvScaleFactors: np.ndarray      # f32 [nlevels]
+    width: int
+    height: int
+    mvuRight: np.ndarray | None = None     # f32 [N], -1 = none
+    mb: float = 0.0
+    mbf: float = 0.0
+    mnMinX: float = 0.0
+    mnMinY: float = 0.0
+    mnMaxX: float | None = None
+    mnMaxY: float | None = None
+    # mvpMapPoints: index of the bound MapPoint (-1 = NULL) and whether it has Observations() > 0
+    mvpMapPoints: np.ndarray = field(default=None)
+    mvpHasObs: np.ndarray = field(default=None)
+
+    def __post_init__(self):
+        self.mvKeysUn = np.ascontiguousarray(self.mvKeysUn, KP_DTYPE)
+        self.mDescriptors = np.ascontiguousarray(self.mDescriptors, np.uint8)
+        self.mvScaleFactors = np.ascontiguousarray(self.mvScaleFactors, np.float32)
+        self.N = len(self.mvKeysUn)
+        if self.mnMaxX is None: self.mnMaxX = float(self.width)
+        if self.mnMaxY is None: self.mnMaxY = float(self.height)
+        if self.mvpMapPoints is None: self.mvpMapPoints = np.full(self.N, -1, np.int64)
+        if self.mvpHasObs is None: self.mvpHasObs = np.zeros(self.N, np.uint8)
+        if self.mvuRight is not None:
+            self.mvuRight = np.ascontiguousarray(self.mvuRight, np.float32)
+
+    def view(self):
+        """cuorb_frame_view + keepalive (src/Frame.cc:240-257 for the grid constants)."""
+        f32 = np.float32
+        bound = np.ascontiguousarray(((self.mvpMapPoints >= 0) & (self.mvpHasObs > 0)).astype(np.uint8))
+        fv = _lib.FrameView()
+        fv.n = self.N
+        fv.keys_un = ptr(self.mvKeysUn); fv.descriptors = ptr(self.mDescriptors)
+        fv.u_right = ptr(self.mvuRight); fv.bound_with_obs = ptr(bound)
+        fv.min_x, fv.min_y, fv.max_x, fv.max_y = self.mnMinX, self.mnMinY, self.mnMaxX, self.mnMaxY
+        fv.grid_w_inv = float(f32(FRAME_GRID_COLS) / f32(f32(self.mnMaxX) - f32(self.mnMinX)))
+        fv.grid_h_inv = float(f32(FRAME_GRID_ROWS) / f32(f32(self.mnMaxY) - f32(self.mnMinY)))
+        fv.mb, fv.mbf = self.mb, self.mbf
+        fv.nlevels = len(self.mvScaleFactors)
+        fv.scale_factors = ptr(self.mvScaleFactors)
+        return fv, bound
+
+
+@dataclass
+class MapPointSoA:
+    """Per-MapPoint fields SearchByProjection reads (src/ORBmatcher.cc:50-111), flattened."""
+    descriptor: np.ndarray     # u8 [M, 32]   GetDescriptor()
+    mTrackProjX: np.ndarray    # f32 [M]
+    mTrackProjY: np.ndarray
+    mTrackProjXR: np.ndarray
+    mnTrackScaleLevel: np.ndarray  # i32 [M]
+    mTrackViewCos: np.ndarray
+    mTrackDepth: np.ndarray
+    mbTrackInView: np.ndarray  # bool [M]
+    isBad: np.ndarray          # bool [M]
+    hasObservations: np.ndarray  # bool [M]  Observations() > 0
+
+    def flags(self):
+        return (np.asarray(self.mbTrackInView, np.uint8) * _lib.MP_IN_VIEW |
+                np.asarray(self.isBad, np.uint8) * _lib.MP_BAD |
+                np.asarray(self.hasObservations, np.uint8) * _lib.MP_HAS_OBS).astype(np.uint8)
+
+
+def _c(a, dt):
+    return np.ascontiguousarray(a, dt)
+
+
+class ORBmatcher:
+    TH_HIGH, TH_LOW, HISTO_LENGTH = 100, 50, 30  # src/ORBmatcher.cc:30-32
+
+    def __init__(self, nnratio=0.6, checkOri=True, device=0):
+        self._L = _lib.load()
+        self.mfNNratio, self.mbCheckOrientation, self.device = float(nnratio), bool(checkOri), int(device)
+
+    # static int DescriptorDistance(const cv::Mat&, const cv::Mat&) — include/ORBmatcher.h:40
+    @staticmethod
+    def DescriptorDistance(a, b) -> int:
+        a = _c(a, np.uint8); b = _c(b, np.uint8)
+        assert a.size == 32 and b.size == 32
+        return _lib.load().cuorb_hamming256(ptr(a), ptr(b))
+
+    def DescriptorDistanceBatch(self, a, b, ia=None, ib=None):
+        a = _c(a, np.uint8).reshape(-1, 32); b = _c(b, np.uint8).reshape(-1, 32)
+        ia = None if ia is None else _c(ia, np.int32); ib = None if ib is None else _c(ib, np.int32)
+        n = len(ia) if ia is not None else (len(ib) if ib is not None else min(len(a), len(b)))
+        out = np.zeros(n, np.int32)
+        check(self._L.cuorb_hamming_batch(self.device, ptr(a), len(a), ptr(b), len(b), ptr(ia), ptr(ib), n, ptr(out)))
+        return out
+
+    # Frame::ComputeStereoMatches (src/Frame.cc:944-1113); "SearchStereo" in BASELINE.json
+    def SearchStereo(self, extractorLeft, extractorRight, mb, mbf, debug=False):
+        """Device-resident: matches the last batch of the two extractors.  Returns
+        (mvuRight[n, cap], mvDepth[n, cap]) (+ dict of debug arrays)."""
+        check(self._L.cuorb_stereo_match_batch_async(extractorLeft.handle, extractorRight.handle, mb, mbf))
+        n, cap = extractorLeft._n_last, extractorLeft.capacity
+        u = np.zeros((n, cap), np.float32); d = np.zeros((n, cap), np.float32)
+        if not debug:
+            check(self._L.cuorb_stereo_fetch(extractorLeft.handle, ptr(u), ptr(d), cap, None, None, None))
+            return u, d
+        bi, bd, sad = (np.zeros((n, cap), np.int32) for _ in range(3))
+        check(self._L.cuorb_stereo_fetch(extractorLeft.handle, ptr(u), ptr(d), cap, ptr(bi), ptr(bd), ptr(sad)))
+        return u, d, dict(best_idx_r=bi, best_dist=bd, sad=sad)
+
+    def ComputeStereoMatches(self, extractorLeft, extractorRight, mvKeys, mDescriptors, mvKeysRight,
+                             mDescriptorsRight, mb, mbf):
+        """Host-pointer form with the member set the reference method reads. Returns (mvuRight, mvDepth)."""
+        kl = _c(mvKeys, KP_DTYPE); kr = _c(mvKeysRight, KP_DTYPE)
+        dl = _c(mDescriptors, np.uint8); dr = _c(mDescriptorsRight, np.uint8)
+        u = np.zeros(len(kl), np.float32); d = np.zeros(len(kl), np.float32)
+        check(self._L.cuorb_stereo_match(extractorLeft.handle, extractorRight.handle, len(kl), ptr(kl), ptr(dl),
+                                         len(kr), ptr(kr), ptr(dr), mb, mbf, ptr(u), ptr(d)))
+        return u, d
+
+    # int SearchByProjection(Frame&, const vector<MapPoint*>&, th, bFarPoints, thFarPoints)
+    def SearchByProjection(self, F: Frame, mps: MapPointSoA, th=3.0, bFarPoints=False, thFarPoints=50.0):
+        fv, keep = F.view()
+        M = len(mps.mTrackProjX)
+        flags = mps.flags()
+        arrs = [_c(mps.descriptor, np.uint8), _c(mps.mTrackProjX, np.float32), _c(mps.mTrackProjY, np.float32),
+                _c(mps.mTrackProjXR, np.float32), _c(mps.mnTrackScaleLevel, np.int32),
+                _c(mps.mTrackViewCos, np.float32), _c(mps.mTrackDepth, np.float32), flags]
+        best = np.zeros(M, np.int32)
+        n = check(self._L.cuorb_search_by_projection(self.device, C.byref(fv), M, *[ptr(a) for a in arrs], th,
+                                                     int(bFarPoints), thFarPoints, self.mfNNratio, ptr(best)))
+        # replay F.mvpMapPoints[bestIdx] = pMP in MapPoint order (src/ORBmatcher.cc:137)
+        for i in np.nonzero(best >= 0)[0]:
+            F.mvpMapPoints[best[i]] = i
+            F.mvpHasObs[best[i]] = 1 if (flags[i] & _lib.MP_HAS_OBS) else 0
+        return n, best
+
+    # int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, th, bMono) with the
+    # projections of the last frame's MapPoints supplied by the caller (src/ORBmatcher.cc:1710-1721)
+    def SearchByProjectionLastFrame(self, Cur: Frame, last_desc, u, v, inv_z, last_octave, last_angle,
+                                    flags, th, bForward=False, bBackward=False):
+        fv, keep = Cur.view()
+        n_last = len(u)
+        flags = _c(flags, np.uint8)
+        arrs = [_c(last_desc, np.uint8), _c(u, np.float32), _c(v, np.float32), _c(inv_z, np.float32),
+                _c(last_octave, np.int32), _c(last_angle, np.float32), flags]
+        best = np.zeros(n_last, np.int32); rot = np.zeros(n_last, np.int32); keepb = np.zeros(3, np.int32)
+        n = check(self._L.cuorb_search_by_projection_frame(
+            self.device, C.byref(fv), n_last, *[ptr(a) for a in arrs], th, int(bForward), int(bBackward),
+            int(self.mbCheckOrientation), ptr(best), ptr(rot), ptr(keepb)))
+        for i in np.nonzero(best >= 0)[0]:           # bind in order (:1790)
+            Cur.mvpMapPoints[best[i]] = i
+            Cur.mvpHasObs[best[i]] = 1 if (flags[i] & _lib.MP_HAS_OBS) else 0
+        if self.mbCheckOrientation:                   # rotation consistency (:1889-1905)
+            for i in np.nonzero(best >= 0)[0]:
+                if rot[i] not in keepb:
+                    Cur.mvpMapPoints[best[i]] = -1
+        return n, best, rot, keepb
