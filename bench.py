@@ -1,0 +1,337 @@
+#!/usr/bin/env python
+"""bench.py — ORB extract + stereo match throughput (BASELINE.json metric) on N B200s.
+
+A "step" = one batch of synthetic 752x480 stereo pairs through the hot path: left + right
+ORBextractor::operator() (1000 features, 8 levels, 1.2, FAST 20/7) and Frame::ComputeStereoMatches.
+  value : frames/s with the frames already resident in HBM (results stay on the device)
+  e2e   : frames/s through the host-facing C ABI: pinned host frames -> H2D -> kernels -> D2H of
+          keypoints, descriptors, mvuRight, mvDepth, every step, double-buffered over two handle pairs
+  roofline : the dominant kernel stage (CUDA events on the launching stream) against measured HBM
+  cpu_baseline : the CPU oracle (port of the reference path) on the host cores, bounded sample
+--impl reference times that CPU path alone (rank 0 only).
+Frames are sharded across ranks with no collective (each rank: own GPU, own handles, own streams).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W, H, NFEAT = 752, 480, 1000
+FX, MBF = 458.654, 47.90639384423901  # EuRoC stereo: Camera.fx, Camera.bf (Examples_old/Stereo/EuRoC.yaml:40)
+MB = MBF / FX
+METRIC = "ORB extract+match frames/s @752x480,1000kp"
+
+
+def level_sizes(w, h, nlevels=8, sf=1.2):
+    s = np.float32(1.0)
+    out = []
+    for _ in range(nlevels):
+        inv = np.float32(1.0) / s
+        out.append((int(np.rint(np.float32(w) * inv)), int(np.rint(np.float32(h) * inv))))
+        s = np.float32(float(s) * float(np.float32(sf)))
+    return out
+
+
+def algorithmic_bytes(w, h):
+    """per-image algorithmic bytes of the three pixel stages."""
+    lv = level_sizes(w, h)
+    P = [a * b for a, b in lv]
+    B = [(a + 38) * (b + 38) for a, b in lv]
+    return dict(pyramid=sum(P[:-1]) + P[0] + sum(B), blur=2 * sum(P), fast=2 * sum(P))
+
+
+def make_pool(n_pairs, base=24):
+    """n_pairs distinct synthetic stereo pairs: `base` generated, the rest are horizontal rolls
+    (same roll on both eyes keeps the disparity field)."""
+    from orbslam3_cpp_fork_b200 import synth
+    Ls, Rs = [], []
+    for i in range(min(base, n_pairs)):
+        l, r = synth.synth_stereo_pair(W, H, 1000 + i)
+        Ls.append(l); Rs.append(r)
+    i = 0
+    while len(Ls) < n_pairs:
+        sh = 37 * (len(Ls) // base) + 11
+        Ls.append(np.roll(Ls[i % base], sh, axis=1)); Rs.append(np.roll(Rs[i % base], sh, axis=1))
+        i += 1
+    return np.stack(Ls), np.stack(Rs)
+
+
+class ClockSampler:
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+             "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.gpu), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=lambda: [self.lines.append(l) for l in self.proc.stdout], daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_baseline(n_threads, frames_per_thread=12):
+    """Oracle (CPU port of the reference path) on the host cores; bounded sample."""
+    from oracle import oracle_py as op
+    n = max(4, n_threads * frames_per_thread)
+    L, R = make_pool(min(n, 48))
+    reps = (n + len(L) - 1) // len(L)
+    L = np.concatenate([L] * reps)[:n]; R = np.concatenate([R] * reps)[:n]
+    op.bench_stereo(L[:n_threads], R[:n_threads], MB, MBF, n_threads)  # warm-up
+    sec, kps, matches = op.bench_stereo(L, R, MB, MBF, n_threads)
+    return n / sec, n, kps, matches
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    from oracle import oracle_py as op
+    per_step = max(4, 2 * cores)
+    L, R = make_pool(min(per_step, 48))
+    reps = (per_step + len(L) - 1) // len(L)
+    L = np.concatenate([L] * reps)[:per_step]; R = np.concatenate([R] * reps)[:per_step]
+    for _ in range(args.warmup):
+        op.bench_stereo(L, R, MB, MBF, cores)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        op.bench_stereo(L, R, MB, MBF, cores)
+    sec = time.perf_counter() - t0
+    fps = per_step * args.steps / sec
+    sample = f"{per_step} synthetic 752x480 stereo pairs per step x {args.steps} steps, {cores} std::threads (one frame each)"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sec / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "cfg5: 752x480 stereo pairs, 1000 features, 8 levels, 1.2, FAST 20/7; "
+                               "2x ORBextractor::operator() + Frame::ComputeStereoMatches per frame",
+                   "frames_per_step": per_step},
+        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def run_cuorb(args):
+    import torch
+    import torch.distributed as dist
+    from orbslam3_cpp_fork_b200 import ORBextractor, _lib
+    L_ = _lib.load()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; libcuorb has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    B = args.batch
+    Lh, Rh = make_pool(B)                       # host pool, distinct frames
+    in_bytes = Lh.nbytes + Rh.nbytes            # > L2 (126 MB) at the default batch: no L2 flush needed
+    # --- handles: two pairs for the double-buffered e2e path; pair 0 also serves the resident path
+    pairs = [(ORBextractor(NFEAT, 1.2, 8, 20, 7, max_width=W, max_height=H, max_batch=B, device=local),
+              ORBextractor(NFEAT, 1.2, 8, 20, 7, max_width=W, max_height=H, max_batch=B, device=local))
+             for _ in range(2)]
+    cap = pairs[0][0].capacity
+    Ld = torch.from_numpy(Lh).cuda(); Rd = torch.from_numpy(Rh).cuda()
+
+    def step_resident(eL, eR):
+        eL.extract_batch_async(Ld); eR.extract_batch_async(Rd)
+        _lib.check(L_.cuorb_stereo_match_batch_async(eL.handle, eR.handle, MB, MBF))
+
+    # ---------------- value: device-resident, CUDA events on the launching (left) stream ----------
+    eL, eR = pairs[0]
+    sL = torch.cuda.ExternalStream(eL.stream, device=local)
+    for _ in range(args.warmup):
+        step_resident(eL, eR)
+    eL.sync(); eR.sync()
+    sampler = ClockSampler(local); sampler.start()
+    barrier()
+    launches0 = L_.cuorb_kernel_launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(sL)
+    for _ in range(args.steps):
+        step_resident(eL, eR)
+    ev1.record(sL)
+    eL.sync(); eR.sync()
+    barrier()
+    launches = L_.cuorb_kernel_launch_count() - launches0
+    ms_resident = ev0.elapsed_time(ev1)
+    clocks = sampler.stop()
+
+    # ---------------- per-stage times (one profiled step, CUDA events inside libcuorb) -------------
+    eL.set_profiling(True); eR.set_profiling(True)
+    stage_acc = {}
+    for _ in range(3):
+        step_resident(eL, eR)
+        eL.sync(); eR.sync()
+        for k, v in eL.stage_ms().items():
+            stage_acc.setdefault(k, []).append(v)
+    eL.set_profiling(False); eR.set_profiling(False)
+    stage_ms = {k: float(np.median(v)) for k, v in stage_acc.items()}   # left handle: B images (+ stereo)
+
+    # ---------------- e2e: pinned host frames in, all results out, every step ----------------------
+    def pinned(shape, dtype):
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        p = L_.cuorb_host_alloc(n)
+        if not p:
+            raise RuntimeError(_lib.last_error())
+        buf = (ctypes.c_char * n).from_address(p)
+        return np.frombuffer(buf, dtype=dtype).reshape(shape)
+
+    import ctypes
+    hostL, hostR = pinned(Lh.shape, np.uint8), pinned(Rh.shape, np.uint8)
+    hostL[:] = Lh; hostR[:] = Rh
+    outs = []
+    for _ in range(2):
+        outs.append(dict(
+            kl=pinned((B, cap), _lib.KP_DTYPE), dl=pinned((B, cap, 32), np.uint8), nl=pinned((B,), np.int32), ml=pinned((B,), np.int32),
+            kr=pinned((B, cap), _lib.KP_DTYPE), dr=pinned((B, cap, 32), np.uint8), nr=pinned((B,), np.int32), mr=pinned((B,), np.int32),
+            u=pinned((B, cap), np.float32), d=pinned((B, cap), np.float32)))
+    d2h_bytes = sum(v.nbytes for v in outs[0].values())
+
+    def step_e2e(i):
+        eL, eR = pairs[i & 1]
+        o = outs[i & 1]
+        eL.sync(); eR.sync()                         # buffers of step i-2 are free again
+        eL.extract_batch_async(hostL); eR.extract_batch_async(hostR)
+        eR.fetch(o["kr"], o["dr"], o["nr"], o["mr"], sync=False)
+        _lib.check(L_.cuorb_stereo_match_batch_async(eL.handle, eR.handle, MB, MBF))
+        eL.fetch(o["kl"], o["dl"], o["nl"], o["ml"], sync=False)
+        _lib.check(L_.cuorb_stereo_fetch_async(eL.handle, _lib.ptr(o["u"]), _lib.ptr(o["d"]), cap))
+
+    for i in range(max(args.warmup, 2)):
+        step_e2e(i)
+    for p in pairs:
+        p[0].sync(); p[1].sync()
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        step_e2e(i)
+    for p in pairs:
+        p[0].sync(); p[1].sync()
+    torch.cuda.synchronize()
+    t_e2e = time.perf_counter() - t0
+    total_kp = int(outs[0]["nl"].sum() + outs[0]["nr"].sum())
+    total_matches = int((outs[0]["u"] >= 0).sum())
+
+    # ---------------- max over ranks ----------------
+    if world > 1:
+        t = torch.tensor([ms_resident, t_e2e], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_resident, t_e2e = float(t[0]), float(t[1])
+        ln = torch.tensor([launches], dtype=torch.int64, device="cuda")
+        dist.all_reduce(ln, op=dist.ReduceOp.SUM)
+        launches = int(ln[0])
+
+    if rank == 0:
+        frames = B * args.steps * world
+        value = frames / (ms_resident * 1e-3)
+        e2e = frames / t_e2e
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+        ab = algorithmic_bytes(W, H)
+        pix = {k: stage_ms[k] for k in ("pyramid", "blur", "fast")}
+        dom = max(pix, key=pix.get)
+        dom_all = max({k: v for k, v in stage_ms.items() if k != "h2d"}, key=lambda k: stage_ms[k])
+        ach = ab[dom] * B / (stage_ms[dom] * 1e-3) / 1e9
+        stage_gbs = {k: ab[k] * B / (stage_ms[k] * 1e-3) / 1e9 for k in pix}
+        cores = os.cpu_count() or 1
+        cpu_fps, cpu_n, _, _ = cpu_baseline(cores) if not args.no_cpu_baseline else (None, 0, 0, 0)
+        line = {
+            "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_resident / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "cfg5: 752x480 stereo pairs, 1000 features, 8 levels, 1.2, FAST 20/7; "
+                                   "2x ORBextractor::operator() + Frame::ComputeStereoMatches per frame",
+                       "frames_per_step_per_gpu": B, "parallelism": f"frame-sharded x{world}, no collective",
+                       "l2": f"inputs {in_bytes / 1e6:.0f} MB + pyramids per step exceed the 126 MB L2 (no flush needed)",
+                       "value_leg": "frames resident in HBM, results left in HBM",
+                       "keypoints_per_frame": total_kp / B, "stereo_matches_per_frame": total_matches / B},
+            "clocks": clocks,
+            "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": in_bytes * world,
+                    "d2h_bytes_per_step": d2h_bytes * world, "ms_per_step": 1e3 * t_e2e / args.steps},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
+                         "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                         "stage_ms_per_step": stage_ms, "stage_gbs": stage_gbs,
+                         "dominant_stage_overall": dom_all,
+                         "algorithmic_bytes_per_image": ab},
+            "cpu_baseline": None if cpu_fps is None else {
+                "value": cpu_fps, "unit": "frames/s", "cores": cores, "kind": "port",
+                "sample": f"{cpu_n} synthetic 752x480 stereo pairs, {cores} std::threads (one frame each), CPU oracle -O2"},
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="cuorb", choices=["cuorb", "reference"])
+    ap.add_argument("--batch", type=int, default=256, help="stereo pairs per step per GPU")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "cuorb" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_cuorb(args)
+
+
+if __name__ == "__main__":
+    main()

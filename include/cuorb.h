@@ -114,6 +114,9 @@ int cuorb_extract_fetch(cuorb_extractor* ext, cuorb_keypoint* kps, uint8_t* desc
 int cuorb_extract_fetch_async(cuorb_extractor* ext, cuorb_keypoint* kps, uint8_t* desc,
                               int capacity, int32_t* n_out, int32_t* mono_index_out);
 int cuorb_sync(cuorb_extractor* ext);
+/* The handle's cudaStream_t (as void*): lets a caller order its own work / record CUDA events
+ * (e.g. torch.cuda.ExternalStream) against the enqueued pipeline. */
+void* cuorb_extractor_stream(cuorb_extractor* ext);
 
 /* std::vector<cv::Mat> mvImagePyramid (include/ORBextractor.h:87; read by
  * Frame::ComputeStereoMatches, src/Frame.cc:950,1039,1056).  Device pointer to pixel (0,0) of

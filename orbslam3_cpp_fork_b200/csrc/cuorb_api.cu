@@ -357,6 +357,8 @@ int cuorb_extractor_capacity(const cuorb_extractor* e) {
   return e->g.kp_cap;
 }
 
+void* cuorb_extractor_stream(cuorb_extractor* e) { return e ? (void*)e->stream : nullptr; }
+
 int cuorb_set_profiling(cuorb_extractor* e, int enabled) {
   if (!e) { set_error("null handle"); return CUORB_E_BADARG; }
   e->profiling = enabled != 0;

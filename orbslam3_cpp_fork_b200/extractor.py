@@ -125,6 +125,11 @@ class ORBextractor:
         check(fn(self._h, ptr(kps), ptr(desc), kps.shape[1], ptr(counts), ptr(mono)))
         return counts, mono, kps, desc
 
+    @property
+    def stream(self) -> int:
+        """cudaStream_t of the handle (integer address), e.g. for torch.cuda.ExternalStream."""
+        return int(self._L.cuorb_extractor_stream(self._h) or 0)
+
     def sync(self):
         check(self._L.cuorb_sync(self._h))
 

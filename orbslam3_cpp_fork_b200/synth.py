@@ -35,10 +35,12 @@ def synth_image(w: int, h: int, seed: int, n_shapes: int = 320, noise: int = 2) 
         sw = int(rng.integers(6, 70)); sh = int(rng.integers(6, 70))
         x1 = min(w, x0 + sw); y1 = min(h, y0 + sh); x0 = max(0, x0); y0 = max(0, y0)
         g = float(rng.integers(0, 256))
+        c = int(rng.integers(4, 12))
+        if x1 <= x0 or y1 <= y0:
+            continue
         if kind < 3:
             img[y0:y1, x0:x1] = g
         else:  # checker patch
-            c = int(rng.integers(4, 12))
             yy, xx = np.mgrid[y0:y1, x0:x1]
             m = ((yy // c + xx // c) & 1).astype(bool)
             sub = img[y0:y1, x0:x1]

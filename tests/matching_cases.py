@@ -1,0 +1,80 @@
+"""Synthetic inputs for the matching paths, shared by CPU and GPU tests."""
+import numpy as np
+
+from oracle import oracle_py as op
+from orbslam3_cpp_fork_b200 import synth
+
+
+def flip_bits(desc, rng, kmax=40):
+    d = desc.copy()
+    for row in d:
+        k = int(rng.integers(0, kmax + 1))
+        pos = rng.choice(256, size=k, replace=False)
+        for p in pos:
+            row[p >> 3] ^= np.uint8(1 << (p & 7))
+    return d
+
+
+def extracted_frame(w=752, h=480, nf=1000, seed=31):
+    e = op.OracleExtractor(nf, 1.2, 8, 20, 7)
+    _, k, d = e.extract(synth.synth_image(w, h, seed))
+    return e, k, d
+
+
+def mappoint_case(k, d, scale_factors, M, seed, w=752, h=480, with_uright=False, dup_frac=0.1):
+    """cfg4: M MapPoints vs the frame (k, d). ~20% true matches (bit-flipped descriptors, jittered
+    projections), some duplicated targets (order-dependent conflicts), the rest distractors."""
+    rng = np.random.default_rng(seed)
+    N = len(k)
+    n_true = int(0.2 * M)
+    tgt = rng.integers(0, N, n_true)
+    n_dup = int(dup_frac * n_true)
+    tgt[:n_dup] = tgt[n_dup:2 * n_dup]                     # several MapPoints chase the same feature
+    desc = rng.integers(0, 256, (M, 32), dtype=np.uint8)
+    px = rng.uniform(0, w, M).astype(np.float32); py = rng.uniform(0, h, M).astype(np.float32)
+    level = rng.integers(0, 8, M).astype(np.int32)
+    sel = rng.permutation(M)[:n_true]
+    desc[sel] = flip_bits(d[tgt], rng)
+    oct_t = k["octave"][tgt]
+    level[sel] = np.minimum(oct_t + rng.integers(0, 2, n_true), 7)
+    rad = 2.5 * np.asarray(scale_factors)[level[sel]]
+    px[sel] = k["x"][tgt] + rng.uniform(-0.5, 0.5, n_true).astype(np.float32) * rad
+    py[sel] = k["y"][tgt] + rng.uniform(-0.5, 0.5, n_true).astype(np.float32) * rad
+    view_cos = np.where(rng.random(M) < 0.5, 0.9985, 0.9995).astype(np.float32)
+    depth = rng.uniform(1, 80, M).astype(np.float32)
+    in_view = rng.random(M) < 0.95
+    bad = rng.random(M) < 0.02
+    has_obs = rng.random(M) < 0.9
+    flags = (in_view * 1 + bad * 2 + has_obs * 4).astype(np.uint8)
+    u_right = None
+    pxr = (px - np.float32(40.0) / depth).astype(np.float32)
+    if with_uright:
+        u_right = np.where(rng.random(N) < 0.6, k["x"] - rng.uniform(1, 60, N), -1).astype(np.float32)
+        ok = u_right[tgt] > 0
+        pxr[sel] = np.where(ok, u_right[tgt] + rng.uniform(-3, 3, n_true), pxr[sel]).astype(np.float32)
+    bound = (rng.random(N) < 0.1).astype(np.uint8)         # features already bound on entry
+    return dict(desc=desc, px=px, py=py, pxr=pxr, level=level, view_cos=view_cos, depth=depth, flags=flags,
+                u_right=u_right, bound=bound)
+
+
+def lastframe_case(k, d, seed, w=752, h=480):
+    """SearchByProjection(Cur, Last): last-frame points projected near current features."""
+    rng = np.random.default_rng(seed)
+    N = len(k)
+    n = N + 200
+    tgt = rng.integers(0, N, n)
+    desc = flip_bits(d[tgt], rng, 60)
+    rnd = rng.random(n) < 0.25
+    desc[rnd] = rng.integers(0, 256, (int(rnd.sum()), 32), dtype=np.uint8)
+    u = (k["x"][tgt] + rng.uniform(-6, 6, n)).astype(np.float32)
+    v = (k["y"][tgt] + rng.uniform(-6, 6, n)).astype(np.float32)
+    u[:5] = -3.0; v[5:10] = h + 2.0                         # out of image bounds
+    inv_z = rng.uniform(0.02, 1.0, n).astype(np.float32); inv_z[10:15] = -0.1
+    octave = np.clip(k["octave"][tgt] + rng.integers(-1, 2, n), 0, 7).astype(np.int32)
+    angle = np.mod(k["angle"][tgt] + rng.normal(0, 8, n), 360).astype(np.float32)
+    angle[rng.random(n) < 0.1] = rng.uniform(0, 360)
+    valid = rng.random(n) < 0.8
+    has_obs = rng.random(n) < 0.8
+    flags = (valid * 1 + has_obs * 4).astype(np.uint8)
+    u_right = np.where(rng.random(N) < 0.5, k["x"] - rng.uniform(1, 60, N), -1).astype(np.float32)
+    return dict(desc=desc, u=u, v=v, inv_z=inv_z, octave=octave, angle=angle, flags=flags, u_right=u_right)

@@ -1,0 +1,193 @@
+"""GPU (-m gpu): libcuorb through the C ABI vs the CPU oracle and the committed golden vectors.
+Bar: bit-exact pyramid, blur, FAST candidates, keypoints (order, octave, response, size),
+descriptors, Hamming distances, match indices, SAD, mvuRight/mvDepth; angles within 1e-4 rad
+(expected and asserted bit-exact on these inputs)."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle_py as op
+from orbslam3_cpp_fork_b200 import synth
+from tests.matching_cases import extracted_frame, lastframe_case, mappoint_case
+from tests.test_oracle_golden import GOLDEN, golden_image
+
+pytestmark = pytest.mark.gpu
+
+ANGLE_TOL_DEG = np.degrees(1e-4)
+
+
+@pytest.fixture(scope="module")
+def cu():
+    import orbslam3_cpp_fork_b200 as c
+    if c.load().cuorb_device_count() < 1:
+        pytest.fail("no CUDA device: libcuorb has no CPU fallback")
+    return c
+
+
+def assert_extract_equal(k, d, ko, do):
+    assert len(k) == len(ko)
+    for f in ("x", "y", "size", "response", "octave", "class_id"):
+        assert (k[f] == ko[f]).all(), f
+    assert np.abs(k["angle"] - ko["angle"]).max(initial=0) <= ANGLE_TOL_DEG
+    assert (k["angle"] == ko["angle"]).all()
+    assert (d == do).all()
+
+
+CASES = [(752, 480, 1000, 1, (0, 0), None), (752, 480, 1000, 2, (0, 1000), None), (640, 480, 1000, 3, (0, 0), None),
+         (1241, 376, 2000, 4, (0, 0), None), (320, 240, 500, 5, (100, 200), None), (752, 480, 5000, 8, (0, 0), None),
+         (752, 480, 1000, 6, (0, 0), "black"), (752, 480, 1000, 6, (0, 0), "flat"), (752, 480, 1000, 6, (0, 0), "noise")]
+
+
+@pytest.mark.parametrize("w,h,nf,seed,lap,kind", CASES)
+def test_extractor_stage_parity(cu, w, h, nf, seed, lap, kind):
+    img = synth.degenerate_image(w, h, kind, seed) if kind else synth.synth_image(w, h, seed)
+    e = cu.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    o = op.OracleExtractor(nf, 1.2, 8, 20, 7)
+    mono, k, d = e(img, None, lap)
+    mo, ko, do = o.extract(img, lap)
+    assert (e.GetScaleFactors() == o.tables()[0]).all() and (e.mnFeaturesPerLevel == o.tables()[4]).all()
+    for lv in range(8):
+        assert (e.download_plane(lv, 0) == o.plane(lv, 0)).all(), f"pyramid level {lv}"
+        ob = o.plane(lv, 2)
+        if ob is not None:
+            assert (e.download_plane(lv, 2) == ob).all(), f"blur level {lv}"
+        xs, ys, rs = e.download_candidates(lv)
+        xo, yo, ro = o.candidates(lv)
+        assert len(xs) == len(xo) and (xs == xo).all() and (ys == yo).all() and (rs == ro).all(), f"FAST level {lv}"
+    assert mono == mo
+    assert_extract_equal(k, d, ko, do)
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[:-4] for p in GOLDEN])
+def test_golden_vectors(cu, path):
+    g = np.load(path)
+    img = golden_image(g)
+    h, w = img.shape
+    e = cu.ORBextractor(int(g["nfeatures"]), 1.2, 8, 20, 7, max_width=w, max_height=h)
+    mono, k, d = e(img, None, tuple(int(v) for v in g["lap"]))
+    assert mono == int(g["mono"])
+    assert_extract_equal(k, d, g["kps"], g["desc"])
+
+
+def test_empty_and_oversize(cu):
+    e = cu.ORBextractor(500, max_width=320, max_height=240)
+    mono, k, d = e(np.zeros((0, 0), np.uint8))
+    assert mono == -1 and len(k) == 0 and d.shape == (0, 32)            # src/ORBextractor.cc:1060
+    L = cu.load()
+    buf = np.zeros(4, np.uint8)
+    assert L.cuorb_extract(e.handle, None, 0, 0, 0, 0, 0, None, None, 0, None) == -1
+    with pytest.raises(cu.CuorbError):
+        e(np.zeros((480, 752), np.uint8))                                # larger than the arena
+    with pytest.raises(cu.CuorbError):
+        cu.ORBextractor(500, max_width=60, max_height=60)                # levels smaller than a FAST cell
+
+
+def test_ragged_batch_and_size_change(cu):
+    """A batch mixing textured, black, flat and noise frames == per-image results; a handle reused
+    for a smaller image size rebuilds its geometry."""
+    w, h = 640, 480
+    imgs = np.stack([synth.synth_image(w, h, 40), synth.degenerate_image(w, h, "black"), synth.synth_image(w, h, 41),
+                     synth.degenerate_image(w, h, "flat", 2), synth.degenerate_image(w, h, "noise", 3)])
+    e = cu.ORBextractor(1000, max_width=w, max_height=h, max_batch=8)
+    e.extract_batch_async(imgs)
+    counts, mono, kps, desc = e.fetch()
+    o = op.OracleExtractor(1000)
+    for i in range(len(imgs)):
+        mo, ko, do = o.extract(imgs[i])
+        assert counts[i] == len(ko) and mono[i] == mo
+        assert_extract_equal(kps[i, :counts[i]], desc[i, :counts[i]], ko, do)
+    small = synth.synth_image(400, 300, 42)
+    mo, ko, do = o.extract(small)
+    m2, k2, d2 = e(small)
+    assert m2 == mo
+    assert_extract_equal(k2, d2, ko, do)
+
+
+def test_large_batch_idempotent(cu):
+    """Full-size property (BASELINE cfg2 shape): 64 frames, every copy of a frame gives the same
+    result as its first occurrence, and running the batch twice is idempotent."""
+    w, h = 640, 480
+    base = [synth.synth_image(w, h, 60 + i) for i in range(4)]
+    imgs = np.stack([base[i % 4] for i in range(64)])
+    e = cu.ORBextractor(1000, max_width=w, max_height=h, max_batch=64)
+    e.extract_batch_async(imgs); c1, m1, k1, d1 = e.fetch()
+    e.extract_batch_async(imgs); c2, m2, k2, d2 = e.fetch()
+    assert (c1 == c2).all() and (k1 == k2).all() and (d1 == d2).all()
+    for i in range(4, 64):
+        assert c1[i] == c1[i % 4] and (k1[i] == k1[i % 4]).all() and (d1[i] == d1[i % 4]).all()
+    o = op.OracleExtractor(1000)
+    _, ko, do = o.extract(base[3])
+    assert_extract_equal(k1[63, :c1[63]], d1[63, :c1[63]], ko, do)
+
+
+@pytest.mark.parametrize("w,h,nf,seed,fx,mbf", [(752, 480, 1000, 11, 458.654, 47.906), (1241, 376, 2000, 12, 718.856, 386.1448)])
+def test_stereo_parity(cu, w, h, nf, seed, fx, mbf):
+    L, R = synth.synth_stereo_pair(w, h, seed)
+    eL = cu.ORBextractor(nf, max_width=w, max_height=h, max_batch=2)
+    eR = cu.ORBextractor(nf, max_width=w, max_height=h, max_batch=2)
+    black = np.zeros_like(L)
+    eL.extract_batch_async(np.stack([L, black])); eR.extract_batch_async(np.stack([R, R]))
+    cl, _, kl, dl = eL.fetch(); cr, _, kr, dr = eR.fetch()
+    mb = mbf / fx
+    m = cu.ORBmatcher()
+    u, dep, dbg = m.SearchStereo(eL, eR, mb, mbf, debug=True)
+    oL, oR = op.OracleExtractor(nf), op.OracleExtractor(nf)
+    _, k0, d0 = oL.extract(L); _, k1, d1 = oR.extract(R)
+    assert_extract_equal(kl[0, :cl[0]], dl[0, :cl[0]], k0, d0)
+    so = op.stereo(oL, oR, k0, d0, k1, d1, mb, mbf)
+    n = cl[0]
+    assert (so["u_right"] >= 0).sum() > 100
+    assert (dbg["best_idx_r"][0, :n] == so["best_idx_r"]).all() and (dbg["best_dist"][0, :n] == so["best_dist"]).all()
+    assert (dbg["sad"][0, :n] == so["sad"]).all()
+    assert (u[0, :n] == so["u_right"]).all() and (dep[0, :n] == so["depth"]).all()   # bit-exact floats
+    assert cl[1] == 0                                                                # black left image: nothing to match
+    # host-pointer form (the member set Frame::ComputeStereoMatches reads)
+    u2, d2 = m.ComputeStereoMatches(eL, eR, k0, d0, k1, d1, mb, mbf)
+    assert (u2 == so["u_right"]).all() and (d2 == so["depth"]).all()
+
+
+def test_hamming_batch(cu):
+    rng = np.random.default_rng(5)
+    a = rng.integers(0, 256, (3000, 32), dtype=np.uint8); b = rng.integers(0, 256, (2000, 32), dtype=np.uint8)
+    b[:100] = a[:100]
+    ia = rng.integers(0, 3000, 50000).astype(np.int32); ib = rng.integers(0, 2000, 50000).astype(np.int32)
+    out = cu.ORBmatcher().DescriptorDistanceBatch(a, b, ia, ib)
+    ref = np.unpackbits(a[ia] ^ b[ib], axis=1).sum(1)
+    assert (out == ref).all()
+    assert (cu.ORBmatcher().DescriptorDistanceBatch(a[:100], b[:100]) == 0).all()
+    assert cu.ORBmatcher.DescriptorDistance(a[5], b[7]) == op.hamming(a[5], b[7])
+
+
+@pytest.mark.parametrize("M,th,with_uright,far", [(50000, 3.0, False, False), (50000, 1.0, True, True), (3000, 3.0, True, False)])
+def test_search_by_projection_mappoints(cu, M, th, with_uright, far):
+    """cfg4: 1000 frame descriptors vs M local-map MapPoints (order-dependent binding included)."""
+    e, k, d = extracted_frame()
+    sf = e.tables()[0]
+    c = mappoint_case(k, d, sf, M, 77 + M, with_uright=with_uright)
+    fv, keep = op.make_frame_view(k, d, c["u_right"], c["bound"], 752, 480, sf, mb=0.1, mbf=40.0)
+    n_o, best_o = op.search_by_projection(fv, c["desc"], c["px"], c["py"], c["pxr"], c["level"], c["view_cos"],
+                                          c["depth"], c["flags"], th, far, 60.0, 0.8)
+    F = cu.Frame(k, d, sf, 752, 480, mvuRight=c["u_right"], mb=0.1, mbf=40.0)
+    F.mvpMapPoints[c["bound"] > 0] = 10 ** 9; F.mvpHasObs[c["bound"] > 0] = 1
+    mps = cu.MapPointSoA(c["desc"], c["px"], c["py"], c["pxr"], c["level"], c["view_cos"], c["depth"],
+                         (c["flags"] & 1) > 0, (c["flags"] & 2) > 0, (c["flags"] & 4) > 0)
+    n, best = cu.ORBmatcher(0.8).SearchByProjection(F, mps, th, far, 60.0)
+    assert n_o > 100
+    assert n == n_o and (best == best_o).all()
+
+
+@pytest.mark.parametrize("fwd,bwd,th", [(False, False, 7.0), (True, False, 15.0), (False, True, 7.0)])
+def test_search_by_projection_lastframe(cu, fwd, bwd, th):
+    e, k, d = extracted_frame(seed=33)
+    sf = e.tables()[0]
+    c = lastframe_case(k, d, 5)
+    fv, keep = op.make_frame_view(k, d, c["u_right"], None, 752, 480, sf, mb=0.1, mbf=40.0)
+    n_o, best_o, rot_o, keep_o = op.search_by_projection_frame(fv, c["desc"], c["u"], c["v"], c["inv_z"], c["octave"],
+                                                              c["angle"], c["flags"], th, fwd, bwd, True)
+    F = cu.Frame(k, d, sf, 752, 480, mvuRight=c["u_right"], mb=0.1, mbf=40.0)
+    n, best, rot, keepb = cu.ORBmatcher(0.9, True).SearchByProjectionLastFrame(
+        F, c["desc"], c["u"], c["v"], c["inv_z"], c["octave"], c["angle"], c["flags"], th, fwd, bwd)
+    assert n_o > 50
+    assert n == n_o and (best == best_o).all() and (rot == rot_o).all() and (keepb == keep_o).all()
