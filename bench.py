@@ -209,8 +209,12 @@ def run_cuorb(args):
     eL.set_profiling(True); eR.set_profiling(True)
     stage_acc = {}
     for _ in range(3):
-        step_resident(eL, eR)
-        eL.sync(); eR.sync()
+        # stages are timed with the two handles SERIALISED (no overlap between the two streams),
+        # so each stage's CUDA-event time is that kernel sequence alone on the GPU
+        eR.extract_batch_async(Rd); eR.sync()
+        eL.extract_batch_async(Ld); eL.sync()
+        _lib.check(L_.cuorb_stereo_match_batch_async(eL.handle, eR.handle, MB, MBF))
+        eL.sync()
         for k, v in eL.stage_ms().items():
             stage_acc.setdefault(k, []).append(v)
     eL.set_profiling(False); eR.set_profiling(False)

@@ -5,39 +5,77 @@
 // One CTA per (cell, image).  The detection areas of the reference's overlapping cell ROIs tile
 // the level exactly, so a cell's CTA only needs its own pixels + a 3-px ring halo, and NMS looks
 // only at scores inside the cell (OpenCV zeroes everything outside the ROI's detection area).
-//   phase 1: every pixel -> "is a corner at minThFAST" (opposite-pair reject, then 16-bit
-//            brighter/darker ring masks and a run-of-9 bit test); corners are compacted into a
-//            shared-memory list so phase 2 runs with full warps.
-//   phase 2: cornerScore (threshold independent: max over arcs of min |diff|, minus 1) -> u8 tile
-//   phase 3: strict 8-neighbour NMS inside the cell; CTA-wide "any survivor >= iniThFAST";
-//            survivors at the chosen threshold are appended to the level's candidate list.
+//
+//   phase 1: the cell's pixels (+halo) are staged in shared memory widened to u16, so one 32-bit
+//            word holds two horizontally adjacent pixels.
+//   phase 2: BRANCH-FREE corner score for every pixel, two pixels per thread in 16x2 SIMD:
+//            d[k] = v - ring[k] (+256 bias, so a plain 32-bit subtract never borrows across
+//            lanes), then the threshold-independent score
+//                max_k min(d[k..k+8])  and  min_k max(d[k..k+8])        (k circular, 16 arcs)
+//            as a min/max network of 3-input VIMNMX3.{U16x2} instructions (arcs k and k+1 share
+//            8 of their 9 elements, so 8 shared 8-minima + 8 two-element maxima give all 16 arcs:
+//            36 SIMD ops per polarity for two pixels).  "corner at t" <=> score >= t, so no
+//            per-pixel test, no divergence and no compaction is needed.  Scores below minThFAST
+//            are stored as 0.
+//   phase 3: strict 8-neighbour NMS inside the cell on the u8 score tile (words that are all
+//            zero are skipped); CTA-wide "any survivor >= iniThFAST" picks the threshold;
+//            survivors at that threshold are appended to the level's candidate list.
 // The list is unordered; the reference order (cell-row-major, then row-major) is a pure function
 // of (x, y) and is re-derived where it matters (quadtree tie-break, debug download).
+// Bound: the integer ALU pipe (min/max network), not HBM: ~45 ALU-pipe instructions per pixel.
 #include "common.cuh"
 
 namespace cuorb {
 
-__constant__ int c_ring_dx[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1};
-__constant__ int c_ring_dy[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3};
+namespace {
 
-__device__ __forceinline__ bool has_run9(unsigned m16) {
-  unsigned x = m16 | (m16 << 16);
-  x &= x >> 1;  // runs >= 2
-  x &= x >> 2;  // >= 4
-  x &= x >> 4;  // >= 8
-  x &= x >> 1;  // >= 9
-  return (x & 0xFFFFu) != 0;
+__device__ __forceinline__ unsigned umin2(unsigned a, unsigned b) { return __vminu2(a, b); }
+__device__ __forceinline__ unsigned umax2(unsigned a, unsigned b) { return __vmaxu2(a, b); }
+__device__ __forceinline__ unsigned umin3(unsigned a, unsigned b, unsigned c) { return __vimin3_u16x2(a, b, c); }
+__device__ __forceinline__ unsigned umax3(unsigned a, unsigned b, unsigned c) { return __vimax3_u16x2(a, b, c); }
+// two u16 lanes starting at an odd column: high half of `lo` and low half of `hi`
+__device__ __forceinline__ unsigned odd_pair(unsigned lo, unsigned hi) { return __byte_perm(lo, hi, 0x5432); }
+
+// score of the two pixels held in `c` (u16x2) given the 16 ring values r[k] (u16x2 each).
+// Returns biased extremes: A = 256 + max_k min9(d), B = 256 + min_k max9(d), d = v - ring.
+__device__ __forceinline__ void arc_extremes(unsigned c, const unsigned (&r)[16], unsigned& A, unsigned& B) {
+  const unsigned cb = c + 0x01000100u;
+  unsigned d[16];
+#pragma unroll
+  for (int k = 0; k < 16; k++) d[k] = cb - r[k];  // each lane in [1, 511]: no cross-lane borrow
+  // pairs starting at odd k: m2[j] <-> d[2j+1], d[2j+2]
+  unsigned lo2[8], hi2[8];
+#pragma unroll
+  for (int j = 0; j < 8; j++) {
+    lo2[j] = umin2(d[2 * j + 1], d[(2 * j + 2) & 15]);
+    hi2[j] = umax2(d[2 * j + 1], d[(2 * j + 2) & 15]);
+  }
+  unsigned ta[8], tb[8];
+#pragma unroll
+  for (int j = 0; j < 8; j++) {
+    // arcs 2j and 2j+1 share d[2j+1 .. 2j+8]; they differ in d[2j] vs d[2j+9]
+    const unsigned m6 = umin3(lo2[j], lo2[(j + 1) & 7], lo2[(j + 2) & 7]);
+    const unsigned x6 = umax3(hi2[j], hi2[(j + 1) & 7], hi2[(j + 2) & 7]);
+    const unsigned e_hi = umax2(d[2 * j], d[(2 * j + 9) & 15]);
+    const unsigned e_lo = umin2(d[2 * j], d[(2 * j + 9) & 15]);
+    ta[j] = umin3(m6, lo2[(j + 3) & 7], e_hi);  // max(min9(arc 2j), min9(arc 2j+1))
+    tb[j] = umax3(x6, hi2[(j + 3) & 7], e_lo);  // min(max9(arc 2j), max9(arc 2j+1))
+  }
+  A = umax3(umax3(ta[0], ta[1], ta[2]), umax3(ta[3], ta[4], ta[5]), umax2(ta[6], ta[7]));
+  B = umin3(umin3(tb[0], tb[1], tb[2]), umin3(tb[3], tb[4], tb[5]), umin2(tb[6], tb[7]));
 }
 
-// grid: (total_cells, n_img), block 128, dynamic smem = tile + score + list
+}  // namespace
+
+// grid: (total_cells, n_img), block 128, dynamic smem = u16 pixel tile + u8 score tile + list
 __global__ void __launch_bounds__(128) k_fast_cells(const ExtractorGeom* __restrict__ dg,
                                                     const uint8_t* __restrict__ pyr,
                                                     unsigned* __restrict__ cand,
                                                     int* __restrict__ cand_count,
-                                                    int* __restrict__ flags, int tile_pitch,
+                                                    int* __restrict__ flags, int tile_pitch_w,
                                                     int tile_bytes, int score_bytes) {
   extern __shared__ __align__(16) unsigned char smem[];
-  __shared__ int s_ncorner, s_any_ini, s_nout, s_base;
+  __shared__ int s_nlist, s_nout, s_base;
 
   // which level / cell
   int level = 0;
@@ -45,7 +83,7 @@ __global__ void __launch_bounds__(128) k_fast_cells(const ExtractorGeom* __restr
   while (level + 1 < nlv && (int)blockIdx.x >= dg->lv[level + 1].cell_base) level++;
   const LevelGeom& L = dg->lv[level];
   const int cell = blockIdx.x - L.cell_base;
-  const int ci = cell / L.nCols, cj = cell % L.nCols;
+  const int ci = cell / L.nCols, cj = cell - ci * L.nCols;
   const int x0 = EDGE_THRESHOLD + cj * L.wCell, y0 = EDGE_THRESHOLD + ci * L.hCell;
   const int dw = min(x0 + L.wCell, L.maxBorderX - 3) - x0;
   const int dh = min(y0 + L.hCell, L.maxBorderY - 3) - y0;
@@ -55,118 +93,104 @@ __global__ void __launch_bounds__(128) k_fast_cells(const ExtractorGeom* __restr
   const int tid = threadIdx.x;
   const int ini_th = dg->ini_th, min_th = dg->min_th;
 
-  unsigned char*  s_tile  = smem;                                   // (dh+6) rows of tile_pitch
-  unsigned char*  s_score = smem + tile_bytes;                      // (dh+2) x (dw+2), zero frame
-  unsigned short* s_list  = reinterpret_cast<unsigned short*>(smem + tile_bytes + score_bytes);
-  const int sp = dw + 2;
+  unsigned*      s_tile  = reinterpret_cast<unsigned*>(smem);       // (dh+6) rows of tile_pitch_w words
+  unsigned char* s_score = smem + tile_bytes;                       // (dh+2) rows of sp bytes, zero frame
+  unsigned*      s_list  = reinterpret_cast<unsigned*>(smem + tile_bytes + score_bytes);
+  const int sp = (dw + 5 + 3) & ~3;  // score pitch: pixel px lives at column px + 4
 
-  if (tid == 0) { s_ncorner = 0; s_any_ini = 0; s_nout = 0; }
+  if (tid == 0) { s_nlist = 0; s_nout = 0; }
 
-  // load pixel tile with aligned 32-bit words: level x in [ax, ...), rows y0-3 .. y0+dh+2
-  const uint8_t* src = pyr + (size_t)img * dg->pyr_img_stride + L.pix_off;
-  const int gx0 = x0 - 3, ax = gx0 & ~3, ph = gx0 - ax;
-  const int wpr = (ph + dw + 6 + 3) >> 2;  // words per row
-  for (int i = tid; i < wpr * (dh + 6); i += 128) {
-    const int r = i / wpr, c = i - r * wpr;
-    reinterpret_cast<unsigned*>(s_tile + r * tile_pitch)[c] =
-        *reinterpret_cast<const unsigned*>(src + (ptrdiff_t)(y0 - 3 + r) * L.pitch + ax + c * 4);
-  }
-  for (int i = tid; i < (sp * (dh + 2) + 3) / 4; i += 128) reinterpret_cast<unsigned*>(s_score)[i] = 0;
-  __syncthreads();
-
-  // phase 1: corner test at minThFAST
-  const int npx = dw * dh;
-  for (int i = tid; i < npx; i += 128) {
-    const int py = i / dw, px = i - py * dw;
-    const unsigned char* p = s_tile + (py + 3) * tile_pitch + ph + px + 3;
-    const int v = p[0], hi = v + min_th, lo = v - min_th;
-    const int r0 = p[3 * tile_pitch], r8 = p[-3 * tile_pitch], r4 = p[3], r12 = p[-3];
-    const bool qb = (r0 > hi || r8 > hi) && (r4 > hi || r12 > hi);
-    const bool qd = (r0 < lo || r8 < lo) && (r4 < lo || r12 < lo);
-    if (!qb && !qd) continue;
-    unsigned mb = 0, md = 0;
-#pragma unroll
-    for (int k = 0; k < 16; k++) {
-      const int r = p[c_ring_dy[k] * tile_pitch + c_ring_dx[k]];
-      mb |= (unsigned)(r > hi) << k;
-      md |= (unsigned)(r < lo) << k;
+  // ---- phase 1: stage pixels as u16.  Tile column s <-> level x = ax + s (ax 4-aligned). ----
+  const int ax  = (x0 - 4) & ~3;
+  const int cx0 = x0 - ax;           // 4..7: tile column of the cell's first pixel
+  const int o   = cx0 & 1;           // pairs must start on an even tile column
+  const int npr = (dw + o + 1) >> 1; // pixel pairs per row (a leading / trailing pixel may be unused)
+  const int gw  = (cx0 - o + 2 * npr + 4 + 3) >> 2;  // aligned 4-px global words per row (2 halo words right)
+  const uint8_t* src = pyr + (size_t)img * dg->pyr_img_stride + L.pix_off + (ptrdiff_t)(y0 - 3) * L.pitch + ax;
+  {
+    const int n = gw * (dh + 6);
+    const unsigned inv = 65536u / (unsigned)gw + 1u;
+    for (int i = tid; i < n; i += 128) {
+      const int r = (int)(((unsigned)i * inv) >> 16), c = i - r * gw;
+      const unsigned w = __ldg(reinterpret_cast<const unsigned*>(src + (ptrdiff_t)r * L.pitch + c * 4));
+      *reinterpret_cast<uint2*>(s_tile + r * tile_pitch_w + 2 * c) =
+          make_uint2(__byte_perm(w, 0, 0x4140), __byte_perm(w, 0, 0x4342));
     }
-    if (has_run9(mb) || has_run9(md)) s_list[atomicAdd(&s_ncorner, 1)] = (unsigned short)i;
+    const int nz = (sp * (dh + 2)) >> 2;
+    for (int i = tid; i < nz; i += 128) reinterpret_cast<unsigned*>(s_score)[i] = 0;
   }
   __syncthreads();
 
-  // phase 2: scores of the corners
-  const int nc = s_ncorner;
-  for (int n = tid; n < nc; n += 128) {
-    const int i = s_list[n];
-    const int py = i / dw, px = i - py * dw;
-    const unsigned char* p = s_tile + (py + 3) * tile_pitch + ph + px + 3;
-    const int v = p[0];
-    int d[16];
-#pragma unroll
-    for (int k = 0; k < 16; k++) d[k] = v - (int)p[c_ring_dy[k] * tile_pitch + c_ring_dx[k]];
-    int mn[16], mx[16];
-#pragma unroll
-    for (int k = 0; k < 16; k++) { mn[k] = min(d[k], d[(k + 1) & 15]); mx[k] = max(d[k], d[(k + 1) & 15]); }
-    int mn4[16], mx4[16];
-#pragma unroll
-    for (int k = 0; k < 16; k++) { mn4[k] = min(mn[k], mn[(k + 2) & 15]); mx4[k] = max(mx[k], mx[(k + 2) & 15]); }
-    int a = -1000, b = 1000;
-#pragma unroll
-    for (int k = 0; k < 16; k++) {
-      const int m9 = min(min(mn4[k], mn4[(k + 4) & 15]), d[(k + 8) & 15]);
-      const int x9 = max(max(mx4[k], mx4[(k + 4) & 15]), d[(k + 8) & 15]);
-      a = max(a, m9);
-      b = min(b, x9);
+  // ---- phase 2: scores, two pixels per thread ----
+  {
+    const int npairs = npr * dh;
+    const unsigned inv = 65536u / (unsigned)npr + 1u;
+    const int tp = tile_pitch_w;
+    for (int p = tid; p < npairs; p += 128) {
+      const int r = (int)(((unsigned)p * inv) >> 16), m = p - r * npr;
+      const int px = 2 * m - o;  // first pixel of the pair, cell-relative (may be -1)
+      const unsigned* T = s_tile + (r + 3) * tp + ((cx0 + px) >> 1);
+      unsigned ring[16];
+      {
+        const unsigned a = T[3 * tp - 1], b = T[3 * tp], c = T[3 * tp + 1];
+        ring[0] = b; ring[1] = odd_pair(b, c); ring[15] = odd_pair(a, b);
+      }
+      ring[2] = T[2 * tp + 1]; ring[14] = T[2 * tp - 1];
+      ring[3] = odd_pair(T[tp + 1], T[tp + 2]); ring[13] = odd_pair(T[tp - 2], T[tp - 1]);
+      ring[4] = odd_pair(T[1], T[2]); ring[12] = odd_pair(T[-2], T[-1]);
+      ring[5] = odd_pair(T[-tp + 1], T[-tp + 2]); ring[11] = odd_pair(T[-tp - 2], T[-tp - 1]);
+      ring[6] = T[-2 * tp + 1]; ring[10] = T[-2 * tp - 1];
+      {
+        const unsigned a = T[-3 * tp - 1], b = T[-3 * tp], c = T[-3 * tp + 1];
+        ring[8] = b; ring[7] = odd_pair(b, c); ring[9] = odd_pair(a, b);
+      }
+      unsigned A, B;
+      arc_extremes(T[0], ring, A, B);
+      // score = max(a, -b) - 1 with a = A - 256, b = B - 256   (cornerScore<16>)
+      const int s0 = max((int)(A & 0xFFFFu) - 257, 255 - (int)(B & 0xFFFFu));
+      const int s1 = max((int)(A >> 16) - 257, 255 - (int)(B >> 16));
+      unsigned char* q = s_score + (r + 1) * sp + px + 4;
+      if (px >= 0 && s0 >= min_th) q[0] = (unsigned char)s0;
+      if (px + 1 < dw && s1 >= min_th) q[1] = (unsigned char)s1;
     }
-    s_score[(py + 1) * sp + px + 1] = (unsigned char)(max(a, -b) - 1);
   }
   __syncthreads();
 
-  // phase 3: NMS inside the cell, threshold choice, emit
-  unsigned mine[4];  // up to 4 local maxima per thread kept in registers, rest re-evaluated
-  int n_mine = 0;
+  // ---- phase 3: NMS inside the cell, threshold choice, emit ----
   bool any_ini = false;
-  for (int n = tid; n < nc; n += 128) {
-    const int i = s_list[n];
-    const int py = i / dw, px = i - py * dw;
-    const unsigned char* q = s_score + (py + 1) * sp + px + 1;
-    const int s = q[0];
-    const bool lm = s > q[-1] && s > q[1] && s > q[-sp - 1] && s > q[-sp] && s > q[-sp + 1] &&
-                    s > q[sp - 1] && s > q[sp] && s > q[sp + 1];
-    if (lm) {
-      any_ini |= s >= ini_th;
-      // region coordinates of vToDistributeKeys: roi pt + (j*wCell, i*hCell)   (:842-846)
-      const unsigned c = pack_cand(x0 + px - FAST_BORDER, y0 + py - FAST_BORDER, s);
-      if (n_mine < 4) mine[n_mine] = c;
-      n_mine++;
+  {
+    const int nw = (dw + 3) >> 2;
+    const int n = nw * dh;
+    const unsigned inv = 65536u / (unsigned)nw + 1u;
+    for (int i = tid; i < n; i += 128) {
+      const int r = (int)(((unsigned)i * inv) >> 16), cw = i - r * nw;
+      const unsigned char* q0 = s_score + (r + 1) * sp + 4 + 4 * cw;
+      const unsigned W = *reinterpret_cast<const unsigned*>(q0);
+      if (W == 0) continue;
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const int s = (W >> (8 * k)) & 0xFF;
+        if (s == 0) continue;
+        const unsigned char* q = q0 + k;
+        const bool lm = s > q[-1] && s > q[1] && s > q[-sp - 1] && s > q[-sp] && s > q[-sp + 1] &&
+                        s > q[sp - 1] && s > q[sp] && s > q[sp + 1];
+        if (lm) {
+          any_ini |= s >= ini_th;
+          // region coordinates of vToDistributeKeys: roi pt + (j*wCell, i*hCell)   (:842-846)
+          s_list[atomicAdd(&s_nlist, 1)] =
+              pack_cand(x0 + 4 * cw + k - FAST_BORDER, y0 + r - FAST_BORDER, s);
+        }
+      }
     }
   }
-  if (any_ini) s_any_ini = 1;
-  __syncthreads();
-  const int thr = s_any_ini ? ini_th : min_th;
-
-  // count survivors at thr, reserve, write
-  int my_out = 0;
-  if (n_mine <= 4) {
-    for (int k = 0; k < n_mine; k++) my_out += cand_s(mine[k]) >= thr;
-  } else {
-    my_out = -1;  // rare: re-walk below
+  const int thr = __syncthreads_or(any_ini) ? ini_th : min_th;
+  const int nl = s_nlist;
+  if (nl == 0) return;
+  unsigned* s_out = s_tile;  // pixel tile is dead: reuse it for the compacted survivors
+  for (int n = tid; n < nl; n += 128) {
+    const unsigned c = s_list[n];
+    if (cand_s(c) >= thr) s_out[atomicAdd(&s_nout, 1)] = c;
   }
-  if (my_out < 0) {
-    my_out = 0;
-    for (int n = tid; n < nc; n += 128) {
-      const int i = s_list[n];
-      const int py = i / dw, px = i - py * dw;
-      const unsigned char* q = s_score + (py + 1) * sp + px + 1;
-      const int s = q[0];
-      const bool lm = s > q[-1] && s > q[1] && s > q[-sp - 1] && s > q[-sp] && s > q[-sp + 1] &&
-                      s > q[sp - 1] && s > q[sp] && s > q[sp + 1];
-      my_out += lm && s >= thr;
-    }
-  }
-  int my_off = 0;
-  if (my_out) my_off = atomicAdd(&s_nout, my_out);
   __syncthreads();
   const int nout = s_nout;
   if (nout == 0) return;
@@ -175,40 +199,30 @@ __global__ void __launch_bounds__(128) k_fast_cells(const ExtractorGeom* __restr
   __syncthreads();
   const int base = s_base;
   if (base + nout > L.cand_cap) {  // cannot happen with the worst-case capacity; flagged anyway
-    if (tid == 0) { atomicOr(flags, FLAG_CAND_OVERFLOW); }
+    if (tid == 0) atomicOr(flags, FLAG_CAND_OVERFLOW);
     return;
   }
-  unsigned* out = cand + (size_t)img * dg->cand_img_stride + L.cand_off + base + my_off;
-  if (n_mine <= 4) {
-    for (int k = 0; k < n_mine; k++)
-      if (cand_s(mine[k]) >= thr) *out++ = mine[k];
-  } else {
-    for (int n = tid; n < nc; n += 128) {
-      const int i = s_list[n];
-      const int py = i / dw, px = i - py * dw;
-      const unsigned char* q = s_score + (py + 1) * sp + px + 1;
-      const int s = q[0];
-      const bool lm = s > q[-1] && s > q[1] && s > q[-sp - 1] && s > q[-sp] && s > q[-sp + 1] &&
-                      s > q[sp - 1] && s > q[sp] && s > q[sp + 1];
-      if (lm && s >= thr) *out++ = pack_cand(x0 + px - FAST_BORDER, y0 + py - FAST_BORDER, s);
-    }
-  }
+  unsigned* out = cand + (size_t)img * dg->cand_img_stride + L.cand_off + base;
+  for (int n = tid; n < nout; n += 128) out[n] = s_out[n];
 }
 
 void launch_fast(const ExtractorGeom& g, const ExtractorGeom* dg, int n_img, const uint8_t* pyr,
                  unsigned* cand, int* cand_count, int* flags, cudaStream_t st) {
-  const int tile_pitch  = ((3 + g.max_cell_w + 6 + 3) / 4) * 4;
-  const int tile_bytes  = ((tile_pitch * (g.max_cell_h + 6) + 15) / 16) * 16;
-  const int score_bytes = (((g.max_cell_w + 2) * (g.max_cell_h + 2) + 15) / 16) * 16;
-  const int list_bytes  = 2 * g.max_cell_w * g.max_cell_h;
+  // tile: columns 0 .. 7 + max_cell_w + 4 (+ alignment), as u16 pairs -> words
+  const int tile_cols   = (7 + g.max_cell_w + 5 + 3 + 3) & ~3;
+  const int tile_pitch_w = tile_cols / 2;                         // even: rows stay 8-byte aligned
+  const int tile_bytes  = ((tile_pitch_w * 4 * (g.max_cell_h + 6) + 15) / 16) * 16;
+  const int sp_max      = (g.max_cell_w + 5 + 3) & ~3;
+  const int score_bytes = ((sp_max * (g.max_cell_h + 2) + 15) / 16) * 16;
+  const int list_bytes  = 4 * ((g.max_cell_w + 1) / 2) * ((g.max_cell_h + 1) / 2);
   const int smem        = tile_bytes + score_bytes + list_bytes;
-  static bool attr_set = false;
-  if (!attr_set && smem > 48 * 1024) {
+  static int attr = 48 * 1024;
+  if (smem > attr) {
     cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    attr_set = true;
+    attr = smem;
   }
   k_fast_cells<<<dim3(g.total_cells, n_img), 128, smem, st>>>(dg, pyr, cand, cand_count, flags,
-                                                              tile_pitch, tile_bytes, score_bytes);
+                                                              tile_pitch_w, tile_bytes, score_bytes);
   count_launch();
 }
 
