@@ -143,8 +143,8 @@ static int build_geometry(const cuorb_extractor* e, int w, int h, ExtractorGeom&
     L.cand_cap = L.nCols * L.nRows * ((L.wCell + 1) / 2) * ((L.hCell + 1) / 2);
     L.cand_off = cand_off;
     cand_off += align_up((size_t)L.cand_cap, 32);
-    if (L.w + 2 * EDGE_THRESHOLD >= 4096 || L.h + 2 * EDGE_THRESHOLD >= 4096 || L.node_cap >= 32767) {
-      set_error("image or feature count beyond the packed 12-bit coordinate / 15-bit node range");
+    if (L.w + 2 * EDGE_THRESHOLD >= 4096 || L.h + 2 * EDGE_THRESHOLD >= 4096 || L.node_cap >= 16384) {
+      set_error("image or feature count beyond the packed 12-bit coordinate / 14-bit node range");
       return CUORB_E_UNSUPPORTED;
     }
     // resize tables (OpenCV resize.cpp: scale = 1/(dst/src) in double, float fx, 11-bit weights)

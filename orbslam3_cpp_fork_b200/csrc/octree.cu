@@ -1,23 +1,39 @@
 // K3 — quadtree keypoint distribution (replaces ORBextractor::DistributeOctTree,
 // ExtractorNode::DivideNode and compareNodes, src/ORBextractor.cc:481-753).
 //
-// The reference algorithm is sequential over a std::list: children are push_front'ed, the parent
-// is erased, the last phase walks a std::sort'ed vector from the back and stops the moment the
-// quota is reached.  The OUTPUT ORDER of the keypoints is the final list order, so the list
-// semantics (and libstdc++'s introsort tie placement, see introsort.cuh) are reproduced exactly.
-// Parallelism comes from the batch: one warp per (image, level) problem, thousands of problems
-// per launch; inside a problem the 32 lanes cooperate on the 4-way key partition of each split
-// (ballot + popc prefix sums) while the list bookkeeping lives in shared memory.
-// A node owns a contiguous span of the level's key array; a split re-partitions that span into the
-// other of two ping-pong scratch buffers (the FAST candidate list itself is left untouched).  Key order inside a node is irrelevant: the only place the
-// reference depends on it is the final "max response, first one wins" pick, and "first" is a pure
-// function of (x, y) (cell-row-major, then row-major), re-derived there.
+// The reference is a sequential algorithm over a std::list (children push_front'ed, parent
+// erased, a last phase that walks a std::sort'ed vector from the back and stops the moment the
+// quota is reached), and the OUTPUT ORDER of the keypoints is the final list order.  This kernel
+// produces exactly that list, but as a sequence of data-parallel ROUNDS, one CTA per
+// (image, level) problem:
+//
+//   * A full pass of the reference's main loop (:613-675) splits EVERY node with more than one
+//     key, so its result is a pure function of the list before the pass: the new list is
+//     [children of the last split parent (n4..n1), ..., children of the first split parent]
+//     followed by the unsplit (single-key) nodes in their old order.  Child counts come from one
+//     pass over the keys (shared-memory atomics), list positions from block-wide prefix sums.
+//   * A round of the final phase (:677-725) sorts the expandable nodes by (nKeys, UL.x) — with
+//     a port of libstdc++'s introsort (introsort.cuh) run by one thread, because the comparator
+//     has ties and std::sort is not stable — then splits from the back until the quota is
+//     reached.  Child counts of ALL sorted nodes are computed in parallel first; the stopping
+//     index is then a suffix-sum search, and the new list is
+//     [children of the last processed node, ..., children of the first processed node]
+//     followed by the old list minus the processed parents.
+//   * Keys never move: every key carries the list position of its node (u16), remapped once per
+//     round.  The final "max response, first one wins" pick (:735-750) is a 64-bit atomicMax per
+//     node on (response, reference order of the key), where the reference order
+//     (cell-row-major, then row-major inside a FAST cell) is a pure function of (x, y).
+// Keys and node ids are staged in shared memory when they fit, else read from the L2-resident
+// candidate list / scratch arena.  No roofline claim: latency/occupancy-bound bookkeeping.
 #include "common.cuh"
 #include "introsort.cuh"
 
 namespace cuorb {
 
 namespace {
+
+constexpr int OT_THREADS = 128;
+constexpr int OT_KEYCAP  = 4096;  // keys staged in shared memory (6 bytes each)
 
 struct SortEnt { int size; short ulx; short node; };
 struct SortLess {
@@ -28,289 +44,326 @@ struct SortLess {
   }
 };
 
-struct Pool {  // shared-memory views
-  short *x0, *y0, *x1, *y1, *next, *prev, *freel;
-  int *beg, *cnt;
-  unsigned char* buf;
-  SortEnt *v, *vprev;
-};
+struct Box { short x0, y0, x1, y1; };  // UL = (x0,y0), BR = (x1,y1)
 
-constexpr short NIL = -1;
+typedef unsigned long long u64;
+constexpr u64 F20 = (1ull << 20) - 1;
 
-__host__ __device__ inline size_t pool_bytes(int cap) {
-  // 7 short arrays, 2 int arrays, 2 SortEnt arrays, 1 byte array (+ alignment slack)
-  return (size_t)cap * (7 * 2 + 2 * 4 + 2 * 8 + 1) + 64;
+__host__ __device__ inline size_t octree_node_bytes(int cap) {
+  // 2 Box + 2 cnt + cc[4] + remap[4] (u16) + 2 scan (u64) + 2 SortEnt + jrank (u16)
+  return (size_t)cap * (2 * 8 + 2 * 4 + 16 + 8 + 2 * 8 + 2 * 8 + 2) + 128;
 }
 
-struct State {  // warp-uniform registers
-  int head, size, free_top, vcount;
-  bool fail;  // node pool exhausted (cannot happen with node_cap = max(N, 4*nIni) + 8)
-};
-
-__device__ __forceinline__ void push_front(Pool& P, State& S, int id, int lane) {
-  if (lane == 0) {
-    P.prev[id] = NIL;
-    P.next[id] = (short)S.head;
-    if (S.head != NIL) P.prev[S.head] = (short)id;
+// exclusive prefix sum over a[0..n) (packed 3 x 20-bit fields), returns the total
+__device__ u64 block_scan(u64* a, int n, u64* s_warp) {
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int K = (n + OT_THREADS - 1) / OT_THREADS;
+  const int b = min(tid * K, n), e = min(b + K, n);
+  u64 s = 0;
+  for (int i = b; i < e; i++) s += a[i];
+  u64 inc = s;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const u64 t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
   }
-  S.head = id;
-  S.size++;
+  __syncthreads();  // s_warp may still be read from a previous call
+  if (lane == 31) s_warp[wid] = inc;
+  __syncthreads();
+  u64 woff = 0, total = 0;
+#pragma unroll
+  for (int w = 0; w < OT_THREADS / 32; w++) {
+    const u64 v = s_warp[w];
+    if (w < wid) woff += v;
+    total += v;
+  }
+  u64 run = woff + inc - s;
+  for (int i = b; i < e; i++) { const u64 v = a[i]; a[i] = run; run += v; }
+  __syncthreads();
+  return total;
 }
 
-__device__ __forceinline__ void erase(Pool& P, State& S, int id, int lane) {
-  const int p = P.prev[id], n = P.next[id];
-  __syncwarp();
-  if (lane == 0) {
-    if (p != NIL) P.next[p] = (short)n;
-    if (n != NIL) P.prev[n] = (short)p;
-    P.freel[S.free_top] = (short)id;
-  }
-  if (p == NIL) S.head = n;
-  S.free_top++;
-  S.size--;
-  __syncwarp();
+__device__ __forceinline__ int quadrant(unsigned k, const Box& b) {
+  const int midX = b.x0 + ((b.x1 - b.x0 + 1) >> 1);  // UL.x + ceil((UR.x-UL.x)/2)   (:483-484)
+  const int midY = b.y0 + ((b.y1 - b.y0 + 1) >> 1);
+  return (cand_x(k) >= midX) + 2 * (cand_y(k) >= midY);
 }
 
-// DivideNode + the "add childs" block (:481-540, :633-664).  Returns number of children with >1 key.
-__device__ int split_node(Pool& P, State& S, int id, unsigned* buf0, unsigned* buf1, int lane) {
-  if (S.free_top < 4) { S.fail = true; return 0; }
-  const int x0 = P.x0[id], y0 = P.y0[id], x1 = P.x1[id], y1 = P.y1[id];
-  const int beg = P.beg[id], cnt = P.cnt[id];
-  const int b = P.buf[id];
-  const unsigned* src = b ? buf1 : buf0;
-  unsigned*       dst = b ? buf0 : buf1;
-  const int midX = x0 + ((x1 - x0 + 1) >> 1);  // UL.x + ceil((UR.x-UL.x)/2)
-  const int midY = y0 + ((y1 - y0 + 1) >> 1);
-
-  int c[4] = {0, 0, 0, 0};
-  unsigned kreg = 0;
-  int qreg = -1;
-  if (cnt <= 32) {
-    if (lane < cnt) {
-      kreg = src[beg + lane];
-      qreg = (cand_x(kreg) >= midX) + 2 * (cand_y(kreg) >= midY);
-    }
-#pragma unroll
-    for (int q = 0; q < 4; q++) c[q] = __popc(__ballot_sync(0xffffffffu, qreg == q));
-  } else {
-    for (int i = lane; i < ((cnt + 31) & ~31); i += 32) {
-      int q = -1;
-      if (i < cnt) { const unsigned k = src[beg + i]; q = (cand_x(k) >= midX) + 2 * (cand_y(k) >= midY); }
-#pragma unroll
-      for (int qq = 0; qq < 4; qq++) c[qq] += __popc(__ballot_sync(0xffffffffu, q == qq));
-    }
-  }
-  int o[4];
-  o[0] = beg; o[1] = o[0] + c[0]; o[2] = o[1] + c[1]; o[3] = o[2] + c[2];
-  const unsigned lt_mask = (1u << lane) - 1u;
-  if (cnt <= 32) {
-#pragma unroll
-    for (int q = 0; q < 4; q++) {
-      const unsigned m = __ballot_sync(0xffffffffu, qreg == q);
-      if (qreg == q) dst[o[q] + __popc(m & lt_mask)] = kreg;
-    }
-  } else {
-    int run[4] = {o[0], o[1], o[2], o[3]};
-    for (int i = lane; i < ((cnt + 31) & ~31); i += 32) {
-      int q = -1;
-      unsigned k = 0;
-      if (i < cnt) { k = src[beg + i]; q = (cand_x(k) >= midX) + 2 * (cand_y(k) >= midY); }
-#pragma unroll
-      for (int qq = 0; qq < 4; qq++) {
-        const unsigned m = __ballot_sync(0xffffffffu, q == qq);
-        if (q == qq) dst[run[qq] + __popc(m & lt_mask)] = k;
-        run[qq] += __popc(m);
-      }
-    }
-  }
-  __syncwarp();
-
-  int n_expand = 0;
-#pragma unroll
-  for (int q = 0; q < 4; q++) {
-    if (c[q] == 0) continue;
-    const int cid = P.freel[S.free_top - 1];
-    S.free_top--;
-    if (lane == 0) {
-      P.x0[cid] = (short)((q & 1) ? midX : x0);
-      P.x1[cid] = (short)((q & 1) ? x1 : midX);
-      P.y0[cid] = (short)((q & 2) ? midY : y0);
-      P.y1[cid] = (short)((q & 2) ? y1 : midY);
-      P.beg[cid] = o[q];
-      P.cnt[cid] = c[q];
-      P.buf[cid] = (unsigned char)(b ^ 1);
-    }
-    push_front(P, S, cid, lane);
-    if (c[q] > 1) {
-      if (lane == 0) P.v[S.vcount] = SortEnt{c[q], (short)((q & 1) ? midX : x0), (short)cid};
-      S.vcount++;
-      n_expand++;
-    }
-    __syncwarp();
-  }
-  return n_expand;
+__device__ __forceinline__ Box child_box(const Box& b, int q) {
+  const int midX = b.x0 + ((b.x1 - b.x0 + 1) >> 1);
+  const int midY = b.y0 + ((b.y1 - b.y0 + 1) >> 1);
+  Box c;
+  c.x0 = (short)((q & 1) ? midX : b.x0);
+  c.x1 = (short)((q & 1) ? b.x1 : midX);
+  c.y0 = (short)((q & 2) ? midY : b.y0);
+  c.y1 = (short)((q & 2) ? b.y1 : midY);
+  return c;
 }
 
 }  // namespace
 
-// grid: (nlevels, n_img), block: 32 threads (one warp per problem)
-__global__ void __launch_bounds__(32) k_octree(const ExtractorGeom* __restrict__ dg,
-                                               const unsigned* __restrict__ cand,
-                                               unsigned* __restrict__ scratch,
-                                               const int* __restrict__ cand_count,
-                                               LevelKey* __restrict__ keys, int* __restrict__ key_count,
-                                               int* __restrict__ flags, int pool_cap) {
+// grid: (nlevels, n_img), block OT_THREADS
+__global__ void __launch_bounds__(OT_THREADS) k_octree(const ExtractorGeom* __restrict__ dg,
+                                                       const unsigned* __restrict__ cand,
+                                                       unsigned* __restrict__ scratch,
+                                                       const int* __restrict__ cand_count,
+                                                       LevelKey* __restrict__ keys_out,
+                                                       int* __restrict__ key_count,
+                                                       int* __restrict__ flags, int pool_cap) {
   extern __shared__ __align__(16) unsigned char smem[];
-  const int level = blockIdx.x, img = blockIdx.y, lane = threadIdx.x;
+  __shared__ u64 s_warp[OT_THREADS / 32];
+  __shared__ int s_cnt_ok;
+
+  const int level = blockIdx.x, img = blockIdx.y, tid = threadIdx.x;
   const LevelGeom& L = dg->lv[level];
   const int slot = img * dg->nlevels + level;
   const int M = min(cand_count[slot], L.cand_cap);
-  if (M == 0) { if (lane == 0) key_count[slot] = 0; return; }
+  if (M == 0) { if (tid == 0) key_count[slot] = 0; return; }
+  const int cap = pool_cap;
 
-  Pool P;
-  {
-    unsigned char* p = smem;
-    P.v = (SortEnt*)p;      p += sizeof(SortEnt) * pool_cap;
-    P.vprev = (SortEnt*)p;  p += sizeof(SortEnt) * pool_cap;
-    P.beg = (int*)p;        p += 4 * pool_cap;
-    P.cnt = (int*)p;        p += 4 * pool_cap;
-    P.x0 = (short*)p;       p += 2 * pool_cap;
-    P.y0 = (short*)p;       p += 2 * pool_cap;
-    P.x1 = (short*)p;       p += 2 * pool_cap;
-    P.y1 = (short*)p;       p += 2 * pool_cap;
-    P.next = (short*)p;     p += 2 * pool_cap;
-    P.prev = (short*)p;     p += 2 * pool_cap;
-    P.freel = (short*)p;    p += 2 * pool_cap;
-    P.buf = p;
+  // ---- shared-memory carve-up ----
+  unsigned char* p = smem;
+  u64* scanA = (u64*)p;            p += 8 * cap;
+  u64* scanB = (u64*)p;            p += 8 * cap;
+  SortEnt* V  = (SortEnt*)p;       p += 8 * cap;
+  SortEnt* Vs = (SortEnt*)p;       p += 8 * cap;
+  Box* boxA = (Box*)p;             p += 8 * cap;
+  Box* boxB = (Box*)p;             p += 8 * cap;
+  int* cc   = (int*)p;             p += 16 * cap;
+  int* cntA = (int*)p;             p += 4 * cap;
+  int* cntB = (int*)p;             p += 4 * cap;
+  unsigned short* remap = (unsigned short*)p;  p += 8 * cap;
+  unsigned short* jrank = (unsigned short*)p;  p += 2 * cap;
+  p = (unsigned char*)(((uintptr_t)p + 15) & ~(uintptr_t)15);
+  unsigned* s_keys = (unsigned*)p;                         // OT_KEYCAP entries
+  unsigned short* s_nid = (unsigned short*)(p + 4 * OT_KEYCAP);
+
+  // keys / node ids: shared memory when they fit, else global
+  const unsigned* gkeys = cand + (size_t)img * dg->cand_img_stride + L.cand_off;
+  const unsigned* keys;
+  unsigned short* nid;
+  if (M <= OT_KEYCAP) {
+    for (int i = tid; i < M; i += OT_THREADS) s_keys[i] = gkeys[i];
+    keys = s_keys; nid = s_nid;
+  } else {
+    keys = gkeys;
+    nid  = reinterpret_cast<unsigned short*>(scratch + (size_t)img * 2 * dg->cand_img_stride + L.cand_off);
   }
-  const int cap = L.node_cap;
-  // the FAST candidate list (bufA) stays intact (parity/debug tap); nodes ping-pong between the
-  // two halves of the scratch arena
-  const unsigned* bufA = cand + (size_t)img * dg->cand_img_stride + L.cand_off;
-  unsigned* bufB = scratch + (size_t)img * 2 * dg->cand_img_stride + L.cand_off;
-  unsigned* bufC = bufB + dg->cand_img_stride;
+
+  Box* box = boxA;  Box* nbox = boxB;
+  int* cnt = cntA;  int* ncnt = cntB;
   const int N = L.quota;
+  int size = 0, vcount = 0;
 
-  // free list: ids cap-1 .. 0 (pop from the top gives 0, 1, 2, ...)
-  for (int i = lane; i < cap; i += 32) P.freel[i] = (short)(cap - 1 - i);
-  __syncwarp();
-  State S{NIL, 0, cap, 0, false};
-
-  // roots (:566-591): key -> root int(x / hX); partition A -> B root by root
-  const int   nIni = L.nIni;
-  const float hX   = L.hX;
-  const int   H    = L.maxBorderY - FAST_BORDER;
-  int tail = NIL, off = 0;
-  for (int r = 0; r < nIni; r++) {
-    int run = off;
-    const unsigned lt_mask = (1u << lane) - 1u;
-    for (int i = lane; i < ((M + 31) & ~31); i += 32) {
-      bool mine = false;
-      unsigned k = 0;
-      if (i < M) { k = bufA[i]; mine = (int)((float)cand_x(k) / hX) == r; }
-      const unsigned m = __ballot_sync(0xffffffffu, mine);
-      if (mine) bufB[run + __popc(m & lt_mask)] = k;
-      run += __popc(m);
+  // ---- roots (:566-604): key -> root int(x / hX); empty roots are erased ----
+  {
+    const int   nIni = L.nIni;
+    const float hX   = L.hX;
+    const int   H    = L.maxBorderY - FAST_BORDER;
+    for (int r = tid; r < nIni; r += OT_THREADS) cc[r] = 0;
+    __syncthreads();
+    for (int i = tid; i < M; i += OT_THREADS) {
+      const int r = (int)((float)cand_x(keys[i]) / hX);
+      nid[i] = (unsigned short)r;
+      atomicAdd(&cc[r], 1);
     }
-    const int c = run - off;
-    if (c > 0) {  // empty roots are erased (:595-604); push_back keeps root order
-      const int id = P.freel[S.free_top - 1];
-      S.free_top--;
-      if (lane == 0) {
-        P.x0[id] = (short)(int)(hX * (float)r);
-        P.x1[id] = (short)(int)(hX * (float)(r + 1));
-        P.y0[id] = 0; P.y1[id] = (short)H;
-        P.beg[id] = off; P.cnt[id] = c; P.buf[id] = 1;
-        P.next[id] = NIL; P.prev[id] = (short)tail;
-        if (tail != NIL) P.next[tail] = (short)id;
+    __syncthreads();
+    if (tid == 0) {
+      int n = 0;
+      for (int r = 0; r < nIni; r++) {
+        if (cc[r] == 0) continue;
+        Box b;
+        b.x0 = (short)(int)(hX * (float)r); b.x1 = (short)(int)(hX * (float)(r + 1));
+        b.y0 = 0; b.y1 = (short)H;
+        box[n] = b; cnt[n] = cc[r]; remap[r] = (unsigned short)n;
+        n++;
       }
-      if (tail == NIL) S.head = id;
-      tail = id;
-      S.size++;
+      s_cnt_ok = n;
     }
-    off = run;
-    __syncwarp();
+    __syncthreads();
+    size = s_cnt_ok;
+    for (int i = tid; i < M; i += OT_THREADS) nid[i] = remap[nid[i]];
+    __syncthreads();
   }
 
-  bool finish = false;
-  while (!finish) {
-    const int prevSize = S.size;
-    int nToExpand = 0;
-    S.vcount = 0;
-    int cur = S.head;
-    while (cur != NIL) {
-      const int nxt = P.next[cur];
-      if (P.cnt[cur] != 1) {  // bNoMore <=> exactly one key
-        nToExpand += split_node(P, S, cur, bufC, bufB, lane);
-        if (S.fail) break;
-        erase(P, S, cur, lane);
-      }
-      cur = nxt;
+  bool fail = false;
+  bool final_phase = false;
+  for (;;) {
+    const int prevSize = size;
+    // ---- (final phase only) sort the expandable nodes (:686-689) ----
+    if (final_phase) {
+      for (int i = tid; i < vcount; i += OT_THREADS) Vs[i] = V[i];
+      __syncthreads();
+      if (tid == 0) cuorb_sort::Introsort<SortEnt, SortLess>::sort(Vs, Vs + vcount, SortLess());
+      __syncthreads();
     }
-    if (S.fail) break;
-    if (S.size >= N || S.size == prevSize) {
-      finish = true;
-    } else if (S.size + nToExpand * 3 > N) {
-      while (!finish) {
-        const int prev2 = S.size;
-        const int pc = S.vcount;
-        for (int i = lane; i < pc; i += 32) P.vprev[i] = P.v[i];
-        S.vcount = 0;
-        __syncwarp();
-        if (lane == 0) cuorb_sort::Introsort<SortEnt, SortLess>::sort(P.vprev, P.vprev + pc, SortLess());
-        __syncwarp();
-        for (int j = pc - 1; j >= 0; j--) {
-          const int id = P.vprev[j].node;
-          split_node(P, S, id, bufC, bufB, lane);
-          if (S.fail) { finish = true; break; }
-          erase(P, S, id, lane);
-          if (S.size >= N) break;
+    // ---- child counts of every node with more than one key ----
+    for (int i = tid; i < size * 4; i += OT_THREADS) cc[i] = 0;
+    __syncthreads();
+    for (int i = tid; i < M; i += OT_THREADS) {
+      const int pos = nid[i];
+      if (cnt[pos] > 1) {
+        const int q = quadrant(keys[i], box[pos]);
+        nid[i] = (unsigned short)(pos | (q << 14));
+        atomicAdd(&cc[pos * 4 + q], 1);
+      }
+    }
+    __syncthreads();
+
+    int newSize, newV;
+    if (!final_phase) {
+      // ---- one full pass of the main loop (:613-675) ----
+      for (int pos = tid; pos < size; pos += OT_THREADS) {
+        u64 v = 1ull << 40;  // unsplit
+        if (cnt[pos] > 1) {
+          const int* c = cc + pos * 4;
+          const int nch = (c[0] > 0) + (c[1] > 0) + (c[2] > 0) + (c[3] > 0);
+          const int nex = (c[0] > 1) + (c[1] > 1) + (c[2] > 1) + (c[3] > 1);
+          v = (u64)nch | ((u64)nex << 20);
         }
-        if (S.size >= N || S.size == prev2) finish = true;
+        scanA[pos] = v;
+      }
+      __syncthreads();
+      const u64 tot = block_scan(scanA, size, s_warp);
+      const int totCh = (int)(tot & F20), totEx = (int)((tot >> 20) & F20), nUn = (int)(tot >> 40);
+      newSize = totCh + nUn; newV = totEx;
+      if (newSize > cap) { fail = true; break; }
+      for (int pos = tid; pos < size; pos += OT_THREADS) {
+        const u64 ex = scanA[pos];
+        if (cnt[pos] > 1) {
+          const int* c = cc + pos * 4;
+          const Box b = box[pos];
+          const int nch = (c[0] > 0) + (c[1] > 0) + (c[2] > 0) + (c[3] > 0);
+          // later parents come first; inside a parent n4 is front-most (push_front order)
+          int np = totCh - (int)(ex & F20) - nch;
+          int vi = (int)((ex >> 20) & F20);
+          unsigned short npos[4];
+#pragma unroll
+          for (int q = 3; q >= 0; q--) {
+            npos[q] = 0;
+            if (c[q] > 0) {
+              nbox[np] = child_box(b, q); ncnt[np] = c[q];
+              npos[q] = (unsigned short)np;
+              np++;
+            }
+            remap[pos * 4 + q] = npos[q];
+          }
+#pragma unroll
+          for (int q = 0; q < 4; q++)
+            if (c[q] > 1) { V[vi] = SortEnt{c[q], (q & 1) ? (short)(b.x0 + ((b.x1 - b.x0 + 1) >> 1)) : b.x0, (short)npos[q]}; vi++; }
+        } else {
+          const int np = totCh + (int)(ex >> 40);
+          nbox[np] = box[pos]; ncnt[np] = cnt[pos];
+          remap[pos * 4] = (unsigned short)np;
+        }
+      }
+    } else {
+      // ---- one round of the final phase (:677-725) ----
+      for (int j = tid; j < vcount; j += OT_THREADS) {
+        const int* c = cc + (int)Vs[j].node * 4;
+        const int nch = (c[0] > 0) + (c[1] > 0) + (c[2] > 0) + (c[3] > 0);
+        const int nex = (c[0] > 1) + (c[1] > 1) + (c[2] > 1) + (c[3] > 1);
+        scanA[j] = (u64)(nch - 1) | ((u64)nch << 20) | ((u64)nex << 40);
+      }
+      for (int pos = tid; pos < size; pos += OT_THREADS) jrank[pos] = 0xFFFF;
+      if (tid == 0) s_cnt_ok = 0;
+      __syncthreads();
+      const u64 tot = block_scan(scanA, vcount, s_warp);
+      const int totGain = (int)(tot & F20);
+      // splitting goes from the back and stops as soon as size >= N (:721): j* = largest j with
+      // size + sum_{j' >= j} gain >= N; the sums are non-increasing in j, so count them
+      int ok = 0;
+      for (int j = tid; j < vcount; j += OT_THREADS) ok += (size + totGain - (int)(scanA[j] & F20)) >= N;
+      if (ok) atomicAdd(&s_cnt_ok, ok);
+      __syncthreads();
+      const int jstar = s_cnt_ok > 0 ? s_cnt_ok - 1 : 0;
+      const u64 exStar = vcount > 0 ? scanA[jstar] : 0;
+      for (int j = tid + jstar; j < vcount; j += OT_THREADS) jrank[Vs[j].node] = (unsigned short)j;
+      __syncthreads();
+      for (int pos = tid; pos < size; pos += OT_THREADS) scanB[pos] = jrank[pos] == 0xFFFF ? 1 : 0;
+      __syncthreads();
+      const int nKeep = (int)block_scan(scanB, size, s_warp);
+      const int newCh = (int)((tot >> 20) & F20) - (int)((exStar >> 20) & F20);
+      const int totEx = (int)(tot >> 40);
+      newSize = nKeep + newCh;
+      newV = totEx - (int)(exStar >> 40);
+      if (newSize > cap) { fail = true; break; }
+      for (int j = tid + jstar; j < vcount; j += OT_THREADS) {
+        const int pos = Vs[j].node;
+        const int* c = cc + pos * 4;
+        const Box b = box[pos];
+        const u64 ex = scanA[j];
+        const int nex = (c[0] > 1) + (c[1] > 1) + (c[2] > 1) + (c[3] > 1);
+        int np = (int)((ex >> 20) & F20) - (int)((exStar >> 20) & F20);  // children of j* are front-most
+        int vi = totEx - (int)(ex >> 40) - nex;                          // push order: j from the back
+        unsigned short npos[4];
+#pragma unroll
+        for (int q = 3; q >= 0; q--) {
+          npos[q] = 0;
+          if (c[q] > 0) {
+            nbox[np] = child_box(b, q); ncnt[np] = c[q];
+            npos[q] = (unsigned short)np;
+            np++;
+          }
+          remap[pos * 4 + q] = npos[q];
+        }
+#pragma unroll
+        for (int q = 0; q < 4; q++)
+          if (c[q] > 1) { V[vi] = SortEnt{c[q], (q & 1) ? (short)(b.x0 + ((b.x1 - b.x0 + 1) >> 1)) : b.x0, (short)npos[q]}; vi++; }
+      }
+      for (int pos = tid; pos < size; pos += OT_THREADS) {
+        if (jrank[pos] != 0xFFFF) continue;
+        const unsigned short np = (unsigned short)(newCh + (int)scanB[pos]);
+        nbox[np] = box[pos]; ncnt[np] = cnt[pos];
+        remap[pos * 4] = np; remap[pos * 4 + 1] = np; remap[pos * 4 + 2] = np; remap[pos * 4 + 3] = np;
       }
     }
+    __syncthreads();
+    // ---- move every key to its node's new list position ----
+    for (int i = tid; i < M; i += OT_THREADS) {
+      const int v = nid[i];
+      nid[i] = remap[(v & 0x3FFF) * 4 + (v >> 14)];
+    }
+    { Box* t = box; box = nbox; nbox = t; }
+    { int* t = cnt; cnt = ncnt; ncnt = t; }
+    size = newSize; vcount = newV;
+    __syncthreads();
+    // ---- loop control (:675-677, :727-728) ----
+    if (size >= N || size == prevSize) break;
+    if (!final_phase && size + vcount * 3 > N) final_phase = true;
   }
 
-  // list order -> output order; per node keep the max-response key, first in reference order wins
-  short* order = (short*)P.vprev;
-  if (lane == 0) {
-    int i = 0;
-    for (int c = S.head; c != NIL; c = P.next[c]) order[i++] = (short)c;
-  }
-  __syncwarp();
-  const int nout = S.size;
-  if (S.fail) { if (lane == 0) { atomicOr(flags, FLAG_NODE_OVERFLOW); key_count[slot] = 0; } return; }
-  if (nout > L.key_cap) { if (lane == 0) { atomicOr(flags, FLAG_KEY_OVERFLOW); key_count[slot] = 0; } return; }
-  LevelKey* out = keys + (size_t)img * dg->key_img_stride + L.key_off;
-  for (int i = lane; i < nout; i += 32) {
-    const int id = order[i];
-    const unsigned* src = (P.buf[id] ? bufB : bufC) + P.beg[id];
-    const int cnt = P.cnt[id];
-    unsigned best = src[0];
-    unsigned long long best_ord = ~0ull;
-    bool have_ord = false;
-    for (int k = 1; k < cnt; k++) {
-      const unsigned c = src[k];
-      const int sc = cand_s(c), sb = cand_s(best);
-      if (sc < sb) continue;
-      auto ord = [&](unsigned q) {
-        const int x = cand_x(q), y = cand_y(q);
-        const unsigned long long cell = (unsigned long long)((y - 3) / L.hCell) * L.nCols + (x - 3) / L.wCell;
-        return (cell << 24) | ((unsigned long long)y << 12) | (unsigned long long)x;
-      };
-      if (sc > sb) { best = c; have_ord = false; continue; }
-      if (!have_ord) { best_ord = ord(best); have_ord = true; }
-      const unsigned long long oc = ord(c);
-      if (oc < best_ord) { best = c; best_ord = oc; }
+  if (fail) { if (tid == 0) { atomicOr(flags, FLAG_NODE_OVERFLOW); key_count[slot] = 0; } return; }
+  if (size > L.key_cap) { if (tid == 0) { atomicOr(flags, FLAG_KEY_OVERFLOW); key_count[slot] = 0; } return; }
+
+  // ---- per node keep the max-response key, first in reference order wins (:735-750) ----
+  u64* best = scanA;
+  for (int pos = tid; pos < size; pos += OT_THREADS) best[pos] = 0;
+  __syncthreads();
+  {
+    const int hCell = L.hCell, wCell = L.wCell, nCols = L.nCols;
+    constexpr u64 ORD = (1ull << 38) - 1;
+    for (int i = tid; i < M; i += OT_THREADS) {
+      const unsigned k = keys[i];
+      const int x = cand_x(k), y = cand_y(k);
+      const u64 cell = (u64)(((y - 3) / hCell) * nCols + (x - 3) / wCell);
+      const u64 ord = (cell << 24) | ((u64)y << 12) | (u64)x;
+      atomicMax(&best[nid[i] & 0x3FFF], ((u64)cand_s(k) << 38) | (ORD - ord));
     }
-    LevelKey kq;
-    kq.x = (unsigned short)(cand_x(best) + FAST_BORDER);
-    kq.y = (unsigned short)(cand_y(best) + FAST_BORDER);
-    kq.score = (unsigned short)cand_s(best);
-    kq.pad = 0;
-    out[i] = kq;
   }
-  if (lane == 0) key_count[slot] = nout;
+  __syncthreads();
+  LevelKey* out = keys_out + (size_t)img * dg->key_img_stride + L.key_off;
+  for (int pos = tid; pos < size; pos += OT_THREADS) {
+    const u64 b = best[pos];
+    const u64 ord = ((1ull << 38) - 1) - (b & ((1ull << 38) - 1));
+    LevelKey kq;
+    kq.x = (unsigned short)((int)(ord & 0xFFF) + FAST_BORDER);
+    kq.y = (unsigned short)((int)((ord >> 12) & 0xFFF) + FAST_BORDER);
+    kq.score = (unsigned short)(b >> 38);
+    kq.pad = 0;
+    out[pos] = kq;
+  }
+  if (tid == 0) key_count[slot] = size;
 }
 
 void launch_octree(const ExtractorGeom& g, const ExtractorGeom* dg, int n_img, const unsigned* cand,
@@ -318,14 +371,14 @@ void launch_octree(const ExtractorGeom& g, const ExtractorGeom* dg, int n_img, c
                    int* flags, cudaStream_t st) {
   int cap = 0;
   for (int l = 0; l < g.nlevels; l++) cap = max(cap, g.lv[l].node_cap);
-  const size_t smem = pool_bytes(cap);
+  const size_t smem = octree_node_bytes(cap) + (size_t)OT_KEYCAP * 6;
   static size_t attr = 48 * 1024;
   if (smem > attr) {
     cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     attr = smem;
   }
-  k_octree<<<dim3(g.nlevels, n_img), 32, smem, st>>>(dg, cand, cand_scratch, cand_count, keys,
-                                                     key_count, flags, cap);
+  k_octree<<<dim3(g.nlevels, n_img), OT_THREADS, smem, st>>>(dg, cand, cand_scratch, cand_count, keys,
+                                                             key_count, flags, cap);
   count_launch();
 }
 
