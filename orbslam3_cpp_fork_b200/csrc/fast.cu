@@ -35,6 +35,9 @@ __device__ __forceinline__ unsigned umin3(unsigned a, unsigned b, unsigned c) { 
 __device__ __forceinline__ unsigned umax3(unsigned a, unsigned b, unsigned c) { return __vimax3_u16x2(a, b, c); }
 // two u16 lanes starting at an odd column: high half of `lo` and low half of `hi`
 __device__ __forceinline__ unsigned odd_pair(unsigned lo, unsigned hi) { return __byte_perm(lo, hi, 0x5432); }
+// exact n / d for n * d < 2^32 with inv = magic(d)
+__device__ __forceinline__ unsigned magic(int d) { return 0xFFFFFFFFu / (unsigned)d + 1u; }
+__device__ __forceinline__ int fastdiv(int n, unsigned inv, int d) { return d == 1 ? n : (int)__umulhi((unsigned)n, inv); }
 
 // score of the two pixels held in `c` (u16x2) given the 16 ring values r[k] (u16x2 each).
 // Returns biased extremes: A = 256 + max_k min9(d), B = 256 + min_k max9(d), d = v - ring.
@@ -67,15 +70,18 @@ __device__ __forceinline__ void arc_extremes(unsigned c, const unsigned (&r)[16]
 
 }  // namespace
 
-// grid: (total_cells, n_img), block 128, dynamic smem = u16 pixel tile + u8 score tile + list
+// grid: (total_cells, n_img), block 128, dynamic smem = u16 pixel tile + u8 score tile + lists
+// TP: pixel-tile pitch in 32-bit words (two u16 pixels each).  ODD, and lanes walk down rows, so
+// the 32 lanes of a warp hit 32 different banks.
+template <int TP>
 __global__ void __launch_bounds__(128) k_fast_cells(const ExtractorGeom* __restrict__ dg,
                                                     const uint8_t* __restrict__ pyr,
                                                     unsigned* __restrict__ cand,
                                                     int* __restrict__ cand_count,
-                                                    int* __restrict__ flags, int tile_pitch_w,
-                                                    int tile_bytes, int score_bytes) {
+                                                    int* __restrict__ flags, int tile_bytes,
+                                                    int score_bytes, int plist_bytes, int clist_bytes) {
   extern __shared__ __align__(16) unsigned char smem[];
-  __shared__ int s_nlist, s_nout, s_base;
+  __shared__ int s_np, s_nc, s_nlist, s_nout, s_base;
 
   // which level / cell
   int level = 0;
@@ -90,15 +96,18 @@ __global__ void __launch_bounds__(128) k_fast_cells(const ExtractorGeom* __restr
   if (dw <= 0 || dh <= 0) return;  // cells the reference skips (:781, :791) or that cannot hold a corner
 
   const int img = blockIdx.y;
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31;
   const int ini_th = dg->ini_th, min_th = dg->min_th;
 
-  unsigned*      s_tile  = reinterpret_cast<unsigned*>(smem);       // (dh+6) rows of tile_pitch_w words
-  unsigned char* s_score = smem + tile_bytes;                       // (dh+2) rows of sp bytes, zero frame
-  unsigned*      s_list  = reinterpret_cast<unsigned*>(smem + tile_bytes + score_bytes);
-  const int sp = (dw + 5 + 3) & ~3;  // score pitch: pixel px lives at column px + 4
+  unsigned*       s_tile  = reinterpret_cast<unsigned*>(smem);      // (dh+6) rows of TP words
+  unsigned char*  s_score = smem + tile_bytes;                      // (dh+2) rows of sp bytes, zero frame
+  unsigned short* s_plist = reinterpret_cast<unsigned short*>(smem + tile_bytes + score_bytes);
+  unsigned short* s_clist = reinterpret_cast<unsigned short*>(smem + tile_bytes + score_bytes + plist_bytes);
+  unsigned*       s_list  = reinterpret_cast<unsigned*>(smem + tile_bytes + score_bytes + plist_bytes + clist_bytes);
+  // score pitch: pixel px lives at column px + 4; pitch/4 odd so a column of rows spreads over banks
+  const int sp = (((dw + 5 + 3) >> 2) | 1) << 2;
 
-  if (tid == 0) { s_nlist = 0; s_nout = 0; }
+  if (tid == 0) { s_np = 0; s_nc = 0; s_nlist = 0; s_nout = 0; }
 
   // ---- phase 1: stage pixels as u16.  Tile column s <-> level x = ax + s (ax 4-aligned). ----
   const int ax  = (x0 - 4) & ~3;
@@ -109,39 +118,73 @@ __global__ void __launch_bounds__(128) k_fast_cells(const ExtractorGeom* __restr
   const uint8_t* src = pyr + (size_t)img * dg->pyr_img_stride + L.pix_off + (ptrdiff_t)(y0 - 3) * L.pitch + ax;
   {
     const int n = gw * (dh + 6);
-    const unsigned inv = 65536u / (unsigned)gw + 1u;
+    const unsigned inv = magic(gw);
     for (int i = tid; i < n; i += 128) {
-      const int r = (int)(((unsigned)i * inv) >> 16), c = i - r * gw;
+      const int r = fastdiv(i, inv, gw), c = i - r * gw;
       const unsigned w = __ldg(reinterpret_cast<const unsigned*>(src + (ptrdiff_t)r * L.pitch + c * 4));
-      *reinterpret_cast<uint2*>(s_tile + r * tile_pitch_w + 2 * c) =
-          make_uint2(__byte_perm(w, 0, 0x4140), __byte_perm(w, 0, 0x4342));
+      s_tile[r * TP + 2 * c]     = __byte_perm(w, 0, 0x4140);
+      s_tile[r * TP + 2 * c + 1] = __byte_perm(w, 0, 0x4342);
     }
     const int nz = (sp * (dh + 2)) >> 2;
     for (int i = tid; i < nz; i += 128) reinterpret_cast<unsigned*>(s_score)[i] = 0;
   }
   __syncthreads();
 
-  // ---- phase 2: scores, two pixels per thread ----
+  const int npairs = npr * dh;
+  const unsigned invh = magic(dh);
+  const int cbase = (cx0 - o) >> 1;
+
+  // ---- phase 2a: necessary condition on the 4 compass ring pixels, pairs that pass are listed.
+  // An arc of 9 always contains two adjacent compass points, so a corner at minThFAST needs
+  // max over adjacent compass pairs of min(d_a, d_b) > t  (or the mirrored condition).
   {
-    const int npairs = npr * dh;
-    const unsigned inv = 65536u / (unsigned)npr + 1u;
-    const int tp = tile_pitch_w;
-    for (int p = tid; p < npairs; p += 128) {
-      const int r = (int)(((unsigned)p * inv) >> 16), m = p - r * npr;
+    const unsigned TH = (unsigned)(257 + min_th);
+    const unsigned addc = (0x8000u - TH) * 0x00010001u;
+    for (int p0 = 0; p0 < npairs; p0 += 128) {
+      const int p = p0 + tid;
+      bool pass = false;
+      if (p < npairs) {
+        const int m = fastdiv(p, invh, dh), r = p - m * dh;
+        const unsigned* T = s_tile + (r + 3) * TP + cbase + m;
+        const unsigned cb = T[0] + 0x01000100u;
+        const unsigned dN = cb - T[3 * TP], dS = cb - T[-3 * TP];
+        const unsigned dE = cb - odd_pair(T[1], T[2]), dW = cb - odd_pair(T[-2], T[-1]);
+        const unsigned qd = umax3(umin2(dN, dE), umin2(dE, dS), umax2(umin2(dS, dW), umin2(dW, dN)));
+        const unsigned qb = umin3(umax2(dN, dE), umax2(dE, dS), umin2(umax2(dS, dW), umax2(dW, dN)));
+        const unsigned x = umax2(qd, 0x02000200u - qb);
+        pass = ((x + addc) & 0x80008000u) != 0;
+      }
+      const unsigned bal = __ballot_sync(0xffffffffu, pass);
+      if (bal) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&s_np, __popc(bal));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (pass) s_plist[base + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)p;
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---- phase 2b: full score network on the listed pairs ----
+  {
+    const int np = s_np;
+    for (int i = tid; i < np; i += 128) {
+      const int p = s_plist[i];
+      const int m = fastdiv(p, invh, dh), r = p - m * dh;
       const int px = 2 * m - o;  // first pixel of the pair, cell-relative (may be -1)
-      const unsigned* T = s_tile + (r + 3) * tp + ((cx0 + px) >> 1);
+      const unsigned* T = s_tile + (r + 3) * TP + cbase + m;
       unsigned ring[16];
       {
-        const unsigned a = T[3 * tp - 1], b = T[3 * tp], c = T[3 * tp + 1];
+        const unsigned a = T[3 * TP - 1], b = T[3 * TP], c = T[3 * TP + 1];
         ring[0] = b; ring[1] = odd_pair(b, c); ring[15] = odd_pair(a, b);
       }
-      ring[2] = T[2 * tp + 1]; ring[14] = T[2 * tp - 1];
-      ring[3] = odd_pair(T[tp + 1], T[tp + 2]); ring[13] = odd_pair(T[tp - 2], T[tp - 1]);
+      ring[2] = T[2 * TP + 1]; ring[14] = T[2 * TP - 1];
+      ring[3] = odd_pair(T[TP + 1], T[TP + 2]); ring[13] = odd_pair(T[TP - 2], T[TP - 1]);
       ring[4] = odd_pair(T[1], T[2]); ring[12] = odd_pair(T[-2], T[-1]);
-      ring[5] = odd_pair(T[-tp + 1], T[-tp + 2]); ring[11] = odd_pair(T[-tp - 2], T[-tp - 1]);
-      ring[6] = T[-2 * tp + 1]; ring[10] = T[-2 * tp - 1];
+      ring[5] = odd_pair(T[-TP + 1], T[-TP + 2]); ring[11] = odd_pair(T[-TP - 2], T[-TP - 1]);
+      ring[6] = T[-2 * TP + 1]; ring[10] = T[-2 * TP - 1];
       {
-        const unsigned a = T[-3 * tp - 1], b = T[-3 * tp], c = T[-3 * tp + 1];
+        const unsigned a = T[-3 * TP - 1], b = T[-3 * TP], c = T[-3 * TP + 1];
         ring[8] = b; ring[7] = odd_pair(b, c); ring[9] = odd_pair(a, b);
       }
       unsigned A, B;
@@ -150,36 +193,33 @@ __global__ void __launch_bounds__(128) k_fast_cells(const ExtractorGeom* __restr
       const int s0 = max((int)(A & 0xFFFFu) - 257, 255 - (int)(B & 0xFFFFu));
       const int s1 = max((int)(A >> 16) - 257, 255 - (int)(B >> 16));
       unsigned char* q = s_score + (r + 1) * sp + px + 4;
-      if (px >= 0 && s0 >= min_th) q[0] = (unsigned char)s0;
-      if (px + 1 < dw && s1 >= min_th) q[1] = (unsigned char)s1;
+      if (px >= 0 && s0 >= min_th) {
+        q[0] = (unsigned char)s0;
+        s_clist[atomicAdd(&s_nc, 1)] = (unsigned short)((r << 7) | px);
+      }
+      if (px + 1 < dw && s1 >= min_th) {
+        q[1] = (unsigned char)s1;
+        s_clist[atomicAdd(&s_nc, 1)] = (unsigned short)((r << 7) | (px + 1));
+      }
     }
   }
   __syncthreads();
 
-  // ---- phase 3: NMS inside the cell, threshold choice, emit ----
+  // ---- phase 3: NMS inside the cell over the listed corners, threshold choice, emit ----
   bool any_ini = false;
   {
-    const int nw = (dw + 3) >> 2;
-    const int n = nw * dh;
-    const unsigned inv = 65536u / (unsigned)nw + 1u;
-    for (int i = tid; i < n; i += 128) {
-      const int r = (int)(((unsigned)i * inv) >> 16), cw = i - r * nw;
-      const unsigned char* q0 = s_score + (r + 1) * sp + 4 + 4 * cw;
-      const unsigned W = *reinterpret_cast<const unsigned*>(q0);
-      if (W == 0) continue;
-#pragma unroll
-      for (int k = 0; k < 4; k++) {
-        const int s = (W >> (8 * k)) & 0xFF;
-        if (s == 0) continue;
-        const unsigned char* q = q0 + k;
-        const bool lm = s > q[-1] && s > q[1] && s > q[-sp - 1] && s > q[-sp] && s > q[-sp + 1] &&
-                        s > q[sp - 1] && s > q[sp] && s > q[sp + 1];
-        if (lm) {
-          any_ini |= s >= ini_th;
-          // region coordinates of vToDistributeKeys: roi pt + (j*wCell, i*hCell)   (:842-846)
-          s_list[atomicAdd(&s_nlist, 1)] =
-              pack_cand(x0 + 4 * cw + k - FAST_BORDER, y0 + r - FAST_BORDER, s);
-        }
+    const int nc = s_nc;
+    for (int i = tid; i < nc; i += 128) {
+      const int e = s_clist[i];
+      const int r = e >> 7, px = e & 127;
+      const unsigned char* q = s_score + (r + 1) * sp + px + 4;
+      const int s = q[0];
+      const bool lm = s > q[-1] && s > q[1] && s > q[-sp - 1] && s > q[-sp] && s > q[-sp + 1] &&
+                      s > q[sp - 1] && s > q[sp] && s > q[sp + 1];
+      if (lm) {
+        any_ini |= s >= ini_th;
+        // region coordinates of vToDistributeKeys: roi pt + (j*wCell, i*hCell)   (:842-846)
+        s_list[atomicAdd(&s_nlist, 1)] = pack_cand(x0 + px - FAST_BORDER, y0 + r - FAST_BORDER, s);
       }
     }
   }
@@ -206,23 +246,31 @@ __global__ void __launch_bounds__(128) k_fast_cells(const ExtractorGeom* __restr
   for (int n = tid; n < nout; n += 128) out[n] = s_out[n];
 }
 
-void launch_fast(const ExtractorGeom& g, const ExtractorGeom* dg, int n_img, const uint8_t* pyr,
-                 unsigned* cand, int* cand_count, int* flags, cudaStream_t st) {
-  // tile: columns 0 .. 7 + max_cell_w + 4 (+ alignment), as u16 pairs -> words
-  const int tile_cols   = (7 + g.max_cell_w + 5 + 3 + 3) & ~3;
-  const int tile_pitch_w = tile_cols / 2;                         // even: rows stay 8-byte aligned
-  const int tile_bytes  = ((tile_pitch_w * 4 * (g.max_cell_h + 6) + 15) / 16) * 16;
-  const int sp_max      = (g.max_cell_w + 5 + 3) & ~3;
+template <int TP>
+static void launch_fast_tp(const ExtractorGeom& g, const ExtractorGeom* dg, int n_img, const uint8_t* pyr,
+                           unsigned* cand, int* cand_count, int* flags, cudaStream_t st) {
+  const int tile_bytes  = ((TP * 4 * (g.max_cell_h + 6) + 15) / 16) * 16;
+  const int sp_max      = ((((g.max_cell_w + 5 + 3) >> 2) | 1) << 2);
   const int score_bytes = ((sp_max * (g.max_cell_h + 2) + 15) / 16) * 16;
+  const int plist_bytes = ((2 * ((g.max_cell_w + 2) / 2) * g.max_cell_h + 15) / 16) * 16;
+  const int clist_bytes = ((2 * g.max_cell_w * g.max_cell_h + 15) / 16) * 16;
   const int list_bytes  = 4 * ((g.max_cell_w + 1) / 2) * ((g.max_cell_h + 1) / 2);
-  const int smem        = tile_bytes + score_bytes + list_bytes;
+  const int smem        = tile_bytes + score_bytes + plist_bytes + clist_bytes + list_bytes;
   static int attr = 48 * 1024;
   if (smem > attr) {
-    cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaFuncSetAttribute(k_fast_cells<TP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     attr = smem;
   }
-  k_fast_cells<<<dim3(g.total_cells, n_img), 128, smem, st>>>(dg, pyr, cand, cand_count, flags,
-                                                              tile_pitch_w, tile_bytes, score_bytes);
+  k_fast_cells<TP><<<dim3(g.total_cells, n_img), 128, smem, st>>>(dg, pyr, cand, cand_count, flags, tile_bytes,
+                                                                  score_bytes, plist_bytes, clist_bytes);
+}
+
+void launch_fast(const ExtractorGeom& g, const ExtractorGeom* dg, int n_img, const uint8_t* pyr,
+                 unsigned* cand, int* cand_count, int* flags, cudaStream_t st) {
+  // tile columns 0 .. (6 + max_cell_w + 2 + 4 + alignment) as u16 pairs -> words; cell height
+  // below 512 and width below 128 for the packed corner list
+  if (g.max_cell_w + 16 <= 2 * 29) launch_fast_tp<29>(g, dg, n_img, pyr, cand, cand_count, flags, st);
+  else launch_fast_tp<71>(g, dg, n_img, pyr, cand, cand_count, flags, st);
   count_launch();
 }
 
