@@ -1,0 +1,49 @@
+"""GPU (-m gpu): the C++ drop-in shim (shim/ORBextractor.h, shim/ORBmatcher.h) compiled with g++
+against libcuorb.so, driven like the reference's stereo Frame constructor (src/Frame.cc:202-225),
+and compared bit for bit with the CPU oracle."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import oracle_py as op
+from orbslam3_cpp_fork_b200 import _lib, build, synth
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_cpp_shim_stereo_frame(tmp_path):
+    build.build_libcuorb()
+    exe = str(tmp_path / "shim_check")
+    pkg = os.path.join(ROOT, "orbslam3_cpp_fork_b200")
+    subprocess.check_call(["g++", "-std=c++17", "-O2", os.path.join(ROOT, "tests", "native", "shim_check.cpp"), "-o", exe,
+                           "-L" + pkg, "-l:libcuorb.so", "-Wl,-rpath," + pkg])
+    w, h, nf = 640, 480, 1000
+    fx, mbf = 525.0, 40.0
+    mb = mbf / fx
+    left, right = synth.synth_stereo_pair(w, h, seed=21)
+    left.tofile(tmp_path / "l.raw"); right.tofile(tmp_path / "r.raw")
+    out = str(tmp_path / "out.bin")
+    subprocess.check_call([exe, str(tmp_path / "l.raw"), str(tmp_path / "r.raw"), str(w), str(h), str(nf), repr(mb), repr(mbf), out])
+    raw = open(out, "rb").read()
+    hdr = np.frombuffer(raw, np.int32, 8)
+    nl, nr, mono_l, mono_r, selfdist, d01, pw, ph = [int(v) for v in hdr]
+    off = 32
+    kl = np.frombuffer(raw, _lib.KP_DTYPE, nl, off); off += 28 * nl
+    dl = np.frombuffer(raw, np.uint8, 32 * nl, off).reshape(nl, 32); off += 32 * nl
+    kr = np.frombuffer(raw, _lib.KP_DTYPE, nr, off); off += 28 * nr
+    dr = np.frombuffer(raw, np.uint8, 32 * nr, off).reshape(nr, 32); off += 32 * nr
+    ur = np.frombuffer(raw, np.float32, nl, off); off += 4 * nl
+    dp = np.frombuffer(raw, np.float32, nl, off); off += 4 * nl
+    pyr1 = np.frombuffer(raw, np.uint8, pw * ph, off).reshape(ph, pw)
+
+    oL, oR = op.OracleExtractor(nf, 1.2, 8, 20, 7), op.OracleExtractor(nf, 1.2, 8, 20, 7)
+    m0, k0, d0 = oL.extract(left); m1, k1, d1 = oR.extract(right)
+    assert (nl, nr, mono_l, mono_r) == (len(k0), len(k1), m0, m1)
+    assert (kl == k0).all() and (dl == d0).all() and (kr == k1).all() and (dr == d1).all()
+    so = op.stereo(oL, oR, k0, d0, k1, d1, np.float32(mb), np.float32(mbf))
+    assert (ur == so["u_right"]).all() and (dp == so["depth"]).all()
+    assert selfdist == 0 and d01 == int(np.unpackbits(d0[0] ^ d0[1]).sum())
+    assert (pyr1 == oL.plane(1, 1)).all()
