@@ -120,7 +120,10 @@ struct StereoArgs {
   float mb, mbf;
   float *u_right, *depth;
   int *best_idx_r, *best_dist, *sad;
+  uint4* rtab;   // right keypoints bucketed by row band: {minr | maxr<<13 | octave<<26, x bits, iR, 0}
+  int*   rstart; // per image STEREO_MAX_BUCKETS + 1 bucket starts
 };
+constexpr int STEREO_MAX_BUCKETS = 512;  // 8-row buckets: level-0 height below 4096
 void launch_stereo(const ExtractorGeom& g, const StereoArgs& a, cudaStream_t st);
 
 }  // namespace cuorb

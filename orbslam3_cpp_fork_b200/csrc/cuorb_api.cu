@@ -50,6 +50,8 @@ struct cuorb_extractor {
   int *      d_out_n = nullptr, *d_out_mono = nullptr;
   float *    d_uright = nullptr, *d_depth = nullptr;
   int *      d_sad = nullptr, *d_best_idx = nullptr, *d_best_dist = nullptr;
+  uint4*     d_rtab = nullptr;        // stereo: right keypoints bucketed by row (per image kp_cap entries)
+  int*       d_rstart = nullptr;      // stereo: bucket starts (per image STEREO_MAX_BUCKETS + 1)
   // pinned host mirrors of the small per-image results
   int *h_out_n = nullptr, *h_out_mono = nullptr, *h_flags = nullptr;
   size_t cap_input = 0, cap_pyr = 0, cap_blur = 0, cap_cand = 0, cap_keys = 0, cap_kp = 0;
@@ -200,7 +202,7 @@ static void free_all(cuorb_extractor* e) {
   void* dev[] = {e->d_geom, e->d_xtab, e->d_ytab, e->d_blur_tiles, e->d_input, e->d_pyr, e->d_blur,
                  e->d_cand, e->d_cand_scratch, e->d_cand_count, e->d_key_count, e->d_flags, e->d_slot,
                  e->d_keys, e->d_out_kps, e->d_out_desc, e->d_out_n, e->d_out_mono, e->d_uright,
-                 e->d_depth, e->d_sad, e->d_best_idx, e->d_best_dist};
+                 e->d_depth, e->d_sad, e->d_best_idx, e->d_best_dist, e->d_rtab, e->d_rstart};
   for (void* p : dev) if (p) cudaFree(p);
   void* host[] = {e->h_out_n, e->h_out_mono, e->h_flags};
   for (void* p : host) if (p) cudaFreeHost(p);
@@ -315,6 +317,8 @@ cuorb_extractor* cuorb_extractor_create(const cuorb_config* cfg) {
   ok &= dev_alloc(&e->d_depth, e->cap_kp) == cudaSuccess;
   ok &= dev_alloc(&e->d_sad, e->cap_kp) == cudaSuccess;
   ok &= dev_alloc(&e->d_best_idx, e->cap_kp) == cudaSuccess;
+  ok &= dev_alloc(&e->d_rtab, e->cap_kp) == cudaSuccess;
+  ok &= dev_alloc(&e->d_rstart, nb * (STEREO_MAX_BUCKETS + 1)) == cudaSuccess;
   ok &= dev_alloc(&e->d_best_dist, e->cap_kp) == cudaSuccess;
   ok &= cudaMallocHost((void**)&e->h_out_n, nb * sizeof(int)) == cudaSuccess;
   ok &= cudaMallocHost((void**)&e->h_out_mono, nb * sizeof(int)) == cudaSuccess;
@@ -573,6 +577,7 @@ int cuorb_stereo_match_batch_async(cuorb_extractor* l, cuorb_extractor* r, float
   a.nL = l->d_out_n; a.nR = r->d_out_n; a.kp_cap = l->g.kp_cap; a.n_img = l->n_img;
   a.mb = mb; a.mbf = mbf; a.u_right = l->d_uright; a.depth = l->d_depth;
   a.best_idx_r = l->d_best_idx; a.best_dist = l->d_best_dist; a.sad = l->d_sad;
+  a.rtab = l->d_rtab; a.rstart = l->d_rstart;
   launch_stereo(l->g, a, l->stream);
   if (l->profiling) { cudaEventRecord(l->ev_stage[CUORB_STAGE_COUNT], l->stream); l->stereo_timed = true; }
   CUORB_CUDA_TRY(cudaGetLastError());

@@ -2,13 +2,19 @@
 // path BASELINE.json calls "SearchStereo").  Device-resident: consumes the keypoints, descriptors
 // and pyramids the two extractor handles left in HBM.
 //
-// k_stereo_match: one warp per left keypoint.  The reference's per-row candidate table
-//   (:953-971) is replaced by evaluating its membership predicate directly
-//   (floor(yR - r) <= int(vL) <= ceil(yR + r), r = 2*scale[octR]) for every right keypoint: lanes
-//   stride over iR, so the ascending-iR visiting order and the strict "<" of :1021 become a warp
-//   arg-min on the key (dist << 16 | iR).  Hamming = 8 x (XOR, POPC) per pair.  The winner is
-//   refined by the 11-window SAD slide on the un-blurred pyramid level (:1028-1067, lanes 0..10 own
-//   one patch row each) and the parabola fit (:1074-1098) in FMA-free float.
+// k_stereo_rows: one CTA per image.  The reference's per-row candidate table (vRowIndices,
+//   :953-971) becomes a counting sort of the right keypoints into 8-row buckets of their y; an
+//   entry carries the exact membership interval [floor(y-r), ceil(y+r)], r = 2*scale[octave],
+//   the octave, x and the original index iR.
+// k_stereo_match: one warp per left keypoint.  Only the buckets that can hold a right keypoint
+//   whose interval contains int(vL) are scanned (a few dozen entries instead of all ~1000); the
+//   reference's predicates (:1007-1018) are evaluated exactly, Hamming = 8 x (XOR, POPC), and the
+//   ascending-iR visiting order with strict "<" (:1021) becomes a warp arg-min on the key
+//   (dist << 16 | iR), which makes the bucket order irrelevant.  The winner is refined by the
+//   11-window SAD slide on the un-blurred pyramid level (:1028-1067): lane (2*row + half) owns one
+//   patch row and half of the 11 shifts, rows are fetched as aligned words, re-aligned with
+//   funnel shifts and compared 4 pixels per VABSDIFF4; a butterfly sums the rows.  The parabola
+//   fit (:1074-1098) runs in FMA-free float.
 // k_stereo_outliers: one CTA per image.  median = element size/2 of the sorted SAD list (:1101-1103)
 //   by a two-level histogram select; matches with SAD >= 1.5*1.4*median are reset (:1105-1112).
 #include "common.cuh"
@@ -16,13 +22,64 @@
 namespace cuorb {
 
 constexpr int TH_HIGH = 100, TH_LOW = 50;  // src/ORBmatcher.cc:30-31
+constexpr int BUCKET_SHIFT = 3;
+
+__device__ __forceinline__ int row_bucket(float y, int nb) {
+  return min(max((int)y, 0) >> BUCKET_SHIFT, nb - 1);
+}
+
+// grid: n_img, block 256
+__global__ void __launch_bounds__(256) k_stereo_rows(StereoArgs A) {
+  __shared__ int s_cnt[STEREO_MAX_BUCKETS + 1];
+  __shared__ int s_warp[8];
+  const ExtractorGeom* dg = A.dgL;
+  const int img = blockIdx.x, tid = threadIdx.x;
+  const int nR = A.nR[img];
+  const int nb = min((dg->lv[0].h + (1 << BUCKET_SHIFT) - 1) >> BUCKET_SHIFT, STEREO_MAX_BUCKETS);
+  const size_t base = (size_t)img * A.kp_cap;
+  for (int b = tid; b <= STEREO_MAX_BUCKETS; b += 256) s_cnt[b] = 0;
+  __syncthreads();
+  for (int i = tid; i < nR; i += 256) atomicAdd(&s_cnt[row_bucket(A.kpsR[base + i].y, nb)], 1);
+  __syncthreads();
+  // exclusive scan of s_cnt[0..nb) (two buckets per thread)
+  {
+    const int b0 = 2 * tid, b1 = 2 * tid + 1;
+    const int c0 = b0 < nb ? s_cnt[b0] : 0, c1 = b1 < nb ? s_cnt[b1] : 0;
+    int inc = c0 + c1;
+    const int lane = tid & 31, wid = tid >> 5;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+    if (lane == 31) s_warp[wid] = inc;
+    __syncthreads();
+    int woff = 0;
+    for (int w = 0; w < wid; w++) woff += s_warp[w];
+    const int ex = woff + inc - (c0 + c1);
+    __syncthreads();
+    if (b0 < nb) s_cnt[b0] = ex;
+    if (b1 < nb) s_cnt[b1] = ex + c0;
+    if (tid == 0) s_cnt[nb] = nR;
+  }
+  __syncthreads();
+  int* gstart = A.rstart + (size_t)img * (STEREO_MAX_BUCKETS + 1);
+  for (int b = tid; b <= nb; b += 256) gstart[b] = s_cnt[b];
+  __syncthreads();
+  for (int i = tid; i < nR; i += 256) {
+    const cuorb_keypoint kp = A.kpsR[base + i];
+    const float r = __fmul_rn(2.0f, dg->lv[kp.octave].scale);                         // :963
+    const int maxr = (int)ceilf(__fadd_rn(kp.y, r)), minr = (int)floorf(__fsub_rn(kp.y, r));  // :965-966
+    const int pos = atomicAdd(&s_cnt[row_bucket(kp.y, nb)], 1);
+    A.rtab[base + pos] = make_uint4((unsigned)min(max(minr, 0), 8191) | ((unsigned)min(max(maxr, 0), 8191) << 13) |
+                                        ((unsigned)kp.octave << 26),
+                                    __float_as_uint(kp.x), (unsigned)i, 0u);
+  }
+}
 
 // grid: (ceil(kp_cap/8), n_img), block 256
-__global__ void __launch_bounds__(256) k_stereo_match(StereoArgs A) {
+__global__ void __launch_bounds__(256) k_stereo_match(StereoArgs A, int band) {
   const ExtractorGeom* dg = A.dgL;
   const int img = blockIdx.y, lane = threadIdx.x & 31;
   const int iL = blockIdx.x * 8 + (threadIdx.x >> 5);
-  const int nL = A.nL[img], nR = A.nR[img];
+  const int nL = A.nL[img];
   if (iL >= nL) return;
   const size_t base = (size_t)img * A.kp_cap;
   const cuorb_keypoint kpL = A.kpsL[base + iL];
@@ -39,16 +96,18 @@ __global__ void __launch_bounds__(256) k_stereo_match(StereoArgs A) {
   if (row >= 0 && row < nRows && !(maxU < 0.f)) {
     const uint4* dl = reinterpret_cast<const uint4*>(A.descL + (base + iL) * 32);
     const uint4 l0 = dl[0], l1 = dl[1];
-    for (int iR = lane; iR < nR; iR += 32) {
-      const cuorb_keypoint* kr = A.kpsR + base + iR;
-      const int octR = kr->octave;
-      if (octR < levelL - 1 || octR > levelL + 1) continue;
-      const float yR = kr->y;
-      const float r = __fmul_rn(2.0f, dg->lv[octR].scale);
-      const int maxr = (int)ceilf(__fadd_rn(yR, r)), minr = (int)floorf(__fsub_rn(yR, r));
-      if (row < minr || row > maxr) continue;
-      const float uR = kr->x;
-      if (!(uR >= minU && uR <= maxU)) continue;
+    const int nb = min((nRows + (1 << BUCKET_SHIFT) - 1) >> BUCKET_SHIFT, STEREO_MAX_BUCKETS);
+    const int* gstart = A.rstart + (size_t)img * (STEREO_MAX_BUCKETS + 1);
+    const int lo = gstart[max(row - band, 0) >> BUCKET_SHIFT];
+    const int hi = gstart[min(((row + band) >> BUCKET_SHIFT) + 1, nb)];
+    for (int j = lo + lane; j < hi; j += 32) {
+      const uint4 e = A.rtab[base + j];
+      const int minr = e.x & 0x1FFF, maxr = (e.x >> 13) & 0x1FFF, octR = e.x >> 26;
+      if (row < minr || row > maxr) continue;                           // vRowIndices membership
+      if (octR < levelL - 1 || octR > levelL + 1) continue;             // :1011
+      const float uR = __uint_as_float(e.y);
+      if (!(uR >= minU && uR <= maxU)) continue;                        // :1017
+      const int iR = (int)e.z;
       const uint4* dr = reinterpret_cast<const uint4*>(A.descR + (base + iR) * 32);
       const uint4 r0 = dr[0], r1 = dr[1];
       const int dist = __popc(l0.x ^ r0.x) + __popc(l0.y ^ r0.y) + __popc(l0.z ^ r0.z) + __popc(l0.w ^ r0.w) +
@@ -71,34 +130,46 @@ __global__ void __launch_bounds__(256) k_stereo_match(StereoArgs A) {
     const int w = 5, Lw = 5;
     const float iniu = scaleduR0 + Lw - w, endu = scaleduR0 + Lw + w + 1;
     if (!(iniu < 0 || endu >= (float)G.w)) {
-      int sad[11];
+      // lane = 2*row + half: half 0 owns shifts 0..5, half 1 shifts 6..10 (its 6th value is unused)
+      const int prow = min(lane >> 1, 10), half = lane & 1;
+      unsigned part[6] = {0, 0, 0, 0, 0, 0};
+      {
+        const int y = (int)(scaledvL - w) + prow;
+        const size_t rowoff = (size_t)img * dg->pyr_img_stride + G.pix_off + (ptrdiff_t)y * G.pitch;
+        const uint8_t* pl = A.pyrL + rowoff + (int)(scaleduL - w);
+        const uint8_t* pr = A.pyrR + rowoff + (int)(scaleduR0 - Lw - w) + 6 * half;
+        const unsigned offl = (unsigned)((uintptr_t)pl & 3), offr = (unsigned)((uintptr_t)pr & 3);
+        const unsigned* al = reinterpret_cast<const unsigned*>(pl - offl);
+        const unsigned* ar = reinterpret_cast<const unsigned*>(pr - offr);
+        const unsigned a0 = al[0], a1 = al[1], a2 = al[2], a3 = al[3];
+        unsigned rw[6];
 #pragma unroll
-      for (int k = 0; k < 11; k++) sad[k] = 0;
-      if (lane < 11) {
-        const int y = (int)(scaledvL - w) + lane;
-        const uint8_t* pl = A.pyrL + (size_t)img * dg->pyr_img_stride + G.pix_off + (ptrdiff_t)y * G.pitch +
-                            (int)(scaleduL - w);
-        const uint8_t* pr = A.pyrR + (size_t)img * dg->pyr_img_stride + G.pix_off + (ptrdiff_t)y * G.pitch +
-                            (int)(scaleduR0 - Lw - w);
-        int lv[11], rv[21];
+        for (int k = 0; k < 6; k++) rw[k] = ar[k];
+        const unsigned L0 = __funnelshift_r(a0, a1, 8 * offl), L1 = __funnelshift_r(a1, a2, 8 * offl),
+                       L2 = __funnelshift_r(a2, a3, 8 * offl) & 0x00FFFFFFu;
+        unsigned R[5];
 #pragma unroll
-        for (int k = 0; k < 11; k++) lv[k] = pl[k];
+        for (int k = 0; k < 5; k++) R[k] = __funnelshift_r(rw[k], rw[k + 1], 8 * offr);
 #pragma unroll
-        for (int k = 0; k < 21; k++) rv[k] = pr[k];
+        for (int s = 0; s < 6; s++) {
+          const int q = s >> 2, sh = 8 * (s & 3);
+          const unsigned r0 = __funnelshift_r(R[q], R[q + 1], sh), r1 = __funnelshift_r(R[q + 1], R[q + 2], sh),
+                         r2 = __funnelshift_r(R[q + 2], R[(q + 3) < 5 ? q + 3 : 4], sh) & 0x00FFFFFFu;
+          part[s] = __vsadu4(L0, r0) + __vsadu4(L1, r1) + __vsadu4(L2, r2);
+        }
+        if (lane >= 22) {
 #pragma unroll
-        for (int k = 0; k < 11; k++) {
-          int s = 0;
-#pragma unroll
-          for (int x = 0; x < 11; x++) s += abs(lv[x] - rv[k + x]);
-          sad[k] = s;
+          for (int s = 0; s < 6; s++) part[s] = 0;
         }
       }
 #pragma unroll
-      for (int k = 0; k < 11; k++) {
+      for (int s = 0; s < 6; s++) {
 #pragma unroll
-        for (int o = 8; o > 0; o >>= 1) sad[k] += __shfl_xor_sync(0xffffffffu, sad[k], o);
+        for (int o = 2; o < 32; o <<= 1) part[s] += __shfl_xor_sync(0xffffffffu, part[s], o);
       }
-      // lanes 0..15 now hold the totals (lanes 11..15 contributed zeros)
+      int sad[11];
+#pragma unroll
+      for (int k = 0; k < 11; k++) sad[k] = (int)__shfl_sync(0xffffffffu, part[k < 6 ? k : k - 6], k < 6 ? 0 : 1);
       int bestSad = 0x7fffffff, bestinc = 0;
 #pragma unroll
       for (int k = 0; k < 11; k++)
@@ -181,9 +252,12 @@ __global__ void __launch_bounds__(256) k_stereo_outliers(StereoArgs A) {
 }
 
 void launch_stereo(const ExtractorGeom& g, const StereoArgs& a, cudaStream_t st) {
-  k_stereo_match<<<dim3((g.kp_cap + 7) / 8, a.n_img), 256, 0, st>>>(a);
+  // a right keypoint can register in rows up to ceil(2*scale_max)+1 away from its own
+  const int band = (int)ceilf(2.0f * g.lv[g.nlevels - 1].scale) + 2;
+  k_stereo_rows<<<a.n_img, 256, 0, st>>>(a);
+  k_stereo_match<<<dim3((g.kp_cap + 7) / 8, a.n_img), 256, 0, st>>>(a, band);
   k_stereo_outliers<<<a.n_img, 256, 0, st>>>(a);
-  count_launch(2);
+  count_launch(3);
 }
 
 }  // namespace cuorb
