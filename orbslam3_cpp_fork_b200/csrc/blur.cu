@@ -1,93 +1,83 @@
 // K7 — 7x7 sigma-2 Gaussian blur of every pyramid level (replaces the per-level
 // clone() + cv::GaussianBlur(7x7, 2, 2, BORDER_REFLECT_101), src/ORBextractor.cc:1103-1104).
 // OpenCV's CV_8U path is fixed point: kernel {18,34,48,56,48,34,18}/256, rows in 8.8, columns in
-// 16.16, result (v + 32768) >> 16.  The REFLECT_101 halo is the border K1 already stored, so the
-// tile loader never reflects.  Separable in shared memory: 128x32 output tile per 256-thread CTA,
-// aligned 32-bit loads, 16-bit row sums, uchar4 stores.  Bound: HBM (read P, write P).
+// 16.16, result (v + 32768) >> 16.  The REFLECT_101 halo is the border K1 already stored, so no
+// reflection is computed here.
+//
+// One thread owns one aligned output word (4 px) and walks down a strip of rows, entirely in
+// registers: per source row three aligned 32-bit loads, the four 7-tap row sums as two DP4A each
+// on funnel-shifted words (taps {18,34,48,56} and {48,34,18,0}), and a rolling window of the last
+// seven row sums feeds the column pass (symmetric taps: 3 adds + 4 IMAD per pixel).  No shared
+// memory, no barriers; the loop is unrolled by 7 so the window rotates by register renaming.
+// Bound: HBM (read P, write P); ~14 instructions per pixel.
 #include "common.cuh"
 
 namespace cuorb {
 
-constexpr int BT_W = 128, BT_H = 32, BT_IN_H = BT_H + 6, BT_IN_WORDS = (BT_W + 8) / 4;
+constexpr int BL_THREADS = 64;   // words (4 px each) per CTA row segment
+constexpr int BL_ROWS    = 32;   // output rows per thread strip
 
-// grid: (tiles over all levels, n_img); tile list in constant-sized table passed by pointer
-__global__ void __launch_bounds__(256) k_blur(const ExtractorGeom* __restrict__ dg,
-                                              const int4* __restrict__ tiles,
-                                              const uint8_t* __restrict__ pyr,
-                                              uint8_t* __restrict__ blur) {
-  __shared__ unsigned       s_in[BT_IN_H][BT_IN_WORDS];  // bytes x0-4 .. x0+131
-  __shared__ unsigned short s_mid[BT_IN_H][BT_W];
+__device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ row, unsigned (&h)[4]) {
+  const unsigned* p = reinterpret_cast<const unsigned*>(row);
+  const unsigned A = p[-1], B = p[0], C = p[1];
+  const unsigned K0 = 18u | (34u << 8) | (48u << 16) | (56u << 24), K1 = 48u | (34u << 8) | (18u << 16);
+  h[0] = __dp4a(__funnelshift_r(A, B, 8), K0, __dp4a(__funnelshift_r(B, C, 8), K1, 0u));
+  h[1] = __dp4a(__funnelshift_r(A, B, 16), K0, __dp4a(__funnelshift_r(B, C, 16), K1, 0u));
+  h[2] = __dp4a(__funnelshift_r(A, B, 24), K0, __dp4a(__funnelshift_r(B, C, 24), K1, 0u));
+  h[3] = __dp4a(B, K0, __dp4a(C, K1, 0u));
+}
 
+// grid: (tiles over all levels, n_img); tiles = (level, word block, row strip)
+__global__ void __launch_bounds__(BL_THREADS) k_blur(const ExtractorGeom* __restrict__ dg,
+                                                     const int4* __restrict__ tiles,
+                                                     const uint8_t* __restrict__ pyr,
+                                                     uint8_t* __restrict__ blur) {
   const int4 t = tiles[blockIdx.x];
   const LevelGeom& L = dg->lv[t.x];
-  const int x0 = t.y * BT_W, y0 = t.z * BT_H;
+  const int word = t.y * BL_THREADS + threadIdx.x;
+  if (word * 4 >= L.bpitch) return;
   const int img = blockIdx.y;
-  const uint8_t* src = pyr + (size_t)img * dg->pyr_img_stride + L.pix_off;
-  const int tid = threadIdx.x;
+  const int y0 = t.z * BL_ROWS, y1 = min(y0 + BL_ROWS, L.h);
+  const uint8_t* src = pyr + (size_t)img * dg->pyr_img_stride + L.pix_off + word * 4;
+  uint8_t* dst = blur + (size_t)img * dg->blur_img_stride + L.blur_off + word * 4;
+  const int pitch = L.pitch, bpitch = L.bpitch;
 
-  for (int i = tid; i < BT_IN_H * BT_IN_WORDS; i += 256) {
-    const int r = i / BT_IN_WORDS, c = i % BT_IN_WORDS;
-    const int y = min(y0 - 3 + r, L.h + EDGE_THRESHOLD - 1);  // rows past the border are unused
-    const int xb = min(x0 - 4 + c * 4, L.pitch - ROW_LEAD - 4);  // stay inside the padded row
-    s_in[r][c] = *reinterpret_cast<const unsigned*>(src + (ptrdiff_t)y * L.pitch + xb);
-  }
-  __syncthreads();
-
-  const int lx = tid & 31, ly = tid >> 5;
-  // horizontal pass: 4 px per thread per row
-  for (int r = ly; r < BT_IN_H; r += 8) {
-    const unsigned w0 = s_in[r][lx], w1 = s_in[r][lx + 1], w2 = s_in[r][lx + 2];
-    // bytes at tile offsets lx*4+1 .. lx*4+10  (x-3 .. x+6 for x = x0 + lx*4)
-    int p[10];
-    p[0] = (w0 >> 8) & 0xFF; p[1] = (w0 >> 16) & 0xFF; p[2] = w0 >> 24;
-    p[3] = w1 & 0xFF; p[4] = (w1 >> 8) & 0xFF; p[5] = (w1 >> 16) & 0xFF; p[6] = w1 >> 24;
-    p[7] = w2 & 0xFF; p[8] = (w2 >> 8) & 0xFF; p[9] = (w2 >> 16) & 0xFF;
-    unsigned short o[4];
+  unsigned win[7][4];  // row sums of source rows y-3 .. y+3
 #pragma unroll
-    for (int k = 0; k < 4; k++)
-      o[k] = (unsigned short)(18 * (p[k] + p[k + 6]) + 34 * (p[k + 1] + p[k + 5]) +
-                              48 * (p[k + 2] + p[k + 4]) + 56 * p[k + 3]);
-    *reinterpret_cast<uint2*>(&s_mid[r][lx * 4]) =
-        make_uint2(o[0] | ((unsigned)o[1] << 16), o[2] | ((unsigned)o[3] << 16));
-  }
-  __syncthreads();
-
-  // vertical pass: 4 rows x 4 px per thread
-  unsigned m[10][4];
+  for (int j = 0; j < 6; j++) blur_hrow(src + (ptrdiff_t)(y0 - 3 + j) * pitch, win[j]);
+  for (int yb = y0; yb < y1; yb += 7) {
 #pragma unroll
-  for (int r = 0; r < 10; r++) {
-    const uint2 v = *reinterpret_cast<const uint2*>(&s_mid[ly * 4 + r][lx * 4]);
-    m[r][0] = v.x & 0xFFFF; m[r][1] = v.x >> 16; m[r][2] = v.y & 0xFFFF; m[r][3] = v.y >> 16;
-  }
-  uint8_t* dst = blur + (size_t)img * dg->blur_img_stride + L.blur_off;
-  const int x = x0 + lx * 4;
-  if (x < L.bpitch) {
+    for (int u = 0; u < 7; u++) {
+      const int y = yb + u;
+      if (y < y1) {
+        // slot (u + 6) % 7 receives source row y + 3; the window then is slots u, u+1, ..., u+6 (mod 7)
+        blur_hrow(src + (ptrdiff_t)(y + 3) * pitch, win[(u + 6) % 7]);
+        unsigned out = 0;
 #pragma unroll
-    for (int r = 0; r < 4; r++) {
-      const int y = y0 + ly * 4 + r;
-      if (y >= L.h) break;
-      unsigned out = 0;
-#pragma unroll
-      for (int k = 0; k < 4; k++) {
-        const unsigned acc = 18u * (m[r][k] + m[r + 6][k]) + 34u * (m[r + 1][k] + m[r + 5][k]) +
-                             48u * (m[r + 2][k] + m[r + 4][k]) + 56u * m[r + 3][k];
-        out |= ((acc + 32768u) >> 16) << (8 * k);
+        for (int k = 0; k < 4; k++) {
+          const unsigned acc = 32768u + 18u * (win[u][k] + win[(u + 6) % 7][k]) +
+                               34u * (win[(u + 1) % 7][k] + win[(u + 5) % 7][k]) +
+                               48u * (win[(u + 2) % 7][k] + win[(u + 4) % 7][k]) + 56u * win[(u + 3) % 7][k];
+          out |= (acc >> 16) << (8 * k);
+        }
+        *reinterpret_cast<unsigned*>(dst + (size_t)y * bpitch) = out;
       }
-      *reinterpret_cast<unsigned*>(dst + (size_t)y * L.bpitch + x) = out;
     }
   }
 }
 
 void build_blur_tiles(const ExtractorGeom& g, std::vector<int4>& v) {
   v.clear();
-  for (int l = 0; l < g.nlevels; l++)
-    for (int ty = 0; ty < (g.lv[l].h + BT_H - 1) / BT_H; ty++)
-      for (int tx = 0; tx < (g.lv[l].w + BT_W - 1) / BT_W; tx++) v.push_back(make_int4(l, tx, ty, 0));
+  for (int l = 0; l < g.nlevels; l++) {
+    const int nwb = (g.lv[l].bpitch / 4 + BL_THREADS - 1) / BL_THREADS;
+    for (int ty = 0; ty < (g.lv[l].h + BL_ROWS - 1) / BL_ROWS; ty++)
+      for (int tx = 0; tx < nwb; tx++) v.push_back(make_int4(l, tx, ty, 0));
+  }
 }
 
 void launch_blur(const ExtractorGeom*, const ExtractorGeom* dg, int n_img, const int4* tiles,
                  int n_tiles, const uint8_t* pyr, uint8_t* blur, cudaStream_t st) {
-  k_blur<<<dim3(n_tiles, n_img), 256, 0, st>>>(dg, tiles, pyr, blur);
+  k_blur<<<dim3(n_tiles, n_img), BL_THREADS, 0, st>>>(dg, tiles, pyr, blur);
   count_launch();
 }
 
