@@ -5,11 +5,17 @@
 // k_finalize: one CTA per image.  Level offsets, then the reference's two-ended scatter
 //   (keypoints inside vLappingArea go to the back, the others to the front) turned into a block
 //   scan over the "stereo" flags.
-// k_describe: one warp per keypoint.  Lanes 0..30 each sum one row of the radius-15 disc
-//   (int32 moments, shuffle reduction); cv::fastAtan2 is evaluated with explicit _rn intrinsics so
-//   no FMA is contracted (bit-exact with OpenCV's scalar float code); lane l then builds descriptor
-//   byte l from 16 rotated taps of the blurred level.  cos/sin are taken in double and rounded to
-//   float (the reference uses glibc cosf/sinf; see DESIGN.md "float reproducibility").
+// k_describe: one CTA per 32 keypoints (8 warps x 4), three phases.
+//   A  IC_Angle: a warp per keypoint, lane = patch row.  The row is fetched as nine aligned 32-bit
+//      words; the radius-15 disc is a per-lane byte mask, and the two integer moments are DP4A
+//      dot products (sum I, sum position*I; the position weights are compile-time constants, the
+//      centre offset is subtracted afterwards), reduced with shuffles.
+//   B  one lane per keypoint: cv::fastAtan2 with explicit _rn intrinsics (no FMA contraction,
+//      bit-exact with OpenCV's scalar float code) and cos/sin taken in double and rounded to float
+//      (the reference uses glibc cosf/sinf; see DESIGN.md "float policy") — 32 keypoints at once
+//      instead of one lane of a warp per keypoint.
+//   C  steered BRIEF: a warp per keypoint, lane l builds descriptor byte l from 16 rotated taps
+//      of the blurred level; the pattern is read as pre-converted float4 pairs.
 #include <cfloat>
 
 #include "../../include/cuorb_pattern.h"
@@ -17,7 +23,7 @@
 
 namespace cuorb {
 
-__device__ int4 d_pattern[64];  // 256 pairs x (x0,y0,x1,y1) int8; lane l reads int4 2l, 2l+1
+__device__ float4 d_patternf[256];  // 256 pairs (x0,y0,x1,y1) as float; lane l reads pairs 8l .. 8l+7
 __constant__ int c_umax[16];
 
 // IEEE, FMA-free restatement of OpenCV's scalar fastAtan2 (core/mathfuncs_core.simd.hpp)
@@ -88,7 +94,12 @@ __global__ void __launch_bounds__(256) k_finalize(const ExtractorGeom* __restric
   if (tid == 0) { out_n[img] = n; out_mono[img] = n - s_run; }
 }
 
-// grid: (ceil(kp_cap/8), n_img), block 256 = 8 warps, warp per keypoint
+// exact |u| <= d disc row mask -> byte mask of word k (bit j of the nibble -> byte j = 0xFF)
+__device__ __forceinline__ unsigned nibble_to_bytemask(unsigned nib) {
+  return ((nib * 0x00204081u) & 0x01010101u) * 0xFFu;
+}
+
+// grid: (ceil(kp_cap/32), n_img), block 256 = 8 warps x 4 keypoints
 __global__ void __launch_bounds__(256) k_describe(const ExtractorGeom* __restrict__ dg,
                                                   const uint8_t* __restrict__ pyr,
                                                   const uint8_t* __restrict__ blur,
@@ -97,86 +108,117 @@ __global__ void __launch_bounds__(256) k_describe(const ExtractorGeom* __restric
                                                   const int* __restrict__ slot_map,
                                                   cuorb_keypoint* __restrict__ out_kps,
                                                   uint8_t* __restrict__ out_desc) {
+  __shared__ int   s_m01[32], s_m10[32], s_lvl[32];
+  __shared__ int   s_xy[32], s_score[32];
+  __shared__ float s_angle[32], s_cos[32], s_sin[32];
+  __shared__ int   s_off[MAX_LEVELS + 1];
   const int img = blockIdx.y, nlv = dg->nlevels;
-  const int lane = threadIdx.x & 31;
-  const int g = blockIdx.x * 8 + (threadIdx.x >> 5);
-  int l = 0, off = 0;
-  {
-    int c = key_count[img * nlv];
-    while (g >= off + c) {
-      off += c;
-      if (++l == nlv) return;  // g beyond this image's keypoints
-      c = key_count[img * nlv + l];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  if (tid == 0) {
+    int o = 0;
+    for (int l = 0; l < nlv; l++) { s_off[l] = o; o += key_count[img * nlv + l]; }
+    s_off[nlv] = o;
+  }
+  __syncthreads();
+  const int n = s_off[nlv];
+  const int g0 = blockIdx.x * 32;
+  if (g0 >= n) return;
+
+  // ---- phase A: integer moments of the radius-15 disc ----
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+    const int kl = wid * 4 + q, g = min(g0 + kl, n - 1);  // tail slots recompute the last keypoint (never stored)
+    int l = 0;
+    while (g >= s_off[l + 1]) l++;
+    const LevelGeom& L = dg->lv[l];
+    const LevelKey k = keys[(size_t)img * dg->key_img_stride + L.key_off + (g - s_off[l])];
+    const int cx = k.x, cy = k.y;
+    int m01 = 0, m10 = 0;
+    if (lane < 31) {
+      const int v = lane - HALF_PATCH_SIZE;
+      const int d = c_umax[v < 0 ? -v : v];
+      const int a_off = ((cx - HALF_PATCH_SIZE) & ~3) - cx;  // -18 .. -15, word aligned in memory
+      const unsigned* row = reinterpret_cast<const unsigned*>(
+          pyr + (size_t)img * dg->pyr_img_stride + L.pix_off + (ptrdiff_t)(cy + v) * L.pitch + cx + a_off);
+      // valid byte positions p (0..35): |a_off + p| <= d
+      const int lo = -d - a_off, hi = d - a_off;
+      const unsigned long long mask = ((2ull << hi) - 1ull) & ~((1ull << lo) - 1ull);
+      unsigned S = 0, P = 0;
+#pragma unroll
+      for (int kk = 0; kk < 9; kk++) {
+        const unsigned bm = nibble_to_bytemask((unsigned)(mask >> (4 * kk)) & 0xFu);
+        const unsigned w = row[kk] & bm;
+        const unsigned pos = (4u * kk) | ((4u * kk + 1u) << 8) | ((4u * kk + 2u) << 16) | ((4u * kk + 3u) << 24);
+        S = __dp4a(w, 0x01010101u, S);
+        P = __dp4a(w, pos, P);
+      }
+      m01 = v * (int)S;
+      m10 = (int)P + a_off * (int)S;
     }
-  }
-  const LevelGeom& L = dg->lv[l];
-  const LevelKey k = keys[(size_t)img * dg->key_img_stride + L.key_off + (g - off)];
-  const int cx = k.x, cy = k.y;
-
-  // --- IC_Angle: integer moments over the disc, one row per lane ---
-  const uint8_t* center = pyr + (size_t)img * dg->pyr_img_stride + L.pix_off + (size_t)cy * L.pitch + cx;
-  int m01 = 0, m10 = 0;
-  if (lane < 31) {
-    const int v = lane - HALF_PATCH_SIZE;
-    const int d = c_umax[v < 0 ? -v : v];
-    const uint8_t* row = center + (ptrdiff_t)v * L.pitch;
-    int s = 0, t = 0;
-    for (int u = -d; u <= d; ++u) { const int val = row[u]; s += val; t += u * val; }
-    m01 = v * s;
-    m10 = t;
-  }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    m01 += __shfl_xor_sync(0xffffffffu, m01, o);
-    m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+    for (int o = 16; o > 0; o >>= 1) {
+      m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+      m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+    }
+    if (lane == 0) { s_m01[kl] = m01; s_m10[kl] = m10; s_lvl[kl] = l; s_xy[kl] = cx | (cy << 16); s_score[kl] = k.score; }
   }
-  const float angle = fast_atan2_deg((float)m01, (float)m10);
+  __syncthreads();
 
-  // --- steered BRIEF ---
-  const float factorPI = (float)(3.14159265358979323846 / (double)180.f);
-  const float ang = __fmul_rn(angle, factorPI);
-  float a, b;
-  {
-    float ta = 0.f, tb = 0.f;
-    if (lane == 0) { ta = (float)cos((double)ang); tb = (float)sin((double)ang); }
-    a = __shfl_sync(0xffffffffu, ta, 0);
-    b = __shfl_sync(0xffffffffu, tb, 0);
+  // ---- phase B: angle and rotation, one lane per keypoint ----
+  if (tid < 32) {
+    const float angle = fast_atan2_deg((float)s_m01[tid], (float)s_m10[tid]);
+    const float factorPI = (float)(3.14159265358979323846 / (double)180.f);
+    const float ang = __fmul_rn(angle, factorPI);
+    double sn, cs;
+    sincos((double)ang, &sn, &cs);
+    s_angle[tid] = angle; s_cos[tid] = (float)cs; s_sin[tid] = (float)sn;
   }
-  const uint8_t* bc = blur + (size_t)img * dg->blur_img_stride + L.blur_off + (size_t)cy * L.bpitch + cx;
-  const int bp = L.bpitch;
-  const int4 q0 = d_pattern[lane * 2], q1 = d_pattern[lane * 2 + 1];
-  const int pw[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};  // one word = (x0,y0,x1,y1) int8
-  unsigned val = 0;
+  __syncthreads();
+
+  // ---- phase C: steered BRIEF ----
 #pragma unroll
-  for (int j = 0; j < 8; j++) {
-    const float x0 = (float)(signed char)(pw[j] & 0xFF), y0 = (float)(signed char)((pw[j] >> 8) & 0xFF);
-    const float x1 = (float)(signed char)((pw[j] >> 16) & 0xFF), y1 = (float)(signed char)((pw[j] >> 24) & 0xFF);
-    const int iy0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
-    const int ix0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
-    const int iy1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
-    const int ix1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
-    const int t0 = bc[iy0 * bp + ix0], t1 = bc[iy1 * bp + ix1];
-    val |= (unsigned)(t0 < t1) << j;
-  }
-  // pack 4 bytes per word, lanes 0,4,8,.. store
-  unsigned w = val | (__shfl_down_sync(0xffffffffu, val, 1) << 8) |
-               (__shfl_down_sync(0xffffffffu, val, 2) << 16) | (__shfl_down_sync(0xffffffffu, val, 3) << 24);
-  const int slot = slot_map[(size_t)img * dg->kp_cap + g];
-  const size_t o = (size_t)img * dg->kp_cap + slot;
-  if ((lane & 3) == 0) reinterpret_cast<unsigned*>(out_desc + o * 32)[lane >> 2] = w;
-  if (lane == 0) {
-    cuorb_keypoint kp;
-    kp.x = (float)cx; kp.y = (float)cy;
-    if (l != 0) { kp.x = __fmul_rn(kp.x, L.scale); kp.y = __fmul_rn(kp.y, L.scale); }
-    kp.size = L.kp_size; kp.angle = angle; kp.response = (float)k.score;
-    kp.octave = l; kp.class_id = -1;
-    out_kps[o] = kp;
+  for (int q = 0; q < 4; q++) {
+    const int kl = wid * 4 + q, g = g0 + kl;
+    const bool live = g < n;
+    const int l = s_lvl[kl];
+    const LevelGeom& L = dg->lv[l];
+    const int cx = s_xy[kl] & 0xFFFF, cy = s_xy[kl] >> 16;
+    const float a = s_cos[kl], b = s_sin[kl];
+    const uint8_t* bc = blur + (size_t)img * dg->blur_img_stride + L.blur_off + (size_t)cy * L.bpitch + cx;
+    const int bp = L.bpitch;
+    unsigned val = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      const float4 pt = d_patternf[lane * 8 + j];
+      const int iy0 = __float2int_rn(__fadd_rn(__fmul_rn(pt.x, b), __fmul_rn(pt.y, a)));
+      const int ix0 = __float2int_rn(__fsub_rn(__fmul_rn(pt.x, a), __fmul_rn(pt.y, b)));
+      const int iy1 = __float2int_rn(__fadd_rn(__fmul_rn(pt.z, b), __fmul_rn(pt.w, a)));
+      const int ix1 = __float2int_rn(__fsub_rn(__fmul_rn(pt.z, a), __fmul_rn(pt.w, b)));
+      const int t0 = bc[iy0 * bp + ix0], t1 = bc[iy1 * bp + ix1];
+      val |= (unsigned)(t0 < t1) << j;
+    }
+    // pack 4 bytes per word, lanes 0,4,8,.. store
+    unsigned w = val | (__shfl_down_sync(0xffffffffu, val, 1) << 8) |
+                 (__shfl_down_sync(0xffffffffu, val, 2) << 16) | (__shfl_down_sync(0xffffffffu, val, 3) << 24);
+    const int slot = live ? slot_map[(size_t)img * dg->kp_cap + g] : 0;
+    const size_t o = (size_t)img * dg->kp_cap + slot;
+    if (live && (lane & 3) == 0) reinterpret_cast<unsigned*>(out_desc + o * 32)[lane >> 2] = w;
+    if (live && lane == 0) {
+      cuorb_keypoint kp;
+      kp.x = (float)cx; kp.y = (float)cy;
+      if (l != 0) { kp.x = __fmul_rn(kp.x, L.scale); kp.y = __fmul_rn(kp.y, L.scale); }
+      kp.size = L.kp_size; kp.angle = s_angle[kl]; kp.response = (float)s_score[kl];
+      kp.octave = l; kp.class_id = -1;
+      out_kps[o] = kp;
+    }
   }
 }
 
 int init_describe_constants() {
-  // pattern: 256 pairs x 4 int8 = 1024 bytes = 64 int4
-  if (cudaMemcpyToSymbol(d_pattern, CUORB_BIT_PATTERN_31, 1024) != cudaSuccess) return -1;
+  // pattern: 256 pairs x (x0,y0,x1,y1) converted to float once
+  float pf[1024];
+  for (int i = 0; i < 1024; i++) pf[i] = (float)CUORB_BIT_PATTERN_31[i];
+  if (cudaMemcpyToSymbol(d_patternf, pf, sizeof(pf)) != cudaSuccess) return -1;
   // umax (src/ORBextractor.cc:446-464), same float/double sequence as the reference ctor
   int umax[16];
   int v, v0, vmax = (int)floorf(HALF_PATCH_SIZE * sqrtf(2.f) / 2 + 1);
@@ -197,7 +239,7 @@ void launch_describe(const ExtractorGeom& g, const ExtractorGeom* dg, int n_img,
                      int lap1, int* slot_map, cuorb_keypoint* out_kps, uint8_t* out_desc, int* out_n,
                      int* out_mono, cudaStream_t st) {
   k_finalize<<<n_img, 256, 0, st>>>(dg, keys, key_count, lap0, lap1, slot_map, out_n, out_mono);
-  k_describe<<<dim3((g.kp_cap + 7) / 8, n_img), 256, 0, st>>>(dg, pyr, blur, keys, key_count, slot_map,
+  k_describe<<<dim3((g.kp_cap + 31) / 32, n_img), 256, 0, st>>>(dg, pyr, blur, keys, key_count, slot_map,
                                                              out_kps, out_desc);
   count_launch(2);
 }
