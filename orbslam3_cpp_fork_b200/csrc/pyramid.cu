@@ -17,6 +17,7 @@
 namespace cuorb {
 
 constexpr int PYR_RS = 16;  // interior rows per thread strip
+constexpr int PYR_TX = 64;  // threads (output words) per CTA
 
 __device__ __forceinline__ int reflect101(int i, int n) {
   // border (19) < n is checked on the host, so one reflection suffices
@@ -25,7 +26,7 @@ __device__ __forceinline__ int reflect101(int i, int n) {
 }
 
 // grid: (ceil(pitch/4/128), ceil(h/PYR_RS), n_img)
-__global__ void __launch_bounds__(128) k_pyr_level0(const ExtractorGeom* __restrict__ dg,
+__global__ void __launch_bounds__(PYR_TX) k_pyr_level0(const ExtractorGeom* __restrict__ dg,
                                                     const uint8_t* __restrict__ imgs, size_t stride,
                                                     size_t image_stride, uint8_t* __restrict__ pyr,
                                                     int aligned) {
@@ -59,106 +60,116 @@ __global__ void __launch_bounds__(128) k_pyr_level0(const ExtractorGeom* __restr
   }
 }
 
-// horizontal sums (>> 4) of one source row for the thread's four columns
+// per-thread tap setup for its four output columns
 struct ColTaps {
   unsigned coef[4];   // a0 | a1 << 16
   unsigned sel[4];    // PRMT selector picking (p[sx], p[sx+1]) out of a word pair
   unsigned hi;        // bit b: column b's window starts in the second word pair (w1,w2)
-  int      base;      // 4-aligned source x of the 12-byte window
-  int      sx[4];     // only used by the wide fallback
-  bool     wide;      // window does not fit 12 bytes (scale factors far above 2)
 };
 
-__device__ __forceinline__ void hrow(const uint8_t* __restrict__ srow, const ColTaps& T, int (&h)[4]) {
-  if (!T.wide) {
-    const unsigned* p = reinterpret_cast<const unsigned*>(srow + T.base);
-    const unsigned w0 = p[0], w1 = p[1], w2 = p[2];
+// horizontal sums (>> 4) of one source row (three aligned words w0..w2) for the four columns
+__device__ __forceinline__ void hsum(unsigned w0, unsigned w1, unsigned w2, const ColTaps& T, unsigned (&h)[4]) {
 #pragma unroll
-    for (int b = 0; b < 4; b++) {
-      const bool up = (T.hi >> b) & 1;
-      const unsigned v = __byte_perm(up ? w1 : w0, up ? w2 : w1, T.sel[b]);
-      h[b] = (int)(__dp2a_lo(T.coef[b], v, 0u) >> 4);
-    }
-  } else {
-#pragma unroll
-    for (int b = 0; b < 4; b++)
-      h[b] = (int)((srow[T.sx[b]] * (T.coef[b] & 0xFFFFu) + srow[T.sx[b] + 1] * (T.coef[b] >> 16)) >> 4);
+  for (int b = 0; b < 4; b++) {
+    const bool up = (T.hi >> b) & 1;
+    const unsigned v = __byte_perm(up ? w1 : w0, up ? w2 : w1, T.sel[b]);
+    h[b] = __dp2a_lo(T.coef[b], v, 0u) >> 4;
   }
 }
 
-// grid: (ceil(pitch/4/128), ceil(h/PYR_RS), n_img)
-__global__ void __launch_bounds__(128) k_pyr_resize(const ExtractorGeom* __restrict__ dg, int level,
-                                                    uint8_t* __restrict__ pyr,
-                                                    const ResizeTap* __restrict__ xtab,
-                                                    const ResizeTap* __restrict__ ytab) {
+// ((b0*hA)>>16 + (b1*hB)>>16 + 2) >> 2 for four columns, packed.  b0s/b1s = weight << 16, so the
+// truncated product is one IMAD.HI
+__device__ __forceinline__ unsigned vblend(const unsigned (&hA)[4], const unsigned (&hB)[4], unsigned b0s, unsigned b1s) {
+  unsigned v[4];
+#pragma unroll
+  for (int b = 0; b < 4; b++) v[b] = (__umulhi(b0s, hA[b]) + __umulhi(b1s, hB[b]) + 2u) >> 2;
+  return __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
+}
+
+// grid: (ceil(pitch/4/PYR_TX), ceil(h/PYR_RS), n_img).  Source-row driven: every source row of the
+// strip is summed horizontally exactly once (two register sets alternate as "upper"/"lower" row, so
+// nothing is copied), and each output row whose upper source row is the current one is emitted.
+// WIDE: tap windows that do not fit 12 bytes (scale factors far above 2) use byte loads.
+template <bool WIDE>
+__global__ void __launch_bounds__(PYR_TX) k_pyr_resize(const ExtractorGeom* __restrict__ dg, int level,
+                                                       uint8_t* __restrict__ pyr,
+                                                       const ResizeTap* __restrict__ xtab,
+                                                       const ResizeTap* __restrict__ ytab) {
   const LevelGeom& L = dg->lv[level];
   const LevelGeom& S = dg->lv[level - 1];
-  const int word = blockIdx.x * blockDim.x + threadIdx.x;
+  const int word = blockIdx.x * PYR_TX + threadIdx.x;
   if (word * 4 >= L.pitch) return;
   const int img = blockIdx.z;
   uint8_t* base = pyr + (size_t)img * dg->pyr_img_stride;
-  const uint8_t* src = base + S.pix_off;
-  uint8_t* dst = base + L.plane_off;
+  const int spitch = S.pitch, dpitch = L.pitch, sh1 = S.h - 1, lh = L.h;
+  unsigned* dst = reinterpret_cast<unsigned*>(base + L.plane_off) + word;
 
   ColTaps T;
+  int sxs[4];
+  int cbase;
   {
-    int smin = 1 << 30, smax = 0;
+    int smin = 1 << 30;
 #pragma unroll
     for (int b = 0; b < 4; b++) {
       int x = word * 4 + b - ROW_LEAD;
       x = reflect101(min(max(x, -EDGE_THRESHOLD), L.w + EDGE_THRESHOLD - 1), L.w);
       const ResizeTap tx = xtab[L.xtab_off + x];
       // sx+1 may equal S.w: that byte is the stored border pixel and its weight a1 is 0 there
-      T.sx[b] = tx.s;
+      sxs[b] = tx.s;
       T.coef[b] = (unsigned)(unsigned short)tx.a0 | ((unsigned)(unsigned short)tx.a1 << 16);
-      smin = min(smin, (int)tx.s); smax = max(smax, (int)tx.s);
+      smin = min(smin, (int)tx.s);
     }
-    T.base = smin & ~3;
-    T.wide = smax + 1 - T.base > 11;
+    cbase = smin & ~3;
     T.hi = 0;
 #pragma unroll
     for (int b = 0; b < 4; b++) {
-      int t = T.sx[b] - T.base;
+      int t = sxs[b] - cbase;
       if (t >= 4) { T.hi |= 1u << b; t -= 4; }
       T.sel[b] = (unsigned)t | ((unsigned)(t + 1) << 4);
     }
   }
+  const uint8_t* src = base + S.pix_off + (WIDE ? 0 : cbase);
 
-  const int y0 = blockIdx.y * PYR_RS, y1 = min(y0 + PYR_RS, L.h);
-  int rowA = -1, rowB = -1;
-  int hA[4] = {0, 0, 0, 0}, hB[4] = {0, 0, 0, 0};
-  for (int y = y0; y < y1; y++) {
-    const ResizeTap ty = ytab[L.ytab_off + y];
-    // OpenCV clips the two source rows to [0, sh-1] (resizeGeneric_Invoker)
-    const int sy0 = min(max((int)ty.s, 0), S.h - 1), sy1 = min(max((int)ty.s + 1, 0), S.h - 1);
-    if (sy0 == rowB) {
+  auto load_row = [&](int sy, unsigned (&h)[4]) {
+    const uint8_t* r = src + (size_t)min(sy, sh1) * spitch;  // OpenCV clips source rows to sh-1
+    if (!WIDE) {
+      const unsigned* p = reinterpret_cast<const unsigned*>(r);
+      hsum(p[0], p[1], p[2], T, h);
+    } else {
 #pragma unroll
-      for (int b = 0; b < 4; b++) hA[b] = hB[b];
-      rowA = rowB;
-    } else if (sy0 != rowA) {
-      hrow(src + (size_t)sy0 * S.pitch, T, hA);
-      rowA = sy0;
+      for (int b = 0; b < 4; b++)
+        h[b] = (r[sxs[b]] * (T.coef[b] & 0xFFFFu) + r[sxs[b] + 1] * (T.coef[b] >> 16)) >> 4;
     }
-    if (sy1 == rowA) {
-#pragma unroll
-      for (int b = 0; b < 4; b++) hB[b] = hA[b];
-      rowB = rowA;
-    } else if (sy1 != rowB) {
-      hrow(src + (size_t)sy1 * S.pitch, T, hB);
-      rowB = sy1;
+  };
+  auto emit = [&](int y, const unsigned (&hA)[4], const unsigned (&hB)[4], const ResizeTap ty) {
+    const unsigned out = vblend(hA, hB, (unsigned)ty.a0 << 16, (unsigned)ty.a1 << 16);
+    dst[(size_t)(y + EDGE_THRESHOLD) * (dpitch >> 2)] = out;
+    if (y >= 1 && y <= EDGE_THRESHOLD) dst[(size_t)(EDGE_THRESHOLD - y) * (dpitch >> 2)] = out;
+    if (y >= lh - 1 - EDGE_THRESHOLD && y <= lh - 2) dst[(size_t)(2 * lh + EDGE_THRESHOLD - 2 - y) * (dpitch >> 2)] = out;
+  };
+
+  const int y0 = blockIdx.y * PYR_RS, y1 = min(y0 + PYR_RS, lh);
+  const ResizeTap* yt = ytab + L.ytab_off;
+  int y = y0;
+  ResizeTap ty = yt[y];
+  int s = max((int)ty.s, 0);
+  unsigned h0[4], h1[4];
+  load_row(s, h0);
+  for (;;) {
+    load_row(s + 1, h1);                       // h0 = source row s, h1 = row s+1
+    while (max((int)ty.s, 0) == s) {
+      emit(y, h0, h1, ty);
+      if (++y >= y1) return;
+      ty = yt[y];
     }
-    const int b0 = ty.a0, b1 = ty.a1;
-    unsigned out = 0;
-#pragma unroll
-    for (int b = 0; b < 4; b++) {
-      const int v = (((b0 * hA[b]) >> 16) + ((b1 * hB[b]) >> 16) + 2) >> 2;
-      out |= (unsigned)(v & 0xFF) << (8 * b);
+    s++;
+    load_row(s + 1, h0);                       // h1 = source row s, h0 = row s+1
+    while (max((int)ty.s, 0) == s) {
+      emit(y, h1, h0, ty);
+      if (++y >= y1) return;
+      ty = yt[y];
     }
-    reinterpret_cast<unsigned*>(dst + (size_t)(y + EDGE_THRESHOLD) * L.pitch)[word] = out;
-    if (y >= 1 && y <= EDGE_THRESHOLD)
-      reinterpret_cast<unsigned*>(dst + (size_t)(EDGE_THRESHOLD - y) * L.pitch)[word] = out;
-    if (y >= L.h - 1 - EDGE_THRESHOLD && y <= L.h - 2)
-      reinterpret_cast<unsigned*>(dst + (size_t)(2 * L.h + EDGE_THRESHOLD - 2 - y) * L.pitch)[word] = out;
+    s++;
   }
 }
 
@@ -168,9 +179,15 @@ void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8
   const int aligned = (((uintptr_t)imgs | stride | image_stride) & 3) == 0;
   for (int l = 0; l < g.nlevels; l++) {
     const LevelGeom& L = g.lv[l];
-    dim3 grid((L.pitch / 4 + 127) / 128, (L.h + PYR_RS - 1) / PYR_RS, n_img);
-    if (l == 0) k_pyr_level0<<<grid, 128, 0, st>>>(dg, imgs, stride, image_stride, pyr, aligned);
-    else k_pyr_resize<<<grid, 128, 0, st>>>(dg, l, pyr, xtab, ytab);
+    dim3 grid((L.pitch / 4 + PYR_TX - 1) / PYR_TX, (L.h + PYR_RS - 1) / PYR_RS, n_img);
+    if (l == 0) {
+      k_pyr_level0<<<grid, PYR_TX, 0, st>>>(dg, imgs, stride, image_stride, pyr, aligned);
+    } else {
+      // four adjacent output columns span 3*scale + 2 source bytes (+3 for alignment): 12 bytes up to scale 2
+      const double sx = (double)g.lv[l - 1].w / L.w;
+      if (3.0 * sx + 5.0 < 11.5) k_pyr_resize<false><<<grid, PYR_TX, 0, st>>>(dg, l, pyr, xtab, ytab);
+      else k_pyr_resize<true><<<grid, PYR_TX, 0, st>>>(dg, l, pyr, xtab, ytab);
+    }
     count_launch();
   }
 }
