@@ -98,7 +98,8 @@ void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8
 void build_blur_tiles(const ExtractorGeom& g, std::vector<int4>& tiles);
 void launch_blur(const ExtractorGeom* g, const ExtractorGeom* dg, int n_img, const int4* tiles,
                  int n_tiles, const uint8_t* pyr, uint8_t* blur, cudaStream_t st);
-void launch_fast(const ExtractorGeom& g, const ExtractorGeom* dg, int n_img, const uint8_t* pyr,
+void build_fast_cells(const ExtractorGeom& g, std::vector<int4>& cells);
+void launch_fast(const ExtractorGeom& g, const ExtractorGeom* dg, const int4* cells, int n_img, const uint8_t* pyr,
                  unsigned* cand, int* cand_count, int* flags, cudaStream_t st);
 void launch_octree(const ExtractorGeom& g, const ExtractorGeom* dg, int n_img, const unsigned* cand,
                    unsigned* cand_scratch, const int* cand_count, LevelKey* keys, int* key_count,

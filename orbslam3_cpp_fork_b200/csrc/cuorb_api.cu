@@ -40,6 +40,7 @@ struct cuorb_extractor {
   ExtractorGeom* d_geom = nullptr;
   ResizeTap *d_xtab = nullptr, *d_ytab = nullptr;
   int4*      d_blur_tiles = nullptr;
+  int4*      d_fast_cells = nullptr;  // per FAST cell: level, x0 | y0 << 16, dw | dh << 16
   int        n_blur_tiles = 0;
   uint8_t *  d_input = nullptr, *d_pyr = nullptr, *d_blur = nullptr;
   unsigned * d_cand = nullptr, *d_cand_scratch = nullptr;
@@ -55,7 +56,7 @@ struct cuorb_extractor {
   // pinned host mirrors of the small per-image results
   int *h_out_n = nullptr, *h_out_mono = nullptr, *h_flags = nullptr;
   size_t cap_input = 0, cap_pyr = 0, cap_blur = 0, cap_cand = 0, cap_keys = 0, cap_kp = 0;
-  size_t cap_xtab = 0, cap_ytab = 0, cap_tiles = 0;
+  size_t cap_xtab = 0, cap_ytab = 0, cap_tiles = 0, cap_cells = 0;
   int    n_img = 0;       // images in the last batch
   bool   have_batch = false, have_stereo = false;
 };
@@ -199,7 +200,7 @@ static cudaError_t dev_alloc(T** p, size_t count) {
 
 static void free_all(cuorb_extractor* e) {
   cudaSetDevice(e->cfg.device);
-  void* dev[] = {e->d_geom, e->d_xtab, e->d_ytab, e->d_blur_tiles, e->d_input, e->d_pyr, e->d_blur,
+  void* dev[] = {e->d_geom, e->d_xtab, e->d_ytab, e->d_blur_tiles, e->d_fast_cells, e->d_input, e->d_pyr, e->d_blur,
                  e->d_cand, e->d_cand_scratch, e->d_cand_count, e->d_key_count, e->d_flags, e->d_slot,
                  e->d_keys, e->d_out_kps, e->d_out_desc, e->d_out_n, e->d_out_mono, e->d_uright,
                  e->d_depth, e->d_sad, e->d_best_idx, e->d_best_dist, e->d_rtab, e->d_rstart};
@@ -224,11 +225,13 @@ static int set_size(cuorb_extractor* e, int w, int h) {
   if (rc != CUORB_OK) return rc;
   std::vector<int4> tiles;
   build_blur_tiles(g, tiles);
+  std::vector<int4> cells;
+  build_fast_cells(g, cells);
   const size_t nb = (size_t)e->cfg.max_batch;
   if (g.pyr_img_stride * nb + 4096 > e->cap_pyr || g.blur_img_stride * nb > e->cap_blur ||
       g.cand_img_stride * nb > e->cap_cand || (size_t)g.key_img_stride * nb > e->cap_keys ||
       (size_t)g.kp_cap * nb > e->cap_kp || xt.size() > e->cap_xtab || yt.size() > e->cap_ytab ||
-      tiles.size() > e->cap_tiles) {
+      tiles.size() > e->cap_tiles || cells.size() > e->cap_cells) {
     set_error("internal: geometry of this size exceeds the arena sized for max_width x max_height");
     return CUORB_E_CAPACITY;
   }
@@ -239,6 +242,7 @@ static int set_size(cuorb_extractor* e, int w, int h) {
   if (!yt.empty()) CUORB_CUDA_TRY(cudaMemcpy(e->d_ytab, yt.data(), yt.size() * sizeof(ResizeTap), cudaMemcpyHostToDevice));
   CUORB_CUDA_TRY(cudaMemcpy(e->d_blur_tiles, tiles.data(), tiles.size() * sizeof(int4), cudaMemcpyHostToDevice));
   e->n_blur_tiles = (int)tiles.size();
+  CUORB_CUDA_TRY(cudaMemcpy(e->d_fast_cells, cells.data(), cells.size() * sizeof(int4), cudaMemcpyHostToDevice));
   e->g = g; e->cur_w = w; e->cur_h = h;
   e->have_batch = false; e->have_stereo = false;
   return CUORB_OK;
@@ -291,6 +295,7 @@ cuorb_extractor* cuorb_extractor_create(const cuorb_config* cfg) {
   e->cap_keys  = (size_t)g.key_img_stride * nb;
   e->cap_kp    = (size_t)g.kp_cap * nb;
   e->cap_xtab  = xt.size() + 64; e->cap_ytab = yt.size() + 64; e->cap_tiles = tiles.size() + 64;
+  e->cap_cells = (size_t)g.total_cells + 64;
   bool ok = true;
   ok &= cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess;
   ok &= cudaEventCreateWithFlags(&e->ev_done, cudaEventDisableTiming) == cudaSuccess;
@@ -299,6 +304,7 @@ cuorb_extractor* cuorb_extractor_create(const cuorb_config* cfg) {
   ok &= dev_alloc(&e->d_xtab, e->cap_xtab) == cudaSuccess;
   ok &= dev_alloc(&e->d_ytab, e->cap_ytab) == cudaSuccess;
   ok &= dev_alloc(&e->d_blur_tiles, e->cap_tiles) == cudaSuccess;
+  ok &= dev_alloc(&e->d_fast_cells, e->cap_cells) == cudaSuccess;
   ok &= dev_alloc(&e->d_input, e->cap_input) == cudaSuccess;
   ok &= dev_alloc(&e->d_pyr, e->cap_pyr) == cudaSuccess;
   ok &= dev_alloc(&e->d_blur, e->cap_blur) == cudaSuccess;
@@ -414,7 +420,7 @@ int cuorb_extract_batch_async(cuorb_extractor* e, int n_images, const uint8_t* i
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_PYRAMID], st);
   launch_pyramid(e->g, e->d_geom, dimgs, width, height, dstride, dimg_stride, n_images, e->d_pyr, e->d_xtab, e->d_ytab, st);
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_FAST], st);
-  launch_fast(e->g, e->d_geom, n_images, e->d_pyr, e->d_cand, e->d_cand_count, e->d_flags, st);
+  launch_fast(e->g, e->d_geom, e->d_fast_cells, n_images, e->d_pyr, e->d_cand, e->d_cand_count, e->d_flags, st);
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_OCTREE], st);
   launch_octree(e->g, e->d_geom, n_images, e->d_cand, e->d_cand_scratch, e->d_cand_count, e->d_keys,
                 e->d_key_count, e->d_flags, st);

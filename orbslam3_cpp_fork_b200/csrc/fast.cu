@@ -23,6 +23,8 @@
 // The list is unordered; the reference order (cell-row-major, then row-major) is a pure function
 // of (x, y) and is re-derived where it matters (quadtree tie-break, debug download).
 // Bound: the integer ALU pipe (min/max network), not HBM: ~45 ALU-pipe instructions per pixel.
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace cuorb {
@@ -70,147 +72,169 @@ __device__ __forceinline__ void arc_extremes(unsigned c, const unsigned (&r)[16]
 
 }  // namespace
 
-// grid: (total_cells, n_img), block 128, dynamic smem = u16 pixel tile + u8 score tile + lists
-// TP: pixel-tile pitch in 32-bit words (two u16 pixels each).  ODD, and lanes walk down rows, so
-// the 32 lanes of a warp hit 32 different banks.
-template <int TP>
+// warp-uniform list append: `cnt` is a warp-uniform register, `seg` the warp's own segment
+__device__ __forceinline__ void warp_append(bool f, unsigned short v, unsigned short* seg, int& cnt, unsigned lt) {
+  const unsigned b = __ballot_sync(0xffffffffu, f);
+  if (f) seg[cnt + __popc(b & lt)] = v;
+  cnt += __popc(b);
+}
+
+// flat index over four per-warp segments -> entry
+__device__ __forceinline__ int seg_fetch(const unsigned short* list, int cap, const int (&c)[4], int i) {
+  const int w = (i >= c[0]) + (i >= c[0] + c[1]) + (i >= c[0] + c[1] + c[2]);
+  const int off = (w > 0 ? c[0] : 0) + (w > 1 ? c[1] : 0) + (w > 2 ? c[2] : 0);
+  return list[w * cap + (i - off)];
+}
+
+// grid: (total_cells, n_img), block 128, dynamic smem = u16 + u8 pixel tiles, u8 score tile, lists
+// TP:  pitch of the u16 pixel tile in 32-bit words (two pixels each).
+// TPB: pitch of the u8 pixel tile in 32-bit words (four pixels each).
+// cells[]: per FAST cell {level, x0 | y0 << 16, dw | dh << 16} (host-built: no per-CTA geometry math)
+template <int TP, int TPB>
 __global__ void __launch_bounds__(128) k_fast_cells(const ExtractorGeom* __restrict__ dg,
+                                                    const int4* __restrict__ cells,
                                                     const uint8_t* __restrict__ pyr,
                                                     unsigned* __restrict__ cand,
                                                     int* __restrict__ cand_count,
-                                                    int* __restrict__ flags, int tile_bytes,
-                                                    int score_bytes, int plist_bytes, int clist_bytes) {
+                                                    int* __restrict__ flags, int tile_bytes, int tile8_bytes,
+                                                    int score_bytes, int pcap, int ccap) {
   extern __shared__ __align__(16) unsigned char smem[];
-  __shared__ int s_np, s_nc, s_nlist, s_nout, s_base;
+  __shared__ int s_pcnt[4], s_ccnt[4], s_nlist, s_nout, s_base;
 
-  // which level / cell
-  int level = 0;
-  const int nlv = dg->nlevels;
-  while (level + 1 < nlv && (int)blockIdx.x >= dg->lv[level + 1].cell_base) level++;
-  const LevelGeom& L = dg->lv[level];
-  const int cell = blockIdx.x - L.cell_base;
-  const int ci = cell / L.nCols, cj = cell - ci * L.nCols;
-  const int x0 = EDGE_THRESHOLD + cj * L.wCell, y0 = EDGE_THRESHOLD + ci * L.hCell;
-  const int dw = min(x0 + L.wCell, L.maxBorderX - 3) - x0;
-  const int dh = min(y0 + L.hCell, L.maxBorderY - 3) - y0;
+  const int4 cd = __ldg(&cells[blockIdx.x]);
+  const int level = cd.x;
+  const int x0 = cd.y & 0xFFFF, y0 = cd.y >> 16, dw = cd.z & 0xFFFF, dh = cd.z >> 16;
   if (dw <= 0 || dh <= 0) return;  // cells the reference skips (:781, :791) or that cannot hold a corner
+  const LevelGeom& L = dg->lv[level];
 
   const int img = blockIdx.y;
-  const int tid = threadIdx.x, lane = tid & 31;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const unsigned lt = (1u << lane) - 1u;
   const int ini_th = dg->ini_th, min_th = dg->min_th;
 
-  unsigned*       s_tile  = reinterpret_cast<unsigned*>(smem);      // (dh+6) rows of TP words
-  unsigned char*  s_score = smem + tile_bytes;                      // (dh+2) rows of sp bytes, zero frame
-  unsigned short* s_plist = reinterpret_cast<unsigned short*>(smem + tile_bytes + score_bytes);
-  unsigned short* s_clist = reinterpret_cast<unsigned short*>(smem + tile_bytes + score_bytes + plist_bytes);
-  unsigned*       s_list  = reinterpret_cast<unsigned*>(smem + tile_bytes + score_bytes + plist_bytes + clist_bytes);
+  unsigned*       s_tile  = reinterpret_cast<unsigned*>(smem);                  // (dh+6) rows of TP words (u16 px)
+  unsigned*       s_tile8 = reinterpret_cast<unsigned*>(smem + tile_bytes);     // (dh+6) rows of TPB words (u8 px)
+  unsigned char*  s_score = smem + tile_bytes + tile8_bytes;                    // (dh+2) rows of sp bytes, zero frame
+  unsigned short* s_plist = reinterpret_cast<unsigned short*>(s_score + score_bytes);  // 4 segments of pcap
+  unsigned short* s_clist = s_plist + 4 * pcap;                                         // 4 segments of ccap
+  unsigned*       s_list  = reinterpret_cast<unsigned*>(s_clist + 4 * ccap);
   // score pitch: pixel px lives at column px + 4; pitch/4 odd so a column of rows spreads over banks
   const int sp = (((dw + 5 + 3) >> 2) | 1) << 2;
 
-  if (tid == 0) { s_np = 0; s_nc = 0; s_nlist = 0; s_nout = 0; }
+  if (tid == 0) { s_nlist = 0; s_nout = 0; }
 
-  // ---- phase 1: stage pixels as u16.  Tile column s <-> level x = ax + s (ax 4-aligned). ----
+  // ---- phase 1: stage pixels.  Tile column s <-> level x = ax + s (ax 4-aligned); the cell's
+  // first pixel sits at column cx0 = 4..7, so the ring (3 px) and one more column fit on the left.
   const int ax  = (x0 - 4) & ~3;
-  const int cx0 = x0 - ax;           // 4..7: tile column of the cell's first pixel
-  const int o   = cx0 & 1;           // pairs must start on an even tile column
-  const int npr = (dw + o + 1) >> 1; // pixel pairs per row (a leading / trailing pixel may be unused)
-  const int gw  = (cx0 - o + 2 * npr + 4 + 3) >> 2;  // aligned 4-px global words per row (2 halo words right)
-  const uint8_t* src = pyr + (size_t)img * dg->pyr_img_stride + L.pix_off + (ptrdiff_t)(y0 - 3) * L.pitch + ax;
+  const int cx0 = x0 - ax;
+  const int gw  = (cx0 + dw + 3 + 4 + 3) >> 2;  // aligned 4-px words per row: ring + one spare pixel right
   {
-    const int n = gw * (dh + 6);
-    const unsigned inv = magic(gw);
-    for (int i = tid; i < n; i += 128) {
-      const int r = fastdiv(i, inv, gw), c = i - r * gw;
-      const unsigned w = __ldg(reinterpret_cast<const unsigned*>(src + (ptrdiff_t)r * L.pitch + c * 4));
-      s_tile[r * TP + 2 * c]     = __byte_perm(w, 0, 0x4140);
-      s_tile[r * TP + 2 * c + 1] = __byte_perm(w, 0, 0x4342);
+    const uint8_t* src = pyr + (size_t)img * dg->pyr_img_stride + L.pix_off + (ptrdiff_t)(y0 - 3) * L.pitch + ax;
+    const int pitch = L.pitch;
+    for (int c = tid & 15; c < gw; c += 16) {
+      const uint8_t* p = src + (ptrdiff_t)(tid >> 4) * pitch + c * 4;
+      for (int r = tid >> 4; r < dh + 6; r += 8, p += 8 * (ptrdiff_t)pitch) {
+        const unsigned w = __ldg(reinterpret_cast<const unsigned*>(p));
+        s_tile8[r * TPB + c] = w;
+        *reinterpret_cast<uint2*>(s_tile + r * TP + 2 * c) = make_uint2(__byte_perm(w, 0, 0x4140), __byte_perm(w, 0, 0x4342));
+      }
     }
     const int nz = (sp * (dh + 2)) >> 2;
     for (int i = tid; i < nz; i += 128) reinterpret_cast<unsigned*>(s_score)[i] = 0;
   }
   __syncthreads();
 
-  const int npairs = npr * dh;
-  const unsigned invh = magic(dh);
-  const int cbase = (cx0 - o) >> 1;
-
-  // ---- phase 2a: necessary condition on the 4 compass ring pixels, pairs that pass are listed.
-  // An arc of 9 always contains two adjacent compass points, so a corner at minThFAST needs
-  // max over adjacent compass pairs of min(d_a, d_b) > t  (or the mirrored condition).
+  // ---- phase 2a: necessary condition on the 4 compass ring pixels, four pixels per thread on the
+  // u8 tile.  An arc of 9 always contains two adjacent compass points, so a corner at minThFAST
+  // needs (|N-c| > t or |S-c| > t) and (|E-c| > t or |W-c| > t).  Pixel pairs with a passing pixel
+  // are appended to the warp's own list segment as (row << 7 | pair column).
   {
-    const unsigned TH = (unsigned)(257 + min_th);
-    const unsigned addc = (0x8000u - TH) * 0x00010001u;
-    for (int p0 = 0; p0 < npairs; p0 += 128) {
-      const int p = p0 + tid;
-      bool pass = false;
-      if (p < npairs) {
-        const int m = fastdiv(p, invh, dh), r = p - m * dh;
-        const unsigned* T = s_tile + (r + 3) * TP + cbase + m;
-        const unsigned cb = T[0] + 0x01000100u;
-        const unsigned dN = cb - T[3 * TP], dS = cb - T[-3 * TP];
-        const unsigned dE = cb - odd_pair(T[1], T[2]), dW = cb - odd_pair(T[-2], T[-1]);
-        const unsigned qd = umax3(umin2(dN, dE), umin2(dE, dS), umax2(umin2(dS, dW), umin2(dW, dN)));
-        const unsigned qb = umin3(umax2(dN, dE), umax2(dE, dS), umin2(umax2(dS, dW), umax2(dW, dN)));
-        const unsigned x = umax2(qd, 0x02000200u - qb);
-        pass = ((x + addc) & 0x80008000u) != 0;
+    const int nqm = ((cx0 + dw + 3) >> 2) - 1;  // quads = tile words 1 .. nqm (columns 4 .. 4*nqm+3)
+    const int nquads = nqm * dh;
+    const unsigned inv = magic(nqm);
+    const unsigned K = (unsigned)(127 - min(min_th, 127)) * 0x01010101u;
+    unsigned short* seg = s_plist + wid * pcap;
+    int cnt = 0;
+    for (int i0 = 0; i0 < nquads; i0 += 128) {
+      const int i = i0 + tid;
+      bool f0 = false, f1 = false;
+      int r = 0, q = 0;
+      if (i < nquads) {
+        r = fastdiv(i, inv, nqm); q = i - r * nqm + 1;
+        const unsigned* T = s_tile8 + (r + 3) * TPB + q;
+        const unsigned C = T[0];
+        const unsigned E = __funnelshift_r(C, T[1], 24), W = __funnelshift_r(T[-1], C, 8);
+        const unsigned aN = __vabsdiffu4(T[3 * TPB], C), aS = __vabsdiffu4(T[-3 * TPB], C);
+        const unsigned aE = __vabsdiffu4(E, C), aW = __vabsdiffu4(W, C);
+        // per byte "a > t": bit 7 of a | ((a & 0x7f) + (127 - t))
+        const unsigned mN = aN | ((aN & 0x7f7f7f7fu) + K), mS = aS | ((aS & 0x7f7f7f7fu) + K);
+        const unsigned mE = aE | ((aE & 0x7f7f7f7fu) + K), mW = aW | ((aW & 0x7f7f7f7fu) + K);
+        const unsigned pass = (mN | mS) & (mE | mW) & 0x80808080u;
+        f0 = (pass & 0x0000FFFFu) != 0; f1 = (pass & 0xFFFF0000u) != 0;
       }
-      const unsigned bal = __ballot_sync(0xffffffffu, pass);
-      if (bal) {
-        int base = 0;
-        if (lane == 0) base = atomicAdd(&s_np, __popc(bal));
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (pass) s_plist[base + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)p;
-      }
+      const unsigned short e = (unsigned short)((r << 7) | (2 * q - 2));   // pair column = (s - 4) / 2
+      warp_append(f0, e, seg, cnt, lt);
+      warp_append(f1, (unsigned short)(e + 1), seg, cnt, lt);
     }
+    if (lane == 0) s_pcnt[wid] = cnt;
   }
   __syncthreads();
 
-  // ---- phase 2b: full score network on the listed pairs ----
+  // ---- phase 2b: full score network on the listed pairs; corners go to the warp's corner list ----
   {
-    const int np = s_np;
-    for (int i = tid; i < np; i += 128) {
-      const int p = s_plist[i];
-      const int m = fastdiv(p, invh, dh), r = p - m * dh;
-      const int px = 2 * m - o;  // first pixel of the pair, cell-relative (may be -1)
-      const unsigned* T = s_tile + (r + 3) * TP + cbase + m;
-      unsigned ring[16];
-      {
-        const unsigned a = T[3 * TP - 1], b = T[3 * TP], c = T[3 * TP + 1];
-        ring[0] = b; ring[1] = odd_pair(b, c); ring[15] = odd_pair(a, b);
+    const int pc4[4] = {s_pcnt[0], s_pcnt[1], s_pcnt[2], s_pcnt[3]};
+    const int np = pc4[0] + pc4[1] + pc4[2] + pc4[3];
+    unsigned short* seg = s_clist + wid * ccap;
+    int cnt = 0;
+    for (int i0 = 0; i0 < np; i0 += 128) {
+      const int i = i0 + tid;
+      bool c0 = false, c1 = false;
+      int r = 0, px = 0;
+      if (i < np) {
+        const int e = seg_fetch(s_plist, pcap, pc4, i);
+        r = e >> 7;
+        const int pc = e & 127;
+        px = 4 + 2 * pc - cx0;  // first pixel of the pair, cell-relative (may be outside the cell)
+        const unsigned* T = s_tile + (r + 3) * TP + 2 + pc;
+        unsigned ring[16];
+        {
+          const unsigned a = T[3 * TP - 1], b = T[3 * TP], c = T[3 * TP + 1];
+          ring[0] = b; ring[1] = odd_pair(b, c); ring[15] = odd_pair(a, b);
+        }
+        ring[2] = T[2 * TP + 1]; ring[14] = T[2 * TP - 1];
+        ring[3] = odd_pair(T[TP + 1], T[TP + 2]); ring[13] = odd_pair(T[TP - 2], T[TP - 1]);
+        ring[4] = odd_pair(T[1], T[2]); ring[12] = odd_pair(T[-2], T[-1]);
+        ring[5] = odd_pair(T[-TP + 1], T[-TP + 2]); ring[11] = odd_pair(T[-TP - 2], T[-TP - 1]);
+        ring[6] = T[-2 * TP + 1]; ring[10] = T[-2 * TP - 1];
+        {
+          const unsigned a = T[-3 * TP - 1], b = T[-3 * TP], c = T[-3 * TP + 1];
+          ring[8] = b; ring[7] = odd_pair(b, c); ring[9] = odd_pair(a, b);
+        }
+        unsigned A, B;
+        arc_extremes(T[0], ring, A, B);
+        // score = max(a, -b) - 1 with a = A - 256, b = B - 256   (cornerScore<16>)
+        const int s0 = max((int)(A & 0xFFFFu) - 257, 255 - (int)(B & 0xFFFFu));
+        const int s1 = max((int)(A >> 16) - 257, 255 - (int)(B >> 16));
+        unsigned char* q = s_score + (r + 1) * sp + px + 4;
+        c0 = px >= 0 && px < dw && s0 >= min_th;
+        c1 = px + 1 >= 0 && px + 1 < dw && s1 >= min_th;
+        if (c0) q[0] = (unsigned char)s0;
+        if (c1) q[1] = (unsigned char)s1;
       }
-      ring[2] = T[2 * TP + 1]; ring[14] = T[2 * TP - 1];
-      ring[3] = odd_pair(T[TP + 1], T[TP + 2]); ring[13] = odd_pair(T[TP - 2], T[TP - 1]);
-      ring[4] = odd_pair(T[1], T[2]); ring[12] = odd_pair(T[-2], T[-1]);
-      ring[5] = odd_pair(T[-TP + 1], T[-TP + 2]); ring[11] = odd_pair(T[-TP - 2], T[-TP - 1]);
-      ring[6] = T[-2 * TP + 1]; ring[10] = T[-2 * TP - 1];
-      {
-        const unsigned a = T[-3 * TP - 1], b = T[-3 * TP], c = T[-3 * TP + 1];
-        ring[8] = b; ring[7] = odd_pair(b, c); ring[9] = odd_pair(a, b);
-      }
-      unsigned A, B;
-      arc_extremes(T[0], ring, A, B);
-      // score = max(a, -b) - 1 with a = A - 256, b = B - 256   (cornerScore<16>)
-      const int s0 = max((int)(A & 0xFFFFu) - 257, 255 - (int)(B & 0xFFFFu));
-      const int s1 = max((int)(A >> 16) - 257, 255 - (int)(B >> 16));
-      unsigned char* q = s_score + (r + 1) * sp + px + 4;
-      if (px >= 0 && s0 >= min_th) {
-        q[0] = (unsigned char)s0;
-        s_clist[atomicAdd(&s_nc, 1)] = (unsigned short)((r << 7) | px);
-      }
-      if (px + 1 < dw && s1 >= min_th) {
-        q[1] = (unsigned char)s1;
-        s_clist[atomicAdd(&s_nc, 1)] = (unsigned short)((r << 7) | (px + 1));
-      }
+      warp_append(c0, (unsigned short)((r << 7) | px), seg, cnt, lt);
+      warp_append(c1, (unsigned short)((r << 7) | (px + 1)), seg, cnt, lt);
     }
+    if (lane == 0) s_ccnt[wid] = cnt;
   }
   __syncthreads();
 
   // ---- phase 3: NMS inside the cell over the listed corners, threshold choice, emit ----
   bool any_ini = false;
   {
-    const int nc = s_nc;
+    const int cc4[4] = {s_ccnt[0], s_ccnt[1], s_ccnt[2], s_ccnt[3]};
+    const int nc = cc4[0] + cc4[1] + cc4[2] + cc4[3];
     for (int i = tid; i < nc; i += 128) {
-      const int e = s_clist[i];
+      const int e = seg_fetch(s_clist, ccap, cc4, i);
       const int r = e >> 7, px = e & 127;
       const unsigned char* q = s_score + (r + 1) * sp + px + 4;
       const int s = q[0];
@@ -234,7 +258,7 @@ __global__ void __launch_bounds__(128) k_fast_cells(const ExtractorGeom* __restr
   __syncthreads();
   const int nout = s_nout;
   if (nout == 0) return;
-  const int slot = img * nlv + level;
+  const int slot = img * dg->nlevels + level;
   if (tid == 0) s_base = atomicAdd(&cand_count[slot], nout);
   __syncthreads();
   const int base = s_base;
@@ -246,31 +270,49 @@ __global__ void __launch_bounds__(128) k_fast_cells(const ExtractorGeom* __restr
   for (int n = tid; n < nout; n += 128) out[n] = s_out[n];
 }
 
-template <int TP>
-static void launch_fast_tp(const ExtractorGeom& g, const ExtractorGeom* dg, int n_img, const uint8_t* pyr,
-                           unsigned* cand, int* cand_count, int* flags, cudaStream_t st) {
-  const int tile_bytes  = ((TP * 4 * (g.max_cell_h + 6) + 15) / 16) * 16;
-  const int sp_max      = ((((g.max_cell_w + 5 + 3) >> 2) | 1) << 2);
-  const int score_bytes = ((sp_max * (g.max_cell_h + 2) + 15) / 16) * 16;
-  const int plist_bytes = ((2 * ((g.max_cell_w + 2) / 2) * g.max_cell_h + 15) / 16) * 16;
-  const int clist_bytes = ((2 * g.max_cell_w * g.max_cell_h + 15) / 16) * 16;
-  const int list_bytes  = 4 * ((g.max_cell_w + 1) / 2) * ((g.max_cell_h + 1) / 2);
-  const int smem        = tile_bytes + score_bytes + plist_bytes + clist_bytes + list_bytes;
-  static int attr = 48 * 1024;
-  if (smem > attr) {
-    cudaFuncSetAttribute(k_fast_cells<TP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    attr = smem;
+// per-cell geometry (src/ORBextractor.cc:777-796), cell-row-major per level
+void build_fast_cells(const ExtractorGeom& g, std::vector<int4>& cells) {
+  cells.clear();
+  for (int l = 0; l < g.nlevels; l++) {
+    const LevelGeom& L = g.lv[l];
+    for (int ci = 0; ci < L.nRows; ci++)
+      for (int cj = 0; cj < L.nCols; cj++) {
+        const int x0 = EDGE_THRESHOLD + cj * L.wCell, y0 = EDGE_THRESHOLD + ci * L.hCell;
+        const int dw = std::max(std::min(x0 + L.wCell, L.maxBorderX - 3) - x0, 0);
+        const int dh = std::max(std::min(y0 + L.hCell, L.maxBorderY - 3) - y0, 0);
+        cells.push_back(make_int4(l, x0 | (y0 << 16), dw | (dh << 16), 0));
+      }
   }
-  k_fast_cells<TP><<<dim3(g.total_cells, n_img), 128, smem, st>>>(dg, pyr, cand, cand_count, flags, tile_bytes,
-                                                                  score_bytes, plist_bytes, clist_bytes);
 }
 
-void launch_fast(const ExtractorGeom& g, const ExtractorGeom* dg, int n_img, const uint8_t* pyr,
+template <int TP, int TPB>
+static void launch_fast_tp(const ExtractorGeom& g, const ExtractorGeom* dg, const int4* cells, int n_img,
+                           const uint8_t* pyr, unsigned* cand, int* cand_count, int* flags, cudaStream_t st) {
+  const int rows        = g.max_cell_h + 6;
+  const int tile_bytes  = ((TP * 4 * rows + 15) / 16) * 16;
+  const int tile8_bytes = ((TPB * 4 * rows + 15) / 16) * 16;
+  const int sp_max      = ((((g.max_cell_w + 5 + 3) >> 2) | 1) << 2);
+  const int score_bytes = ((sp_max * (g.max_cell_h + 2) + 15) / 16) * 16;
+  const int maxquads    = ((g.max_cell_w + 10) / 4) * g.max_cell_h;
+  const int pcap        = 64 * ((maxquads + 127) / 128);          // per-warp pair list (entries)
+  const int ccap        = 64 * ((2 * maxquads + 127) / 128);      // per-warp corner list (entries)
+  const int list_bytes  = 4 * ((g.max_cell_w + 1) / 2) * ((g.max_cell_h + 1) / 2);
+  const int smem        = tile_bytes + tile8_bytes + score_bytes + 2 * 4 * (pcap + ccap) + list_bytes;
+  static int attr = 48 * 1024;
+  if (smem > attr) {
+    cudaFuncSetAttribute(k_fast_cells<TP, TPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    attr = smem;
+  }
+  k_fast_cells<TP, TPB><<<dim3(g.total_cells, n_img), 128, smem, st>>>(dg, cells, pyr, cand, cand_count, flags, tile_bytes,
+                                                                       tile8_bytes, score_bytes, pcap, ccap);
+}
+
+void launch_fast(const ExtractorGeom& g, const ExtractorGeom* dg, const int4* cells, int n_img, const uint8_t* pyr,
                  unsigned* cand, int* cand_count, int* flags, cudaStream_t st) {
-  // tile columns 0 .. (6 + max_cell_w + 2 + 4 + alignment) as u16 pairs -> words; cell height
-  // below 512 and width below 128 for the packed corner list
-  if (g.max_cell_w + 16 <= 2 * 29) launch_fast_tp<29>(g, dg, n_img, pyr, cand, cand_count, flags, st);
-  else launch_fast_tp<71>(g, dg, n_img, pyr, cand, cand_count, flags, st);
+  // tile columns 0 .. 7 + max_cell_w + 3 + 4 (+ alignment): u8 words of 4 px, u16 words of 2 px;
+  // the packed lists need cell height below 512 and pair columns below 128
+  if (g.max_cell_w + 17 <= 4 * 15) launch_fast_tp<38, 15>(g, dg, cells, n_img, pyr, cand, cand_count, flags, st);
+  else launch_fast_tp<76, 37>(g, dg, cells, n_img, pyr, cand, cand_count, flags, st);
   count_launch();
 }
 
