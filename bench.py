@@ -291,6 +291,14 @@ def run_cuorb(args):
         dom_all = max({k: v for k, v in stage_ms.items() if k != "h2d"}, key=lambda k: stage_ms[k])
         ach = ab[dom] * B / (stage_ms[dom] * 1e-3) / 1e9
         stage_gbs = {k: ab[k] * B / (stage_ms[k] * 1e-3) / 1e9 for k in pix}
+        # DRAM traffic of the dominant kernel from the committed `ncu --set full` capture (per image)
+        traffic = None
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+            if dom in tj:
+                traffic = tj[dom]["dram_bytes_per_image"] * B
+        except Exception:
+            pass
         cores = os.cpu_count() or 1
         cpu_fps, cpu_n, _, _ = cpu_baseline(cores) if not args.no_cpu_baseline else (None, 0, 0, 0)
         line = {
@@ -308,7 +316,9 @@ def run_cuorb(args):
                     "d2h_bytes_per_step": d2h_bytes * world, "ms_per_step": 1e3 * t_e2e / args.steps},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
-                         "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,
+                         "note": "stage times: CUDA events on the launching stream, handles serialised; FAST is bound by the "
+                                 "integer ALU pipe (min/max network), not HBM - see DESIGN.md section 6",
                          "stage_ms_per_step": stage_ms, "stage_gbs": stage_gbs,
                          "dominant_stage_overall": dom_all,
                          "algorithmic_bytes_per_image": ab},
