@@ -104,7 +104,8 @@ void launch_fast(const ExtractorGeom& g, const ExtractorGeom* dg, const int4* ce
 void launch_octree(const ExtractorGeom& g, const ExtractorGeom* dg, int n_img, const unsigned* cand,
                    unsigned* cand_scratch, const int* cand_count, LevelKey* keys, int* key_count,
                    int* flags, cudaStream_t st);
-void launch_describe(const ExtractorGeom& g, const ExtractorGeom* dg, int n_img, const uint8_t* pyr,
+struct TmaMaps;
+void launch_describe(const ExtractorGeom& g, const ExtractorGeom* dg, const TmaMaps& tmaps, int n_img, const uint8_t* pyr,
                      const uint8_t* blur, const LevelKey* keys, const int* key_count, int lap0,
                      int lap1, int* slot_map, cuorb_keypoint* out_kps, uint8_t* out_desc,
                      int* out_n, int* out_mono, cudaStream_t st);

@@ -6,6 +6,7 @@
 #include <mutex>
 
 #include "common.cuh"
+#include "tma.cuh"
 
 namespace cuorb {
 
@@ -40,6 +41,7 @@ struct cuorb_extractor {
   ExtractorGeom* d_geom = nullptr;
   ResizeTap *d_xtab = nullptr, *d_ytab = nullptr;
   int4*      d_blur_tiles = nullptr;
+  TmaMaps    tmaps;                   // TMA tensor maps of the pyramid / blurred planes (per level), passed as __grid_constant__
   int4*      d_fast_cells = nullptr;  // per FAST cell: level, x0 | y0 << 16, dw | dh << 16
   int        n_blur_tiles = 0;
   uint8_t *  d_input = nullptr, *d_pyr = nullptr, *d_blur = nullptr;
@@ -188,6 +190,30 @@ static int build_geometry(const cuorb_extractor* e, int w, int h, ExtractorGeom&
 
 }  // namespace cuorb
 
+// TMA tensor-map encoding through the driver entry point (no link-time dependency on libcuda)
+namespace cuorb {
+int tma_encode_u8_3d(CUtensorMap* out, void* base, uint64_t width_bytes, uint64_t rows, uint64_t images,
+                     uint64_t row_pitch, uint64_t image_stride, uint32_t box_w, uint32_t box_h) {
+  typedef CUresult (*encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static encode_fn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || !p) return -1;
+    fn = (encode_fn)p;
+  }
+  const cuuint64_t dims[3] = {width_bytes, rows, images};
+  const cuuint64_t strides[2] = {row_pitch, image_stride};
+  const cuuint32_t box[3] = {box_w, box_h, 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  return fn(out, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS
+             ? 0 : -1;
+}
+}  // namespace cuorb
+
 // ------------------------------------------------------------------------------------------
 // handle lifetime
 // ------------------------------------------------------------------------------------------
@@ -243,6 +269,21 @@ static int set_size(cuorb_extractor* e, int w, int h) {
   CUORB_CUDA_TRY(cudaMemcpy(e->d_blur_tiles, tiles.data(), tiles.size() * sizeof(int4), cudaMemcpyHostToDevice));
   e->n_blur_tiles = (int)tiles.size();
   CUORB_CUDA_TRY(cudaMemcpy(e->d_fast_cells, cells.data(), cells.size() * sizeof(int4), cudaMemcpyHostToDevice));
+  {
+    TmaMaps tm;
+    memset(&tm, 0, sizeof(tm));
+    for (int l = 0; l < g.nlevels; l++) {
+      const LevelGeom& L = g.lv[l];
+      if (tma_encode_u8_3d(&tm.pyr_ic[l], e->d_pyr + L.plane_off, (uint64_t)L.pitch, (uint64_t)L.h + 2 * EDGE_THRESHOLD, nb,
+                           (uint64_t)L.pitch, g.pyr_img_stride, IC_BOX_W, IC_BOX_H) != 0 ||
+          tma_encode_u8_3d(&tm.blur_br[l], e->d_blur + L.blur_off, (uint64_t)L.bpitch, (uint64_t)L.h, nb, (uint64_t)L.bpitch,
+                           g.blur_img_stride, BR_BOX_W, BR_BOX_H) != 0) {
+        set_error("cuTensorMapEncodeTiled failed (TMA tensor map for the pyramid planes)");
+        return CUORB_E_CUDA;
+      }
+    }
+    e->tmaps = tm;
+  }
   e->g = g; e->cur_w = w; e->cur_h = h;
   e->have_batch = false; e->have_stereo = false;
   return CUORB_OK;
@@ -427,7 +468,7 @@ int cuorb_extract_batch_async(cuorb_extractor* e, int n_images, const uint8_t* i
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_BLUR], st);
   launch_blur(&e->g, e->d_geom, n_images, e->d_blur_tiles, e->n_blur_tiles, e->d_pyr, e->d_blur, st);
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_DESCRIBE], st);
-  launch_describe(e->g, e->d_geom, n_images, e->d_pyr, e->d_blur, e->d_keys, e->d_key_count, lap0, lap1,
+  launch_describe(e->g, e->d_geom, e->tmaps, n_images, e->d_pyr, e->d_blur, e->d_keys, e->d_key_count, lap0, lap1,
                   e->d_slot, e->d_out_kps, e->d_out_desc, e->d_out_n, e->d_out_mono, st);
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_STEREO], st);
   CUORB_CUDA_TRY(cudaGetLastError());

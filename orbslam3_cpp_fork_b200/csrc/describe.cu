@@ -5,21 +5,23 @@
 // k_finalize: one CTA per image.  Level offsets, then the reference's two-ended scatter
 //   (keypoints inside vLappingArea go to the back, the others to the front) turned into a block
 //   scan over the "stereo" flags.
-// k_describe: one CTA per 32 keypoints (8 warps x 4), three phases.
-//   A  IC_Angle: a warp per keypoint, lane = patch row.  The row is fetched as nine aligned 32-bit
-//      words; the radius-15 disc is a per-lane byte mask, and the two integer moments are DP4A
-//      dot products (sum I, sum position*I; the position weights are compile-time constants, the
-//      centre offset is subtracted afterwards), reduced with shuffles.
+// k_describe: one CTA per 16 keypoints, one warp per keypoint, three phases.
+//   A  lane 0 of each warp fetches the keypoint's two patches with TMA (cp.async.bulk.tensor,
+//      rank-3 maps over the batch-major planes): the 48x31-byte un-blurred box for IC_Angle and
+//      the 64x37-byte blurred box that holds every rotated BRIEF tap (box x is 16-byte aligned).  The boxes land in shared
+//      memory without touching L1 or registers and are signalled on the warp's mbarrier.
+//      IC_Angle: lane = patch row, two 128-bit shared loads, the radius-15 disc as a per-lane
+//      byte mask, the two integer moments as DP4A dot products, shuffle reduction.
 //   B  one lane per keypoint: cv::fastAtan2 with explicit _rn intrinsics (no FMA contraction,
 //      bit-exact with OpenCV's scalar float code) and cos/sin taken in double and rounded to float
-//      (the reference uses glibc cosf/sinf; see DESIGN.md "float policy") — 32 keypoints at once
-//      instead of one lane of a warp per keypoint.
-//   C  steered BRIEF: a warp per keypoint, lane l builds descriptor byte l from 16 rotated taps
-//      of the blurred level; the pattern is read as pre-converted float4 pairs.
+//      (the reference uses glibc cosf/sinf; see DESIGN.md "float policy").
+//   C  steered BRIEF: lane l builds descriptor byte l from 16 rotated taps read from the shared
+//      blurred box; the pattern is read as pre-converted float4 pairs.
 #include <cfloat>
 
 #include "../../include/cuorb_pattern.h"
 #include "common.cuh"
+#include "tma.cuh"
 
 namespace cuorb {
 
@@ -99,18 +101,24 @@ __device__ __forceinline__ unsigned nibble_to_bytemask(unsigned nib) {
   return ((nib * 0x00204081u) & 0x01010101u) * 0xFFu;
 }
 
-// grid: (ceil(kp_cap/32), n_img), block 256 = 8 warps x 4 keypoints
-__global__ void __launch_bounds__(256) k_describe(const ExtractorGeom* __restrict__ dg,
-                                                  const uint8_t* __restrict__ pyr,
-                                                  const uint8_t* __restrict__ blur,
-                                                  const LevelKey* __restrict__ keys,
-                                                  const int* __restrict__ key_count,
-                                                  const int* __restrict__ slot_map,
-                                                  cuorb_keypoint* __restrict__ out_kps,
-                                                  uint8_t* __restrict__ out_desc) {
-  __shared__ int   s_m01[32], s_m10[32], s_lvl[32];
-  __shared__ int   s_xy[32], s_score[32];
-  __shared__ float s_angle[32], s_cos[32], s_sin[32];
+constexpr int DESC_WARPS = 16;                               // keypoints per CTA
+constexpr int IC_BYTES = IC_BOX_W * IC_BOX_H;                // 1488
+constexpr int BR_BYTES = BR_BOX_W * BR_BOX_H;                // 2368
+constexpr int IC_SLOT = (IC_BYTES + 127) / 128 * 128;        // 1536
+constexpr int BR_SLOT = (BR_BYTES + 127) / 128 * 128;        // 2432
+
+// grid: (ceil(kp_cap/16), n_img), block 512 = 16 warps, warp per keypoint
+__global__ void __launch_bounds__(DESC_WARPS * 32) k_describe(const ExtractorGeom* __restrict__ dg,
+                                                              const __grid_constant__ TmaMaps tmaps,
+                                                              const LevelKey* __restrict__ keys,
+                                                              const int* __restrict__ key_count,
+                                                              const int* __restrict__ slot_map,
+                                                              cuorb_keypoint* __restrict__ out_kps,
+                                                              uint8_t* __restrict__ out_desc) {
+  extern __shared__ __align__(128) unsigned char smem[];     // DESC_WARPS x (IC_SLOT + BR_SLOT)
+  __shared__ uint64_t s_bar[DESC_WARPS];
+  __shared__ int   s_m01[DESC_WARPS], s_m10[DESC_WARPS];
+  __shared__ float s_angle[DESC_WARPS], s_cos[DESC_WARPS], s_sin[DESC_WARPS];
   __shared__ int   s_off[MAX_LEVELS + 1];
   const int img = blockIdx.y, nlv = dg->nlevels;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -119,53 +127,65 @@ __global__ void __launch_bounds__(256) k_describe(const ExtractorGeom* __restric
     for (int l = 0; l < nlv; l++) { s_off[l] = o; o += key_count[img * nlv + l]; }
     s_off[nlv] = o;
   }
+  if (lane == 0) mbar_init(&s_bar[wid], 1);
+  mbar_fence_init();
   __syncthreads();
   const int n = s_off[nlv];
-  const int g0 = blockIdx.x * 32;
+  const int g0 = blockIdx.x * DESC_WARPS;
   if (g0 >= n) return;
+  const int g = g0 + wid;
+  const bool live = g < n;
 
-  // ---- phase A: integer moments of the radius-15 disc ----
-#pragma unroll
-  for (int q = 0; q < 4; q++) {
-    const int kl = wid * 4 + q, g = min(g0 + kl, n - 1);  // tail slots recompute the last keypoint (never stored)
-    int l = 0;
+  // ---- phase A: fetch the two patches with TMA, then the integer moments of the disc ----
+  int l = 0, cx = 0, cy = 0, score = 0;
+  unsigned char* ic = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem) + 127) & ~(uintptr_t)127) + wid * (IC_SLOT + BR_SLOT);
+  unsigned char* br = ic + IC_SLOT;
+  if (live) {
     while (g >= s_off[l + 1]) l++;
     const LevelGeom& L = dg->lv[l];
     const LevelKey k = keys[(size_t)img * dg->key_img_stride + L.key_off + (g - s_off[l])];
-    const int cx = k.x, cy = k.y;
+    cx = k.x; cy = k.y; score = k.score;
+    const int icx = ROW_LEAD + cx - HALF_PATCH_SIZE;   // padded-plane x of the patch's first column
+    const int ioff = icx & 15;
+    if (lane == 0) {
+      mbar_expect_tx(&s_bar[wid], IC_BYTES + BR_BYTES);
+      // un-blurred plane is addressed in padded-plane coordinates (ROW_LEAD / EDGE_THRESHOLD offsets)
+      tma_load_3d(ic, &tmaps.pyr_ic[l], &s_bar[wid], icx - ioff, EDGE_THRESHOLD + cy - HALF_PATCH_SIZE, img);
+      tma_load_3d(br, &tmaps.blur_br[l], &s_bar[wid], (cx - 18) & ~15, cy - 18, img);
+    }
+    mbar_wait(&s_bar[wid], 0);
     int m01 = 0, m10 = 0;
     if (lane < 31) {
       const int v = lane - HALF_PATCH_SIZE;
       const int d = c_umax[v < 0 ? -v : v];
-      const int a_off = ((cx - HALF_PATCH_SIZE) & ~3) - cx;  // -18 .. -15, word aligned in memory
-      const unsigned* row = reinterpret_cast<const unsigned*>(
-          pyr + (size_t)img * dg->pyr_img_stride + L.pix_off + (ptrdiff_t)(cy + v) * L.pitch + cx + a_off);
-      // valid byte positions p (0..35): |a_off + p| <= d
-      const int lo = -d - a_off, hi = d - a_off;
+      // byte p of the box row is u = p - ioff - 15; valid |u| <= d
+      const int lo = ioff + HALF_PATCH_SIZE - d, hi = ioff + HALF_PATCH_SIZE + d;
       const unsigned long long mask = ((2ull << hi) - 1ull) & ~((1ull << lo) - 1ull);
+      const uint4* rowp = reinterpret_cast<const uint4*>(ic + lane * IC_BOX_W);
+      const uint4 w0 = rowp[0], w1 = rowp[1], w2 = rowp[2];
+      const unsigned w[12] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w, w2.x, w2.y, w2.z, w2.w};
       unsigned S = 0, P = 0;
 #pragma unroll
-      for (int kk = 0; kk < 9; kk++) {
-        const unsigned bm = nibble_to_bytemask((unsigned)(mask >> (4 * kk)) & 0xFu);
-        const unsigned w = row[kk] & bm;
+      for (int kk = 0; kk < 12; kk++) {
+        const unsigned wm = w[kk] & nibble_to_bytemask((unsigned)(mask >> (4 * kk)) & 0xFu);
         const unsigned pos = (4u * kk) | ((4u * kk + 1u) << 8) | ((4u * kk + 2u) << 16) | ((4u * kk + 3u) << 24);
-        S = __dp4a(w, 0x01010101u, S);
-        P = __dp4a(w, pos, P);
+        S = __dp4a(wm, 0x01010101u, S);
+        P = __dp4a(wm, pos, P);
       }
       m01 = v * (int)S;
-      m10 = (int)P + a_off * (int)S;
+      m10 = (int)P - (ioff + HALF_PATCH_SIZE) * (int)S;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       m01 += __shfl_xor_sync(0xffffffffu, m01, o);
       m10 += __shfl_xor_sync(0xffffffffu, m10, o);
     }
-    if (lane == 0) { s_m01[kl] = m01; s_m10[kl] = m10; s_lvl[kl] = l; s_xy[kl] = cx | (cy << 16); s_score[kl] = k.score; }
+    if (lane == 0) { s_m01[wid] = m01; s_m10[wid] = m10; }
   }
   __syncthreads();
 
   // ---- phase B: angle and rotation, one lane per keypoint ----
-  if (tid < 32) {
+  if (tid < DESC_WARPS && g0 + tid < n) {
     const float angle = fast_atan2_deg((float)s_m01[tid], (float)s_m10[tid]);
     const float factorPI = (float)(3.14159265358979323846 / (double)180.f);
     const float ang = __fmul_rn(angle, factorPI);
@@ -174,43 +194,36 @@ __global__ void __launch_bounds__(256) k_describe(const ExtractorGeom* __restric
     s_angle[tid] = angle; s_cos[tid] = (float)cs; s_sin[tid] = (float)sn;
   }
   __syncthreads();
+  if (!live) return;
 
-  // ---- phase C: steered BRIEF ----
+  // ---- phase C: steered BRIEF from the shared blurred box ----
+  const LevelGeom& L = dg->lv[l];
+  const float a = s_cos[wid], b = s_sin[wid];
+  const unsigned char* bc = br + 18 * BR_BOX_W + 18 + ((cx - 18) & 15);
+  unsigned val = 0;
 #pragma unroll
-  for (int q = 0; q < 4; q++) {
-    const int kl = wid * 4 + q, g = g0 + kl;
-    const bool live = g < n;
-    const int l = s_lvl[kl];
-    const LevelGeom& L = dg->lv[l];
-    const int cx = s_xy[kl] & 0xFFFF, cy = s_xy[kl] >> 16;
-    const float a = s_cos[kl], b = s_sin[kl];
-    const uint8_t* bc = blur + (size_t)img * dg->blur_img_stride + L.blur_off + (size_t)cy * L.bpitch + cx;
-    const int bp = L.bpitch;
-    unsigned val = 0;
-#pragma unroll
-    for (int j = 0; j < 8; j++) {
-      const float4 pt = d_patternf[lane * 8 + j];
-      const int iy0 = __float2int_rn(__fadd_rn(__fmul_rn(pt.x, b), __fmul_rn(pt.y, a)));
-      const int ix0 = __float2int_rn(__fsub_rn(__fmul_rn(pt.x, a), __fmul_rn(pt.y, b)));
-      const int iy1 = __float2int_rn(__fadd_rn(__fmul_rn(pt.z, b), __fmul_rn(pt.w, a)));
-      const int ix1 = __float2int_rn(__fsub_rn(__fmul_rn(pt.z, a), __fmul_rn(pt.w, b)));
-      const int t0 = bc[iy0 * bp + ix0], t1 = bc[iy1 * bp + ix1];
-      val |= (unsigned)(t0 < t1) << j;
-    }
-    // pack 4 bytes per word, lanes 0,4,8,.. store
-    unsigned w = val | (__shfl_down_sync(0xffffffffu, val, 1) << 8) |
-                 (__shfl_down_sync(0xffffffffu, val, 2) << 16) | (__shfl_down_sync(0xffffffffu, val, 3) << 24);
-    const int slot = live ? slot_map[(size_t)img * dg->kp_cap + g] : 0;
-    const size_t o = (size_t)img * dg->kp_cap + slot;
-    if (live && (lane & 3) == 0) reinterpret_cast<unsigned*>(out_desc + o * 32)[lane >> 2] = w;
-    if (live && lane == 0) {
-      cuorb_keypoint kp;
-      kp.x = (float)cx; kp.y = (float)cy;
-      if (l != 0) { kp.x = __fmul_rn(kp.x, L.scale); kp.y = __fmul_rn(kp.y, L.scale); }
-      kp.size = L.kp_size; kp.angle = s_angle[kl]; kp.response = (float)s_score[kl];
-      kp.octave = l; kp.class_id = -1;
-      out_kps[o] = kp;
-    }
+  for (int j = 0; j < 8; j++) {
+    const float4 pt = d_patternf[lane * 8 + j];
+    const int iy0 = __float2int_rn(__fadd_rn(__fmul_rn(pt.x, b), __fmul_rn(pt.y, a)));
+    const int ix0 = __float2int_rn(__fsub_rn(__fmul_rn(pt.x, a), __fmul_rn(pt.y, b)));
+    const int iy1 = __float2int_rn(__fadd_rn(__fmul_rn(pt.z, b), __fmul_rn(pt.w, a)));
+    const int ix1 = __float2int_rn(__fsub_rn(__fmul_rn(pt.z, a), __fmul_rn(pt.w, b)));
+    const int t0 = bc[iy0 * BR_BOX_W + ix0], t1 = bc[iy1 * BR_BOX_W + ix1];
+    val |= (unsigned)(t0 < t1) << j;
+  }
+  // pack 4 bytes per word, lanes 0,4,8,.. store
+  unsigned w = val | (__shfl_down_sync(0xffffffffu, val, 1) << 8) |
+               (__shfl_down_sync(0xffffffffu, val, 2) << 16) | (__shfl_down_sync(0xffffffffu, val, 3) << 24);
+  const int slot = slot_map[(size_t)img * dg->kp_cap + g];
+  const size_t o = (size_t)img * dg->kp_cap + slot;
+  if ((lane & 3) == 0) reinterpret_cast<unsigned*>(out_desc + o * 32)[lane >> 2] = w;
+  if (lane == 0) {
+    cuorb_keypoint kp;
+    kp.x = (float)cx; kp.y = (float)cy;
+    if (l != 0) { kp.x = __fmul_rn(kp.x, L.scale); kp.y = __fmul_rn(kp.y, L.scale); }
+    kp.size = L.kp_size; kp.angle = s_angle[wid]; kp.response = (float)score;
+    kp.octave = l; kp.class_id = -1;
+    out_kps[o] = kp;
   }
 }
 
@@ -234,13 +247,17 @@ int init_describe_constants() {
   return 0;
 }
 
-void launch_describe(const ExtractorGeom& g, const ExtractorGeom* dg, int n_img, const uint8_t* pyr,
+void launch_describe(const ExtractorGeom& g, const ExtractorGeom* dg, const TmaMaps& tmaps, int n_img, const uint8_t* pyr,
                      const uint8_t* blur, const LevelKey* keys, const int* key_count, int lap0,
                      int lap1, int* slot_map, cuorb_keypoint* out_kps, uint8_t* out_desc, int* out_n,
                      int* out_mono, cudaStream_t st) {
+  (void)pyr; (void)blur;  // read through the TMA tensor maps
+  const int smem = DESC_WARPS * (IC_SLOT + BR_SLOT) + 128;
+  static bool attr = false;
+  if (!attr) { cudaFuncSetAttribute(k_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); attr = true; }
   k_finalize<<<n_img, 256, 0, st>>>(dg, keys, key_count, lap0, lap1, slot_map, out_n, out_mono);
-  k_describe<<<dim3((g.kp_cap + 31) / 32, n_img), 256, 0, st>>>(dg, pyr, blur, keys, key_count, slot_map,
-                                                             out_kps, out_desc);
+  k_describe<<<dim3((g.kp_cap + DESC_WARPS - 1) / DESC_WARPS, n_img), DESC_WARPS * 32, smem, st>>>(
+      dg, tmaps, keys, key_count, slot_map, out_kps, out_desc);
   count_launch(2);
 }
 
