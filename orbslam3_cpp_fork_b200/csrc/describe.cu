@@ -25,7 +25,7 @@
 
 namespace cuorb {
 
-__device__ float4 d_patternf[256];  // 256 pairs (x0,y0,x1,y1) as float; lane l reads pairs 8l .. 8l+7
+__device__ float4 d_patternf[256];  // pair 8l+j (x0,y0,x1,y1) as float at index 32j + l: a warp reads 512 contiguous bytes
 __constant__ int c_umax[16];
 
 // IEEE, FMA-free restatement of OpenCV's scalar fastAtan2 (core/mathfuncs_core.simd.hpp)
@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_describe(const ExtractorGeo
   unsigned val = 0;
 #pragma unroll
   for (int j = 0; j < 8; j++) {
-    const float4 pt = d_patternf[lane * 8 + j];
+    const float4 pt = d_patternf[j * 32 + lane];
     const int iy0 = __float2int_rn(__fadd_rn(__fmul_rn(pt.x, b), __fmul_rn(pt.y, a)));
     const int ix0 = __float2int_rn(__fsub_rn(__fmul_rn(pt.x, a), __fmul_rn(pt.y, b)));
     const int iy1 = __float2int_rn(__fadd_rn(__fmul_rn(pt.z, b), __fmul_rn(pt.w, a)));
@@ -230,7 +230,9 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_describe(const ExtractorGeo
 int init_describe_constants() {
   // pattern: 256 pairs x (x0,y0,x1,y1) converted to float once
   float pf[1024];
-  for (int i = 0; i < 1024; i++) pf[i] = (float)CUORB_BIT_PATTERN_31[i];
+  for (int l = 0; l < 32; l++)
+    for (int j = 0; j < 8; j++)
+      for (int c = 0; c < 4; c++) pf[(j * 32 + l) * 4 + c] = (float)CUORB_BIT_PATTERN_31[(l * 8 + j) * 4 + c];
   if (cudaMemcpyToSymbol(d_patternf, pf, sizeof(pf)) != cudaSuccess) return -1;
   // umax (src/ORBextractor.cc:446-464), same float/double sequence as the reference ctor
   int umax[16];
