@@ -130,46 +130,60 @@ __global__ void __launch_bounds__(PYR_TX) k_pyr_resize(const ExtractorGeom* __re
   }
   const uint8_t* src = base + S.pix_off + (WIDE ? 0 : cbase);
 
-  auto load_row = [&](int sy, unsigned (&h)[4]) {
+  // raw words of one source row (WIDE: the four columns' tap pairs packed as p0 | p1 << 8)
+  auto fetch = [&](int sy, unsigned (&w)[4]) {
     const uint8_t* r = src + (size_t)min(sy, sh1) * spitch;  // OpenCV clips source rows to sh-1
     if (!WIDE) {
       const unsigned* p = reinterpret_cast<const unsigned*>(r);
-      hsum(p[0], p[1], p[2], T, h);
+      w[0] = p[0]; w[1] = p[1]; w[2] = p[2]; w[3] = 0;
     } else {
 #pragma unroll
-      for (int b = 0; b < 4; b++)
-        h[b] = (r[sxs[b]] * (T.coef[b] & 0xFFFFu) + r[sxs[b] + 1] * (T.coef[b] >> 16)) >> 4;
+      for (int b = 0; b < 4; b++) w[b] = (unsigned)r[sxs[b]] | ((unsigned)r[sxs[b] + 1] << 8);
     }
   };
-  auto emit = [&](int y, const unsigned (&hA)[4], const unsigned (&hB)[4], const ResizeTap ty) {
-    const unsigned out = vblend(hA, hB, (unsigned)ty.a0 << 16, (unsigned)ty.a1 << 16);
-    dst[(size_t)(y + EDGE_THRESHOLD) * (dpitch >> 2)] = out;
-    if (y >= 1 && y <= EDGE_THRESHOLD) dst[(size_t)(EDGE_THRESHOLD - y) * (dpitch >> 2)] = out;
-    if (y >= lh - 1 - EDGE_THRESHOLD && y <= lh - 2) dst[(size_t)(2 * lh + EDGE_THRESHOLD - 2 - y) * (dpitch >> 2)] = out;
+  auto hsum_row = [&](const unsigned (&w)[4], unsigned (&h)[4]) {
+    if (!WIDE) {
+      hsum(w[0], w[1], w[2], T, h);
+    } else {
+#pragma unroll
+      for (int b = 0; b < 4; b++) h[b] = __dp2a_lo(T.coef[b], w[b], 0u) >> 4;
+    }
   };
-
   const int y0 = blockIdx.y * PYR_RS, y1 = min(y0 + PYR_RS, lh);
   const ResizeTap* yt = ytab + L.ytab_off;
   int y = y0;
   ResizeTap ty = yt[y];
   int s = max((int)ty.s, 0);
-  unsigned h0[4], h1[4];
-  load_row(s, h0);
+  // emit every output row whose upper source row is `s` (hA = row s, hB = row s+1); false when the strip is done
+  auto emit_rows = [&](const unsigned (&hA)[4], const unsigned (&hB)[4]) -> bool {
+    while (max((int)ty.s, 0) == s) {
+      const unsigned out = vblend(hA, hB, (unsigned)ty.a0 << 16, (unsigned)ty.a1 << 16);
+      dst[(size_t)(y + EDGE_THRESHOLD) * (dpitch >> 2)] = out;
+      if (y >= 1 && y <= EDGE_THRESHOLD) dst[(size_t)(EDGE_THRESHOLD - y) * (dpitch >> 2)] = out;
+      if (y >= lh - 1 - EDGE_THRESHOLD && y <= lh - 2) dst[(size_t)(2 * lh + EDGE_THRESHOLD - 2 - y) * (dpitch >> 2)] = out;
+      if (++y >= y1) return false;
+      ty = yt[y];
+    }
+    s++;
+    return true;
+  };
+
+  unsigned h0[4], h1[4], raw[4][4];
+  fetch(s, raw[0]);
+  hsum_row(raw[0], h0);
   for (;;) {
-    load_row(s + 1, h1);                       // h0 = source row s, h1 = row s+1
-    while (max((int)ty.s, 0) == s) {
-      emit(y, h0, h1, ty);
-      if (++y >= y1) return;
-      ty = yt[y];
-    }
-    s++;
-    load_row(s + 1, h0);                       // h1 = source row s, h0 = row s+1
-    while (max((int)ty.s, 0) == s) {
-      emit(y, h1, h0, ty);
-      if (++y >= y1) return;
-      ty = yt[y];
-    }
-    s++;
+    // four source rows in flight per iteration (memory-level parallelism: the small levels are
+    // DRAM-latency bound); h0 holds source row s on entry
+#pragma unroll
+    for (int k = 0; k < 4; k++) fetch(s + 1 + k, raw[k]);
+    hsum_row(raw[0], h1);
+    if (!emit_rows(h0, h1)) return;
+    hsum_row(raw[1], h0);
+    if (!emit_rows(h1, h0)) return;
+    hsum_row(raw[2], h1);
+    if (!emit_rows(h0, h1)) return;
+    hsum_row(raw[3], h0);
+    if (!emit_rows(h1, h0)) return;
   }
 }
 
