@@ -144,110 +144,123 @@ __global__ void __launch_bounds__(128) k_fast_cells(const ExtractorGeom* __restr
   }
   __syncthreads();
 
-  // ---- phase 2a: necessary condition on the 4 compass ring pixels, four pixels per thread on the
-  // u8 tile.  An arc of 9 always contains two adjacent compass points, so a corner at minThFAST
-  // needs (|N-c| > t or |S-c| > t) and (|E-c| > t or |W-c| > t).  Pixel pairs with a passing pixel
-  // are appended to the warp's own list segment as (row << 7 | pair column).
-  {
-    const int nqm = ((cx0 + dw + 3) >> 2) - 1;  // quads = tile words 1 .. nqm (columns 4 .. 4*nqm+3)
-    const int nquads = nqm * dh;
-    const unsigned inv = magic(nqm);
-    const unsigned K = (unsigned)(127 - min(min_th, 127)) * 0x01010101u;
-    unsigned short* seg = s_plist + wid * pcap;
-    int cnt = 0;
-    for (int i0 = 0; i0 < nquads; i0 += 128) {
-      const int i = i0 + tid;
-      bool f0 = false, f1 = false;
-      int r = 0, q = 0;
-      if (i < nquads) {
-        r = fastdiv(i, inv, nqm); q = i - r * nqm + 1;
-        const unsigned* T = s_tile8 + (r + 3) * TPB + q;
-        const unsigned C = T[0];
-        const unsigned E = __funnelshift_r(C, T[1], 24), W = __funnelshift_r(T[-1], C, 8);
-        const unsigned aN = __vabsdiffu4(T[3 * TPB], C), aS = __vabsdiffu4(T[-3 * TPB], C);
-        const unsigned aE = __vabsdiffu4(E, C), aW = __vabsdiffu4(W, C);
-        // per byte "a > t": bit 7 of a | ((a & 0x7f) + (127 - t))
-        const unsigned mN = aN | ((aN & 0x7f7f7f7fu) + K), mS = aS | ((aS & 0x7f7f7f7fu) + K);
-        const unsigned mE = aE | ((aE & 0x7f7f7f7fu) + K), mW = aW | ((aW & 0x7f7f7f7fu) + K);
-        const unsigned pass = (mN | mS) & (mE | mW) & 0x80808080u;
-        f0 = (pass & 0x0000FFFFu) != 0; f1 = (pass & 0xFFFF0000u) != 0;
-      }
-      const unsigned short e = (unsigned short)((r << 7) | (2 * q - 2));   // pair column = (s - 4) / 2
-      warp_append(f0, e, seg, cnt, lt);
-      warp_append(f1, (unsigned short)(e + 1), seg, cnt, lt);
-    }
-    if (lane == 0) s_pcnt[wid] = cnt;
-  }
-  __syncthreads();
-
-  // ---- phase 2b: full score network on the listed pairs; corners go to the warp's corner list ----
-  {
-    const int pc4[4] = {s_pcnt[0], s_pcnt[1], s_pcnt[2], s_pcnt[3]};
-    const int np = pc4[0] + pc4[1] + pc4[2] + pc4[3];
-    unsigned short* seg = s_clist + wid * ccap;
-    int cnt = 0;
-    for (int i0 = 0; i0 < np; i0 += 128) {
-      const int i = i0 + tid;
-      bool c0 = false, c1 = false;
-      int r = 0, px = 0;
-      if (i < np) {
-        const int e = seg_fetch(s_plist, pcap, pc4, i);
-        r = e >> 7;
-        const int pc = e & 127;
-        px = 4 + 2 * pc - cx0;  // first pixel of the pair, cell-relative (may be outside the cell)
-        const unsigned* T = s_tile + (r + 3) * TP + 2 + pc;
-        unsigned ring[16];
-        {
-          const unsigned a = T[3 * TP - 1], b = T[3 * TP], c = T[3 * TP + 1];
-          ring[0] = b; ring[1] = odd_pair(b, c); ring[15] = odd_pair(a, b);
+  // The reference runs FAST at iniThFAST and, only if the cell yields no keypoint, again at
+  // minThFAST (:798-826).  Same here: pass 0 scores only what can reach iniThFAST (its NMS sees
+  // exactly the corners FAST(ini) would see); pass 1 repeats everything at minThFAST for the
+  // (rare on textured images) cells that came up empty.
+  int thr = ini_th;
+  for (int pass = 0; pass < 2; pass++) {
+    const int cur_th = pass == 0 ? ini_th : min_th;
+    thr = cur_th;
+    // ---- phase 2a: necessary condition on the 4 compass ring pixels, four pixels per thread on the
+    // u8 tile.  An arc of 9 always contains two adjacent compass points, so a corner at minThFAST
+    // at threshold t needs (|N-c| > t or |S-c| > t) and (|E-c| > t or |W-c| > t).  Pixel pairs with a passing pixel
+    // are appended to the warp's own list segment as (row << 7 | pair column).
+    {
+      const int nqm = ((cx0 + dw + 3) >> 2) - 1;  // quads = tile words 1 .. nqm (columns 4 .. 4*nqm+3)
+      const int nquads = nqm * dh;
+      const unsigned inv = magic(nqm);
+      const unsigned K = (unsigned)(127 - min(cur_th, 127)) * 0x01010101u;
+      unsigned short* seg = s_plist + wid * pcap;
+      int cnt = 0;
+      for (int i0 = 0; i0 < nquads; i0 += 128) {
+        const int i = i0 + tid;
+        bool f0 = false, f1 = false;
+        int r = 0, q = 0;
+        if (i < nquads) {
+          r = fastdiv(i, inv, nqm); q = i - r * nqm + 1;
+          const unsigned* T = s_tile8 + (r + 3) * TPB + q;
+          const unsigned C = T[0];
+          const unsigned E = __funnelshift_r(C, T[1], 24), W = __funnelshift_r(T[-1], C, 8);
+          const unsigned aN = __vabsdiffu4(T[3 * TPB], C), aS = __vabsdiffu4(T[-3 * TPB], C);
+          const unsigned aE = __vabsdiffu4(E, C), aW = __vabsdiffu4(W, C);
+          // per byte "a > t": bit 7 of a | ((a & 0x7f) + (127 - t))
+          const unsigned mN = aN | ((aN & 0x7f7f7f7fu) + K), mS = aS | ((aS & 0x7f7f7f7fu) + K);
+          const unsigned mE = aE | ((aE & 0x7f7f7f7fu) + K), mW = aW | ((aW & 0x7f7f7f7fu) + K);
+          const unsigned pass = (mN | mS) & (mE | mW) & 0x80808080u;
+          f0 = (pass & 0x0000FFFFu) != 0; f1 = (pass & 0xFFFF0000u) != 0;
         }
-        ring[2] = T[2 * TP + 1]; ring[14] = T[2 * TP - 1];
-        ring[3] = odd_pair(T[TP + 1], T[TP + 2]); ring[13] = odd_pair(T[TP - 2], T[TP - 1]);
-        ring[4] = odd_pair(T[1], T[2]); ring[12] = odd_pair(T[-2], T[-1]);
-        ring[5] = odd_pair(T[-TP + 1], T[-TP + 2]); ring[11] = odd_pair(T[-TP - 2], T[-TP - 1]);
-        ring[6] = T[-2 * TP + 1]; ring[10] = T[-2 * TP - 1];
-        {
-          const unsigned a = T[-3 * TP - 1], b = T[-3 * TP], c = T[-3 * TP + 1];
-          ring[8] = b; ring[7] = odd_pair(b, c); ring[9] = odd_pair(a, b);
-        }
-        unsigned A, B;
-        arc_extremes(T[0], ring, A, B);
-        // score = max(a, -b) - 1 with a = A - 256, b = B - 256   (cornerScore<16>)
-        const int s0 = max((int)(A & 0xFFFFu) - 257, 255 - (int)(B & 0xFFFFu));
-        const int s1 = max((int)(A >> 16) - 257, 255 - (int)(B >> 16));
-        unsigned char* q = s_score + (r + 1) * sp + px + 4;
-        c0 = px >= 0 && px < dw && s0 >= min_th;
-        c1 = px + 1 >= 0 && px + 1 < dw && s1 >= min_th;
-        if (c0) q[0] = (unsigned char)s0;
-        if (c1) q[1] = (unsigned char)s1;
+        const unsigned short e = (unsigned short)((r << 7) | (2 * q - 2));   // pair column = (s - 4) / 2
+        warp_append(f0, e, seg, cnt, lt);
+        warp_append(f1, (unsigned short)(e + 1), seg, cnt, lt);
       }
-      warp_append(c0, (unsigned short)((r << 7) | px), seg, cnt, lt);
-      warp_append(c1, (unsigned short)((r << 7) | (px + 1)), seg, cnt, lt);
+      if (lane == 0) s_pcnt[wid] = cnt;
     }
-    if (lane == 0) s_ccnt[wid] = cnt;
-  }
-  __syncthreads();
+    __syncthreads();
 
-  // ---- phase 3: NMS inside the cell over the listed corners, threshold choice, emit ----
-  bool any_ini = false;
-  {
-    const int cc4[4] = {s_ccnt[0], s_ccnt[1], s_ccnt[2], s_ccnt[3]};
-    const int nc = cc4[0] + cc4[1] + cc4[2] + cc4[3];
-    for (int i = tid; i < nc; i += 128) {
-      const int e = seg_fetch(s_clist, ccap, cc4, i);
-      const int r = e >> 7, px = e & 127;
-      const unsigned char* q = s_score + (r + 1) * sp + px + 4;
-      const int s = q[0];
-      const bool lm = s > q[-1] && s > q[1] && s > q[-sp - 1] && s > q[-sp] && s > q[-sp + 1] &&
-                      s > q[sp - 1] && s > q[sp] && s > q[sp + 1];
-      if (lm) {
-        any_ini |= s >= ini_th;
-        // region coordinates of vToDistributeKeys: roi pt + (j*wCell, i*hCell)   (:842-846)
-        s_list[atomicAdd(&s_nlist, 1)] = pack_cand(x0 + px - FAST_BORDER, y0 + r - FAST_BORDER, s);
+    // ---- phase 2b: full score network on the listed pairs; corners go to the warp's corner list ----
+    {
+      const int pc4[4] = {s_pcnt[0], s_pcnt[1], s_pcnt[2], s_pcnt[3]};
+      const int np = pc4[0] + pc4[1] + pc4[2] + pc4[3];
+      unsigned short* seg = s_clist + wid * ccap;
+      int cnt = 0;
+      for (int i0 = 0; i0 < np; i0 += 128) {
+        const int i = i0 + tid;
+        bool c0 = false, c1 = false;
+        int r = 0, px = 0;
+        if (i < np) {
+          const int e = seg_fetch(s_plist, pcap, pc4, i);
+          r = e >> 7;
+          const int pc = e & 127;
+          px = 4 + 2 * pc - cx0;  // first pixel of the pair, cell-relative (may be outside the cell)
+          const unsigned* T = s_tile + (r + 3) * TP + 2 + pc;
+          unsigned ring[16];
+          {
+            const unsigned a = T[3 * TP - 1], b = T[3 * TP], c = T[3 * TP + 1];
+            ring[0] = b; ring[1] = odd_pair(b, c); ring[15] = odd_pair(a, b);
+          }
+          ring[2] = T[2 * TP + 1]; ring[14] = T[2 * TP - 1];
+          ring[3] = odd_pair(T[TP + 1], T[TP + 2]); ring[13] = odd_pair(T[TP - 2], T[TP - 1]);
+          ring[4] = odd_pair(T[1], T[2]); ring[12] = odd_pair(T[-2], T[-1]);
+          ring[5] = odd_pair(T[-TP + 1], T[-TP + 2]); ring[11] = odd_pair(T[-TP - 2], T[-TP - 1]);
+          ring[6] = T[-2 * TP + 1]; ring[10] = T[-2 * TP - 1];
+          {
+            const unsigned a = T[-3 * TP - 1], b = T[-3 * TP], c = T[-3 * TP + 1];
+            ring[8] = b; ring[7] = odd_pair(b, c); ring[9] = odd_pair(a, b);
+          }
+          unsigned A, B;
+          arc_extremes(T[0], ring, A, B);
+          // score = max(a, -b) - 1 with a = A - 256, b = B - 256   (cornerScore<16>)
+          const int s0 = max((int)(A & 0xFFFFu) - 257, 255 - (int)(B & 0xFFFFu));
+          const int s1 = max((int)(A >> 16) - 257, 255 - (int)(B >> 16));
+          unsigned char* q = s_score + (r + 1) * sp + px + 4;
+          c0 = px >= 0 && px < dw && s0 >= cur_th;
+          c1 = px + 1 >= 0 && px + 1 < dw && s1 >= cur_th;
+          if (c0) q[0] = (unsigned char)s0;
+          if (c1) q[1] = (unsigned char)s1;
+        }
+        warp_append(c0, (unsigned short)((r << 7) | px), seg, cnt, lt);
+        warp_append(c1, (unsigned short)((r << 7) | (px + 1)), seg, cnt, lt);
+      }
+      if (lane == 0) s_ccnt[wid] = cnt;
+    }
+    __syncthreads();
+
+    // ---- phase 3: NMS inside the cell over the listed corners, threshold choice, emit ----
+    {
+      const int cc4[4] = {s_ccnt[0], s_ccnt[1], s_ccnt[2], s_ccnt[3]};
+      const int nc = cc4[0] + cc4[1] + cc4[2] + cc4[3];
+      for (int i = tid; i < nc; i += 128) {
+        const int e = seg_fetch(s_clist, ccap, cc4, i);
+        const int r = e >> 7, px = e & 127;
+        const unsigned char* q = s_score + (r + 1) * sp + px + 4;
+        const int s = q[0];
+        const bool lm = s > q[-1] && s > q[1] && s > q[-sp - 1] && s > q[-sp] && s > q[-sp + 1] &&
+                        s > q[sp - 1] && s > q[sp] && s > q[sp + 1];
+        if (lm) {
+          // region coordinates of vToDistributeKeys: roi pt + (j*wCell, i*hCell)   (:842-846)
+          s_list[atomicAdd(&s_nlist, 1)] = pack_cand(x0 + px - FAST_BORDER, y0 + r - FAST_BORDER, s);
+        }
       }
     }
+    if (__syncthreads_or(s_nlist > 0) || pass == 1 || min_th == ini_th) break;
+    // empty at iniThFAST: clear the score tile and retry at minThFAST
+    {
+      const int nz = (sp * (dh + 2)) >> 2;
+      for (int i = tid; i < nz; i += 128) reinterpret_cast<unsigned*>(s_score)[i] = 0;
+    }
+    __syncthreads();
   }
-  const int thr = __syncthreads_or(any_ini) ? ini_th : min_th;
   const int nl = s_nlist;
   if (nl == 0) return;
   unsigned* s_out = s_tile;  // pixel tile is dead: reuse it for the compacted survivors
