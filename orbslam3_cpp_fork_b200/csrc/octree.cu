@@ -100,6 +100,127 @@ __device__ __forceinline__ Box child_box(const Box& b, int q) {
   return c;
 }
 
+// ---- CTA-parallel std::sort -------------------------------------------------------------------
+// Produces the very permutation libstdc++'s introsort (introsort.cuh) produces, ties included,
+// without running it serially:
+//   * the parts of __introsort_loop are disjoint ranges, so all parts of one recursion depth are
+//     partitioned concurrently, one warp per part;
+//   * __unguarded_partition is a Hoare scan whose k-th swap pairs the k-th element (from the
+//     left) that is not less than the pivot with the k-th element (from the right) that is not
+//     greater, for as long as the former lies left of the latter.  Both sequences come from
+//     ballot prefix counts over the ORIGINAL contents (the pointers never re-read a swapped
+//     slot before they cross), the swaps are disjoint, and the returned cut is
+//     min(next left stopper, last swapped right slot);
+//   * the parts left for __final_insertion_sort are at most 16 long and no element is ever
+//     moved across a part boundary (everything left of a boundary is <= everything right of it
+//     and the insertion only passes strictly greater elements), so it equals a stable rank
+//     inside each part.
+// A part that exhausts the depth limit (heapsort branch) makes the function return false and the
+// caller runs the serial port instead.
+typedef unsigned short u16;
+
+__device__ __forceinline__ u64 sort_key(const SortEnt* a, int i) {
+  const u64 v = reinterpret_cast<const u64*>(a)[i];   // size | ulx << 32 | node << 48
+  return ((v & 0xFFFFFFFFull) << 16) | ((v >> 32) & 0xFFFFull);
+}
+
+__device__ int warp_partition(SortEnt* a, int first, int last, u16* Lpos, u16* Rpos, int lane) {
+  typedef cuorb_sort::Introsort<SortEnt, SortLess> IS;
+  if (lane == 0) IS::move_median_to_first(a + first, a + first + 1, a + first + (last - first) / 2, a + last - 1, SortLess());
+  __syncwarp();
+  const u64 pk = sort_key(a, first);
+  const unsigned lt = (1u << lane) - 1u;
+  int nL = 0, nR = 0;
+  for (int base = first + 1; base < last; base += 32) {
+    const int q = base + lane;
+    const bool isL = q < last && sort_key(a, q) >= pk;
+    const unsigned b = __ballot_sync(0xffffffffu, isL);
+    if (isL) Lpos[first + nL + __popc(b & lt)] = (u16)q;
+    nL += __popc(b);
+  }
+  for (int base = last - 1; base > first; base -= 32) {
+    const int q = base - lane;
+    const bool isR = q > first && sort_key(a, q) <= pk;
+    const unsigned b = __ballot_sync(0xffffffffu, isR);
+    if (isR) Rpos[first + nR + __popc(b & lt)] = (u16)q;
+    nR += __popc(b);
+  }
+  __syncwarp();
+  const int nmin = min(nL, nR);
+  int K = 0;
+  for (int base = 0; base < nmin; base += 32) {
+    const int k = base + lane;
+    const bool ok = k < nmin && Lpos[first + k] < Rpos[first + k];
+    K += __popc(__ballot_sync(0xffffffffu, ok));
+  }
+  u64* a64 = reinterpret_cast<u64*>(a);
+  for (int k = lane; k < K; k += 32) {
+    const int i = Lpos[first + k], j = Rpos[first + k];
+    const u64 t = a64[i]; a64[i] = a64[j]; a64[j] = t;
+  }
+  int cut = 0x7fffffff;
+  if (K < nL) cut = Lpos[first + K];
+  if (K > 0) cut = min(cut, (int)Rpos[first + K - 1]);
+  __syncwarp();
+  return cut;
+}
+
+// sorts a[0..n) (n <= cap); work arrays: seg (3*cap u16), pos (4*cap u16), tmp (cap entries)
+__device__ bool block_std_sort(SortEnt* a, int n, u16* seg, u16* pos, SortEnt* tmp, int cap) {
+  __shared__ int s_nseg, s_more, s_fb;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  u16 *segF = seg, *segL = seg + cap, *segD = seg + 2 * cap;
+  u16 *Lpos = pos, *Rpos = pos + cap, *lo = pos + 2 * cap, *hi = pos + 3 * cap;
+  if (tid == 0) {
+    segF[0] = 0; segL[0] = (u16)n; segD[0] = (u16)(2 * cuorb_sort::Introsort<SortEnt, SortLess>::lg(n));
+    s_nseg = 1; s_fb = 0;
+  }
+  __syncthreads();
+  if (n > 16) {
+    for (;;) {
+      const int nseg = s_nseg;
+      __syncthreads();
+      if (tid == 0) s_more = 0;
+      __syncthreads();
+      for (int si = wid; si < nseg; si += OT_THREADS / 32) {
+        const int f = segF[si], l = segL[si], d = segD[si];
+        if (l - f <= 16) continue;
+        if (d == 0) { if (lane == 0) s_fb = 1; continue; }
+        const int cut = warp_partition(a, f, l, Lpos, Rpos, lane);
+        if (lane == 0) {
+          segL[si] = (u16)cut; segD[si] = (u16)(d - 1);
+          const int j = atomicAdd(&s_nseg, 1);
+          segF[j] = (u16)cut; segL[j] = (u16)l; segD[j] = (u16)(d - 1);
+          if (cut - f > 16 || l - cut > 16) s_more = 1;
+        }
+      }
+      __syncthreads();
+      if (!s_more || s_fb) break;
+    }
+    if (s_fb) return false;
+  }
+  const int nseg = s_nseg;
+  for (int si = tid; si < nseg; si += OT_THREADS) {
+    const int f = segF[si], l = segL[si];
+    for (int q = f; q < l; q++) { lo[q] = (u16)f; hi[q] = (u16)l; }
+  }
+  __syncthreads();
+  for (int q = tid; q < n; q += OT_THREADS) {
+    const int f = lo[q], l = hi[q];
+    const u64 mk = sort_key(a, q);
+    int r = f;
+    for (int j = f; j < l; j++) {
+      const u64 kj = sort_key(a, j);
+      r += (kj < mk) || (kj == mk && j < q);
+    }
+    tmp[r] = a[q];
+  }
+  __syncthreads();
+  for (int q = tid; q < n; q += OT_THREADS) a[q] = tmp[q];
+  __syncthreads();
+  return true;
+}
+
 }  // namespace
 
 // grid: (nlevels, n_img), block OT_THREADS
@@ -194,8 +315,13 @@ __global__ void __launch_bounds__(OT_THREADS) k_octree(const ExtractorGeom* __re
     if (final_phase) {
       for (int i = tid; i < vcount; i += OT_THREADS) Vs[i] = V[i];
       __syncthreads();
-      if (tid == 0) cuorb_sort::Introsort<SortEnt, SortLess>::sort(Vs, Vs + vcount, SortLess());
-      __syncthreads();
+      if (vcount > 1 && !block_std_sort(Vs, vcount, remap, reinterpret_cast<u16*>(cc), reinterpret_cast<SortEnt*>(scanA), cap)) {
+        // depth limit reached somewhere (heapsort branch): run the serial port on a fresh copy
+        for (int i = tid; i < vcount; i += OT_THREADS) Vs[i] = V[i];
+        __syncthreads();
+        if (tid == 0) cuorb_sort::Introsort<SortEnt, SortLess>::sort(Vs, Vs + vcount, SortLess());
+        __syncthreads();
+      }
     }
     // ---- child counts of every node with more than one key ----
     for (int i = tid; i < size * 4; i += OT_THREADS) cc[i] = 0;

@@ -88,3 +88,14 @@ def test_introsort_port_equals_std_sort(tmp_path):
         assert L.introsort_check(1500, 700, 11 + mode, mode) == 0
     for n in (100, 1000, 20000):
         assert L.introsort_check_killer(n) == 0
+
+
+def test_parallel_sort_formulation_equals_std_sort(tmp_path):
+    """Host model of csrc/octree.cu's CTA-parallel sort (stopper sequences + stable rank per part)
+    reproduces std::sort's permutation on tie-heavy inputs."""
+    exe = tmp_path / "psc"
+    subprocess.check_call(["g++", "-O2", "-o", str(exe),
+                           os.path.join(ROOT, "tests", "native", "parallel_sort_check.cpp")])
+    out = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout
+    assert "ok cases=" in out.stdout
