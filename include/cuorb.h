@@ -216,6 +216,41 @@ int cuorb_search_by_projection_frame(int device, const cuorb_frame_view* cur, in
                                      int32_t* best_idx_out, int32_t* rot_bin_out,
                                      int32_t* keep_bins_out);
 
+/* ---- pre-extraction image operations ----
+ * What System::TrackStereo / TrackRGBD / TrackMonocular (src/System.cc:280-300, 384-386, 476) and
+ * Tracking::GrabImageStereo / RGBD / Monocular (src/Tracking.cc:1339-1357, 1449-1462, 1520-1533)
+ * do to a camera frame before ORBextractor::operator() sees it, fused into one device pass:
+ *   mode CUORB_PRE_REMAP : cv::remap(im, out, M1, M2, cv::INTER_LINEAR), M1/M2 = the CV_32FC1 maps of
+ *                          cv::initUndistortRectifyMap (src/Settings.cc:492-510), BORDER_CONSTANT 0
+ *   mode CUORB_PRE_RESIZE: cv::resize(im, out, newImSize)  (INTER_LINEAR; exact 2x2 -> INTER_AREA)
+ *   then cv::cvtColor(... -> GRAY) when the frame has 3 or 4 channels.
+ * Results are bit-identical to OpenCV 4.13's 8-bit fixed-point paths. */
+typedef enum cuorb_pixfmt {
+  CUORB_PIX_GRAY8 = 0, CUORB_PIX_RGB8 = 1, CUORB_PIX_BGR8 = 2, CUORB_PIX_RGBA8 = 3, CUORB_PIX_BGRA8 = 4
+} cuorb_pixfmt;
+typedef enum cuorb_pre_mode { CUORB_PRE_NONE = 0, CUORB_PRE_REMAP = 1, CUORB_PRE_RESIZE = 2 } cuorb_pre_mode;
+typedef struct cuorb_preproc cuorb_preproc;
+
+/* src_w x src_h: camera frame; dst_w x dst_h: what the extractor gets (== src for CUORB_PRE_NONE;
+ * the map size for REMAP; newImSize for RESIZE).  map_x / map_y: host float arrays dst_h x dst_w
+ * (REMAP only, else NULL).  max_batch frames per call.  NULL on error. */
+cuorb_preproc* cuorb_preproc_create(int device, cuorb_pre_mode mode, int src_w, int src_h, int dst_w,
+                                    int dst_h, const float* map_x, const float* map_y, int max_batch);
+void cuorb_preproc_destroy(cuorb_preproc* pre);
+
+/* Stand-alone (synchronous): n frames (row pitch `stride` bytes, `image_stride` bytes apart, host or
+ * device) -> n gray planes dst_h x dst_w, tightly packed, in host or device memory. */
+int cuorb_preprocess(cuorb_preproc* pre, int n_images, const uint8_t* src, size_t stride,
+                     size_t image_stride, cuorb_mem src_where, cuorb_pixfmt fmt, uint8_t* dst_gray,
+                     cuorb_mem dst_where);
+
+/* Fused with extraction: the gray planes are written straight into the extractor's level-0 input on
+ * the extractor's stream, then the cuorb_extract_batch_async pipeline runs on them (asynchronous;
+ * fetch as usual).  The extractor must have been created for at least dst_w x dst_h. */
+int cuorb_extract_batch_async_pre(cuorb_extractor* ext, cuorb_preproc* pre, int n_images,
+                                  const uint8_t* src, size_t stride, size_t image_stride,
+                                  cuorb_mem where, cuorb_pixfmt fmt, int lap0, int lap1);
+
 /* ---- instrumentation ---- */
 
 /* number of libcuorb kernel launches issued by this process so far (bench.py's gpu_launches) */

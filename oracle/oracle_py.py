@@ -36,7 +36,7 @@ class FrameViewC(C.Structure):
 
 def build(force: bool = False) -> str:
     srcs = [os.path.join(_HERE, f) for f in
-            ("orb_oracle.cpp", "orb_oracle_match.cpp", "orb_oracle_capi.cpp", "orb_oracle.hpp")]
+            ("orb_oracle.cpp", "orb_oracle_match.cpp", "orb_oracle_capi.cpp", "preproc_oracle.cpp", "orb_oracle.hpp")]
     stale = (not os.path.exists(_LIB_PATH)) or any(
         os.path.getmtime(s) > os.path.getmtime(_LIB_PATH) for s in srcs)
     if force or stale:
@@ -84,6 +84,13 @@ def lib() -> C.CDLL:
         L.oo_bench_stereo.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                       C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float,
                                       C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        L.oo_cvt_gray.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_size_t]
+        L.oo_remap.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p,
+                               C.c_void_p, C.c_int, C.c_int, C.c_size_t]
+        L.oo_resize_cn.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_void_p, C.c_int,
+                                   C.c_int, C.c_size_t]
+        L.oo_preprocess.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, C.c_void_p,
+                                    C.c_void_p, C.c_void_p, C.c_int, C.c_int]
         _lib = L
     return _lib
 
@@ -228,6 +235,58 @@ def fast_atan2(y, x):
     x = np.ascontiguousarray(x, np.float32)
     out = np.zeros_like(y)
     lib().oo_fast_atan2(_p(y), _p(x), _p(out), y.size)
+    return out
+
+
+# ---- pre-extraction image ops (preproc_oracle.cpp) ----
+PIX_GRAY, PIX_RGB, PIX_BGR, PIX_RGBA, PIX_BGRA = range(5)
+PRE_NONE, PRE_REMAP, PRE_RESIZE = range(3)
+
+
+def _channels(a):
+    return 1 if a.ndim == 2 else a.shape[2]
+
+
+def cvt_gray(img, rgb_order):
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    h, w, ch = img.shape
+    out = np.empty((h, w), np.uint8)
+    lib().oo_cvt_gray(_p(img), w, h, w * ch, ch, int(bool(rgb_order)), _p(out), w)
+    return out
+
+
+def remap(img, mapx, mapy):
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    mapx = np.ascontiguousarray(mapx, dtype=np.float32); mapy = np.ascontiguousarray(mapy, dtype=np.float32)
+    ch = _channels(img)
+    dh, dw = mapx.shape
+    out = np.empty((dh, dw) if ch == 1 else (dh, dw, ch), np.uint8)
+    lib().oo_remap(_p(img), img.shape[1], img.shape[0], img.shape[1] * ch, ch, _p(mapx), _p(mapy), _p(out), dw, dh, dw * ch)
+    return out
+
+
+def resize_cn(img, dw, dh):
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    ch = _channels(img)
+    out = np.empty((dh, dw) if ch == 1 else (dh, dw, ch), np.uint8)
+    lib().oo_resize_cn(_p(img), img.shape[1], img.shape[0], img.shape[1] * ch, ch, _p(out), dw, dh, dw * ch)
+    return out
+
+
+def preprocess(img, fmt, mode=PRE_NONE, mapx=None, mapy=None, dsize=None):
+    """remap|resize (on the raw channels) then gray conversion, as System::Track* + Tracking::GrabImage* do."""
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    ch = _channels(img)
+    sh, sw = img.shape[:2]
+    if mode == PRE_REMAP:
+        mapx = np.ascontiguousarray(mapx, dtype=np.float32); mapy = np.ascontiguousarray(mapy, dtype=np.float32)
+        dh, dw = mapx.shape
+    elif mode == PRE_RESIZE:
+        dw, dh = dsize
+    else:
+        dw, dh = sw, sh
+    out = np.empty((dh, dw), np.uint8)
+    lib().oo_preprocess(_p(img), sw, sh, sw * ch, int(fmt), int(mode), _p(mapx), _p(mapy), _p(out), dw, dh)
     return out
 
 

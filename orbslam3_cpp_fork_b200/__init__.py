@@ -6,3 +6,4 @@ include/cuorb.h), the ctypes binding, and the host-side mirrors of ORBextractor 
 from ._lib import KP_DTYPE, CuorbError, load  # noqa: F401
 from .extractor import ORBextractor  # noqa: F401
 from .matcher import Frame, MapPointSoA, ORBmatcher  # noqa: F401
+from .preproc import FramePreprocessor  # noqa: F401

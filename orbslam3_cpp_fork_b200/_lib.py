@@ -84,6 +84,13 @@ SIGNATURES = {
                                    [C.c_float, C.c_int, C.c_float, C.c_float, C.c_void_p]),
     "cuorb_search_by_projection_frame": (C.c_int, [C.c_int, C.POINTER(FrameView), C.c_int] + [C.c_void_p] * 7 +
                                          [C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "cuorb_preproc_create": (C.c_void_p, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                          C.c_void_p, C.c_int]),
+    "cuorb_preproc_destroy": (None, [C.c_void_p]),
+    "cuorb_preprocess": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, C.c_int,
+                                   C.c_void_p, C.c_int]),
+    "cuorb_extract_batch_async_pre": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_size_t,
+                                                C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int]),
     "cuorb_kernel_launch_count": (C.c_uint64, []),
     "cuorb_set_profiling": (C.c_int, [C.c_void_p, C.c_int]),
     "cuorb_stage_ms": (C.c_int, [C.c_void_p, C.c_void_p]),

@@ -128,4 +128,15 @@ struct StereoArgs {
 constexpr int STEREO_MAX_BUCKETS = 512;  // 8-row buckets: level-0 height below 4096
 void launch_stereo(const ExtractorGeom& g, const StereoArgs& a, cudaStream_t st);
 
+// pre-extraction image ops (preproc.cu): src = n images of sh x sw x channels, dst = gray dh x dw
+struct PreArgs {
+  const uint8_t* src; size_t sstride, simg_stride; int sw, sh;
+  uint8_t* dst; size_t dstride, dimg_stride; int dw, dh;
+  const float* mapx; const float* mapy;                                   // mode 1 (remap), dh x dw each
+  const int* xofs; const short* xa; const int* yofs; const short* yb;     // mode 2 (resize) tables
+  int area2;                                                              // mode 2: exact 2x2 decimation
+  int ir, ib;                                                             // channel index of R and B
+};
+void launch_preproc(const PreArgs& a, int channels, int mode, int n_img, cudaStream_t st);
+
 }  // namespace cuorb

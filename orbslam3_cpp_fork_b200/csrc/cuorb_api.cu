@@ -432,30 +432,11 @@ static int check_flags(cuorb_extractor* e) {
 
 extern "C" {
 
-int cuorb_extract_batch_async(cuorb_extractor* e, int n_images, const uint8_t* imgs, int width,
-                              int height, size_t stride, size_t image_stride, cuorb_mem where,
-                              int lap0, int lap1) {
-  if (!e) { set_error("null handle"); return CUORB_E_BADARG; }
-  if (!imgs || width <= 0 || height <= 0 || n_images <= 0) { set_error("empty image"); return CUORB_E_EMPTY; }
-  if (n_images > e->cfg.max_batch || stride < (size_t)width) { set_error("batch larger than max_batch or stride < width"); return CUORB_E_BADARG; }
-  CUORB_CUDA_TRY(cudaSetDevice(e->cfg.device));
-  int rc = set_size(e, width, height);
-  if (rc != CUORB_OK) return rc;
+// enqueue pyramid .. describe on device-resident gray planes (the H2D stage event is the caller's)
+static int enqueue_pipeline(cuorb_extractor* e, int n_images, const uint8_t* dimgs, int width, int height,
+                            size_t dstride, size_t dimg_stride, int lap0, int lap1) {
   cudaStream_t st = e->stream;
   const bool prof = e->profiling;
-  if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_H2D], st);
-  const uint8_t* dimgs = imgs;
-  size_t dstride = stride, dimg_stride = image_stride;
-  if (where == CUORB_MEM_HOST) {
-    if (stride == (size_t)width && (n_images == 1 || image_stride == (size_t)width * height)) {
-      CUORB_CUDA_TRY(cudaMemcpyAsync(e->d_input, imgs, (size_t)width * height * n_images, cudaMemcpyHostToDevice, st));
-    } else {
-      for (int i = 0; i < n_images; i++)
-        CUORB_CUDA_TRY(cudaMemcpy2DAsync(e->d_input + (size_t)i * width * height, width, imgs + (size_t)i * image_stride,
-                                         stride, width, height, cudaMemcpyHostToDevice, st));
-    }
-    dimgs = e->d_input; dstride = width; dimg_stride = (size_t)width * height;
-  }
   CUORB_CUDA_TRY(cudaMemsetAsync(e->d_cand_count, 0, sizeof(int) * (size_t)n_images * e->g.nlevels, st));
   CUORB_CUDA_TRY(cudaMemsetAsync(e->d_flags, 0, sizeof(int), st));
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_PYRAMID], st);
@@ -476,6 +457,184 @@ int cuorb_extract_batch_async(cuorb_extractor* e, int n_images, const uint8_t* i
   e->n_img = n_images; e->have_batch = true; e->have_stereo = false;
   e->have_stage_times = prof; e->stereo_timed = false;
   return CUORB_OK;
+}
+
+int cuorb_extract_batch_async(cuorb_extractor* e, int n_images, const uint8_t* imgs, int width,
+                              int height, size_t stride, size_t image_stride, cuorb_mem where,
+                              int lap0, int lap1) {
+  if (!e) { set_error("null handle"); return CUORB_E_BADARG; }
+  if (!imgs || width <= 0 || height <= 0 || n_images <= 0) { set_error("empty image"); return CUORB_E_EMPTY; }
+  if (n_images > e->cfg.max_batch || stride < (size_t)width) { set_error("batch larger than max_batch or stride < width"); return CUORB_E_BADARG; }
+  CUORB_CUDA_TRY(cudaSetDevice(e->cfg.device));
+  int rc = set_size(e, width, height);
+  if (rc != CUORB_OK) return rc;
+  cudaStream_t st = e->stream;
+  if (e->profiling) cudaEventRecord(e->ev_stage[CUORB_STAGE_H2D], st);
+  const uint8_t* dimgs = imgs;
+  size_t dstride = stride, dimg_stride = image_stride;
+  if (where == CUORB_MEM_HOST) {
+    if (stride == (size_t)width && (n_images == 1 || image_stride == (size_t)width * height)) {
+      CUORB_CUDA_TRY(cudaMemcpyAsync(e->d_input, imgs, (size_t)width * height * n_images, cudaMemcpyHostToDevice, st));
+    } else {
+      for (int i = 0; i < n_images; i++)
+        CUORB_CUDA_TRY(cudaMemcpy2DAsync(e->d_input + (size_t)i * width * height, width, imgs + (size_t)i * image_stride,
+                                         stride, width, height, cudaMemcpyHostToDevice, st));
+    }
+    dimgs = e->d_input; dstride = width; dimg_stride = (size_t)width * height;
+  }
+  return enqueue_pipeline(e, n_images, dimgs, width, height, dstride, dimg_stride, lap0, lap1);
+}
+
+// ------------------------------------------------------------------------------------------
+// pre-extraction image operations
+// ------------------------------------------------------------------------------------------
+struct cuorb_preproc {
+  int device = 0, mode = 0, sw = 0, sh = 0, dw = 0, dh = 0, max_batch = 1, area2 = 0;
+  float *d_mapx = nullptr, *d_mapy = nullptr;
+  int *  d_xofs = nullptr, *d_yofs = nullptr;
+  short *d_xa = nullptr, *d_yb = nullptr;
+  uint8_t *d_raw = nullptr, *d_gray = nullptr;  // staging: raw frames from the host / gray planes for the host
+  cudaStream_t stream = nullptr;
+};
+
+static int pix_channels(int fmt) { return fmt == CUORB_PIX_GRAY8 ? 1 : (fmt <= CUORB_PIX_BGR8 ? 3 : 4); }
+
+void cuorb_preproc_destroy(cuorb_preproc* p) {
+  if (!p) return;
+  cudaSetDevice(p->device);
+  void* dev[] = {p->d_mapx, p->d_mapy, p->d_xofs, p->d_yofs, p->d_xa, p->d_yb, p->d_raw, p->d_gray};
+  for (void* d : dev) if (d) cudaFree(d);
+  if (p->stream) cudaStreamDestroy(p->stream);
+  delete p;
+}
+
+cuorb_preproc* cuorb_preproc_create(int device, cuorb_pre_mode mode, int src_w, int src_h, int dst_w, int dst_h,
+                                    const float* map_x, const float* map_y, int max_batch) {
+  if (src_w <= 0 || src_h <= 0 || max_batch <= 0 || mode < CUORB_PRE_NONE || mode > CUORB_PRE_RESIZE) {
+    set_error("cuorb_preproc_create: bad size / mode"); return nullptr;
+  }
+  if (mode == CUORB_PRE_NONE) { dst_w = src_w; dst_h = src_h; }
+  if (dst_w <= 0 || dst_h <= 0 || (mode == CUORB_PRE_REMAP && (!map_x || !map_y))) {
+    set_error("cuorb_preproc_create: bad destination size or missing maps"); return nullptr;
+  }
+  if (cudaSetDevice(device) != cudaSuccess) { set_error("cuorb_preproc_create: cudaSetDevice failed (no CUDA device; libcuorb has no CPU fallback)"); return nullptr; }
+  cuorb_preproc* p = new cuorb_preproc();
+  p->device = device; p->mode = mode; p->sw = src_w; p->sh = src_h; p->dw = dst_w; p->dh = dst_h; p->max_batch = max_batch;
+  bool ok = cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking) == cudaSuccess;
+  ok &= dev_alloc(&p->d_raw, (size_t)src_w * src_h * 4 * max_batch) == cudaSuccess;
+  ok &= dev_alloc(&p->d_gray, (size_t)dst_w * dst_h * max_batch) == cudaSuccess;
+  if (ok && mode == CUORB_PRE_REMAP) {
+    const size_t n = (size_t)dst_w * dst_h;
+    ok &= dev_alloc(&p->d_mapx, n) == cudaSuccess && dev_alloc(&p->d_mapy, n) == cudaSuccess;
+    ok = ok && cudaMemcpy(p->d_mapx, map_x, n * sizeof(float), cudaMemcpyHostToDevice) == cudaSuccess &&
+         cudaMemcpy(p->d_mapy, map_y, n * sizeof(float), cudaMemcpyHostToDevice) == cudaSuccess;
+  }
+  if (ok && mode == CUORB_PRE_RESIZE) {
+    p->area2 = (src_w == 2 * dst_w && src_h == 2 * dst_h) ? 1 : 0;
+    // cv::resize INTER_LINEAR coefficient tables (imgproc/resize.cpp; same float sequence as the pyramid's)
+    std::vector<int> xofs(dst_w), yofs(dst_h);
+    std::vector<short> xa(2 * (size_t)dst_w), yb(2 * (size_t)dst_h);
+    const double scale_x = 1. / ((double)dst_w / src_w), scale_y = 1. / ((double)dst_h / src_h);
+    for (int dx = 0; dx < dst_w; dx++) {
+      float fx = (float)((dx + 0.5) * scale_x - 0.5);
+      int sx = (int)std::floor(fx);
+      fx -= sx;
+      if (sx < 0) { fx = 0; sx = 0; }
+      if (sx >= src_w - 1) { fx = 0; sx = src_w - 1; }
+      xofs[dx] = sx; xa[2 * dx] = sat_short((1.f - fx) * 2048.f); xa[2 * dx + 1] = sat_short(fx * 2048.f);
+    }
+    for (int dy = 0; dy < dst_h; dy++) {
+      float fy = (float)((dy + 0.5) * scale_y - 0.5);
+      int sy = (int)std::floor(fy);
+      fy -= sy;
+      yofs[dy] = sy; yb[2 * dy] = sat_short((1.f - fy) * 2048.f); yb[2 * dy + 1] = sat_short(fy * 2048.f);
+    }
+    ok &= dev_alloc(&p->d_xofs, xofs.size()) == cudaSuccess && dev_alloc(&p->d_yofs, yofs.size()) == cudaSuccess;
+    ok &= dev_alloc(&p->d_xa, xa.size()) == cudaSuccess && dev_alloc(&p->d_yb, yb.size()) == cudaSuccess;
+    ok = ok && cudaMemcpy(p->d_xofs, xofs.data(), xofs.size() * sizeof(int), cudaMemcpyHostToDevice) == cudaSuccess &&
+         cudaMemcpy(p->d_yofs, yofs.data(), yofs.size() * sizeof(int), cudaMemcpyHostToDevice) == cudaSuccess &&
+         cudaMemcpy(p->d_xa, xa.data(), xa.size() * sizeof(short), cudaMemcpyHostToDevice) == cudaSuccess &&
+         cudaMemcpy(p->d_yb, yb.data(), yb.size() * sizeof(short), cudaMemcpyHostToDevice) == cudaSuccess;
+  }
+  if (!ok) {
+    set_error(std::string("cuorb_preproc_create: ") + cudaGetErrorString(cudaGetLastError()));
+    cuorb_preproc_destroy(p);
+    return nullptr;
+  }
+  return p;
+}
+
+// src (host or device) -> gray planes at dst (device), on stream st
+static int enqueue_preproc(cuorb_preproc* p, int n, const uint8_t* src, size_t stride, size_t image_stride,
+                           cuorb_mem where, int fmt, uint8_t* d_dst, cudaStream_t st) {
+  const int ch = pix_channels(fmt);
+  const size_t row = (size_t)p->sw * ch;
+  if (stride < row) { set_error("preprocess: stride smaller than one row"); return CUORB_E_BADARG; }
+  const uint8_t* dsrc = src;
+  size_t dstride = stride, dimg = image_stride;
+  if (where == CUORB_MEM_HOST) {
+    if (stride == row && (n == 1 || image_stride == row * p->sh)) {
+      CUORB_CUDA_TRY(cudaMemcpyAsync(p->d_raw, src, row * p->sh * n, cudaMemcpyHostToDevice, st));
+    } else {
+      for (int i = 0; i < n; i++)
+        CUORB_CUDA_TRY(cudaMemcpy2DAsync(p->d_raw + (size_t)i * row * p->sh, row, src + (size_t)i * image_stride, stride,
+                                         row, p->sh, cudaMemcpyHostToDevice, st));
+    }
+    dsrc = p->d_raw; dstride = row; dimg = row * p->sh;
+  }
+  if (ch == 1 && p->mode == CUORB_PRE_NONE) {  // nothing to compute: the reference clones the frame
+    for (int i = 0; i < n; i++)
+      CUORB_CUDA_TRY(cudaMemcpy2DAsync(d_dst + (size_t)i * p->dw * p->dh, p->dw, dsrc + (size_t)i * dimg, dstride, p->dw,
+                                       p->dh, cudaMemcpyDeviceToDevice, st));
+    return CUORB_OK;
+  }
+  PreArgs a;
+  a.src = dsrc; a.sstride = dstride; a.simg_stride = dimg; a.sw = p->sw; a.sh = p->sh;
+  a.dst = d_dst; a.dstride = p->dw; a.dimg_stride = (size_t)p->dw * p->dh; a.dw = p->dw; a.dh = p->dh;
+  a.mapx = p->d_mapx; a.mapy = p->d_mapy; a.xofs = p->d_xofs; a.xa = p->d_xa; a.yofs = p->d_yofs; a.yb = p->d_yb;
+  a.area2 = p->area2;
+  const bool rgb = fmt == CUORB_PIX_RGB8 || fmt == CUORB_PIX_RGBA8;
+  a.ir = rgb ? 0 : 2; a.ib = rgb ? 2 : 0;
+  launch_preproc(a, ch, p->mode, n, st);
+  CUORB_CUDA_TRY(cudaGetLastError());
+  return CUORB_OK;
+}
+
+static int preproc_args_ok(cuorb_preproc* p, int n, const uint8_t* src, int fmt) {
+  if (!p) { set_error("null preproc handle"); return CUORB_E_BADARG; }
+  if (!src || n <= 0) { set_error("empty image"); return CUORB_E_EMPTY; }
+  if (n > p->max_batch || fmt < CUORB_PIX_GRAY8 || fmt > CUORB_PIX_BGRA8) { set_error("batch larger than max_batch or unknown pixel format"); return CUORB_E_BADARG; }
+  return CUORB_OK;
+}
+
+int cuorb_preprocess(cuorb_preproc* p, int n, const uint8_t* src, size_t stride, size_t image_stride,
+                     cuorb_mem src_where, cuorb_pixfmt fmt, uint8_t* dst, cuorb_mem dst_where) {
+  int rc = preproc_args_ok(p, n, src, fmt);
+  if (rc != CUORB_OK) return rc;
+  if (!dst) { set_error("null destination"); return CUORB_E_BADARG; }
+  CUORB_CUDA_TRY(cudaSetDevice(p->device));
+  uint8_t* d_dst = dst_where == CUORB_MEM_DEVICE ? dst : p->d_gray;
+  rc = enqueue_preproc(p, n, src, stride, image_stride, src_where, fmt, d_dst, p->stream);
+  if (rc != CUORB_OK) return rc;
+  if (dst_where == CUORB_MEM_HOST)
+    CUORB_CUDA_TRY(cudaMemcpyAsync(dst, p->d_gray, (size_t)p->dw * p->dh * n, cudaMemcpyDeviceToHost, p->stream));
+  CUORB_CUDA_TRY(cudaStreamSynchronize(p->stream));
+  return n;
+}
+
+int cuorb_extract_batch_async_pre(cuorb_extractor* e, cuorb_preproc* p, int n, const uint8_t* src, size_t stride,
+                                  size_t image_stride, cuorb_mem where, cuorb_pixfmt fmt, int lap0, int lap1) {
+  if (!e) { set_error("null handle"); return CUORB_E_BADARG; }
+  int rc = preproc_args_ok(p, n, src, fmt);
+  if (rc != CUORB_OK) return rc;
+  if (n > e->cfg.max_batch || p->device != e->cfg.device) { set_error("batch larger than the extractor's max_batch, or handles on different devices"); return CUORB_E_BADARG; }
+  CUORB_CUDA_TRY(cudaSetDevice(e->cfg.device));
+  rc = set_size(e, p->dw, p->dh);
+  if (rc != CUORB_OK) return rc;
+  if (e->profiling) cudaEventRecord(e->ev_stage[CUORB_STAGE_H2D], e->stream);
+  rc = enqueue_preproc(p, n, src, stride, image_stride, where, fmt, e->d_input, e->stream);
+  if (rc != CUORB_OK) return rc;
+  return enqueue_pipeline(e, n, e->d_input, p->dw, p->dh, (size_t)p->dw, (size_t)p->dw * p->dh, lap0, lap1);
 }
 
 int cuorb_extract_fetch_async(cuorb_extractor* e, cuorb_keypoint* kps, uint8_t* desc, int capacity,
