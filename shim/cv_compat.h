@@ -1,5 +1,5 @@
 // Minimal stand-in for the handful of OpenCV core types the ORB front-end API uses
-// (cv::Point2f, cv::KeyPoint, cv::Mat for CV_8UC1, InputArray/OutputArray), so the drop-in
+// (cv::Point2f, cv::KeyPoint, cv::Mat for CV_8UC1/3/4 and CV_32F, InputArray/OutputArray), so the drop-in
 // classes in this directory compile in an image without OpenCV C++ headers.  In the reference
 // tree this header is NOT used: define CUORB_SHIM_USE_OPENCV and <opencv2/core.hpp> supplies the
 // real types (cuorb_keypoint is layout-identical to cv::KeyPoint, so the shim memcpy's).
@@ -16,7 +16,10 @@
 
 #define CV_8U 0
 #define CV_8UC1 0
+#define CV_8UC3 16
+#define CV_8UC4 24
 #define CV_32F 5
+#define CV_32FC1 5
 
 namespace cv {
 
@@ -54,6 +57,7 @@ public:
   void release() { own_.reset(); data = nullptr; rows = cols = 0; step = 0; }
   bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
   int  type() const { return type_; }
+  int  channels() const { return (type_ >> 3) + 1; }
   Mat  row(int y) const { Mat m; m.rows = 1; m.cols = cols; m.step = step; m.data = data + (size_t)y * step; m.type_ = type_; m.own_ = own_; return m; }
   Mat  clone() const { Mat m(rows, cols, type_); for (int y = 0; y < rows; y++) std::memcpy(m.data + y * m.step, data + y * step, (size_t)cols * esz(type_)); return m; }
   template <typename T> T* ptr(int y = 0) { return (T*)(data + (size_t)y * step); }
@@ -63,7 +67,7 @@ public:
   Mat getMat() const { return *this; }   // so InputArray/OutputArray code reads like OpenCV's
 
 private:
-  static size_t esz(int type) { return type == CV_32F ? 4 : 1; }
+  static size_t esz(int type) { return (size_t)((type & 7) == CV_32F ? 4 : 1) * ((type >> 3) + 1); }
   int type_ = CV_8UC1;
   std::shared_ptr<unsigned char> own_;
 };

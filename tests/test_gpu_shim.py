@@ -47,3 +47,30 @@ def test_cpp_shim_stereo_frame(tmp_path):
     assert (ur == so["u_right"]).all() and (dp == so["depth"]).all()
     assert selfdist == 0 and d01 == int(np.unpackbits(d0[0] ^ d0[1]).sum())
     assert (pyr1 == oL.plane(1, 1)).all()
+
+
+def test_cpp_shim_frame_prep(tmp_path):
+    """shim/FramePrep.h: rectify + gray (+ fused extraction) of a BGR frame == oracle chain."""
+    from tests.preproc_cases import color_frames, rectify_maps
+    build.build_libcuorb()
+    exe = str(tmp_path / "prep_check")
+    pkg = os.path.join(ROOT, "orbslam3_cpp_fork_b200")
+    subprocess.check_call(["g++", "-std=c++17", "-O2", os.path.join(ROOT, "tests", "native", "prep_check.cpp"), "-o", exe,
+                           "-L" + pkg, "-l:libcuorb.so", "-Wl,-rpath," + pkg])
+    w, h, nf = 752, 480, 1000
+    frame = color_frames(1, h, w, 3, 90)[0]
+    mx, my = rectify_maps(w, h, 2)
+    frame.tofile(tmp_path / "f.raw"); mx.tofile(tmp_path / "mx.raw"); my.tofile(tmp_path / "my.raw")
+    out = str(tmp_path / "out.bin")
+    subprocess.check_call([exe, str(tmp_path / "f.raw"), str(w), str(h), str(tmp_path / "mx.raw"), str(tmp_path / "my.raw"), str(nf), out])
+    raw = open(out, "rb").read()
+    n, mono = [int(v) for v in np.frombuffer(raw, np.int32, 2)]
+    off = 8
+    gray = np.frombuffer(raw, np.uint8, w * h, off).reshape(h, w); off += w * h
+    k = np.frombuffer(raw, _lib.KP_DTYPE, n, off); off += 28 * n
+    d = np.frombuffer(raw, np.uint8, 32 * n, off).reshape(n, 32)
+    ref_gray = op.preprocess(frame, op.PIX_BGR, op.PRE_REMAP, mx, my)
+    assert (gray == ref_gray).all()
+    m0, k0, d0 = op.OracleExtractor(nf, 1.2, 8, 20, 7).extract(ref_gray)
+    assert (n, mono) == (len(k0), m0)
+    assert (k == k0).all() and (d == d0).all()
