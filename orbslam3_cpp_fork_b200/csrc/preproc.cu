@@ -13,8 +13,8 @@
 //           out = (((b0*(H0>>4))>>16) + ((b1*(H1>>4))>>16) + 2) >> 2; exact 2x2 decimation is
 //           OpenCV's INTER_AREA reroute (a+b+c+d+2)>>2;
 //   gray    (B*3735 + G*19235 + R*9798 + 2^14) >> 15.
-// One thread produces four horizontally adjacent gray pixels (one aligned store when the
-// destination pitch allows).  Bound: HBM/L2 gather — src bytes + 1 byte per output pixel.
+// Lanes of a warp work on adjacent pixels, four pixels per thread 64 apart.
+// Bound: L1 wavefronts of the byte gathers — src bytes + 1 byte per output pixel of HBM traffic.
 #include "common.cuh"
 
 namespace cuorb {
@@ -87,26 +87,23 @@ __device__ __forceinline__ int px_resize(const PreArgs& a, const uint8_t* img, i
   return gray_of<C>(v, a.ir, a.ib);
 }
 
-// grid: (ceil(dw/4/64), dh, n_img), block 64
+// grid: (ceil(dw/256), dh, n_img), block 64.  A thread produces pixels x0 + lane + 64k (k = 0..3):
+// the lanes of a warp read ADJACENT source pixels (one or two L1 wavefronts per tap instead of four)
+// and each byte store of a warp fills one 32-byte sector.
 template <int C, int MODE>
 __global__ void __launch_bounds__(64) k_preproc(const PreArgs a) {
-  const int x4 = (blockIdx.x * 64 + threadIdx.x) * 4, y = blockIdx.y, img = blockIdx.z;
-  if (x4 >= a.dw) return;
+  const int x0 = blockIdx.x * 256 + threadIdx.x, y = blockIdx.y, img = blockIdx.z;
   const uint8_t* src = a.src + (size_t)img * a.simg_stride;
-  uint8_t* d = a.dst + (size_t)img * a.dimg_stride + (size_t)y * a.dstride + x4;
-  unsigned w = 0;
-  const int n = min(4, a.dw - x4);
-  for (int k = 0; k < n; k++) {
+  uint8_t* d = a.dst + (size_t)img * a.dimg_stride + (size_t)y * a.dstride;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    const int x = x0 + 64 * k;
+    if (x >= a.dw) break;
     int g;
-    if (MODE == 1) g = px_remap<C>(a, src, x4 + k, y);
-    else if (MODE == 2) g = px_resize<C>(a, src, x4 + k, y);
-    else g = px_none<C>(a, src, x4 + k, y);
-    w |= (unsigned)g << (8 * k);
-  }
-  if (n == 4 && ((a.dstride | a.dimg_stride | (size_t)(uintptr_t)a.dst) & 3) == 0) {
-    *reinterpret_cast<unsigned*>(d) = w;
-  } else {
-    for (int k = 0; k < n; k++) d[k] = (uint8_t)(w >> (8 * k));
+    if (MODE == 1) g = px_remap<C>(a, src, x, y);
+    else if (MODE == 2) g = px_resize<C>(a, src, x, y);
+    else g = px_none<C>(a, src, x, y);
+    d[x] = (uint8_t)g;
   }
 }
 

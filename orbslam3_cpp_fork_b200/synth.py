@@ -94,3 +94,31 @@ def degenerate_image(w: int, h: int, kind: str, seed: int = 0) -> np.ndarray:
     if kind == "noise":
         return rng.integers(0, 256, size=(h, w), dtype=np.uint8)
     raise ValueError(kind)
+
+
+def color_frames(n: int, h: int, w: int, ch: int, seed: int) -> np.ndarray:
+    """n seeded raw camera frames [n, h, w(, ch)] with structure in every channel (the gray synthetic
+    frame plus per-channel offsets and noise) for the frame-preparation stage."""
+    rng = np.random.default_rng(seed)
+    out = []
+    for i in range(n):
+        g = synth_image(w, h, seed * 100 + i).astype(np.int32)
+        if ch == 1:
+            out.append(g.astype(np.uint8))
+            continue
+        chans = [np.clip(g + rng.integers(-30, 31, (h, w)) + 17 * (c - 1), 0, 255) for c in range(ch)]
+        out.append(np.stack(chans, -1).astype(np.uint8))
+    return np.stack(out)
+
+
+def rectify_maps(w: int, h: int, seed: int = 0):
+    """EuRoC-like stereo rectification maps (what cv::initUndistortRectifyMap would hand to cv::remap):
+    radial distortion plus a small rotation, float32 [h, w] each."""
+    yy, xx = np.mgrid[0:h, 0:w].astype(np.float64)
+    fx, fy, cx, cy = 0.61 * w, 0.95 * h, 0.49 * w, 0.52 * h
+    x = (xx - cx) / fx; y = (yy - cy) / fy
+    th = 0.012 + 0.001 * seed
+    xr = x * np.cos(th) - y * np.sin(th) + 0.004; yr = x * np.sin(th) + y * np.cos(th) - 0.003
+    r2 = xr * xr + yr * yr
+    k = 1 - 0.2834 * r2 + 0.0739 * r2 * r2
+    return (xr * k * fx + cx).astype(np.float32), (yr * k * fy + cy).astype(np.float32)
