@@ -101,6 +101,11 @@ void launch_blur(const ExtractorGeom* g, const ExtractorGeom* dg, int n_img, con
 void build_fast_cells(const ExtractorGeom& g, std::vector<int4>& cells);
 void launch_fast(const ExtractorGeom& g, const ExtractorGeom* dg, const int4* cells, int n_img, const uint8_t* pyr,
                  unsigned* cand, int* cand_count, int* flags, cudaStream_t st);
+struct FastMaps;
+int  build_fast_recs(const ExtractorGeom& g, std::vector<int4>& recs);
+bool fast_persist_supported(const ExtractorGeom& g);
+void launch_fast_persist(const ExtractorGeom& g, const FastMaps& maps, const int4* recs, int n_cells, int n_img,
+                         unsigned* cand, int* cand_count, int* flags, int* work_counter, cudaStream_t st);
 void launch_octree(const ExtractorGeom& g, const ExtractorGeom* dg, int n_img, const unsigned* cand,
                    unsigned* cand_scratch, const int* cand_count, LevelKey* keys, int* key_count,
                    int* flags, cudaStream_t st);

@@ -43,6 +43,10 @@ struct cuorb_extractor {
   int4*      d_blur_tiles = nullptr;
   TmaMaps    tmaps;                   // TMA tensor maps of the pyramid / blurred planes (per level), passed as __grid_constant__
   int4*      d_fast_cells = nullptr;  // per FAST cell: level, x0 | y0 << 16, dw | dh << 16
+  int4*      d_fast_recs = nullptr;   // k_fast_persist work records (2 per non-empty cell)
+  int        n_fast_recs = 0;
+  bool       fast_persist = false;
+  FastMaps   fmaps;
   int        n_blur_tiles = 0;
   uint8_t *  d_input = nullptr, *d_pyr = nullptr, *d_blur = nullptr;
   unsigned * d_cand = nullptr, *d_cand_scratch = nullptr;
@@ -226,7 +230,7 @@ static cudaError_t dev_alloc(T** p, size_t count) {
 
 static void free_all(cuorb_extractor* e) {
   cudaSetDevice(e->cfg.device);
-  void* dev[] = {e->d_geom, e->d_xtab, e->d_ytab, e->d_blur_tiles, e->d_fast_cells, e->d_input, e->d_pyr, e->d_blur,
+  void* dev[] = {e->d_geom, e->d_xtab, e->d_ytab, e->d_blur_tiles, e->d_fast_cells, e->d_fast_recs, e->d_input, e->d_pyr, e->d_blur,
                  e->d_cand, e->d_cand_scratch, e->d_cand_count, e->d_key_count, e->d_flags, e->d_slot,
                  e->d_keys, e->d_out_kps, e->d_out_desc, e->d_out_n, e->d_out_mono, e->d_uright,
                  e->d_depth, e->d_sad, e->d_best_idx, e->d_best_dist, e->d_rtab, e->d_rstart};
@@ -269,6 +273,22 @@ static int set_size(cuorb_extractor* e, int w, int h) {
   CUORB_CUDA_TRY(cudaMemcpy(e->d_blur_tiles, tiles.data(), tiles.size() * sizeof(int4), cudaMemcpyHostToDevice));
   e->n_blur_tiles = (int)tiles.size();
   CUORB_CUDA_TRY(cudaMemcpy(e->d_fast_cells, cells.data(), cells.size() * sizeof(int4), cudaMemcpyHostToDevice));
+  e->fast_persist = fast_persist_supported(g) && getenv("CUORB_FAST_LEGACY") == nullptr;
+  if (e->fast_persist) {
+    std::vector<int4> recs;
+    e->n_fast_recs = build_fast_recs(g, recs);
+    if (recs.size() > 2 * e->cap_cells) { set_error("internal: FAST work records exceed the arena"); return CUORB_E_CAPACITY; }
+    if (!recs.empty()) CUORB_CUDA_TRY(cudaMemcpy(e->d_fast_recs, recs.data(), recs.size() * sizeof(int4), cudaMemcpyHostToDevice));
+    memset(&e->fmaps, 0, sizeof(e->fmaps));
+    for (int l = 0; l < g.nlevels; l++) {
+      const LevelGeom& L = g.lv[l];
+      if (tma_encode_u8_3d(&e->fmaps.lv[l], e->d_pyr + L.plane_off, (uint64_t)L.pitch, (uint64_t)L.h + 2 * EDGE_THRESHOLD, nb,
+                           (uint64_t)L.pitch, g.pyr_img_stride, FT_PITCH, (uint32_t)(g.max_cell_h + 6)) != 0) {
+        set_error("cuTensorMapEncodeTiled failed (TMA tensor map for the FAST tiles)");
+        return CUORB_E_CUDA;
+      }
+    }
+  }
   {
     TmaMaps tm;
     memset(&tm, 0, sizeof(tm));
@@ -346,6 +366,7 @@ cuorb_extractor* cuorb_extractor_create(const cuorb_config* cfg) {
   ok &= dev_alloc(&e->d_ytab, e->cap_ytab) == cudaSuccess;
   ok &= dev_alloc(&e->d_blur_tiles, e->cap_tiles) == cudaSuccess;
   ok &= dev_alloc(&e->d_fast_cells, e->cap_cells) == cudaSuccess;
+  ok &= dev_alloc(&e->d_fast_recs, 2 * e->cap_cells) == cudaSuccess;
   ok &= dev_alloc(&e->d_input, e->cap_input) == cudaSuccess;
   ok &= dev_alloc(&e->d_pyr, e->cap_pyr) == cudaSuccess;
   ok &= dev_alloc(&e->d_blur, e->cap_blur) == cudaSuccess;
@@ -353,7 +374,7 @@ cuorb_extractor* cuorb_extractor_create(const cuorb_config* cfg) {
   ok &= dev_alloc(&e->d_cand_scratch, 2 * e->cap_cand) == cudaSuccess;
   ok &= dev_alloc(&e->d_cand_count, nb * MAX_LEVELS) == cudaSuccess;
   ok &= dev_alloc(&e->d_key_count, nb * MAX_LEVELS) == cudaSuccess;
-  ok &= dev_alloc(&e->d_flags, 1) == cudaSuccess;
+  ok &= dev_alloc(&e->d_flags, 2) == cudaSuccess;
   ok &= dev_alloc(&e->d_slot, e->cap_kp) == cudaSuccess;
   ok &= dev_alloc(&e->d_keys, e->cap_keys) == cudaSuccess;
   ok &= dev_alloc(&e->d_out_kps, e->cap_kp) == cudaSuccess;
@@ -438,11 +459,17 @@ static int enqueue_pipeline(cuorb_extractor* e, int n_images, const uint8_t* dim
   cudaStream_t st = e->stream;
   const bool prof = e->profiling;
   CUORB_CUDA_TRY(cudaMemsetAsync(e->d_cand_count, 0, sizeof(int) * (size_t)n_images * e->g.nlevels, st));
-  CUORB_CUDA_TRY(cudaMemsetAsync(e->d_flags, 0, sizeof(int), st));
+  CUORB_CUDA_TRY(cudaMemsetAsync(e->d_flags, 0, 2 * sizeof(int), st));  // [0] overflow flags, [1] FAST work counter
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_PYRAMID], st);
   launch_pyramid(e->g, e->d_geom, dimgs, width, height, dstride, dimg_stride, n_images, e->d_pyr, e->d_xtab, e->d_ytab, st);
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_FAST], st);
-  launch_fast(e->g, e->d_geom, e->d_fast_cells, n_images, e->d_pyr, e->d_cand, e->d_cand_count, e->d_flags, st);
+  if (e->fast_persist) {
+    if (e->n_fast_recs > 0)
+      launch_fast_persist(e->g, e->fmaps, e->d_fast_recs, e->n_fast_recs, n_images, e->d_cand, e->d_cand_count, e->d_flags,
+                          e->d_flags + 1, st);
+  } else {
+    launch_fast(e->g, e->d_geom, e->d_fast_cells, n_images, e->d_pyr, e->d_cand, e->d_cand_count, e->d_flags, st);
+  }
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_OCTREE], st);
   launch_octree(e->g, e->d_geom, n_images, e->d_cand, e->d_cand_scratch, e->d_cand_count, e->d_keys,
                 e->d_key_count, e->d_flags, st);

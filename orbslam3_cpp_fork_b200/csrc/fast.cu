@@ -2,30 +2,34 @@
 // ORBextractor::ComputeKeyPointsOctTree + cv::FAST(roi, thr, nonmax=true),
 // src/ORBextractor.cc:755-850; OpenCV features2d/fast.cpp FAST_t<16>, fast_score.cpp).
 //
-// One CTA per (cell, image).  The detection areas of the reference's overlapping cell ROIs tile
-// the level exactly, so a cell's CTA only needs its own pixels + a 3-px ring halo, and NMS looks
-// only at scores inside the cell (OpenCV zeroes everything outside the ROI's detection area).
-//
-//   phase 1: the cell's pixels (+halo) are staged in shared memory widened to u16, so one 32-bit
-//            word holds two horizontally adjacent pixels.
-//   phase 2: BRANCH-FREE corner score for every pixel, two pixels per thread in 16x2 SIMD:
-//            d[k] = v - ring[k] (+256 bias, so a plain 32-bit subtract never borrows across
-//            lanes), then the threshold-independent score
-//                max_k min(d[k..k+8])  and  min_k max(d[k..k+8])        (k circular, 16 arcs)
-//            as a min/max network of 3-input VIMNMX3.{U16x2} instructions (arcs k and k+1 share
-//            8 of their 9 elements, so 8 shared 8-minima + 8 two-element maxima give all 16 arcs:
-//            36 SIMD ops per polarity for two pixels).  "corner at t" <=> score >= t, so no
-//            per-pixel test, no divergence and no compaction is needed.  Scores below minThFAST
-//            are stored as 0.
-//   phase 3: strict 8-neighbour NMS inside the cell on the u8 score tile (words that are all
-//            zero are skipped); CTA-wide "any survivor >= iniThFAST" picks the threshold;
-//            survivors at that threshold are appended to the level's candidate list.
-// The list is unordered; the reference order (cell-row-major, then row-major) is a pure function
-// of (x, y) and is re-derived where it matters (quadtree tie-break, debug download).
-// Bound: the integer ALU pipe (min/max network), not HBM: ~45 ALU-pipe instructions per pixel.
+// The detection areas of the reference's overlapping cell ROIs tile the level exactly, so a cell
+// only needs its own pixels + a 3-px ring halo, and NMS looks only at scores inside the cell
+// (OpenCV zeroes everything outside the ROI's detection area).  Per cell, in shared memory:
+//   2a  necessary condition on the 4 compass ring pixels, four pixels per thread in u8x4 SIMD
+//       (VABSDIFF4); pixel pairs with a passing pixel are compacted into per-warp lists with
+//       warp ballots (no atomics);
+//   2b  BRANCH-FREE corner score on the listed pairs, two pixels per thread in 16x2 SIMD:
+//       d[k] = v - ring[k] (+256 bias, so a 32-bit subtract never borrows across lanes), then
+//           max_k min(d[k..k+8])  and  min_k max(d[k..k+8])        (k circular, 16 arcs)
+//       as a network of 3-input VIMNMX3.U16x2 (arcs k and k+1 share 8 of 9 elements: 36 SIMD ops
+//       per polarity for two pixels); "corner at t" <=> score >= t; corners go to a second list;
+//   3   strict 8-neighbour NMS over the listed corners on a u8 score tile;
+//   the whole thing first at iniThFAST and, only if the cell stays empty, again at minThFAST
+//   (:798-826), decided CTA-wide with __syncthreads_or.
+// Two kernels share these phases:
+//   k_fast_persist (cells <= 54 px wide, the normal case): persistent CTAs pull (image, cell) items
+//       from a global counter; the next item's u8 tile is fetched by TMA into the other half of a
+//       double buffer while the current one is processed; per-cell scalars come from a host-built
+//       record; bytes are widened to u16x2 with PRMT as the network reads them.
+//   k_fast_cells<TP,TPB> (wider cells): one CTA per cell, tile staged with aligned 32-bit loads as a
+//       u8 and a u16 copy.
+// The candidate list is unordered; the reference order (cell-row-major, then row-major) is a pure
+// function of (x, y) and is re-derived where it matters (quadtree tie-break, debug download).
+// Bound: the integer ALU pipe (VIMNMX/PRMT/LOP3 all issue there at 2 warp-inst/clk/SM), not HBM.
 #include <algorithm>
 
 #include "common.cuh"
+#include "tma.cuh"
 
 namespace cuorb {
 
@@ -283,6 +287,236 @@ __global__ void __launch_bounds__(128) k_fast_cells(const ExtractorGeom* __restr
   for (int n = tid; n < nout; n += 128) out[n] = s_out[n];
 }
 
+// ------------------------------------------------------------------------------------------------
+// Persistent variant (cells up to 54 px wide): CTAs loop over (image, cell) work items; the u8 pixel
+// tile of the NEXT item is fetched by TMA (cp.async.bulk.tensor.3d, mbarrier completion) into the
+// other half of a double buffer while the current item is processed, so no thread spends an
+// instruction on the tile load and its latency is hidden behind compute.  Per-cell scalars come
+// pre-digested from a host-built record; there is no u16 copy of the tile (the score network
+// widens byte pairs with PRMT as it reads them); the score tile is zeroed once and then only the
+// entries a cell wrote are cleared again.
+//   rec[2c]   = {level | cx0 << 8 | qf << 16 | nq << 24,  x0 | y0 << 16,  dw | dh << 16,  magic(nq)}
+//   rec[2c+1] = {plane x of tile column 0 (16-aligned) | plane row of tile row 0 << 16,  sp,  cand_off,  cand_cap}
+struct FastParams {
+  const int4* recs; int n_cells; int total_work;
+  unsigned* cand; int* cand_count; int* flags; int* work_counter;
+  unsigned long long cand_img_stride;
+  int nlevels, ini_th, min_th;
+  int box_rows, tile_bytes, score_bytes, pcap, ccap;
+};
+
+constexpr int FT_WORDS = FT_PITCH / 4;
+
+__device__ __forceinline__ unsigned widen_even(unsigned h) { return __byte_perm(h, 0, 0x4140); }
+// bytes 1 of lo and 0 of hi (two zero-extended u16 loads two bytes apart) -> u16x2
+__device__ __forceinline__ unsigned widen_odd(unsigned lo, unsigned hi) { return __byte_perm(lo, hi, 0x2421); }
+
+__global__ void __launch_bounds__(128) k_fast_persist(const __grid_constant__ FastMaps maps, const FastParams P) {
+  extern __shared__ unsigned char smem_raw[];
+  __shared__ uint64_t s_bar[2];
+  __shared__ int s_pcnt[4], s_ccnt[4], s_nlist, s_base, s_next[2];
+
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+  unsigned char*  s_tiles = smem;                                              // 2 x tile_bytes
+  unsigned char*  s_score = smem + 2 * P.tile_bytes;
+  unsigned short* s_plist = reinterpret_cast<unsigned short*>(s_score + P.score_bytes);
+  unsigned short* s_clist = s_plist + 4 * P.pcap;
+  unsigned*       s_list  = reinterpret_cast<unsigned*>(s_clist + 4 * P.ccap);
+
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const unsigned lt = (1u << lane) - 1u;
+  const int pcap = P.pcap, ccap = P.ccap;
+  int w = blockIdx.x;
+  if (w >= P.total_work) return;
+
+  if (tid == 0) {
+    mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1);
+    mbar_fence_init();
+    s_nlist = 0;
+  }
+  for (int i = tid; i < (P.score_bytes >> 2); i += 128) reinterpret_cast<unsigned*>(s_score)[i] = 0;
+  __syncthreads();
+
+  auto issue = [&](int work, int buf) {  // one thread
+    const int img = work / P.n_cells, cell = work - img * P.n_cells;
+    const int lvl = __ldg(&P.recs[2 * cell].x) & 0xFF;
+    const int org = __ldg(&P.recs[2 * cell + 1].x);
+    mbar_expect_tx(&s_bar[buf], (unsigned)(FT_PITCH * P.box_rows));
+    tma_load_3d(s_tiles + buf * P.tile_bytes, &maps.lv[lvl], &s_bar[buf], org & 0xFFFF, org >> 16, img);
+  };
+  if (tid == 0) issue(w, 0);
+
+  // items beyond the first come from a global counter (dynamic balance: cell cost varies 3x)
+  for (int it = 0;; it++) {
+    const int buf = it & 1;
+    if (tid == 0) {
+      const int nw = (int)gridDim.x + atomicAdd(P.work_counter, 1);
+      s_next[buf ^ 1] = nw;
+      if (nw < P.total_work) {
+        fence_proxy_async();  // the other buffer was read/written through the generic proxy one item ago
+        issue(nw, buf ^ 1);
+      }
+    }
+    const int img = w / P.n_cells, cell = w - img * P.n_cells;
+    const int4 c0 = __ldg(&P.recs[2 * cell]), c1 = __ldg(&P.recs[2 * cell + 1]);
+    const int level = c0.x & 0xFF, cx0 = (c0.x >> 8) & 0xFF, qf = (c0.x >> 16) & 0xFF, nq = (c0.x >> 24) & 0xFF;
+    const int x0 = c0.y & 0xFFFF, y0 = c0.y >> 16, dw = c0.z & 0xFFFF, dh = c0.z >> 16;
+    const unsigned inv = (unsigned)c0.w;
+    const int sp = c1.y;
+    const unsigned char* tile = s_tiles + buf * P.tile_bytes;
+    const unsigned* s_tile8 = reinterpret_cast<const unsigned*>(tile);
+    mbar_wait(&s_bar[buf], (unsigned)((it >> 1) & 1));
+
+    for (int pass = 0; pass < 2; pass++) {
+      const int cur_th = pass == 0 ? P.ini_th : P.min_th;
+      // ---- 2a: compass test, four pixels per thread, passing pairs -> per-warp list ----
+      {
+        const int nquads = nq * dh;
+        const unsigned K = (unsigned)(127 - min(cur_th, 127)) * 0x01010101u;
+        unsigned short* seg = s_plist + wid * pcap;
+        int cnt = 0;
+        for (int i0 = 0; i0 < nquads; i0 += 128) {
+          const int i = i0 + tid;
+          bool f0 = false, f1 = false;
+          int r = 0, q = 0;
+          if (i < nquads) {
+            r = fastdiv(i, inv, nq); q = i - r * nq + qf;
+            const unsigned* T = s_tile8 + (r + 3) * FT_WORDS + q;
+            const unsigned C = T[0];
+            const unsigned E = __funnelshift_r(C, T[1], 24), W = __funnelshift_r(T[-1], C, 8);
+            const unsigned aN = __vabsdiffu4(T[3 * FT_WORDS], C), aS = __vabsdiffu4(T[-3 * FT_WORDS], C);
+            const unsigned aE = __vabsdiffu4(E, C), aW = __vabsdiffu4(W, C);
+            const unsigned mN = aN | ((aN & 0x7f7f7f7fu) + K), mS = aS | ((aS & 0x7f7f7f7fu) + K);
+            const unsigned mE = aE | ((aE & 0x7f7f7f7fu) + K), mW = aW | ((aW & 0x7f7f7f7fu) + K);
+            const unsigned ok = (mN | mS) & (mE | mW) & 0x80808080u;
+            f0 = (ok & 0x0000FFFFu) != 0; f1 = (ok & 0xFFFF0000u) != 0;
+          }
+          const unsigned short e = (unsigned short)((r << 7) | (2 * q - 2));   // pair column = (tile column - 4) / 2
+          warp_append(f0, e, seg, cnt, lt);
+          warp_append(f1, (unsigned short)(e + 1), seg, cnt, lt);
+        }
+        if (lane == 0) s_pcnt[wid] = cnt;
+      }
+      __syncthreads();
+
+      // ---- 2b: score network on the listed pairs, bytes widened on the fly ----
+      {
+        const int pc4[4] = {s_pcnt[0], s_pcnt[1], s_pcnt[2], s_pcnt[3]};
+        const int np = pc4[0] + pc4[1] + pc4[2] + pc4[3];
+        unsigned short* seg = s_clist + wid * ccap;
+        int cnt = 0;
+        for (int i0 = 0; i0 < np; i0 += 128) {
+          const int i = i0 + tid;
+          bool k0 = false, k1 = false;
+          int r = 0, px = 0;
+          if (i < np) {
+            const int e = seg_fetch(s_plist, pcap, pc4, i);
+            r = e >> 7;
+            const int pc = e & 127;
+            px = 4 + 2 * pc - cx0;
+            const unsigned char* B = tile + (r + 3) * FT_PITCH + 4 + 2 * pc;
+#define H16(dy, dx) ((unsigned)*reinterpret_cast<const unsigned short*>(B + (dy) * FT_PITCH + (dx)))
+            unsigned ring[16];
+            {
+              const unsigned a = H16(3, -2), b = H16(3, 0), c = H16(3, 2);
+              ring[15] = widen_odd(a, b); ring[0] = widen_even(b); ring[1] = widen_odd(b, c);
+            }
+            ring[2] = widen_even(H16(2, 2)); ring[14] = widen_even(H16(2, -2));
+            ring[3] = widen_odd(H16(1, 2), H16(1, 4)); ring[13] = widen_odd(H16(1, -4), H16(1, -2));
+            unsigned ctr;
+            {
+              const unsigned m4 = H16(0, -4), m2 = H16(0, -2), c = H16(0, 0), p2 = H16(0, 2), p4 = H16(0, 4);
+              ring[4] = widen_odd(p2, p4); ring[12] = widen_odd(m4, m2); ctr = widen_even(c);
+            }
+            ring[5] = widen_odd(H16(-1, 2), H16(-1, 4)); ring[11] = widen_odd(H16(-1, -4), H16(-1, -2));
+            ring[6] = widen_even(H16(-2, 2)); ring[10] = widen_even(H16(-2, -2));
+            {
+              const unsigned a = H16(-3, -2), b = H16(-3, 0), c = H16(-3, 2);
+              ring[9] = widen_odd(a, b); ring[8] = widen_even(b); ring[7] = widen_odd(b, c);
+            }
+#undef H16
+            unsigned A, Bx;
+            arc_extremes(ctr, ring, A, Bx);
+            const int s0 = max((int)(A & 0xFFFFu) - 257, 255 - (int)(Bx & 0xFFFFu));
+            const int s1 = max((int)(A >> 16) - 257, 255 - (int)(Bx >> 16));
+            unsigned char* q = s_score + (r + 1) * sp + px + 4;
+            k0 = px >= 0 && px < dw && s0 >= cur_th;
+            k1 = px + 1 >= 0 && px + 1 < dw && s1 >= cur_th;
+            if (k0) q[0] = (unsigned char)s0;
+            if (k1) q[1] = (unsigned char)s1;
+          }
+          warp_append(k0, (unsigned short)((r << 7) | px), seg, cnt, lt);
+          warp_append(k1, (unsigned short)((r << 7) | (px + 1)), seg, cnt, lt);
+        }
+        if (lane == 0) s_ccnt[wid] = cnt;
+      }
+      __syncthreads();
+
+      // ---- 3: NMS over the listed corners ----
+      const int cc4[4] = {s_ccnt[0], s_ccnt[1], s_ccnt[2], s_ccnt[3]};
+      const int nc = cc4[0] + cc4[1] + cc4[2] + cc4[3];
+      for (int i = tid; i < nc; i += 128) {
+        const int e = seg_fetch(s_clist, ccap, cc4, i);
+        const int r = e >> 7, px = e & 127;
+        const unsigned char* q = s_score + (r + 1) * sp + px + 4;
+        const int s = q[0];
+        const bool lm = s > q[-1] && s > q[1] && s > q[-sp - 1] && s > q[-sp] && s > q[-sp + 1] &&
+                        s > q[sp - 1] && s > q[sp] && s > q[sp + 1];
+        if (lm) s_list[atomicAdd(&s_nlist, 1)] = pack_cand(x0 + px - FAST_BORDER, y0 + r - FAST_BORDER, s);
+      }
+      const bool done = __syncthreads_or(s_nlist > 0) || pass == 1 || P.min_th == P.ini_th;
+      // clear exactly the scores this pass wrote (all NMS reads are behind the barrier above)
+      for (int i = tid; i < nc; i += 128) {
+        const int e = seg_fetch(s_clist, ccap, cc4, i);
+        s_score[((e >> 7) + 1) * sp + (e & 127) + 4] = 0;
+      }
+      if (done) break;
+      __syncthreads();
+    }
+
+    // ---- emit: every listed survivor is a keypoint of this cell at the threshold that produced it ----
+    const int nl = s_nlist;
+    if (nl > 0) {
+      if (tid == 0) s_base = atomicAdd(&P.cand_count[img * P.nlevels + level], nl);
+      __syncthreads();
+      const int base = s_base;
+      if (base + nl > c1.w) {
+        if (tid == 0) atomicOr(P.flags, FLAG_CAND_OVERFLOW);
+      } else {
+        unsigned* out = P.cand + (size_t)img * P.cand_img_stride + (unsigned)c1.z + base;
+        for (int n = tid; n < nl; n += 128) out[n] = s_list[n];
+      }
+    }
+    __syncthreads();  // lists, counters and this tile buffer are free again
+    if (tid == 0) s_nlist = 0;
+    w = s_next[buf ^ 1];
+    if (w >= P.total_work) break;
+  }
+}
+
+// work records for k_fast_persist (cells the reference skips are left out); returns the cell count
+int build_fast_recs(const ExtractorGeom& g, std::vector<int4>& recs) {
+  recs.clear();
+  for (int l = 0; l < g.nlevels; l++) {
+    const LevelGeom& L = g.lv[l];
+    for (int ci = 0; ci < L.nRows; ci++)
+      for (int cj = 0; cj < L.nCols; cj++) {
+        const int x0 = EDGE_THRESHOLD + cj * L.wCell, y0 = EDGE_THRESHOLD + ci * L.hCell;
+        const int dw = std::min(x0 + L.wCell, L.maxBorderX - 3) - x0;
+        const int dh = std::min(y0 + L.hCell, L.maxBorderY - 3) - y0;
+        if (dw <= 0 || dh <= 0) continue;
+        const int pxo = (ROW_LEAD + x0 - 4) & ~15;            // plane column of tile column 0
+        const int cx0 = ROW_LEAD + x0 - pxo;                  // 4..19
+        const int qf = cx0 >> 2, ql = (cx0 + dw - 1) >> 2, nq = ql - qf + 1;
+        const int sp = (((dw + 5 + 3) >> 2) | 1) << 2;
+        const unsigned inv = 0xFFFFFFFFu / (unsigned)nq + 1u;
+        recs.push_back(make_int4(l | (cx0 << 8) | (qf << 16) | (nq << 24), x0 | (y0 << 16), dw | (dh << 16), (int)inv));
+        recs.push_back(make_int4(pxo | ((EDGE_THRESHOLD + y0 - 3) << 16), sp, (int)L.cand_off, L.cand_cap));
+      }
+  }
+  return (int)recs.size() / 2;
+}
+
 // per-cell geometry (src/ORBextractor.cc:777-796), cell-row-major per level
 void build_fast_cells(const ExtractorGeom& g, std::vector<int4>& cells) {
   cells.clear();
@@ -326,6 +560,42 @@ void launch_fast(const ExtractorGeom& g, const ExtractorGeom* dg, const int4* ce
   // the packed lists need cell height below 512 and pair columns below 128
   if (g.max_cell_w + 17 <= 4 * 15) launch_fast_tp<38, 15>(g, dg, cells, n_img, pyr, cand, cand_count, flags, st);
   else launch_fast_tp<76, 37>(g, dg, cells, n_img, pyr, cand, cand_count, flags, st);
+  count_launch();
+}
+
+// persistent TMA variant; returns false when the cell geometry does not fit its tile (caller then
+// uses launch_fast)
+bool fast_persist_supported(const ExtractorGeom& g) { return g.max_cell_w <= 54 && g.max_cell_h + 6 <= 256 && g.max_cell_h < 512; }
+
+void launch_fast_persist(const ExtractorGeom& g, const FastMaps& maps, const int4* recs, int n_cells, int n_img,
+                         unsigned* cand, int* cand_count, int* flags, int* work_counter, cudaStream_t st) {
+  FastParams P;
+  P.recs = recs; P.n_cells = n_cells; P.total_work = n_cells * n_img;
+  P.cand = cand; P.cand_count = cand_count; P.flags = flags; P.work_counter = work_counter;
+  P.cand_img_stride = g.cand_img_stride; P.nlevels = g.nlevels; P.ini_th = g.ini_th; P.min_th = g.min_th;
+  P.box_rows    = g.max_cell_h + 6;
+  P.tile_bytes  = ((FT_PITCH * P.box_rows + 127) / 128) * 128;
+  const int sp_max = ((((g.max_cell_w + 5 + 3) >> 2) | 1) << 2);
+  P.score_bytes = ((sp_max * (g.max_cell_h + 2) + 15) / 16) * 16;
+  const int maxquads = ((g.max_cell_w + 3) / 4 + 1) * g.max_cell_h;
+  P.pcap = 64 * ((maxquads + 127) / 128);
+  P.ccap = 64 * ((2 * maxquads + 127) / 128);
+  const int list_bytes = 4 * ((g.max_cell_w + 1) / 2) * ((g.max_cell_h + 1) / 2);
+  const int smem = 128 + 2 * P.tile_bytes + P.score_bytes + 2 * 4 * (P.pcap + P.ccap) + list_bytes;
+  static int attr = 48 * 1024, per_sm = 0, attr_smem = -1, n_sm = 0;
+  if (smem > attr) {
+    cudaFuncSetAttribute(k_fast_persist, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    attr = smem;
+  }
+  if (attr_smem != smem) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fast_persist, 128, smem);
+    attr_smem = smem;
+  }
+  const int grid = std::max(1, std::min(P.total_work, n_sm * std::max(per_sm, 1)));
+  k_fast_persist<<<grid, 128, smem, st>>>(maps, P);
   count_launch();
 }
 

@@ -20,7 +20,14 @@ struct TmaMaps {
   CUtensorMap blur_br[CUORB_MAX_LEVELS];
 };
 
+// k_fast_persist: one map per level over the padded pyramid plane, box FT_PITCH bytes x (max cell height + 6) rows
+constexpr int FT_PITCH = 80;   // 20 words: rows r and r+8 share banks, so a warp's ~3 rows never collide
+struct FastMaps {
+  CUtensorMap lv[CUORB_MAX_LEVELS];
+};
+
 #ifdef __CUDACC__
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
