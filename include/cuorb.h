@@ -251,6 +251,22 @@ int cuorb_extract_batch_async_pre(cuorb_extractor* ext, cuorb_preproc* pre, int 
                                   const uint8_t* src, size_t stride, size_t image_stride,
                                   cuorb_mem where, cuorb_pixfmt fmt, int lap0, int lap1);
 
+/* ---- per-frame glue after extraction ---- */
+
+/* void Frame::UndistortKeyPoints() (src/Frame.cc:886-913): cv::undistortPoints(mvKeys, K, D, cv::Mat(), K)
+ * with OpenCV's double arithmetic (5 iterations), or a plain copy when dist5[0] == 0 as the reference
+ * does.  K4 = fx, fy, cx, cy (the float entries of mK); dist5 = k1, k2, p1, p2, k3 (k3 = 0 if absent).
+ * Host arrays; kps_un may alias kps.  Returns n. */
+int cuorb_undistort_keypoints(int device, int n, const cuorb_keypoint* kps, const float* K4,
+                              const float* dist5, cuorb_keypoint* kps_un);
+
+/* void Frame::ComputeStereoFromRGBD(const cv::Mat& imDepth) (src/Frame.cc:1115-1133): depth = CV_32F
+ * image (row pitch stride_bytes) in host or device memory; d = imDepth(v, u) at the truncated
+ * keypoint position; if d > 0: depth_out = d, u_right = kps_un.x - mbf / d, else both -1. */
+int cuorb_stereo_from_rgbd(int device, int n, const cuorb_keypoint* kps, const cuorb_keypoint* kps_un,
+                           const float* depth, int width, int height, size_t stride_bytes,
+                           cuorb_mem depth_where, float mbf, float* u_right, float* depth_out);
+
 /* ---- instrumentation ---- */
 
 /* number of libcuorb kernel launches issued by this process so far (bench.py's gpu_launches) */

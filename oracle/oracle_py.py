@@ -36,7 +36,7 @@ class FrameViewC(C.Structure):
 
 def build(force: bool = False) -> str:
     srcs = [os.path.join(_HERE, f) for f in
-            ("orb_oracle.cpp", "orb_oracle_match.cpp", "orb_oracle_capi.cpp", "preproc_oracle.cpp", "orb_oracle.hpp")]
+            ("orb_oracle.cpp", "orb_oracle_match.cpp", "orb_oracle_capi.cpp", "preproc_oracle.cpp", "frameglue_oracle.cpp", "orb_oracle.hpp")]
     stale = (not os.path.exists(_LIB_PATH)) or any(
         os.path.getmtime(s) > os.path.getmtime(_LIB_PATH) for s in srcs)
     if force or stale:
@@ -91,6 +91,9 @@ def lib() -> C.CDLL:
                                    C.c_int, C.c_size_t]
         L.oo_preprocess.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, C.c_void_p,
                                     C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+        L.oo_undistort_keypoints.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        L.oo_stereo_from_rgbd.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_float,
+                                          C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -288,6 +291,26 @@ def preprocess(img, fmt, mode=PRE_NONE, mapx=None, mapy=None, dsize=None):
     out = np.empty((dh, dw), np.uint8)
     lib().oo_preprocess(_p(img), sw, sh, sw * ch, int(fmt), int(mode), _p(mapx), _p(mapy), _p(out), dw, dh)
     return out
+
+
+# ---- post-extraction frame glue (frameglue_oracle.cpp) ----
+def undistort_keypoints(kps, K4, dist):
+    """Frame::UndistortKeyPoints: K4 = (fx, fy, cx, cy), dist = (k1, k2, p1, p2[, k3])."""
+    kps = np.ascontiguousarray(kps, dtype=KP_DTYPE)
+    out = np.empty_like(kps)
+    K4 = np.ascontiguousarray(K4, dtype=np.float32)
+    d5 = np.zeros(5, np.float32); d5[:len(dist)] = np.asarray(dist, np.float32)
+    lib().oo_undistort_keypoints(_p(kps), _p(out), len(kps), _p(K4), _p(d5))
+    return out
+
+
+def stereo_from_rgbd(kps, kps_un, depth, mbf):
+    """Frame::ComputeStereoFromRGBD: depth float32 [h, w] -> (mvuRight, mvDepth)."""
+    kps = np.ascontiguousarray(kps, dtype=KP_DTYPE); kps_un = np.ascontiguousarray(kps_un, dtype=KP_DTYPE)
+    depth = np.ascontiguousarray(depth, dtype=np.float32)
+    u = np.empty(len(kps), np.float32); d = np.empty(len(kps), np.float32)
+    lib().oo_stereo_from_rgbd(_p(kps), _p(kps_un), len(kps), _p(depth), depth.shape[1], np.float32(mbf), _p(u), _p(d))
+    return u, d
 
 
 def hamming(a, b):

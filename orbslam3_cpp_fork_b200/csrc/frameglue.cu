@@ -1,0 +1,158 @@
+// Per-frame glue right after ORBextractor::operator():
+//   Frame::UndistortKeyPoints    src/Frame.cc:886-913  (cv::undistortPoints(mat, mat, K, D, cv::Mat(), K))
+//   Frame::ComputeStereoFromRGBD src/Frame.cc:1115-1133
+// cv::undistortPoints' arithmetic (calib3d cvUndistortPointsInternal: doubles, 5 fixed iterations,
+// projection by P = K, result rounded to float) is evaluated with explicit round-to-nearest
+// double intrinsics in the reference's operation order, so no FMA contraction can change a bit.
+// One thread per keypoint; these are tiny kernels (a frame has ~1000 keypoints) whose point is to
+// keep the Frame's arrays on the device between extraction and the matchers.
+#include "common.cuh"
+
+namespace cuorb {
+void set_error(const std::string& msg);
+
+namespace {
+
+struct UndistortArgs {
+  double fx, fy, cx, cy, ifx, ify;
+  double k[12];
+};
+
+__global__ void k_undistort(const cuorb_keypoint* __restrict__ in, cuorb_keypoint* __restrict__ out, int n, const UndistortArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  cuorb_keypoint kp = in[i];
+  double x = (double)kp.x, y = (double)kp.y;
+  const double u = x, v = y;
+  x = __dmul_rn(__dsub_rn(x, a.cx), a.ifx); y = __dmul_rn(__dsub_rn(y, a.cy), a.ify);
+  const double x0 = x, y0 = y;
+  const double* k = a.k;
+  for (int j = 0; j < 5; j++) {
+    const double r2 = __dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y));
+    const double num = __dadd_rn(1.0, __dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn(__dmul_rn(k[7], r2), k[6]), r2), k[5]), r2));
+    const double den = __dadd_rn(1.0, __dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn(__dmul_rn(k[4], r2), k[1]), r2), k[0]), r2));
+    const double icdist = __ddiv_rn(num, den);
+    if (icdist < 0) { x = __dmul_rn(__dsub_rn(u, a.cx), a.ifx); y = __dmul_rn(__dsub_rn(v, a.cy), a.ify); break; }
+    // deltaX = 2*k2*x*y + k3*(r2 + 2*x*x) + k8*r2 + k9*r2*r2   (left to right)
+    double dX = __dmul_rn(__dmul_rn(__dmul_rn(2.0, k[2]), x), y);
+    dX = __dadd_rn(dX, __dmul_rn(k[3], __dadd_rn(r2, __dmul_rn(__dmul_rn(2.0, x), x))));
+    dX = __dadd_rn(dX, __dmul_rn(k[8], r2));
+    dX = __dadd_rn(dX, __dmul_rn(__dmul_rn(k[9], r2), r2));
+    // deltaY = k2*(r2 + 2*y*y) + 2*k3*x*y + k10*r2 + k11*r2*r2
+    double dY = __dmul_rn(k[2], __dadd_rn(r2, __dmul_rn(__dmul_rn(2.0, y), y)));
+    dY = __dadd_rn(dY, __dmul_rn(__dmul_rn(__dmul_rn(2.0, k[3]), x), y));
+    dY = __dadd_rn(dY, __dmul_rn(k[10], r2));
+    dY = __dadd_rn(dY, __dmul_rn(__dmul_rn(k[11], r2), r2));
+    x = __dmul_rn(__dsub_rn(x0, dX), icdist);
+    y = __dmul_rn(__dsub_rn(y0, dY), icdist);
+  }
+  const double xx = __dadd_rn(__dadd_rn(__dmul_rn(a.fx, x), __dmul_rn(0.0, y)), a.cx);
+  const double yy = __dadd_rn(__dadd_rn(__dmul_rn(0.0, x), __dmul_rn(a.fy, y)), a.cy);
+  kp.x = (float)xx;   // ww = 1 / (0*x + 0*y + 1) = 1
+  kp.y = (float)yy;
+  out[i] = kp;
+}
+
+__global__ void k_stereo_from_rgbd(const cuorb_keypoint* __restrict__ kps, const cuorb_keypoint* __restrict__ kps_un, int n,
+                                   const float* __restrict__ depth, size_t stride_floats, int w, int h, float mbf,
+                                   float* __restrict__ u_right, float* __restrict__ depth_out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int u = (int)kps[i].x, v = (int)kps[i].y;  // imDepth.at<float>(v, u): float -> int truncation
+  float ur = -1.0f, dz = -1.0f;
+  if (u >= 0 && u < w && v >= 0 && v < h) {
+    const float d = depth[(size_t)v * stride_floats + u];
+    if (d > 0) { dz = d; ur = __fsub_rn(kps_un[i].x, __fdiv_rn(mbf, d)); }
+  }
+  u_right[i] = ur; depth_out[i] = dz;
+}
+
+struct Scratch {  // grow-only device scratch per host thread
+  void* p = nullptr; size_t cap = 0; int device = -1;
+  void* get(int dev, size_t bytes) {
+    if (dev != device || bytes > cap) {
+      if (p) { cudaSetDevice(device); cudaFree(p); p = nullptr; cap = 0; }
+      cudaSetDevice(dev);
+      if (cudaMalloc(&p, bytes) != cudaSuccess) { p = nullptr; return nullptr; }
+      cap = bytes; device = dev;
+    }
+    return p;
+  }
+};
+thread_local Scratch t_scratch;
+
+}  // namespace
+}  // namespace cuorb
+
+using namespace cuorb;
+
+#define GLUE_TRY(call)                                                             \
+  do {                                                                             \
+    cudaError_t err__ = (call);                                                    \
+    if (err__ != cudaSuccess) { set_error(std::string(#call) + ": " + cudaGetErrorString(err__)); return CUORB_E_CUDA; } \
+  } while (0)
+
+extern "C" {
+
+int cuorb_undistort_keypoints(int device, int n, const cuorb_keypoint* kps, const float* K4, const float* dist5,
+                              cuorb_keypoint* kps_un) {
+  if (n < 0 || (n > 0 && (!kps || !kps_un)) || !K4 || !dist5) { set_error("cuorb_undistort_keypoints: bad argument"); return CUORB_E_BADARG; }
+  if (n == 0) return 0;
+  if (dist5[0] == 0.0f) {  // src/Frame.cc:887-890: mvKeysUn = mvKeys
+    if (kps_un != kps) memcpy(kps_un, kps, sizeof(cuorb_keypoint) * (size_t)n);
+    return n;
+  }
+  GLUE_TRY(cudaSetDevice(device));
+  const size_t bytes = sizeof(cuorb_keypoint) * (size_t)n;
+  char* d = (char*)t_scratch.get(device, 2 * bytes + 512);
+  if (!d) { set_error("cudaMalloc failed (undistort workspace)"); return CUORB_E_CUDA; }
+  cuorb_keypoint* din = (cuorb_keypoint*)d;
+  cuorb_keypoint* dout = (cuorb_keypoint*)(d + ((bytes + 255) & ~(size_t)255));
+  UndistortArgs a;
+  a.fx = K4[0]; a.fy = K4[1]; a.cx = K4[2]; a.cy = K4[3]; a.ifx = 1. / a.fx; a.ify = 1. / a.fy;
+  for (int i = 0; i < 12; i++) a.k[i] = i < 5 ? (double)dist5[i] : 0.0;
+  cudaStream_t st = cudaStreamPerThread;
+  GLUE_TRY(cudaMemcpyAsync(din, kps, bytes, cudaMemcpyHostToDevice, st));
+  k_undistort<<<(n + 127) / 128, 128, 0, st>>>(din, dout, n, a);
+  count_launch();
+  GLUE_TRY(cudaMemcpyAsync(kps_un, dout, bytes, cudaMemcpyDeviceToHost, st));
+  GLUE_TRY(cudaStreamSynchronize(st));
+  return n;
+}
+
+int cuorb_stereo_from_rgbd(int device, int n, const cuorb_keypoint* kps, const cuorb_keypoint* kps_un, const float* depth,
+                           int width, int height, size_t stride_bytes, cuorb_mem depth_where, float mbf, float* u_right,
+                           float* depth_out) {
+  if (n < 0 || (n > 0 && (!kps || !kps_un || !u_right || !depth_out)) || !depth || width <= 0 || height <= 0 ||
+      stride_bytes < (size_t)width * 4 || (stride_bytes & 3)) {
+    set_error("cuorb_stereo_from_rgbd: bad argument"); return CUORB_E_BADARG;
+  }
+  if (n == 0) return 0;
+  GLUE_TRY(cudaSetDevice(device));
+  const size_t kb = (sizeof(cuorb_keypoint) * (size_t)n + 255) & ~(size_t)255, fb = (4 * (size_t)n + 255) & ~(size_t)255;
+  const size_t img = depth_where == CUORB_MEM_HOST ? (size_t)width * 4 * height : 0;
+  char* d = (char*)t_scratch.get(device, 2 * kb + 2 * fb + img + 512);
+  if (!d) { set_error("cudaMalloc failed (rgbd workspace)"); return CUORB_E_CUDA; }
+  cuorb_keypoint* dk = (cuorb_keypoint*)d;
+  cuorb_keypoint* dku = (cuorb_keypoint*)(d + kb);
+  float* du = (float*)(d + 2 * kb);
+  float* dz = (float*)(d + 2 * kb + fb);
+  cudaStream_t st = cudaStreamPerThread;
+  const float* ddepth = depth;
+  size_t dstride = stride_bytes / 4;
+  if (depth_where == CUORB_MEM_HOST) {
+    float* dd = (float*)(d + 2 * kb + 2 * fb);
+    GLUE_TRY(cudaMemcpy2DAsync(dd, (size_t)width * 4, depth, stride_bytes, (size_t)width * 4, height, cudaMemcpyHostToDevice, st));
+    ddepth = dd; dstride = width;
+  }
+  GLUE_TRY(cudaMemcpyAsync(dk, kps, sizeof(cuorb_keypoint) * (size_t)n, cudaMemcpyHostToDevice, st));
+  GLUE_TRY(cudaMemcpyAsync(dku, kps_un, sizeof(cuorb_keypoint) * (size_t)n, cudaMemcpyHostToDevice, st));
+  k_stereo_from_rgbd<<<(n + 127) / 128, 128, 0, st>>>(dk, dku, n, ddepth, dstride, width, height, mbf, du, dz);
+  count_launch();
+  GLUE_TRY(cudaMemcpyAsync(u_right, du, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+  GLUE_TRY(cudaMemcpyAsync(depth_out, dz, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+  GLUE_TRY(cudaStreamSynchronize(st));
+  return n;
+}
+
+}  // extern "C"

@@ -1,0 +1,49 @@
+"""Host-side mirror of the per-frame glue the reference runs right after ORBextractor::operator()
+(SURVEY.md §8f row N2): Frame::UndistortKeyPoints (src/Frame.cc:886-913) and
+Frame::ComputeStereoFromRGBD (src/Frame.cc:1115-1133).  Compute is libcuorb's (no CPU fallback).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import _lib
+from ._lib import KP_DTYPE, check, ptr
+from .extractor import _as_device_ptr
+
+
+def UndistortKeyPoints(mvKeys, K, mDistCoef, device=0):
+    """mvKeys: KP_DTYPE array; K: 3x3 camera matrix or (fx, fy, cx, cy); mDistCoef: k1, k2, p1, p2[, k3].
+    Returns mvKeysUn (a copy of mvKeys when mDistCoef[0] == 0, as the reference does)."""
+    L = _lib.load()
+    kps = np.ascontiguousarray(mvKeys, dtype=KP_DTYPE)
+    K = np.asarray(K, dtype=np.float32)
+    K4 = np.array([K[0, 0], K[1, 1], K[0, 2], K[1, 2]], np.float32) if K.ndim == 2 else np.ascontiguousarray(K, np.float32)
+    d5 = np.zeros(5, np.float32)
+    d = np.asarray(mDistCoef, np.float32).ravel()
+    d5[:min(5, len(d))] = d[:5]
+    out = np.empty_like(kps)
+    check(L.cuorb_undistort_keypoints(int(device), len(kps), ptr(kps), ptr(K4), ptr(d5), ptr(out)))
+    return out
+
+
+def ComputeStereoFromRGBD(mvKeys, mvKeysUn, imDepth, mbf, device=0):
+    """imDepth: float32 [h, w] numpy (host) or torch CUDA tensor.  Returns (mvuRight, mvDepth)."""
+    L = _lib.load()
+    kps = np.ascontiguousarray(mvKeys, dtype=KP_DTYPE)
+    kun = np.ascontiguousarray(mvKeysUn, dtype=KP_DTYPE)
+    dev = _as_device_ptr(imDepth)
+    if dev is not None:
+        p, shape, strides = dev
+        where = _lib.MEM_DEVICE
+    else:
+        imDepth = np.asarray(imDepth)
+        if imDepth.dtype != np.float32:
+            raise ValueError("imDepth must be float32 (CV_32F)")
+        p, shape, strides, where = imDepth.ctypes.data, imDepth.shape, imDepth.strides, _lib.MEM_HOST
+    if len(shape) != 2 or strides[1] != 4:
+        raise ValueError("imDepth must be [h, w] float32 with unit pixel stride")
+    u = np.empty(len(kps), np.float32)
+    z = np.empty(len(kps), np.float32)
+    check(L.cuorb_stereo_from_rgbd(int(device), len(kps), ptr(kps), ptr(kun), ptr(p), shape[1], shape[0], strides[0],
+                                   where, float(mbf), ptr(u), ptr(z)))
+    return u, z
