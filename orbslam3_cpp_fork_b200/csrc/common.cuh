@@ -92,9 +92,10 @@ inline void count_launch(int n = 1) { g_launch_count.fetch_add((unsigned long lo
 enum { FLAG_CAND_OVERFLOW = 1, FLAG_NODE_OVERFLOW = 2, FLAG_KEY_OVERFLOW = 4 };
 
 // ---- kernel launchers (one per stage; all asynchronous on `st`) ----
+void build_resize_words(const ExtractorGeom& g, const std::vector<ResizeTap>& xtab, std::vector<uint4>& wt, int* off);
 void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8_t* imgs, int w, int h,
-                    size_t stride, size_t image_stride, int n_img, uint8_t* pyr,
-                    const ResizeTap* xtab, const ResizeTap* ytab, cudaStream_t st);
+                    size_t stride, size_t image_stride, int n_img, uint8_t* pyr, const ResizeTap* xtab,
+                    const ResizeTap* ytab, const uint4* wtab, const int* wtab_off, cudaStream_t st);
 void build_blur_tiles(const ExtractorGeom& g, std::vector<int4>& tiles);
 void launch_blur(const ExtractorGeom* g, const ExtractorGeom* dg, int n_img, const int4* tiles,
                  int n_tiles, const uint8_t* pyr, uint8_t* blur, cudaStream_t st);

@@ -40,6 +40,9 @@ struct cuorb_extractor {
   // device buffers (sized for max_width x max_height x max_batch)
   ExtractorGeom* d_geom = nullptr;
   ResizeTap *d_xtab = nullptr, *d_ytab = nullptr;
+  uint4*     d_wtab = nullptr;        // per-word horizontal tap tables of k_pyr_resize_tab
+  int        wtab_off[MAX_LEVELS];
+  size_t     cap_wtab = 0;
   int4*      d_blur_tiles = nullptr;
   TmaMaps    tmaps;                   // TMA tensor maps of the pyramid / blurred planes (per level), passed as __grid_constant__
   int4*      d_fast_cells = nullptr;  // per FAST cell: level, x0 | y0 << 16, dw | dh << 16
@@ -230,7 +233,7 @@ static cudaError_t dev_alloc(T** p, size_t count) {
 
 static void free_all(cuorb_extractor* e) {
   cudaSetDevice(e->cfg.device);
-  void* dev[] = {e->d_geom, e->d_xtab, e->d_ytab, e->d_blur_tiles, e->d_fast_cells, e->d_fast_recs, e->d_input, e->d_pyr, e->d_blur,
+  void* dev[] = {e->d_geom, e->d_xtab, e->d_ytab, e->d_wtab, e->d_blur_tiles, e->d_fast_cells, e->d_fast_recs, e->d_input, e->d_pyr, e->d_blur,
                  e->d_cand, e->d_cand_scratch, e->d_cand_count, e->d_key_count, e->d_flags, e->d_slot,
                  e->d_keys, e->d_out_kps, e->d_out_desc, e->d_out_n, e->d_out_mono, e->d_uright,
                  e->d_depth, e->d_sad, e->d_best_idx, e->d_best_dist, e->d_rtab, e->d_rstart};
@@ -270,6 +273,12 @@ static int set_size(cuorb_extractor* e, int w, int h) {
   CUORB_CUDA_TRY(cudaMemcpy(e->d_geom, &g, sizeof(g), cudaMemcpyHostToDevice));
   if (!xt.empty()) CUORB_CUDA_TRY(cudaMemcpy(e->d_xtab, xt.data(), xt.size() * sizeof(ResizeTap), cudaMemcpyHostToDevice));
   if (!yt.empty()) CUORB_CUDA_TRY(cudaMemcpy(e->d_ytab, yt.data(), yt.size() * sizeof(ResizeTap), cudaMemcpyHostToDevice));
+  {
+    std::vector<uint4> wt;
+    build_resize_words(g, xt, wt, e->wtab_off);
+    if (wt.size() > e->cap_wtab) { set_error("internal: resize word tables exceed the arena"); return CUORB_E_CAPACITY; }
+    if (!wt.empty()) CUORB_CUDA_TRY(cudaMemcpy(e->d_wtab, wt.data(), wt.size() * sizeof(uint4), cudaMemcpyHostToDevice));
+  }
   CUORB_CUDA_TRY(cudaMemcpy(e->d_blur_tiles, tiles.data(), tiles.size() * sizeof(int4), cudaMemcpyHostToDevice));
   e->n_blur_tiles = (int)tiles.size();
   CUORB_CUDA_TRY(cudaMemcpy(e->d_fast_cells, cells.data(), cells.size() * sizeof(int4), cudaMemcpyHostToDevice));
@@ -357,12 +366,15 @@ cuorb_extractor* cuorb_extractor_create(const cuorb_config* cfg) {
   e->cap_kp    = (size_t)g.kp_cap * nb;
   e->cap_xtab  = xt.size() + 64; e->cap_ytab = yt.size() + 64; e->cap_tiles = tiles.size() + 64;
   e->cap_cells = (size_t)g.total_cells + 64;
+  e->cap_wtab  = 64;
+  for (int l = 1; l < g.nlevels; l++) e->cap_wtab += 2 * (size_t)(g.lv[l].pitch / 4 + 1);
   bool ok = true;
   ok &= cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess;
   ok &= cudaEventCreateWithFlags(&e->ev_done, cudaEventDisableTiming) == cudaSuccess;
   for (auto& ev : e->ev_stage) ok &= cudaEventCreate(&ev) == cudaSuccess;
   ok &= dev_alloc(&e->d_geom, 1) == cudaSuccess;
   ok &= dev_alloc(&e->d_xtab, e->cap_xtab) == cudaSuccess;
+  ok &= dev_alloc(&e->d_wtab, e->cap_wtab) == cudaSuccess;
   ok &= dev_alloc(&e->d_ytab, e->cap_ytab) == cudaSuccess;
   ok &= dev_alloc(&e->d_blur_tiles, e->cap_tiles) == cudaSuccess;
   ok &= dev_alloc(&e->d_fast_cells, e->cap_cells) == cudaSuccess;
@@ -461,7 +473,8 @@ static int enqueue_pipeline(cuorb_extractor* e, int n_images, const uint8_t* dim
   CUORB_CUDA_TRY(cudaMemsetAsync(e->d_cand_count, 0, sizeof(int) * (size_t)n_images * e->g.nlevels, st));
   CUORB_CUDA_TRY(cudaMemsetAsync(e->d_flags, 0, 2 * sizeof(int), st));  // [0] overflow flags, [1] FAST work counter
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_PYRAMID], st);
-  launch_pyramid(e->g, e->d_geom, dimgs, width, height, dstride, dimg_stride, n_images, e->d_pyr, e->d_xtab, e->d_ytab, st);
+  launch_pyramid(e->g, e->d_geom, dimgs, width, height, dstride, dimg_stride, n_images, e->d_pyr, e->d_xtab, e->d_ytab,
+                 e->d_wtab, e->wtab_off, st);
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_FAST], st);
   if (e->fast_persist) {
     if (e->n_fast_recs > 0)

@@ -12,6 +12,8 @@
 // instead of 2.  Border rows are not recomputed: an interior row y is also stored to the padded
 // rows that REFLECT_101 maps onto it; border columns are ordinary words whose four columns are
 // reflected before the tap lookup.  Bound: HBM (reads P_{l-1}, writes (w+38)(h+38)).
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace cuorb {
@@ -187,9 +189,119 @@ __global__ void __launch_bounds__(PYR_TX) k_pyr_resize(const ExtractorGeom* __re
   }
 }
 
+// ---- table-driven variant (all scale factors whose 4-column tap window fits 8 source bytes) ----
+// Everything a thread needs about its four output columns comes from a host-built table
+// (build_resize_words): the aligned source offset of its 12-byte window, the funnel shift that
+// brings the first tap to byte 0, four PRMT selectors and the four coefficient pairs.  Per source
+// row: 3 aligned loads, 2 funnel shifts, then per column PRMT + dp2a + shift.  The strip's vertical
+// taps sit in shared memory, so the row loop has no dependent global load; the horizontal sums of
+// the previous lower source row are reused whenever the source step is 1.
+//   wtab[2*word]   = {window byte offset (4-aligned), funnel shift (bits), sel0 | sel1 << 16, sel2 | sel3 << 16}
+//   wtab[2*word+1] = {a0 | a1 << 16} for the four columns
+__global__ void __launch_bounds__(PYR_TX, 24) k_pyr_resize_tab(const ExtractorGeom* __restrict__ dg, int level,
+                                                           uint8_t* __restrict__ pyr,
+                                                           const uint4* __restrict__ wtab,
+                                                           const ResizeTap* __restrict__ ytab) {
+  __shared__ int s_ys[PYR_RS];
+  __shared__ unsigned s_b0[PYR_RS], s_b1[PYR_RS];
+  const LevelGeom& L = dg->lv[level];
+  const LevelGeom& S = dg->lv[level - 1];
+  const int lh = L.h;
+  const int y0 = blockIdx.y * PYR_RS, y1 = min(y0 + PYR_RS, lh);
+  if (threadIdx.x < PYR_RS && y0 + (int)threadIdx.x < lh) {
+    const ResizeTap t = ytab[L.ytab_off + y0 + threadIdx.x];
+    s_ys[threadIdx.x] = max((int)t.s, 0);
+    s_b0[threadIdx.x] = (unsigned)t.a0 << 16;
+    s_b1[threadIdx.x] = (unsigned)t.a1 << 16;
+  }
+  __syncthreads();
+  const int word = blockIdx.x * PYR_TX + threadIdx.x;
+  if (word * 4 >= L.pitch) return;
+  const uint4 e0 = __ldg(&wtab[2 * word]), cf = __ldg(&wtab[2 * word + 1]);
+  uint8_t* base = pyr + (size_t)blockIdx.z * dg->pyr_img_stride;
+  const uint8_t* src = base + S.pix_off + e0.x;
+  const int spitch = S.pitch, sh1 = S.h - 1, dp4 = L.pitch >> 2;
+  unsigned* dst = reinterpret_cast<unsigned*>(base + L.plane_off) + word;
+  const unsigned shift = e0.y, sel0 = e0.z & 0xFFFFu, sel1 = e0.z >> 16, sel2 = e0.w & 0xFFFFu, sel3 = e0.w >> 16;
+
+  auto fetch = [&](int sy, unsigned (&w)[3]) {
+    const unsigned* p = reinterpret_cast<const unsigned*>(src + (size_t)min(sy, sh1) * spitch);  // OpenCV clips rows to sh-1
+    w[0] = p[0]; w[1] = p[1]; w[2] = p[2];
+  };
+  auto hsum4 = [&](const unsigned (&w)[3], unsigned (&h)[4]) {
+    const unsigned X0 = __funnelshift_r(w[0], w[1], shift), X1 = __funnelshift_r(w[1], w[2], shift);
+    h[0] = __dp2a_lo(cf.x, __byte_perm(X0, X1, sel0), 0u) >> 4;
+    h[1] = __dp2a_lo(cf.y, __byte_perm(X0, X1, sel1), 0u) >> 4;
+    h[2] = __dp2a_lo(cf.z, __byte_perm(X0, X1, sel2), 0u) >> 4;
+    h[3] = __dp2a_lo(cf.w, __byte_perm(X0, X1, sel3), 0u) >> 4;
+  };
+  // software pipeline: the source rows the NEXT output row needs are requested before the current
+  // row is blended and stored
+  unsigned hA[4], hB[4], rA[3], rB[3];
+  int s = s_ys[0];
+  fetch(s, rA); fetch(s + 1, rB);
+  hsum4(rA, hA); hsum4(rB, hB);
+  for (int y = y0; y < y1; y++) {
+    const int sN = y + 1 < y1 ? s_ys[y + 1 - y0] : s;
+    const int adv = sN - s;
+    if (adv != 0) {
+      fetch(sN + 1, rB);
+      if (adv != 1) fetch(sN, rA);
+    }
+    const unsigned out = vblend(hA, hB, s_b0[y - y0], s_b1[y - y0]);
+    dst[(size_t)(y + EDGE_THRESHOLD) * dp4] = out;
+    if (y >= 1 && y <= EDGE_THRESHOLD) dst[(size_t)(EDGE_THRESHOLD - y) * dp4] = out;
+    if (y >= lh - 1 - EDGE_THRESHOLD && y <= lh - 2) dst[(size_t)(2 * lh + EDGE_THRESHOLD - 2 - y) * dp4] = out;
+    if (adv != 0) {
+      if (adv == 1) {
+#pragma unroll
+        for (int b = 0; b < 4; b++) hA[b] = hB[b];
+      } else {
+        hsum4(rA, hA);
+      }
+      hsum4(rB, hB);
+    }
+    s = sN;
+  }
+}
+
+// host: per-word tables for k_pyr_resize_tab, levels 1..n-1 back to back; off[l] = first entry (in
+// uint4) of level l, or -1 when the level needs the byte-load kernel (window wider than 8 bytes)
+void build_resize_words(const ExtractorGeom& g, const std::vector<ResizeTap>& xtab, std::vector<uint4>& wt, int* off) {
+  wt.clear();
+  off[0] = -1;
+  for (int l = 1; l < g.nlevels; l++) {
+    const LevelGeom& L = g.lv[l];
+    const size_t start = wt.size();
+    bool ok = true;
+    for (int word = 0; word * 4 < L.pitch && ok; word++) {
+      int sx[4], smin = 1 << 30, smax = 0;
+      unsigned coef[4];
+      for (int b = 0; b < 4; b++) {
+        int x = word * 4 + b - ROW_LEAD;
+        x = std::min(std::max(x, -EDGE_THRESHOLD), L.w + EDGE_THRESHOLD - 1);
+        x = x < 0 ? -x : x;
+        x = x >= L.w ? 2 * L.w - 2 - x : x;
+        const ResizeTap t = xtab[L.xtab_off + x];
+        sx[b] = t.s; smin = std::min(smin, (int)t.s); smax = std::max(smax, (int)t.s);
+        coef[b] = (unsigned)(unsigned short)t.a0 | ((unsigned)(unsigned short)t.a1 << 16);
+      }
+      if (smax - smin + 1 > 7) { ok = false; break; }
+      const int cbase = smin & ~3, t0 = smin - cbase;
+      unsigned sel[4];
+      for (int b = 0; b < 4; b++) { const int d = sx[b] - smin; sel[b] = (unsigned)d | ((unsigned)(d + 1) << 4); }
+      wt.push_back(make_uint4((unsigned)cbase, (unsigned)(8 * t0), sel[0] | (sel[1] << 16), sel[2] | (sel[3] << 16)));
+      wt.push_back(make_uint4(coef[0], coef[1], coef[2], coef[3]));
+    }
+    if (ok) off[l] = (int)start;
+    else { wt.resize(start); off[l] = -1; }
+  }
+}
+
 void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8_t* imgs, int, int,
                     size_t stride, size_t image_stride, int n_img, uint8_t* pyr,
-                    const ResizeTap* xtab, const ResizeTap* ytab, cudaStream_t st) {
+                    const ResizeTap* xtab, const ResizeTap* ytab, const uint4* wtab, const int* wtab_off,
+                    cudaStream_t st) {
   const int aligned = (((uintptr_t)imgs | stride | image_stride) & 3) == 0;
   for (int l = 0; l < g.nlevels; l++) {
     const LevelGeom& L = g.lv[l];
@@ -199,7 +311,8 @@ void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8
     } else {
       // four adjacent output columns span 3*scale + 2 source bytes (+3 for alignment): 12 bytes up to scale 2
       const double sx = (double)g.lv[l - 1].w / L.w;
-      if (3.0 * sx + 5.0 < 11.5) k_pyr_resize<false><<<grid, PYR_TX, 0, st>>>(dg, l, pyr, xtab, ytab);
+      if (wtab && wtab_off[l] >= 0) k_pyr_resize_tab<<<grid, PYR_TX, 0, st>>>(dg, l, pyr, wtab + wtab_off[l], ytab);
+      else if (3.0 * sx + 5.0 < 11.5) k_pyr_resize<false><<<grid, PYR_TX, 0, st>>>(dg, l, pyr, xtab, ytab);
       else k_pyr_resize<true><<<grid, PYR_TX, 0, st>>>(dg, l, pyr, xtab, ytab);
     }
     count_launch();
