@@ -15,7 +15,7 @@
 namespace cuorb {
 
 constexpr int BL_THREADS = 64;   // words (4 px each) per CTA row segment
-constexpr int BL_ROWS    = 32;   // output rows per thread strip
+constexpr int BL_ROWS    = 21;   // output rows per thread strip
 
 __device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ row, unsigned (&h)[4]) {
   const unsigned* p = reinterpret_cast<const unsigned*>(row);
