@@ -375,6 +375,11 @@ def run_cuorb(args):
                 traffic = tj[dom]["dram_bytes_per_image"] * B
         except Exception:
             pass
+        pipe = None
+        try:
+            pipe = json.load(open(os.path.join(ROOT, "profiles", "pipe_util.json"))).get(dom_all)
+        except Exception:
+            pass
         cores = os.cpu_count() or 1
         with_cpu = not args.no_cpu_baseline and world == 1      # the CPU baseline is an N=1 figure
         cpu_fps, cpu_n, _, _ = cpu_baseline(cores) if with_cpu else (None, 0, 0, 0)
@@ -399,7 +404,7 @@ def run_cuorb(args):
                          "note": "stage times: CUDA events on the launching stream, handles serialised; FAST is bound by the "
                                  "integer ALU pipe (min/max network), not HBM - see DESIGN.md section 6",
                          "stage_ms_per_step": stage_ms, "stage_gbs": stage_gbs,
-                         "dominant_stage_overall": dom_all,
+                         "dominant_stage_overall": dom_all, "dominant_stage_pipe_utilisation": pipe,
                          "algorithmic_bytes_per_image": ab},
             "cpu_baseline": None if cpu_fps is None else {
                 "value": cpu_fps, "unit": "frames/s", "cores": cores, "kind": "port",
