@@ -267,6 +267,26 @@ int cuorb_stereo_from_rgbd(int device, int n, const cuorb_keypoint* kps, const c
                            const float* depth, int width, int height, size_t stride_bytes,
                            cuorb_mem depth_where, float mbf, float* u_right, float* depth_out);
 
+/* ---- dense all-pairs Hamming ---- */
+
+/* cv::BFMatcher(cv::NORM_HAMMING).knnMatch(query, train, matches, 2) as Frame::ComputeStereoFishEyeMatches
+ * uses it (src/Frame.cc:1304-1355), batched: n_sets independent (query, train) pairs of descriptor sets laid
+ * out back to back; query_off / train_off hold n_sets + 1 ascending row offsets.  Per query row:
+ * idx_out[2i..2i+1] / dist_out[2i..2i+1] = the two nearest train rows (index relative to the set's first
+ * train row) in (distance, trainIdx) order, -1 where the train set has fewer than two rows.
+ * ratio_match_out (optional, one int per query): idx0 if dist0 < dist1 * 0.7 (the Lowe test of :1329)
+ * else -1.  Host arrays.  Returns the number of query rows. */
+int cuorb_knn_match2(int device, int n_sets, const int32_t* query_off, const uint8_t* query_desc,
+                     const int32_t* train_off, const uint8_t* train_desc, int32_t* idx_out,
+                     int32_t* dist_out, int32_t* ratio_match_out);
+
+/* void MapPoint::ComputeDistinctiveDescriptors() (src/MapPoint.cc:376-450) for n_points MapPoints at once:
+ * desc = the observed descriptors of all points back to back (the reference's vDescriptors order),
+ * off = n_points + 1 ascending row offsets.  best_out[p] = BestIdx (row inside point p's block; -1 for a
+ * point without descriptors).  At most 1024 observations per point.  Host arrays. */
+int cuorb_distinctive_descriptors(int device, int n_points, const int32_t* off, const uint8_t* desc,
+                                  int32_t* best_out);
+
 /* ---- instrumentation ---- */
 
 /* number of libcuorb kernel launches issued by this process so far (bench.py's gpu_launches) */

@@ -36,7 +36,7 @@ class FrameViewC(C.Structure):
 
 def build(force: bool = False) -> str:
     srcs = [os.path.join(_HERE, f) for f in
-            ("orb_oracle.cpp", "orb_oracle_match.cpp", "orb_oracle_capi.cpp", "preproc_oracle.cpp", "frameglue_oracle.cpp", "orb_oracle.hpp")]
+            ("orb_oracle.cpp", "orb_oracle_match.cpp", "orb_oracle_capi.cpp", "preproc_oracle.cpp", "frameglue_oracle.cpp", "bfmatch_oracle.cpp", "orb_oracle.hpp")]
     stale = (not os.path.exists(_LIB_PATH)) or any(
         os.path.getmtime(s) > os.path.getmtime(_LIB_PATH) for s in srcs)
     if force or stale:
@@ -94,6 +94,9 @@ def lib() -> C.CDLL:
         L.oo_undistort_keypoints.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.oo_stereo_from_rgbd.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_float,
                                           C.c_void_p, C.c_void_p]
+        L.oo_knn_match2.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        L.oo_fisheye_ratio_test.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.oo_distinctive_descriptors.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         _lib = L
     return _lib
 
@@ -311,6 +314,30 @@ def stereo_from_rgbd(kps, kps_un, depth, mbf):
     u = np.empty(len(kps), np.float32); d = np.empty(len(kps), np.float32)
     lib().oo_stereo_from_rgbd(_p(kps), _p(kps_un), len(kps), _p(depth), depth.shape[1], np.float32(mbf), _p(u), _p(d))
     return u, d
+
+
+# ---- dense all-pairs Hamming (bfmatch_oracle.cpp) ----
+def knn_match2(q, t):
+    """cv::BFMatcher(NORM_HAMMING).knnMatch(q, t, k=2) -> (idx [nq, 2], dist [nq, 2]); -1 where missing."""
+    q = np.ascontiguousarray(q, dtype=np.uint8).reshape(-1, 32); t = np.ascontiguousarray(t, dtype=np.uint8).reshape(-1, 32)
+    idx = np.empty((len(q), 2), np.int32); dist = np.empty((len(q), 2), np.int32)
+    lib().oo_knn_match2(_p(q), len(q), _p(t), len(t), _p(idx), _p(dist))
+    return idx, dist
+
+
+def fisheye_ratio_test(idx, dist):
+    idx = np.ascontiguousarray(idx, dtype=np.int32); dist = np.ascontiguousarray(dist, dtype=np.int32)
+    out = np.empty(len(idx), np.int32)
+    lib().oo_fisheye_ratio_test(_p(idx), _p(dist), len(idx), _p(out))
+    return out
+
+
+def distinctive_descriptors(desc, off):
+    """MapPoint::ComputeDistinctiveDescriptors for many points: desc [sum n, 32], off [n_points + 1]."""
+    desc = np.ascontiguousarray(desc, dtype=np.uint8).reshape(-1, 32); off = np.ascontiguousarray(off, dtype=np.int32)
+    best = np.empty(len(off) - 1, np.int32)
+    lib().oo_distinctive_descriptors(_p(desc), _p(off), len(off) - 1, _p(best))
+    return best
 
 
 def hamming(a, b):

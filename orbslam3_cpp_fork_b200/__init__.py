@@ -8,3 +8,4 @@ from .extractor import ORBextractor  # noqa: F401
 from .matcher import Frame, MapPointSoA, ORBmatcher  # noqa: F401
 from .preproc import FramePreprocessor  # noqa: F401
 from .frame_ops import ComputeStereoFromRGBD, UndistortKeyPoints  # noqa: F401
+from .bfmatch import ComputeDistinctiveDescriptors, knnMatch2  # noqa: F401

@@ -94,6 +94,9 @@ SIGNATURES = {
     "cuorb_undistort_keypoints": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "cuorb_stereo_from_rgbd": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                          C.c_size_t, C.c_int, C.c_float, C.c_void_p, C.c_void_p]),
+    "cuorb_knn_match2": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                   C.c_void_p, C.c_void_p]),
+    "cuorb_distinctive_descriptors": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "cuorb_kernel_launch_count": (C.c_uint64, []),
     "cuorb_set_profiling": (C.c_int, [C.c_void_p, C.c_int]),
     "cuorb_stage_ms": (C.c_int, [C.c_void_p, C.c_void_p]),

@@ -45,3 +45,42 @@ void ComputeStereoFromRGBD(FrameT& F, const cv::Mat& imDepth, int device = 0) {
 }
 
 }  // namespace ORB_SLAM3
+
+// ---- dense all-pairs Hamming users ----
+namespace ORB_SLAM3 {
+
+// The matching half of void Frame::ComputeStereoFishEyeMatches() (src/Frame.cc:1304-1355):
+// BFmatcher.knnMatch(stereoDescLeft, stereoDescRight, matches, 2) + the 0.7 ratio test (:1329).
+// accepted[i] = trainIdx of the accepted match of left row i, or -1; the caller keeps the
+// triangulation loop (:1331-1352, KannalaBrandt8::TriangulateMatches) on accepted rows.
+inline void FisheyeStereoCandidates(const cv::Mat& stereoDescLeft, const cv::Mat& stereoDescRight,
+                                    std::vector<int>& accepted, int device = 0) {
+  accepted.assign(stereoDescLeft.rows, -1);
+  if (stereoDescLeft.rows == 0 || stereoDescRight.rows == 0) return;
+  if ((stereoDescLeft.rows > 1 && stereoDescLeft.step != 32) || (stereoDescRight.rows > 1 && stereoDescRight.step != 32))
+    throw std::invalid_argument("FisheyeStereoCandidates: descriptor matrices must be n x 32 contiguous");
+  const int32_t qo[2] = {0, stereoDescLeft.rows}, to[2] = {0, stereoDescRight.rows};
+  std::vector<int32_t> idx(2 * (size_t)stereoDescLeft.rows), dist(idx.size());
+  const int rc = cuorb_knn_match2(device, 1, qo, stereoDescLeft.ptr<unsigned char>(0), to, stereoDescRight.ptr<unsigned char>(0),
+                                  idx.data(), dist.data(), accepted.data());
+  if (rc < 0) throw std::runtime_error(std::string("FisheyeStereoCandidates (libcuorb): ") + cuorb_last_error());
+}
+
+// void MapPoint::ComputeDistinctiveDescriptors() (src/MapPoint.cc:376-450) for a batch of MapPoints
+// (LocalMapping calls it once per new/fused point): vDescriptors[p] = the observed descriptor rows of
+// point p in the reference's iteration order; returns BestIdx per point.
+inline std::vector<int> DistinctiveDescriptorIndices(const std::vector<std::vector<cv::Mat>>& vDescriptors, int device = 0) {
+  std::vector<int32_t> off(vDescriptors.size() + 1, 0);
+  for (size_t p = 0; p < vDescriptors.size(); p++) off[p + 1] = off[p] + (int32_t)vDescriptors[p].size();
+  std::vector<unsigned char> flat((size_t)off.back() * 32 + 32);
+  for (size_t p = 0; p < vDescriptors.size(); p++)
+    for (size_t k = 0; k < vDescriptors[p].size(); k++)
+      std::memcpy(&flat[((size_t)off[p] + k) * 32], vDescriptors[p][k].ptr<unsigned char>(0), 32);
+  std::vector<int> best(vDescriptors.size(), -1);
+  if (vDescriptors.empty()) return best;
+  const int rc = cuorb_distinctive_descriptors(device, (int)vDescriptors.size(), off.data(), flat.data(), best.data());
+  if (rc < 0) throw std::runtime_error(std::string("DistinctiveDescriptorIndices (libcuorb): ") + cuorb_last_error());
+  return best;
+}
+
+}  // namespace ORB_SLAM3

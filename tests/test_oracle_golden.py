@@ -11,7 +11,7 @@ from oracle import oracle_py as op
 from orbslam3_cpp_fork_b200 import synth
 
 GOLDEN = sorted(p for p in glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz"))
-                if not os.path.basename(p).startswith(("preproc_", "frameglue_")))
+                if not os.path.basename(p).startswith(("preproc_", "frameglue_", "bfmatch_")))
 
 
 def sha(a):
