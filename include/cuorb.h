@@ -267,6 +267,25 @@ int cuorb_stereo_from_rgbd(int device, int n, const cuorb_keypoint* kps, const c
                            const float* depth, int width, int height, size_t stride_bytes,
                            cuorb_mem depth_where, float mbf, float* u_right, float* depth_out);
 
+/* ---- vocabulary-node searches ---- */
+
+/* int ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches)
+ * (src/ORBmatcher.cc:237-420, mode 0) and
+ * int ORBmatcher::SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12)
+ * (src/ORBmatcher.cc:784-916, mode 1), mono branches, on flattened inputs.  Side 1 = pKF / pKF1,
+ * side 2 = F / pKF2.  valid1[i] = side-1 feature i has a non-bad MapPoint; eligible2[j] = side-2 feature
+ * j may be matched (all ones for a Frame; "has a non-bad MapPoint" for a KeyFrame); angle1/angle2 =
+ * keypoint angles (may be NULL when check_orientation == 0).  The merge-join of the two
+ * DBoW2::FeatureVectors is passed as its n_nodes common nodes: node k lists side-1 features
+ * node_idx1[node_off1[k] .. node_off1[k+1]) and side-2 features node_idx2[node_off2[k] ..), both in the
+ * FeatureVector's order.  match12_out[i] = side-2 feature matched to side-1 feature i, or -1, after
+ * the rotation-consistency cut.  Returns nmatches. */
+int cuorb_search_by_bow(int device, int n1, const uint8_t* desc1, const uint8_t* valid1,
+                        const float* angle1, int n2, const uint8_t* desc2, const uint8_t* eligible2,
+                        const float* angle2, int n_nodes, const int32_t* node_off1,
+                        const int32_t* node_idx1, const int32_t* node_off2, const int32_t* node_idx2,
+                        int mode, float nnratio, int check_orientation, int32_t* match12_out);
+
 /* ---- dense all-pairs Hamming ---- */
 
 /* cv::BFMatcher(cv::NORM_HAMMING).knnMatch(query, train, matches, 2) as Frame::ComputeStereoFishEyeMatches

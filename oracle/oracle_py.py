@@ -36,7 +36,7 @@ class FrameViewC(C.Structure):
 
 def build(force: bool = False) -> str:
     srcs = [os.path.join(_HERE, f) for f in
-            ("orb_oracle.cpp", "orb_oracle_match.cpp", "orb_oracle_capi.cpp", "preproc_oracle.cpp", "frameglue_oracle.cpp", "bfmatch_oracle.cpp", "orb_oracle.hpp")]
+            ("orb_oracle.cpp", "orb_oracle_match.cpp", "orb_oracle_capi.cpp", "preproc_oracle.cpp", "frameglue_oracle.cpp", "bfmatch_oracle.cpp", "bow_oracle.cpp", "orb_oracle.hpp")]
     stale = (not os.path.exists(_LIB_PATH)) or any(
         os.path.getmtime(s) > os.path.getmtime(_LIB_PATH) for s in srcs)
     if force or stale:
@@ -97,6 +97,9 @@ def lib() -> C.CDLL:
         L.oo_knn_match2.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.oo_fisheye_ratio_test.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.oo_distinctive_descriptors.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.oo_search_by_bow.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                       C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                       C.c_float, C.c_int, C.c_void_p]
         _lib = L
     return _lib
 
@@ -338,6 +341,23 @@ def distinctive_descriptors(desc, off):
     best = np.empty(len(off) - 1, np.int32)
     lib().oo_distinctive_descriptors(_p(desc), _p(off), len(off) - 1, _p(best))
     return best
+
+
+# ---- vocabulary-node searches (bow_oracle.cpp) ----
+def search_by_bow(desc1, valid1, angle1, desc2, eligible2, angle2, off1, idx1, off2, idx2, mode, nnratio=0.7,
+                  check_orientation=True):
+    """ORBmatcher::SearchByBoW on flattened inputs; mode 0 = (KeyFrame, Frame), 1 = (KeyFrame, KeyFrame).
+    Returns (nmatches, match12 [n1])."""
+    desc1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32); desc2 = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+    valid1 = np.ascontiguousarray(valid1, np.uint8); eligible2 = np.ascontiguousarray(eligible2, np.uint8)
+    angle1 = np.ascontiguousarray(angle1, np.float32); angle2 = np.ascontiguousarray(angle2, np.float32)
+    off1 = np.ascontiguousarray(off1, np.int32); idx1 = np.ascontiguousarray(idx1, np.int32)
+    off2 = np.ascontiguousarray(off2, np.int32); idx2 = np.ascontiguousarray(idx2, np.int32)
+    m = np.empty(len(desc1), np.int32)
+    n = lib().oo_search_by_bow(len(desc1), _p(desc1), _p(valid1), _p(angle1), len(desc2), _p(desc2), _p(eligible2), _p(angle2),
+                               len(off1) - 1, _p(off1), _p(idx1), _p(off2), _p(idx2), int(mode), np.float32(nnratio),
+                               int(bool(check_orientation)), _p(m))
+    return n, m
 
 
 def hamming(a, b):

@@ -97,6 +97,9 @@ SIGNATURES = {
     "cuorb_knn_match2": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                    C.c_void_p, C.c_void_p]),
     "cuorb_distinctive_descriptors": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "cuorb_search_by_bow": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                      C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_int, C.c_float, C.c_int, C.c_void_p]),
     "cuorb_kernel_launch_count": (C.c_uint64, []),
     "cuorb_set_profiling": (C.c_int, [C.c_void_p, C.c_int]),
     "cuorb_stage_ms": (C.c_int, [C.c_void_p, C.c_void_p]),

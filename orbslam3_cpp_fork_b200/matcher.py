@@ -172,3 +172,49 @@ class ORBmatcher:
                 if rot[i] not in keepb:
                     Cur.mvpMapPoints[best[i]] = -1
         return n, best, rot, keepb
+
+
+def join_feature_vectors(mFeatVec1, mFeatVec2):
+    """The merge-join SearchByBoW does over two DBoW2::FeatureVectors (std::map<NodeId, std::vector<unsigned>>,
+    src/ORBmatcher.cc:252-259, 395-399): common nodes in ascending NodeId order.
+    mFeatVec*: dict {node_id: sequence of feature indices}.  Returns (off1, idx1, off2, idx2)."""
+    common = sorted(set(mFeatVec1) & set(mFeatVec2))
+    off1 = np.zeros(len(common) + 1, np.int32); off2 = np.zeros(len(common) + 1, np.int32)
+    l1, l2 = [], []
+    for k, node in enumerate(common):
+        a = np.asarray(mFeatVec1[node], np.int32); b = np.asarray(mFeatVec2[node], np.int32)
+        l1.append(a); l2.append(b)
+        off1[k + 1] = off1[k] + len(a); off2[k + 1] = off2[k] + len(b)
+    idx1 = np.concatenate(l1).astype(np.int32) if l1 else np.zeros(0, np.int32)
+    idx2 = np.concatenate(l2).astype(np.int32) if l2 else np.zeros(0, np.int32)
+    return off1, idx1, off2, idx2
+
+
+def _search_by_bow(self, desc1, valid1, angle1, mFeatVec1, desc2, eligible2, angle2, mFeatVec2, mode):
+    desc1 = _c(desc1, np.uint8).reshape(-1, 32); desc2 = _c(desc2, np.uint8).reshape(-1, 32)
+    valid1 = _c(np.asarray(valid1).astype(np.uint8), np.uint8); eligible2 = _c(np.asarray(eligible2).astype(np.uint8), np.uint8)
+    angle1 = _c(angle1, np.float32); angle2 = _c(angle2, np.float32)
+    off1, idx1, off2, idx2 = join_feature_vectors(mFeatVec1, mFeatVec2)
+    match12 = np.full(len(desc1), -1, np.int32)
+    n = check(self._L.cuorb_search_by_bow(self.device, len(desc1), ptr(desc1), ptr(valid1), ptr(angle1), len(desc2), ptr(desc2),
+                                          ptr(eligible2), ptr(angle2), len(off1) - 1, ptr(off1), ptr(idx1), ptr(off2), ptr(idx2),
+                                          int(mode), self.mfNNratio, int(self.mbCheckOrientation), ptr(match12)))
+    return n, match12
+
+
+def SearchByBoW_KF_F(self, kf_desc, kf_has_mappoint, kf_angle, kf_featvec, f_desc, f_angle, f_featvec):
+    """int SearchByBoW(KeyFrame* pKF, Frame& F, vpMapPointMatches) (src/ORBmatcher.cc:237-420), mono branch.
+    Returns (nmatches, match[kf feature] = F feature or -1); the reference's
+    vpMapPointMatches[match[i]] = pKF->GetMapPointMatches()[i] is the caller's replay."""
+    return _search_by_bow(self, kf_desc, kf_has_mappoint, kf_angle, kf_featvec, f_desc, np.ones(len(f_desc), np.uint8), f_angle,
+                          f_featvec, 0)
+
+
+def SearchByBoW_KF_KF(self, desc1, has_mp1, angle1, featvec1, desc2, has_mp2, angle2, featvec2):
+    """int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vpMatches12) (src/ORBmatcher.cc:784-916).
+    Returns (nmatches, match12[i1] = feature of pKF2 or -1)."""
+    return _search_by_bow(self, desc1, has_mp1, angle1, featvec1, desc2, has_mp2, angle2, featvec2, 1)
+
+
+ORBmatcher.SearchByBoW_KF_F = SearchByBoW_KF_F
+ORBmatcher.SearchByBoW_KF_KF = SearchByBoW_KF_KF

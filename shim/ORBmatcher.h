@@ -7,6 +7,8 @@
 // F.mvpMapPoints[idx] = pMP are replayed in the reference's order.  Pinhole (Nleft == -1) only.
 #pragma once
 #include <cmath>
+#include <cstring>
+#include <map>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -79,6 +81,48 @@ public:
     return n;
   }
 
+  // int SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches)
+  // (include/ORBmatcher.h:66, src/ORBmatcher.cc:237-420), mono branch.  Reads pKF->GetMapPointMatches(),
+  // pKF->mFeatVec, pKF->mDescriptors, pKF->mvKeysUn, F.mFeatVec, F.mDescriptors, F.mvKeys, F.N.
+  template <class KeyFrameT, class FrameT, class MapPointT>
+  int SearchByBoW(KeyFrameT* pKF, FrameT& F, std::vector<MapPointT*>& vpMapPointMatches) {
+    if (F.Nleft != -1) throw std::runtime_error("ORBmatcher shim: fisheye (Nleft != -1) branch is not built");
+    const std::vector<MapPointT*> vpMapPointsKF = pKF->GetMapPointMatches();
+    vpMapPointMatches.assign(F.N, static_cast<MapPointT*>(nullptr));
+    const int n1 = (int)vpMapPointsKF.size(), n2 = F.N;
+    if (n1 == 0 || n2 == 0) return 0;
+    std::vector<uint8_t> valid1(n1), elig2(n2, 1);
+    std::vector<float> a1(n1), a2(n2);
+    for (int i = 0; i < n1; i++) { valid1[i] = vpMapPointsKF[i] && !vpMapPointsKF[i]->isBad(); a1[i] = pKF->mvKeysUn[i].angle; }
+    for (int j = 0; j < n2; j++) a2[j] = F.mvKeys[j].angle;
+    std::vector<int32_t> match(n1, -1);
+    const int n = bow(pKF->mFeatVec, F.mFeatVec, n1, contiguous(pKF->mDescriptors), valid1, a1, n2, contiguous(F.mDescriptors),
+                      elig2, a2, 0, match);
+    for (int i = 0; i < n1; i++)
+      if (match[i] >= 0) vpMapPointMatches[match[i]] = vpMapPointsKF[i];   // :304
+    return n;
+  }
+
+  // int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12)
+  // (include/ORBmatcher.h:67, src/ORBmatcher.cc:784-916), NLeft == -1.
+  template <class KeyFrameT, class MapPointT>
+  int SearchByBoW(KeyFrameT* pKF1, KeyFrameT* pKF2, std::vector<MapPointT*>& vpMatches12) {
+    const std::vector<MapPointT*> mp1 = pKF1->GetMapPointMatches(), mp2 = pKF2->GetMapPointMatches();
+    vpMatches12.assign(mp1.size(), static_cast<MapPointT*>(nullptr));
+    const int n1 = (int)mp1.size(), n2 = (int)mp2.size();
+    if (n1 == 0 || n2 == 0) return 0;
+    std::vector<uint8_t> valid1(n1), elig2(n2);
+    std::vector<float> a1(n1), a2(n2);
+    for (int i = 0; i < n1; i++) { valid1[i] = mp1[i] && !mp1[i]->isBad(); a1[i] = pKF1->mvKeysUn[i].angle; }
+    for (int j = 0; j < n2; j++) { elig2[j] = mp2[j] && !mp2[j]->isBad(); a2[j] = pKF2->mvKeysUn[j].angle; }
+    std::vector<int32_t> match(n1, -1);
+    const int n = bow(pKF1->mFeatVec, pKF2->mFeatVec, n1, contiguous(pKF1->mDescriptors), valid1, a1, n2,
+                      contiguous(pKF2->mDescriptors), elig2, a2, 1, match);
+    for (int i = 0; i < n1; i++)
+      if (match[i] >= 0) vpMatches12[i] = mp2[match[i]];                   // :858
+    return n;
+  }
+
   // float RadiusByViewingCos(const float& viewCos)  (src/ORBmatcher.cc:229-235)
   static float RadiusByViewingCos(const float& viewCos) { return viewCos > 0.998f ? 2.5f : 4.0f; }
 
@@ -87,6 +131,29 @@ public:
 
 private:
   int device_;
+
+  // merge-join of two DBoW2::FeatureVectors (std::map<NodeId, std::vector<unsigned>>) + the device search
+  template <class FeatVecT>
+  int bow(const FeatVecT& fv1, const FeatVecT& fv2, int n1, const uint8_t* d1, const std::vector<uint8_t>& valid1,
+          const std::vector<float>& a1, int n2, const uint8_t* d2, const std::vector<uint8_t>& elig2,
+          const std::vector<float>& a2, int mode, std::vector<int32_t>& match) {
+    std::vector<int32_t> off1(1, 0), off2(1, 0), idx1, idx2;
+    auto it1 = fv1.begin(); auto it2 = fv2.begin();
+    while (it1 != fv1.end() && it2 != fv2.end()) {
+      if (it1->first == it2->first) {
+        for (auto v : it1->second) idx1.push_back((int32_t)v);
+        for (auto v : it2->second) idx2.push_back((int32_t)v);
+        off1.push_back((int32_t)idx1.size()); off2.push_back((int32_t)idx2.size());
+        ++it1; ++it2;
+      } else if (it1->first < it2->first) it1 = fv1.lower_bound(it2->first);
+      else it2 = fv2.lower_bound(it1->first);
+    }
+    const int n = cuorb_search_by_bow(device_, n1, d1, valid1.data(), a1.data(), n2, d2, elig2.data(), a2.data(),
+                                      (int)off1.size() - 1, off1.data(), idx1.data(), off2.data(), idx2.data(), mode, mfNNratio,
+                                      mbCheckOrientation ? 1 : 0, match.data());
+    if (n < 0) throw std::runtime_error(std::string("SearchByBoW (libcuorb): ") + cuorb_last_error());
+    return n;
+  }
 
   static const uint8_t* contiguous(const cv::Mat& m) {
     if (m.rows > 1 && m.step != 32) throw std::runtime_error("descriptor matrix must be n x 32 contiguous");
