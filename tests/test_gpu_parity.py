@@ -191,3 +191,28 @@ def test_search_by_projection_lastframe(cu, fwd, bwd, th):
         F, c["desc"], c["u"], c["v"], c["inv_z"], c["octave"], c["angle"], c["flags"], th, fwd, bwd)
     assert n_o > 50
     assert n == n_o and (best == best_o).all() and (rot == rot_o).all() and (keepb == keep_o).all()
+
+
+@pytest.mark.parametrize("w,h,nf,scale,nlevels,ini,mn,seed", [
+    (641, 479, 1000, 1.2, 8, 20, 7, 91),       # odd size: unaligned pitches, ragged last cells
+    (1280, 720, 1500, 1.2, 8, 20, 7, 92),
+    (1920, 1080, 2000, 1.2, 8, 20, 7, 93),     # largest size the shim defaults to
+    (752, 480, 1000, 1.1, 12, 20, 7, 94),      # many shallow levels
+    (752, 480, 800, 1.5, 5, 20, 7, 95),        # steep pyramid: wide resize windows
+    (400, 300, 300, 1.3, 6, 12, 12, 96),       # iniThFAST == minThFAST: no retry pass
+])
+def test_other_geometries(cu, w, h, nf, scale, nlevels, ini, mn, seed):
+    """Sizes, pyramid shapes and thresholds other than the benchmark's: keypoints, descriptors and the
+    per-level FAST candidates stay bit-identical to the oracle."""
+    img = synth.synth_image(w, h, seed)
+    e = cu.ORBextractor(nf, scale, nlevels, ini, mn, max_width=w, max_height=h)
+    o = op.OracleExtractor(nf, scale, nlevels, ini, mn)
+    mono, k, d = e(img, None, (0, 0))
+    mo, ko, do = o.extract(img, (0, 0))
+    for lv in range(nlevels):
+        assert (e.download_plane(lv, 0) == o.plane(lv, 0)).all(), f"pyramid level {lv}"
+        xs, ys, rs = e.download_candidates(lv)
+        xo, yo, ro = o.candidates(lv)
+        assert len(xs) == len(xo) and (xs == xo).all() and (ys == yo).all() and (rs == ro).all(), f"FAST level {lv}"
+    assert mono == mo
+    assert_extract_equal(k, d, ko, do)
