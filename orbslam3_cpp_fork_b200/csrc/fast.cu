@@ -370,93 +370,84 @@ __global__ void __launch_bounds__(128) k_fast_persist(const __grid_constant__ Fa
     for (int pass = 0; pass < 2; pass++) {
       const int cur_th = pass == 0 ? P.ini_th : P.min_th;
       // ---- 2a: compass test, four pixels per thread, passing pairs -> per-warp list ----
+      int npairs;
       {
         const int nquads = nq * dh;
         const unsigned K = (unsigned)(127 - min(cur_th, 127)) * 0x01010101u;
         unsigned short* seg = s_plist + wid * pcap;
         int cnt = 0;
         for (int i0 = 0; i0 < nquads; i0 += 128) {
-          const int i = i0 + tid;
-          bool f0 = false, f1 = false;
-          int r = 0, q = 0;
-          if (i < nquads) {
-            r = fastdiv(i, inv, nq); q = i - r * nq + qf;
-            const unsigned* T = s_tile8 + (r + 3) * FT_WORDS + q;
-            const unsigned C = T[0];
-            const unsigned E = __funnelshift_r(C, T[1], 24), W = __funnelshift_r(T[-1], C, 8);
-            const unsigned aN = __vabsdiffu4(T[3 * FT_WORDS], C), aS = __vabsdiffu4(T[-3 * FT_WORDS], C);
-            const unsigned aE = __vabsdiffu4(E, C), aW = __vabsdiffu4(W, C);
-            const unsigned mN = aN | ((aN & 0x7f7f7f7fu) + K), mS = aS | ((aS & 0x7f7f7f7fu) + K);
-            const unsigned mE = aE | ((aE & 0x7f7f7f7fu) + K), mW = aW | ((aW & 0x7f7f7f7fu) + K);
-            const unsigned ok = (mN | mS) & (mE | mW) & 0x80808080u;
-            f0 = (ok & 0x0000FFFFu) != 0; f1 = (ok & 0xFFFF0000u) != 0;
-          }
+          // no branch around the body: out-of-range threads redo the last quad and are masked out
+          const bool in = i0 + tid < nquads;
+          const int i = min(i0 + tid, nquads - 1);
+          const int r = (int)__umulhi((unsigned)i, inv), q = i - r * nq + qf;   // nq >= 2 (host), so the magic is exact
+          const unsigned* T = s_tile8 + (r + 3) * FT_WORDS + q;
+          const unsigned C = T[0];
+          const unsigned E = __funnelshift_r(C, T[1], 24), W = __funnelshift_r(T[-1], C, 8);
+          const unsigned aN = __vabsdiffu4(T[3 * FT_WORDS], C), aS = __vabsdiffu4(T[-3 * FT_WORDS], C);
+          const unsigned aE = __vabsdiffu4(E, C), aW = __vabsdiffu4(W, C);
+          const unsigned mN = aN | ((aN & 0x7f7f7f7fu) + K), mS = aS | ((aS & 0x7f7f7f7fu) + K);
+          const unsigned mE = aE | ((aE & 0x7f7f7f7fu) + K), mW = aW | ((aW & 0x7f7f7f7fu) + K);
+          const unsigned ok = (mN | mS) & (mE | mW) & 0x80808080u;
+          const bool f0 = in && (ok & 0x0000FFFFu) != 0, f1 = in && (ok & 0xFFFF0000u) != 0;
           const unsigned short e = (unsigned short)((r << 7) | (2 * q - 2));   // pair column = (tile column - 4) / 2
           warp_append(f0, e, seg, cnt, lt);
           warp_append(f1, (unsigned short)(e + 1), seg, cnt, lt);
         }
-        if (lane == 0) s_pcnt[wid] = cnt;
+        npairs = cnt;
       }
-      __syncthreads();
+      __syncwarp();   // each warp consumes only the list it wrote: no CTA barrier between 2a and 2b
 
-      // ---- 2b: score network on the listed pairs, bytes widened on the fly ----
+      // ---- 2b: score network on the warp's own pairs, bytes widened on the fly ----
+      int ncorn = 0;
       {
-        const int pc4[4] = {s_pcnt[0], s_pcnt[1], s_pcnt[2], s_pcnt[3]};
-        const int np = pc4[0] + pc4[1] + pc4[2] + pc4[3];
+        const unsigned short* pl = s_plist + wid * pcap;
         unsigned short* seg = s_clist + wid * ccap;
-        int cnt = 0;
-        for (int i0 = 0; i0 < np; i0 += 128) {
-          const int i = i0 + tid;
-          bool k0 = false, k1 = false;
-          int r = 0, px = 0;
-          if (i < np) {
-            const int e = seg_fetch(s_plist, pcap, pc4, i);
-            r = e >> 7;
-            const int pc = e & 127;
-            px = 4 + 2 * pc - cx0;
-            const unsigned char* B = tile + (r + 3) * FT_PITCH + 4 + 2 * pc;
+        for (int j0 = 0; j0 < npairs; j0 += 32) {
+          const bool in = j0 + lane < npairs;
+          const int e = pl[min(j0 + lane, npairs - 1)];
+          const int r = e >> 7, pc = e & 127;
+          const int px = 4 + 2 * pc - cx0;
+          const unsigned char* B = tile + (r + 3) * FT_PITCH + 4 + 2 * pc;
 #define H16(dy, dx) ((unsigned)*reinterpret_cast<const unsigned short*>(B + (dy) * FT_PITCH + (dx)))
-            unsigned ring[16];
-            {
-              const unsigned a = H16(3, -2), b = H16(3, 0), c = H16(3, 2);
-              ring[15] = widen_odd(a, b); ring[0] = widen_even(b); ring[1] = widen_odd(b, c);
-            }
-            ring[2] = widen_even(H16(2, 2)); ring[14] = widen_even(H16(2, -2));
-            ring[3] = widen_odd(H16(1, 2), H16(1, 4)); ring[13] = widen_odd(H16(1, -4), H16(1, -2));
-            unsigned ctr;
-            {
-              const unsigned m4 = H16(0, -4), m2 = H16(0, -2), c = H16(0, 0), p2 = H16(0, 2), p4 = H16(0, 4);
-              ring[4] = widen_odd(p2, p4); ring[12] = widen_odd(m4, m2); ctr = widen_even(c);
-            }
-            ring[5] = widen_odd(H16(-1, 2), H16(-1, 4)); ring[11] = widen_odd(H16(-1, -4), H16(-1, -2));
-            ring[6] = widen_even(H16(-2, 2)); ring[10] = widen_even(H16(-2, -2));
-            {
-              const unsigned a = H16(-3, -2), b = H16(-3, 0), c = H16(-3, 2);
-              ring[9] = widen_odd(a, b); ring[8] = widen_even(b); ring[7] = widen_odd(b, c);
-            }
-#undef H16
-            unsigned A, Bx;
-            arc_extremes(ctr, ring, A, Bx);
-            const int s0 = max((int)(A & 0xFFFFu) - 257, 255 - (int)(Bx & 0xFFFFu));
-            const int s1 = max((int)(A >> 16) - 257, 255 - (int)(Bx >> 16));
-            unsigned char* q = s_score + (r + 1) * sp + px + 4;
-            k0 = px >= 0 && px < dw && s0 >= cur_th;
-            k1 = px + 1 >= 0 && px + 1 < dw && s1 >= cur_th;
-            if (k0) q[0] = (unsigned char)s0;
-            if (k1) q[1] = (unsigned char)s1;
+          unsigned ring[16];
+          {
+            const unsigned a = H16(3, -2), b = H16(3, 0), c = H16(3, 2);
+            ring[15] = widen_odd(a, b); ring[0] = widen_even(b); ring[1] = widen_odd(b, c);
           }
-          warp_append(k0, (unsigned short)((r << 7) | px), seg, cnt, lt);
-          warp_append(k1, (unsigned short)((r << 7) | (px + 1)), seg, cnt, lt);
+          ring[2] = widen_even(H16(2, 2)); ring[14] = widen_even(H16(2, -2));
+          ring[3] = widen_odd(H16(1, 2), H16(1, 4)); ring[13] = widen_odd(H16(1, -4), H16(1, -2));
+          unsigned ctr;
+          {
+            const unsigned m4 = H16(0, -4), m2 = H16(0, -2), c = H16(0, 0), p2 = H16(0, 2), p4 = H16(0, 4);
+            ring[4] = widen_odd(p2, p4); ring[12] = widen_odd(m4, m2); ctr = widen_even(c);
+          }
+          ring[5] = widen_odd(H16(-1, 2), H16(-1, 4)); ring[11] = widen_odd(H16(-1, -4), H16(-1, -2));
+          ring[6] = widen_even(H16(-2, 2)); ring[10] = widen_even(H16(-2, -2));
+          {
+            const unsigned a = H16(-3, -2), b = H16(-3, 0), c = H16(-3, 2);
+            ring[9] = widen_odd(a, b); ring[8] = widen_even(b); ring[7] = widen_odd(b, c);
+          }
+#undef H16
+          unsigned A, Bx;
+          arc_extremes(ctr, ring, A, Bx);
+          const int s0 = max((int)(A & 0xFFFFu) - 257, 255 - (int)(Bx & 0xFFFFu));
+          const int s1 = max((int)(A >> 16) - 257, 255 - (int)(Bx >> 16));
+          unsigned char* q = s_score + (r + 1) * sp + px + 4;
+          const bool k0 = in && px >= 0 && px < dw && s0 >= cur_th;
+          const bool k1 = in && px + 1 >= 0 && px + 1 < dw && s1 >= cur_th;
+          if (k0) q[0] = (unsigned char)s0;
+          if (k1) q[1] = (unsigned char)s1;
+          warp_append(k0, (unsigned short)((r << 7) | px), seg, ncorn, lt);
+          warp_append(k1, (unsigned short)((r << 7) | (px + 1)), seg, ncorn, lt);
         }
-        if (lane == 0) s_ccnt[wid] = cnt;
       }
-      __syncthreads();
+      __syncthreads();   // all scores of the cell are in place
 
-      // ---- 3: NMS over the listed corners ----
-      const int cc4[4] = {s_ccnt[0], s_ccnt[1], s_ccnt[2], s_ccnt[3]};
-      const int nc = cc4[0] + cc4[1] + cc4[2] + cc4[3];
-      for (int i = tid; i < nc; i += 128) {
-        const int e = seg_fetch(s_clist, ccap, cc4, i);
+      // ---- 3: NMS over the warp's own corners ----
+      const unsigned short* cl = s_clist + wid * ccap;
+      for (int j = lane; j < ncorn; j += 32) {
+        const int e = cl[j];
         const int r = e >> 7, px = e & 127;
         const unsigned char* q = s_score + (r + 1) * sp + px + 4;
         const int s = q[0];
@@ -466,8 +457,8 @@ __global__ void __launch_bounds__(128) k_fast_persist(const __grid_constant__ Fa
       }
       const bool done = __syncthreads_or(s_nlist > 0) || pass == 1 || P.min_th == P.ini_th;
       // clear exactly the scores this pass wrote (all NMS reads are behind the barrier above)
-      for (int i = tid; i < nc; i += 128) {
-        const int e = seg_fetch(s_clist, ccap, cc4, i);
+      for (int j = lane; j < ncorn; j += 32) {
+        const int e = cl[j];
         s_score[((e >> 7) + 1) * sp + (e & 127) + 4] = 0;
       }
       if (done) break;
@@ -507,7 +498,8 @@ int build_fast_recs(const ExtractorGeom& g, std::vector<int4>& recs) {
         if (dw <= 0 || dh <= 0) continue;
         const int pxo = (ROW_LEAD + x0 - 4) & ~15;            // plane column of tile column 0
         const int cx0 = ROW_LEAD + x0 - pxo;                  // 4..19
-        const int qf = cx0 >> 2, ql = (cx0 + dw - 1) >> 2, nq = ql - qf + 1;
+        const int qf = cx0 >> 2, ql = (cx0 + dw - 1) >> 2;
+        const int nq = std::max(ql - qf + 1, 2);   // >= 2 keeps the division magic exact; a surplus quad only holds masked pixels
         const int sp = (((dw + 5 + 3) >> 2) | 1) << 2;
         const unsigned inv = 0xFFFFFFFFu / (unsigned)nq + 1u;
         recs.push_back(make_int4(l | (cx0 << 8) | (qf << 16) | (nq << 24), x0 | (y0 << 16), dw | (dh << 16), (int)inv));
