@@ -314,14 +314,13 @@ __device__ __forceinline__ unsigned widen_odd(unsigned lo, unsigned hi) { return
 __global__ void __launch_bounds__(128) k_fast_persist(const __grid_constant__ FastMaps maps, const FastParams P) {
   extern __shared__ unsigned char smem_raw[];
   __shared__ uint64_t s_bar[2];
-  __shared__ int s_pcnt[4], s_ccnt[4], s_nlist, s_base, s_next[2];
+  __shared__ int s_next[2];
 
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
   unsigned char*  s_tiles = smem;                                              // 2 x tile_bytes
-  unsigned char*  s_score = smem + 2 * P.tile_bytes;
-  unsigned short* s_plist = reinterpret_cast<unsigned short*>(s_score + P.score_bytes);
+  unsigned char*  s_scores = smem + 2 * P.tile_bytes;                           // 2 x score_bytes (items alternate)
+  unsigned short* s_plist = reinterpret_cast<unsigned short*>(s_scores + 2 * P.score_bytes);
   unsigned short* s_clist = s_plist + 4 * P.pcap;
-  unsigned*       s_list  = reinterpret_cast<unsigned*>(s_clist + 4 * P.ccap);
 
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const unsigned lt = (1u << lane) - 1u;
@@ -332,9 +331,8 @@ __global__ void __launch_bounds__(128) k_fast_persist(const __grid_constant__ Fa
   if (tid == 0) {
     mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1);
     mbar_fence_init();
-    s_nlist = 0;
   }
-  for (int i = tid; i < (P.score_bytes >> 2); i += 128) reinterpret_cast<unsigned*>(s_score)[i] = 0;
+  for (int i = tid; i < (P.score_bytes >> 1); i += 128) reinterpret_cast<unsigned*>(s_scores)[i] = 0;
   __syncthreads();
 
   auto issue = [&](int work, int buf) {  // one thread
@@ -364,6 +362,10 @@ __global__ void __launch_bounds__(128) k_fast_persist(const __grid_constant__ Fa
     const unsigned inv = (unsigned)c0.w;
     const int sp = c1.y;
     const unsigned char* tile = s_tiles + buf * P.tile_bytes;
+    // score tile of this item; the other one is still being cleared by slower warps of the previous item
+    unsigned char* s_score = s_scores + buf * P.score_bytes;
+    unsigned* out = P.cand + (size_t)img * P.cand_img_stride + (unsigned)c1.z;
+    int* out_count = P.cand_count + img * P.nlevels + level;
     const unsigned* s_tile8 = reinterpret_cast<const unsigned*>(tile);
     mbar_wait(&s_bar[buf], (unsigned)((it >> 1) & 1));
 
@@ -444,18 +446,31 @@ __global__ void __launch_bounds__(128) k_fast_persist(const __grid_constant__ Fa
       }
       __syncthreads();   // all scores of the cell are in place
 
-      // ---- 3: NMS over the warp's own corners ----
+      // ---- 3: NMS over the warp's own corners; survivors go straight to the level's candidate list
+      // (one global atomicAdd per warp and 32 corners): whatever a pass finds is final, because a
+      // pass-0 survivor means the cell keeps its iniThFAST result and pass 1 only runs on empty cells
       const unsigned short* cl = s_clist + wid * ccap;
-      for (int j = lane; j < ncorn; j += 32) {
-        const int e = cl[j];
+      int found = 0;
+      for (int j0 = 0; j0 < ncorn; j0 += 32) {
+        const bool in = j0 + lane < ncorn;
+        const int e = cl[min(j0 + lane, ncorn - 1)];
         const int r = e >> 7, px = e & 127;
         const unsigned char* q = s_score + (r + 1) * sp + px + 4;
         const int s = q[0];
-        const bool lm = s > q[-1] && s > q[1] && s > q[-sp - 1] && s > q[-sp] && s > q[-sp + 1] &&
+        const bool lm = in && s > q[-1] && s > q[1] && s > q[-sp - 1] && s > q[-sp] && s > q[-sp + 1] &&
                         s > q[sp - 1] && s > q[sp] && s > q[sp + 1];
-        if (lm) s_list[atomicAdd(&s_nlist, 1)] = pack_cand(x0 + px - FAST_BORDER, y0 + r - FAST_BORDER, s);
+        const unsigned bal = __ballot_sync(0xffffffffu, lm);
+        if (bal) {
+          const int n = __popc(bal);
+          int base = 0;
+          if (lane == 0) base = atomicAdd(out_count, n);
+          base = __shfl_sync(0xffffffffu, base, 0);
+          if (base + n > c1.w) { if (lane == 0) atomicOr(P.flags, FLAG_CAND_OVERFLOW); }
+          else if (lm) out[base + __popc(bal & lt)] = pack_cand(x0 + px - FAST_BORDER, y0 + r - FAST_BORDER, s);
+          found += n;
+        }
       }
-      const bool done = __syncthreads_or(s_nlist > 0) || pass == 1 || P.min_th == P.ini_th;
+      const bool done = __syncthreads_or(found > 0) || pass == 1 || P.min_th == P.ini_th;
       // clear exactly the scores this pass wrote (all NMS reads are behind the barrier above)
       for (int j = lane; j < ncorn; j += 32) {
         const int e = cl[j];
@@ -465,21 +480,6 @@ __global__ void __launch_bounds__(128) k_fast_persist(const __grid_constant__ Fa
       __syncthreads();
     }
 
-    // ---- emit: every listed survivor is a keypoint of this cell at the threshold that produced it ----
-    const int nl = s_nlist;
-    if (nl > 0) {
-      if (tid == 0) s_base = atomicAdd(&P.cand_count[img * P.nlevels + level], nl);
-      __syncthreads();
-      const int base = s_base;
-      if (base + nl > c1.w) {
-        if (tid == 0) atomicOr(P.flags, FLAG_CAND_OVERFLOW);
-      } else {
-        unsigned* out = P.cand + (size_t)img * P.cand_img_stride + (unsigned)c1.z + base;
-        for (int n = tid; n < nl; n += 128) out[n] = s_list[n];
-      }
-    }
-    __syncthreads();  // lists, counters and this tile buffer are free again
-    if (tid == 0) s_nlist = 0;
     w = s_next[buf ^ 1];
     if (w >= P.total_work) break;
   }
@@ -572,8 +572,7 @@ void launch_fast_persist(const ExtractorGeom& g, const FastMaps& maps, const int
   const int maxquads = ((g.max_cell_w + 3) / 4 + 1) * g.max_cell_h;
   P.pcap = 64 * ((maxquads + 127) / 128);
   P.ccap = 64 * ((2 * maxquads + 127) / 128);
-  const int list_bytes = 4 * ((g.max_cell_w + 1) / 2) * ((g.max_cell_h + 1) / 2);
-  const int smem = 128 + 2 * P.tile_bytes + P.score_bytes + 2 * 4 * (P.pcap + P.ccap) + list_bytes;
+  const int smem = 128 + 2 * P.tile_bytes + 2 * P.score_bytes + 2 * 4 * (P.pcap + P.ccap);
   static int attr = 48 * 1024, per_sm = 0, attr_smem = -1, n_sm = 0;
   if (smem > attr) {
     cudaFuncSetAttribute(k_fast_persist, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
