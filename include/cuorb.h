@@ -286,6 +286,83 @@ int cuorb_search_by_bow(int device, int n1, const uint8_t* desc1, const uint8_t*
                         const int32_t* node_idx1, const int32_t* node_off2, const int32_t* node_idx2,
                         int mode, float nnratio, int check_orientation, int32_t* match12_out);
 
+/* ---- the remaining ORBmatcher searches, pinhole / NLeft == -1 branches ----
+ * The caller keeps what needs Sophus / Eigen / MapPoint state (pose transform, camera projection,
+ * distance-invariance range, viewing-angle test, MapPoint::PredictScale) and passes one SoA entry per
+ * query: active (all of those gates passed), the projected pixel (u, v), the predicted pyramid level
+ * and the MapPoint descriptor.  The window search, the per-candidate gates, the reference's visiting
+ * order and first/last-wins tie rules, the order-dependent binding and the rotation histogram run in
+ * the library.  Views: keys_un = mvKeysUn, u_right = mvuRight; the meaning of bound_with_obs is stated
+ * per function.  Host arrays throughout. */
+
+/* int ORBmatcher::SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const std::set<MapPoint*>&
+ * sAlreadyFound, const float th, const int ORBdist)  (include/ORBmatcher.h:60-66,
+ * src/ORBmatcher.cc:1910-2036).  One entry per pKF->GetMapPointMatches()[i]: active = pMP && !isBad()
+ * && !sAlreadyFound.count(pMP) && minDistance <= dist3D <= maxDistance; kf_angle = pKF->mvKeysUn[i].angle.
+ * cur->bound_with_obs[i2] = CurrentFrame.mvpMapPoints[i2] != NULL on entry.  The image-bounds test
+ * (:1937-1942) is applied here.  Outputs as cuorb_search_by_projection_frame.  Returns nmatches. */
+int cuorb_search_by_projection_reloc(int device, const cuorb_frame_view* cur, int n_points,
+                                     const uint8_t* mp_desc, const float* u, const float* v,
+                                     const int32_t* level, const float* kf_angle, const uint8_t* active,
+                                     float th, int orb_dist, int check_orientation, int32_t* best_idx_out,
+                                     int32_t* rot_bin_out, int32_t* keep_bins_out);
+
+/* int ORBmatcher::SearchByProjection(KeyFrame* pKF, Sophus::Sim3f& Scw, const std::vector<MapPoint*>&
+ * vpPoints, std::vector<MapPoint*>& vpMatched, int th, float ratioHamming)  (include/ORBmatcher.h:70-77,
+ * src/ORBmatcher.cc:423-538) and its overload that also fills vpMatchedKF (include/ORBmatcher.h:81-90,
+ * src/ORBmatcher.cc:540-664; the search is the same, the caller copies vpPointsKFs[i] beside the match).
+ * kf->bound_with_obs[idx] = vpMatched[idx] != NULL on entry.  best_idx_out[i] = KeyFrame feature now
+ * matched to point i (the caller replays vpMatched[best] = vpPoints[i]) or -1.  Returns nmatches. */
+int cuorb_search_by_projection_sim3(int device, const cuorb_frame_view* kf, int n_points,
+                                    const uint8_t* mp_desc, const float* u, const float* v,
+                                    const int32_t* level, const uint8_t* active, int th, float ratio_hamming,
+                                    int32_t* best_idx_out);
+
+/* int ORBmatcher::Fuse(KeyFrame* pKF, const std::vector<MapPoint*>& vpMapPoints, const float th, const
+ * bool bRight = false)  (include/ORBmatcher.h:129-134, src/ORBmatcher.cc:1149-1328; check_reprojection
+ * = 1: the 5.99 / 7.8 chi-square gates with inv_level_sigma2 = pKF->mvInvLevelSigma2 and ur = uv(0) -
+ * bf * invz, :1208) and int ORBmatcher::Fuse(KeyFrame* pKF, Sophus::Sim3f& Scw, const
+ * std::vector<MapPoint*>& vpPoints, float th, std::vector<MapPoint*>& vpReplacePoint)
+ * (include/ORBmatcher.h:137-143, src/ORBmatcher.cc:1330-1452; check_reprojection = 0, ur unused).
+ * best_idx_out[i] = the KeyFrame feature MapPoint i fuses into (bestDist <= TH_LOW) or -1; the caller
+ * performs the Replace / AddObservation / AddMapPoint bookkeeping (:1301-1318).  Returns nFused. */
+int cuorb_fuse(int device, const cuorb_frame_view* kf, const float* inv_level_sigma2, int n_points,
+               const uint8_t* mp_desc, const float* u, const float* v, const float* ur, const int32_t* level,
+               const uint8_t* active, float th, int check_reprojection, int32_t* best_idx_out);
+
+/* int ORBmatcher::SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12, const
+ * Sophus::Sim3f& S12, const float th)  (include/ORBmatcher.h:120-126, src/ORBmatcher.cc:1454-1682).
+ * Direction 1->2 has kf1->n entries (MapPoints of pKF1 projected into pKF2: mp_desc1, u12, v12,
+ * level12, active1 = pMP && !vbAlreadyMatched1 && !isBad() && the geometric gates), direction 2->1 has
+ * kf2->n entries.  match12_out[i1] = feature of pKF2 when both directions agree (:1667-1679), else -1.
+ * Returns nFound. */
+int cuorb_search_by_sim3(int device, const cuorb_frame_view* kf1, const cuorb_frame_view* kf2,
+                         const uint8_t* mp_desc1, const float* u12, const float* v12, const int32_t* level12,
+                         const uint8_t* active1, const uint8_t* mp_desc2, const float* u21, const float* v21,
+                         const int32_t* level21, const uint8_t* active2, float th, int32_t* match12_out);
+
+/* int ORBmatcher::SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched,
+ * std::vector<int>& vnMatches12, int windowSize = 10)  (include/ORBmatcher.h:99-105,
+ * src/ORBmatcher.cc:666-782).  prev_matched = vbPrevMatched as f1->n (x, y) pairs, updated in place
+ * (:771-776); matches12_out = vnMatches12 (f1->n).  Returns nmatches. */
+int cuorb_search_for_initialization(int device, const cuorb_frame_view* f1, const cuorb_frame_view* f2,
+                                    float* prev_matched, int window_size, float nnratio,
+                                    int check_orientation, int32_t* matches12_out);
+
+/* int ORBmatcher::SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<std::pair<size_t,
+ * size_t>>& vMatchedPairs, const bool bOnlyStereo, const bool bCoarse = false)
+ * (include/ORBmatcher.h:108-114, src/ORBmatcher.cc:916-1147; mpCamera2 == NULL).  The common nodes of the
+ * two FeatureVectors are passed as for cuorb_search_by_bow.  kfX->bound_with_obs[idx] =
+ * pKFX->GetMapPoint(idx) != NULL; F12 = K1^-T [t12]x R12 K2^-1 row-major and epipole = project(T2w * Cw1)
+ * come from the caller (:927-939, src/CameraModels/Pinhole.cpp:153-156); level_sigma2_2 =
+ * pKF2->mvLevelSigma2.  match12_out[idx1] = idx2 or -1 after the rotation cut (the caller builds
+ * vMatchedPairs from it, :1133-1144).  Returns nmatches. */
+int cuorb_search_for_triangulation(int device, const cuorb_frame_view* kf1, const cuorb_frame_view* kf2,
+                                   int n_nodes, const int32_t* node_off1, const int32_t* node_idx1,
+                                   const int32_t* node_off2, const int32_t* node_idx2, const float* F12,
+                                   const float* epipole, const float* level_sigma2_2, int only_stereo,
+                                   int coarse, int check_orientation, int32_t* match12_out);
+
 /* ---- dense all-pairs Hamming ---- */
 
 /* cv::BFMatcher(cv::NORM_HAMMING).knnMatch(query, train, matches, 2) as Frame::ComputeStereoFishEyeMatches

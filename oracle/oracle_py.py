@@ -36,7 +36,7 @@ class FrameViewC(C.Structure):
 
 def build(force: bool = False) -> str:
     srcs = [os.path.join(_HERE, f) for f in
-            ("orb_oracle.cpp", "orb_oracle_match.cpp", "orb_oracle_capi.cpp", "preproc_oracle.cpp", "frameglue_oracle.cpp", "bfmatch_oracle.cpp", "bow_oracle.cpp", "orb_oracle.hpp")]
+            ("orb_oracle.cpp", "orb_oracle_match.cpp", "orb_oracle_capi.cpp", "preproc_oracle.cpp", "frameglue_oracle.cpp", "bfmatch_oracle.cpp", "bow_oracle.cpp", "search_oracle.cpp", "orb_oracle.hpp")]
     stale = (not os.path.exists(_LIB_PATH)) or any(
         os.path.getmtime(s) > os.path.getmtime(_LIB_PATH) for s in srcs)
     if force or stale:
@@ -100,6 +100,13 @@ def lib() -> C.CDLL:
         L.oo_search_by_bow.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                        C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
                                        C.c_float, C.c_int, C.c_void_p]
+        FV = C.POINTER(FrameViewC)
+        L.oo_search_by_projection_reloc.argtypes = [FV, C.c_int] + [C.c_void_p] * 6 + [C.c_float, C.c_int, C.c_int] + [C.c_void_p] * 3
+        L.oo_search_by_projection_sim3.argtypes = [FV, C.c_int] + [C.c_void_p] * 5 + [C.c_int, C.c_float, C.c_void_p]
+        L.oo_fuse.argtypes = [FV, C.c_void_p, C.c_int] + [C.c_void_p] * 6 + [C.c_float, C.c_int, C.c_void_p]
+        L.oo_search_by_sim3.argtypes = [FV, FV] + [C.c_void_p] * 10 + [C.c_float, C.c_void_p]
+        L.oo_search_for_initialization.argtypes = [FV, FV, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p]
+        L.oo_search_for_triangulation.argtypes = [FV, FV, C.c_int] + [C.c_void_p] * 7 + [C.c_int, C.c_int, C.c_int, C.c_void_p]
         _lib = L
     return _lib
 
@@ -415,3 +422,56 @@ def bench_stereo(left, right, mb, mbf, n_threads, nfeatures=1000, scale=1.2, nle
     sec = lib().oo_bench_stereo(nfeatures, scale, nlevels, ini, mn, _p(left), _p(right), n, w, h, mb,
                                 mbf, n_threads, C.byref(k), C.byref(m))
     return sec, k.value, m.value
+
+
+# ---- the remaining ORBmatcher searches (search_oracle.cpp) ----
+def _f32(a): return None if a is None else np.ascontiguousarray(a, np.float32)
+def _i32(a): return None if a is None else np.ascontiguousarray(a, np.int32)
+def _u8(a): return None if a is None else np.ascontiguousarray(a, np.uint8)
+
+
+def search_by_projection_reloc(fv, mp_desc, u, v, level, kf_angle, active, th, orb_dist, check_ori=True):
+    n = len(u)
+    arrs = [_u8(mp_desc), _f32(u), _f32(v), _i32(level), _f32(kf_angle), _u8(active)]
+    best = np.empty(n, np.int32); rot = np.empty(n, np.int32); keep = np.empty(3, np.int32)
+    r = lib().oo_search_by_projection_reloc(C.byref(fv), n, *[_p(a) for a in arrs], th, int(orb_dist), int(check_ori),
+                                            _p(best), _p(rot), _p(keep))
+    return r, best, rot, keep
+
+
+def search_by_projection_sim3(fv, mp_desc, u, v, level, active, th, ratio_hamming):
+    n = len(u)
+    arrs = [_u8(mp_desc), _f32(u), _f32(v), _i32(level), _u8(active)]
+    best = np.empty(n, np.int32)
+    r = lib().oo_search_by_projection_sim3(C.byref(fv), n, *[_p(a) for a in arrs], int(th), ratio_hamming, _p(best))
+    return r, best
+
+
+def fuse(fv, inv_sigma2, mp_desc, u, v, ur, level, active, th, check_reprojection):
+    n = len(u)
+    arrs = [_u8(mp_desc), _f32(u), _f32(v), _f32(ur), _i32(level), _u8(active)]
+    best = np.empty(n, np.int32)
+    r = lib().oo_fuse(C.byref(fv), _p(_f32(inv_sigma2)), n, *[_p(a) for a in arrs], th, int(check_reprojection), _p(best))
+    return r, best
+
+
+def search_by_sim3(fv1, fv2, d1, u12, v12, l12, a1, d2, u21, v21, l21, a2, th):
+    arrs = [_u8(d1), _f32(u12), _f32(v12), _i32(l12), _u8(a1), _u8(d2), _f32(u21), _f32(v21), _i32(l21), _u8(a2)]
+    m12 = np.empty(max(fv1.n, 1), np.int32)
+    r = lib().oo_search_by_sim3(C.byref(fv1), C.byref(fv2), *[_p(a) for a in arrs], th, _p(m12))
+    return r, m12[:fv1.n]
+
+
+def search_for_initialization(fv1, fv2, prev_matched, window, nnratio, check_ori=True):
+    pm = np.ascontiguousarray(prev_matched, np.float32).copy()
+    m12 = np.empty(max(fv1.n, 1), np.int32)
+    r = lib().oo_search_for_initialization(C.byref(fv1), C.byref(fv2), _p(pm), int(window), nnratio, int(check_ori), _p(m12))
+    return r, m12[:fv1.n], pm
+
+
+def search_for_triangulation(fv1, fv2, off1, idx1, off2, idx2, F12, ep, sigma2_2, only_stereo, coarse, check_ori=True):
+    arrs = [_i32(off1), _i32(idx1), _i32(off2), _i32(idx2), _f32(F12), _f32(ep), _f32(sigma2_2)]
+    m12 = np.empty(max(fv1.n, 1), np.int32)
+    r = lib().oo_search_for_triangulation(C.byref(fv1), C.byref(fv2), len(off1) - 1, *[_p(a) for a in arrs],
+                                          int(only_stereo), int(coarse), int(check_ori), _p(m12))
+    return r, m12[:fv1.n]

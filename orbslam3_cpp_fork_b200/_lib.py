@@ -100,6 +100,18 @@ SIGNATURES = {
     "cuorb_search_by_bow": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
                                       C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                       C.c_int, C.c_float, C.c_int, C.c_void_p]),
+    "cuorb_search_by_projection_reloc": (C.c_int, [C.c_int, C.POINTER(FrameView), C.c_int] + [C.c_void_p] * 6 +
+                                         [C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "cuorb_search_by_projection_sim3": (C.c_int, [C.c_int, C.POINTER(FrameView), C.c_int] + [C.c_void_p] * 5 +
+                                        [C.c_int, C.c_float, C.c_void_p]),
+    "cuorb_fuse": (C.c_int, [C.c_int, C.POINTER(FrameView), C.c_void_p, C.c_int] + [C.c_void_p] * 6 +
+                   [C.c_float, C.c_int, C.c_void_p]),
+    "cuorb_search_by_sim3": (C.c_int, [C.c_int, C.POINTER(FrameView), C.POINTER(FrameView)] + [C.c_void_p] * 10 +
+                             [C.c_float, C.c_void_p]),
+    "cuorb_search_for_initialization": (C.c_int, [C.c_int, C.POINTER(FrameView), C.POINTER(FrameView), C.c_void_p,
+                                                  C.c_int, C.c_float, C.c_int, C.c_void_p]),
+    "cuorb_search_for_triangulation": (C.c_int, [C.c_int, C.POINTER(FrameView), C.POINTER(FrameView), C.c_int] +
+                                       [C.c_void_p] * 7 + [C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "cuorb_kernel_launch_count": (C.c_uint64, []),
     "cuorb_set_profiling": (C.c_int, [C.c_void_p, C.c_int]),
     "cuorb_stage_ms": (C.c_int, [C.c_void_p, C.c_void_p]),

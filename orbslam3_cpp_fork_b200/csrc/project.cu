@@ -18,20 +18,9 @@
 #include <cmath>
 #include <mutex>
 
-#include "common.cuh"
+#include "project.cuh"
 
 namespace cuorb {
-
-struct ProjFrame {  // device SoA of the frame members the searches read
-  int n;
-  const float *x, *y, *uright;
-  const int *octave;
-  const short *cellx, *celly;  // PosInGrid result, -1 if outside the grid
-  const uint8_t* desc;
-  const uint8_t* blocked0;     // mvpMapPoints[i] && Observations() > 0 on entry
-  float minX, minY, maxX, maxY, gwinv, ghinv, mbf;
-  float scale[MAX_LEVELS];
-};
 
 struct ProjQuery {
   int n;
@@ -44,15 +33,6 @@ struct ProjQuery {
   float th, thFar, nnratio;
   int far_points, forward, backward;
 };
-
-constexpr int FRAME_GRID_ROWS = 48, FRAME_GRID_COLS = 64, TH_HIGH_P = 100;
-constexpr int NO_BINDER = 0x7fffffff;
-
-__device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, const uint4* b) {
-  const uint4 b0 = b[0], b1 = b[1];
-  return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
-         __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
-}
 
 // grid: ceil(n/8), block 256 (warp per query point)
 __global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, ProjQuery Q,
@@ -147,11 +127,6 @@ __global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, ProjQuery Q,
   }
 }
 
-__global__ void k_fill(int* p, int n, int v) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) p[i] = v;
-}
-
 // grid: ceil(n/256)
 __global__ void k_hamming_pairs(const uint8_t* a, const uint8_t* b, const int* ia, const int* ib, int n, int* out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -162,33 +137,7 @@ __global__ void k_hamming_pairs(const uint8_t* a, const uint8_t* b, const int* i
 }
 
 // ---- host side ----
-struct Arena {  // grow-only device scratch per thread
-  void* p = nullptr; size_t cap = 0, used = 0; int device = -1;
-  int reserve(int dev, size_t bytes) {
-    if (dev != device || bytes > cap) {
-      if (p) { cudaSetDevice(device); cudaFree(p); p = nullptr; cap = 0; }
-      cudaSetDevice(dev);
-      if (cudaMalloc(&p, bytes) != cudaSuccess) { p = nullptr; return -1; }
-      cap = bytes; device = dev;
-    }
-    used = 0;
-    return 0;
-  }
-  template <typename T> T* take(size_t count) {
-    used = (used + 255) & ~(size_t)255;
-    T* r = reinterpret_cast<T*>(static_cast<char*>(p) + used);
-    used += count * sizeof(T);
-    return r;
-  }
-};
-static thread_local Arena t_arena;
-
-template <typename T>
-static T* up(Arena& A, const T* host, size_t count, cudaStream_t st) {
-  T* d = A.take<T>(count);
-  if (host && count) cudaMemcpyAsync(d, host, count * sizeof(T), cudaMemcpyHostToDevice, st);
-  return d;
-}
+thread_local Arena t_arena;
 
 static int run_projection(int device, const cuorb_frame_view* fv, ProjQuery Q, const uint8_t* qdesc,
                           const float* px, const float* py, const float* aux, const int32_t* level,
@@ -199,35 +148,12 @@ static int run_projection(int device, const cuorb_frame_view* fv, ProjQuery Q, c
   for (int i = 0; i < m; i++) result_out[i] = -1;
   if (n <= 0 || m <= 0) return 0;
   CUORB_CUDA_TRY(cudaSetDevice(device));
-  // host-side flattening of the Frame: SoA + PosInGrid (src/Frame.cc:867-877, std::round)
-  std::vector<float> fx(n), fy(n);
-  std::vector<int> foct(n);
-  std::vector<short> cxv(n), cyv(n);
-  std::vector<uint8_t> blk(n, 0);
-  for (int i = 0; i < n; i++) {
-    const cuorb_keypoint& k = fv->keys_un[i];
-    fx[i] = k.x; fy[i] = k.y; foct[i] = k.octave;
-    const int posX = (int)std::round((k.x - fv->min_x) * fv->grid_w_inv);
-    const int posY = (int)std::round((k.y - fv->min_y) * fv->grid_h_inv);
-    const bool in = !(posX < 0 || posX >= FRAME_GRID_COLS || posY < 0 || posY >= FRAME_GRID_ROWS);
-    cxv[i] = in ? (short)posX : (short)-1; cyv[i] = in ? (short)posY : (short)-1;
-    if (fv->bound_with_obs) blk[i] = fv->bound_with_obs[i];
-  }
-  const size_t bytes = (size_t)n * (4 * 4 + 2 * 2 + 32 + 1 + 8) + (size_t)m * (32 + 6 * 4 + 1 + 4) + 64 * 1024;
+  const size_t bytes = frame_bytes(n) + (size_t)m * (32 + 6 * 4 + 1 + 4) + 64 * 1024;
   if (t_arena.reserve(device, bytes) != 0) { set_error("cudaMalloc failed (projection workspace)"); return CUORB_E_CUDA; }
   Arena& A = t_arena;
   cudaStream_t st = cudaStreamPerThread;
   ProjFrame F;
-  F.n = n;
-  F.x = up(A, fx.data(), n, st); F.y = up(A, fy.data(), n, st);
-  F.uright = fv->u_right ? up(A, fv->u_right, n, st) : nullptr;
-  F.octave = up(A, foct.data(), n, st);
-  F.cellx = up(A, cxv.data(), n, st); F.celly = up(A, cyv.data(), n, st);
-  F.desc = up(A, fv->descriptors, (size_t)n * 32, st);
-  F.blocked0 = up(A, blk.data(), n, st);
-  F.minX = fv->min_x; F.minY = fv->min_y; F.maxX = fv->max_x; F.maxY = fv->max_y;
-  F.gwinv = fv->grid_w_inv; F.ghinv = fv->grid_h_inv; F.mbf = fv->mbf;
-  for (int l = 0; l < MAX_LEVELS; l++) F.scale[l] = l < fv->nlevels ? fv->scale_factors[l] : 0.f;
+  upload_frame(A, fv, st, F);
   Q.desc = up(A, qdesc, (size_t)m * 32, st);
   Q.px = up(A, px, m, st); Q.py = up(A, py, m, st);
   Q.aux = aux ? up(A, aux, m, st) : nullptr;

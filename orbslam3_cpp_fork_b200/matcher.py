@@ -47,10 +47,13 @@ class Frame:
         if self.mvuRight is not None:
             self.mvuRight = np.ascontiguousarray(self.mvuRight, np.float32)
 
-    def view(self):
-        """cuorb_frame_view + keepalive (src/Frame.cc:240-257 for the grid constants)."""
+    def view(self, bound=None):
+        """cuorb_frame_view + keepalive (src/Frame.cc:240-257 for the grid constants).  bound: the per-feature
+        "already taken" flags of the search at hand (default: bound to a MapPoint with observations)."""
         f32 = np.float32
-        bound = np.ascontiguousarray(((self.mvpMapPoints >= 0) & (self.mvpHasObs > 0)).astype(np.uint8))
+        if bound is None:
+            bound = (self.mvpMapPoints >= 0) & (self.mvpHasObs > 0)
+        bound = np.ascontiguousarray(np.asarray(bound).astype(np.uint8))
         fv = _lib.FrameView()
         fv.n = self.N
         fv.keys_un = ptr(self.mvKeysUn); fv.descriptors = ptr(self.mDescriptors)
@@ -218,3 +221,93 @@ def SearchByBoW_KF_KF(self, desc1, has_mp1, angle1, featvec1, desc2, has_mp2, an
 
 ORBmatcher.SearchByBoW_KF_F = SearchByBoW_KF_F
 ORBmatcher.SearchByBoW_KF_KF = SearchByBoW_KF_KF
+
+
+# ---- the remaining searches; a KeyFrame is passed as a Frame (same members) ----
+def SearchByProjectionReloc(self, Cur: Frame, mp_desc, u, v, level, kf_angle, active, th, ORBdist):
+    """int SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, sAlreadyFound, th, ORBdist)
+    (src/ORBmatcher.cc:1910-2036).  Binds Cur.mvpMapPoints like the reference; returns (nmatches, best, rot, keep)."""
+    fv, keep = Cur.view(bound=Cur.mvpMapPoints >= 0)
+    n = len(u)
+    arrs = [_c(mp_desc, np.uint8), _c(u, np.float32), _c(v, np.float32), _c(level, np.int32), _c(kf_angle, np.float32),
+            _c(np.asarray(active).astype(np.uint8), np.uint8)]
+    best = np.zeros(n, np.int32); rot = np.zeros(n, np.int32); keepb = np.zeros(3, np.int32)
+    r = check(self._L.cuorb_search_by_projection_reloc(self.device, C.byref(fv), n, *[ptr(a) for a in arrs], th, int(ORBdist),
+                                                       int(self.mbCheckOrientation), ptr(best), ptr(rot), ptr(keepb)))
+    for i in np.nonzero(best >= 0)[0]:
+        Cur.mvpMapPoints[best[i]] = i if (not self.mbCheckOrientation or rot[i] in keepb) else -1
+    return r, best, rot, keepb
+
+
+def SearchByProjectionSim3(self, KF: Frame, vpMatched_set, mp_desc, u, v, level, active, th, ratioHamming):
+    """int SearchByProjection(KeyFrame* pKF, Sim3& Scw, vpPoints, [vpPointsKFs,] vpMatched, [vpMatchedKF,] th,
+    ratioHamming) (src/ORBmatcher.cc:423-538, 540-664).  vpMatched_set[idx] = vpMatched[idx] != NULL on entry."""
+    fv, keep = KF.view(bound=vpMatched_set)
+    n = len(u)
+    arrs = [_c(mp_desc, np.uint8), _c(u, np.float32), _c(v, np.float32), _c(level, np.int32),
+            _c(np.asarray(active).astype(np.uint8), np.uint8)]
+    best = np.zeros(n, np.int32)
+    r = check(self._L.cuorb_search_by_projection_sim3(self.device, C.byref(fv), n, *[ptr(a) for a in arrs], int(th),
+                                                      ratioHamming, ptr(best)))
+    return r, best
+
+
+def Fuse(self, KF: Frame, mvInvLevelSigma2, mp_desc, u, v, ur, level, active, th=3.0, check_reprojection=True):
+    """int Fuse(KeyFrame*, vpMapPoints, th, bRight=false) (src/ORBmatcher.cc:1149-1328; check_reprojection=True) and
+    int Fuse(KeyFrame*, Sim3f&, vpPoints, th, vpReplacePoint) (:1330-1452; check_reprojection=False)."""
+    fv, keep = KF.view()
+    n = len(u)
+    inv = _c(mvInvLevelSigma2, np.float32) if mvInvLevelSigma2 is not None else None
+    arrs = [_c(mp_desc, np.uint8), _c(u, np.float32), _c(v, np.float32), None if ur is None else _c(ur, np.float32),
+            _c(level, np.int32), _c(np.asarray(active).astype(np.uint8), np.uint8)]
+    best = np.zeros(n, np.int32)
+    r = check(self._L.cuorb_fuse(self.device, C.byref(fv), ptr(inv), n, *[ptr(a) for a in arrs], th,
+                                 int(check_reprojection), ptr(best)))
+    return r, best
+
+
+def SearchBySim3(self, KF1: Frame, KF2: Frame, mp_desc1, u12, v12, level12, active1, mp_desc2, u21, v21, level21,
+                 active2, th):
+    """int SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, vpMatches12, S12, th) (src/ORBmatcher.cc:1454-1682)."""
+    fv1, k1 = KF1.view(); fv2, k2 = KF2.view()
+    arrs = [_c(mp_desc1, np.uint8), _c(u12, np.float32), _c(v12, np.float32), _c(level12, np.int32),
+            _c(np.asarray(active1).astype(np.uint8), np.uint8), _c(mp_desc2, np.uint8), _c(u21, np.float32),
+            _c(v21, np.float32), _c(level21, np.int32), _c(np.asarray(active2).astype(np.uint8), np.uint8)]
+    m12 = np.full(max(KF1.N, 1), -1, np.int32)
+    r = check(self._L.cuorb_search_by_sim3(self.device, C.byref(fv1), C.byref(fv2), *[ptr(a) for a in arrs], th, ptr(m12)))
+    return r, m12[:KF1.N]
+
+
+def SearchForInitialization(self, F1: Frame, F2: Frame, vbPrevMatched, windowSize=10):
+    """int SearchForInitialization(Frame& F1, Frame& F2, vbPrevMatched, vnMatches12, windowSize)
+    (src/ORBmatcher.cc:666-782).  vbPrevMatched: f32 [N1, 2], updated in place.  Returns (nmatches, vnMatches12)."""
+    fv1, k1 = F1.view(); fv2, k2 = F2.view()
+    pm = _c(vbPrevMatched, np.float32).reshape(-1, 2).copy()
+    m12 = np.full(max(F1.N, 1), -1, np.int32)
+    r = check(self._L.cuorb_search_for_initialization(self.device, C.byref(fv1), C.byref(fv2), ptr(pm), int(windowSize),
+                                                      self.mfNNratio, int(self.mbCheckOrientation), ptr(m12)))
+    np.asarray(vbPrevMatched)[...] = pm.reshape(np.asarray(vbPrevMatched).shape)
+    return r, m12[:F1.N]
+
+
+def SearchForTriangulation(self, KF1: Frame, KF2: Frame, has_mp1, has_mp2, featvec1, featvec2, F12, epipole,
+                           mvLevelSigma2_2, bOnlyStereo=False, bCoarse=False):
+    """int SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, vMatchedPairs, bOnlyStereo, bCoarse)
+    (src/ORBmatcher.cc:916-1147).  Returns (nmatches, match12); vMatchedPairs = [(i, match12[i]) for match12[i] >= 0]."""
+    fv1, k1 = KF1.view(bound=has_mp1); fv2, k2 = KF2.view(bound=has_mp2)
+    off1, idx1, off2, idx2 = join_feature_vectors(featvec1, featvec2)
+    F12 = _c(np.asarray(F12, np.float32).reshape(9), np.float32); ep = _c(epipole, np.float32)
+    s2 = _c(mvLevelSigma2_2, np.float32)
+    m12 = np.full(max(KF1.N, 1), -1, np.int32)
+    r = check(self._L.cuorb_search_for_triangulation(self.device, C.byref(fv1), C.byref(fv2), len(off1) - 1, ptr(off1),
+                                                     ptr(idx1), ptr(off2), ptr(idx2), ptr(F12), ptr(ep), ptr(s2),
+                                                     int(bOnlyStereo), int(bCoarse), int(self.mbCheckOrientation), ptr(m12)))
+    return r, m12[:KF1.N]
+
+
+ORBmatcher.SearchByProjectionReloc = SearchByProjectionReloc
+ORBmatcher.SearchByProjectionSim3 = SearchByProjectionSim3
+ORBmatcher.Fuse = Fuse
+ORBmatcher.SearchBySim3 = SearchBySim3
+ORBmatcher.SearchForInitialization = SearchForInitialization
+ORBmatcher.SearchForTriangulation = SearchForTriangulation
