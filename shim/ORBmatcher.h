@@ -1,4 +1,4 @@
-// Drop-in for the tracking-time subset of the reference's class ORB_SLAM3::ORBmatcher
+// Drop-in for the reference's class ORB_SLAM3::ORBmatcher (pinhole branches)
 // (include/ORBmatcher.h:35-158) and for Frame::ComputeStereoMatches (include/Frame.h:155,
 // src/Frame.cc:944-1113; BASELINE.json's "SearchStereo").  The methods are templates over the
 // Frame / MapPoint types so the very same header compiles against the reference's real classes
@@ -11,6 +11,7 @@
 #include <map>
 #include <stdexcept>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../include/cuorb.h"
@@ -123,6 +124,159 @@ public:
     return n;
   }
 
+  // ---- the searches outside the tracking path ----
+  // One entry per query MapPoint: what the reference computes with Sophus / Eigen / MapPoint state BEFORE its
+  // candidate loop (pose transform, projection, distance range, viewing angle, PredictScale; the lines are cited
+  // at each method and in INTEGRATION.md), flattened.  Everything after that runs in libcuorb.
+  struct ProjectedPoints {
+    std::vector<uint8_t> active;   // every gate before GetFeaturesInArea passed
+    std::vector<float>   u, v, ur; // projected pixel; ur = uv(0) - bf * invz (Fuse with reprojection gate)
+    std::vector<int32_t> level;    // MapPoint::PredictScale
+    std::vector<float>   angle;    // relocalisation: pKF->mvKeysUn[i].angle
+    std::vector<uint8_t> desc;     // n x 32: MapPoint::GetDescriptor()
+    int size() const { return (int)u.size(); }
+    void skip() { push(false, 0.f, 0.f, 0, nullptr); }
+    void push(bool ok, float u_, float v_, int level_, const unsigned char* d32, float ur_ = 0.f, float angle_ = 0.f) {
+      active.push_back(ok ? 1 : 0); u.push_back(u_); v.push_back(v_); ur.push_back(ur_); level.push_back(level_);
+      angle.push_back(angle_);
+      desc.resize(desc.size() + 32, 0);
+      if (d32) std::memcpy(&desc[desc.size() - 32], d32, 32);
+    }
+  };
+
+  // int SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const std::set<MapPoint*>& sAlreadyFound, const
+  // float th, const int ORBdist)  (include/ORBmatcher.h:60-66, src/ORBmatcher.cc:1910-2036).  P has one entry
+  // per pKF->GetMapPointMatches()[i] (:1927-1955 is the caller's prologue); binds CurrentFrame.mvpMapPoints.
+  template <class FrameT, class MapPointT>
+  int SearchByProjection(FrameT& CurrentFrame, const std::vector<MapPointT*>& vpMPs, const ProjectedPoints& P,
+                         const float th, const int ORBdist) {
+    if (CurrentFrame.Nleft != -1) throw std::runtime_error("ORBmatcher shim: fisheye (Nleft != -1) branch is not built");
+    const int n = P.size();
+    if (n == 0 || CurrentFrame.N == 0) return 0;
+    std::vector<uint8_t> bound(CurrentFrame.N);
+    for (int i = 0; i < CurrentFrame.N; i++) bound[i] = CurrentFrame.mvpMapPoints[i] ? 1 : 0;      // :1974
+    const cuorb_frame_view fv = view_of(CurrentFrame, bound);
+    std::vector<int32_t> best(n), rot(n);
+    int32_t keep[3];
+    const int r = cuorb_search_by_projection_reloc(device_, &fv, n, P.desc.data(), P.u.data(), P.v.data(), P.level.data(),
+                                                   P.angle.data(), P.active.data(), th, ORBdist, mbCheckOrientation ? 1 : 0,
+                                                   best.data(), rot.data(), keep);
+    if (r < 0) throw std::runtime_error(std::string("SearchByProjection (libcuorb): ") + cuorb_last_error());
+    for (int i = 0; i < n; i++) {
+      if (best[i] < 0) continue;
+      const bool kept = !mbCheckOrientation || rot[i] == keep[0] || rot[i] == keep[1] || rot[i] == keep[2];
+      CurrentFrame.mvpMapPoints[best[i]] = kept ? vpMPs[i] : static_cast<MapPointT*>(nullptr);     // :1985, :2027
+    }
+    return r;
+  }
+
+  // int SearchByProjection(KeyFrame* pKF, Sophus::Sim3f& Scw, const std::vector<MapPoint*>& vpPoints,
+  // std::vector<MapPoint*>& vpMatched, int th, float ratioHamming)  (include/ORBmatcher.h:70-77,
+  // src/ORBmatcher.cc:423-538); the overload with vpPointsKFs / vpMatchedKF (:540-664) passes both extra vectors.
+  template <class KeyFrameT, class MapPointT>
+  int SearchByProjection(KeyFrameT* pKF, const ProjectedPoints& P, const std::vector<MapPointT*>& vpPoints,
+                         std::vector<MapPointT*>& vpMatched, int th, float ratioHamming,
+                         const std::vector<KeyFrameT*>* vpPointsKFs = nullptr, std::vector<KeyFrameT*>* vpMatchedKF = nullptr) {
+    const int n = P.size();
+    if (n == 0 || pKF->N == 0) return 0;
+    std::vector<uint8_t> bound(pKF->N);
+    for (int i = 0; i < pKF->N; i++) bound[i] = vpMatched[i] ? 1 : 0;                              // :510
+    const cuorb_frame_view fv = view_of(*pKF, bound);
+    std::vector<int32_t> best(n);
+    const int r = cuorb_search_by_projection_sim3(device_, &fv, n, P.desc.data(), P.u.data(), P.v.data(), P.level.data(),
+                                                  P.active.data(), th, ratioHamming, best.data());
+    if (r < 0) throw std::runtime_error(std::string("SearchByProjection (libcuorb): ") + cuorb_last_error());
+    for (int i = 0; i < n; i++)
+      if (best[i] >= 0) {
+        vpMatched[best[i]] = vpPoints[i];                                                          // :531
+        if (vpPointsKFs && vpMatchedKF) (*vpMatchedKF)[best[i]] = (*vpPointsKFs)[i];               // :656
+      }
+    return r;
+  }
+
+  // int Fuse(KeyFrame* pKF, const std::vector<MapPoint*>& vpMapPoints, const float th, const bool bRight)
+  // (include/ORBmatcher.h:129-134, src/ORBmatcher.cc:1149-1328; checkReprojection = true) and
+  // int Fuse(KeyFrame* pKF, Sophus::Sim3f& Scw, vpPoints, float th, vpReplacePoint)
+  // (include/ORBmatcher.h:137-143, src/ORBmatcher.cc:1330-1452; checkReprojection = false).
+  // bestIdx[i] = pKF feature MapPoint i fuses into, or -1; the Replace / AddObservation / AddMapPoint
+  // bookkeeping (:1301-1318, :1436-1447) stays in the caller's loop over bestIdx.
+  template <class KeyFrameT>
+  int Fuse(KeyFrameT* pKF, const ProjectedPoints& P, const float th, bool checkReprojection, std::vector<int>& bestIdx) {
+    const int n = P.size();
+    bestIdx.assign(n, -1);
+    if (n == 0 || pKF->N == 0) return 0;
+    std::vector<uint8_t> bound(pKF->N, 0);
+    const cuorb_frame_view fv = view_of(*pKF, bound);
+    const int r = cuorb_fuse(device_, &fv, pKF->mvInvLevelSigma2.data(), n, P.desc.data(), P.u.data(), P.v.data(), P.ur.data(),
+                             P.level.data(), P.active.data(), th, checkReprojection ? 1 : 0, bestIdx.data());
+    if (r < 0) throw std::runtime_error(std::string("Fuse (libcuorb): ") + cuorb_last_error());
+    return r;
+  }
+
+  // int SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12, const Sophus::Sim3f& S12,
+  // const float th)  (include/ORBmatcher.h:120-126, src/ORBmatcher.cc:1454-1682).  P12: one entry per feature of pKF1
+  // (its MapPoint projected into pKF2, :1501-1553), P21 the other way (:1586-1634).
+  template <class KeyFrameT, class MapPointT>
+  int SearchBySim3(KeyFrameT* pKF1, KeyFrameT* pKF2, const ProjectedPoints& P12, const ProjectedPoints& P21,
+                   std::vector<MapPointT*>& vpMatches12, const float th) {
+    if (P12.size() != pKF1->N || P21.size() != pKF2->N) throw std::runtime_error("SearchBySim3 shim: one entry per feature");
+    if (pKF1->N == 0 || pKF2->N == 0) return 0;
+    std::vector<uint8_t> b1(pKF1->N, 0), b2(pKF2->N, 0);
+    const cuorb_frame_view fv1 = view_of(*pKF1, b1), fv2 = view_of(*pKF2, b2);
+    std::vector<int32_t> m12(pKF1->N);
+    const int r = cuorb_search_by_sim3(device_, &fv1, &fv2, P12.desc.data(), P12.u.data(), P12.v.data(), P12.level.data(),
+                                       P12.active.data(), P21.desc.data(), P21.u.data(), P21.v.data(), P21.level.data(),
+                                       P21.active.data(), th, m12.data());
+    if (r < 0) throw std::runtime_error(std::string("SearchBySim3 (libcuorb): ") + cuorb_last_error());
+    const std::vector<MapPointT*> vpMapPoints2 = pKF2->GetMapPointMatches();
+    for (int i = 0; i < pKF1->N; i++)
+      if (m12[i] >= 0) vpMatches12[i] = vpMapPoints2[m12[i]];                                      // :1674
+    return r;
+  }
+
+  // int SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>&
+  // vnMatches12, int windowSize = 10)  (include/ORBmatcher.h:99-105, src/ORBmatcher.cc:666-782)
+  template <class FrameT>
+  int SearchForInitialization(FrameT& F1, FrameT& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12,
+                              int windowSize = 10) {
+    vnMatches12.assign(F1.mvKeysUn.size(), -1);
+    if (F1.N == 0 || F2.N == 0) return 0;
+    static_assert(sizeof(cv::Point2f) == 8, "cv::Point2f must be two floats");
+    std::vector<uint8_t> b1(F1.N, 0), b2(F2.N, 0);
+    const cuorb_frame_view fv1 = view_of(F1, b1), fv2 = view_of(F2, b2);
+    const int r = cuorb_search_for_initialization(device_, &fv1, &fv2, reinterpret_cast<float*>(vbPrevMatched.data()),
+                                                  windowSize, mfNNratio, mbCheckOrientation ? 1 : 0, vnMatches12.data());
+    if (r < 0) throw std::runtime_error(std::string("SearchForInitialization (libcuorb): ") + cuorb_last_error());
+    return r;
+  }
+
+  // int SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<std::pair<size_t, size_t>>& vMatchedPairs,
+  // const bool bOnlyStereo, const bool bCoarse = false)  (include/ORBmatcher.h:108-114, src/ORBmatcher.cc:916-1147;
+  // mpCamera2 == NULL).  F12 (row-major K1^-T [t12]x R12 K2^-1, src/CameraModels/Pinhole.cpp:153-156) and the epipole
+  // ep = pKF2->mpCamera->project(T2w * Cw) (:927-933) are the caller's Eigen prologue.
+  template <class KeyFrameT>
+  int SearchForTriangulation(KeyFrameT* pKF1, KeyFrameT* pKF2, const float F12[9], const float ep[2],
+                             std::vector<std::pair<std::size_t, std::size_t>>& vMatchedPairs, const bool bOnlyStereo,
+                             const bool bCoarse = false) {
+    vMatchedPairs.clear();
+    if (pKF1->N == 0 || pKF2->N == 0) return 0;
+    std::vector<uint8_t> b1(pKF1->N), b2(pKF2->N);
+    for (int i = 0; i < pKF1->N; i++) b1[i] = pKF1->GetMapPoint(i) ? 1 : 0;                        // :984-988
+    for (int i = 0; i < pKF2->N; i++) b2[i] = pKF2->GetMapPoint(i) ? 1 : 0;                        // :1012-1017
+    const cuorb_frame_view fv1 = view_of(*pKF1, b1), fv2 = view_of(*pKF2, b2);
+    std::vector<int32_t> off1, idx1, off2, idx2;
+    join(pKF1->mFeatVec, pKF2->mFeatVec, off1, idx1, off2, idx2);
+    std::vector<int32_t> m12(pKF1->N);
+    const int r = cuorb_search_for_triangulation(device_, &fv1, &fv2, (int)off1.size() - 1, off1.data(), idx1.data(), off2.data(),
+                                                 idx2.data(), F12, ep, pKF2->mvLevelSigma2.data(), bOnlyStereo ? 1 : 0,
+                                                 bCoarse ? 1 : 0, mbCheckOrientation ? 1 : 0, m12.data());
+    if (r < 0) throw std::runtime_error(std::string("SearchForTriangulation (libcuorb): ") + cuorb_last_error());
+    vMatchedPairs.reserve(r);
+    for (int i = 0; i < pKF1->N; i++)                                                              // :1133-1144
+      if (m12[i] >= 0) vMatchedPairs.push_back(std::make_pair((std::size_t)i, (std::size_t)m12[i]));
+    return r;
+  }
+
   // float RadiusByViewingCos(const float& viewCos)  (src/ORBmatcher.cc:229-235)
   static float RadiusByViewingCos(const float& viewCos) { return viewCos > 0.998f ? 2.5f : 4.0f; }
 
@@ -137,7 +291,20 @@ private:
   int bow(const FeatVecT& fv1, const FeatVecT& fv2, int n1, const uint8_t* d1, const std::vector<uint8_t>& valid1,
           const std::vector<float>& a1, int n2, const uint8_t* d2, const std::vector<uint8_t>& elig2,
           const std::vector<float>& a2, int mode, std::vector<int32_t>& match) {
-    std::vector<int32_t> off1(1, 0), off2(1, 0), idx1, idx2;
+    std::vector<int32_t> off1, idx1, off2, idx2;
+    join(fv1, fv2, off1, idx1, off2, idx2);
+    const int n = cuorb_search_by_bow(device_, n1, d1, valid1.data(), a1.data(), n2, d2, elig2.data(), a2.data(),
+                                      (int)off1.size() - 1, off1.data(), idx1.data(), off2.data(), idx2.data(), mode, mfNNratio,
+                                      mbCheckOrientation ? 1 : 0, match.data());
+    if (n < 0) throw std::runtime_error(std::string("SearchByBoW (libcuorb): ") + cuorb_last_error());
+    return n;
+  }
+
+  // the common nodes of two DBoW2::FeatureVectors in NodeId order (src/ORBmatcher.cc:252-259, 395-399)
+  template <class FeatVecT>
+  static void join(const FeatVecT& fv1, const FeatVecT& fv2, std::vector<int32_t>& off1, std::vector<int32_t>& idx1,
+                   std::vector<int32_t>& off2, std::vector<int32_t>& idx2) {
+    off1.assign(1, 0); off2.assign(1, 0); idx1.clear(); idx2.clear();
     auto it1 = fv1.begin(); auto it2 = fv2.begin();
     while (it1 != fv1.end() && it2 != fv2.end()) {
       if (it1->first == it2->first) {
@@ -148,11 +315,23 @@ private:
       } else if (it1->first < it2->first) it1 = fv1.lower_bound(it2->first);
       else it2 = fv2.lower_bound(it1->first);
     }
-    const int n = cuorb_search_by_bow(device_, n1, d1, valid1.data(), a1.data(), n2, d2, elig2.data(), a2.data(),
-                                      (int)off1.size() - 1, off1.data(), idx1.data(), off2.data(), idx2.data(), mode, mfNNratio,
-                                      mbCheckOrientation ? 1 : 0, match.data());
-    if (n < 0) throw std::runtime_error(std::string("SearchByBoW (libcuorb): ") + cuorb_last_error());
-    return n;
+  }
+
+  // a Frame or KeyFrame (same member names) with the caller's per-feature "taken" flags
+  template <class T>
+  static cuorb_frame_view view_of(T& F, const std::vector<uint8_t>& bound) {
+    cuorb_frame_view v;
+    v.n = F.N;
+    v.keys_un = (const cuorb_keypoint*)F.mvKeysUn.data();
+    v.descriptors = contiguous(F.mDescriptors);
+    v.u_right = F.mvuRight.empty() ? nullptr : F.mvuRight.data();
+    v.bound_with_obs = bound.data();
+    v.min_x = F.mnMinX; v.min_y = F.mnMinY; v.max_x = F.mnMaxX; v.max_y = F.mnMaxY;
+    v.grid_w_inv = F.mfGridElementWidthInv; v.grid_h_inv = F.mfGridElementHeightInv;
+    v.mb = F.mb; v.mbf = F.mbf;
+    v.nlevels = (int)F.mvScaleFactors.size();
+    v.scale_factors = F.mvScaleFactors.data();
+    return v;
   }
 
   static const uint8_t* contiguous(const cv::Mat& m) {

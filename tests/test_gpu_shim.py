@@ -74,3 +74,66 @@ def test_cpp_shim_frame_prep(tmp_path):
     m0, k0, d0 = op.OracleExtractor(nf, 1.2, 8, 20, 7).extract(ref_gray)
     assert (n, mono) == (len(k0), m0)
     assert (k == k0).all() and (d == d0).all()
+
+
+def test_cpp_shim_searches(tmp_path):
+    """shim/ORBmatcher.h: SearchForInitialization (twice, as monocular initialisation does), the Sim3
+    SearchByProjection, Fuse and SearchForTriangulation on reference-named structs == oracle."""
+    from orbslam3_cpp_fork_b200.matcher import join_feature_vectors
+    build.build_libcuorb()
+    exe = str(tmp_path / "search_check")
+    pkg = os.path.join(ROOT, "orbslam3_cpp_fork_b200")
+    subprocess.check_call(["g++", "-std=c++17", "-O2", os.path.join(ROOT, "tests", "native", "search_check.cpp"), "-o", exe,
+                           "-L" + pkg, "-l:libcuorb.so", "-Wl,-rpath," + pkg])
+    w, h, nf = 640, 480, 2000
+    a, b = synth.synth_stereo_pair(w, h, seed=33)
+    a.tofile(tmp_path / "a.raw"); b.tofile(tmp_path / "b.raw")
+    out = str(tmp_path / "out.bin")
+    subprocess.check_call([exe, str(tmp_path / "a.raw"), str(tmp_path / "b.raw"), str(w), str(h), str(nf), out])
+    raw = open(out, "rb").read()
+    na, nb, n_ini1, n_ini2, n_sim3, n_fuse, n_tri, _ = [int(v) for v in np.frombuffer(raw, np.int32, 8)]
+    off = 32
+    ka = np.frombuffer(raw, _lib.KP_DTYPE, na, off); off += 28 * na
+    da = np.frombuffer(raw, np.uint8, 32 * na, off).reshape(na, 32); off += 32 * na
+    kb = np.frombuffer(raw, _lib.KP_DTYPE, nb, off); off += 28 * nb
+    db = np.frombuffer(raw, np.uint8, 32 * nb, off).reshape(nb, 32); off += 32 * nb
+    ini1 = np.frombuffer(raw, np.int32, na, off); off += 4 * na
+    ini2 = np.frombuffer(raw, np.int32, na, off); off += 4 * na
+    prev = np.frombuffer(raw, np.float32, 2 * na, off).reshape(na, 2); off += 8 * na
+    sim3 = np.frombuffer(raw, np.int32, na, off); off += 4 * na
+    fused = np.frombuffer(raw, np.int32, na, off); off += 4 * na
+    tri = np.frombuffer(raw, np.int32, na, off)
+
+    o = op.OracleExtractor(nf, 1.2, 8, 20, 7)
+    sf = np.asarray(o.tables()[0], np.float32)
+    fva, keep_a = op.make_frame_view(ka, da, None, None, w, h, sf, mb=0.1, mbf=40.0)
+    fvb, keep_b = op.make_frame_view(kb, db, None, None, w, h, sf, mb=0.1, mbf=40.0)
+    p0 = np.stack([ka["x"], ka["y"]], 1).astype(np.float32)
+    r1, m1, p1 = op.search_for_initialization(fva, fvb, p0, 100, 0.9, True)
+    r2, m2, p2 = op.search_for_initialization(fva, fvb, p1, 100, 0.9, True)
+    assert (n_ini1, n_ini2) == (r1, r2) and (ini1 == m1).all() and (ini2 == m2).all() and (prev == p2).all() and r1 > 20
+
+    i = np.arange(na)
+    level = np.minimum(ka["octave"] + (i & 1), 7).astype(np.int32)
+    active = (i % 7 != 0).astype(np.uint8)
+    u = (ka["x"] + np.float32(1.5)).astype(np.float32); v = (ka["y"] - np.float32(0.75)).astype(np.float32)
+    bound = (i % 5 == 0).astype(np.uint8)
+    fvs, keep_s = op.make_frame_view(ka, da, None, bound, w, h, sf, mb=0.1, mbf=40.0)
+    rs, best = op.search_by_projection_sim3(fvs, da, u, v, level, active, 10, 1.0)
+    ref = np.full(na, -1, np.int32)
+    ref[best[best >= 0]] = i[best >= 0]
+    assert n_sim3 == rs and (sim3 == ref).all() and rs > 100
+    inv_sigma2 = (np.float32(1.0) / (sf * sf)).astype(np.float32)
+    rf, bf = op.fuse(fva, inv_sigma2, da, u, v, (ka["x"] - np.float32(9.0)).astype(np.float32), level, active, 3.0, True)
+    assert n_fuse == rf and (fused == bf).all() and rf > 100
+
+    F12 = np.array([0, 1e-4, 0, -2e-4, 0, -1, 3e-4, 1, 0], np.float32)
+    ep = np.array([w * 0.5, h * 0.5], np.float32)
+    has_a = (i % 3 == 0).astype(np.uint8)
+    fv1 = {}; fv2 = {}
+    for j in range(na): fv1.setdefault(int(ka["y"][j]) // 10, []).append(j)
+    for j in range(nb): fv2.setdefault(int(kb["y"][j]) // 10, []).append(j)
+    off1, idx1, off2, idx2 = join_feature_vectors(fv1, fv2)
+    fvt, keep_t = op.make_frame_view(ka, da, None, has_a, w, h, sf, mb=0.1, mbf=40.0)
+    rt, mt = op.search_for_triangulation(fvt, fvb, off1, idx1, off2, idx2, F12, ep, (sf * sf).astype(np.float32), False, False, True)
+    assert n_tri == rt and (tri == mt).all() and rt > 5
