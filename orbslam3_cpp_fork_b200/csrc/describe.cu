@@ -138,7 +138,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_describe(const ExtractorGeo
 
   // ---- phase A: fetch the two patches with TMA, then the integer moments of the disc ----
   int l = 0, cx = 0, cy = 0, score = 0;
-  unsigned char* ic = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem) + 127) & ~(uintptr_t)127) + wid * (IC_SLOT + BR_SLOT);
+  unsigned char* ic = smem + ((128u - ((unsigned)__cvta_generic_to_shared(smem) & 127u)) & 127u) + wid * (IC_SLOT + BR_SLOT);
   unsigned char* br = ic + IC_SLOT;
   if (live) {
     while (g >= s_off[l + 1]) l++;

@@ -316,7 +316,8 @@ __global__ void __launch_bounds__(128) k_fast_persist(const __grid_constant__ Fa
   __shared__ uint64_t s_bar[2];
   __shared__ int s_next[2];
 
-  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+  // pointer arithmetic on the array (not an integer round trip) so the accesses stay LDS/STS, not generic LD/ST
+  unsigned char* smem = smem_raw + ((128u - ((unsigned)__cvta_generic_to_shared(smem_raw) & 127u)) & 127u);
   unsigned char*  s_tiles = smem;                                              // 2 x tile_bytes
   unsigned char*  s_scores = smem + 2 * P.tile_bytes;                           // 2 x score_bytes (items alternate)
   unsigned short* s_plist = reinterpret_cast<unsigned short*>(s_scores + 2 * P.score_bytes);
