@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(OT_THREADS) k_octree(const ExtractorGeom* __re
   int* cntB = (int*)p;             p += 4 * cap;
   unsigned short* remap = (unsigned short*)p;  p += 8 * cap;
   unsigned short* jrank = (unsigned short*)p;  p += 2 * cap;
-  p += (16u - ((unsigned)__cvta_generic_to_shared(p) & 15u)) & 15u;
+  p = (unsigned char*)(((uintptr_t)p + 15) & ~(uintptr_t)15);
   unsigned* s_keys = (unsigned*)p;                         // OT_KEYCAP entries
   unsigned short* s_nid = (unsigned short*)(p + 4 * OT_KEYCAP);
 

@@ -45,20 +45,28 @@ __global__ void __launch_bounds__(PYR_TX) k_pyr_level0(const ExtractorGeom* __re
   for (int b = 0; b < 4; b++)
     xs[b] = reflect101(min(max(xw + b, -EDGE_THRESHOLD), L.w + EDGE_THRESHOLD - 1), L.w);  // pad bytes: clamp
   const int y0 = blockIdx.y * PYR_RS, y1 = min(y0 + PYR_RS, L.h);
-  for (int y = y0; y < y1; y++) {
-    const uint8_t* srow = src + (size_t)y * stride;
-    unsigned out;
+  // all loads of the strip first (16 independent requests in flight), then the stores
+  unsigned v[PYR_RS];
+#pragma unroll
+  for (int r = 0; r < PYR_RS; r++) {
+    const uint8_t* srow = src + (size_t)min(y0 + r, y1 - 1) * stride;
     if (inner) {
-      out = __ldg(reinterpret_cast<const unsigned*>(srow + xw));
+      v[r] = __ldg(reinterpret_cast<const unsigned*>(srow + xw));
     } else {
-      out = (unsigned)__ldg(srow + xs[0]) | ((unsigned)__ldg(srow + xs[1]) << 8) |
-            ((unsigned)__ldg(srow + xs[2]) << 16) | ((unsigned)__ldg(srow + xs[3]) << 24);
+      v[r] = (unsigned)__ldg(srow + xs[0]) | ((unsigned)__ldg(srow + xs[1]) << 8) |
+             ((unsigned)__ldg(srow + xs[2]) << 16) | ((unsigned)__ldg(srow + xs[3]) << 24);
     }
-    reinterpret_cast<unsigned*>(dst + (size_t)(y + EDGE_THRESHOLD) * L.pitch)[word] = out;
-    if (y >= 1 && y <= EDGE_THRESHOLD)
-      reinterpret_cast<unsigned*>(dst + (size_t)(EDGE_THRESHOLD - y) * L.pitch)[word] = out;
-    if (y >= L.h - 1 - EDGE_THRESHOLD && y <= L.h - 2)
-      reinterpret_cast<unsigned*>(dst + (size_t)(2 * L.h + EDGE_THRESHOLD - 2 - y) * L.pitch)[word] = out;
+  }
+  unsigned* drow = reinterpret_cast<unsigned*>(dst) + word;
+  const int dp4 = L.pitch >> 2;
+#pragma unroll
+  for (int r = 0; r < PYR_RS; r++) {
+    const int y = y0 + r;
+    if (y >= y1) break;
+    const unsigned out = v[r];
+    drow[(size_t)(y + EDGE_THRESHOLD) * dp4] = out;
+    if (y >= 1 && y <= EDGE_THRESHOLD) drow[(size_t)(EDGE_THRESHOLD - y) * dp4] = out;
+    if (y >= L.h - 1 - EDGE_THRESHOLD && y <= L.h - 2) drow[(size_t)(2 * L.h + EDGE_THRESHOLD - 2 - y) * dp4] = out;
   }
 }
 

@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(256) k_stereo_rows(StereoArgs A) {
 }
 
 // grid: (ceil(kp_cap/8), n_img), block 256
-__global__ void __launch_bounds__(256) k_stereo_match(StereoArgs A, int band) {
+__global__ void __launch_bounds__(256, 6) k_stereo_match(StereoArgs A, int band) {
   const ExtractorGeom* dg = A.dgL;
   const int img = blockIdx.y, lane = threadIdx.x & 31;
   const int iL = blockIdx.x * 8 + (threadIdx.x >> 5);
