@@ -27,6 +27,7 @@
 // function of (x, y) and is re-derived where it matters (quadtree tie-break, debug download).
 // Bound: the integer ALU pipe (VIMNMX/PRMT/LOP3 all issue there at 2 warp-inst/clk/SM), not HBM.
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "tma.cuh"
@@ -311,7 +312,8 @@ __device__ __forceinline__ unsigned widen_even(unsigned h) { return __byte_perm(
 // bytes 1 of lo and 0 of hi (two zero-extended u16 loads two bytes apart) -> u16x2
 __device__ __forceinline__ unsigned widen_odd(unsigned lo, unsigned hi) { return __byte_perm(lo, hi, 0x2421); }
 
-__global__ void __launch_bounds__(128) k_fast_persist(const __grid_constant__ FastMaps maps, const FastParams P) {
+template <int NW>
+__global__ void __launch_bounds__(32 * NW) k_fast_persist(const __grid_constant__ FastMaps maps, const FastParams P) {
   extern __shared__ unsigned char smem_raw[];
   __shared__ uint64_t s_bar[2];
   __shared__ int s_next[2];
@@ -321,7 +323,8 @@ __global__ void __launch_bounds__(128) k_fast_persist(const __grid_constant__ Fa
   unsigned char*  s_tiles = smem;                                              // 2 x tile_bytes
   unsigned char*  s_scores = smem + 2 * P.tile_bytes;                           // 2 x score_bytes (items alternate)
   unsigned short* s_plist = reinterpret_cast<unsigned short*>(s_scores + 2 * P.score_bytes);
-  unsigned short* s_clist = s_plist + 4 * P.pcap;
+  constexpr int NT = 32 * NW;   // NW warps share one cell
+  unsigned short* s_clist = s_plist + NW * P.pcap;
 
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const unsigned lt = (1u << lane) - 1u;
@@ -333,7 +336,7 @@ __global__ void __launch_bounds__(128) k_fast_persist(const __grid_constant__ Fa
     mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1);
     mbar_fence_init();
   }
-  for (int i = tid; i < (P.score_bytes >> 1); i += 128) reinterpret_cast<unsigned*>(s_scores)[i] = 0;
+  for (int i = tid; i < (P.score_bytes >> 1); i += NT) reinterpret_cast<unsigned*>(s_scores)[i] = 0;
   __syncthreads();
 
   auto issue = [&](int work, int buf) {  // one thread
@@ -379,7 +382,7 @@ __global__ void __launch_bounds__(128) k_fast_persist(const __grid_constant__ Fa
         const unsigned K = (unsigned)(127 - min(cur_th, 127)) * 0x01010101u;
         unsigned short* seg = s_plist + wid * pcap;
         int cnt = 0;
-        for (int i0 = 0; i0 < nquads; i0 += 128) {
+        for (int i0 = 0; i0 < nquads; i0 += NT) {
           // no branch around the body: out-of-range threads redo the last quad and are masked out
           const bool in = i0 + tid < nquads;
           const int i = min(i0 + tid, nquads - 1);
@@ -571,23 +574,27 @@ void launch_fast_persist(const ExtractorGeom& g, const FastMaps& maps, const int
   const int sp_max = ((((g.max_cell_w + 5 + 3) >> 2) | 1) << 2);
   P.score_bytes = ((sp_max * (g.max_cell_h + 2) + 15) / 16) * 16;
   const int maxquads = ((g.max_cell_w + 3) / 4 + 1) * g.max_cell_h;
-  P.pcap = 64 * ((maxquads + 127) / 128);
-  P.ccap = 64 * ((2 * maxquads + 127) / 128);
-  const int smem = 128 + 2 * P.tile_bytes + 2 * P.score_bytes + 2 * 4 * (P.pcap + P.ccap);
+  // warps per cell: 2 measured best on B200 (0.667 ms per 256 images; 4 warps 0.675, 1 warp 0.810): fewer
+  // warps wait at the two per-cell barriers, more cells are in flight per SM; CUORB_FAST_WARPS overrides
+  static const int NW = []() { const char* e = getenv("CUORB_FAST_WARPS"); const int v = e ? atoi(e) : 2; return v == 1 || v == 4 ? v : 2; }();
+  P.pcap = 64 * ((maxquads + 32 * NW - 1) / (32 * NW));
+  P.ccap = 2 * P.pcap;
+  const int smem = 128 + 2 * P.tile_bytes + 2 * P.score_bytes + 2 * NW * (P.pcap + P.ccap);
+  void (*kern)(const FastMaps, const FastParams) = NW == 1 ? k_fast_persist<1> : NW == 2 ? k_fast_persist<2> : k_fast_persist<4>;
   static int attr = 48 * 1024, per_sm = 0, attr_smem = -1, n_sm = 0;
   if (smem > attr) {
-    cudaFuncSetAttribute(k_fast_persist, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     attr = smem;
   }
   if (attr_smem != smem) {
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fast_persist, 128, smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 32 * NW, smem);
     attr_smem = smem;
   }
   const int grid = std::max(1, std::min(P.total_work, n_sm * std::max(per_sm, 1)));
-  k_fast_persist<<<grid, 128, smem, st>>>(maps, P);
+  kern<<<grid, 32 * NW, smem, st>>>(maps, P);
   count_launch();
 }
 
