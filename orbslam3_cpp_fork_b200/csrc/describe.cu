@@ -107,8 +107,9 @@ constexpr int BR_BYTES = BR_BOX_W * BR_BOX_H;                // 2368
 constexpr int IC_SLOT = (IC_BYTES + 127) / 128 * 128;        // 1536
 constexpr int BR_SLOT = (BR_BYTES + 127) / 128 * 128;        // 2432
 
-// grid: (ceil(kp_cap/DESC_WARPS), n_img), block = DESC_WARPS warps, warp per keypoint.  Four warps per CTA:
-// the two CTA barriers around the angle phase cost 0.253 ms at 16 warps, 0.226 at 8, 0.222 at 4 (256 images)
+// grid: (ceil(kp_cap/DESC_WARPS), n_img), block = DESC_WARPS warps, warp per keypoint.  Four warps per CTA
+// (0.253 ms at 16 warps, 0.226 at 8, 0.222 at 4 per 256 images); the angle is computed on lane 0 of the keypoint's
+// own warp, so the only CTA barrier is the one after the level offsets
 __global__ void __launch_bounds__(DESC_WARPS * 32) k_describe(const ExtractorGeom* __restrict__ dg,
                                                               const __grid_constant__ TmaMaps tmaps,
                                                               const LevelKey* __restrict__ keys,
@@ -118,7 +119,6 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_describe(const ExtractorGeo
                                                               uint8_t* __restrict__ out_desc) {
   extern __shared__ __align__(128) unsigned char smem[];     // DESC_WARPS x (IC_SLOT + BR_SLOT)
   __shared__ uint64_t s_bar[DESC_WARPS];
-  __shared__ int   s_m01[DESC_WARPS], s_m10[DESC_WARPS];
   __shared__ float s_angle[DESC_WARPS], s_cos[DESC_WARPS], s_sin[DESC_WARPS];
   __shared__ int   s_off[MAX_LEVELS + 1];
   const int img = blockIdx.y, nlv = dg->nlevels;
@@ -181,20 +181,17 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_describe(const ExtractorGeo
       m01 += __shfl_xor_sync(0xffffffffu, m01, o);
       m10 += __shfl_xor_sync(0xffffffffu, m10, o);
     }
-    if (lane == 0) { s_m01[wid] = m01; s_m10[wid] = m10; }
+    // ---- phase B: angle and rotation on lane 0 of the keypoint's own warp (no CTA barrier) ----
+    if (lane == 0) {
+      const float angle = fast_atan2_deg((float)m01, (float)m10);
+      const float factorPI = (float)(3.14159265358979323846 / (double)180.f);
+      const float ang = __fmul_rn(angle, factorPI);
+      double sn, cs;
+      sincos((double)ang, &sn, &cs);
+      s_angle[wid] = angle; s_cos[wid] = (float)cs; s_sin[wid] = (float)sn;
+    }
+    __syncwarp();
   }
-  __syncthreads();
-
-  // ---- phase B: angle and rotation, one lane per keypoint ----
-  if (tid < DESC_WARPS && g0 + tid < n) {
-    const float angle = fast_atan2_deg((float)s_m01[tid], (float)s_m10[tid]);
-    const float factorPI = (float)(3.14159265358979323846 / (double)180.f);
-    const float ang = __fmul_rn(angle, factorPI);
-    double sn, cs;
-    sincos((double)ang, &sn, &cs);
-    s_angle[tid] = angle; s_cos[tid] = (float)cs; s_sin[tid] = (float)sn;
-  }
-  __syncthreads();
   if (!live) return;
 
   // ---- phase C: steered BRIEF from the shared blurred box ----
