@@ -2,6 +2,7 @@
 // computed with the reference's float arithmetic, stream-ordered batch pipeline.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 
@@ -33,7 +34,9 @@ struct cuorb_extractor {
   int   quota[MAX_LEVELS];
 
   cudaStream_t stream = nullptr;
+  cudaStream_t side_stream = nullptr;   // blur runs here, beside FAST + quadtree (both only read the pyramid)
   cudaEvent_t  ev_done = nullptr;       // recorded after the last enqueued work
+  cudaEvent_t  ev_pyr = nullptr, ev_blur = nullptr;   // fork / join of the side stream
   cudaEvent_t  ev_stage[CUORB_STAGE_COUNT + 1] = {};
   bool         profiling = false, have_stage_times = false, stereo_timed = false;
 
@@ -242,6 +245,9 @@ static void free_all(cuorb_extractor* e) {
   for (void* p : host) if (p) cudaFreeHost(p);
   for (auto& ev : e->ev_stage) if (ev) cudaEventDestroy(ev);
   if (e->ev_done) cudaEventDestroy(e->ev_done);
+  if (e->ev_pyr) cudaEventDestroy(e->ev_pyr);
+  if (e->ev_blur) cudaEventDestroy(e->ev_blur);
+  if (e->side_stream) cudaStreamDestroy(e->side_stream);
   if (e->stream) cudaStreamDestroy(e->stream);
 }
 
@@ -370,7 +376,10 @@ cuorb_extractor* cuorb_extractor_create(const cuorb_config* cfg) {
   for (int l = 1; l < g.nlevels; l++) e->cap_wtab += 2 * (size_t)(g.lv[l].pitch / 4 + 1);
   bool ok = true;
   ok &= cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess;
+  ok &= cudaStreamCreateWithFlags(&e->side_stream, cudaStreamNonBlocking) == cudaSuccess;
   ok &= cudaEventCreateWithFlags(&e->ev_done, cudaEventDisableTiming) == cudaSuccess;
+  ok &= cudaEventCreateWithFlags(&e->ev_pyr, cudaEventDisableTiming) == cudaSuccess;
+  ok &= cudaEventCreateWithFlags(&e->ev_blur, cudaEventDisableTiming) == cudaSuccess;
   for (auto& ev : e->ev_stage) ok &= cudaEventCreate(&ev) == cudaSuccess;
   ok &= dev_alloc(&e->d_geom, 1) == cudaSuccess;
   ok &= dev_alloc(&e->d_xtab, e->cap_xtab) == cudaSuccess;
@@ -475,6 +484,12 @@ static int enqueue_pipeline(cuorb_extractor* e, int n_images, const uint8_t* dim
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_PYRAMID], st);
   launch_pyramid(e->g, e->d_geom, dimgs, width, height, dstride, dimg_stride, n_images, e->d_pyr, e->d_xtab, e->d_ytab,
                  e->d_wtab, e->wtab_off, st);
+  // FAST (integer-ALU bound, 20 warps per SM) and the blur (FMA pipe + loads) both depend only on the
+  // pyramid: outside profiling runs the blur goes to the side stream, after FAST in launch order so
+  // FAST's CTAs get their shared memory first and blur CTAs fill the remaining warp slots of each SM
+  static const bool side_blur = []() { const char* v = getenv("CUORB_SIDE_BLUR"); return !v || atoi(v) != 0; }();
+  const bool fork = side_blur && !prof;
+  if (fork) CUORB_CUDA_TRY(cudaEventRecord(e->ev_pyr, st));
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_FAST], st);
   if (e->fast_persist) {
     if (e->n_fast_recs > 0)
@@ -483,11 +498,17 @@ static int enqueue_pipeline(cuorb_extractor* e, int n_images, const uint8_t* dim
   } else {
     launch_fast(e->g, e->d_geom, e->d_fast_cells, n_images, e->d_pyr, e->d_cand, e->d_cand_count, e->d_flags, st);
   }
+  if (fork) {
+    CUORB_CUDA_TRY(cudaStreamWaitEvent(e->side_stream, e->ev_pyr, 0));
+    launch_blur(&e->g, e->d_geom, n_images, e->d_blur_tiles, e->n_blur_tiles, e->d_pyr, e->d_blur, e->side_stream);
+    CUORB_CUDA_TRY(cudaEventRecord(e->ev_blur, e->side_stream));
+  }
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_OCTREE], st);
   launch_octree(e->g, e->d_geom, n_images, e->d_cand, e->d_cand_scratch, e->d_cand_count, e->d_keys,
                 e->d_key_count, e->d_flags, st);
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_BLUR], st);
-  launch_blur(&e->g, e->d_geom, n_images, e->d_blur_tiles, e->n_blur_tiles, e->d_pyr, e->d_blur, st);
+  if (fork) CUORB_CUDA_TRY(cudaStreamWaitEvent(st, e->ev_blur, 0));
+  else launch_blur(&e->g, e->d_geom, n_images, e->d_blur_tiles, e->n_blur_tiles, e->d_pyr, e->d_blur, st);
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_DESCRIBE], st);
   launch_describe(e->g, e->d_geom, e->tmaps, n_images, e->d_pyr, e->d_blur, e->d_keys, e->d_key_count, lap0, lap1,
                   e->d_slot, e->d_out_kps, e->d_out_desc, e->d_out_n, e->d_out_mono, st);
