@@ -27,17 +27,20 @@ __device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ row, unsig
   h[3] = __dp4a(B, K0, __dp4a(C, K1, 0u));
 }
 
-// grid: (tiles over all levels, n_img); tiles = (level, word block, row strip)
+// grid: (tiles over all levels, n_img); a tile = BL_THREADS consecutive (row strip, word) items of one
+// level, numbered strip-major, so only the last CTA of a level has idle lanes (a lane's neighbours may
+// belong to the next strip: both are contiguous row segments, still coalesced)
 __global__ void __launch_bounds__(BL_THREADS) k_blur(const ExtractorGeom* __restrict__ dg,
                                                      const int4* __restrict__ tiles,
                                                      const uint8_t* __restrict__ pyr,
                                                      uint8_t* __restrict__ blur) {
-  const int4 t = tiles[blockIdx.x];
+  const int4 t = tiles[blockIdx.x];   // {level, first item, words per row, items in the level}
   const LevelGeom& L = dg->lv[t.x];
-  const int word = t.y * BL_THREADS + threadIdx.x;
-  if (word * 4 >= L.bpitch) return;
+  const int item = t.y + threadIdx.x;
+  if (item >= t.w) return;
+  const int strip = item / t.z, word = item - strip * t.z;
   const int img = blockIdx.y;
-  const int y0 = t.z * BL_ROWS, y1 = min(y0 + BL_ROWS, L.h);
+  const int y0 = strip * BL_ROWS, y1 = min(y0 + BL_ROWS, L.h);
   const uint8_t* src = pyr + (size_t)img * dg->pyr_img_stride + L.pix_off + word * 4;
   uint8_t* dst = blur + (size_t)img * dg->blur_img_stride + L.blur_off + word * 4;
   const int pitch = L.pitch, bpitch = L.bpitch;
@@ -69,9 +72,9 @@ __global__ void __launch_bounds__(BL_THREADS) k_blur(const ExtractorGeom* __rest
 void build_blur_tiles(const ExtractorGeom& g, std::vector<int4>& v) {
   v.clear();
   for (int l = 0; l < g.nlevels; l++) {
-    const int nwb = (g.lv[l].bpitch / 4 + BL_THREADS - 1) / BL_THREADS;
-    for (int ty = 0; ty < (g.lv[l].h + BL_ROWS - 1) / BL_ROWS; ty++)
-      for (int tx = 0; tx < nwb; tx++) v.push_back(make_int4(l, tx, ty, 0));
+    const int words = g.lv[l].bpitch / 4;
+    const int items = words * ((g.lv[l].h + BL_ROWS - 1) / BL_ROWS);
+    for (int i = 0; i < items; i += BL_THREADS) v.push_back(make_int4(l, i, words, items));
   }
 }
 

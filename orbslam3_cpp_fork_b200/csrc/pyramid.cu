@@ -13,6 +13,7 @@
 // rows that REFLECT_101 maps onto it; border columns are ordinary words whose four columns are
 // reflected before the tap lookup.  Bound: HBM (reads P_{l-1}, writes (w+38)(h+38)).
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -20,6 +21,7 @@ namespace cuorb {
 
 constexpr int PYR_RS = 16;  // interior rows per thread strip
 constexpr int PYR_TX = 64;  // threads (output words) per CTA
+constexpr int PYR_TAB_TX = 192;  // k_pyr_resize_tab: upper bound of its per-level CTA width
 
 __device__ __forceinline__ int reflect101(int i, int n) {
   // border (19) < n is checked on the host, so one reflection suffices
@@ -206,24 +208,27 @@ __global__ void __launch_bounds__(PYR_TX) k_pyr_resize(const ExtractorGeom* __re
 // the previous lower source row are reused whenever the source step is 1.
 //   wtab[2*word]   = {window byte offset (4-aligned), funnel shift (bits), sel0 | sel1 << 16, sel2 | sel3 << 16}
 //   wtab[2*word+1] = {a0 | a1 << 16} for the four columns
-__global__ void __launch_bounds__(PYR_TX, 24) k_pyr_resize_tab(const ExtractorGeom* __restrict__ dg, int level,
+// blockDim.x = the row's word count rounded up to whole warps (at most PYR_TAB_TX), so few lanes idle
+// on the narrow levels; `rs` = output rows per strip (<= PYR_RS), shorter on the small levels so their
+// grids still cover several waves.
+__global__ void __launch_bounds__(PYR_TAB_TX, 1536 / PYR_TAB_TX) k_pyr_resize_tab(const ExtractorGeom* __restrict__ dg, int level,
                                                            uint8_t* __restrict__ pyr,
                                                            const uint4* __restrict__ wtab,
-                                                           const ResizeTap* __restrict__ ytab) {
+                                                           const ResizeTap* __restrict__ ytab, int rs) {
   __shared__ int s_ys[PYR_RS];
   __shared__ unsigned s_b0[PYR_RS], s_b1[PYR_RS];
   const LevelGeom& L = dg->lv[level];
   const LevelGeom& S = dg->lv[level - 1];
   const int lh = L.h;
-  const int y0 = blockIdx.y * PYR_RS, y1 = min(y0 + PYR_RS, lh);
-  if (threadIdx.x < PYR_RS && y0 + (int)threadIdx.x < lh) {
+  const int y0 = blockIdx.y * rs, y1 = min(y0 + rs, lh);
+  if ((int)threadIdx.x < rs && y0 + (int)threadIdx.x < lh) {
     const ResizeTap t = ytab[L.ytab_off + y0 + threadIdx.x];
     s_ys[threadIdx.x] = max((int)t.s, 0);
     s_b0[threadIdx.x] = (unsigned)t.a0 << 16;
     s_b1[threadIdx.x] = (unsigned)t.a1 << 16;
   }
   __syncthreads();
-  const int word = blockIdx.x * PYR_TX + threadIdx.x;
+  const int word = blockIdx.x * blockDim.x + threadIdx.x;
   if (word * 4 >= L.pitch) return;
   const uint4 e0 = __ldg(&wtab[2 * word]), cf = __ldg(&wtab[2 * word + 1]);
   uint8_t* base = pyr + (size_t)blockIdx.z * dg->pyr_img_stride;
@@ -319,7 +324,22 @@ void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8
     } else {
       // four adjacent output columns span 3*scale + 2 source bytes (+3 for alignment): 12 bytes up to scale 2
       const double sx = (double)g.lv[l - 1].w / L.w;
-      if (wtab && wtab_off[l] >= 0) k_pyr_resize_tab<<<grid, PYR_TX, 0, st>>>(dg, l, pyr, wtab + wtab_off[l], ytab);
+      if (wtab && wtab_off[l] >= 0) {
+        static const int flex = []() { const char* e = getenv("CUORB_PYR_FLEX"); return e ? atoi(e) : 1; }();
+        static const int rs_small = []() { const char* e = getenv("CUORB_PYR_RS_SMALL"); const int v = e ? atoi(e) : 8; return v >= 1 && v <= PYR_RS ? v : 8; }();
+        static const int min_waves = []() { const char* e = getenv("CUORB_PYR_WAVES"); return e ? atoi(e) : 4; }();
+        const int words = L.pitch / 4;
+        int tx = PYR_TX, rs = PYR_RS;
+        if (flex) {
+          const int nb = (words + PYR_TAB_TX - 1) / PYR_TAB_TX;            // CTAs per row
+          tx = (((words + nb - 1) / nb) + 31) / 32 * 32;
+          const long wave = 148L * (1536 / tx);
+          const long ctas = (long)((words + tx - 1) / tx) * ((L.h + PYR_RS - 1) / PYR_RS) * n_img;
+          if (ctas < min_waves * wave) rs = rs_small;
+        }
+        dim3 tgrid((words + tx - 1) / tx, (L.h + rs - 1) / rs, n_img);
+        k_pyr_resize_tab<<<tgrid, tx, 0, st>>>(dg, l, pyr, wtab + wtab_off[l], ytab, rs);
+      }
       else if (3.0 * sx + 5.0 < 11.5) k_pyr_resize<false><<<grid, PYR_TX, 0, st>>>(dg, l, pyr, xtab, ytab);
       else k_pyr_resize<true><<<grid, PYR_TX, 0, st>>>(dg, l, pyr, xtab, ytab);
     }
