@@ -30,7 +30,7 @@ __device__ __forceinline__ int reflect101(int i, int n) {
 }
 
 // grid: (ceil(pitch/4/128), ceil(h/PYR_RS), n_img)
-__global__ void __launch_bounds__(PYR_TX) k_pyr_level0(const ExtractorGeom* __restrict__ dg,
+__global__ void __launch_bounds__(256) k_pyr_level0(const ExtractorGeom* __restrict__ dg,
                                                     const uint8_t* __restrict__ imgs, size_t stride,
                                                     size_t image_stride, uint8_t* __restrict__ pyr,
                                                     int aligned) {
@@ -320,7 +320,10 @@ void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8
     const LevelGeom& L = g.lv[l];
     dim3 grid((L.pitch / 4 + PYR_TX - 1) / PYR_TX, (L.h + PYR_RS - 1) / PYR_RS, n_img);
     if (l == 0) {
-      k_pyr_level0<<<grid, PYR_TX, 0, st>>>(dg, imgs, stride, image_stride, pyr, aligned);
+      // CTA width = the padded row's word count split evenly over whole warps (208 words -> one CTA of 224)
+      const int words = L.pitch / 4, nb = (words + 255) / 256;
+      const int tx = (((words + nb - 1) / nb) + 31) / 32 * 32;
+      k_pyr_level0<<<dim3((words + tx - 1) / tx, grid.y, n_img), tx, 0, st>>>(dg, imgs, stride, image_stride, pyr, aligned);
     } else {
       // four adjacent output columns span 3*scale + 2 source bytes (+3 for alignment): 12 bytes up to scale 2
       const double sx = (double)g.lv[l - 1].w / L.w;
