@@ -262,20 +262,29 @@ def run_cuorb(args):
         _lib.check(L_.cuorb_stereo_match_batch_async(eL.handle, eR.handle, MB, MBF))
 
     # ---------------- value: device-resident, CUDA events on the launching (left) stream ----------
+    # Steps alternate between the two handle pairs (as in the e2e leg), so step i+1's extraction runs
+    # beside step i's quadtree / describe / stereo kernels; within a pair the library orders the right
+    # handle's next extraction after the stereo match that reads its buffers.
     eL, eR = pairs[0]
     sL = torch.cuda.ExternalStream(eL.stream, device=local)
-    for _ in range(args.warmup):
-        step_resident(eL, eR)
-    eL.sync(); eR.sync()
+    sL1 = torch.cuda.ExternalStream(pairs[1][0].stream, device=local)
+    for i in range(max(args.warmup, 2)):
+        step_resident(*pairs[i & 1])
+    for p in pairs:
+        p[0].sync(); p[1].sync()
     sampler = ClockSampler(local); sampler.start()
     barrier()
     launches0 = L_.cuorb_kernel_launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record(sL)
-    for _ in range(args.steps):
-        step_resident(eL, eR)
+    evj = torch.cuda.Event()
+    ev0.record(sL)                      # every stream is idle here (barrier above)
+    for i in range(args.steps):
+        step_resident(*pairs[i & 1])
+    evj.record(sL1)                     # a pair's left stream ends with the stereo match, which waited for the right one
+    sL.wait_event(evj)
     ev1.record(sL)
-    eL.sync(); eR.sync()
+    for p in pairs:
+        p[0].sync(); p[1].sync()
     barrier()
     launches = L_.cuorb_kernel_launch_count() - launches0
     ms_resident = ev0.elapsed_time(ev1)

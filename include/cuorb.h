@@ -141,7 +141,9 @@ int cuorb_extractor_download_candidates(cuorb_extractor* ext, int image_index, i
 
 /* Device-resident form: matches the last batch extracted on `left` against the last batch on
  * `right` (same n_images, kps/descriptors/pyramids still on the device).  Enqueued on left's
- * stream after right's work.  mb/mbf: Frame::mb, Frame::mbf (src/Frame.cc:257). */
+ * stream after right's work; whatever is enqueued on `right` afterwards (its next extraction
+ * overwrites the buffers the match reads) is ordered behind the match, so no host synchronisation
+ * is needed between steps.  mb/mbf: Frame::mb, Frame::mbf (src/Frame.cc:257). */
 int cuorb_stereo_match_batch_async(cuorb_extractor* left, cuorb_extractor* right, float mb,
                                    float mbf);
 /* mvuRight / mvDepth (src/Frame.cc:945-946) of the last stereo batch: n_images*capacity floats

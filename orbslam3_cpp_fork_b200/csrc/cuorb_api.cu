@@ -849,6 +849,9 @@ int cuorb_stereo_match_batch_async(cuorb_extractor* l, cuorb_extractor* r, float
   if (l->profiling) { cudaEventRecord(l->ev_stage[CUORB_STAGE_COUNT], l->stream); l->stereo_timed = true; }
   CUORB_CUDA_TRY(cudaGetLastError());
   CUORB_CUDA_TRY(cudaEventRecord(l->ev_done, l->stream));
+  // the match reads the right handle's pyramid, keypoints and descriptors: whatever is enqueued on the
+  // right handle next (its next extraction overwrites them) has to wait for it
+  CUORB_CUDA_TRY(cudaStreamWaitEvent(r->stream, l->ev_done, 0));
   l->have_stereo = true;
   return CUORB_OK;
 }

@@ -122,6 +122,33 @@ def test_large_batch_idempotent(cu):
     assert_extract_equal(k1[63, :c1[63]], d1[63, :c1[63]], ko, do)
 
 
+def test_stereo_match_then_next_extraction_is_ordered(cu):
+    """The async stereo match reads the RIGHT handle's pyramid / keypoints / descriptors on the LEFT
+    handle's stream; an extraction enqueued on the right handle straight afterwards (no host sync)
+    must not overwrite them under the match (cuorb.h: cuorb_stereo_match_batch_async)."""
+    w, h, nb = 752, 480, 32
+    pairs = [synth.synth_stereo_pair(w, h, 300 + i) for i in range(4)]
+    Ls = np.stack([pairs[i % 4][0] for i in range(nb)]); Rs = np.stack([pairs[i % 4][1] for i in range(nb)])
+    other = np.stack([synth.synth_image(w, h, 900 + (i % 3)) for i in range(nb)])
+    eL = cu.ORBextractor(1000, max_width=w, max_height=h, max_batch=nb)
+    eR = cu.ORBextractor(1000, max_width=w, max_height=h, max_batch=nb)
+    m = cu.ORBmatcher()
+    mb, mbf = 47.906 / 458.654, 47.906
+    eL.extract_batch_async(Ls); eR.extract_batch_async(Rs)
+    eL.sync(); eR.sync()
+    u0, d0 = m.SearchStereo(eL, eR, mb, mbf)                       # reference run, fully synchronised
+    from orbslam3_cpp_fork_b200 import _lib
+    L_ = _lib.load()
+    for _ in range(5):
+        eL.extract_batch_async(Ls); eR.extract_batch_async(Rs)
+        _lib.check(L_.cuorb_stereo_match_batch_async(eL.handle, eR.handle, mb, mbf))
+        eR.extract_batch_async(other)                              # would race with the match if unordered
+        u = np.zeros_like(u0); d = np.zeros_like(d0)
+        _lib.check(L_.cuorb_stereo_fetch(eL.handle, _lib.ptr(u), _lib.ptr(d), eL.capacity, None, None, None))
+        eR.sync()
+        assert (u == u0).all() and (d == d0).all()
+
+
 @pytest.mark.parametrize("w,h,nf,seed,fx,mbf", [(752, 480, 1000, 11, 458.654, 47.906), (1241, 376, 2000, 12, 718.856, 386.1448)])
 def test_stereo_parity(cu, w, h, nf, seed, fx, mbf):
     L, R = synth.synth_stereo_pair(w, h, seed)
