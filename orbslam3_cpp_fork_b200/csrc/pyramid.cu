@@ -209,23 +209,31 @@ __global__ void __launch_bounds__(PYR_TX) k_pyr_resize(const ExtractorGeom* __re
 //   wtab[2*word]   = {window byte offset (4-aligned), funnel shift (bits), sel0 | sel1 << 16, sel2 | sel3 << 16}
 //   wtab[2*word+1] = {a0 | a1 << 16} for the four columns
 // blockDim.x = the row's word count rounded up to whole warps (at most PYR_TAB_TX), so few lanes idle
-// on the narrow levels; `rs` = output rows per strip (<= PYR_RS), shorter on the small levels so their
-// grids still cover several waves.
+// on the narrow levels; `rs` = output rows per strip (<= PYR_RS).
+// The row loop is written for instruction count (the kernel is issue bound, not DRAM bound): one
+// 16-byte shared-memory record per output row {source row offsets, advance, vertical weights}, 32-bit
+// offsets from two base pointers, border rows on a rare uniform path, and the two horizontal-sum
+// register sets swap roles by code duplication (state A: H0 = upper row; state B: H1 = upper row)
+// instead of register copies.
 __global__ void __launch_bounds__(PYR_TAB_TX, 1536 / PYR_TAB_TX) k_pyr_resize_tab(const ExtractorGeom* __restrict__ dg, int level,
                                                            uint8_t* __restrict__ pyr,
                                                            const uint4* __restrict__ wtab,
                                                            const ResizeTap* __restrict__ ytab, int rs) {
-  __shared__ int s_ys[PYR_RS];
-  __shared__ unsigned s_b0[PYR_RS], s_b1[PYR_RS];
+  // per output row of the strip: {offset of source row s | advance from the previous row (0, 1, 2 = reload both),
+  //                               offset of source row s+1, b0 << 16, b1 << 16}; offsets in bytes, rows clipped to sh-1
+  __shared__ uint4 s_rec[PYR_RS];
   const LevelGeom& L = dg->lv[level];
   const LevelGeom& S = dg->lv[level - 1];
   const int lh = L.h;
-  const int y0 = blockIdx.y * rs, y1 = min(y0 + rs, lh);
-  if ((int)threadIdx.x < rs && y0 + (int)threadIdx.x < lh) {
-    const ResizeTap t = ytab[L.ytab_off + y0 + threadIdx.x];
-    s_ys[threadIdx.x] = max((int)t.s, 0);
-    s_b0[threadIdx.x] = (unsigned)t.a0 << 16;
-    s_b1[threadIdx.x] = (unsigned)t.a1 << 16;
+  const int y0 = blockIdx.y * rs, n = min(rs, lh - y0);
+  if ((int)threadIdx.x < n) {
+    const ResizeTap* yt = ytab + L.ytab_off + y0 + threadIdx.x;
+    const ResizeTap t = yt[0];
+    const int sy = max((int)t.s, 0), sh1 = S.h - 1;
+    const int prev = threadIdx.x == 0 ? -4 : max((int)yt[-1].s, 0);
+    const unsigned adv = (unsigned)min(max(sy - prev, 0), 2);
+    s_rec[threadIdx.x] = make_uint4((unsigned)(min(sy, sh1) * S.pitch) | adv, (unsigned)(min(sy + 1, sh1) * S.pitch),
+                                    (unsigned)t.a0 << 16, (unsigned)t.a1 << 16);
   }
   __syncthreads();
   const int word = blockIdx.x * blockDim.x + threadIdx.x;
@@ -233,12 +241,12 @@ __global__ void __launch_bounds__(PYR_TAB_TX, 1536 / PYR_TAB_TX) k_pyr_resize_ta
   const uint4 e0 = __ldg(&wtab[2 * word]), cf = __ldg(&wtab[2 * word + 1]);
   uint8_t* base = pyr + (size_t)blockIdx.z * dg->pyr_img_stride;
   const uint8_t* src = base + S.pix_off + e0.x;
-  const int spitch = S.pitch, sh1 = S.h - 1, dp4 = L.pitch >> 2;
-  unsigned* dst = reinterpret_cast<unsigned*>(base + L.plane_off) + word;
+  const unsigned dp = (unsigned)L.pitch;
+  uint8_t* dst = base + L.plane_off + 4 * (size_t)word;               // padded row 0 of this word column
   const unsigned shift = e0.y, sel0 = e0.z & 0xFFFFu, sel1 = e0.z >> 16, sel2 = e0.w & 0xFFFFu, sel3 = e0.w >> 16;
 
-  auto fetch = [&](int sy, unsigned (&w)[3]) {
-    const unsigned* p = reinterpret_cast<const unsigned*>(src + (size_t)min(sy, sh1) * spitch);  // OpenCV clips rows to sh-1
+  auto fetch = [&](unsigned off, unsigned (&w)[3]) {
+    const unsigned* p = reinterpret_cast<const unsigned*>(src + off);
     w[0] = p[0]; w[1] = p[1]; w[2] = p[2];
   };
   auto hsum4 = [&](const unsigned (&w)[3], unsigned (&h)[4]) {
@@ -248,33 +256,59 @@ __global__ void __launch_bounds__(PYR_TAB_TX, 1536 / PYR_TAB_TX) k_pyr_resize_ta
     h[2] = __dp2a_lo(cf.z, __byte_perm(X0, X1, sel2), 0u) >> 4;
     h[3] = __dp2a_lo(cf.w, __byte_perm(X0, X1, sel3), 0u) >> 4;
   };
-  // software pipeline: the source rows the NEXT output row needs are requested before the current
-  // row is blended and stored
-  unsigned hA[4], hB[4], rA[3], rB[3];
-  int s = s_ys[0];
-  fetch(s, rA); fetch(s + 1, rB);
-  hsum4(rA, hA); hsum4(rB, hB);
-  for (int y = y0; y < y1; y++) {
-    const int sN = y + 1 < y1 ? s_ys[y + 1 - y0] : s;
-    const int adv = sN - s;
-    if (adv != 0) {
-      fetch(sN + 1, rB);
-      if (adv != 1) fetch(sN, rA);
-    }
-    const unsigned out = vblend(hA, hB, s_b0[y - y0], s_b1[y - y0]);
-    dst[(size_t)(y + EDGE_THRESHOLD) * dp4] = out;
-    if (y >= 1 && y <= EDGE_THRESHOLD) dst[(size_t)(EDGE_THRESHOLD - y) * dp4] = out;
-    if (y >= lh - 1 - EDGE_THRESHOLD && y <= lh - 2) dst[(size_t)(2 * lh + EDGE_THRESHOLD - 2 - y) * dp4] = out;
-    if (adv != 0) {
-      if (adv == 1) {
+  // ((b0*hA)>>16 + (b1*hB)>>16 + 2) >> 2 per column; two columns share one shift (sums are 10-bit)
+  auto blend = [&](const unsigned (&hA)[4], const unsigned (&hB)[4], unsigned b0s, unsigned b1s) -> unsigned {
+    unsigned v[4];
 #pragma unroll
-        for (int b = 0; b < 4; b++) hA[b] = hB[b];
-      } else {
-        hsum4(rA, hA);
+    for (int b = 0; b < 4; b++) v[b] = __umulhi(b0s, hA[b]) + __umulhi(b1s, hB[b]) + 2u;
+    const unsigned lo = (v[0] | (v[1] << 16)) >> 2, hi = (v[2] | (v[3] << 16)) >> 2;
+    return __byte_perm(lo, hi, 0x6420);
+  };
+
+  unsigned H0[4], H1[4], rA[3], rB[3];
+  uint4 rec = s_rec[0];
+  fetch(rec.x & ~3u, rA); fetch(rec.y, rB);
+  hsum4(rA, H0); hsum4(rB, H1);
+  int i = 0;
+  unsigned doff = (unsigned)(y0 + EDGE_THRESHOLD) * dp;               // byte offset of the padded output row
+  const bool edge_strip = y0 <= EDGE_THRESHOLD || y0 + n >= lh - 1 - EDGE_THRESHOLD;   // strip touches rows that are mirrored into the border
+  // one output row: request the next row's sources, blend + store the current one, then fold the
+  // new sources into the register set that held the retired upper row.  Returns the advance.
+  auto row = [&](unsigned (&hA)[4], unsigned (&hB)[4]) -> unsigned {
+    const unsigned b0s = rec.z, b1s = rec.w;
+    unsigned adv = 0;
+    if (i + 1 < n) {
+      rec = s_rec[i + 1];
+      adv = rec.x & 3u;
+      if (adv != 0) {
+        fetch(rec.y, rB);
+        if (adv == 2) fetch(rec.x & ~3u, rA);
       }
-      hsum4(rB, hB);
     }
-    s = sN;
+    const unsigned out = blend(hA, hB, b0s, b1s);
+    *reinterpret_cast<unsigned*>(dst + doff) = out;
+    if (edge_strip) {
+      const int y = y0 + i;
+      if (y >= 1 && y <= EDGE_THRESHOLD) *reinterpret_cast<unsigned*>(dst + (unsigned)(EDGE_THRESHOLD - y) * dp) = out;
+      if (y >= lh - 1 - EDGE_THRESHOLD && y <= lh - 2) *reinterpret_cast<unsigned*>(dst + (unsigned)(2 * lh + EDGE_THRESHOLD - 2 - y) * dp) = out;
+    }
+    doff += dp;
+    i++;
+    if (adv == 1) hsum4(rB, hA);                       // hB (row s+1) becomes the upper row: roles swap
+    else if (adv == 2) { hsum4(rA, hA); hsum4(rB, hB); }
+    return adv;
+  };
+  for (;;) {
+    // state A: H0 = source row s, H1 = row s+1
+    const unsigned a = row(H0, H1);
+    if (i >= n) return;
+    if (a != 1) continue;
+    // state B: H1 = source row s, H0 = row s+1
+    for (;;) {
+      const unsigned b = row(H1, H0);
+      if (i >= n) return;
+      if (b == 1) break;
+    }
   }
 }
 
