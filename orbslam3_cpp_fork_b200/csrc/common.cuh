@@ -93,9 +93,19 @@ enum { FLAG_CAND_OVERFLOW = 1, FLAG_NODE_OVERFLOW = 2, FLAG_KEY_OVERFLOW = 4 };
 
 // ---- kernel launchers (one per stage; all asynchronous on `st`) ----
 void build_resize_words(const ExtractorGeom& g, const std::vector<ResizeTap>& xtab, std::vector<uint4>& wt, int* off);
+// launch plan of the staged resize kernel (k_pyr_resize_stage) for one level; tx == 0: not usable there
+constexpr int PYR_MAX_COLBLOCKS = 4;
+struct PyrPlan {
+  int tx = 0, nb = 0;     // CTA width (threads = output words), CTAs per output row
+  int max_rows = 0;       // source rows a strip can need
+  int smem = 0;           // dynamic shared memory per CTA
+  int xlo[PYR_MAX_COLBLOCKS] = {}, tw[PYR_MAX_COLBLOCKS] = {};   // per column block: first staged source byte (16-aligned), staged bytes per row
+};
+void build_pyr_plan(const ExtractorGeom& g, const std::vector<uint4>& wt, const int* wtab_off,
+                    const std::vector<ResizeTap>& ytab, PyrPlan* plan);
 void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8_t* imgs, int w, int h,
                     size_t stride, size_t image_stride, int n_img, uint8_t* pyr, const ResizeTap* xtab,
-                    const ResizeTap* ytab, const uint4* wtab, const int* wtab_off, cudaStream_t st);
+                    const ResizeTap* ytab, const uint4* wtab, const int* wtab_off, const PyrPlan* plan, cudaStream_t st);
 void build_blur_tiles(const ExtractorGeom& g, std::vector<int4>& tiles);
 void launch_blur(const ExtractorGeom* g, const ExtractorGeom* dg, int n_img, const int4* tiles,
                  int n_tiles, const uint8_t* pyr, uint8_t* blur, cudaStream_t st);

@@ -45,6 +45,7 @@ struct cuorb_extractor {
   ResizeTap *d_xtab = nullptr, *d_ytab = nullptr;
   uint4*     d_wtab = nullptr;        // per-word horizontal tap tables of k_pyr_resize_tab
   int        wtab_off[MAX_LEVELS];
+  PyrPlan    pyr_plan[MAX_LEVELS];    // staged resize kernel: CTA shape and staged source window per level
   size_t     cap_wtab = 0;
   int4*      d_blur_tiles = nullptr;
   TmaMaps    tmaps;                   // TMA tensor maps of the pyramid / blurred planes (per level), passed as __grid_constant__
@@ -284,6 +285,7 @@ static int set_size(cuorb_extractor* e, int w, int h) {
     build_resize_words(g, xt, wt, e->wtab_off);
     if (wt.size() > e->cap_wtab) { set_error("internal: resize word tables exceed the arena"); return CUORB_E_CAPACITY; }
     if (!wt.empty()) CUORB_CUDA_TRY(cudaMemcpy(e->d_wtab, wt.data(), wt.size() * sizeof(uint4), cudaMemcpyHostToDevice));
+    build_pyr_plan(g, wt, e->wtab_off, yt, e->pyr_plan);
   }
   CUORB_CUDA_TRY(cudaMemcpy(e->d_blur_tiles, tiles.data(), tiles.size() * sizeof(int4), cudaMemcpyHostToDevice));
   e->n_blur_tiles = (int)tiles.size();
@@ -483,7 +485,7 @@ static int enqueue_pipeline(cuorb_extractor* e, int n_images, const uint8_t* dim
   CUORB_CUDA_TRY(cudaMemsetAsync(e->d_flags, 0, 2 * sizeof(int), st));  // [0] overflow flags, [1] FAST work counter
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_PYRAMID], st);
   launch_pyramid(e->g, e->d_geom, dimgs, width, height, dstride, dimg_stride, n_images, e->d_pyr, e->d_xtab, e->d_ytab,
-                 e->d_wtab, e->wtab_off, st);
+                 e->d_wtab, e->wtab_off, e->pyr_plan, st);
   // FAST (integer-ALU bound, 20 warps per SM) and the blur (FMA pipe + loads) both depend only on the
   // pyramid: outside profiling runs the blur goes to the side stream, after FAST in launch order so
   // FAST's CTAs get their shared memory first and blur CTAs fill the remaining warp slots of each SM

@@ -16,6 +16,7 @@
 #include <cstdlib>
 
 #include "common.cuh"
+#include "tma.cuh"
 
 namespace cuorb {
 
@@ -47,7 +48,20 @@ __global__ void __launch_bounds__(256) k_pyr_level0(const ExtractorGeom* __restr
   for (int b = 0; b < 4; b++)
     xs[b] = reflect101(min(max(xw + b, -EDGE_THRESHOLD), L.w + EDGE_THRESHOLD - 1), L.w);  // pad bytes: clamp
   const int y0 = blockIdx.y * PYR_RS, y1 = min(y0 + PYR_RS, L.h);
-  // all loads of the strip first (16 independent requests in flight), then the stores
+  const int dp4 = L.pitch >> 2;
+  unsigned* drow = reinterpret_cast<unsigned*>(dst) + word;
+  // common case (aligned interior word, full strip away from the mirrored rows): pointer-increment copy,
+  // all loads of the strip issued before the stores
+  if (inner && y0 > EDGE_THRESHOLD && y0 + PYR_RS < L.h - 1 - EDGE_THRESHOLD) {
+    const uint8_t* sp = src + (size_t)y0 * stride + xw;
+    unsigned v[PYR_RS];
+#pragma unroll
+    for (int r = 0; r < PYR_RS; r++, sp += stride) v[r] = __ldg(reinterpret_cast<const unsigned*>(sp));
+    unsigned* dpz = drow + (size_t)(y0 + EDGE_THRESHOLD) * dp4;
+#pragma unroll
+    for (int r = 0; r < PYR_RS; r++, dpz += dp4) *dpz = v[r];
+    return;
+  }
   unsigned v[PYR_RS];
 #pragma unroll
   for (int r = 0; r < PYR_RS; r++) {
@@ -59,8 +73,6 @@ __global__ void __launch_bounds__(256) k_pyr_level0(const ExtractorGeom* __restr
              ((unsigned)__ldg(srow + xs[2]) << 16) | ((unsigned)__ldg(srow + xs[3]) << 24);
     }
   }
-  unsigned* drow = reinterpret_cast<unsigned*>(dst) + word;
-  const int dp4 = L.pitch >> 2;
 #pragma unroll
   for (int r = 0; r < PYR_RS; r++) {
     const int y = y0 + r;
@@ -312,6 +324,162 @@ __global__ void __launch_bounds__(PYR_TAB_TX, 1536 / PYR_TAB_TX) k_pyr_resize_ta
   }
 }
 
+// ---- staged variant: the strip's source rows arrive in shared memory by bulk async copies ----
+// Same arithmetic and row loop as k_pyr_resize_tab, but the CTA first stages every source row its strip
+// needs (rows s_first .. s_last+1, clipped to the last row; bytes [xlo, xlo + tw) of each) with one
+// cp.async.bulk per row, all in flight at once and signalled on one mbarrier.  The register variant keeps
+// ~1 row (12 bytes) per thread in flight, far too little to cover DRAM latency at 1536 threads per SM; here
+// a CTA has ~20 rows x ~700 bytes outstanding and the row loop only touches shared memory.
+struct PyrCols { int xlo[PYR_MAX_COLBLOCKS], tw[PYR_MAX_COLBLOCKS]; };
+
+__global__ void __launch_bounds__(PYR_TAB_TX, 1536 / PYR_TAB_TX) k_pyr_resize_stage(const ExtractorGeom* __restrict__ dg, int level,
+                                                           uint8_t* __restrict__ pyr,
+                                                           const uint4* __restrict__ wtab,
+                                                           const ResizeTap* __restrict__ ytab, int rs,
+                                                           const PyrCols pc) {
+  extern __shared__ __align__(128) unsigned char s_tile[];
+  __shared__ uint4 s_rec[PYR_RS];   // as in k_pyr_resize_tab, offsets relative to the staged tile
+  __shared__ uint64_t s_bar;
+  const LevelGeom& L = dg->lv[level];
+  const LevelGeom& S = dg->lv[level - 1];
+  const int lh = L.h, sh1 = S.h - 1;
+  const int y0 = blockIdx.y * rs, n = min(rs, lh - y0);
+  int tw = pc.tw[0], xlo = pc.xlo[0];
+#pragma unroll
+  for (int b = 1; b < PYR_MAX_COLBLOCKS; b++)
+    if ((int)blockIdx.x == b) { tw = pc.tw[b]; xlo = pc.xlo[b]; }   // (constant-bank reads; a dynamic index would spill the struct)
+  const ResizeTap* yt = ytab + L.ytab_off + y0;
+  const int r_first = max((int)yt[0].s, 0), n_rows = max((int)yt[n - 1].s, 0) + 2 - r_first;
+  uint8_t* base = pyr + (size_t)blockIdx.z * dg->pyr_img_stride;
+  if (threadIdx.x == 0) {
+    mbar_init(&s_bar, 1);
+    mbar_fence_init();
+  }
+  if ((int)threadIdx.x < n) {
+    const ResizeTap t = yt[threadIdx.x];
+    const int sy = max((int)t.s, 0);
+    const int prev = threadIdx.x == 0 ? -4 : max((int)yt[(int)threadIdx.x - 1].s, 0);
+    const unsigned adv = (unsigned)min(max(sy - prev, 0), 2);
+    s_rec[threadIdx.x] = make_uint4((unsigned)((sy - r_first) * tw) | adv, (unsigned)((sy + 1 - r_first) * tw),
+                                    (unsigned)t.a0 << 16, (unsigned)t.a1 << 16);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) mbar_expect_tx(&s_bar, (unsigned)(n_rows * tw));
+  {
+    const uint8_t* srow0 = base + S.pix_off + xlo;
+    for (int j = threadIdx.x; j < n_rows; j += blockDim.x)
+      bulk_load_1d(s_tile + j * tw, srow0 + (size_t)min(r_first + j, sh1) * S.pitch, (unsigned)tw, &s_bar);
+  }
+  const int word = blockIdx.x * blockDim.x + threadIdx.x;
+  if (word * 4 >= L.pitch) return;
+  const uint4 e0 = __ldg(&wtab[2 * word]), cf = __ldg(&wtab[2 * word + 1]);
+  const unsigned char* src = s_tile + ((int)e0.x - xlo);
+  const unsigned dp = (unsigned)L.pitch;
+  uint8_t* dst = base + L.plane_off + 4 * (size_t)word;               // padded row 0 of this word column
+  const unsigned shift = e0.y, sel0 = e0.z & 0xFFFFu, sel1 = e0.z >> 16, sel2 = e0.w & 0xFFFFu, sel3 = e0.w >> 16;
+
+  auto fetch = [&](unsigned off, unsigned (&w)[3]) {
+    const unsigned* p = reinterpret_cast<const unsigned*>(src + off);
+    w[0] = p[0]; w[1] = p[1]; w[2] = p[2];
+  };
+  auto hsum4 = [&](const unsigned (&w)[3], unsigned (&h)[4]) {
+    const unsigned X0 = __funnelshift_r(w[0], w[1], shift), X1 = __funnelshift_r(w[1], w[2], shift);
+    h[0] = __dp2a_lo(cf.x, __byte_perm(X0, X1, sel0), 0u) >> 4;
+    h[1] = __dp2a_lo(cf.y, __byte_perm(X0, X1, sel1), 0u) >> 4;
+    h[2] = __dp2a_lo(cf.z, __byte_perm(X0, X1, sel2), 0u) >> 4;
+    h[3] = __dp2a_lo(cf.w, __byte_perm(X0, X1, sel3), 0u) >> 4;
+  };
+  auto blend = [&](const unsigned (&hA)[4], const unsigned (&hB)[4], unsigned b0s, unsigned b1s) -> unsigned {
+    unsigned v[4];
+#pragma unroll
+    for (int b = 0; b < 4; b++) v[b] = __umulhi(b0s, hA[b]) + __umulhi(b1s, hB[b]) + 2u;
+    const unsigned lo = (v[0] | (v[1] << 16)) >> 2, hi = (v[2] | (v[3] << 16)) >> 2;
+    return __byte_perm(lo, hi, 0x6420);
+  };
+
+  unsigned H0[4], H1[4], rA[3], rB[3];
+  uint4 rec = s_rec[0];
+  mbar_wait(&s_bar, 0u);
+  fetch(rec.x & ~3u, rA); fetch(rec.y, rB);
+  hsum4(rA, H0); hsum4(rB, H1);
+  int i = 0;
+  unsigned doff = (unsigned)(y0 + EDGE_THRESHOLD) * dp;
+  const bool edge_strip = y0 <= EDGE_THRESHOLD || y0 + n >= lh - 1 - EDGE_THRESHOLD;
+  auto row = [&](unsigned (&hA)[4], unsigned (&hB)[4]) -> unsigned {
+    const unsigned b0s = rec.z, b1s = rec.w;
+    unsigned adv = 0;
+    if (i + 1 < n) {
+      rec = s_rec[i + 1];
+      adv = rec.x & 3u;
+      if (adv != 0) {
+        fetch(rec.y, rB);
+        if (adv == 2) fetch(rec.x & ~3u, rA);
+      }
+    }
+    const unsigned out = blend(hA, hB, b0s, b1s);
+    *reinterpret_cast<unsigned*>(dst + doff) = out;
+    if (edge_strip) {
+      const int y = y0 + i;
+      if (y >= 1 && y <= EDGE_THRESHOLD) *reinterpret_cast<unsigned*>(dst + (unsigned)(EDGE_THRESHOLD - y) * dp) = out;
+      if (y >= lh - 1 - EDGE_THRESHOLD && y <= lh - 2) *reinterpret_cast<unsigned*>(dst + (unsigned)(2 * lh + EDGE_THRESHOLD - 2 - y) * dp) = out;
+    }
+    doff += dp;
+    i++;
+    if (adv == 1) hsum4(rB, hA);
+    else if (adv == 2) { hsum4(rA, hA); hsum4(rB, hB); }
+    return adv;
+  };
+  for (;;) {
+    const unsigned a = row(H0, H1);
+    if (i >= n) return;
+    if (a != 1) continue;
+    for (;;) {
+      const unsigned b = row(H1, H0);
+      if (i >= n) return;
+      if (b == 1) break;
+    }
+  }
+}
+
+// host: CTA shape and staged source window per level for k_pyr_resize_stage
+void build_pyr_plan(const ExtractorGeom& g, const std::vector<uint4>& wt, const int* wtab_off,
+                    const std::vector<ResizeTap>& ytab, PyrPlan* plan) {
+  for (int l = 0; l < MAX_LEVELS; l++) plan[l] = PyrPlan();
+  for (int l = 1; l < g.nlevels; l++) {
+    if (wtab_off[l] < 0) continue;
+    const LevelGeom& L = g.lv[l];
+    const LevelGeom& S = g.lv[l - 1];
+    PyrPlan p;
+    const int words = L.pitch / 4;
+    p.nb = (words + PYR_TAB_TX - 1) / PYR_TAB_TX;
+    if (p.nb > PYR_MAX_COLBLOCKS) continue;
+    p.tx = (((words + p.nb - 1) / p.nb) + 31) / 32 * 32;
+    int tw_max = 0;
+    bool ok = true;
+    for (int b = 0; b < p.nb; b++) {
+      int lo = 1 << 30, hi = 0;
+      for (int w = b * p.tx; w < std::min((b + 1) * p.tx, words); w++) {
+        const int x = (int)wt[(size_t)wtab_off[l] + 2 * w].x;
+        lo = std::min(lo, x); hi = std::max(hi, x + 12);
+      }
+      if (lo > hi) { lo = 0; hi = 16; }                       // column block without words (cannot happen: nb = ceil)
+      p.xlo[b] = lo & ~15;
+      // never past the end of the padded source row (the bytes a capped window loses are not selected by any tap)
+      p.tw[b] = std::min((hi - p.xlo[b] + 15) & ~15, S.pitch - ROW_LEAD - p.xlo[b]);
+      if (p.tw[b] <= 0) ok = false;
+      tw_max = std::max(tw_max, p.tw[b]);
+    }
+    for (int y0 = 0; y0 < L.h; y0 += PYR_RS) {
+      const int n = std::min(PYR_RS, L.h - y0);
+      const int first = std::max((int)ytab[L.ytab_off + y0].s, 0), last = std::max((int)ytab[L.ytab_off + y0 + n - 1].s, 0) + 1;
+      p.max_rows = std::max(p.max_rows, last - first + 1);
+    }
+    p.smem = p.max_rows * tw_max + 16;
+    if (!ok || p.smem > 64 * 1024) continue;
+    plan[l] = p;
+  }
+}
+
 // host: per-word tables for k_pyr_resize_tab, levels 1..n-1 back to back; off[l] = first entry (in
 // uint4) of level l, or -1 when the level needs the byte-load kernel (window wider than 8 bytes)
 void build_resize_words(const ExtractorGeom& g, const std::vector<ResizeTap>& xtab, std::vector<uint4>& wt, int* off) {
@@ -348,7 +516,7 @@ void build_resize_words(const ExtractorGeom& g, const std::vector<ResizeTap>& xt
 void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8_t* imgs, int, int,
                     size_t stride, size_t image_stride, int n_img, uint8_t* pyr,
                     const ResizeTap* xtab, const ResizeTap* ytab, const uint4* wtab, const int* wtab_off,
-                    cudaStream_t st) {
+                    const PyrPlan* plan, cudaStream_t st) {
   const int aligned = (((uintptr_t)imgs | stride | image_stride) & 3) == 0;
   for (int l = 0; l < g.nlevels; l++) {
     const LevelGeom& L = g.lv[l];
@@ -361,21 +529,22 @@ void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8
     } else {
       // four adjacent output columns span 3*scale + 2 source bytes (+3 for alignment): 12 bytes up to scale 2
       const double sx = (double)g.lv[l - 1].w / L.w;
-      if (wtab && wtab_off[l] >= 0) {
-        static const int flex = []() { const char* e = getenv("CUORB_PYR_FLEX"); return e ? atoi(e) : 1; }();
-        static const int rs_small = []() { const char* e = getenv("CUORB_PYR_RS_SMALL"); const int v = e ? atoi(e) : 8; return v >= 1 && v <= PYR_RS ? v : 8; }();
-        static const int min_waves = []() { const char* e = getenv("CUORB_PYR_WAVES"); return e ? atoi(e) : 4; }();
-        const int words = L.pitch / 4;
-        int tx = PYR_TX, rs = PYR_RS;
-        if (flex) {
-          const int nb = (words + PYR_TAB_TX - 1) / PYR_TAB_TX;            // CTAs per row
-          tx = (((words + nb - 1) / nb) + 31) / 32 * 32;
-          const long wave = 148L * (1536 / tx);
-          const long ctas = (long)((words + tx - 1) / tx) * ((L.h + PYR_RS - 1) / PYR_RS) * n_img;
-          if (ctas < min_waves * wave) rs = rs_small;
+      static const int staged = []() { const char* e = getenv("CUORB_PYR_STAGED"); return e ? atoi(e) : 0; }();
+      if (wtab && wtab_off[l] >= 0 && staged && plan && plan[l].tx > 0) {
+        const PyrPlan& p = plan[l];
+        PyrCols pc;
+        for (int b = 0; b < PYR_MAX_COLBLOCKS; b++) { pc.xlo[b] = p.xlo[b]; pc.tw[b] = p.tw[b]; }
+        static int attr = 48 * 1024;
+        if (p.smem > attr) {
+          cudaFuncSetAttribute(k_pyr_resize_stage, cudaFuncAttributeMaxDynamicSharedMemorySize, p.smem);
+          attr = p.smem;
         }
-        dim3 tgrid((words + tx - 1) / tx, (L.h + rs - 1) / rs, n_img);
-        k_pyr_resize_tab<<<tgrid, tx, 0, st>>>(dg, l, pyr, wtab + wtab_off[l], ytab, rs);
+        k_pyr_resize_stage<<<dim3(p.nb, (L.h + PYR_RS - 1) / PYR_RS, n_img), p.tx, p.smem, st>>>(dg, l, pyr, wtab + wtab_off[l], ytab, PYR_RS, pc);
+      } else if (wtab && wtab_off[l] >= 0) {
+        // CTA width = the row's word count split evenly over whole warps
+        const int words = L.pitch / 4, nb = (words + PYR_TAB_TX - 1) / PYR_TAB_TX;
+        const int tx = (((words + nb - 1) / nb) + 31) / 32 * 32;
+        k_pyr_resize_tab<<<dim3((words + tx - 1) / tx, (L.h + PYR_RS - 1) / PYR_RS, n_img), tx, 0, st>>>(dg, l, pyr, wtab + wtab_off[l], ytab, PYR_RS);
       }
       else if (3.0 * sx + 5.0 < 11.5) k_pyr_resize<false><<<grid, PYR_TX, 0, st>>>(dg, l, pyr, xtab, ytab);
       else k_pyr_resize<true><<<grid, PYR_TX, 0, st>>>(dg, l, pyr, xtab, ytab);

@@ -60,6 +60,12 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, u
       ::"r"(smem_u32(dst)), "l"((unsigned long long)map), "r"(smem_u32(bar)), "r"(x), "r"(y), "r"(z)
       : "memory");
 }
+// 1-D bulk copy global -> shared (both 16-byte aligned, bytes a multiple of 16), completion on an mbarrier
+__device__ __forceinline__ void bulk_load_1d(void* dst, const void* src, unsigned bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst)), "l"((unsigned long long)src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
 #endif
 
 // host: encode a rank-3 u8 map {x bytes, rows, images}; returns 0 on success
