@@ -1,71 +1,135 @@
 // K7 — 7x7 sigma-2 Gaussian blur of every pyramid level (replaces the per-level
 // clone() + cv::GaussianBlur(7x7, 2, 2, BORDER_REFLECT_101), src/ORBextractor.cc:1103-1104).
 // OpenCV's CV_8U path is fixed point: kernel {18,34,48,56,48,34,18}/256, rows in 8.8, columns in
-// 16.16, result (v + 32768) >> 16.  The REFLECT_101 halo is the border K1 already stored, so no
-// reflection is computed here.
+// 16.16, result (v + 32768) >> 16.  Nothing is rounded between the two passes, so the sum
+//   out = (sum_j k_j * sum_i k_i * p[y+j][x+i] + 32768) >> 16
+// may be evaluated in either order; this kernel runs the COLUMN pass first because both passes then
+// map onto the packed dot-product instructions.  The REFLECT_101 halo is the border K1 already
+// stored, so no reflection is computed here.
 //
-// One thread owns one aligned output word (4 px) and walks down a strip of rows, entirely in
-// registers: per source row three aligned 32-bit loads, the four 7-tap row sums as two DP4A each
-// on funnel-shifted words (taps {18,34,48,56} and {48,34,18,0}), and a rolling window of the last
-// seven row sums feeds the column pass (symmetric taps: 3 adds + 4 IMAD per pixel).  No shared
-// memory, no barriers; the loop is unrolled by 7 so the window rotates by register renaming.
-// Bound: HBM (read P, write P); ~14 instructions per pixel.
+// One lane owns one aligned output word (4 px) and walks down a strip in groups of four rows:
+//   * four source rows of its word are loaded and byte-transposed (8 PRMT), so each column's four
+//     vertically adjacent pixels share a register; a group's 7-tap column sums V (<= 255*256, 16 bit)
+//     are then 2-3 DP4A per pixel on three such blocks (two of them carried over from the previous
+//     group: every source row is loaded and transposed once);
+//   * V of adjacent columns is packed in u16 pairs; the pairs of the left and right neighbour word
+//     come from the neighbouring lanes (4 SHFL per row), and each output pixel is 4 DP2A on pairs
+//     with the 32768 rounding term as the accumulator seed.
+// About 10 instructions per pixel, against 16 (+29 % row halo) for a row-pass-first register
+// formulation.  Lanes 0 and 31 of a warp only supply halo columns, so a warp covers 30 output words.
+// No shared memory, no barriers.  Bound: issue slots (it runs beside k_fast_persist on a second
+// stream), then HBM (read P, write P).
 #include "common.cuh"
 
 namespace cuorb {
 
-constexpr int BL_THREADS = 64;   // words (4 px each) per CTA row segment
-constexpr int BL_ROWS    = 21;   // output rows per thread strip
+constexpr int BL_WARPS = 4;     // warps per CTA (each works on its own item)
+constexpr int BL_ROWS  = 32;    // output rows per strip (8 groups of 4)
+constexpr int BL_CHUNK = 30;    // output words per warp (lanes 1..30)
 
-__device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ row, unsigned (&h)[4]) {
-  const unsigned* p = reinterpret_cast<const unsigned*>(row);
-  const unsigned A = p[-1], B = p[0], C = p[1];
-  const unsigned K0 = 18u | (34u << 8) | (48u << 16) | (56u << 24), K1 = 48u | (34u << 8) | (18u << 16);
-  h[0] = __dp4a(__funnelshift_r(A, B, 8), K0, __dp4a(__funnelshift_r(B, C, 8), K1, 0u));
-  h[1] = __dp4a(__funnelshift_r(A, B, 16), K0, __dp4a(__funnelshift_r(B, C, 16), K1, 0u));
-  h[2] = __dp4a(__funnelshift_r(A, B, 24), K0, __dp4a(__funnelshift_r(B, C, 24), K1, 0u));
-  h[3] = __dp4a(B, K0, __dp4a(C, K1, 0u));
+namespace {
+
+// 4x4 byte transpose: r[j] = four pixels of source row j  ->  t[c] = column c's pixels of rows 0..3
+__device__ __forceinline__ void transpose4(const unsigned (&r)[4], unsigned (&t)[4]) {
+  const unsigned a = __byte_perm(r[0], r[1], 0x5140), b = __byte_perm(r[2], r[3], 0x5140);
+  const unsigned c = __byte_perm(r[0], r[1], 0x7362), d = __byte_perm(r[2], r[3], 0x7362);
+  t[0] = __byte_perm(a, b, 0x5410); t[1] = __byte_perm(a, b, 0x7632);
+  t[2] = __byte_perm(c, d, 0x5410); t[3] = __byte_perm(c, d, 0x7632);
 }
 
-// grid: (tiles over all levels, n_img); a tile = BL_THREADS consecutive (row strip, word) items of one
-// level, numbered strip-major, so only the last CTA of a level has idle lanes (a lane's neighbours may
-// belong to the next strip: both are contiguous row segments, still coalesced)
-__global__ void __launch_bounds__(BL_THREADS) k_blur(const ExtractorGeom* __restrict__ dg,
-                                                     const int4* __restrict__ tiles,
-                                                     const uint8_t* __restrict__ pyr,
-                                                     uint8_t* __restrict__ blur) {
-  const int4 t = tiles[blockIdx.x];   // {level, first item, words per row, items in the level}
-  const LevelGeom& L = dg->lv[t.x];
-  const int item = t.y + threadIdx.x;
+__host__ __device__ constexpr unsigned pk4(unsigned a, unsigned b, unsigned c, unsigned d) { return a | (b << 8) | (c << 16) | (d << 24); }
+
+}  // namespace
+
+// grid: (tiles over all levels, n_img); a tile = BL_WARPS consecutive items of one level, an item =
+// (row strip, chunk of BL_CHUNK words), numbered strip-major
+__global__ void __launch_bounds__(BL_WARPS * 32) k_blur(const ExtractorGeom* __restrict__ dg,
+                                                        const int4* __restrict__ tiles,
+                                                        const uint8_t* __restrict__ pyr,
+                                                        uint8_t* __restrict__ blur) {
+  const int4 t = tiles[blockIdx.x];   // {level, first item, chunks per row, items in the level}
+  const int lane = threadIdx.x & 31;
+  const int item = t.y + (threadIdx.x >> 5);
   if (item >= t.w) return;
-  const int strip = item / t.z, word = item - strip * t.z;
+  const LevelGeom& L = dg->lv[t.x];
+  const int strip = item / t.z, chunk = item - strip * t.z;
+  const int words = L.bpitch >> 2;
+  const int word = chunk * BL_CHUNK + lane - 1;                 // -1 .. words: lanes 0 / 31 are halo columns
   const int img = blockIdx.y;
   const int y0 = strip * BL_ROWS, y1 = min(y0 + BL_ROWS, L.h);
-  const uint8_t* src = pyr + (size_t)img * dg->pyr_img_stride + L.pix_off + word * 4;
-  uint8_t* dst = blur + (size_t)img * dg->blur_img_stride + L.blur_off + word * 4;
-  const int pitch = L.pitch, bpitch = L.bpitch;
+  const unsigned pitch = (unsigned)L.pitch, bpitch = (unsigned)L.bpitch;
+  // word `words` (first word right of the blurred plane) still lies inside the 19-px border of the source
+  const uint8_t* src = pyr + (size_t)img * dg->pyr_img_stride + L.pix_off + 4 * (ptrdiff_t)min(word, words) +
+                       (ptrdiff_t)(y0 - 3) * (ptrdiff_t)pitch;
+  uint8_t* dst = blur + (size_t)img * dg->blur_img_stride + L.blur_off + 4 * (ptrdiff_t)word + (size_t)y0 * bpitch;
+  const bool writer = lane >= 1 && lane <= BL_CHUNK && word < words;
 
-  unsigned win[7][4];  // row sums of source rows y-3 .. y+3
+  // column-pass weights for output row r of a group: block A holds source rows r0-3 .. r0, B r0+1 .. r0+4, C r0+5 .. r0+8
+  constexpr unsigned WA0 = pk4(18, 34, 48, 56), WB0 = pk4(48, 34, 18, 0);
+  constexpr unsigned WA1 = pk4(0, 18, 34, 48),  WB1 = pk4(56, 48, 34, 18);
+  constexpr unsigned WA2 = pk4(0, 0, 18, 34),   WB2 = pk4(48, 56, 48, 34), WC2 = pk4(18, 0, 0, 0);
+  constexpr unsigned WA3 = pk4(0, 0, 0, 18),    WB3 = pk4(34, 48, 56, 48), WC3 = pk4(34, 18, 0, 0);
+  // row-pass weights on u16 pairs (dp2a_lo uses bytes 0,1; dp2a_hi bytes 2,3)
+  constexpr unsigned H0 = pk4(0, 18, 34, 48);    // lo (0,18)   hi (34,48)
+  constexpr unsigned H1 = pk4(56, 48, 34, 18);   // lo (56,48)  hi (34,18)
+  constexpr unsigned H2 = pk4(18, 34, 48, 56);   // lo (18,34)  hi (48,56)
+  constexpr unsigned H3 = pk4(48, 34, 18, 0);    // lo (48,34)  hi (18,0)
+
+  auto load_block = [&](int first_row, unsigned (&tb)[4]) {   // rows relative to y0 - 3
+    unsigned r[4];
+    const uint8_t* p = src + (unsigned)first_row * pitch;
 #pragma unroll
-  for (int j = 0; j < 6; j++) blur_hrow(src + (ptrdiff_t)(y0 - 3 + j) * pitch, win[j]);
-  for (int yb = y0; yb < y1; yb += 7) {
+    for (int j = 0; j < 4; j++) r[j] = __ldg(reinterpret_cast<const unsigned*>(p + (unsigned)j * pitch));
+    transpose4(r, tb);
+  };
+
+  // one output row: column sums v[0..3] of this lane's word -> pairs -> neighbours' pairs -> 4 px
+  auto emit_row = [&](const unsigned (&v)[4], int y) {
+    const unsigned P0 = __byte_perm(v[0], v[1], 0x5410), P1 = __byte_perm(v[2], v[3], 0x5410);
+    const unsigned L0 = __shfl_up_sync(0xffffffffu, P0, 1), L1 = __shfl_up_sync(0xffffffffu, P1, 1);
+    const unsigned R0 = __shfl_down_sync(0xffffffffu, P0, 1), R1 = __shfl_down_sync(0xffffffffu, P1, 1);
+    // pixel c: taps V[c-3 .. c+3]; own columns 0..3 = P0, P1; left word -4..-1 = L0, L1; right word 4..7 = R0, R1
+    const unsigned a0 = __dp2a_lo(L0, H0, __dp2a_hi(L1, H0, __dp2a_lo(P0, H1, __dp2a_hi(P1, H1, 32768u))));
+    const unsigned a1 = __dp2a_lo(L1, H2, __dp2a_hi(P0, H2, __dp2a_lo(P1, H3, __dp2a_hi(R0, H3, 32768u))));
+    const unsigned a2 = __dp2a_lo(L1, H0, __dp2a_hi(P0, H0, __dp2a_lo(P1, H1, __dp2a_hi(R0, H1, 32768u))));
+    const unsigned a3 = __dp2a_lo(P0, H2, __dp2a_hi(P1, H2, __dp2a_lo(R0, H3, __dp2a_hi(R1, H3, 32768u))));
+    if (writer && y < y1)
+      *reinterpret_cast<unsigned*>(dst + (unsigned)(y - y0) * bpitch) =
+          __byte_perm(__byte_perm(a0, a1, 0x0062), __byte_perm(a2, a3, 0x0062), 0x5410);
+  };
+
+  // one group of four output rows starting at y; A, B, C as above
+  auto group = [&](const unsigned (&A)[4], const unsigned (&B)[4], const unsigned (&C)[4], int y) {
+    unsigned v[4];
 #pragma unroll
-    for (int u = 0; u < 7; u++) {
-      const int y = yb + u;
-      if (y < y1) {
-        // slot (u + 6) % 7 receives source row y + 3; the window then is slots u, u+1, ..., u+6 (mod 7)
-        blur_hrow(src + (ptrdiff_t)(y + 3) * pitch, win[(u + 6) % 7]);
-        unsigned out = 0;
+    for (int c = 0; c < 4; c++) v[c] = __dp4a(A[c], WA0, __dp4a(B[c], WB0, 0u));
+    emit_row(v, y);
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-          const unsigned acc = 32768u + 18u * (win[u][k] + win[(u + 6) % 7][k]) +
-                               34u * (win[(u + 1) % 7][k] + win[(u + 5) % 7][k]) +
-                               48u * (win[(u + 2) % 7][k] + win[(u + 4) % 7][k]) + 56u * win[(u + 3) % 7][k];
-          out |= (acc >> 16) << (8 * k);
-        }
-        *reinterpret_cast<unsigned*>(dst + (size_t)y * bpitch) = out;
-      }
-    }
+    for (int c = 0; c < 4; c++) v[c] = __dp4a(A[c], WA1, __dp4a(B[c], WB1, 0u));
+    emit_row(v, y + 1);
+#pragma unroll
+    for (int c = 0; c < 4; c++) v[c] = __dp4a(A[c], WA2, __dp4a(B[c], WB2, __dp4a(C[c], WC2, 0u)));
+    emit_row(v, y + 2);
+#pragma unroll
+    for (int c = 0; c < 4; c++) v[c] = __dp4a(A[c], WA3, __dp4a(B[c], WB3, __dp4a(C[c], WC3, 0u)));
+    emit_row(v, y + 3);
+  };
+
+  // the three blocks rotate through three register sets (no copies)
+  unsigned T0[4], T1[4], T2[4];
+  load_block(0, T0);
+  load_block(4, T1);
+  int row = 8;                         // next source row to load, relative to y0 - 3
+  for (int y = y0;;) {
+    load_block(row, T2); row += 4;
+    group(T0, T1, T2, y); y += 4;
+    if (y >= y1) break;
+    load_block(row, T0); row += 4;
+    group(T1, T2, T0, y); y += 4;
+    if (y >= y1) break;
+    load_block(row, T1); row += 4;
+    group(T2, T0, T1, y); y += 4;
+    if (y >= y1) break;
   }
 }
 
@@ -73,14 +137,15 @@ void build_blur_tiles(const ExtractorGeom& g, std::vector<int4>& v) {
   v.clear();
   for (int l = 0; l < g.nlevels; l++) {
     const int words = g.lv[l].bpitch / 4;
-    const int items = words * ((g.lv[l].h + BL_ROWS - 1) / BL_ROWS);
-    for (int i = 0; i < items; i += BL_THREADS) v.push_back(make_int4(l, i, words, items));
+    const int chunks = (words + BL_CHUNK - 1) / BL_CHUNK;
+    const int items = chunks * ((g.lv[l].h + BL_ROWS - 1) / BL_ROWS);
+    for (int i = 0; i < items; i += BL_WARPS) v.push_back(make_int4(l, i, chunks, items));
   }
 }
 
 void launch_blur(const ExtractorGeom*, const ExtractorGeom* dg, int n_img, const int4* tiles,
                  int n_tiles, const uint8_t* pyr, uint8_t* blur, cudaStream_t st) {
-  k_blur<<<dim3(n_tiles, n_img), BL_THREADS, 0, st>>>(dg, tiles, pyr, blur);
+  k_blur<<<dim3(n_tiles, n_img), BL_WARPS * 32, 0, st>>>(dg, tiles, pyr, blur);
   count_launch();
 }
 
