@@ -300,6 +300,7 @@ __global__ void __launch_bounds__(128) k_fast_cells(const ExtractorGeom* __restr
 //   rec[2c+1] = {plane x of tile column 0 (16-aligned) | plane row of tile row 0 << 16,  sp,  cand_off,  cand_cap}
 struct FastParams {
   const int4* recs; int n_cells; int total_work;
+  float inv_cells;   // 1 / n_cells (work item -> image, cell without an integer division)
   unsigned* cand; int* cand_count; int* flags; int* work_counter;
   unsigned long long cand_img_stride;
   int nlevels, ini_th, min_th;
@@ -312,11 +313,21 @@ __device__ __forceinline__ unsigned widen_even(unsigned h) { return __byte_perm(
 // bytes 1 of lo and 0 of hi (two zero-extended u16 loads two bytes apart) -> u16x2
 __device__ __forceinline__ unsigned widen_odd(unsigned lo, unsigned hi) { return __byte_perm(lo, hi, 0x2421); }
 
+// work item -> (image, cell): float reciprocal + one correction step each way (the quotient is an image
+// index < 65536, so the float estimate is off by at most one)
+__device__ __forceinline__ void split_work(int w, int n_cells, float inv, int& img, int& cell) {
+  int q = __float2int_rz(__fmul_rz(__int2float_rz(w), inv));
+  int r = w - q * n_cells;
+  if (r < 0) { q--; r += n_cells; }
+  if (r >= n_cells) { q++; r -= n_cells; }
+  img = q; cell = r;
+}
+
 template <int NW>
 __global__ void __launch_bounds__(32 * NW) k_fast_persist(const __grid_constant__ FastMaps maps, const FastParams P) {
   extern __shared__ unsigned char smem_raw[];
   __shared__ uint64_t s_bar[2];
-  __shared__ int s_next[2];
+  __shared__ int s_next[2], s_img[2], s_cell[2];
 
   // pointer arithmetic on the array (not an integer round trip) so the accesses stay LDS/STS, not generic LD/ST
   unsigned char* smem = smem_raw + ((128u - ((unsigned)__cvta_generic_to_shared(smem_raw) & 127u)) & 127u);
@@ -339,14 +350,15 @@ __global__ void __launch_bounds__(32 * NW) k_fast_persist(const __grid_constant_
   for (int i = tid; i < (P.score_bytes >> 1); i += NT) reinterpret_cast<unsigned*>(s_scores)[i] = 0;
   __syncthreads();
 
-  auto issue = [&](int work, int buf) {  // one thread
-    const int img = work / P.n_cells, cell = work - img * P.n_cells;
+  auto issue = [&](int img, int cell, int buf) {  // one thread
     const int lvl = __ldg(&P.recs[2 * cell].x) & 0xFF;
     const int org = __ldg(&P.recs[2 * cell + 1].x);
     mbar_expect_tx(&s_bar[buf], (unsigned)(FT_PITCH * P.box_rows));
     tma_load_3d(s_tiles + buf * P.tile_bytes, &maps.lv[lvl], &s_bar[buf], org & 0xFFFF, org >> 16, img);
   };
-  if (tid == 0) issue(w, 0);
+  int img, cell;
+  split_work(w, P.n_cells, P.inv_cells, img, cell);
+  if (tid == 0) issue(img, cell, 0);
 
   // items beyond the first come from a global counter (dynamic balance: cell cost varies 3x)
   for (int it = 0;; it++) {
@@ -355,11 +367,13 @@ __global__ void __launch_bounds__(32 * NW) k_fast_persist(const __grid_constant_
       const int nw = (int)gridDim.x + atomicAdd(P.work_counter, 1);
       s_next[buf ^ 1] = nw;
       if (nw < P.total_work) {
+        int ni, nc;
+        split_work(nw, P.n_cells, P.inv_cells, ni, nc);
+        s_img[buf ^ 1] = ni; s_cell[buf ^ 1] = nc;
         fence_proxy_async();  // the other buffer was read/written through the generic proxy one item ago
-        issue(nw, buf ^ 1);
+        issue(ni, nc, buf ^ 1);
       }
     }
-    const int img = w / P.n_cells, cell = w - img * P.n_cells;
     const int4 c0 = __ldg(&P.recs[2 * cell]), c1 = __ldg(&P.recs[2 * cell + 1]);
     const int level = c0.x & 0xFF, cx0 = (c0.x >> 8) & 0xFF, qf = (c0.x >> 16) & 0xFF, nq = (c0.x >> 24) & 0xFF;
     const int x0 = c0.y & 0xFFFF, y0 = c0.y >> 16, dw = c0.z & 0xFFFF, dh = c0.z >> 16;
@@ -486,6 +500,7 @@ __global__ void __launch_bounds__(32 * NW) k_fast_persist(const __grid_constant_
 
     w = s_next[buf ^ 1];
     if (w >= P.total_work) break;
+    img = s_img[buf ^ 1]; cell = s_cell[buf ^ 1];
   }
 }
 
@@ -566,7 +581,7 @@ bool fast_persist_supported(const ExtractorGeom& g) { return g.max_cell_w <= 54 
 void launch_fast_persist(const ExtractorGeom& g, const FastMaps& maps, const int4* recs, int n_cells, int n_img,
                          unsigned* cand, int* cand_count, int* flags, int* work_counter, cudaStream_t st) {
   FastParams P;
-  P.recs = recs; P.n_cells = n_cells; P.total_work = n_cells * n_img;
+  P.recs = recs; P.n_cells = n_cells; P.total_work = n_cells * n_img; P.inv_cells = 1.0f / (float)n_cells;
   P.cand = cand; P.cand_count = cand_count; P.flags = flags; P.work_counter = work_counter;
   P.cand_img_stride = g.cand_img_stride; P.nlevels = g.nlevels; P.ini_th = g.ini_th; P.min_th = g.min_th;
   P.box_rows    = g.max_cell_h + 6;
