@@ -382,8 +382,6 @@ __global__ void __launch_bounds__(32 * NW) k_fast_persist(const __grid_constant_
     const unsigned char* tile = s_tiles + buf * P.tile_bytes;
     // score tile of this item; the other one is still being cleared by slower warps of the previous item
     unsigned char* s_score = s_scores + buf * P.score_bytes;
-    unsigned* out = P.cand + (size_t)img * P.cand_img_stride + (unsigned)c1.z;
-    int* out_count = P.cand_count + img * P.nlevels + level;
     const unsigned* s_tile8 = reinterpret_cast<const unsigned*>(tile);
     mbar_wait(&s_bar[buf], (unsigned)((it >> 1) & 1));
 
@@ -479,6 +477,9 @@ __global__ void __launch_bounds__(32 * NW) k_fast_persist(const __grid_constant_
                         s > q[sp - 1] && s > q[sp] && s > q[sp + 1];
         const unsigned bal = __ballot_sync(0xffffffffu, lm);
         if (bal) {
+          // output addresses only here (the common iteration emits nothing)
+          unsigned* out = P.cand + (size_t)img * P.cand_img_stride + (unsigned)c1.z;
+          int* out_count = P.cand_count + img * P.nlevels + level;
           const int n = __popc(bal);
           int base = 0;
           if (lane == 0) base = atomicAdd(out_count, n);
