@@ -23,7 +23,7 @@
 
 namespace cuorb {
 
-constexpr int BL_WARPS = 4;     // warps per CTA (each works on its own item)
+constexpr int BL_WARPS = 1;     // one warp per CTA: every strip quantity is CTA-uniform, so loop control and the weights live on the uniform datapath
 constexpr int BL_ROWS  = 32;    // output rows per strip (8 groups of 4)
 constexpr int BL_CHUNK = 30;    // output words per warp (lanes 1..30)
 
@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(BL_WARPS * 32) k_blur(const ExtractorGeom* __r
                                                         uint8_t* __restrict__ blur) {
   const int4 t = tiles[blockIdx.x];   // {level, first item, chunks per row, items in the level}
   const int lane = threadIdx.x & 31;
-  const int item = t.y + (threadIdx.x >> 5);
+  const int item = BL_WARPS == 1 ? t.y : t.y + (int)(threadIdx.x >> 5);
   if (item >= t.w) return;
   const LevelGeom& L = dg->lv[t.x];
   const int strip = item / t.z, chunk = item - strip * t.z;
@@ -83,8 +83,14 @@ __global__ void __launch_bounds__(BL_WARPS * 32) k_blur(const ExtractorGeom* __r
     transpose4(r, tb);
   };
 
-  // one output row: column sums v[0..3] of this lane's word -> pairs -> neighbours' pairs -> 4 px
-  auto emit_row = [&](const unsigned (&v)[4], int y) {
+  // running 32-bit offsets from the two base pointers (one add per row instead of 64-bit products)
+  unsigned soff = 8u * pitch;          // next source row to load, relative to y0 - 3 (blocks 0 and 1 are loaded up front)
+  unsigned doff = 0;                   // output row, relative to y0
+  int rows_left = y1 - y0;
+
+  // one output row: column sums v[0..3] of this lane's word -> pairs -> neighbours' pairs -> 4 px.
+  // FULL: the strip has all BL_ROWS rows, so the store needs no row test (a single predicated STG)
+  auto emit_row = [&](const unsigned (&v)[4], bool in_rows) {
     const unsigned P0 = __byte_perm(v[0], v[1], 0x5410), P1 = __byte_perm(v[2], v[3], 0x5410);
     const unsigned L0 = __shfl_up_sync(0xffffffffu, P0, 1), L1 = __shfl_up_sync(0xffffffffu, P1, 1);
     const unsigned R0 = __shfl_down_sync(0xffffffffu, P0, 1), R1 = __shfl_down_sync(0xffffffffu, P1, 1);
@@ -93,43 +99,49 @@ __global__ void __launch_bounds__(BL_WARPS * 32) k_blur(const ExtractorGeom* __r
     const unsigned a1 = __dp2a_lo(L1, H2, __dp2a_hi(P0, H2, __dp2a_lo(P1, H3, __dp2a_hi(R0, H3, 32768u))));
     const unsigned a2 = __dp2a_lo(L1, H0, __dp2a_hi(P0, H0, __dp2a_lo(P1, H1, __dp2a_hi(R0, H1, 32768u))));
     const unsigned a3 = __dp2a_lo(P0, H2, __dp2a_hi(P1, H2, __dp2a_lo(R0, H3, __dp2a_hi(R1, H3, 32768u))));
-    if (writer && y < y1)
-      *reinterpret_cast<unsigned*>(dst + (unsigned)(y - y0) * bpitch) =
-          __byte_perm(__byte_perm(a0, a1, 0x0062), __byte_perm(a2, a3, 0x0062), 0x5410);
+    if (writer && in_rows)
+      *reinterpret_cast<unsigned*>(dst + doff) = __byte_perm(__byte_perm(a0, a1, 0x0062), __byte_perm(a2, a3, 0x0062), 0x5410);
+    doff += bpitch;
   };
 
-  // one group of four output rows starting at y; A, B, C as above
-  auto group = [&](const unsigned (&A)[4], const unsigned (&B)[4], const unsigned (&C)[4], int y) {
+  // one group of four output rows; A, B, C as above
+  auto group = [&](const unsigned (&A)[4], const unsigned (&B)[4], const unsigned (&C)[4], bool full) {
     unsigned v[4];
 #pragma unroll
     for (int c = 0; c < 4; c++) v[c] = __dp4a(A[c], WA0, __dp4a(B[c], WB0, 0u));
-    emit_row(v, y);
+    emit_row(v, true);
 #pragma unroll
     for (int c = 0; c < 4; c++) v[c] = __dp4a(A[c], WA1, __dp4a(B[c], WB1, 0u));
-    emit_row(v, y + 1);
+    emit_row(v, full || rows_left > 1);
 #pragma unroll
     for (int c = 0; c < 4; c++) v[c] = __dp4a(A[c], WA2, __dp4a(B[c], WB2, __dp4a(C[c], WC2, 0u)));
-    emit_row(v, y + 2);
+    emit_row(v, full || rows_left > 2);
 #pragma unroll
     for (int c = 0; c < 4; c++) v[c] = __dp4a(A[c], WA3, __dp4a(B[c], WB3, __dp4a(C[c], WC3, 0u)));
-    emit_row(v, y + 3);
+    emit_row(v, full || rows_left > 3);
+    rows_left -= 4;
+  };
+  auto load_next = [&](unsigned (&tb)[4]) {
+    unsigned r[4];
+    const uint8_t* p = src + soff;
+#pragma unroll
+    for (int j = 0; j < 4; j++) r[j] = __ldg(reinterpret_cast<const unsigned*>(p + (unsigned)j * pitch));
+    transpose4(r, tb);
+    soff += 4u * pitch;
   };
 
   // the three blocks rotate through three register sets (no copies)
   unsigned T0[4], T1[4], T2[4];
   load_block(0, T0);
   load_block(4, T1);
-  int row = 8;                         // next source row to load, relative to y0 - 3
-  for (int y = y0;;) {
-    load_block(row, T2); row += 4;
-    group(T0, T1, T2, y); y += 4;
-    if (y >= y1) break;
-    load_block(row, T0); row += 4;
-    group(T1, T2, T0, y); y += 4;
-    if (y >= y1) break;
-    load_block(row, T1); row += 4;
-    group(T2, T0, T1, y); y += 4;
-    if (y >= y1) break;
+  const bool full = rows_left == BL_ROWS;   // the common case: no per-row test
+  for (;;) {
+    load_next(T2); group(T0, T1, T2, full);
+    if (rows_left <= 0) break;
+    load_next(T0); group(T1, T2, T0, full);
+    if (rows_left <= 0) break;
+    load_next(T1); group(T2, T0, T1, full);
+    if (rows_left <= 0) break;
   }
 }
 
