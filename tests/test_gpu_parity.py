@@ -243,3 +243,30 @@ def test_other_geometries(cu, w, h, nf, scale, nlevels, ini, mn, seed):
         assert len(xs) == len(xo) and (xs == xo).all() and (ys == yo).all() and (rs == ro).all(), f"FAST level {lv}"
     assert mono == mo
     assert_extract_equal(k, d, ko, do)
+
+
+def test_staged_pyramid_variant_subprocess(cu):
+    """The opt-in bulk-copy staged resize kernel (CUORB_PYR_STAGED=1) must produce the same
+    pyramid, keypoints and descriptors as the oracle; the switch is read once per process, hence the subprocess."""
+    import subprocess, sys, textwrap
+    code = textwrap.dedent("""
+        import numpy as np
+        import orbslam3_cpp_fork_b200 as c
+        from oracle import oracle_py as op
+        from orbslam3_cpp_fork_b200 import synth
+        for (w, h, nf, seed) in ((752, 480, 1000, 21), (1241, 376, 2000, 22), (333, 251, 300, 23)):
+            img = synth.synth_image(w, h, seed)
+            e = c.ORBextractor(nf, max_width=w, max_height=h, max_batch=2)
+            e.extract_batch_async(np.stack([img, img[::-1].copy()]))
+            cnt, mono, k, d = e.fetch()
+            o = op.OracleExtractor(nf)
+            _, ko, do = o.extract(img)
+            assert cnt[0] == len(ko) and (d[0, :cnt[0]] == do).all()
+            for f in ("x", "y", "angle", "response", "octave"):
+                assert (k[0, :cnt[0]][f] == ko[f]).all(), f
+        print("staged ok")
+    """)
+    env = dict(os.environ, CUORB_PYR_STAGED="1")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "staged ok" in r.stdout, r.stdout + r.stderr
