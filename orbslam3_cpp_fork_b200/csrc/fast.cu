@@ -304,7 +304,7 @@ struct FastParams {
   unsigned* cand; int* cand_count; int* flags; int* work_counter;
   unsigned long long cand_img_stride;
   int nlevels, ini_th, min_th;
-  int box_rows, tile_bytes, score_bytes, pcap, ccap;
+  int box_rows, tile_bytes, score_bytes, pcap;
 };
 
 constexpr int FT_WORDS = FT_PITCH / 4;
@@ -335,11 +335,10 @@ __global__ void __launch_bounds__(32 * NW) k_fast_persist(const __grid_constant_
   unsigned char*  s_scores = smem + 2 * P.tile_bytes;                           // 2 x score_bytes (items alternate)
   unsigned short* s_plist = reinterpret_cast<unsigned short*>(s_scores + 2 * P.score_bytes);
   constexpr int NT = 32 * NW;   // NW warps share one cell
-  unsigned short* s_clist = s_plist + NW * P.pcap;
 
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const unsigned lt = (1u << lane) - 1u;
-  const int pcap = P.pcap, ccap = P.ccap;
+  const int pcap = P.pcap;
   int w = blockIdx.x;
   if (w >= P.total_work) return;
 
@@ -419,8 +418,9 @@ __global__ void __launch_bounds__(32 * NW) k_fast_persist(const __grid_constant_
       // ---- 2b: score network on the warp's own pairs, bytes widened on the fly ----
       int ncorn = 0;
       {
-        const unsigned short* pl = s_plist + wid * pcap;
-        unsigned short* seg = s_clist + wid * ccap;
+        // corner entries (row << 8 | pair column << 2 | pixel flags) overwrite the pair list in place: a chunk of 32
+        // pairs yields at most 32 entries, written at or below the chunk's own positions, after the chunk was read
+        unsigned short* pl = s_plist + wid * pcap;
         for (int j0 = 0; j0 < npairs; j0 += 32) {
           const bool in = j0 + lane < npairs;
           const int e = pl[min(j0 + lane, npairs - 1)];
@@ -456,8 +456,8 @@ __global__ void __launch_bounds__(32 * NW) k_fast_persist(const __grid_constant_
           const bool k1 = in && px + 1 >= 0 && px + 1 < dw && s1 >= cur_th;
           if (k0) q[0] = (unsigned char)s0;
           if (k1) q[1] = (unsigned char)s1;
-          warp_append(k0, (unsigned short)((r << 7) | px), seg, ncorn, lt);
-          warp_append(k1, (unsigned short)((r << 7) | (px + 1)), seg, ncorn, lt);
+          __syncwarp();   // every lane holds its pair entry before the list is overwritten
+          warp_append(k0 || k1, (unsigned short)((r << 8) | (pc << 2) | (k1 ? 2 : 0) | (k0 ? 1 : 0)), pl, ncorn, lt);
         }
       }
       __syncthreads();   // all scores of the cell are in place
@@ -465,27 +465,33 @@ __global__ void __launch_bounds__(32 * NW) k_fast_persist(const __grid_constant_
       // ---- 3: NMS over the warp's own corners; survivors go straight to the level's candidate list
       // (one global atomicAdd per warp and 32 corners): whatever a pass finds is final, because a
       // pass-0 survivor means the cell keeps its iniThFAST result and pass 1 only runs on empty cells
-      const unsigned short* cl = s_clist + wid * ccap;
+      const unsigned short* cl = s_plist + wid * pcap;
       int found = 0;
       for (int j0 = 0; j0 < ncorn; j0 += 32) {
         const bool in = j0 + lane < ncorn;
         const int e = cl[min(j0 + lane, ncorn - 1)];
-        const int r = e >> 7, px = e & 127;
+        const int r = e >> 8, px = 4 + 2 * ((e >> 2) & 63) - cx0;
         const unsigned char* q = s_score + (r + 1) * sp + px + 4;
-        const int s = q[0];
-        const bool lm = in && s > q[-1] && s > q[1] && s > q[-sp - 1] && s > q[-sp] && s > q[-sp + 1] &&
-                        s > q[sp - 1] && s > q[sp] && s > q[sp + 1];
-        const unsigned bal = __ballot_sync(0xffffffffu, lm);
-        if (bal) {
+        // the two pixels of the pair share the 3 x 4 score neighbourhood
+        const int a0 = q[-sp - 1], a1 = q[-sp], a2 = q[-sp + 1], a3 = q[-sp + 2];
+        const int m0 = q[-1], s0 = q[0], s1 = q[1], m3 = q[2];
+        const int b0 = q[sp - 1], b1 = q[sp], b2 = q[sp + 1], b3 = q[sp + 2];
+        const bool lm0 = in && (e & 1) && s0 > m0 && s0 > s1 && s0 > a0 && s0 > a1 && s0 > a2 && s0 > b0 && s0 > b1 && s0 > b2;
+        const bool lm1 = in && (e & 2) && s1 > s0 && s1 > m3 && s1 > a1 && s1 > a2 && s1 > a3 && s1 > b1 && s1 > b2 && s1 > b3;
+        const unsigned bal0 = __ballot_sync(0xffffffffu, lm0), bal1 = __ballot_sync(0xffffffffu, lm1);
+        if (bal0 | bal1) {
           // output addresses only here (the common iteration emits nothing)
           unsigned* out = P.cand + (size_t)img * P.cand_img_stride + (unsigned)c1.z;
           int* out_count = P.cand_count + img * P.nlevels + level;
-          const int n = __popc(bal);
+          const int n0 = __popc(bal0), n = n0 + __popc(bal1);
           int base = 0;
           if (lane == 0) base = atomicAdd(out_count, n);
           base = __shfl_sync(0xffffffffu, base, 0);
           if (base + n > c1.w) { if (lane == 0) atomicOr(P.flags, FLAG_CAND_OVERFLOW); }
-          else if (lm) out[base + __popc(bal & lt)] = pack_cand(x0 + px - FAST_BORDER, y0 + r - FAST_BORDER, s);
+          else {
+            if (lm0) out[base + __popc(bal0 & lt)] = pack_cand(x0 + px - FAST_BORDER, y0 + r - FAST_BORDER, s0);
+            if (lm1) out[base + n0 + __popc(bal1 & lt)] = pack_cand(x0 + px + 1 - FAST_BORDER, y0 + r - FAST_BORDER, s1);
+          }
           found += n;
         }
       }
@@ -493,7 +499,9 @@ __global__ void __launch_bounds__(32 * NW) k_fast_persist(const __grid_constant_
       // clear exactly the scores this pass wrote (all NMS reads are behind the barrier above)
       for (int j = lane; j < ncorn; j += 32) {
         const int e = cl[j];
-        s_score[((e >> 7) + 1) * sp + (e & 127) + 4] = 0;
+        unsigned char* q = s_score + ((e >> 8) + 1) * sp + 4 + 2 * ((e >> 2) & 63) - cx0 + 4;
+        if (e & 1) q[0] = 0;
+        if (e & 2) q[1] = 0;
       }
       if (done) break;
       __syncthreads();
@@ -594,8 +602,7 @@ void launch_fast_persist(const ExtractorGeom& g, const FastMaps& maps, const int
   // warps wait at the two per-cell barriers, more cells are in flight per SM; CUORB_FAST_WARPS overrides
   static const int NW = []() { const char* e = getenv("CUORB_FAST_WARPS"); const int v = e ? atoi(e) : 2; return v == 1 || v == 4 ? v : 2; }();
   P.pcap = 64 * ((maxquads + 32 * NW - 1) / (32 * NW));
-  P.ccap = 2 * P.pcap;
-  const int smem = 128 + 2 * P.tile_bytes + 2 * P.score_bytes + 2 * NW * (P.pcap + P.ccap);
+  const int smem = 128 + 2 * P.tile_bytes + 2 * P.score_bytes + 2 * NW * P.pcap;   // one u16 list per warp: pairs, then corner pairs in place
   void (*kern)(const FastMaps, const FastParams) = NW == 1 ? k_fast_persist<1> : NW == 2 ? k_fast_persist<2> : k_fast_persist<4>;
   static int attr = 48 * 1024, per_sm = 0, attr_smem = -1, n_sm = 0;
   if (smem > attr) {
@@ -609,7 +616,13 @@ void launch_fast_persist(const ExtractorGeom& g, const FastMaps& maps, const int
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 32 * NW, smem);
     attr_smem = smem;
   }
-  const int grid = std::max(1, std::min(P.total_work, n_sm * std::max(per_sm, 1)));
+  // CTAs per SM: with the single in-place list 13-14 CTAs fit, and FAST alone is fastest that way (0.594 ms per 256
+  // images against 0.627 at 10), but the whole step is fastest at 10 (93.0k against 90.6k frames/s): the shared
+  // memory and warp slots left over let the other handles' blur / quadtree / describe CTAs onto the SM beside it.
+  // CUORB_FAST_CTAS overrides (0 = as many as fit).
+  static const int cap = []() { const char* e = getenv("CUORB_FAST_CTAS"); return e ? atoi(e) : 10; }();
+  const int use_per_sm = cap > 0 ? std::min(cap, std::max(per_sm, 1)) : std::max(per_sm, 1);
+  const int grid = std::max(1, std::min(P.total_work, n_sm * use_per_sm));
   kern<<<grid, 32 * NW, smem, st>>>(maps, P);
   count_launch();
 }
