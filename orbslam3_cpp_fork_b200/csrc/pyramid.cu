@@ -529,7 +529,7 @@ void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8
     } else {
       // four adjacent output columns span 3*scale + 2 source bytes (+3 for alignment): 12 bytes up to scale 2
       const double sx = (double)g.lv[l - 1].w / L.w;
-      static const int staged = []() { const char* e = getenv("CUORB_PYR_STAGED"); return e ? atoi(e) : 0; }();
+      static const int staged = []() { const char* e = getenv("CUORB_PYR_STAGED"); return e ? atoi(e) : 1; }();
       if (wtab && wtab_off[l] >= 0 && staged && plan && plan[l].tx > 0) {
         const PyrPlan& p = plan[l];
         PyrCols pc;

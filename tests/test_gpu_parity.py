@@ -245,9 +245,10 @@ def test_other_geometries(cu, w, h, nf, scale, nlevels, ini, mn, seed):
     assert_extract_equal(k, d, ko, do)
 
 
-def test_staged_pyramid_variant_subprocess(cu):
-    """The opt-in bulk-copy staged resize kernel (CUORB_PYR_STAGED=1) must produce the same
-    pyramid, keypoints and descriptors as the oracle; the switch is read once per process, hence the subprocess."""
+def test_register_pyramid_variant_subprocess(cu):
+    """The register-only resize kernel (CUORB_PYR_STAGED=0; the default is the bulk-copy staged kernel, DESIGN.md
+    section 6) must produce the same keypoints and descriptors as the oracle; the switch is read once per process,
+    hence the subprocess."""
     import subprocess, sys, textwrap
     code = textwrap.dedent("""
         import numpy as np
@@ -264,9 +265,9 @@ def test_staged_pyramid_variant_subprocess(cu):
             assert cnt[0] == len(ko) and (d[0, :cnt[0]] == do).all()
             for f in ("x", "y", "angle", "response", "octave"):
                 assert (k[0, :cnt[0]][f] == ko[f]).all(), f
-        print("staged ok")
+        print("variant ok")
     """)
-    env = dict(os.environ, CUORB_PYR_STAGED="1")
+    env = dict(os.environ, CUORB_PYR_STAGED="0")
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True, timeout=600)
-    assert r.returncode == 0 and "staged ok" in r.stdout, r.stdout + r.stderr
+    assert r.returncode == 0 and "variant ok" in r.stdout, r.stdout + r.stderr
