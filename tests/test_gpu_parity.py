@@ -245,10 +245,15 @@ def test_other_geometries(cu, w, h, nf, scale, nlevels, ini, mn, seed):
     assert_extract_equal(k, d, ko, do)
 
 
-def test_register_pyramid_variant_subprocess(cu):
-    """The register-only resize kernel (CUORB_PYR_STAGED=0; the default is the bulk-copy staged kernel, DESIGN.md
-    section 6) must produce the same keypoints and descriptors as the oracle; the switch is read once per process,
-    hence the subprocess."""
+VARIANTS = [{"CUORB_PYR_STAGED": "0"}, {"CUORB_FAST_LEGACY": "1"}, {"CUORB_SIDE_BLUR": "0"},
+            {"CUORB_FAST_CTAS": "0", "CUORB_FAST_WARPS": "4"}, {"CUORB_FAST_WARPS": "1", "CUORB_FAST_CTAS": "3"}]
+
+
+@pytest.mark.parametrize("env_over", VARIANTS, ids=lambda d: ",".join(f"{k[6:]}={v}" for k, v in d.items()))
+def test_kernel_variants_subprocess(cu, env_over):
+    """Every runtime switch of DESIGN.md section 6 selects between kernels / launch shapes that must stay bit-identical
+    to the oracle (register-only resize kernel, one-CTA-per-cell FAST, serial blur, other FAST CTA shapes).  The
+    switches are read once per process, hence the subprocess."""
     import subprocess, sys, textwrap
     code = textwrap.dedent("""
         import numpy as np
@@ -267,7 +272,7 @@ def test_register_pyramid_variant_subprocess(cu):
                 assert (k[0, :cnt[0]][f] == ko[f]).all(), f
         print("variant ok")
     """)
-    env = dict(os.environ, CUORB_PYR_STAGED="0")
+    env = dict(os.environ, **env_over)
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "variant ok" in r.stdout, r.stdout + r.stderr
