@@ -496,12 +496,13 @@ __global__ void __launch_bounds__(32 * NW) k_fast_persist(const __grid_constant_
         }
       }
       const bool done = __syncthreads_or(found > 0) || pass == 1 || P.min_th == P.ini_th;
-      // clear exactly the scores this pass wrote (all NMS reads are behind the barrier above)
-      for (int j = lane; j < ncorn; j += 32) {
-        const int e = cl[j];
-        unsigned char* q = s_score + ((e >> 8) + 1) * sp + 4 + 2 * ((e >> 2) & 63) - cx0 + 4;
-        if (e & 1) q[0] = 0;
-        if (e & 2) q[1] = 0;
+      // clear the cell's score tile with 16-byte stores (all NMS reads are behind the barrier above; the tile is
+      // next used two items later, or after the barrier below in a retry): ~2 stores per thread, cheaper than
+      // walking the corner list again
+      {
+        const int n16 = (sp * (dh + 2) + 15) >> 4;
+        uint4* z = reinterpret_cast<uint4*>(s_score);
+        for (int j = tid; j < n16; j += NT) z[j] = make_uint4(0u, 0u, 0u, 0u);
       }
       if (done) break;
       __syncthreads();
