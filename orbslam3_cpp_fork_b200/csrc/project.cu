@@ -3,11 +3,11 @@
 // and SearchByProjection(Frame& Cur, const Frame& Last, th, bMono), :1684-1811, 1889-1908; pinhole
 // branches) plus Frame::GetFeaturesInArea / PosInGrid (src/Frame.cc:788-877).
 //
-// One warp per MapPoint; the frame (<= a few thousand features) is scanned brute force with the
-// exact GetFeaturesInArea predicate (grid-cell window, level window, |dx|,|dy| < r), so no grid
-// has to be built; the reference's candidate visiting order (cell ix, then iy, then insertion =
-// feature index) becomes part of the arg-min key, which reproduces its "first strict minimum
-// wins" and best/second-best bookkeeping.
+// One warp per MapPoint; it visits the features of its GetFeaturesInArea cell window through a cell-sorted CSR
+// of the frame (built on the host while the frame is flattened: a counting sort of <= a few thousand features)
+// and applies the exact predicate (level window, |dx|,|dy| < r); the reference's candidate visiting order (cell
+// ix, then iy, then insertion = feature index) is part of the arg-min key, which reproduces its "first strict
+// minimum wins" and best/second-best bookkeeping whatever order the lanes see the candidates in.
 //
 // The reference loop is order dependent: a feature bound to a MapPoint with observations is
 // skipped by all later MapPoints (:96-100, :1763-1767).  That is resolved by fixed-point rounds:
@@ -79,9 +79,13 @@ __global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, ProjQuery Q,
     const uint4 q0 = qd[0], q1 = qd[1];
     const float aux = Q.aux ? Q.aux[i] : 0.f;
     unsigned long long b1 = ~0ull, b2 = ~0ull;  // (dist << 32 | visiting position), two smallest
-    for (int f = lane; f < F.n; f += 32) {
-      const int cx = F.cellx[f], cy = F.celly[f];
-      if (cx < cx0 || cx > cx1 || cy < cy0 || cy > cy1) continue;
+    // GetFeaturesInArea: only the features of the window's cells are visited (cell-sorted CSR); the reference's
+    // visiting order is carried by the key, so the iteration order here is free
+    for (int cy = cy0; cy <= cy1; cy++) {
+     const int js = F.cstart[cy * FRAME_GRID_COLS + cx0], je = F.cstart[cy * FRAME_GRID_COLS + cx1 + 1];
+     for (int j = js + lane; j < je; j += 32) {
+      const int f = F.order[j];
+      const int cx = F.cellx[f];
       const int oct = F.octave[f];
       if (checkLevels) {
         if (oct < minLevel) continue;
@@ -100,6 +104,7 @@ __global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, ProjQuery Q,
       const unsigned long long key = ((unsigned long long)dist << 32) | ((unsigned)cx << 22) | ((unsigned)cy << 16) | (unsigned)f;
       if (key < b1) { b2 = b1; b1 = key; }
       else if (key < b2) b2 = key;
+     }
     }
     unsigned long long B1 = b1;
 #pragma unroll

@@ -1,6 +1,7 @@
 // Shared pieces of the projection / window searches (project.cu, search.cu): the device view of a
 // Frame or KeyFrame, the Hamming primitive and the per-thread device scratch arena.
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <vector>
 
@@ -13,6 +14,11 @@ struct ProjFrame {  // device SoA of the frame members the searches read
   const float *x, *y, *uright;
   const int *octave;
   const short *cellx, *celly;  // PosInGrid result, -1 if outside the grid
+  // features inside the grid, ordered by cell (row-major: celly * 64 + cellx); cstart[c] .. cstart[c + 1] = cell c
+  // (Frame::AssignFeaturesToGrid's mGrid as CSR, src/Frame.cc:524-553); the features of cells cx0..cx1 of one grid
+  // row are one contiguous range
+  const int* cstart;
+  const unsigned short* order;
   const uint8_t* desc;
   const uint8_t* blocked0;     // mvpMapPoints[i] && Observations() > 0 on entry
   float minX, minY, maxX, maxY, gwinv, ghinv, mbf;
@@ -62,7 +68,7 @@ inline T* up(Arena& A, const T* host, size_t count, cudaStream_t st) {
 }
 
 
-inline size_t frame_bytes(int n) { return (size_t)n * (4 * 4 + 2 * 2 + 32 + 1 + 8) + 16 * 256; }
+inline size_t frame_bytes(int n) { return (size_t)n * (4 * 4 + 2 * 2 + 32 + 1 + 8 + 2) + (FRAME_GRID_ROWS * FRAME_GRID_COLS + 1) * 4 + 20 * 256; }
 
 // host-side flattening of the Frame: SoA + PosInGrid (src/Frame.cc:867-877, std::round); the arena must
 // already hold frame_bytes(n) more bytes
@@ -81,7 +87,18 @@ inline void upload_frame(Arena& A, const cuorb_frame_view* fv, cudaStream_t st, 
     cxv[i] = in ? (short)posX : (short)-1; cyv[i] = in ? (short)posY : (short)-1;
     if (fv->bound_with_obs) blk[i] = fv->bound_with_obs[i];
   }
+  // counting sort of the in-grid features by cell
+  std::vector<int> cstart(FRAME_GRID_ROWS * FRAME_GRID_COLS + 1, 0);
+  for (int i = 0; i < n; i++) if (cxv[i] >= 0) cstart[cyv[i] * FRAME_GRID_COLS + cxv[i] + 1]++;
+  for (size_t c = 1; c < cstart.size(); c++) cstart[c] += cstart[c - 1];
+  std::vector<unsigned short> order((size_t)std::max(n, 1));
+  {
+    std::vector<int> fill(cstart.begin(), cstart.end() - 1);
+    for (int i = 0; i < n; i++) if (cxv[i] >= 0) order[fill[cyv[i] * FRAME_GRID_COLS + cxv[i]]++] = (unsigned short)i;
+  }
   F.n = n;
+  F.cstart = up(A, cstart.data(), cstart.size(), st);
+  F.order = up(A, order.data(), order.size(), st);
   F.x = up(A, fx.data(), n, st); F.y = up(A, fy.data(), n, st);
   F.uright = fv->u_right ? up(A, fv->u_right, n, st) : nullptr;
   F.octave = up(A, foct.data(), n, st);
