@@ -76,9 +76,12 @@ __global__ void __launch_bounds__(256) k_area_round(ProjFrame F, AreaQuery Q, co
     const uint4 q0 = qd[0], q1 = qd[1];
     const float ur = (Q.chi2 && Q.ur) ? Q.ur[i] : 0.f;
     unsigned long long b1 = ~0ull;
-    for (int f = lane; f < F.n; f += 32) {
-      const int cx = F.cellx[f], cy = F.celly[f];
-      if (cx < cx0 || cx > cx1 || cy < cy0 || cy > cy1) continue;
+    // the window's cells through the frame's cell-sorted CSR (project.cuh); the visiting order is in the key
+    for (int cy = cy0; cy <= cy1; cy++) {
+     const int js = F.cstart[cy * FRAME_GRID_COLS + cx0], je = F.cstart[cy * FRAME_GRID_COLS + cx1 + 1];
+     for (int j = js + lane; j < je; j += 32) {
+      const int f = F.order[j];
+      const int cx = F.cellx[f];
       const float kx = F.x[f], ky = F.y[f];
       const float ex = __fsub_rn(kx, x), ey = __fsub_rn(ky, y);
       if (!(fabsf(ex) < rad && fabsf(ey) < rad)) continue;
@@ -98,6 +101,7 @@ __global__ void __launch_bounds__(256) k_area_round(ProjFrame F, AreaQuery Q, co
       const int dist = hamming256(q0, q1, reinterpret_cast<const uint4*>(F.desc + (size_t)f * 32));
       const unsigned long long key = ((unsigned long long)dist << 32) | ((unsigned)cx << 22) | ((unsigned)cy << 16) | (unsigned)f;
       b1 = min(b1, key);
+     }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) b1 = min(b1, __shfl_xor_sync(0xffffffffu, b1, o));
