@@ -42,6 +42,27 @@ t0 = time.perf_counter()
 for F in frames:
     m.SearchByProjection(F, mps, 3.0, False, 60.0)
 dt_gpu = (time.perf_counter() - t0) / len(frames)
+# the C-ABI call alone (what the C++ shim would time: host SoA in, best indices out)
+import ctypes as C
+from orbslam3_cpp_fork_b200 import _lib
+from orbslam3_cpp_fork_b200.matcher import _c
+L_ = _lib.load()
+F = make_frame()
+fvv, keep_alive = F.view()
+flags = mps.flags()
+arrs = [_c(mps.descriptor, np.uint8), _c(mps.mTrackProjX, np.float32), _c(mps.mTrackProjY, np.float32),
+        _c(mps.mTrackProjXR, np.float32), _c(mps.mnTrackScaleLevel, np.int32), _c(mps.mTrackViewCos, np.float32),
+        _c(mps.mTrackDepth, np.float32), flags]
+best_c = np.zeros(M, np.int32)
+def c_call():
+    return _lib.check(L_.cuorb_search_by_projection(0, C.byref(fvv), M, *[_lib.ptr(a) for a in arrs], 3.0, 0, 60.0, 0.8,
+                                                    _lib.ptr(best_c)))
+c_call()
+assert (best_c == best_o).all()
+t0 = time.perf_counter()
+for _ in range(50):
+    rounds = c_call()
+dt_c = (time.perf_counter() - t0) / 50
 t0 = time.perf_counter()
 for _ in range(5):
     op.search_by_projection(fv, c["desc"], c["px"], c["py"], c["pxr"], c["level"], c["view_cos"], c["depth"], c["flags"],
@@ -49,7 +70,8 @@ for _ in range(5):
 dt_cpu = (time.perf_counter() - t0) / 5
 out = {"workload": f"cfg4: SearchByProjection(F, {M} MapPoints), frame 752x480 / {len(k)} keypoints, th 3",
        "matches": int(n_gpu), "parity": "match count and every best index equal to the oracle",
-       "cuorb_ms_per_call_host_buffers": dt_gpu * 1e3, "mappoints_per_s": M / dt_gpu,
+       "cuorb_c_abi_ms_per_call_host_buffers": dt_c * 1e3, "mappoints_per_s": M / dt_c,
+       "python_wrapper_ms_per_call": dt_gpu * 1e3,
        "cpu_oracle_ms_per_call_1core": dt_cpu * 1e3, "cpu_mappoints_per_s_1core": M / dt_cpu}
 
 print(json.dumps(out))
