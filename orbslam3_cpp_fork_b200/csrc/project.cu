@@ -38,7 +38,8 @@ struct ProjQuery {
 __global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, ProjQuery Q,
                                                     const int* __restrict__ binder_prev,
                                                     int* __restrict__ binder_next,
-                                                    int* __restrict__ result, int* __restrict__ changed) {
+                                                    int* __restrict__ result, int* __restrict__ changed,
+                                                    const unsigned* __restrict__ dirty) {
   const int i = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (i >= Q.n) return;
   int res = -1;
@@ -72,6 +73,27 @@ __global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, ProjQuery Q,
     cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, F.minY), rad), F.ghinv)));
     cy1 = min(FRAME_GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, F.minY), rad), F.ghinv)));
     if (cx0 >= FRAME_GRID_COLS || cx1 < 0 || cy0 >= FRAME_GRID_ROWS || cy1 < 0) active = false;
+  }
+  // Rounds after the first: a MapPoint's outcome is a function of "binder_prev[f] < i" over the features of its
+  // window, so it can only differ from the previous round's if a feature of one of the window's cells changed its
+  // binder in between.  `dirty` has one bit per grid cell holding such a feature (k_dirty_cells); a clean window
+  // keeps result[i] and only re-asserts its claim in this round's binder table.
+  if (dirty) {
+    bool hit = false;
+    if (active) {
+      const unsigned long long cols = (cx1 >= 63 ? ~0ull : ((2ull << cx1) - 1ull)) & ~((1ull << cx0) - 1ull);
+      for (int cy = cy0 + lane; cy <= cy1; cy += 32) {
+        const unsigned long long row = ((unsigned long long)dirty[2 * cy + 1] << 32) | dirty[2 * cy];
+        hit |= (row & cols) != 0;
+      }
+    }
+    if (!__any_sync(0xffffffffu, hit)) {
+      if (lane == 0) {
+        const int r0 = result[i];
+        if (r0 >= 0 && (fl & CUORB_MP_HAS_OBS)) atomicMin(&binder_next[r0], i);
+      }
+      return;
+    }
   }
   if (active) {
     const bool checkLevels = (minLevel > 0) || (maxLevel >= 0);
@@ -132,6 +154,15 @@ __global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, ProjQuery Q,
   }
 }
 
+// grid: ceil(n/256): one bit per grid cell (row-major, 64 columns = 2 words per row) that holds a feature whose
+// binder differs between two consecutive rounds
+__global__ void k_dirty_cells(ProjFrame F, const int* __restrict__ a, const int* __restrict__ b, unsigned* __restrict__ dirty) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= F.n || a[f] == b[f]) return;
+  const int cx = F.cellx[f], cy = F.celly[f];
+  if (cx >= 0) atomicOr(&dirty[2 * cy + (cx >> 5)], 1u << (cx & 31));
+}
+
 // grid: ceil(n/256)
 __global__ void k_hamming_pairs(const uint8_t* a, const uint8_t* b, const int* ia, const int* ib, int n, int* out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -169,6 +200,7 @@ static int run_projection(int device, const cuorb_frame_view* fv, ProjQuery Q, c
   int* binder[2] = {A.take<int>(n), A.take<int>(n)};
   int* result = A.take<int>(m);
   int* changed = A.take<int>(1);
+  unsigned* dirty = A.take<unsigned>(2 * FRAME_GRID_ROWS);
   k_fill<<<(n + 255) / 256, 256, 0, st>>>(binder[0], n, NO_BINDER);
   k_fill<<<(m + 255) / 256, 256, 0, st>>>(result, m, -2);
   count_launch(2);
@@ -177,9 +209,14 @@ static int run_projection(int device, const cuorb_frame_view* fv, ProjQuery Q, c
     if (rounds > m + 2) { set_error("projection search did not converge"); return CUORB_E_CUDA; }
     int* prev = binder[rounds & 1];
     int* next = binder[(rounds + 1) & 1];
-    k_fill<<<(n + 255) / 256, 256, 0, st>>>(next, n, NO_BINDER);
     CUORB_CUDA_TRY(cudaMemsetAsync(changed, 0, sizeof(int), st));
-    k_proj_round<<<(m + 7) / 8, 256, 0, st>>>(F, Q, prev, next, result, changed);
+    if (rounds > 0) {   // cells whose features changed binder between the last two rounds (next still holds round-2's table)
+      CUORB_CUDA_TRY(cudaMemsetAsync(dirty, 0, 2 * FRAME_GRID_ROWS * sizeof(unsigned), st));
+      k_dirty_cells<<<(n + 255) / 256, 256, 0, st>>>(F, prev, next, dirty);
+      count_launch();
+    }
+    k_fill<<<(n + 255) / 256, 256, 0, st>>>(next, n, NO_BINDER);
+    k_proj_round<<<(m + 7) / 8, 256, 0, st>>>(F, Q, prev, next, result, changed, rounds > 0 ? dirty : nullptr);
     count_launch(2);
     int h_changed = 0;
     CUORB_CUDA_TRY(cudaMemcpyAsync(&h_changed, changed, sizeof(int), cudaMemcpyDeviceToHost, st));
