@@ -115,7 +115,10 @@ int cuorb_extract_fetch_async(cuorb_extractor* ext, cuorb_keypoint* kps, uint8_t
                               int capacity, int32_t* n_out, int32_t* mono_index_out);
 int cuorb_sync(cuorb_extractor* ext);
 /* The handle's cudaStream_t (as void*): lets a caller order its own work / record CUDA events
- * (e.g. torch.cuda.ExternalStream) against the enqueued pipeline. */
+ * (e.g. torch.cuda.ExternalStream) against the enqueued pipeline.  The library also runs part of an
+ * extraction (the blur) on a second, internal stream; that work is forked from and joined back into
+ * this stream inside every extract call, so anything ordered after the handle's stream is ordered
+ * after the whole extraction. */
 void* cuorb_extractor_stream(cuorb_extractor* ext);
 
 /* std::vector<cv::Mat> mvImagePyramid (include/ORBextractor.h:87; read by
