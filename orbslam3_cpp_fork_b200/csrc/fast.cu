@@ -617,11 +617,12 @@ void launch_fast_persist(const ExtractorGeom& g, const FastMaps& maps, const int
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 32 * NW, smem);
     attr_smem = smem;
   }
-  // CTAs per SM: with the single in-place list 13-14 CTAs fit, and FAST alone is fastest that way (0.594 ms per 256
-  // images against 0.627 at 10), but the whole step is fastest at 10 (93.0k against 90.6k frames/s): the shared
-  // memory and warp slots left over let the other handles' blur / quadtree / describe CTAs onto the SM beside it.
+  // CTAs per SM: with the single in-place list 13-14 CTAs fit and FAST alone is fastest that way (0.594 ms per 256
+  // images), but the whole step then loses 3 % (90.6k against 93k frames/s): the other handles' blur / quadtree /
+  // describe / staged-pyramid CTAs need shared memory and warp slots on the same SMs.  Between 9 and 12 CTAs the step
+  // is flat within 0.5 % (93.3k - 93.8k) while FAST alone goes 0.655 -> 0.596 ms, so 12 is the default.
   // CUORB_FAST_CTAS overrides (0 = as many as fit).
-  static const int cap = []() { const char* e = getenv("CUORB_FAST_CTAS"); return e ? atoi(e) : 10; }();
+  static const int cap = []() { const char* e = getenv("CUORB_FAST_CTAS"); return e ? atoi(e) : 12; }();
   const int use_per_sm = cap > 0 ? std::min(cap, std::max(per_sm, 1)) : std::max(per_sm, 1);
   const int grid = std::max(1, std::min(P.total_work, n_sm * use_per_sm));
   kern<<<grid, 32 * NW, smem, st>>>(maps, P);
