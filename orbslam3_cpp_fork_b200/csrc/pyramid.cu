@@ -534,11 +534,9 @@ void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8
         const PyrPlan& p = plan[l];
         PyrCols pc;
         for (int b = 0; b < PYR_MAX_COLBLOCKS; b++) { pc.xlo[b] = p.xlo[b]; pc.tw[b] = p.tw[b]; }
-        static int attr = 48 * 1024;
-        if (p.smem > attr) {
-          cudaFuncSetAttribute(k_pyr_resize_stage, cudaFuncAttributeMaxDynamicSharedMemorySize, p.smem);
-          attr = p.smem;
-        }
+        // above the 48 KB default only for very wide levels; the attribute is per device, so it is set on every
+        // such launch rather than cached per process
+        if (p.smem > 48 * 1024) cudaFuncSetAttribute(k_pyr_resize_stage, cudaFuncAttributeMaxDynamicSharedMemorySize, p.smem);
         k_pyr_resize_stage<<<dim3(p.nb, (L.h + PYR_RS - 1) / PYR_RS, n_img), p.tx, p.smem, st>>>(dg, l, pyr, wtab + wtab_off[l], ytab, PYR_RS, pc);
       } else if (wtab && wtab_off[l] >= 0) {
         // CTA width = the row's word count split evenly over whole warps
