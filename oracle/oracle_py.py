@@ -80,6 +80,8 @@ def lib() -> C.CDLL:
         L.oo_search_by_projection_frame.argtypes = (
             [C.POINTER(FrameViewC), C.c_int] + [C.c_void_p] * 7 +
             [C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p])
+        L.oo_features_in_area.argtypes = [C.POINTER(FrameViewC), C.c_float, C.c_float, C.c_float, C.c_int, C.c_int,
+                                          C.c_void_p, C.c_int]
         L.oo_bench_stereo.restype = C.c_double
         L.oo_bench_stereo.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                       C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float,

@@ -162,6 +162,14 @@ static FrameView make_view(const cuorb_frame_view* f) {
   F.assign_features_to_grid();
   return F;
 }
+// Frame::GetFeaturesInArea on its own (src/Frame.cc:788-865), in the reference's visiting order
+int oo_features_in_area(const cuorb_frame_view* frame, float x, float y, float r, int min_level,
+                        int max_level, int32_t* out, int cap) {
+  FrameView F = make_view(frame);
+  std::vector<int> v = F.features_in_area(x, y, r, min_level, max_level);
+  for (size_t i = 0; i < v.size() && (int)i < cap; i++) out[i] = v[i];
+  return (int)v.size();
+}
 int oo_search_by_projection(const cuorb_frame_view* frame, int M, const uint8_t* mp_desc,
                             const float* px, const float* py, const float* pxr,
                             const int32_t* level, const float* view_cos, const float* depth,

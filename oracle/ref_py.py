@@ -1,0 +1,224 @@
+"""TEST INFRASTRUCTURE — NOT PRODUCT CODE.
+
+ctypes binding of oracle/_ref/liborb_ref.so: the reference's OWN sources (unmodified
+src/ORBextractor.cc and src/ORBmatcher.cc, plus function bodies lifted verbatim out of src/Frame.cc,
+src/KeyFrame.cc, src/MapPoint.cc, src/CameraModels/Pinhole.cpp) compiled over the stand-in headers of
+oracle/ref_compat (recipe: `make -C oracle ref`).  It is what pins the restated oracle
+(tests/test_oracle_vs_ref.py) and, through it or directly, libcuorb (tests/test_gpu_ref_parity.py).
+
+/root/reference only exists in the build container: there the library is (re)built on demand; on the
+GPU box the prebuilt, git-ignored oracle/_ref/liborb_ref.so that travelled with the snapshot is
+loaded as it is.  Only tests/, __graft_entry__ and bench.py's CPU legs import this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import json
+import os
+import subprocess
+
+import numpy as np
+
+from .oracle_py import KP_DTYPE, FrameViewC, _p
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "_ref", "liborb_ref.so")
+
+
+def reference_root() -> str:
+    try:
+        with open(os.path.join(_HERE, "..", "BASELINE.json")) as f:
+            return json.load(f).get("reference_path", "/root/reference")
+    except OSError:
+        return "/root/reference"
+
+
+def available() -> bool:
+    return os.path.exists(_LIB_PATH) or os.path.isdir(os.path.join(reference_root(), "src"))
+
+
+def build(force: bool = False) -> str | None:
+    """Build oracle/_ref when the reference checkout is present; otherwise keep the prebuilt file."""
+    ref = reference_root()
+    if os.path.isfile(os.path.join(ref, "src", "ORBextractor.cc")):
+        subprocess.check_call(["make", "-C", _HERE, "-s", "ref", f"REF={ref}"] + (["-B"] if force else []))
+    return _LIB_PATH if os.path.exists(_LIB_PATH) else None
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if build() is None:
+            raise RuntimeError("oracle/_ref/liborb_ref.so is missing and the reference checkout is not here to build it")
+        L = C.CDLL(_LIB_PATH)
+        FV = C.POINTER(FrameViewC)
+        L.ref_create.restype = C.c_void_p
+        L.ref_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        L.ref_destroy.argtypes = [C.c_void_p]
+        L.ref_get_tables.argtypes = [C.c_void_p] + [C.c_void_p] * 5
+        L.ref_get_umax.argtypes = [C.c_void_p, C.c_void_p]
+        L.ref_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int,
+                                  C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
+        L.ref_level_size.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.ref_get_plane.restype = C.c_int64
+        L.ref_get_plane.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t]
+        L.ref_get_level_keys.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        L.ref_octree.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                 C.c_void_p, C.c_int]
+        L.ref_hamming.argtypes = [C.c_void_p, C.c_void_p]
+        L.ref_stereo.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                 C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+        L.ref_features_in_area.argtypes = [FV, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.ref_grid_cell.argtypes = [FV, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.ref_search_by_projection.argtypes = ([FV, C.c_int] + [C.c_void_p] * 8 +
+                                               [C.c_float, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p])
+        L.ref_search_by_projection_frame.argtypes = ([FV, C.c_int] + [C.c_void_p] * 7 +
+                                                     [C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p])
+        L.ref_bench_stereo.restype = C.c_double
+        L.ref_bench_stereo.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                       C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int,
+                                       C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        _lib = L
+    return _lib
+
+
+class RefExtractor:
+    """The reference's ORBextractor (same ctor arguments as include/ORBextractor.h:48)."""
+
+    def __init__(self, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7):
+        self.L = lib()
+        self.nlevels = nlevels
+        self.h = self.L.ref_create(nfeatures, scale_factor, nlevels, ini_th, min_th)
+        self.cap = max(4 * nfeatures, 64)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.ref_destroy(self.h)
+            self.h = None
+
+    def tables(self):
+        n = self.nlevels
+        sf, inv, s2, is2 = (np.zeros(n, np.float32) for _ in range(4))
+        per = np.zeros(n, np.int32)
+        self.L.ref_get_tables(self.h, _p(sf), _p(inv), _p(s2), _p(is2), _p(per))
+        return sf, inv, s2, is2, per
+
+    def umax(self):
+        out = np.zeros(16, np.int32)
+        self.L.ref_get_umax(self.h, _p(out))
+        return out
+
+    def extract(self, img, lap=(0, 0)):
+        """operator(): returns (monoIndex, keypoints[KP_DTYPE], descriptors[n,32])."""
+        if img is None or img.size == 0:
+            n = C.c_int(0)
+            r = self.L.ref_extract(self.h, None, 0, 0, 0, lap[0], lap[1], None, None, 0, C.byref(n))
+            return r, np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8)
+        img = np.ascontiguousarray(img, dtype=np.uint8)
+        h, w = img.shape
+        kps = np.zeros(self.cap, KP_DTYPE)
+        desc = np.zeros((self.cap, 32), np.uint8)
+        n = C.c_int(0)
+        mono = self.L.ref_extract(self.h, _p(img), w, h, img.strides[0], lap[0], lap[1], _p(kps), _p(desc),
+                                  self.cap, C.byref(n))
+        if mono < 0:
+            raise RuntimeError(f"reference extract failed: {mono}")
+        return mono, kps[: n.value].copy(), desc[: n.value].copy()
+
+    def level_size(self, level):
+        w, h = C.c_int(), C.c_int()
+        self.L.ref_level_size(self.h, level, C.byref(w), C.byref(h))
+        return w.value, h.value
+
+    def plane(self, level, plane):
+        """0: bordered level (temp), 1: level ROI.  The blurred copy is a local of operator()."""
+        w, h = self.level_size(level)
+        out = np.zeros((h + 38, w + 38) if plane == 0 else (h, w), np.uint8)
+        r = self.L.ref_get_plane(self.h, level, plane, _p(out), out.size)
+        assert r == out.size, r
+        return out
+
+    def level_keys(self, level):
+        out = np.zeros(self.cap, KP_DTYPE)
+        n = self.L.ref_get_level_keys(self.h, level, _p(out), self.cap)
+        return out[:n].copy()
+
+    def octree(self, keys, min_x, max_x, min_y, max_y, n_desired):
+        keys = np.ascontiguousarray(keys, dtype=KP_DTYPE)
+        cap = max(len(keys), 16)
+        out = np.zeros(cap, KP_DTYPE)
+        n = self.L.ref_octree(self.h, _p(keys), len(keys), min_x, max_x, min_y, max_y, n_desired, _p(out), cap)
+        return out[:n].copy()
+
+
+def hamming(a, b):
+    a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+    return lib().ref_hamming(_p(a), _p(b))
+
+
+def stereo(ext_l: RefExtractor, ext_r: RefExtractor, kps_l, desc_l, kps_r, desc_r, mb, mbf):
+    """Frame::ComputeStereoMatches (src/Frame.cc:944-1113, the reference's own body) on the pyramids of the
+    two extractors' last extract.  Returns (mvuRight, mvDepth)."""
+    kps_l = np.ascontiguousarray(kps_l, KP_DTYPE); kps_r = np.ascontiguousarray(kps_r, KP_DTYPE)
+    desc_l = np.ascontiguousarray(desc_l, np.uint8); desc_r = np.ascontiguousarray(desc_r, np.uint8)
+    n = len(kps_l)
+    u = np.full(n, -1, np.float32); d = np.full(n, -1, np.float32)
+    lib().ref_stereo(ext_l.h, ext_r.h, n, _p(kps_l), _p(desc_l), len(kps_r), _p(kps_r), _p(desc_r), mb, mbf,
+                     _p(u), _p(d))
+    return u, d
+
+
+def features_in_area(fv, x, y, r, min_level=-1, max_level=-1, cap=4096):
+    out = np.zeros(cap, np.int32)
+    n = lib().ref_features_in_area(C.byref(fv), x, y, r, min_level, max_level, _p(out), cap)
+    return out[:n].copy()
+
+
+def grid_cell(fv, ix, iy, cap=4096):
+    out = np.zeros(cap, np.int32)
+    n = lib().ref_grid_cell(C.byref(fv), ix, iy, _p(out), cap)
+    return out[:n].copy()
+
+
+def search_by_projection(fv, mp_desc, px, py, pxr, level, view_cos, depth, flags, th, far_points, th_far,
+                         nn_ratio):
+    """ORBmatcher::SearchByProjection(F, vpMapPoints, th, bFarPoints, thFarPoints).
+    Returns (nmatches, best_idx[M], final_binding[N])."""
+    M = len(px)
+    arrs = [np.ascontiguousarray(mp_desc, np.uint8), np.ascontiguousarray(px, np.float32),
+            np.ascontiguousarray(py, np.float32), np.ascontiguousarray(pxr, np.float32),
+            np.ascontiguousarray(level, np.int32), np.ascontiguousarray(view_cos, np.float32),
+            np.ascontiguousarray(depth, np.float32), np.ascontiguousarray(flags, np.uint8)]
+    best = np.zeros(M, np.int32); final = np.zeros(fv.n, np.int32)
+    n = lib().ref_search_by_projection(C.byref(fv), M, *[_p(a) for a in arrs], th, int(far_points), th_far,
+                                       nn_ratio, _p(best), _p(final))
+    return n, best, final
+
+
+def search_by_projection_frame(fv, last_desc, u, v, z, last_octave, last_angle, flags, th, forward, backward,
+                               check_ori=True):
+    """ORBmatcher::SearchByProjection(Cur, Last, th, bMono=false).  z = camera-frame depth (the reference
+    computes 1.0 / z itself).  Returns (nmatches, final_binding[N]: last-frame feature bound to each current
+    feature after the rotation-consistency pass, -1 none)."""
+    n_last = len(u)
+    arrs = [np.ascontiguousarray(last_desc, np.uint8), np.ascontiguousarray(u, np.float32),
+            np.ascontiguousarray(v, np.float32), np.ascontiguousarray(z, np.float32),
+            np.ascontiguousarray(last_octave, np.int32), np.ascontiguousarray(last_angle, np.float32),
+            np.ascontiguousarray(flags, np.uint8)]
+    final = np.zeros(fv.n, np.int32)
+    n = lib().ref_search_by_projection_frame(C.byref(fv), n_last, *[_p(a) for a in arrs], th, int(forward),
+                                             int(backward), int(check_ori), _p(final))
+    return n, final
+
+
+def bench_stereo(left, right, mb, mbf, n_threads, nfeatures=1000, scale=1.2, nlevels=8, ini=20, mn=7):
+    """Time the reference's stereo path over a stack of frames [n,h,w]; returns (seconds, kps, matches)."""
+    left = np.ascontiguousarray(left, np.uint8); right = np.ascontiguousarray(right, np.uint8)
+    n, h, w = left.shape
+    k, m = C.c_int64(0), C.c_int64(0)
+    sec = lib().ref_bench_stereo(nfeatures, scale, nlevels, ini, mn, _p(left), _p(right), n, w, h, mb, mbf,
+                                 n_threads, C.byref(k), C.byref(m))
+    return sec, k.value, m.value
