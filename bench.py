@@ -77,7 +77,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
-                                          "-i", str(self.gpu), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+                                          "-i", str(self.gpu), "-lms", "20"], stdout=subprocess.PIPE, text=True)
             self.t = threading.Thread(target=lambda: [self.lines.append(l) for l in self.proc.stdout], daemon=True)
             self.t.start()
         except Exception:
@@ -108,16 +108,31 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def cpu_module():
+    """(module, kind, label): oracle/_ref (the reference's own ORBextractor.cc + ComputeStereoMatches, compiled
+    unmodified over scalar restated OpenCV primitives) when it is there, else the oracle port."""
+    from oracle import ref_py
+    if ref_py.available():
+        try:
+            ref_py.lib()
+            return ref_py, "reference", ("oracle/_ref: unmodified src/ORBextractor.cc + Frame::ComputeStereoMatches, -O2, "
+                                         "OpenCV calls served by scalar restated primitives (no SIMD/IPP)")
+        except Exception:
+            pass
+    from oracle import oracle_py
+    return oracle_py, "port", "CPU oracle -O2 (restatement)"
+
+
 def cpu_baseline(n_threads, frames_per_thread=12):
-    """Oracle (CPU port of the reference path) on the host cores; bounded sample."""
-    from oracle import oracle_py as op
+    """The reference path on the host cores (oracle/_ref, else the oracle port); bounded sample."""
+    op, kind, label = cpu_module()
     n = max(4, n_threads * frames_per_thread)
     L, R = make_pool(min(n, 48))
     reps = (n + len(L) - 1) // len(L)
     L = np.concatenate([L] * reps)[:n]; R = np.concatenate([R] * reps)[:n]
     op.bench_stereo(L[:n_threads], R[:n_threads], MB, MBF, n_threads)  # warm-up
     sec, kps, matches = op.bench_stereo(L, R, MB, MBF, n_threads)
-    return n / sec, n, kps, matches
+    return n / sec, n, kind, label
 
 
 def run_reference(args):
@@ -125,7 +140,7 @@ def run_reference(args):
     if rank != 0:
         return
     cores = os.cpu_count() or 1
-    from oracle import oracle_py as op
+    op, kind, label = cpu_module()
     per_step = max(4, 2 * cores)
     L, R = make_pool(min(per_step, 48))
     reps = (per_step + len(L) - 1) // len(L)
@@ -137,7 +152,16 @@ def run_reference(args):
         op.bench_stereo(L, R, MB, MBF, cores)
     sec = time.perf_counter() - t0
     fps = per_step * args.steps / sec
-    sample = f"{per_step} synthetic 752x480 stereo pairs per step x {args.steps} steps, {cores} std::threads (one frame each)"
+    sample = f"{per_step} synthetic 752x480 stereo pairs per step x {args.steps} steps, {cores} std::threads (one frame each); {label}"
+    # W2 of the round-1 verdict: the reference links SIMD OpenCV; its pixel stages alone through the real cv2
+    simd = None
+    try:
+        import bench_extras
+        simd = bench_extras.simd_primitives(L[0], reps=2, threads=cores)
+        simd1 = bench_extras.simd_primitives(L[0], reps=6, threads=1)
+        simd["ms_per_image_1core"] = simd1.get("ms_per_image")
+    except Exception as ex:
+        simd = {"unavailable": str(ex)}
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sec / args.steps,
@@ -145,7 +169,11 @@ def run_reference(args):
         "config": {"workload": "cfg5: 752x480 stereo pairs, 1000 features, 8 levels, 1.2, FAST 20/7; "
                                "2x ORBextractor::operator() + Frame::ComputeStereoMatches per frame",
                    "frames_per_step": per_step},
-        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample,
+                         "simd_primitives": simd,
+                         "note": "value = the reference's own control code over SCALAR pixel primitives; simd_primitives = the "
+                                 "pixel stages of one image (1 of the 2 per stereo frame) through the real SIMD cv2, i.e. an "
+                                 "upper bound on what the library the reference links would do for those stages alone"},
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
@@ -250,16 +278,45 @@ def run_cuorb(args):
     B = args.batch
     Lh, Rh = make_pool(B)                       # host pool, distinct frames
     in_bytes = Lh.nbytes + Rh.nbytes            # > L2 (126 MB) at the default batch: no L2 flush needed
-    # --- handles: two pairs for the double-buffered e2e path; pair 0 also serves the resident path
-    pairs = [(ORBextractor(NFEAT, 1.2, 8, 20, 7, max_width=W, max_height=H, max_batch=B, device=local),
-              ORBextractor(NFEAT, 1.2, 8, 20, 7, max_width=W, max_height=H, max_batch=B, device=local))
-             for _ in range(2)]
+    # --- handles: args.pairs pairs in flight on the e2e path; the first two also serve the resident path
+    NP = max(2, args.pairs)
+    all_pairs = [(ORBextractor(NFEAT, 1.2, 8, 20, 7, max_width=W, max_height=H, max_batch=B, device=local),
+                  ORBextractor(NFEAT, 1.2, 8, 20, 7, max_width=W, max_height=H, max_batch=B, device=local))
+                 for _ in range(NP)]
+    pairs = all_pairs[:2]
     cap = pairs[0][0].capacity
     Ld = torch.from_numpy(Lh).cuda(); Rd = torch.from_numpy(Rh).cuda()
 
-    def step_resident(eL, eR):
-        eL.extract_batch_async(Ld); eR.extract_batch_async(Rd)
+    import ctypes
+
+    def pinned(shape, dtype):
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        p = L_.cuorb_host_alloc(n)
+        if not p:
+            raise RuntimeError(_lib.last_error())
+        buf = (ctypes.c_char * n).from_address(p)
+        return np.frombuffer(buf, dtype=dtype).reshape(shape)
+
+    outs = []
+    for _ in range(NP):
+        outs.append(dict(
+            kl=pinned((B, cap), _lib.KP_DTYPE), dl=pinned((B, cap, 32), np.uint8), nl=pinned((B,), np.int32), ml=pinned((B,), np.int32),
+            kr=pinned((B, cap), _lib.KP_DTYPE), dr=pinned((B, cap, 32), np.uint8), nr=pinned((B,), np.int32), mr=pinned((B,), np.int32),
+            u=pinned((B, cap), np.float32), d=pinned((B, cap), np.float32)))
+    d2h_bytes = sum(v.nbytes for v in outs[0].values())
+
+    def enqueue_step(eL, eR, o, srcL, srcR, d2h):
+        """one step on one handle pair: 2 x operator() + ComputeStereoMatches (+ every result back to pinned host)"""
+        eL.extract_batch_async(srcL); eR.extract_batch_async(srcR)
+        if d2h:
+            eR.fetch(o["kr"], o["dr"], o["nr"], o["mr"], sync=False)
         _lib.check(L_.cuorb_stereo_match_batch_async(eL.handle, eR.handle, MB, MBF))
+        if d2h:
+            eL.fetch(o["kl"], o["dl"], o["nl"], o["ml"], sync=False)
+            _lib.check(L_.cuorb_stereo_fetch_async(eL.handle, _lib.ptr(o["u"]), _lib.ptr(o["d"]), cap))
+
+    def step_resident(eL, eR, o=None):
+        enqueue_step(eL, eR, o, Ld, Rd, o is not None)
 
     # ---------------- value: device-resident, CUDA events on the launching (left) stream ----------
     # Steps alternate between the two handle pairs (as in the e2e leg), so step i+1's extraction runs
@@ -267,27 +324,33 @@ def run_cuorb(args):
     # handle's next extraction after the stereo match that reads its buffers.
     eL, eR = pairs[0]
     sL = torch.cuda.ExternalStream(eL.stream, device=local)
-    sL1 = torch.cuda.ExternalStream(pairs[1][0].stream, device=local)
-    for i in range(max(args.warmup, 2)):
-        step_resident(*pairs[i & 1])
-    for p in pairs:
-        p[0].sync(); p[1].sync()
+    others = [torch.cuda.ExternalStream(hd.stream, device=local) for p in pairs for hd in p][1:]
+    def timed_resident(steps, with_d2h):
+        """device-timed loop: frames resident in HBM; with_d2h copies every result (keypoints, descriptors, counts,
+        mvuRight, mvDepth of both eyes) back to pinned host memory each step, as SURVEY 8(d) asks"""
+        for i in range(max(args.warmup, 2)):
+            step_resident(*pairs[i & 1], outs[i & 1] if with_d2h else None)
+        for p in pairs:
+            p[0].sync(); p[1].sync()
+        barrier()
+        l0 = L_.cuorb_kernel_launch_count()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(sL)                  # every stream is idle here (barrier above)
+        for i in range(steps):
+            step_resident(*pairs[i & 1], outs[i & 1] if with_d2h else None)
+        for st in others:               # the timed region ends when all four handle streams (kernels and copies) are done
+            evj = torch.cuda.Event()
+            evj.record(st)
+            sL.wait_event(evj)
+        ev1.record(sL)
+        for p in pairs:
+            p[0].sync(); p[1].sync()
+        barrier()
+        return ev0.elapsed_time(ev1), L_.cuorb_kernel_launch_count() - l0
+
+    ms_nod2h, _ = timed_resident(args.steps, False)
     sampler = ClockSampler(local); sampler.start()
-    barrier()
-    launches0 = L_.cuorb_kernel_launch_count()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    evj = torch.cuda.Event()
-    ev0.record(sL)                      # every stream is idle here (barrier above)
-    for i in range(args.steps):
-        step_resident(*pairs[i & 1])
-    evj.record(sL1)                     # a pair's left stream ends with the stereo match, which waited for the right one
-    sL.wait_event(evj)
-    ev1.record(sL)
-    for p in pairs:
-        p[0].sync(); p[1].sync()
-    barrier()
-    launches = L_.cuorb_kernel_launch_count() - launches0
-    ms_resident = ev0.elapsed_time(ev1)
+    ms_resident, launches = timed_resident(args.steps, True)
     clocks = sampler.stop()
 
     # ---------------- per-stage times (one profiled step, CUDA events inside libcuorb) -------------
@@ -306,55 +369,38 @@ def run_cuorb(args):
     stage_ms = {k: float(np.median(v)) for k, v in stage_acc.items()}   # left handle: B images (+ stereo)
 
     # ---------------- e2e: pinned host frames in, all results out, every step ----------------------
-    def pinned(shape, dtype):
-        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
-        p = L_.cuorb_host_alloc(n)
-        if not p:
-            raise RuntimeError(_lib.last_error())
-        buf = (ctypes.c_char * n).from_address(p)
-        return np.frombuffer(buf, dtype=dtype).reshape(shape)
-
-    import ctypes
     hostL, hostR = pinned(Lh.shape, np.uint8), pinned(Rh.shape, np.uint8)
     hostL[:] = Lh; hostR[:] = Rh
-    outs = []
-    for _ in range(2):
-        outs.append(dict(
-            kl=pinned((B, cap), _lib.KP_DTYPE), dl=pinned((B, cap, 32), np.uint8), nl=pinned((B,), np.int32), ml=pinned((B,), np.int32),
-            kr=pinned((B, cap), _lib.KP_DTYPE), dr=pinned((B, cap, 32), np.uint8), nr=pinned((B,), np.int32), mr=pinned((B,), np.int32),
-            u=pinned((B, cap), np.float32), d=pinned((B, cap), np.float32)))
-    d2h_bytes = sum(v.nbytes for v in outs[0].values())
 
     def step_e2e(i):
-        eL, eR = pairs[i & 1]
-        o = outs[i & 1]
-        eL.sync(); eR.sync()                         # buffers of step i-2 are free again
-        eL.extract_batch_async(hostL); eR.extract_batch_async(hostR)
-        eR.fetch(o["kr"], o["dr"], o["nr"], o["mr"], sync=False)
-        _lib.check(L_.cuorb_stereo_match_batch_async(eL.handle, eR.handle, MB, MBF))
-        eL.fetch(o["kl"], o["dl"], o["nl"], o["ml"], sync=False)
-        _lib.check(L_.cuorb_stereo_fetch_async(eL.handle, _lib.ptr(o["u"]), _lib.ptr(o["d"]), cap))
+        eL, eR = all_pairs[i % NP]
+        eL.sync(); eR.sync()                         # buffers of step i-NP are free again
+        enqueue_step(eL, eR, outs[i % NP], hostL, hostR, True)
 
-    for i in range(max(args.warmup, 2)):
+    for i in range(max(args.warmup, NP)):
         step_e2e(i)
-    for p in pairs:
+    for p in all_pairs:
         p[0].sync(); p[1].sync()
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
         step_e2e(i)
-    for p in pairs:
+    for p in all_pairs:
         p[0].sync(); p[1].sync()
     torch.cuda.synchronize()
     t_e2e = time.perf_counter() - t0
+    # a truncated candidate list / node pool would be a silently wrong batch: ask every handle
+    for p in all_pairs:
+        for hdl in p:
+            _lib.check(L_.cuorb_extractor_status(hdl.handle))
     total_kp = int(outs[0]["nl"].sum() + outs[0]["nr"].sum())
     total_matches = int((outs[0]["u"] >= 0).sum())
 
     # ---------------- max over ranks ----------------
     if world > 1:
-        t = torch.tensor([ms_resident, t_e2e], dtype=torch.float64, device="cuda")
+        t = torch.tensor([ms_resident, t_e2e, ms_nod2h], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_resident, t_e2e = float(t[0]), float(t[1])
+        ms_resident, t_e2e, ms_nod2h = float(t[0]), float(t[1]), float(t[2])
         ln = torch.tensor([launches], dtype=torch.int64, device="cuda")
         dist.all_reduce(ln, op=dist.ReduceOp.SUM)
         launches = int(ln[0])
@@ -391,8 +437,38 @@ def run_cuorb(args):
             pass
         cores = os.cpu_count() or 1
         with_cpu = not args.no_cpu_baseline and world == 1      # the CPU baseline is an N=1 figure
-        cpu_fps, cpu_n, _, _ = cpu_baseline(cores) if with_cpu else (None, 0, 0, 0)
+        cpu_fps, cpu_n, cpu_kind, cpu_label = cpu_baseline(cores) if with_cpu else (None, 0, None, None)
+        # the GPU-side extras run after this rank's handles are gone (they allocate their own arenas)
+        for p_ in all_pairs:
+            for hd in p_:
+                hd.close()
+        del Ld, Rd
+        torch.cuda.empty_cache()
         n1 = preproc_leg(local, min(B, 64), peak, with_cpu) if world == 1 else None
+        extra = {}
+        if world == 1 and not args.no_extras:
+            import bench_extras as bx
+            for name, fn in (("cfg1_single_frame_latency", lambda: bx.cfg1_latency(local, with_cpu)),
+                             ("cfg2_640x480_batched", lambda: bx.cfg2_batched(local, peak)),
+                             ("cfg3_kitti_stereo", lambda: bx.cfg3_kitti(local, peak)),
+                             ("cfg4_projection_50k", lambda: bx.cfg4_projection(local, with_cpu))):
+                try:
+                    extra[name] = fn()
+                except Exception as ex:             # an extra must never take the headline line down with it
+                    extra[name] = {"error": f"{type(ex).__name__}: {ex}"}
+                torch.cuda.empty_cache()
+            try:
+                extra["matcher_pipe_utilisation"] = json.load(open(os.path.join(ROOT, "profiles", "pipe_util.json")))
+            except Exception:
+                pass
+        copy_ceiling = None
+        try:
+            sw = json.load(open(os.path.join(ROOT, "profiles", "r02_h2d_sweep.json")))
+            rows = [r for r in sw["rows"] if r["n"] == world and r["mem"] == "pinned" and r["d2h"]]
+            if rows:
+                copy_ceiling = max(r["stereo_frames_per_s_ceiling"] for r in rows)
+        except Exception:
+            pass
         line = {
             "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_resident / args.steps, "higher_is_better": True,
@@ -402,11 +478,19 @@ def run_cuorb(args):
                        "frames_per_step_per_gpu": B, "parallelism": f"frame-sharded x{world}, no collective",
                        "cpu_affinity_rank0": numa,
                        "l2": f"inputs {in_bytes / 1e6:.0f} MB + pyramids per step exceed the 126 MB L2 (no flush needed)",
-                       "value_leg": "frames resident in HBM, results left in HBM",
+                       "value_leg": "frames resident in HBM; keypoints, descriptors, counts, mvuRight, mvDepth of every frame "
+                                    "copied back to pinned host memory inside the timed region (SURVEY 8d)",
+                       "e2e_pairs_in_flight": NP,
                        "keypoints_per_frame": total_kp / B, "stereo_matches_per_frame": total_matches / B},
             "clocks": clocks,
+            "value_results_left_in_hbm": frames / (ms_nod2h * 1e-3),
             "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": in_bytes * world,
-                    "d2h_bytes_per_step": d2h_bytes * world, "ms_per_step": 1e3 * t_e2e / args.steps},
+                    "d2h_bytes_per_step": d2h_bytes * world, "ms_per_step": 1e3 * t_e2e / args.steps,
+                    "h2d_gbs": in_bytes * world / (t_e2e / args.steps) / 1e9,
+                    "copy_ceiling_frames_per_s": copy_ceiling,
+                    "frac_of_copy_ceiling": (e2e / copy_ceiling) if copy_ceiling else None,
+                    "copy_ceiling_source": "profiles/r02_h2d_sweep.json: bare pinned->device + device->pinned copies of one "
+                                           "step's bytes per GPU, no kernels, same N (scripts/h2d_sweep.py)"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
                          "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,
@@ -416,9 +500,10 @@ def run_cuorb(args):
                          "dominant_stage_overall": dom_all, "dominant_stage_pipe_utilisation": pipe,
                          "algorithmic_bytes_per_image": ab},
             "cpu_baseline": None if cpu_fps is None else {
-                "value": cpu_fps, "unit": "frames/s", "cores": cores, "kind": "port",
-                "sample": f"{cpu_n} synthetic 752x480 stereo pairs, {cores} std::threads (one frame each), CPU oracle -O2"},
+                "value": cpu_fps, "unit": "frames/s", "cores": cores, "kind": cpu_kind,
+                "sample": f"{cpu_n} synthetic 752x480 stereo pairs, {cores} std::threads (one frame each); {cpu_label}"},
             "n1_frame_preparation": n1,
+            "extra": extra,
         }
         sys.stdout.flush()
         os.write(json_fd, (json.dumps(line) + "\n").encode())
@@ -437,6 +522,8 @@ def main():
     ap.add_argument("--impl", default="cuorb", choices=["cuorb", "reference"])
     ap.add_argument("--batch", type=int, default=256, help="stereo pairs per step per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the cfg1-cfg4 side measurements (N=1 only)")
+    ap.add_argument("--pairs", type=int, default=3, help="handle pairs in flight on the e2e leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "cuorb" else args.warmup
     if args.impl == "reference":

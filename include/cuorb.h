@@ -114,6 +114,12 @@ int cuorb_extract_fetch(cuorb_extractor* ext, cuorb_keypoint* kps, uint8_t* desc
 int cuorb_extract_fetch_async(cuorb_extractor* ext, cuorb_keypoint* kps, uint8_t* desc,
                               int capacity, int32_t* n_out, int32_t* mono_index_out);
 int cuorb_sync(cuorb_extractor* ext);
+/* Status of the last batch fetched with cuorb_extract_fetch_async, to be called after cuorb_sync():
+ * CUORB_OK, or CUORB_E_CAPACITY when an internal list overflowed (FAST candidates / quadtree nodes:
+ * the batch is truncated, not silently wrong) or when an image produced more keypoints than the
+ * `capacity` given to the fetch.  The synchronous calls perform the same check themselves.  (The
+ * reference has no such failure mode: its std::vectors grow; src/ORBextractor.cc:767 only reserves.) */
+int cuorb_extractor_status(cuorb_extractor* ext);
 /* The handle's cudaStream_t (as void*): lets a caller order its own work / record CUDA events
  * (e.g. torch.cuda.ExternalStream) against the enqueued pipeline.  The library also runs part of an
  * extraction (the blur) on a second, internal stream; that work is forked from and joined back into

@@ -65,6 +65,7 @@ SIGNATURES = {
     "cuorb_extract_fetch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "cuorb_extract_fetch_async": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "cuorb_sync": (C.c_int, [C.c_void_p]),
+    "cuorb_extractor_status": (C.c_int, [C.c_void_p]),
     "cuorb_extractor_stream": (C.c_void_p, [C.c_void_p]),
     "cuorb_extractor_pyramid": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p),
                                           C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_size_t)]),

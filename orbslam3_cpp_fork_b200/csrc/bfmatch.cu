@@ -202,8 +202,7 @@ int cuorb_distinctive_descriptors(int device, int n_points, const int32_t* off, 
   if (total > 0) BF_TRY(cudaMemcpyAsync(dd, desc, 32 * (size_t)total, cudaMemcpyHostToDevice, st));
   BF_TRY(cudaMemcpyAsync(doff, off, 4 * (size_t)(n_points + 1), cudaMemcpyHostToDevice, st));
   const int smem = 32 * std::max(maxn, 1) + 32 * 258 * 2;
-  static int attr = 48 * 1024;
-  if (smem > attr) { cudaFuncSetAttribute(k_distinctive, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); attr = smem; }
+  if (smem > 48 * 1024) cudaFuncSetAttribute(k_distinctive, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);   // per device
   k_distinctive<<<n_points, 32, smem, st>>>(dd, doff, dbest);
   count_launch();
   BF_TRY(cudaGetLastError());

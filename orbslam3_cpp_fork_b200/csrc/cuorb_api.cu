@@ -71,6 +71,7 @@ struct cuorb_extractor {
   size_t cap_input = 0, cap_pyr = 0, cap_blur = 0, cap_cand = 0, cap_keys = 0, cap_kp = 0;
   size_t cap_xtab = 0, cap_ytab = 0, cap_tiles = 0, cap_cells = 0;
   int    n_img = 0;       // images in the last batch
+  int    fetch_n = 0, fetch_capacity = 0;   // last fetch: images copied to h_out_n / caller capacity (0: no kps/desc asked)
   bool   have_batch = false, have_stereo = false;
 };
 
@@ -708,6 +709,7 @@ int cuorb_extract_fetch_async(cuorb_extractor* e, cuorb_keypoint* kps, uint8_t* 
   CUORB_CUDA_TRY(cudaSetDevice(e->cfg.device));
   cudaStream_t st = e->stream;
   const int n = e->n_img, cap = e->g.kp_cap, cw = std::min(capacity, cap);
+  e->fetch_n = n; e->fetch_capacity = (kps || desc) ? capacity : 0;
   CUORB_CUDA_TRY(cudaMemcpyAsync(e->h_out_n, e->d_out_n, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
   CUORB_CUDA_TRY(cudaMemcpyAsync(e->h_out_mono, e->d_out_mono, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
   CUORB_CUDA_TRY(cudaMemcpyAsync(e->h_flags, e->d_flags, sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -730,17 +732,26 @@ int cuorb_sync(cuorb_extractor* e) {
   return CUORB_OK;
 }
 
+// after a fetch has completed (stream synchronised): overflow flags and caller capacity
+int cuorb_extractor_status(cuorb_extractor* e) {
+  if (!e) { set_error("null handle"); return CUORB_E_BADARG; }
+  if (e->fetch_n <= 0) return CUORB_OK;
+  int rc = check_flags(e);
+  if (rc != CUORB_OK) return rc;
+  if (e->fetch_capacity > 0)
+    for (int i = 0; i < e->fetch_n; i++)
+      if (e->h_out_n[i] > e->fetch_capacity) { set_error("caller capacity smaller than the keypoint count"); return CUORB_E_CAPACITY; }
+  return CUORB_OK;
+}
+
 int cuorb_extract_fetch(cuorb_extractor* e, cuorb_keypoint* kps, uint8_t* desc, int capacity,
                         int32_t* n_out, int32_t* mono_out) {
   int n = cuorb_extract_fetch_async(e, kps, desc, capacity, n_out, mono_out);
   if (n < 0) return n;
   int rc = cuorb_sync(e);
   if (rc != CUORB_OK) return rc;
-  rc = check_flags(e);
+  rc = cuorb_extractor_status(e);
   if (rc != CUORB_OK) return rc;
-  if (kps || desc)
-    for (int i = 0; i < n; i++)
-      if (e->h_out_n[i] > capacity) { set_error("caller capacity smaller than the keypoint count"); return CUORB_E_CAPACITY; }
   return n;
 }
 
@@ -903,7 +914,10 @@ int cuorb_stereo_match(cuorb_extractor* l, cuorb_extractor* r, int n_left, const
   CUORB_CUDA_TRY(cudaStreamSynchronize(l->stream));  // &n_left / &n_right are stack variables
   CUORB_CUDA_TRY(cudaStreamSynchronize(r->stream));
   CUORB_CUDA_TRY(cudaEventRecord(r->ev_done, r->stream));
-  const int saved_l = l->n_img, saved_r = r->n_img;
+  struct Restore {  // the batch size of both handles is put back on every exit path
+    cuorb_extractor *l, *r; int nl, nr;
+    ~Restore() { l->n_img = nl; r->n_img = nr; }
+  } restore{l, r, l->n_img, r->n_img};
   l->n_img = 1; r->n_img = 1;
   int rc = cuorb_stereo_match_batch_async(l, r, mb, mbf);
   if (rc == CUORB_OK) {
@@ -911,7 +925,6 @@ int cuorb_stereo_match(cuorb_extractor* l, cuorb_extractor* r, int n_left, const
     CUORB_CUDA_TRY(cudaMemcpyAsync(depth, l->d_depth, 4 * (size_t)n_left, cudaMemcpyDeviceToHost, l->stream));
     rc = cuorb_sync(l);
   }
-  l->n_img = saved_l; r->n_img = saved_r;
   return rc;
 }
 

@@ -253,8 +253,7 @@ void launch_describe(const ExtractorGeom& g, const ExtractorGeom* dg, const TmaM
                      int* out_mono, cudaStream_t st) {
   (void)pyr; (void)blur;  // read through the TMA tensor maps
   const int smem = DESC_WARPS * (IC_SLOT + BR_SLOT) + 128;
-  static bool attr = false;
-  if (!attr) { cudaFuncSetAttribute(k_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); attr = true; }
+  if (smem > 48 * 1024) cudaFuncSetAttribute(k_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);   // per device
   k_finalize<<<n_img, 256, 0, st>>>(dg, keys, key_count, lap0, lap1, slot_map, out_n, out_mono);
   k_describe<<<dim3((g.kp_cap + DESC_WARPS - 1) / DESC_WARPS, n_img), DESC_WARPS * 32, smem, st>>>(
       dg, tmaps, keys, key_count, slot_map, out_kps, out_desc);

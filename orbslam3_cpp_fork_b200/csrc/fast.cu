@@ -29,6 +29,8 @@
 #include <algorithm>
 #include <cstdlib>
 
+#include <mutex>
+
 #include "common.cuh"
 #include "tma.cuh"
 
@@ -566,11 +568,8 @@ static void launch_fast_tp(const ExtractorGeom& g, const ExtractorGeom* dg, cons
   const int ccap        = 64 * ((2 * maxquads + 127) / 128);      // per-warp corner list (entries)
   const int list_bytes  = 4 * ((g.max_cell_w + 1) / 2) * ((g.max_cell_h + 1) / 2);
   const int smem        = tile_bytes + tile8_bytes + score_bytes + 2 * 4 * (pcap + ccap) + list_bytes;
-  static int attr = 48 * 1024;
-  if (smem > attr) {
-    cudaFuncSetAttribute(k_fast_cells<TP, TPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    attr = smem;
-  }
+  // the attribute is per device, not per process: set on every launch that needs it
+  if (smem > 48 * 1024) cudaFuncSetAttribute(k_fast_cells<TP, TPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   k_fast_cells<TP, TPB><<<dim3(g.total_cells, n_img), 128, smem, st>>>(dg, cells, pyr, cand, cand_count, flags, tile_bytes,
                                                                        tile8_bytes, score_bytes, pcap, ccap);
 }
@@ -605,17 +604,23 @@ void launch_fast_persist(const ExtractorGeom& g, const FastMaps& maps, const int
   P.pcap = 64 * ((maxquads + 32 * NW - 1) / (32 * NW));
   const int smem = 128 + 2 * P.tile_bytes + 2 * P.score_bytes + 2 * NW * P.pcap;   // one u16 list per warp: pairs, then corner pairs in place
   void (*kern)(const FastMaps, const FastParams) = NW == 1 ? k_fast_persist<1> : NW == 2 ? k_fast_persist<2> : k_fast_persist<4>;
-  static int attr = 48 * 1024, per_sm = 0, attr_smem = -1, n_sm = 0;
-  if (smem > attr) {
-    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    attr = smem;
-  }
-  if (attr_smem != smem) {
+  if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);   // per device
+  // occupancy and SM count, cached per (device, smem) under a lock: the two ExtractORB threads of the stereo
+  // Frame constructor pass through here concurrently, possibly for handles on different devices
+  int per_sm = 0, n_sm = 0;
+  {
+    static std::mutex mu;
+    static int c_smem[64], c_per_sm[64], c_n_sm[64];
     int dev = 0;
     cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 32 * NW, smem);
-    attr_smem = smem;
+    std::lock_guard<std::mutex> lk(mu);
+    const int slot = dev & 63;
+    if (c_n_sm[slot] == 0 || c_smem[slot] != smem) {
+      cudaDeviceGetAttribute(&c_n_sm[slot], cudaDevAttrMultiProcessorCount, dev);
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c_per_sm[slot], kern, 32 * NW, smem);
+      c_smem[slot] = smem;
+    }
+    per_sm = c_per_sm[slot]; n_sm = c_n_sm[slot];
   }
   // CTAs per SM: with the single in-place list 13-14 CTAs fit and FAST alone is fastest that way (0.594 ms per 256
   // images), but the whole step then loses 3 % (90.6k against 93k frames/s): the other handles' blur / quadtree /

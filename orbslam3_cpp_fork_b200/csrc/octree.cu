@@ -498,11 +498,7 @@ void launch_octree(const ExtractorGeom& g, const ExtractorGeom* dg, int n_img, c
   int cap = 0;
   for (int l = 0; l < g.nlevels; l++) cap = max(cap, g.lv[l].node_cap);
   const size_t smem = octree_node_bytes(cap) + (size_t)OT_KEYCAP * 6;
-  static size_t attr = 48 * 1024;
-  if (smem > attr) {
-    cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    attr = smem;
-  }
+  if (smem > 48 * 1024) cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   // per device
   k_octree<<<dim3(g.nlevels, n_img), OT_THREADS, smem, st>>>(dg, cand, cand_scratch, cand_count, keys,
                                                              key_count, flags, cap);
   count_launch();
