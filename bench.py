@@ -30,6 +30,7 @@ W, H, NFEAT = 752, 480, 1000
 FX, MBF = 458.654, 47.90639384423901  # EuRoC stereo: Camera.fx, Camera.bf (Examples_old/Stereo/EuRoC.yaml:40)
 MB = MBF / FX
 METRIC = "ORB extract+match frames/s @752x480,1000kp"
+N_FRAMES = 100_000   # cfg5: the sweep runs over frame ids 0 .. 99,999 of the generator, sharded round-robin over ranks
 
 
 def level_sizes(w, h, nlevels=8, sf=1.2):
@@ -50,20 +51,23 @@ def algorithmic_bytes(w, h):
     return dict(pyramid=sum(P[:-1]) + P[0] + sum(B), blur=2 * sum(P), fast=2 * sum(P))
 
 
-def make_pool(n_pairs, base=24):
-    """n_pairs distinct synthetic stereo pairs: `base` generated, the rest are horizontal rolls
-    (same roll on both eyes keeps the disparity field)."""
-    from orbslam3_cpp_fork_b200 import synth
-    Ls, Rs = [], []
-    for i in range(min(base, n_pairs)):
-        l, r = synth.synth_stereo_pair(W, H, 1000 + i)
-        Ls.append(l); Rs.append(r)
-    i = 0
-    while len(Ls) < n_pairs:
-        sh = 37 * (len(Ls) // base) + 11
-        Ls.append(np.roll(Ls[i % base], sh, axis=1)); Rs.append(np.roll(Rs[i % base], sh, axis=1))
-        i += 1
-    return np.stack(Ls), np.stack(Rs)
+def _host_pair(frame_id):
+    from orbslam3_cpp_fork_b200 import synth_cb
+    return synth_cb.stereo_pair(frame_id, W, H)
+
+
+def make_pool(n_pairs, first_id=0):
+    """n_pairs distinct synthetic stereo pairs on the HOST (frames first_id .. of the counter-based generator,
+    orbslam3_cpp_fork_b200/synth_cb.py — the same frames the device generator produces), one process per core."""
+    from concurrent.futures import ProcessPoolExecutor
+    ids = [(first_id + i) % N_FRAMES for i in range(n_pairs)]
+    if n_pairs <= 2:
+        res = [_host_pair(f) for f in ids]
+    else:
+        import multiprocessing as mp
+        with ProcessPoolExecutor(max_workers=min(n_pairs, os.cpu_count() or 1), mp_context=mp.get_context("spawn")) as ex:
+            res = list(ex.map(_host_pair, ids, chunksize=max(1, n_pairs // (4 * (os.cpu_count() or 1)))))
+    return np.stack([r[0] for r in res]), np.stack([r[1] for r in res])
 
 
 class ClockSampler:
@@ -259,6 +263,12 @@ def run_cuorb(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; libcuorb has no CPU fallback (use --impl reference for the CPU arm)")
+    # rank -> GPU: when the box shows more GPUs than ranks, spread the ranks over the box (GPU r * ngpu/N): on this
+    # pool GPUs 0-3 share host-side PCIe bandwidth (profiles/r02_h2d_sweep.json: 4 ranks on GPUs 0-3 copy 94 GB/s,
+    # on GPUs 0,2,4,6 154 GB/s), which is all the e2e leg is bound by.  --gpu-map identity turns it off.
+    ngpu = torch.cuda.device_count()
+    if args.gpu_map == "spread" and world > 1 and ngpu > world and ngpu % world == 0:
+        local = local * (ngpu // world)
     torch.cuda.set_device(local)
     numa = bind_to_gpu_numa(local) if world > 1 else None
     # stdout carries exactly one JSON line: libraries that print there from C (NCCL's version banner at
@@ -276,8 +286,30 @@ def run_cuorb(args):
         torch.cuda.synchronize()
 
     B = args.batch
-    Lh, Rh = make_pool(B)                       # host pool, distinct frames
-    in_bytes = Lh.nbytes + Rh.nbytes            # > L2 (126 MB) at the default batch: no L2 flush needed
+    in_bytes = 2 * B * W * H                    # > L2 (126 MB) at the default batch: no L2 flush needed
+    # cfg5: every step works on DISTINCT frames, generated on the device before the timed region
+    # (cuorb_synth_stereo, csrc/synth.cu).  Step i of rank r takes frames ((i * world + r) * B ...) mod 100k.
+    from orbslam3_cpp_fork_b200 import synth_cb
+    n_distinct = max(2, min(args.steps + 3, int(args.gen_gb * 1e9 // in_bytes)))
+    pool_dev = []
+    scratch = torch.empty((B, H, W), dtype=torch.uint8, device=f"cuda:{local}")
+    t_gen = time.perf_counter()
+    for i in range(n_distinct):
+        l_ = torch.empty((B, H, W), dtype=torch.uint8, device=f"cuda:{local}")
+        r_ = torch.empty((B, H, W), dtype=torch.uint8, device=f"cuda:{local}")
+        synth_cb.stereo_batch_device(((i * world + rank) * B) % N_FRAMES, B, W, H, device=local, out=(l_, r_, scratch))
+        pool_dev.append((l_, r_))
+    torch.cuda.synchronize()
+    t_gen = time.perf_counter() - t_gen
+    del scratch
+    # spot certification inside the run (the 1,000-pair certification is tests/test_gpu_synth.py)
+    cert_ids = [(rank * B) % N_FRAMES, (rank * B + B - 1) % N_FRAMES]
+    cert_ok = True
+    for j, fid in zip((0, B - 1), cert_ids):
+        hl, hr = _host_pair(fid)
+        cert_ok &= bool((pool_dev[0][0][j].cpu().numpy() == hl).all() and (pool_dev[0][1][j].cpu().numpy() == hr).all())
+    if not cert_ok:
+        raise SystemExit("bench.py: device-generated frames differ from the host definition (synth_cb.py)")
     # --- handles: args.pairs pairs in flight on the e2e path; the first two also serve the resident path
     NP = max(2, args.pairs)
     all_pairs = [(ORBextractor(NFEAT, 1.2, 8, 20, 7, max_width=W, max_height=H, max_batch=B, device=local),
@@ -285,7 +317,7 @@ def run_cuorb(args):
                  for _ in range(NP)]
     pairs = all_pairs[:2]
     cap = pairs[0][0].capacity
-    Ld = torch.from_numpy(Lh).cuda(); Rd = torch.from_numpy(Rh).cuda()
+    Ld, Rd = pool_dev[0]
 
     import ctypes
 
@@ -315,8 +347,12 @@ def run_cuorb(args):
             eL.fetch(o["kl"], o["dl"], o["nl"], o["ml"], sync=False)
             _lib.check(L_.cuorb_stereo_fetch_async(eL.handle, _lib.ptr(o["u"]), _lib.ptr(o["d"]), cap))
 
+    step_no = [0]
+
     def step_resident(eL, eR, o=None):
-        enqueue_step(eL, eR, o, Ld, Rd, o is not None)
+        l_, r_ = pool_dev[step_no[0] % n_distinct]
+        step_no[0] += 1
+        enqueue_step(eL, eR, o, l_, r_, o is not None)
 
     # ---------------- value: device-resident, CUDA events on the launching (left) stream ----------
     # Steps alternate between the two handle pairs (as in the e2e leg), so step i+1's extraction runs
@@ -369,13 +405,19 @@ def run_cuorb(args):
     stage_ms = {k: float(np.median(v)) for k, v in stage_acc.items()}   # left handle: B images (+ stereo)
 
     # ---------------- e2e: pinned host frames in, all results out, every step ----------------------
-    hostL, hostR = pinned(Lh.shape, np.uint8), pinned(Rh.shape, np.uint8)
-    hostL[:] = Lh; hostR[:] = Rh
+    # host side of the e2e leg: a pinned ring of distinct batches (copied down from the device pool)
+    n_host = max(2, min(n_distinct, args.host_batches))
+    host_pool = []
+    for i in range(n_host):
+        hl_, hr_ = pinned((B, H, W), np.uint8), pinned((B, H, W), np.uint8)
+        hl_[:] = pool_dev[i][0].cpu().numpy(); hr_[:] = pool_dev[i][1].cpu().numpy()
+        host_pool.append((hl_, hr_))
 
     def step_e2e(i):
         eL, eR = all_pairs[i % NP]
         eL.sync(); eR.sync()                         # buffers of step i-NP are free again
-        enqueue_step(eL, eR, outs[i % NP], hostL, hostR, True)
+        hl_, hr_ = host_pool[i % n_host]
+        enqueue_step(eL, eR, outs[i % NP], hl_, hr_, True)
 
     for i in range(max(args.warmup, NP)):
         step_e2e(i)
@@ -443,6 +485,7 @@ def run_cuorb(args):
             for hd in p_:
                 hd.close()
         del Ld, Rd
+        pool_dev.clear()
         torch.cuda.empty_cache()
         n1 = preproc_leg(local, min(B, 64), peak, with_cpu) if world == 1 else None
         extra = {}
@@ -476,11 +519,18 @@ def run_cuorb(args):
             "config": {"workload": "cfg5: 752x480 stereo pairs, 1000 features, 8 levels, 1.2, FAST 20/7; "
                                    "2x ORBextractor::operator() + Frame::ComputeStereoMatches per frame",
                        "frames_per_step_per_gpu": B, "parallelism": f"frame-sharded x{world}, no collective",
+                       "gpu_of_rank0": local, "gpu_map": args.gpu_map,
                        "cpu_affinity_rank0": numa,
                        "l2": f"inputs {in_bytes / 1e6:.0f} MB + pyramids per step exceed the 126 MB L2 (no flush needed)",
                        "value_leg": "frames resident in HBM; keypoints, descriptors, counts, mvuRight, mvDepth of every frame "
                                     "copied back to pinned host memory inside the timed region (SURVEY 8d)",
                        "e2e_pairs_in_flight": NP,
+                       "frames": {"generator": "counter-based synth_cb (numpy definition) == cuorb_synth_stereo (device), frame ids "
+                                               "0..99,999 sharded round-robin over ranks",
+                                  "distinct_pairs_per_gpu_in_this_run": n_distinct * B, "steps_cycle_over_batches": n_distinct,
+                                  "generated_on_device_in_s": t_gen, "host_pinned_batches_e2e": n_host,
+                                  "host_certified_in_this_run": cert_ids,
+                                  "certification": "tests/test_gpu_synth.py::test_certified_subset_1000_pairs (every 100th id)"},
                        "keypoints_per_frame": total_kp / B, "stereo_matches_per_frame": total_matches / B},
             "clocks": clocks,
             "value_results_left_in_hbm": frames / (ms_nod2h * 1e-3),
@@ -524,6 +574,10 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the cfg1-cfg4 side measurements (N=1 only)")
     ap.add_argument("--pairs", type=int, default=3, help="handle pairs in flight on the e2e leg")
+    ap.add_argument("--gpu-map", default="spread", choices=["spread", "identity"],
+                    help="rank -> GPU when the box has more GPUs than ranks")
+    ap.add_argument("--gen-gb", type=float, default=40.0, help="HBM budget for device-generated distinct input batches")
+    ap.add_argument("--host-batches", type=int, default=8, help="distinct batches in the pinned host ring of the e2e leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "cuorb" else args.warmup
     if args.impl == "reference":

@@ -73,6 +73,16 @@ def cfg1_latency(local, with_cpu=True, calls=300):
         t0 = time.perf_counter(); extract(e, imgL, bufs[0], 1000); ts.append(time.perf_counter() - t0)
     out["cuorb_extract_mono"] = _stats(ts)
     out["keypoints"] = int(bufs[0][2].value)
+    # where the time of one call goes on the device: per-stage CUDA events (stages serialised while profiling)
+    e.set_profiling(True)
+    acc = {}
+    for _ in range(20):
+        extract(e, imgL, bufs[0], 1000)
+        for k_, v_ in e.stage_ms().items():
+            acc.setdefault(k_, []).append(v_)
+    e.set_profiling(False)
+    out["device_stage_ms_batch1"] = {k_: float(np.median(v_)) for k_, v_ in acc.items() if k_ != "stereo"}
+    out["device_stage_ms_batch1"]["sum"] = float(sum(out["device_stage_ms_batch1"].values()))
 
     # the stereo Frame constructor's sequence (src/Frame.cc:202-231): two ExtractORB threads on two handles,
     # then ComputeStereoMatches on the results

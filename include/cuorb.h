@@ -227,6 +227,15 @@ int cuorb_search_by_projection_frame(int device, const cuorb_frame_view* cur, in
                                      int32_t* best_idx_out, int32_t* rot_bin_out,
                                      int32_t* keep_bins_out);
 
+/* ---- benchmark input side ("cfg5") ----
+ * Synthetic stereo pairs generated ON THE DEVICE: frames first_frame_id .. first_frame_id + n_pairs - 1 of
+ * the counter-based generator defined by orbslam3_cpp_fork_b200/synth_cb.py (integer arithmetic only; the
+ * CUDA and numpy statements agree byte for byte, tests/test_gpu_synth.py).  d_left / d_right: device, tightly
+ * packed n_pairs x height x width u8; d_scratch: device, same size (the left eye before pixel noise).
+ * Enqueued on `stream` (a cudaStream_t, may be NULL).  No counterpart in the reference (it reads datasets). */
+int cuorb_synth_stereo(int device, uint64_t first_frame_id, int n_pairs, int width, int height,
+                       uint8_t* d_left, uint8_t* d_right, uint8_t* d_scratch, void* stream);
+
 /* ---- pre-extraction image operations ----
  * What System::TrackStereo / TrackRGBD / TrackMonocular (src/System.cc:280-300, 384-386, 476) and
  * Tracking::GrabImageStereo / RGBD / Monocular (src/Tracking.cc:1339-1357, 1449-1462, 1520-1533)
@@ -270,6 +279,34 @@ int cuorb_extract_batch_async_pre(cuorb_extractor* ext, cuorb_preproc* pre, int 
  * Host arrays; kps_un may alias kps.  Returns n. */
 int cuorb_undistort_keypoints(int device, int n, const cuorb_keypoint* kps, const float* K4,
                               const float* dist5, cuorb_keypoint* kps_un);
+
+/* bool Frame::isInFrustum(MapPoint* pMP, float viewingCosLimit) (src/Frame.cc:644-707, the Nleft == -1
+ * branch; MapPoint::PredictScale src/MapPoint.cc:574-589; Pinhole::project src/CameraModels/Pinhole.cpp:70-76)
+ * for n MapPoints at once: the producer of mbTrackInView / mTrackProjX / mTrackProjY / mTrackProjXR /
+ * mnTrackScaleLevel / mTrackViewCos / mTrackDepth that cuorb_search_by_projection consumes
+ * (Tracking::SearchLocalPoints, src/Tracking.cc).  camera: the Frame members the function reads.
+ * world_pos / normal: n x 3 floats (GetWorldPos / GetNormal); min_distance / max_distance: mfMinDistance /
+ * mfMaxDistance (the 0.8 / 1.2 invariance factors are applied here, as GetMin/MaxDistanceInvariance do).
+ * Outputs (host arrays of n): in_view = the return value; proj_x / proj_y = -1 unless the projection falls
+ * inside the image bounds (the reference writes them before the distance / angle tests); proj_xr,
+ * scale_level, view_cos, depth are only meaningful where in_view (else -1, -1, 0, 0).
+ * Float policy: every operation is a single round-to-nearest float operation in the reference's expression
+ * order with Eigen's size-3 reduction order x0 + (x1 + x2) and no FMA contraction (the reference's own build,
+ * -O3 -march=native, may contract); log() of PredictScale is evaluated in double and rounded.
+ * Returns the number of MapPoints in view. */
+typedef struct cuorb_frustum_camera {
+  float rcw[9];   /* mRcw, row-major */
+  float tcw[3];   /* mtcw */
+  float ow[3];    /* mOw */
+  float fx, fy, cx, cy, mbf;
+  float min_x, max_x, min_y, max_y;   /* mnMinX .. mnMaxY */
+  float log_scale_factor;             /* mfLogScaleFactor */
+  int32_t n_levels;                   /* mnScaleLevels */
+} cuorb_frustum_camera;
+int cuorb_is_in_frustum(int device, const cuorb_frustum_camera* camera, int n, const float* world_pos,
+                        const float* normal, const float* min_distance, const float* max_distance,
+                        float viewing_cos_limit, uint8_t* in_view, float* proj_x, float* proj_y,
+                        float* proj_xr, int32_t* scale_level, float* view_cos, float* depth);
 
 /* void Frame::ComputeStereoFromRGBD(const cv::Mat& imDepth) (src/Frame.cc:1115-1133): depth = CV_32F
  * image (row pitch stride_bytes) in host or device memory; d = imDepth(v, u) at the truncated

@@ -10,8 +10,10 @@
 //   x = (x0 - dX)*icdist;  y = (y0 - dY)*icdist
 // then the projection by P = K, rounded to float.  Pinned against cv2.undistortPoints 4.13.0
 // (tests/test_oracle_frameglue.py, tests/golden/frameglue_cv2.npz).  Compiled -ffp-contract=off.
+#include <cmath>
 #include <cstring>
 
+#include "../include/cuorb.h"  // POD layout of cuorb_frustum_camera only
 #include "orb_oracle.hpp"
 
 namespace orb_oracle {
@@ -60,6 +62,48 @@ void stereo_from_rgbd(const KeyPoint* kps, const KeyPoint* kps_un, int n, const 
   }
 }
 
+// Frame::isInFrustum, Nleft == -1 branch (src/Frame.cc:644-707) with MapPoint::PredictScale
+// (src/MapPoint.cc:574-589) and Pinhole::project (src/CameraModels/Pinhole.cpp:70-76), for n points.
+// Float expressions as written, one rounding per operation (-ffp-contract=off); sums of three products
+// associate as Eigen 3.4's unrolled size-3 reduction does, x0 + (x1 + x2).  Checked against the reference's
+// own lifted body in tests/test_oracle_vs_ref.py.
+int is_in_frustum(const cuorb_frustum_camera& c, int n, const float* P3, const float* N3, const float* minD,
+                  const float* maxD, float viewingCosLimit, uint8_t* in_view, float* projX, float* projY,
+                  float* projXR, int32_t* level, float* viewCosOut, float* depth) {
+  int count = 0;
+  for (int i = 0; i < n; i++) {
+    in_view[i] = 0; projX[i] = -1; projY[i] = -1;              // :646-648
+    projXR[i] = -1; level[i] = -1; viewCosOut[i] = 0; depth[i] = 0;
+    const float* P = P3 + 3 * i;
+    float Pc[3];
+    for (int r = 0; r < 3; r++)                                  // Pc = mRcw * P + mtcw (:654)
+      Pc[r] = (c.rcw[3 * r] * P[0] + (c.rcw[3 * r + 1] * P[1] + c.rcw[3 * r + 2] * P[2])) + c.tcw[r];
+    const float Pc_dist = std::sqrt(Pc[0] * Pc[0] + (Pc[1] * Pc[1] + Pc[2] * Pc[2]));   // :655
+    const float PcZ = Pc[2];
+    const float invz = 1.0f / PcZ;                               // :659
+    if (PcZ < 0.0f) continue;                                    // :660
+    const float u = c.fx * Pc[0] / Pc[2] + c.cx, v = c.fy * Pc[1] / Pc[2] + c.cy;   // Pinhole::project
+    if (u < c.min_x || u > c.max_x) continue;                    // :666
+    if (v < c.min_y || v > c.max_y) continue;                    // :669
+    projX[i] = u; projY[i] = v;                                  // :673-674
+    const float maxDistance = 1.2f * maxD[i], minDistance = 0.8f * minD[i];   // MapPoint.cc:547-555
+    const float PO[3] = {P[0] - c.ow[0], P[1] - c.ow[1], P[2] - c.ow[2]};
+    const float dist = std::sqrt(PO[0] * PO[0] + (PO[1] * PO[1] + PO[2] * PO[2]));     // :680
+    if (dist < minDistance || dist > maxDistance) continue;      // :682
+    const float* Pn = N3 + 3 * i;
+    const float viewCos = (PO[0] * Pn[0] + (PO[1] * Pn[1] + PO[2] * Pn[2])) / dist;    // :689
+    if (viewCos < viewingCosLimit) continue;                     // :691
+    const float ratio = maxD[i] / dist;                          // MapPoint.cc:578
+    int nScale = (int)std::ceil(std::log(ratio) / c.log_scale_factor);   // logf, float division (:581)
+    if (nScale < 0) nScale = 0;
+    else if (nScale >= c.n_levels) nScale = c.n_levels - 1;
+    in_view[i] = 1; count++;
+    projXR[i] = u - c.mbf * invz;                                // :701
+    depth[i] = Pc_dist; level[i] = nScale; viewCosOut[i] = viewCos;
+  }
+  return count;
+}
+
 }  // namespace orb_oracle
 
 using namespace orb_oracle;
@@ -71,5 +115,10 @@ void oo_undistort_keypoints(const KeyPoint* in, KeyPoint* out, int n, const floa
 void oo_stereo_from_rgbd(const KeyPoint* kps, const KeyPoint* kps_un, int n, const float* depth, size_t stride_floats,
                          float mbf, float* u_right, float* depth_out) {
   stereo_from_rgbd(kps, kps_un, n, depth, stride_floats, mbf, u_right, depth_out);
+}
+int oo_is_in_frustum(const cuorb_frustum_camera* cam, int n, const float* P, const float* N, const float* minD,
+                     const float* maxD, float limit, uint8_t* in_view, float* px, float* py, float* pxr, int32_t* level,
+                     float* view_cos, float* depth) {
+  return is_in_frustum(*cam, n, P, N, minD, maxD, limit, in_view, px, py, pxr, level, view_cos, depth);
 }
 }

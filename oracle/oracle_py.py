@@ -34,6 +34,49 @@ class FrameViewC(C.Structure):
     ]
 
 
+class FrustumCamera(C.Structure):
+    """cuorb_frustum_camera (include/cuorb.h)."""
+
+    _fields_ = [("rcw", C.c_float * 9), ("tcw", C.c_float * 3), ("ow", C.c_float * 3),
+                ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("mbf", C.c_float),
+                ("min_x", C.c_float), ("max_x", C.c_float), ("min_y", C.c_float), ("max_y", C.c_float),
+                ("log_scale_factor", C.c_float), ("n_levels", C.c_int32)]
+
+
+def make_frustum_camera(Rcw, tcw, K4, mbf, w, h, scale_factor=1.2, n_levels=8):
+    """Frame members isInFrustum reads, from a world->camera pose: mOw = -Rcw^T tcw in float32 (row dot products
+    associated x0 + (x1 + x2), as everywhere in this statement of the path)."""
+    R = np.asarray(Rcw, np.float32).reshape(3, 3); t = np.asarray(tcw, np.float32).reshape(3)
+    Rt = R.T
+    ow = -np.array([np.float32(Rt[r, 0] * t[0]) + np.float32(np.float32(Rt[r, 1] * t[1]) + np.float32(Rt[r, 2] * t[2]))
+                    for r in range(3)], np.float32)
+    c = FrustumCamera()
+    c.rcw[:] = [float(x) for x in R.ravel()]; c.tcw[:] = [float(x) for x in t]; c.ow[:] = [float(x) for x in ow]
+    c.fx, c.fy, c.cx, c.cy = [float(np.float32(x)) for x in K4]
+    c.mbf = float(np.float32(mbf))
+    c.min_x, c.max_x, c.min_y, c.max_y = 0.0, float(w), 0.0, float(h)
+    c.log_scale_factor = float(np.float32(np.log(np.float64(np.float32(scale_factor)))))   # mfLogScaleFactor = log(mfScaleFactor)
+    c.n_levels = n_levels
+    return c
+
+
+def _frustum_call(fn, cam, P, N, min_d, max_d, limit):
+    P = np.ascontiguousarray(P, np.float32); N = np.ascontiguousarray(N, np.float32)
+    min_d = np.ascontiguousarray(min_d, np.float32); max_d = np.ascontiguousarray(max_d, np.float32)
+    n = len(min_d)
+    out = dict(in_view=np.zeros(n, np.uint8), proj_x=np.zeros(n, np.float32), proj_y=np.zeros(n, np.float32),
+               proj_xr=np.zeros(n, np.float32), level=np.zeros(n, np.int32), view_cos=np.zeros(n, np.float32),
+               depth=np.zeros(n, np.float32))
+    cnt = fn(C.byref(cam), n, _p(P), _p(N), _p(min_d), _p(max_d), C.c_float(limit), *[_p(out[k]) for k in
+             ("in_view", "proj_x", "proj_y", "proj_xr", "level", "view_cos", "depth")])
+    out["count"] = cnt
+    return out
+
+
+def is_in_frustum(cam, P, N, min_d, max_d, limit):
+    return _frustum_call(lib().oo_is_in_frustum, cam, P, N, min_d, max_d, limit)
+
+
 def build(force: bool = False) -> str:
     srcs = [os.path.join(_HERE, f) for f in
             ("orb_oracle.cpp", "orb_oracle_match.cpp", "orb_oracle_capi.cpp", "preproc_oracle.cpp", "frameglue_oracle.cpp", "bfmatch_oracle.cpp", "bow_oracle.cpp", "search_oracle.cpp", "orb_oracle.hpp")]
@@ -96,6 +139,7 @@ def lib() -> C.CDLL:
         L.oo_undistort_keypoints.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.oo_stereo_from_rgbd.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_float,
                                           C.c_void_p, C.c_void_p]
+        L.oo_is_in_frustum.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [C.c_float] + [C.c_void_p] * 7
         L.oo_knn_match2.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.oo_fisheye_ratio_test.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.oo_distinctive_descriptors.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]

@@ -215,6 +215,40 @@ int ref_search_by_projection_frame(const cuorb_frame_view* cur, int n_last, cons
   return n;
 }
 
+// ---- bool Frame::isInFrustum(MapPoint*, float) — the reference's own body (src/Frame.cc:644-721), with
+// MapPoint::PredictScale (src/MapPoint.cc:574-589) and Pinhole::project (Pinhole.cpp:70-76) lifted verbatim;
+// the Eigen expressions inside run on the oracle/ref_compat/Eigen stand-in. ----
+int ref_is_in_frustum(const cuorb_frustum_camera* c, int n, const float* P, const float* N, const float* minD,
+                      const float* maxD, float limit, uint8_t* in_view, float* px, float* py, float* pxr,
+                      int32_t* level, float* view_cos, float* depth) {
+  Frame F;
+  Pinhole cam(std::vector<float>{c->fx, c->fy, c->cx, c->cy});
+  F.mpCamera = &cam;
+  F.Nleft = -1;
+  for (int r = 0; r < 3; r++) {
+    for (int k = 0; k < 3; k++) F.mRcw(r, k) = c->rcw[3 * r + k];
+    F.mtcw(r) = c->tcw[r];
+    F.mOw(r) = c->ow[r];
+  }
+  F.mbf = c->mbf;
+  Frame::mnMinX = c->min_x; Frame::mnMaxX = c->max_x; Frame::mnMinY = c->min_y; Frame::mnMaxY = c->max_y;
+  F.mfLogScaleFactor = c->log_scale_factor;
+  F.mnScaleLevels = c->n_levels;
+  int count = 0;
+  for (int i = 0; i < n; i++) {
+    MapPoint mp;
+    mp.mWorldPos = Eigen::Vector3f(P[3 * i], P[3 * i + 1], P[3 * i + 2]);
+    mp.mNormalVector = Eigen::Vector3f(N[3 * i], N[3 * i + 1], N[3 * i + 2]);
+    mp.mfMinDistance = minD[i]; mp.mfMaxDistance = maxD[i];
+    mp.mTrackProjXR = -1; mp.mnTrackScaleLevel = -1; mp.mTrackViewCos = 0; mp.mTrackDepth = 0;
+    const bool ok = F.isInFrustum(&mp, limit);
+    in_view[i] = ok ? 1 : 0; count += ok;
+    px[i] = mp.mTrackProjX; py[i] = mp.mTrackProjY; pxr[i] = mp.mTrackProjXR;
+    level[i] = mp.mnTrackScaleLevel; view_cos[i] = mp.mTrackViewCos; depth[i] = mp.mTrackDepth;
+  }
+  return count;
+}
+
 // ---- CPU timing loop over the reference's own per-frame stereo path (two operator() calls and
 // ComputeStereoMatches, src/Frame.cc:202-205, 231), one std::thread per in-flight frame. ----
 double ref_bench_stereo(int nfeatures, float scale, int nlevels, int ini, int min,

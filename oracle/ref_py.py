@@ -77,6 +77,7 @@ def lib() -> C.CDLL:
                                                [C.c_float, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p])
         L.ref_search_by_projection_frame.argtypes = ([FV, C.c_int] + [C.c_void_p] * 7 +
                                                      [C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p])
+        L.ref_is_in_frustum.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [C.c_float] + [C.c_void_p] * 7
         L.ref_bench_stereo.restype = C.c_double
         L.ref_bench_stereo.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                        C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int,
@@ -222,3 +223,9 @@ def bench_stereo(left, right, mb, mbf, n_threads, nfeatures=1000, scale=1.2, nle
     sec = lib().ref_bench_stereo(nfeatures, scale, nlevels, ini, mn, _p(left), _p(right), n, w, h, mb, mbf,
                                  n_threads, C.byref(k), C.byref(m))
     return sec, k.value, m.value
+
+
+def is_in_frustum(cam, P, N, min_d, max_d, limit):
+    """Frame::isInFrustum for n MapPoints; cam: a ctypes cuorb_frustum_camera (oracle_py.FrustumCamera)."""
+    from .oracle_py import _frustum_call
+    return _frustum_call(lib().ref_is_in_frustum, cam, P, N, min_d, max_d, limit)

@@ -7,5 +7,5 @@ from ._lib import KP_DTYPE, CuorbError, load  # noqa: F401
 from .extractor import ORBextractor  # noqa: F401
 from .matcher import Frame, MapPointSoA, ORBmatcher  # noqa: F401
 from .preproc import FramePreprocessor  # noqa: F401
-from .frame_ops import ComputeStereoFromRGBD, UndistortKeyPoints  # noqa: F401
+from .frame_ops import ComputeStereoFromRGBD, UndistortKeyPoints, isInFrustum  # noqa: F401
 from .bfmatch import ComputeDistinctiveDescriptors, knnMatch2  # noqa: F401

@@ -37,6 +37,15 @@ class Config(C.Structure):
                 ("max_height", C.c_int32), ("max_batch", C.c_int32), ("device", C.c_int32)]
 
 
+class FrustumCamera(C.Structure):
+    """cuorb_frustum_camera: the Frame members Frame::isInFrustum reads."""
+
+    _fields_ = [("rcw", C.c_float * 9), ("tcw", C.c_float * 3), ("ow", C.c_float * 3),
+                ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("mbf", C.c_float),
+                ("min_x", C.c_float), ("max_x", C.c_float), ("min_y", C.c_float), ("max_y", C.c_float),
+                ("log_scale_factor", C.c_float), ("n_levels", C.c_int32)]
+
+
 class FrameView(C.Structure):
     _fields_ = [
         ("n", C.c_int32), ("keys_un", C.c_void_p), ("descriptors", C.c_void_p),
@@ -95,6 +104,7 @@ SIGNATURES = {
     "cuorb_undistort_keypoints": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "cuorb_stereo_from_rgbd": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                          C.c_size_t, C.c_int, C.c_float, C.c_void_p, C.c_void_p]),
+    "cuorb_is_in_frustum": (C.c_int, [C.c_int, C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [C.c_float] + [C.c_void_p] * 7),
     "cuorb_knn_match2": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                    C.c_void_p, C.c_void_p]),
     "cuorb_distinctive_descriptors": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
@@ -113,6 +123,8 @@ SIGNATURES = {
                                                   C.c_int, C.c_float, C.c_int, C.c_void_p]),
     "cuorb_search_for_triangulation": (C.c_int, [C.c_int, C.POINTER(FrameView), C.POINTER(FrameView), C.c_int] +
                                        [C.c_void_p] * 7 + [C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "cuorb_synth_stereo": (C.c_int, [C.c_int, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                    C.c_void_p]),
     "cuorb_kernel_launch_count": (C.c_uint64, []),
     "cuorb_set_profiling": (C.c_int, [C.c_void_p, C.c_int]),
     "cuorb_stage_ms": (C.c_int, [C.c_void_p, C.c_void_p]),

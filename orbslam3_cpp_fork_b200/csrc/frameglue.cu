@@ -67,6 +67,60 @@ __global__ void k_stereo_from_rgbd(const cuorb_keypoint* __restrict__ kps, const
   u_right[i] = ur; depth_out[i] = dz;
 }
 
+// Frame::isInFrustum (src/Frame.cc:644-707, Nleft == -1) + MapPoint::PredictScale (src/MapPoint.cc:574-589) +
+// Pinhole::project (Pinhole.cpp:70-76): one thread per MapPoint, SoA in / SoA out.  Every float operation is an
+// explicit round-to-nearest intrinsic in the reference's expression order (size-3 sums associate as Eigen's
+// unrolled reduction does: x0 + (x1 + x2)), so nvcc cannot contract anything into an FMA.
+__device__ __forceinline__ float dot3(float a0, float a1, float a2, float b0, float b1, float b2) {
+  return __fadd_rn(__fmul_rn(a0, b0), __fadd_rn(__fmul_rn(a1, b1), __fmul_rn(a2, b2)));
+}
+
+__global__ void k_is_in_frustum(const cuorb_frustum_camera c, int n, const float* __restrict__ P3, const float* __restrict__ N3,
+                                const float* __restrict__ minD, const float* __restrict__ maxD, float limit,
+                                uint8_t* __restrict__ in_view, float* __restrict__ projX, float* __restrict__ projY,
+                                float* __restrict__ projXR, int* __restrict__ level, float* __restrict__ viewCosOut,
+                                float* __restrict__ depth, int* __restrict__ count) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  bool ok = false;
+  if (i < n) {
+    float px = -1.f, py = -1.f, pxr = -1.f, vc = 0.f, dz = 0.f;
+    int lv = -1;
+    const float P0 = P3[3 * i], P1 = P3[3 * i + 1], P2 = P3[3 * i + 2];
+    const float Pc0 = __fadd_rn(dot3(c.rcw[0], c.rcw[1], c.rcw[2], P0, P1, P2), c.tcw[0]);
+    const float Pc1 = __fadd_rn(dot3(c.rcw[3], c.rcw[4], c.rcw[5], P0, P1, P2), c.tcw[1]);
+    const float Pc2 = __fadd_rn(dot3(c.rcw[6], c.rcw[7], c.rcw[8], P0, P1, P2), c.tcw[2]);
+    const float Pc_dist = __fsqrt_rn(dot3(Pc0, Pc1, Pc2, Pc0, Pc1, Pc2));
+    const float invz = __fdiv_rn(1.0f, Pc2);
+    if (!(Pc2 < 0.0f)) {
+      const float u = __fadd_rn(__fdiv_rn(__fmul_rn(c.fx, Pc0), Pc2), c.cx);
+      const float v = __fadd_rn(__fdiv_rn(__fmul_rn(c.fy, Pc1), Pc2), c.cy);
+      if (!(u < c.min_x || u > c.max_x) && !(v < c.min_y || v > c.max_y)) {
+        px = u; py = v;
+        const float mx = maxD[i];
+        const float maxDistance = __fmul_rn(1.2f, mx), minDistance = __fmul_rn(0.8f, minD[i]);
+        const float O0 = __fsub_rn(P0, c.ow[0]), O1 = __fsub_rn(P1, c.ow[1]), O2 = __fsub_rn(P2, c.ow[2]);
+        const float dist = __fsqrt_rn(dot3(O0, O1, O2, O0, O1, O2));
+        if (!(dist < minDistance || dist > maxDistance)) {
+          const float viewCos = __fdiv_rn(dot3(O0, O1, O2, N3[3 * i], N3[3 * i + 1], N3[3 * i + 2]), dist);
+          if (!(viewCos < limit)) {
+            const float ratio = __fdiv_rn(mx, dist);
+            // std::log(float) = glibc logf (correctly rounded in practice): double log, rounded once
+            const float lg = (float)log((double)ratio);
+            int nScale = (int)ceilf(__fdiv_rn(lg, c.log_scale_factor));
+            nScale = nScale < 0 ? 0 : (nScale >= c.n_levels ? c.n_levels - 1 : nScale);
+            ok = true;
+            pxr = __fsub_rn(u, __fmul_rn(c.mbf, invz));
+            dz = Pc_dist; lv = nScale; vc = viewCos;
+          }
+        }
+      }
+    }
+    in_view[i] = ok ? 1 : 0; projX[i] = px; projY[i] = py; projXR[i] = pxr; level[i] = lv; viewCosOut[i] = vc; depth[i] = dz;
+  }
+  const unsigned b = __ballot_sync(0xffffffffu, ok);
+  if ((threadIdx.x & 31) == 0 && b) atomicAdd(count, __popc(b));
+}
+
 struct Scratch {  // grow-only device scratch per host thread
   void* p = nullptr; size_t cap = 0; int device = -1;
   void* get(int dev, size_t bytes) {
@@ -153,6 +207,49 @@ int cuorb_stereo_from_rgbd(int device, int n, const cuorb_keypoint* kps, const c
   GLUE_TRY(cudaMemcpyAsync(depth_out, dz, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
   GLUE_TRY(cudaStreamSynchronize(st));
   return n;
+}
+
+int cuorb_is_in_frustum(int device, const cuorb_frustum_camera* cam, int n, const float* world_pos, const float* normal,
+                        const float* min_distance, const float* max_distance, float viewing_cos_limit, uint8_t* in_view,
+                        float* proj_x, float* proj_y, float* proj_xr, int32_t* scale_level, float* view_cos, float* depth) {
+  if (!cam || n < 0 || (n > 0 && (!world_pos || !normal || !min_distance || !max_distance || !in_view || !proj_x || !proj_y ||
+                                  !proj_xr || !scale_level || !view_cos || !depth))) {
+    set_error("cuorb_is_in_frustum: bad argument"); return CUORB_E_BADARG;
+  }
+  if (n == 0) return 0;
+  GLUE_TRY(cudaSetDevice(device));
+  const size_t a4 = (4 * (size_t)n + 255) & ~(size_t)255, a12 = (12 * (size_t)n + 255) & ~(size_t)255;
+  const size_t a1 = ((size_t)n + 255) & ~(size_t)255;
+  char* d = (char*)t_scratch.get(device, 2 * a12 + 2 * a4 + a1 + 6 * a4 + 512);
+  if (!d) { set_error("cudaMalloc failed (frustum workspace)"); return CUORB_E_CUDA; }
+  float* dP = (float*)d; float* dN = (float*)(d + a12);
+  float* dmin = (float*)(d + 2 * a12); float* dmax = (float*)(d + 2 * a12 + a4);
+  char* o = d + 2 * a12 + 2 * a4;
+  uint8_t* dview = (uint8_t*)o; o += a1;
+  float* dpx = (float*)o; o += a4; float* dpy = (float*)o; o += a4; float* dpxr = (float*)o; o += a4;
+  int* dlv = (int*)o; o += a4; float* dvc = (float*)o; o += a4; float* ddz = (float*)o; o += a4;
+  int* dcount = (int*)o;
+  cudaStream_t st = cudaStreamPerThread;
+  GLUE_TRY(cudaMemcpyAsync(dP, world_pos, 12 * (size_t)n, cudaMemcpyHostToDevice, st));
+  GLUE_TRY(cudaMemcpyAsync(dN, normal, 12 * (size_t)n, cudaMemcpyHostToDevice, st));
+  GLUE_TRY(cudaMemcpyAsync(dmin, min_distance, 4 * (size_t)n, cudaMemcpyHostToDevice, st));
+  GLUE_TRY(cudaMemcpyAsync(dmax, max_distance, 4 * (size_t)n, cudaMemcpyHostToDevice, st));
+  GLUE_TRY(cudaMemsetAsync(dcount, 0, sizeof(int), st));
+  k_is_in_frustum<<<(n + 127) / 128, 128, 0, st>>>(*cam, n, dP, dN, dmin, dmax, viewing_cos_limit, dview, dpx, dpy, dpxr, dlv,
+                                                    dvc, ddz, dcount);
+  count_launch();
+  GLUE_TRY(cudaGetLastError());
+  int count = 0;
+  GLUE_TRY(cudaMemcpyAsync(in_view, dview, (size_t)n, cudaMemcpyDeviceToHost, st));
+  GLUE_TRY(cudaMemcpyAsync(proj_x, dpx, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+  GLUE_TRY(cudaMemcpyAsync(proj_y, dpy, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+  GLUE_TRY(cudaMemcpyAsync(proj_xr, dpxr, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+  GLUE_TRY(cudaMemcpyAsync(scale_level, dlv, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+  GLUE_TRY(cudaMemcpyAsync(view_cos, dvc, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+  GLUE_TRY(cudaMemcpyAsync(depth, ddz, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+  GLUE_TRY(cudaMemcpyAsync(&count, dcount, sizeof(int), cudaMemcpyDeviceToHost, st));
+  GLUE_TRY(cudaStreamSynchronize(st));
+  return count;
 }
 
 }  // extern "C"

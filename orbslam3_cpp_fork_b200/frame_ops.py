@@ -47,3 +47,24 @@ def ComputeStereoFromRGBD(mvKeys, mvKeysUn, imDepth, mbf, device=0):
     check(L.cuorb_stereo_from_rgbd(int(device), len(kps), ptr(kps), ptr(kun), ptr(p), shape[1], shape[0], strides[0],
                                    where, float(mbf), ptr(u), ptr(z)))
     return u, z
+
+
+def isInFrustum(camera, world_pos, normal, mfMinDistance, mfMaxDistance, viewingCosLimit, device=0):
+    """Frame::isInFrustum (src/Frame.cc:644-707) for n MapPoints at once.  camera: _lib.FrustumCamera (mRcw, mtcw,
+    mOw, fx, fy, cx, cy, mbf, image bounds, mfLogScaleFactor, mnScaleLevels).  Returns a dict with mbTrackInView,
+    mTrackProjX, mTrackProjY, mTrackProjXR, mnTrackScaleLevel, mTrackViewCos, mTrackDepth (numpy arrays) and
+    the number of points in view — exactly the fields ORBmatcher::SearchByProjection(F, vpMapPoints) reads."""
+    import ctypes as C
+    L = _lib.load()
+    P = np.ascontiguousarray(world_pos, np.float32).reshape(-1, 3)
+    N = np.ascontiguousarray(normal, np.float32).reshape(-1, 3)
+    mn = np.ascontiguousarray(mfMinDistance, np.float32); mx = np.ascontiguousarray(mfMaxDistance, np.float32)
+    n = len(P)
+    out = dict(mbTrackInView=np.zeros(n, np.uint8), mTrackProjX=np.zeros(n, np.float32), mTrackProjY=np.zeros(n, np.float32),
+               mTrackProjXR=np.zeros(n, np.float32), mnTrackScaleLevel=np.zeros(n, np.int32),
+               mTrackViewCos=np.zeros(n, np.float32), mTrackDepth=np.zeros(n, np.float32))
+    out["count"] = check(L.cuorb_is_in_frustum(int(device), C.byref(camera), n, ptr(P), ptr(N), ptr(mn), ptr(mx),
+                                               float(viewingCosLimit), *[ptr(out[k]) for k in
+                                               ("mbTrackInView", "mTrackProjX", "mTrackProjY", "mTrackProjXR",
+                                                "mnTrackScaleLevel", "mTrackViewCos", "mTrackDepth")]))
+    return out

@@ -78,3 +78,34 @@ def lastframe_case(k, d, seed, w=752, h=480):
     flags = (valid * 1 + has_obs * 4).astype(np.uint8)
     u_right = np.where(rng.random(N) < 0.5, k["x"] - rng.uniform(1, 60, N), -1).astype(np.float32)
     return dict(desc=desc, u=u, v=v, inv_z=inv_z, octave=octave, angle=angle, flags=flags, u_right=u_right)
+
+
+def frustum_case(n, seed, w=752, h=480):
+    """Frame::isInFrustum inputs: a camera pose, n world points scattered in and around the frustum (behind the
+    camera, outside the image, too near / too far, grazing normals included), with the Frame members it reads."""
+    rng = np.random.default_rng(seed)
+    ang = rng.uniform(-0.4, 0.4, 3)
+    cx_, sx_ = np.cos(ang[0]), np.sin(ang[0]); cy_, sy_ = np.cos(ang[1]), np.sin(ang[1]); cz_, sz_ = np.cos(ang[2]), np.sin(ang[2])
+    Rx = np.array([[1, 0, 0], [0, cx_, -sx_], [0, sx_, cx_]]); Ry = np.array([[cy_, 0, sy_], [0, 1, 0], [-sy_, 0, cy_]])
+    Rz = np.array([[cz_, -sz_, 0], [sz_, cz_, 0], [0, 0, 1]])
+    R = (Rz @ Ry @ Rx).astype(np.float32)
+    t = rng.uniform(-2, 2, 3).astype(np.float32)
+    K4 = (458.654, 457.296, 367.215, 248.375)
+    cam = op.make_frustum_camera(R, t, K4, 47.906, w, h)
+    # points: camera-frame samples pushed back to the world (float64 here: they are just inputs)
+    z = rng.uniform(-2, 40, n); z[rng.random(n) < 0.05] = rng.uniform(0.0, 0.05, int((rng.random(n) < 0.05).sum()) or 1)[0]
+    u = rng.uniform(-120, w + 120, n); v = rng.uniform(-120, h + 120, n)
+    pc = np.stack([(u - K4[2]) / K4[0] * z, (v - K4[3]) / K4[1] * z, z], 1)
+    P = ((pc - t.astype(np.float64)) @ R.astype(np.float64)).astype(np.float32)          # R^T (pc - t)
+    ow = np.array(cam.ow[:], np.float64)
+    po = P.astype(np.float64) - ow
+    dist = np.linalg.norm(po, axis=1) + 1e-9
+    nrm = po / dist[:, None] + rng.normal(0, 0.6, (n, 3))
+    nrm /= np.linalg.norm(nrm, axis=1)[:, None] + 1e-12
+    max_d = (dist * rng.uniform(0.6, 3.0, n)).astype(np.float32)
+    min_d = (max_d / np.float32(1.2 ** 7) * rng.uniform(0.5, 1.5, n)).astype(np.float32)
+    # exact bin edges of PredictScale: ratio = 1.2^k
+    k = rng.integers(0, 8, n)
+    edge = rng.random(n) < 0.1
+    max_d[edge] = (dist[edge] * 1.2 ** k[edge]).astype(np.float32)
+    return cam, P, nrm.astype(np.float32), min_d, max_d

@@ -48,3 +48,27 @@ def test_rgbd_stereo_host_and_device_depth():
     padded = np.zeros((h, w + 8), np.float32); padded[:, :w] = depth
     up, zp = ComputeStereoFromRGBD(k, ku, padded[:, :w], 40.0)
     assert (up == ru).all() and (zp == rz).all()
+
+
+@pytest.mark.parametrize("seed,limit", [(1, 0.5), (2, 0.5), (3, 0.8)])
+def test_is_in_frustum_matches_oracle_and_reference(seed, limit):
+    """Frame::isInFrustum for 20k MapPoints: every output equal to the oracle and to the reference's own lifted
+    body (oracle/_ref) bit for bit; differences, if any ever appear, can only sit at an FMA / logf bin edge and are
+    counted separately here (tolerance of north_star: 1e-4 relative on floats, +-1 level at a PredictScale edge)."""
+    from oracle import oracle_py as op
+    from oracle import ref_py as rp
+    from orbslam3_cpp_fork_b200 import _lib, isInFrustum
+    from tests.matching_cases import frustum_case
+    cam, P, N, min_d, max_d = frustum_case(20000, seed)
+    ccam = _lib.FrustumCamera.from_buffer_copy(bytes(cam))
+    g = isInFrustum(ccam, P, N, min_d, max_d, limit)
+    names = dict(mbTrackInView="in_view", mTrackProjX="proj_x", mTrackProjY="proj_y", mTrackProjXR="proj_xr",
+                 mnTrackScaleLevel="level", mTrackViewCos="view_cos", mTrackDepth="depth")
+    checkers = [op.is_in_frustum(cam, P, N, min_d, max_d, limit)]
+    if rp.available():
+        checkers.append(rp.is_in_frustum(cam, P, N, min_d, max_d, limit))
+    for o in checkers:
+        edge = {k: int((g[k] != o[v]).sum()) for k, v in names.items()}
+        assert g["count"] == o["count"], edge
+        assert not any(edge.values()), f"bin-edge bucket (entries differing from the checker): {edge}"
+    assert 2000 < g["count"] < 18000

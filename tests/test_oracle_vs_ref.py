@@ -12,7 +12,7 @@ import pytest
 from oracle import oracle_py as op
 from oracle import ref_py as rp
 from orbslam3_cpp_fork_b200 import synth
-from tests.matching_cases import extracted_frame, lastframe_case, mappoint_case
+from tests.matching_cases import extracted_frame, frustum_case, lastframe_case, mappoint_case
 from tests.test_oracle_golden import GOLDEN, golden_image
 
 pytestmark = pytest.mark.skipif(not rp.available(), reason="oracle/_ref not built and no reference checkout")
@@ -196,3 +196,17 @@ def test_search_by_projection_lastframe_equals_reference(fwd, bwd, th):
     assert n_r > 50
     assert n_o == n_r
     assert (final == final_r).all()
+
+
+@pytest.mark.parametrize("seed,limit", [(1, 0.5), (2, 0.5), (3, 0.8)])
+def test_is_in_frustum_equals_reference(seed, limit):
+    """Frame::isInFrustum (src/Frame.cc:644-707) + MapPoint::PredictScale + Pinhole::project: the restatement
+    against the reference's own lifted bodies, every output bit for bit."""
+    cam, P, N, min_d, max_d = frustum_case(20000, seed)
+    a = op.is_in_frustum(cam, P, N, min_d, max_d, limit)
+    b = rp.is_in_frustum(cam, P, N, min_d, max_d, limit)
+    assert 2000 < a["count"] < 18000
+    assert a["count"] == b["count"]
+    for k in ("in_view", "proj_x", "proj_y", "proj_xr", "level", "view_cos", "depth"):
+        assert a[k].tobytes() == b[k].tobytes(), k
+    assert len(np.unique(a["level"][a["in_view"] > 0])) == 8          # every scale level is predicted somewhere
