@@ -308,6 +308,22 @@ int cuorb_is_in_frustum(int device, const cuorb_frustum_camera* camera, int n, c
                         float viewing_cos_limit, uint8_t* in_view, float* proj_x, float* proj_y,
                         float* proj_xr, int32_t* scale_level, float* view_cos, float* depth);
 
+/* Allocation-free variant of cuorb_is_in_frustum.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid allocation).  Same arguments, same kernel, same results, but the device
+ * staging area is a file-scope `static __device__` array instead of a cudaMalloc'ed workspace:
+ *   - at most CUORB_FRUSTUM_NOALLOC_MAX MapPoints per call; a larger n returns CUORB_E_CAPACITY with an error text;
+ *   - every GPU that loads libcuorb holds the array (about 3.6 MiB) until the process exits;
+ *   - the call performs no cudaMalloc / cudaFree and calls no allocating library routine;
+ *   - all calls on one device share the array, which keeps the last call's contents (the call clears the one word
+ *     that must start at zero): calls that overlap on the same GPU - other host threads, other streams - RACE on it
+ *     and must be serialised by the caller.  The call itself is synchronous (returns after its stream drained). */
+#define CUORB_FRUSTUM_NOALLOC_MAX 65536
+int cuorb_is_in_frustum_noalloc(int device, const cuorb_frustum_camera* camera, int n, const float* world_pos,
+                                const float* normal, const float* min_distance, const float* max_distance,
+                                float viewing_cos_limit, uint8_t* in_view, float* proj_x, float* proj_y,
+                                float* proj_xr, int32_t* scale_level, float* view_cos, float* depth);
+
 /* void Frame::ComputeStereoFromRGBD(const cv::Mat& imDepth) (src/Frame.cc:1115-1133): depth = CV_32F
  * image (row pitch stride_bytes) in host or device memory; d = imDepth(v, u) at the truncated
  * keypoint position; if d > 0: depth_out = d, u_right = kps_un.x - mbf / d, else both -1. */

@@ -105,6 +105,8 @@ SIGNATURES = {
     "cuorb_stereo_from_rgbd": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                          C.c_size_t, C.c_int, C.c_float, C.c_void_p, C.c_void_p]),
     "cuorb_is_in_frustum": (C.c_int, [C.c_int, C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [C.c_float] + [C.c_void_p] * 7),
+    "cuorb_is_in_frustum_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [C.c_float] +
+                                    [C.c_void_p] * 7),
     "cuorb_knn_match2": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                    C.c_void_p, C.c_void_p]),
     "cuorb_distinctive_descriptors": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),

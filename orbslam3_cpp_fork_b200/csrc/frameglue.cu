@@ -6,6 +6,9 @@
 // double intrinsics in the reference's operation order, so no FMA contraction can change a bit.
 // One thread per keypoint; these are tiny kernels (a frame has ~1000 keypoints) whose point is to
 // keep the Frame's arrays on the device between extraction and the matchers.
+#include <mutex>
+#include <string>
+
 #include "common.cuh"
 
 namespace cuorb {
@@ -235,6 +238,101 @@ int cuorb_is_in_frustum(int device, const cuorb_frustum_camera* cam, int n, cons
   GLUE_TRY(cudaMemcpyAsync(dmin, min_distance, 4 * (size_t)n, cudaMemcpyHostToDevice, st));
   GLUE_TRY(cudaMemcpyAsync(dmax, max_distance, 4 * (size_t)n, cudaMemcpyHostToDevice, st));
   GLUE_TRY(cudaMemsetAsync(dcount, 0, sizeof(int), st));
+  k_is_in_frustum<<<(n + 127) / 128, 128, 0, st>>>(*cam, n, dP, dN, dmin, dmax, viewing_cos_limit, dview, dpx, dpy, dpxr, dlv,
+                                                    dvc, ddz, dcount);
+  count_launch();
+  GLUE_TRY(cudaGetLastError());
+  int count = 0;
+  GLUE_TRY(cudaMemcpyAsync(in_view, dview, (size_t)n, cudaMemcpyDeviceToHost, st));
+  GLUE_TRY(cudaMemcpyAsync(proj_x, dpx, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+  GLUE_TRY(cudaMemcpyAsync(proj_y, dpy, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+  GLUE_TRY(cudaMemcpyAsync(proj_xr, dpxr, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+  GLUE_TRY(cudaMemcpyAsync(scale_level, dlv, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+  GLUE_TRY(cudaMemcpyAsync(view_cos, dvc, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+  GLUE_TRY(cudaMemcpyAsync(depth, ddz, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+  GLUE_TRY(cudaMemcpyAsync(&count, dcount, sizeof(int), cudaMemcpyDeviceToHost, st));
+  GLUE_TRY(cudaStreamSynchronize(st));
+  return count;
+}
+
+// ---- allocation-free variant (no counterpart in the reference) ----
+// cuorb_is_in_frustum above stages its SoA in a grow-only cudaMalloc'ed workspace.  Callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it) use this entry point instead: the
+// same kernel, the same results, with the staging area in a file-scope device array of fixed size.
+//   * limit: CUORB_FRUSTUM_NOALLOC_MAX MapPoints per call (larger n is rejected with CUORB_E_CAPACITY);
+//   * cost: every GPU that loads libcuorb holds the array (about 3.6 MiB) until the process exits;
+//   * the array is shared by ALL calls on a device and keeps the previous call's contents: the one word that has
+//     to start at zero (the in-view counter) is cleared by every call, everything else is overwritten before it is
+//     read; two calls that overlap on the same GPU (two host threads, two streams) race on it - serialise them.
+// No cudaMalloc / cudaFree / cudaMallocAsync and no allocating library routine is called here.
+}  // extern "C"
+
+namespace {
+constexpr size_t FRUSTUM_NA_A4  = ((size_t)4 * CUORB_FRUSTUM_NOALLOC_MAX + 255) & ~(size_t)255;
+constexpr size_t FRUSTUM_NA_A12 = ((size_t)12 * CUORB_FRUSTUM_NOALLOC_MAX + 255) & ~(size_t)255;
+constexpr size_t FRUSTUM_NA_A1  = ((size_t)CUORB_FRUSTUM_NOALLOC_MAX + 255) & ~(size_t)255;
+constexpr size_t FRUSTUM_NA_BYTES = 2 * FRUSTUM_NA_A12 + 2 * FRUSTUM_NA_A4 + FRUSTUM_NA_A1 + 6 * FRUSTUM_NA_A4 + 256;
+}  // namespace
+// In HOST code this name is only a stand-in for the symbol, not a device address: the address a kernel may be
+// given comes from cudaGetSymbolAddress (frustum_scratch_ptr below), once per device with that device current.
+static __device__ __align__(256) unsigned char g_frustum_scratch[FRUSTUM_NA_BYTES];
+
+namespace {
+// device address of g_frustum_scratch on `device` (which must be the current device); nullptr + error text on failure
+unsigned char* frustum_scratch_ptr(int device) {
+  static std::mutex mu;
+  static unsigned char* ptrs[64];
+  if (device < 0 || device >= 64) { set_error("cuorb_is_in_frustum_noalloc: device ordinal beyond 63"); return nullptr; }
+  std::lock_guard<std::mutex> lk(mu);
+  if (!ptrs[device]) {
+    void* p = nullptr;
+    const cudaError_t err = cudaGetSymbolAddress(&p, g_frustum_scratch);
+    if (err != cudaSuccess || !p) {
+      set_error(std::string("cudaGetSymbolAddress(g_frustum_scratch): ") + cudaGetErrorString(err));
+      return nullptr;
+    }
+    ptrs[device] = (unsigned char*)p;
+  }
+  return ptrs[device];
+}
+}  // namespace
+
+extern "C" {
+
+int cuorb_is_in_frustum_noalloc(int device, const cuorb_frustum_camera* cam, int n, const float* world_pos,
+                                const float* normal, const float* min_distance, const float* max_distance,
+                                float viewing_cos_limit, uint8_t* in_view, float* proj_x, float* proj_y, float* proj_xr,
+                                int32_t* scale_level, float* view_cos, float* depth) {
+  if (!cam || n < 0 || (n > 0 && (!world_pos || !normal || !min_distance || !max_distance || !in_view || !proj_x || !proj_y ||
+                                  !proj_xr || !scale_level || !view_cos || !depth))) {
+    set_error("cuorb_is_in_frustum_noalloc: bad argument"); return CUORB_E_BADARG;
+  }
+  if (n > CUORB_FRUSTUM_NOALLOC_MAX) {
+    set_error("cuorb_is_in_frustum_noalloc: n = " + std::to_string(n) + " MapPoints exceeds the fixed scratch array (" +
+              "CUORB_FRUSTUM_NOALLOC_MAX = " + std::to_string(CUORB_FRUSTUM_NOALLOC_MAX) +
+              "); split the call or use cuorb_is_in_frustum");
+    return CUORB_E_CAPACITY;
+  }
+  if (n == 0) return 0;
+  GLUE_TRY(cudaSetDevice(device));
+  unsigned char* d = frustum_scratch_ptr(device);
+  if (!d) return CUORB_E_CUDA;
+  // same layout as cuorb_is_in_frustum's workspace, sized for this n
+  const size_t a4 = (4 * (size_t)n + 255) & ~(size_t)255, a12 = (12 * (size_t)n + 255) & ~(size_t)255;
+  const size_t a1 = ((size_t)n + 255) & ~(size_t)255;
+  float* dP = (float*)d; float* dN = (float*)(d + a12);
+  float* dmin = (float*)(d + 2 * a12); float* dmax = (float*)(d + 2 * a12 + a4);
+  unsigned char* o = d + 2 * a12 + 2 * a4;
+  uint8_t* dview = (uint8_t*)o; o += a1;
+  float* dpx = (float*)o; o += a4; float* dpy = (float*)o; o += a4; float* dpxr = (float*)o; o += a4;
+  int* dlv = (int*)o; o += a4; float* dvc = (float*)o; o += a4; float* ddz = (float*)o; o += a4;
+  int* dcount = (int*)o;
+  cudaStream_t st = cudaStreamPerThread;
+  GLUE_TRY(cudaMemcpyAsync(dP, world_pos, 12 * (size_t)n, cudaMemcpyHostToDevice, st));
+  GLUE_TRY(cudaMemcpyAsync(dN, normal, 12 * (size_t)n, cudaMemcpyHostToDevice, st));
+  GLUE_TRY(cudaMemcpyAsync(dmin, min_distance, 4 * (size_t)n, cudaMemcpyHostToDevice, st));
+  GLUE_TRY(cudaMemcpyAsync(dmax, max_distance, 4 * (size_t)n, cudaMemcpyHostToDevice, st));
+  GLUE_TRY(cudaMemsetAsync(dcount, 0, sizeof(int), st));   // the array keeps the previous call's count
   k_is_in_frustum<<<(n + 127) / 128, 128, 0, st>>>(*cam, n, dP, dN, dmin, dmax, viewing_cos_limit, dview, dpx, dpy, dpxr, dlv,
                                                     dvc, ddz, dcount);
   count_launch();
