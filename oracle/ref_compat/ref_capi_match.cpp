@@ -215,6 +215,49 @@ int ref_search_by_projection_frame(const cuorb_frame_view* cur, int n_last, cons
   return n;
 }
 
+// ---- the same function with its geometric prologue live: real poses (Sophus stand-in), world points, the
+// reference's own Pinhole::project.  pose = 9 floats R (row-major) + 3 floats t, world -> camera.  What
+// shim/ORBmatcher.h's SearchByProjection(Cur, Last) overload is checked against (tests/test_gpu_shim.py). ----
+int ref_search_by_projection_frame_pose(const cuorb_frame_view* cur, const float* pose_cur, const float* pose_last,
+                                        const float* K4, int n_last, const uint8_t* last_desc, const float* world_pos,
+                                        const int32_t* last_octave, const float* last_angle, const uint8_t* has_mp,
+                                        const uint8_t* outlier, const int32_t* n_obs, float th, int mono, int check_ori,
+                                        int32_t* final_binding_out) {
+  FrameFromView fv(cur);
+  Pinhole cam(std::vector<float>{K4[0], K4[1], K4[2], K4[3]});
+  fv.F.mpCamera = &cam;
+  auto pose = [](const float* p) {
+    Eigen::Matrix3f R;
+    for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) R(r, c) = p[3 * r + c];
+    return Sophus::SE3f(R, Eigen::Vector3f(p[9], p[10], p[11]));
+  };
+  fv.F.mTcw = pose(pose_cur);
+  Frame last;
+  std::unique_ptr<MapPoint[]> mps(new MapPoint[n_last > 0 ? n_last : 1]);
+  last.N = n_last; last.Nleft = -1;
+  last.mTcw = pose(pose_last);
+  last.mvKeys.resize(n_last); last.mvKeysUn.resize(n_last);
+  last.mvpMapPoints.assign(n_last, nullptr);
+  last.mvbOutlier.assign(n_last, false);
+  for (int i = 0; i < n_last; i++) {
+    last.mvKeys[i].octave = last_octave[i]; last.mvKeys[i].angle = last_angle[i];
+    last.mvKeysUn[i] = last.mvKeys[i];
+    last.mvbOutlier[i] = outlier[i] != 0;
+    if (!has_mp[i]) continue;
+    mps[i].mWorldPos = Eigen::Vector3f(world_pos[3 * i], world_pos[3 * i + 1], world_pos[3 * i + 2]);
+    mps[i].nObs = n_obs[i];
+    mps[i].mDescriptor = desc_mat(last_desc + (size_t)i * 32, 1);
+    last.mvpMapPoints[i] = &mps[i];
+  }
+  ORBmatcher matcher(0.9f, check_ori != 0);
+  const int n = matcher.SearchByProjection(fv.F, last, th, mono != 0);
+  for (int k = 0; k < fv.F.N; k++) {
+    MapPoint* b = fv.F.mvpMapPoints[k];
+    final_binding_out[k] = !b ? -1 : (b >= &mps[0] && b < &mps[0] + n_last) ? (int32_t)(b - &mps[0]) : -2;
+  }
+  return n;
+}
+
 // ---- bool Frame::isInFrustum(MapPoint*, float) — the reference's own body (src/Frame.cc:644-721), with
 // MapPoint::PredictScale (src/MapPoint.cc:574-589) and Pinhole::project (Pinhole.cpp:70-76) lifted verbatim;
 // the Eigen expressions inside run on the oracle/ref_compat/Eigen stand-in. ----

@@ -77,6 +77,8 @@ def lib() -> C.CDLL:
                                                [C.c_float, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p])
         L.ref_search_by_projection_frame.argtypes = ([FV, C.c_int] + [C.c_void_p] * 7 +
                                                      [C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p])
+        L.ref_search_by_projection_frame_pose.argtypes = ([FV] + [C.c_void_p] * 3 + [C.c_int] + [C.c_void_p] * 7 +
+                                                          [C.c_float, C.c_int, C.c_int, C.c_void_p])
         L.ref_is_in_frustum.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [C.c_float] + [C.c_void_p] * 7
         L.ref_bench_stereo.restype = C.c_double
         L.ref_bench_stereo.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
@@ -229,3 +231,19 @@ def is_in_frustum(cam, P, N, min_d, max_d, limit):
     """Frame::isInFrustum for n MapPoints; cam: a ctypes cuorb_frustum_camera (oracle_py.FrustumCamera)."""
     from .oracle_py import _frustum_call
     return _frustum_call(lib().ref_is_in_frustum, cam, P, N, min_d, max_d, limit)
+
+
+def search_by_projection_frame_pose(fv, pose_cur, pose_last, K4, last_desc, world_pos, last_octave, last_angle, has_mp,
+                                    outlier, n_obs, th, mono, check_ori=True):
+    """ORBmatcher::SearchByProjection(Cur, Last, th, bMono) with its prologue live (poses = 12 floats: R row-major, t).
+    Returns (nmatches, final_binding[N])."""
+    arrs = [np.ascontiguousarray(pose_cur, np.float32), np.ascontiguousarray(pose_last, np.float32),
+            np.ascontiguousarray(K4, np.float32)]
+    per = [np.ascontiguousarray(last_desc, np.uint8), np.ascontiguousarray(world_pos, np.float32),
+           np.ascontiguousarray(last_octave, np.int32), np.ascontiguousarray(last_angle, np.float32),
+           np.ascontiguousarray(has_mp, np.uint8), np.ascontiguousarray(outlier, np.uint8),
+           np.ascontiguousarray(n_obs, np.int32)]
+    final = np.zeros(fv.n, np.int32)
+    n = lib().ref_search_by_projection_frame_pose(C.byref(fv), *[_p(a) for a in arrs], len(last_octave),
+                                                  *[_p(a) for a in per], th, int(mono), int(check_ori), _p(final))
+    return n, final

@@ -63,7 +63,8 @@ public:
     if (n == 0) { _descriptors.release(); return mono; }
     std::memcpy((void*)_keypoints.data(), kp_buf_.data(), sizeof(cuorb_keypoint) * (size_t)n);
     _descriptors.create(n, 32, CV_8U);
-    for (int i = 0; i < n; i++) std::memcpy(_descriptors.ptr<unsigned char>(i), desc_buf_.ptr<unsigned char>(i), 32);
+    cv::Mat out = _descriptors.getMat();   // cv::OutputArray has no ptr<>(): go through the Mat header it wraps
+    for (int i = 0; i < n; i++) std::memcpy(out.ptr<unsigned char>(i), desc_buf_.ptr<unsigned char>(i), 32);
     return mono;
   }
 

@@ -82,6 +82,59 @@ public:
     return n;
   }
 
+  // int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono)
+  // (include/ORBmatcher.h:54-56, src/ORBmatcher.cc:1684-1908; pinhole branch) - Tracking::TrackWithMotionModel.
+  // The geometric prologue (:1696-1721) runs here on the caller's own Sophus / Eigen types, in the reference's
+  // expression order; the window search, the "already bound" skip, the uRight gate, the rotation histogram and
+  // ComputeThreeMaxima run in libcuorb; the bindings are then replayed exactly as the reference makes them:
+  // EVERY accepted match binds in last-frame order (:1786 - a later MapPoint may overwrite an earlier one that
+  // has no observations), and afterwards the features of every non-kept histogram bin are set to NULL (:1889-1905).
+  template <class FrameT>
+  int SearchByProjection(FrameT& CurrentFrame, const FrameT& LastFrame, const float th, const bool bMono) {
+    if (CurrentFrame.Nleft != -1 || LastFrame.Nleft != -1)
+      throw std::runtime_error("ORBmatcher shim: fisheye (Nleft != -1) branch is not built");
+    const int NL = LastFrame.N;
+    if (NL == 0 || CurrentFrame.N == 0) return 0;
+    const auto Tcw = CurrentFrame.GetPose();                         // :1696
+    const auto twc = Tcw.inverse().translation();                    // :1697
+    const auto Tlw = LastFrame.GetPose();                            // :1699
+    const auto tlc = Tlw * twc;                                      // :1700
+    const bool bForward  = tlc(2) > CurrentFrame.mb && !bMono;       // :1702
+    const bool bBackward = -tlc(2) > CurrentFrame.mb && !bMono;      // :1703
+    std::vector<uint8_t> desc((size_t)NL * 32, 0), flags(NL, 0);
+    std::vector<float> u(NL, 0.f), v(NL, 0.f), invz(NL, 0.f), ang(NL, 0.f);
+    std::vector<int32_t> oct(NL, 0), best(NL, -1), bin(NL, -1);
+    for (int i = 0; i < NL; i++) {
+      auto* pMP = LastFrame.mvpMapPoints[i];
+      if (!pMP || LastFrame.mvbOutlier[i]) continue;                 // :1706-1708
+      const auto x3Dw = pMP->GetWorldPos();                          // :1710
+      const auto x3Dc = Tcw * x3Dw;                                  // :1711
+      const float invzc = 1.0 / x3Dc(2);                             // :1715 (double division, rounded to float)
+      if (invzc < 0) continue;                                       // :1717
+      const auto uv = CurrentFrame.mpCamera->project(x3Dc);          // :1721; the image-bounds test (:1723-1728) is libcuorb's
+      u[i] = uv(0); v[i] = uv(1); invz[i] = invzc;
+      oct[i] = LastFrame.mvKeys[i].octave;                           // :1730-1732
+      ang[i] = LastFrame.mvKeysUn[i].angle;                          // :1793 (kpLF, Nleft == -1)
+      flags[i] = (uint8_t)(CUORB_MP_IN_VIEW | (pMP->Observations() > 0 ? CUORB_MP_HAS_OBS : 0));   // :1763-1767
+      const cv::Mat d = pMP->GetDescriptor();
+      std::memcpy(&desc[(size_t)i * 32], d.template ptr<unsigned char>(0), 32);
+    }
+    std::vector<uint8_t> bound;
+    const cuorb_frame_view fv = view(CurrentFrame, bound);
+    int32_t keep[3] = {-1, -1, -1};
+    const int n = cuorb_search_by_projection_frame(device_, &fv, NL, desc.data(), u.data(), v.data(), invz.data(), oct.data(),
+                                                   ang.data(), flags.data(), th, bForward ? 1 : 0, bBackward ? 1 : 0,
+                                                   mbCheckOrientation ? 1 : 0, best.data(), bin.data(), keep);
+    if (n < 0) throw std::runtime_error(std::string("SearchByProjection(Cur, Last) (libcuorb): ") + cuorb_last_error());
+    for (int i = 0; i < NL; i++)                                     // :1786, in last-frame order
+      if (best[i] >= 0) CurrentFrame.mvpMapPoints[best[i]] = LastFrame.mvpMapPoints[i];
+    if (mbCheckOrientation)                                          // :1889-1905
+      for (int i = 0; i < NL; i++)
+        if (best[i] >= 0 && bin[i] != keep[0] && bin[i] != keep[1] && bin[i] != keep[2])
+          CurrentFrame.mvpMapPoints[best[i]] = nullptr;
+    return n;
+  }
+
   // int SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches)
   // (include/ORBmatcher.h:66, src/ORBmatcher.cc:237-420), mono branch.  Reads pKF->GetMapPointMatches(),
   // pKF->mFeatVec, pKF->mDescriptors, pKF->mvKeysUn, F.mFeatVec, F.mDescriptors, F.mvKeys, F.N.
@@ -278,7 +331,9 @@ public:
   }
 
   // float RadiusByViewingCos(const float& viewCos)  (src/ORBmatcher.cc:229-235)
-  static float RadiusByViewingCos(const float& viewCos) { return viewCos > 0.998f ? 2.5f : 4.0f; }
+  // the float argument is promoted and compared with the DOUBLE literal 0.998: (float)0.998 > 0.998, so
+  // viewCos == 0.998f gives 2.5 (src/ORBmatcher.cc:230), as libcuorb's device path does
+  static float RadiusByViewingCos(const float& viewCos) { return (double)viewCos > 0.998 ? 2.5f : 4.0f; }
 
   float mfNNratio;
   bool  mbCheckOrientation;

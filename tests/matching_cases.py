@@ -109,3 +109,44 @@ def frustum_case(n, seed, w=752, h=480):
     edge = rng.random(n) < 0.1
     max_d[edge] = (dist[edge] * 1.2 ** k[edge]).astype(np.float32)
     return cam, P, nrm.astype(np.float32), min_d, max_d
+
+
+def lastframe_pose_case(k, d, seed, motion, w=752, h=480):
+    """Tracking::TrackWithMotionModel inputs with the geometry live: current / last camera poses, world points of the
+    last frame's MapPoints (back-projected near current features, some behind the camera / out of the image), a mix of
+    0- and >0-observation MapPoints and duplicated targets, so that a feature IS bound twice and the later binding
+    overwrites the earlier one (src/ORBmatcher.cc:1763-1767, 1786).  motion: 'forward' | 'backward' | 'none'."""
+    rng = np.random.default_rng(seed)
+    N = len(k)
+    K4 = np.array([458.654, 457.296, 367.215, 248.375], np.float32)
+    a = rng.uniform(-0.05, 0.05, 3)
+    Rx = np.array([[1, 0, 0], [0, np.cos(a[0]), -np.sin(a[0])], [0, np.sin(a[0]), np.cos(a[0])]])
+    Ry = np.array([[np.cos(a[1]), 0, np.sin(a[1])], [0, 1, 0], [-np.sin(a[1]), 0, np.cos(a[1])]])
+    Rz = np.array([[np.cos(a[2]), -np.sin(a[2]), 0], [np.sin(a[2]), np.cos(a[2]), 0], [0, 0, 1]])
+    R = (Rz @ Ry @ Rx).astype(np.float32)
+    t = rng.uniform(-0.5, 0.5, 3).astype(np.float32)
+    pose_cur = np.concatenate([R.ravel(), t]).astype(np.float32)
+    dz = {"forward": -0.6, "backward": 0.6, "none": 0.01}[motion]      # tlc(2) = Tlw * twc: last sees the current centre at +-z
+    t_last = (t.astype(np.float64) + np.array([0.0, 0.0, -dz])).astype(np.float32)
+    pose_last = np.concatenate([R.ravel(), t_last]).astype(np.float32)
+    n = N + 300
+    tgt = rng.integers(0, N, n)
+    tgt[:150] = tgt[150:300]                                           # several last-frame points chase one feature
+    u = k["x"][tgt] + rng.uniform(-5, 5, n); v = k["y"][tgt] + rng.uniform(-5, 5, n)
+    u[300:306] = -4.0; v[306:312] = h + 3.0                            # projected out of the image
+    z = rng.uniform(1.0, 30.0, n); z[312:320] = -2.0                   # behind the camera
+    pc = np.stack([(u - K4[2]) / K4[0] * z, (v - K4[3]) / K4[1] * z, z], 1)
+    world = ((pc - t.astype(np.float64)) @ R.astype(np.float64)).astype(np.float32)
+    desc = flip_bits(d[tgt], rng, 50)
+    rnd_ = rng.random(n) < 0.2
+    desc[rnd_] = rng.integers(0, 256, (int(rnd_.sum()), 32), dtype=np.uint8)
+    octave = np.clip(k["octave"][tgt] + rng.integers(-1, 2, n), 0, 7).astype(np.int32)
+    angle = np.mod(k["angle"][tgt] + rng.normal(0, 8, n), 360).astype(np.float32)
+    angle[rng.random(n) < 0.1] = rng.uniform(0, 360)
+    has_mp = (rng.random(n) < 0.85).astype(np.uint8)
+    outlier = (rng.random(n) < 0.05).astype(np.uint8)
+    n_obs = np.where(rng.random(n) < 0.5, 0, rng.integers(1, 6, n)).astype(np.int32)
+    u_right = np.where(rng.random(N) < 0.5, k["x"] - rng.uniform(1, 60, N), -1).astype(np.float32)
+    bound = (rng.random(N) < 0.05).astype(np.uint8)
+    return dict(K4=K4, pose_cur=pose_cur, pose_last=pose_last, world=world, desc=desc, octave=octave, angle=angle,
+                has_mp=has_mp, outlier=outlier, n_obs=n_obs, u_right=u_right, bound=bound)

@@ -137,3 +137,47 @@ def test_cpp_shim_searches(tmp_path):
     fvt, keep_t = op.make_frame_view(ka, da, None, has_a, w, h, sf, mb=0.1, mbf=40.0)
     rt, mt = op.search_for_triangulation(fvt, fvb, off1, idx1, off2, idx2, F12, ep, (sf * sf).astype(np.float32), False, False, True)
     assert n_tri == rt and (tri == mt).all() and rt > 5
+
+
+@pytest.mark.parametrize("motion,th,mono", [("none", 7.0, False), ("forward", 15.0, False), ("backward", 7.0, False),
+                                            ("forward", 15.0, True)])
+def test_cpp_shim_search_by_projection_lastframe(tmp_path, motion, th, mono):
+    """shim/ORBmatcher.h SearchByProjection(Cur, Last, th, bMono) - Tracking::TrackWithMotionModel's call - with real
+    poses and world points: the FINAL CurrentFrame.mvpMapPoints and the return value equal the reference's own
+    function (oracle/_ref, src/ORBmatcher.cc:1684-1908), including features that are bound twice (a 0-observation
+    MapPoint overwritten by a later one) and the NULLing of the non-kept rotation bins."""
+    from oracle import ref_py as rp
+    from tests.matching_cases import extracted_frame, lastframe_pose_case
+    if not rp.available():
+        pytest.skip("oracle/_ref/liborb_ref.so did not travel to this box")
+    build.build_libcuorb()
+    exe = str(tmp_path / "lastframe_check")
+    pkg = os.path.join(ROOT, "orbslam3_cpp_fork_b200")
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-DCUORB_SHIM_USE_OPENCV",
+                           "-I" + os.path.join(ROOT, "oracle", "ref_compat"),
+                           os.path.join(ROOT, "tests", "native", "lastframe_check.cpp"), "-o", exe,
+                           "-L" + pkg, "-l:libcuorb.so", "-Wl,-rpath," + pkg])
+    e, k, d = extracted_frame(seed=33)
+    sf = e.tables()[0]
+    w, h = 752, 480
+    c = lastframe_pose_case(k, d, 9, motion)
+    mb, mbf = np.float32(0.1), np.float32(40.0)
+    fv, keep = op.make_frame_view(k, d, c["u_right"], c["bound"], w, h, sf, mb=float(mb), mbf=float(mbf))
+    n_r, final_r = rp.search_by_projection_frame_pose(fv, c["pose_cur"], c["pose_last"], c["K4"], c["desc"], c["world"],
+                                                      c["octave"], c["angle"], c["has_mp"], c["outlier"], c["n_obs"], th, mono)
+    case = str(tmp_path / "case.bin"); out = str(tmp_path / "out.bin")
+    with open(case, "wb") as f:
+        np.array([len(k), len(c["octave"]), len(sf), int(mono), 1], np.int32).tofile(f)
+        np.concatenate([[th, mb, mbf, w, h], c["K4"], c["pose_cur"], c["pose_last"]]).astype(np.float32).tofile(f)
+        np.ascontiguousarray(k).tofile(f); np.ascontiguousarray(d).tofile(f)
+        c["u_right"].tofile(f); c["bound"].tofile(f); np.ascontiguousarray(sf, np.float32).tofile(f)
+        c["world"].tofile(f); c["octave"].tofile(f); c["angle"].tofile(f); c["has_mp"].tofile(f); c["outlier"].tofile(f)
+        c["n_obs"].tofile(f); c["desc"].tofile(f)
+    subprocess.check_call([exe, case, out])
+    res = np.fromfile(out, np.int32)
+    n_s, final_s = int(res[0]), res[1:]
+    assert n_r > 100
+    assert n_s == n_r
+    assert (final_s == final_r).all()
+    # the order-dependent situation really occurred: fewer bound features than accepted matches + removed ones
+    assert (final_r >= 0).sum() <= n_r
