@@ -483,6 +483,27 @@ def run_cuorb(args):
             pipe = json.load(open(os.path.join(ROOT, "profiles", "pipe_util.json"))).get(dom_all)
         except Exception:
             pass
+        # the roofline that binds FAST: instruction issue / the integer ALU pipe, not HBM.  Instruction counts are the
+        # committed `ncu --set full` capture's (profiles/pipe_util.json); the kernel time is this run's CUDA-event time.
+        alu = None
+        try:
+            pu = json.load(open(os.path.join(ROOT, "profiles", "pipe_util.json")))["fast"]
+            sm_clock = (clocks.get("sm_mhz") or peaks.get("sm_max_mhz") or 1965.0) * 1e6
+            n_sm = torch.cuda.get_device_properties(local).multi_processor_count
+            winst = pu["warp_inst_per_image"] * B
+            t_fast = stage_ms["fast"] * 1e-3
+            issue_peak = n_sm * 4 * sm_clock                     # 4 schedulers per SM, 1 warp-instruction per clock each
+            alu_peak = n_sm * 2 * sm_clock                       # the ALU pipe takes 2 warp-instructions per clock per SM
+            px = sum(a * b for a, b in level_sizes(W, H))
+            alu = {"bound": "issue slots / integer ALU pipe", "kernel": pu["kernel"],
+                   "warp_inst_per_launch": winst, "thread_inst_per_pixel": pu["warp_inst_per_image"] * pu["thread_inst_per_inst"] / px,
+                   "achieved_warp_inst_per_s": winst / t_fast, "issue_peak_warp_inst_per_s": issue_peak,
+                   "frac_of_issue_peak": winst / t_fast / issue_peak,
+                   "alu_pipe_warp_inst_per_launch": pu["alu_pipe_pct_of_peak"] / 100.0 * alu_peak * pu["time_us"] * 1e-6,
+                   "frac_of_alu_pipe_peak_ncu": pu["alu_pipe_pct_of_peak"] / 100.0,
+                   "source": pu["source"] + "; time = this run's CUDA-event stage time"}
+        except Exception:
+            pass
         cores = os.cpu_count() or 1
         with_cpu = not args.no_cpu_baseline and world == 1      # the CPU baseline is an N=1 figure
         cpu_fps, cpu_n, cpu_kind, cpu_label = cpu_baseline(cores) if with_cpu else (None, 0, None, None)
@@ -553,7 +574,7 @@ def run_cuorb(args):
                          "note": "stage times: CUDA events on the launching stream, handles serialised; FAST is bound by the "
                                  "integer ALU pipe (min/max network), not HBM - see DESIGN.md section 6",
                          "stage_ms_per_step": stage_ms, "stage_gbs": stage_gbs,
-                         "dominant_stage_overall": dom_all, "dominant_stage_pipe_utilisation": pipe,
+                         "dominant_stage_overall": dom_all, "dominant_stage_pipe_utilisation": pipe, "alu": alu,
                          "algorithmic_bytes_per_image": ab},
             "cpu_baseline": None if cpu_fps is None else {
                 "value": cpu_fps, "unit": "frames/s", "cores": cores, "kind": cpu_kind,

@@ -43,7 +43,7 @@ struct cuorb_extractor {
   // device buffers (sized for max_width x max_height x max_batch)
   ExtractorGeom* d_geom = nullptr;
   ResizeTap *d_xtab = nullptr, *d_ytab = nullptr;
-  uint4*     d_wtab = nullptr;        // per-word horizontal tap tables of k_pyr_resize_tab
+  uint4*     d_wtab = nullptr;        // per-word horizontal tap tables of k_pyr_resize_stage
   int        wtab_off[MAX_LEVELS];
   PyrPlan    pyr_plan[MAX_LEVELS];    // staged resize kernel: CTA shape and staged source window per level
   size_t     cap_wtab = 0;

@@ -8,11 +8,11 @@
 //   2a  necessary condition on the 4 compass ring pixels, four pixels per thread in u8x4 SIMD
 //       (VABSDIFF4); pixel pairs with a passing pixel are compacted into per-warp lists with
 //       warp ballots (no atomics);
-//   2b  BRANCH-FREE corner score on the listed pairs, two pixels per thread in 16x2 SIMD:
-//       d[k] = v - ring[k] (+256 bias, so a 32-bit subtract never borrows across lanes), then
-//           max_k min(d[k..k+8])  and  min_k max(d[k..k+8])        (k circular, 16 arcs)
-//       as a network of 3-input VIMNMX3.U16x2 (arcs k and k+1 share 8 of 9 elements: 36 SIMD ops
-//       per polarity for two pixels); "corner at t" <=> score >= t; corners go to a second list;
+//   2b  BRANCH-FREE corner score on the listed pairs, two pixels per thread in 16x2 SIMD, on the raw ring
+//       values: M = min_k max(ring[k..k+8]) and m = max_k min(ring[k..k+8]) (k circular, 16 arcs) as a
+//       network of 3-input VIMNMX3.U16x2 (arcs k and k+1 share 8 of 9 elements: 36 SIMD ops per polarity for
+//       two pixels), then score = max(v - M, m - v) - 1: the differences are taken once at the end, not per
+//       ring element; "corner at t" <=> score >= t; corners go to a second list;
 //   3   strict 8-neighbour NMS over the listed corners on a u8 score tile;
 //   the whole thing first at iniThFAST and, only if the cell stays empty, again at minThFAST
 //   (:798-826), decided CTA-wide with __syncthreads_or.
@@ -48,34 +48,35 @@ __device__ __forceinline__ unsigned odd_pair(unsigned lo, unsigned hi) { return 
 __device__ __forceinline__ unsigned magic(int d) { return 0xFFFFFFFFu / (unsigned)d + 1u; }
 __device__ __forceinline__ int fastdiv(int n, unsigned inv, int d) { return d == 1 ? n : (int)__umulhi((unsigned)n, inv); }
 
-// score of the two pixels held in `c` (u16x2) given the 16 ring values r[k] (u16x2 each).
-// Returns biased extremes: A = 256 + max_k min9(d), B = 256 + min_k max9(d), d = v - ring.
-__device__ __forceinline__ void arc_extremes(unsigned c, const unsigned (&r)[16], unsigned& A, unsigned& B) {
-  const unsigned cb = c + 0x01000100u;
-  unsigned d[16];
-#pragma unroll
-  for (int k = 0; k < 16; k++) d[k] = cb - r[k];  // each lane in [1, 511]: no cross-lane borrow
-  // pairs starting at odd k: m2[j] <-> d[2j+1], d[2j+2]
+// Arc extremes of the two pixels of a pair, on the RAW ring values r[k] (u16x2 each, lanes in 0..255):
+//   M = min over the 16 arcs of 9 of max9(r),   m = max over the 16 arcs of min9(r).
+// With d[k] = v - r[k]:  max_k min9(d) = v - M  and  min_k max9(d) = v - m, so the corner score
+//   max(max_k min9(d), -min_k max9(d)) - 1 = max(v - M, m - v) - 1
+// needs one subtraction per polarity at the end instead of sixteen up front (the min / max network is the same
+// size: arcs 2j and 2j+1 share r[2j+1 .. 2j+8] and differ in r[2j] vs r[2j+9]).
+__device__ __forceinline__ void arc_extremes(const unsigned (&r)[16], unsigned& M, unsigned& m) {
+  // pairs starting at odd k: lo2[j], hi2[j] <-> r[2j+1], r[2j+2]
   unsigned lo2[8], hi2[8];
 #pragma unroll
   for (int j = 0; j < 8; j++) {
-    lo2[j] = umin2(d[2 * j + 1], d[(2 * j + 2) & 15]);
-    hi2[j] = umax2(d[2 * j + 1], d[(2 * j + 2) & 15]);
+    lo2[j] = umin2(r[2 * j + 1], r[(2 * j + 2) & 15]);
+    hi2[j] = umax2(r[2 * j + 1], r[(2 * j + 2) & 15]);
   }
-  unsigned ta[8], tb[8];
+  unsigned tM[8], tm[8];
 #pragma unroll
   for (int j = 0; j < 8; j++) {
-    // arcs 2j and 2j+1 share d[2j+1 .. 2j+8]; they differ in d[2j] vs d[2j+9]
-    const unsigned m6 = umin3(lo2[j], lo2[(j + 1) & 7], lo2[(j + 2) & 7]);
     const unsigned x6 = umax3(hi2[j], hi2[(j + 1) & 7], hi2[(j + 2) & 7]);
-    const unsigned e_hi = umax2(d[2 * j], d[(2 * j + 9) & 15]);
-    const unsigned e_lo = umin2(d[2 * j], d[(2 * j + 9) & 15]);
-    ta[j] = umin3(m6, lo2[(j + 3) & 7], e_hi);  // max(min9(arc 2j), min9(arc 2j+1))
-    tb[j] = umax3(x6, hi2[(j + 3) & 7], e_lo);  // min(max9(arc 2j), max9(arc 2j+1))
+    const unsigned m6 = umin3(lo2[j], lo2[(j + 1) & 7], lo2[(j + 2) & 7]);
+    const unsigned e_lo = umin2(r[2 * j], r[(2 * j + 9) & 15]);
+    const unsigned e_hi = umax2(r[2 * j], r[(2 * j + 9) & 15]);
+    tM[j] = umax3(x6, hi2[(j + 3) & 7], e_lo);  // min(max9(arc 2j), max9(arc 2j+1))
+    tm[j] = umin3(m6, lo2[(j + 3) & 7], e_hi);  // max(min9(arc 2j), min9(arc 2j+1))
   }
-  A = umax3(umax3(ta[0], ta[1], ta[2]), umax3(ta[3], ta[4], ta[5]), umax2(ta[6], ta[7]));
-  B = umin3(umin3(tb[0], tb[1], tb[2]), umin3(tb[3], tb[4], tb[5]), umin2(tb[6], tb[7]));
+  M = umin3(umin3(tM[0], tM[1], tM[2]), umin3(tM[3], tM[4], tM[5]), umin2(tM[6], tM[7]));
+  m = umax3(umax3(tm[0], tm[1], tm[2]), umax3(tm[3], tm[4], tm[5]), umax2(tm[6], tm[7]));
 }
+// score of one u16 lane: max(v - M, m - v) - 1
+__device__ __forceinline__ int lane_score(int v, int M, int m) { return max(v - M, m - v) - 1; }
 
 }  // namespace
 
@@ -225,11 +226,12 @@ __global__ void __launch_bounds__(128) k_fast_cells(const ExtractorGeom* __restr
             const unsigned a = T[-3 * TP - 1], b = T[-3 * TP], c = T[-3 * TP + 1];
             ring[8] = b; ring[7] = odd_pair(b, c); ring[9] = odd_pair(a, b);
           }
-          unsigned A, B;
-          arc_extremes(T[0], ring, A, B);
-          // score = max(a, -b) - 1 with a = A - 256, b = B - 256   (cornerScore<16>)
-          const int s0 = max((int)(A & 0xFFFFu) - 257, 255 - (int)(B & 0xFFFFu));
-          const int s1 = max((int)(A >> 16) - 257, 255 - (int)(B >> 16));
+          unsigned M, m;
+          arc_extremes(ring, M, m);
+          // score = max(v - M, m - v) - 1   (cornerScore<16>)
+          const unsigned ctr = T[0];
+          const int s0 = lane_score((int)(ctr & 0xFFFFu), (int)(M & 0xFFFFu), (int)(m & 0xFFFFu));
+          const int s1 = lane_score((int)(ctr >> 16), (int)(M >> 16), (int)(m >> 16));
           unsigned char* q = s_score + (r + 1) * sp + px + 4;
           c0 = px >= 0 && px < dw && s0 >= cur_th;
           c1 = px + 1 >= 0 && px + 1 < dw && s1 >= cur_th;
@@ -449,10 +451,10 @@ __global__ void __launch_bounds__(32 * NW) k_fast_persist(const __grid_constant_
             ring[9] = widen_odd(a, b); ring[8] = widen_even(b); ring[7] = widen_odd(b, c);
           }
 #undef H16
-          unsigned A, Bx;
-          arc_extremes(ctr, ring, A, Bx);
-          const int s0 = max((int)(A & 0xFFFFu) - 257, 255 - (int)(Bx & 0xFFFFu));
-          const int s1 = max((int)(A >> 16) - 257, 255 - (int)(Bx >> 16));
+          unsigned M, m;
+          arc_extremes(ring, M, m);
+          const int s0 = lane_score((int)(ctr & 0xFFFFu), (int)(M & 0xFFFFu), (int)(m & 0xFFFFu));
+          const int s1 = lane_score((int)(ctr >> 16), (int)(M >> 16), (int)(m >> 16));
           unsigned char* q = s_score + (r + 1) * sp + px + 4;
           const bool k0 = in && px >= 0 && px < dw && s0 >= cur_th;
           const bool k1 = in && px + 1 >= 0 && px + 1 < dw && s1 >= cur_th;
@@ -598,12 +600,12 @@ void launch_fast_persist(const ExtractorGeom& g, const FastMaps& maps, const int
   const int sp_max = ((((g.max_cell_w + 5 + 3) >> 2) | 1) << 2);
   P.score_bytes = ((sp_max * (g.max_cell_h + 2) + 15) / 16) * 16;
   const int maxquads = ((g.max_cell_w + 3) / 4 + 1) * g.max_cell_h;
-  // warps per cell: 2 measured best on B200 (0.667 ms per 256 images; 4 warps 0.675, 1 warp 0.810): fewer
-  // warps wait at the two per-cell barriers, more cells are in flight per SM; CUORB_FAST_WARPS overrides
-  static const int NW = []() { const char* e = getenv("CUORB_FAST_WARPS"); const int v = e ? atoi(e) : 2; return v == 1 || v == 4 ? v : 2; }();
+  // two warps share a cell: measured best on B200 (0.667 ms per 256 images at the time; 4 warps 0.675, 1 warp 0.810):
+  // fewer warps wait at the two per-cell barriers, more cells are in flight per SM
+  constexpr int NW = 2;
   P.pcap = 64 * ((maxquads + 32 * NW - 1) / (32 * NW));
   const int smem = 128 + 2 * P.tile_bytes + 2 * P.score_bytes + 2 * NW * P.pcap;   // one u16 list per warp: pairs, then corner pairs in place
-  void (*kern)(const FastMaps, const FastParams) = NW == 1 ? k_fast_persist<1> : NW == 2 ? k_fast_persist<2> : k_fast_persist<4>;
+  void (*kern)(const FastMaps, const FastParams) = k_fast_persist<NW>;
   if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);   // per device
   // occupancy and SM count, cached per (device, smem) under a lock: the two ExtractORB threads of the stereo
   // Frame constructor pass through here concurrently, possibly for handles on different devices

@@ -199,33 +199,44 @@ static int run_projection(int device, const cuorb_frame_view* fv, ProjQuery Q, c
   Q.flags = up(A, flags, m, st);
   int* binder[2] = {A.take<int>(n), A.take<int>(n)};
   int* result = A.take<int>(m);
-  int* changed = A.take<int>(1);
+  // Binding rounds to the sequential fixed point, enqueued ROUND_BATCH at a time with no host round trip in
+  // between; round k of a batch sets flag[k] when a result changed and the host reads the batch's flags once.
+  // Rounds past the fixed point are idempotent (equal results -> equal binder tables -> no dirty cell -> every
+  // window keeps its result) and cheap (17 us at cfg4), so they simply run: a device-side "skip if the previous
+  // round was quiet" test at the top of k_proj_round cost 0.07-0.15 ms per call in every form tried (per thread,
+  // per block), more than the rounds it saves.  Measured at cfg4 (50k MapPoints, 5 rounds to converge): one sync
+  // per round 0.556 ms per call, batches of 6 0.510 ms (scripts/ab_projection.py, profiles/r02_s9_abproj.txt).
+  constexpr int ROUND_BATCH = 6;
+  int* flag = A.take<int>(ROUND_BATCH);
   unsigned* dirty = A.take<unsigned>(2 * FRAME_GRID_ROWS);
   k_fill<<<(n + 255) / 256, 256, 0, st>>>(binder[0], n, NO_BINDER);
   k_fill<<<(m + 255) / 256, 256, 0, st>>>(result, m, -2);
   count_launch(2);
   int rounds = 0;
-  for (;; rounds++) {
+  for (bool converged = false; !converged;) {
     if (rounds > m + 2) { set_error("projection search did not converge"); return CUORB_E_CUDA; }
-    int* prev = binder[rounds & 1];
-    int* next = binder[(rounds + 1) & 1];
-    CUORB_CUDA_TRY(cudaMemsetAsync(changed, 0, sizeof(int), st));
-    if (rounds > 0) {   // cells whose features changed binder between the last two rounds (next still holds round-2's table)
-      CUORB_CUDA_TRY(cudaMemsetAsync(dirty, 0, 2 * FRAME_GRID_ROWS * sizeof(unsigned), st));
-      k_dirty_cells<<<(n + 255) / 256, 256, 0, st>>>(F, prev, next, dirty);
-      count_launch();
+    CUORB_CUDA_TRY(cudaMemsetAsync(flag, 0, ROUND_BATCH * sizeof(int), st));
+    for (int k = 0; k < ROUND_BATCH; k++, rounds++) {
+      int* prev = binder[rounds & 1];
+      int* next = binder[(rounds + 1) & 1];
+      if (rounds > 0) {   // cells whose features changed binder between the last two rounds (next still holds round-2's table)
+        CUORB_CUDA_TRY(cudaMemsetAsync(dirty, 0, 2 * FRAME_GRID_ROWS * sizeof(unsigned), st));
+        k_dirty_cells<<<(n + 255) / 256, 256, 0, st>>>(F, prev, next, dirty);
+        count_launch();
+      }
+      k_fill<<<(n + 255) / 256, 256, 0, st>>>(next, n, NO_BINDER);
+      k_proj_round<<<(m + 7) / 8, 256, 0, st>>>(F, Q, prev, next, result, flag + k, rounds > 0 ? dirty : nullptr);
+      count_launch(2);
     }
-    k_fill<<<(n + 255) / 256, 256, 0, st>>>(next, n, NO_BINDER);
-    k_proj_round<<<(m + 7) / 8, 256, 0, st>>>(F, Q, prev, next, result, changed, rounds > 0 ? dirty : nullptr);
-    count_launch(2);
-    int h_changed = 0;
-    CUORB_CUDA_TRY(cudaMemcpyAsync(&h_changed, changed, sizeof(int), cudaMemcpyDeviceToHost, st));
+    int h_flag[ROUND_BATCH];
+    CUORB_CUDA_TRY(cudaMemcpyAsync(h_flag, flag, sizeof(h_flag), cudaMemcpyDeviceToHost, st));
     CUORB_CUDA_TRY(cudaStreamSynchronize(st));
-    if (!h_changed) break;
+    for (int k = 0; k < ROUND_BATCH; k++)
+      if (!h_flag[k]) { converged = true; rounds -= ROUND_BATCH - 1 - k; break; }   // rounds to the first quiet one, inclusive
   }
   CUORB_CUDA_TRY(cudaMemcpyAsync(result_out, result, sizeof(int) * m, cudaMemcpyDeviceToHost, st));
   CUORB_CUDA_TRY(cudaStreamSynchronize(st));
-  return rounds + 1;
+  return rounds;
 }
 
 }  // namespace cuorb

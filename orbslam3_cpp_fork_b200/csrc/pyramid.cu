@@ -22,7 +22,7 @@ namespace cuorb {
 
 constexpr int PYR_RS = 16;  // interior rows per thread strip
 constexpr int PYR_TX = 64;  // threads (output words) per CTA
-constexpr int PYR_TAB_TX = 192;  // k_pyr_resize_tab: upper bound of its per-level CTA width
+constexpr int PYR_TAB_TX = 192;  // k_pyr_resize_stage: upper bound of its per-level CTA width
 
 __device__ __forceinline__ int reflect101(int i, int n) {
   // border (19) < n is checked on the host, so one reflection suffices
@@ -211,7 +211,7 @@ __global__ void __launch_bounds__(PYR_TX) k_pyr_resize(const ExtractorGeom* __re
   }
 }
 
-// ---- table-driven variant (all scale factors whose 4-column tap window fits 8 source bytes) ----
+// ---- table-driven, staged variant (all scale factors whose 4-column tap window fits 8 source bytes) ----
 // Everything a thread needs about its four output columns comes from a host-built table
 // (build_resize_words): the aligned source offset of its 12-byte window, the funnel shift that
 // brings the first tap to byte 0, four PRMT selectors and the four coefficient pairs.  Per source
@@ -227,109 +227,12 @@ __global__ void __launch_bounds__(PYR_TX) k_pyr_resize(const ExtractorGeom* __re
 // offsets from two base pointers, border rows on a rare uniform path, and the two horizontal-sum
 // register sets swap roles by code duplication (state A: H0 = upper row; state B: H1 = upper row)
 // instead of register copies.
-__global__ void __launch_bounds__(PYR_TAB_TX, 1536 / PYR_TAB_TX) k_pyr_resize_tab(const ExtractorGeom* __restrict__ dg, int level,
-                                                           uint8_t* __restrict__ pyr,
-                                                           const uint4* __restrict__ wtab,
-                                                           const ResizeTap* __restrict__ ytab, int rs) {
-  // per output row of the strip: {offset of source row s | advance from the previous row (0, 1, 2 = reload both),
-  //                               offset of source row s+1, b0 << 16, b1 << 16}; offsets in bytes, rows clipped to sh-1
-  __shared__ uint4 s_rec[PYR_RS];
-  const LevelGeom& L = dg->lv[level];
-  const LevelGeom& S = dg->lv[level - 1];
-  const int lh = L.h;
-  const int y0 = blockIdx.y * rs, n = min(rs, lh - y0);
-  if ((int)threadIdx.x < n) {
-    const ResizeTap* yt = ytab + L.ytab_off + y0 + threadIdx.x;
-    const ResizeTap t = yt[0];
-    const int sy = max((int)t.s, 0), sh1 = S.h - 1;
-    const int prev = threadIdx.x == 0 ? -4 : max((int)yt[-1].s, 0);
-    const unsigned adv = (unsigned)min(max(sy - prev, 0), 2);
-    s_rec[threadIdx.x] = make_uint4((unsigned)(min(sy, sh1) * S.pitch) | adv, (unsigned)(min(sy + 1, sh1) * S.pitch),
-                                    (unsigned)t.a0 << 16, (unsigned)t.a1 << 16);
-  }
-  __syncthreads();
-  const int word = blockIdx.x * blockDim.x + threadIdx.x;
-  if (word * 4 >= L.pitch) return;
-  const uint4 e0 = __ldg(&wtab[2 * word]), cf = __ldg(&wtab[2 * word + 1]);
-  uint8_t* base = pyr + (size_t)blockIdx.z * dg->pyr_img_stride;
-  const uint8_t* src = base + S.pix_off + e0.x;
-  const unsigned dp = (unsigned)L.pitch;
-  uint8_t* dst = base + L.plane_off + 4 * (size_t)word;               // padded row 0 of this word column
-  const unsigned shift = e0.y, sel0 = e0.z & 0xFFFFu, sel1 = e0.z >> 16, sel2 = e0.w & 0xFFFFu, sel3 = e0.w >> 16;
-
-  auto fetch = [&](unsigned off, unsigned (&w)[3]) {
-    const unsigned* p = reinterpret_cast<const unsigned*>(src + off);
-    w[0] = p[0]; w[1] = p[1]; w[2] = p[2];
-  };
-  auto hsum4 = [&](const unsigned (&w)[3], unsigned (&h)[4]) {
-    const unsigned X0 = __funnelshift_r(w[0], w[1], shift), X1 = __funnelshift_r(w[1], w[2], shift);
-    h[0] = __dp2a_lo(cf.x, __byte_perm(X0, X1, sel0), 0u) >> 4;
-    h[1] = __dp2a_lo(cf.y, __byte_perm(X0, X1, sel1), 0u) >> 4;
-    h[2] = __dp2a_lo(cf.z, __byte_perm(X0, X1, sel2), 0u) >> 4;
-    h[3] = __dp2a_lo(cf.w, __byte_perm(X0, X1, sel3), 0u) >> 4;
-  };
-  // ((b0*hA)>>16 + (b1*hB)>>16 + 2) >> 2 per column; two columns share one shift (sums are 10-bit)
-  auto blend = [&](const unsigned (&hA)[4], const unsigned (&hB)[4], unsigned b0s, unsigned b1s) -> unsigned {
-    unsigned v[4];
-#pragma unroll
-    for (int b = 0; b < 4; b++) v[b] = __umulhi(b0s, hA[b]) + __umulhi(b1s, hB[b]) + 2u;
-    const unsigned lo = (v[0] | (v[1] << 16)) >> 2, hi = (v[2] | (v[3] << 16)) >> 2;
-    return __byte_perm(lo, hi, 0x6420);
-  };
-
-  unsigned H0[4], H1[4], rA[3], rB[3];
-  uint4 rec = s_rec[0];
-  fetch(rec.x & ~3u, rA); fetch(rec.y, rB);
-  hsum4(rA, H0); hsum4(rB, H1);
-  int i = 0;
-  unsigned doff = (unsigned)(y0 + EDGE_THRESHOLD) * dp;               // byte offset of the padded output row
-  const bool edge_strip = y0 <= EDGE_THRESHOLD || y0 + n >= lh - 1 - EDGE_THRESHOLD;   // strip touches rows that are mirrored into the border
-  // one output row: request the next row's sources, blend + store the current one, then fold the
-  // new sources into the register set that held the retired upper row.  Returns the advance.
-  auto row = [&](unsigned (&hA)[4], unsigned (&hB)[4]) -> unsigned {
-    const unsigned b0s = rec.z, b1s = rec.w;
-    unsigned adv = 0;
-    if (i + 1 < n) {
-      rec = s_rec[i + 1];
-      adv = rec.x & 3u;
-      if (adv != 0) {
-        fetch(rec.y, rB);
-        if (adv == 2) fetch(rec.x & ~3u, rA);
-      }
-    }
-    const unsigned out = blend(hA, hB, b0s, b1s);
-    *reinterpret_cast<unsigned*>(dst + doff) = out;
-    if (edge_strip) {
-      const int y = y0 + i;
-      if (y >= 1 && y <= EDGE_THRESHOLD) *reinterpret_cast<unsigned*>(dst + (unsigned)(EDGE_THRESHOLD - y) * dp) = out;
-      if (y >= lh - 1 - EDGE_THRESHOLD && y <= lh - 2) *reinterpret_cast<unsigned*>(dst + (unsigned)(2 * lh + EDGE_THRESHOLD - 2 - y) * dp) = out;
-    }
-    doff += dp;
-    i++;
-    if (adv == 1) hsum4(rB, hA);                       // hB (row s+1) becomes the upper row: roles swap
-    else if (adv == 2) { hsum4(rA, hA); hsum4(rB, hB); }
-    return adv;
-  };
-  for (;;) {
-    // state A: H0 = source row s, H1 = row s+1
-    const unsigned a = row(H0, H1);
-    if (i >= n) return;
-    if (a != 1) continue;
-    // state B: H1 = source row s, H0 = row s+1
-    for (;;) {
-      const unsigned b = row(H1, H0);
-      if (i >= n) return;
-      if (b == 1) break;
-    }
-  }
-}
-
-// ---- staged variant: the strip's source rows arrive in shared memory by bulk async copies ----
-// Same arithmetic and row loop as k_pyr_resize_tab, but the CTA first stages every source row its strip
-// needs (rows s_first .. s_last+1, clipped to the last row; bytes [xlo, xlo + tw) of each) with one
-// cp.async.bulk per row, all in flight at once and signalled on one mbarrier.  The register variant keeps
-// ~1 row (12 bytes) per thread in flight, far too little to cover DRAM latency at 1536 threads per SM; here
-// a CTA has ~20 rows x ~700 bytes outstanding and the row loop only touches shared memory.
+// The CTA first stages every source row its strip needs (rows s_first .. s_last+1, clipped to the last row;
+// bytes [xlo, xlo + tw) of each) in shared memory with one cp.async.bulk per row, all in flight at once and
+// signalled on one mbarrier: ~20 rows x ~700 bytes outstanding per CTA, and the row loop only touches shared
+// memory.  (A register-only form of the same loop, ~12 bytes in flight per thread, was 5 % slower on the
+// stage and was removed in round 2.)  Levels whose staged window does not fit (build_pyr_plan) take the
+// generic k_pyr_resize<WIDE> above.
 struct PyrCols { int xlo[PYR_MAX_COLBLOCKS], tw[PYR_MAX_COLBLOCKS]; };
 
 __global__ void __launch_bounds__(PYR_TAB_TX, 1536 / PYR_TAB_TX) k_pyr_resize_stage(const ExtractorGeom* __restrict__ dg, int level,
@@ -338,7 +241,7 @@ __global__ void __launch_bounds__(PYR_TAB_TX, 1536 / PYR_TAB_TX) k_pyr_resize_st
                                                            const ResizeTap* __restrict__ ytab, int rs,
                                                            const PyrCols pc) {
   extern __shared__ __align__(128) unsigned char s_tile[];
-  __shared__ uint4 s_rec[PYR_RS];   // as in k_pyr_resize_tab, offsets relative to the staged tile
+  __shared__ uint4 s_rec[PYR_RS];   // per output row {source row offsets, advance, vertical weights}, relative to the staged tile
   __shared__ uint64_t s_bar;
   const LevelGeom& L = dg->lv[level];
   const LevelGeom& S = dg->lv[level - 1];
@@ -480,7 +383,7 @@ void build_pyr_plan(const ExtractorGeom& g, const std::vector<uint4>& wt, const 
   }
 }
 
-// host: per-word tables for k_pyr_resize_tab, levels 1..n-1 back to back; off[l] = first entry (in
+// host: per-word tables for k_pyr_resize_stage, levels 1..n-1 back to back; off[l] = first entry (in
 // uint4) of level l, or -1 when the level needs the byte-load kernel (window wider than 8 bytes)
 void build_resize_words(const ExtractorGeom& g, const std::vector<ResizeTap>& xtab, std::vector<uint4>& wt, int* off) {
   wt.clear();
@@ -529,8 +432,7 @@ void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8
     } else {
       // four adjacent output columns span 3*scale + 2 source bytes (+3 for alignment): 12 bytes up to scale 2
       const double sx = (double)g.lv[l - 1].w / L.w;
-      static const int staged = []() { const char* e = getenv("CUORB_PYR_STAGED"); return e ? atoi(e) : 1; }();
-      if (wtab && wtab_off[l] >= 0 && staged && plan && plan[l].tx > 0) {
+      if (wtab && wtab_off[l] >= 0 && plan && plan[l].tx > 0) {
         const PyrPlan& p = plan[l];
         PyrCols pc;
         for (int b = 0; b < PYR_MAX_COLBLOCKS; b++) { pc.xlo[b] = p.xlo[b]; pc.tw[b] = p.tw[b]; }
@@ -538,11 +440,6 @@ void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8
         // such launch rather than cached per process
         if (p.smem > 48 * 1024) cudaFuncSetAttribute(k_pyr_resize_stage, cudaFuncAttributeMaxDynamicSharedMemorySize, p.smem);
         k_pyr_resize_stage<<<dim3(p.nb, (L.h + PYR_RS - 1) / PYR_RS, n_img), p.tx, p.smem, st>>>(dg, l, pyr, wtab + wtab_off[l], ytab, PYR_RS, pc);
-      } else if (wtab && wtab_off[l] >= 0) {
-        // CTA width = the row's word count split evenly over whole warps
-        const int words = L.pitch / 4, nb = (words + PYR_TAB_TX - 1) / PYR_TAB_TX;
-        const int tx = (((words + nb - 1) / nb) + 31) / 32 * 32;
-        k_pyr_resize_tab<<<dim3((words + tx - 1) / tx, (L.h + PYR_RS - 1) / PYR_RS, n_img), tx, 0, st>>>(dg, l, pyr, wtab + wtab_off[l], ytab, PYR_RS);
       }
       else if (3.0 * sx + 5.0 < 11.5) k_pyr_resize<false><<<grid, PYR_TX, 0, st>>>(dg, l, pyr, xtab, ytab);
       else k_pyr_resize<true><<<grid, PYR_TX, 0, st>>>(dg, l, pyr, xtab, ytab);

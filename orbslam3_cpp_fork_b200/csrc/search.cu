@@ -277,23 +277,31 @@ int run_area(int device, const cuorb_frame_view* fv, AreaQuery Q, int32_t* resul
   Q.active = up(A, Q.active, m, st);
   int* binder[2] = {A.take<int>(n), A.take<int>(n)};
   int* result = A.take<int>(m);
-  int* changed = A.take<int>(1);
+  // rounds in batches, as in run_projection (project.cu): one host sync per batch; rounds past the fixed point are
+  // idempotent and simply run
+  constexpr int ROUND_BATCH = 6;
+  int* flag = A.take<int>(ROUND_BATCH);
   k_fill<<<(n + 255) / 256, 256, 0, st>>>(binder[0], n, NO_BINDER);
   k_fill<<<(m + 255) / 256, 256, 0, st>>>(result, m, -2);
   count_launch(2);
-  for (int rounds = 0;; rounds++) {
+  int rounds = 0;
+  for (bool converged = false; !converged;) {
     if (rounds > m + 2) { set_error("window search did not converge"); return CUORB_E_CUDA; }
-    int* prev = binder[rounds & 1];
-    int* next = binder[(rounds + 1) & 1];
-    k_fill<<<(n + 255) / 256, 256, 0, st>>>(next, n, NO_BINDER);
-    CUORB_CUDA_TRY(cudaMemsetAsync(changed, 0, sizeof(int), st));
-    k_area_round<<<(m + 7) / 8, 256, 0, st>>>(F, Q, prev, next, result, changed);
-    count_launch(2);
-    if (!Q.skip_bound) break;   // no query depends on another one: one pass is the answer
-    int h_changed = 0;
-    CUORB_CUDA_TRY(cudaMemcpyAsync(&h_changed, changed, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUORB_CUDA_TRY(cudaMemsetAsync(flag, 0, ROUND_BATCH * sizeof(int), st));
+    const int nb = Q.skip_bound ? ROUND_BATCH : 1;   // no query depends on another one: one pass is the answer
+    for (int k = 0; k < nb; k++, rounds++) {
+      int* prev = binder[rounds & 1];
+      int* next = binder[(rounds + 1) & 1];
+      k_fill<<<(n + 255) / 256, 256, 0, st>>>(next, n, NO_BINDER);
+      k_area_round<<<(m + 7) / 8, 256, 0, st>>>(F, Q, prev, next, result, flag + k);
+      count_launch(2);
+    }
+    if (!Q.skip_bound) break;
+    int h_flag[ROUND_BATCH];
+    CUORB_CUDA_TRY(cudaMemcpyAsync(h_flag, flag, sizeof(h_flag), cudaMemcpyDeviceToHost, st));
     CUORB_CUDA_TRY(cudaStreamSynchronize(st));
-    if (!h_changed) break;
+    for (int k = 0; k < ROUND_BATCH; k++)
+      if (!h_flag[k]) { converged = true; break; }
   }
   CUORB_CUDA_TRY(cudaMemcpyAsync(result_out, result, sizeof(int) * m, cudaMemcpyDeviceToHost, st));
   CUORB_CUDA_TRY(cudaStreamSynchronize(st));
