@@ -390,10 +390,15 @@ def run_cuorb(args):
         barrier()
         return ev0.elapsed_time(ev1), L_.cuorb_kernel_launch_count() - l0
 
+    # clocks / throttle reasons: rank 0's GPU, sampled every 20 ms over BOTH resident legs (one nvidia-smi process per
+    # job: eight of them starting at once deliver no sample inside a 165 ms leg)
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+        time.sleep(0.3)                  # nvidia-smi needs a moment before its first line
     ms_nod2h, _ = timed_resident(args.steps, False)
-    sampler = ClockSampler(local); sampler.start()
     ms_resident, launches = timed_resident(args.steps, True)
-    clocks = sampler.stop()
+    clocks = sampler.stop() if sampler else None
 
     # ---------------- per-stage times (one profiled step, CUDA events inside libcuorb) -------------
     eL.set_profiling(True); eR.set_profiling(True)
