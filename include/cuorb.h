@@ -171,6 +171,20 @@ int cuorb_stereo_match(cuorb_extractor* left, cuorb_extractor* right, int n_left
                        const cuorb_keypoint* kps_right, const uint8_t* desc_right, float mb,
                        float mbf, float* u_right, float* depth);
 
+/* Fused stereo frame: the stereo Frame constructor's three steps - ExtractORB(0, imLeft, 0, 0) and
+ * ExtractORB(1, imRight, 0, 0) on two threads (src/Frame.cc:202-205, 555-562) and ComputeStereoMatches()
+ * (src/Frame.cc:231, 944-1113) - as ONE call: both extractions are enqueued on the two handles' own streams, the
+ * association runs on the device on the resident keypoints / descriptors / pyramids (nothing is uploaded again) and
+ * each handle's results return in a single copy.  Both handles must have been created with max_batch == 1.  Host
+ * images (same size, `stride` bytes per row); lapping area {0, 0} as the reference's stereo constructor passes.
+ * kps_* / desc_*: `capacity` entries each; u_right / depth: `capacity` floats (mvuRight / mvDepth of the left
+ * keypoints, -1 where there is no match).  Results are bit-identical to cuorb_extract x 2 + cuorb_stereo_match.
+ * Returns the left monoIndex (>= 0) or a negative status. */
+int cuorb_extract_stereo(cuorb_extractor* left, cuorb_extractor* right, const uint8_t* img_left,
+                         const uint8_t* img_right, int width, int height, size_t stride, float mb, float mbf,
+                         cuorb_keypoint* kps_left, uint8_t* desc_left, int* n_left, cuorb_keypoint* kps_right,
+                         uint8_t* desc_right, int* n_right, int capacity, float* u_right, float* depth);
+
 /* ---- matcher: replaces the tracking-time subset of class ORB_SLAM3::ORBmatcher ---- */
 
 /* static int ORBmatcher::DescriptorDistance(const cv::Mat&, const cv::Mat&)

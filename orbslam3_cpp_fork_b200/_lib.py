@@ -87,6 +87,9 @@ SIGNATURES = {
     "cuorb_stereo_fetch_async": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
     "cuorb_stereo_match": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                      C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p]),
+    "cuorb_extract_stereo": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_float,
+                                      C.c_float, C.c_void_p, C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.c_void_p,
+                                      C.POINTER(C.c_int), C.c_int, C.c_void_p, C.c_void_p]),
     "cuorb_hamming256": (C.c_int, [C.c_void_p, C.c_void_p]),
     "cuorb_hamming_batch": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p,
                                       C.c_void_p, C.c_int, C.c_void_p]),

@@ -72,6 +72,11 @@ struct cuorb_extractor {
   size_t cap_xtab = 0, cap_ytab = 0, cap_tiles = 0, cap_cells = 0;
   int    n_img = 0;       // images in the last batch
   int    fetch_n = 0, fetch_capacity = 0;   // last fetch: images copied to h_out_n / caller capacity (0: no kps/desc asked)
+  // d_flags, d_out_n, d_out_mono, d_out_kps, d_out_desc, d_uright, d_depth are views into ONE allocation (d_pack), in that order:
+  // a handle made for one image at a time (max_batch == 1, what the SLAM drop-in creates) fetches everything a
+  // frame produces with a single D2H into the pinned mirror h_pack
+  uint8_t *d_pack = nullptr, *h_pack = nullptr;
+  size_t   pack_bytes = 0, pack_n_off = 0, pack_mono_off = 0, pack_kps_off = 0, pack_desc_off = 0, pack_ur_off = 0, pack_depth_off = 0;
   bool   have_batch = false, have_stereo = false;
 };
 
@@ -239,11 +244,10 @@ static cudaError_t dev_alloc(T** p, size_t count) {
 static void free_all(cuorb_extractor* e) {
   cudaSetDevice(e->cfg.device);
   void* dev[] = {e->d_geom, e->d_xtab, e->d_ytab, e->d_wtab, e->d_blur_tiles, e->d_fast_cells, e->d_fast_recs, e->d_input, e->d_pyr, e->d_blur,
-                 e->d_cand, e->d_cand_scratch, e->d_cand_count, e->d_key_count, e->d_flags, e->d_slot,
-                 e->d_keys, e->d_out_kps, e->d_out_desc, e->d_out_n, e->d_out_mono, e->d_uright,
-                 e->d_depth, e->d_sad, e->d_best_idx, e->d_best_dist, e->d_rtab, e->d_rstart};
+                 e->d_cand, e->d_cand_scratch, e->d_cand_count, e->d_key_count, e->d_pack, e->d_slot,
+                 e->d_keys, e->d_sad, e->d_best_idx, e->d_best_dist, e->d_rtab, e->d_rstart};
   for (void* p : dev) if (p) cudaFree(p);
-  void* host[] = {e->h_out_n, e->h_out_mono, e->h_flags};
+  void* host[] = {e->h_out_n, e->h_out_mono, e->h_flags, e->h_pack};
   for (void* p : host) if (p) cudaFreeHost(p);
   for (auto& ev : e->ev_stage) if (ev) cudaEventDestroy(ev);
   if (e->ev_done) cudaEventDestroy(e->ev_done);
@@ -398,15 +402,30 @@ cuorb_extractor* cuorb_extractor_create(const cuorb_config* cfg) {
   ok &= dev_alloc(&e->d_cand_scratch, 2 * e->cap_cand) == cudaSuccess;
   ok &= dev_alloc(&e->d_cand_count, nb * MAX_LEVELS) == cudaSuccess;
   ok &= dev_alloc(&e->d_key_count, nb * MAX_LEVELS) == cudaSuccess;
-  ok &= dev_alloc(&e->d_flags, 2) == cudaSuccess;
   ok &= dev_alloc(&e->d_slot, e->cap_kp) == cudaSuccess;
   ok &= dev_alloc(&e->d_keys, e->cap_keys) == cudaSuccess;
-  ok &= dev_alloc(&e->d_out_kps, e->cap_kp) == cudaSuccess;
-  ok &= dev_alloc(&e->d_out_desc, e->cap_kp * 32) == cudaSuccess;
-  ok &= dev_alloc(&e->d_out_n, nb) == cudaSuccess;
-  ok &= dev_alloc(&e->d_out_mono, nb) == cudaSuccess;
-  ok &= dev_alloc(&e->d_uright, e->cap_kp) == cudaSuccess;
-  ok &= dev_alloc(&e->d_depth, e->cap_kp) == cudaSuccess;
+  {
+    // result pack: [flags (2 ints) | n[nb] | mono[nb] | kps[cap_kp] | desc[cap_kp * 32] | uRight[cap_kp] | depth[cap_kp]],
+    // sections 256-byte aligned
+    e->pack_n_off    = 256;
+    e->pack_mono_off = e->pack_n_off + align_up(nb * sizeof(int), 256);
+    e->pack_kps_off  = e->pack_mono_off + align_up(nb * sizeof(int), 256);
+    e->pack_desc_off = e->pack_kps_off + align_up(e->cap_kp * sizeof(cuorb_keypoint), 256);
+    e->pack_ur_off   = e->pack_desc_off + align_up(e->cap_kp * 32, 256);
+    e->pack_depth_off = e->pack_ur_off + align_up(e->cap_kp * sizeof(float), 256);
+    e->pack_bytes    = e->pack_depth_off + align_up(e->cap_kp * sizeof(float), 256);
+    ok &= dev_alloc(&e->d_pack, e->pack_bytes) == cudaSuccess;
+    if (ok) {
+      e->d_flags    = (int*)e->d_pack;
+      e->d_out_n    = (int*)(e->d_pack + e->pack_n_off);
+      e->d_out_mono = (int*)(e->d_pack + e->pack_mono_off);
+      e->d_out_kps  = (cuorb_keypoint*)(e->d_pack + e->pack_kps_off);
+      e->d_out_desc = e->d_pack + e->pack_desc_off;
+      e->d_uright   = (float*)(e->d_pack + e->pack_ur_off);
+      e->d_depth    = (float*)(e->d_pack + e->pack_depth_off);
+    }
+    if (nb == 1) ok &= cudaMallocHost((void**)&e->h_pack, e->pack_bytes) == cudaSuccess;
+  }
   ok &= dev_alloc(&e->d_sad, e->cap_kp) == cudaSuccess;
   ok &= dev_alloc(&e->d_best_idx, e->cap_kp) == cudaSuccess;
   ok &= dev_alloc(&e->d_rtab, e->cap_kp) == cudaSuccess;
@@ -759,6 +778,26 @@ int cuorb_extract(cuorb_extractor* e, const uint8_t* img, int width, int height,
                   int lap0, int lap1, cuorb_keypoint* kps, uint8_t* desc, int capacity, int* n_out) {
   int rc = cuorb_extract_batch_async(e, 1, img, width, height, stride, stride * (size_t)height, CUORB_MEM_HOST, lap0, lap1);
   if (rc != CUORB_OK) return rc;
+  if (e->h_pack) {
+    // one-image handle: flags, count, monoIndex, keypoints and descriptors come back in ONE copy into the pinned
+    // mirror (62 KB at 1000 features) and are handed to the caller's buffers from there, instead of seven separate
+    // copies, four of them staged through pageable memory
+    const int cap = e->g.kp_cap;
+    const size_t bytes = e->pack_desc_off + (size_t)cap * 32;
+    CUORB_CUDA_TRY(cudaMemcpyAsync(e->h_pack, e->d_pack, bytes, cudaMemcpyDeviceToHost, e->stream));
+    CUORB_CUDA_TRY(cudaStreamSynchronize(e->stream));
+    const int n1 = *(const int*)(e->h_pack + e->pack_n_off), mono1 = *(const int*)(e->h_pack + e->pack_mono_off);
+    *e->h_flags = *(const int*)e->h_pack;
+    e->h_out_n[0] = n1; e->h_out_mono[0] = mono1;
+    e->fetch_n = 1; e->fetch_capacity = (kps || desc) ? capacity : 0;
+    if (n_out) *n_out = n1;
+    rc = check_flags(e);
+    if (rc != CUORB_OK) return rc;
+    if ((kps || desc) && n1 > capacity) { set_error("caller capacity smaller than the keypoint count"); return CUORB_E_CAPACITY; }
+    if (kps && n1 > 0) memcpy(kps, e->h_pack + e->pack_kps_off, sizeof(cuorb_keypoint) * (size_t)n1);
+    if (desc && n1 > 0) memcpy(desc, e->h_pack + e->pack_desc_off, 32 * (size_t)n1);
+    return mono1;
+  }
   int32_t n = 0, mono = 0;
   rc = cuorb_extract_fetch(e, kps, desc, capacity, &n, &mono);
   if (n_out) *n_out = n;
@@ -926,6 +965,59 @@ int cuorb_stereo_match(cuorb_extractor* l, cuorb_extractor* r, int n_left, const
     rc = cuorb_sync(l);
   }
   return rc;
+}
+
+// Fused stereo frame (SURVEY 8b "fused cuorb_extract_stereo"): what the stereo Frame constructor does in three
+// steps - two ExtractORB threads (src/Frame.cc:202-205, lapping {0,0}) and ComputeStereoMatches (:231) - as one call.
+// Both extractions are enqueued on their handles' own streams, the association runs on the device on the resident
+// keypoints / descriptors / pyramids (nothing is re-uploaded), and each handle's results come back in one copy.
+int cuorb_extract_stereo(cuorb_extractor* l, cuorb_extractor* r, const uint8_t* img_left, const uint8_t* img_right,
+                         int width, int height, size_t stride, float mb, float mbf, cuorb_keypoint* kps_left,
+                         uint8_t* desc_left, int* n_left, cuorb_keypoint* kps_right, uint8_t* desc_right, int* n_right,
+                         int capacity, float* u_right, float* depth) {
+  if (!l || !r || l == r) { set_error("cuorb_extract_stereo: two distinct handles needed"); return CUORB_E_BADARG; }
+  if (!l->h_pack || !r->h_pack) { set_error("cuorb_extract_stereo: both handles must be created with max_batch == 1"); return CUORB_E_BADARG; }
+  if (!kps_left || !desc_left || !kps_right || !desc_right || !n_left || !n_right || !u_right || !depth || capacity <= 0) {
+    set_error("cuorb_extract_stereo: null output"); return CUORB_E_BADARG;
+  }
+  int rc = cuorb_extract_batch_async(l, 1, img_left, width, height, stride, stride * (size_t)height, CUORB_MEM_HOST, 0, 0);
+  if (rc != CUORB_OK) return rc;
+  rc = cuorb_extract_batch_async(r, 1, img_right, width, height, stride, stride * (size_t)height, CUORB_MEM_HOST, 0, 0);
+  if (rc != CUORB_OK) return rc;
+  // the right handle's results are complete at its ev_done: fetch them on its own stream, beside the match
+  const size_t rbytes = r->pack_desc_off + (size_t)r->g.kp_cap * 32;
+  CUORB_CUDA_TRY(cudaMemcpyAsync(r->h_pack, r->d_pack, rbytes, cudaMemcpyDeviceToHost, r->stream));
+  rc = cuorb_stereo_match_batch_async(l, r, mb, mbf);          // on l's stream, after r's ev_done
+  if (rc != CUORB_OK) return rc;
+  const size_t lbytes = l->pack_depth_off + (size_t)l->g.kp_cap * sizeof(float);
+  CUORB_CUDA_TRY(cudaMemcpyAsync(l->h_pack, l->d_pack, lbytes, cudaMemcpyDeviceToHost, l->stream));
+  CUORB_CUDA_TRY(cudaStreamSynchronize(r->stream));
+  CUORB_CUDA_TRY(cudaStreamSynchronize(l->stream));
+  cuorb_extractor* hs[2] = {l, r};
+  cuorb_keypoint* ko[2] = {kps_left, kps_right};
+  uint8_t* dd[2] = {desc_left, desc_right};
+  int* no[2] = {n_left, n_right};
+  for (int k = 0; k < 2; k++) {
+    cuorb_extractor* e = hs[k];
+    const int n1 = *(const int*)(e->h_pack + e->pack_n_off);
+    *e->h_flags = *(const int*)e->h_pack;
+    e->h_out_n[0] = n1; e->h_out_mono[0] = *(const int*)(e->h_pack + e->pack_mono_off);
+    e->fetch_n = 1; e->fetch_capacity = capacity;
+    *no[k] = n1;
+    rc = check_flags(e);
+    if (rc != CUORB_OK) return rc;
+    if (n1 > capacity) { set_error("caller capacity smaller than the keypoint count"); return CUORB_E_CAPACITY; }
+    if (n1 > 0) {
+      memcpy(ko[k], e->h_pack + e->pack_kps_off, sizeof(cuorb_keypoint) * (size_t)n1);
+      memcpy(dd[k], e->h_pack + e->pack_desc_off, 32 * (size_t)n1);
+    }
+  }
+  const int nl = *n_left;
+  if (nl > 0) {
+    memcpy(u_right, l->h_pack + l->pack_ur_off, sizeof(float) * (size_t)nl);
+    memcpy(depth, l->h_pack + l->pack_depth_off, sizeof(float) * (size_t)nl);
+  }
+  return l->h_out_mono[0];
 }
 
 int cuorb_stage_ms(cuorb_extractor* e, float* ms_out) {

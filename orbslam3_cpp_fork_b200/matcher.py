@@ -137,6 +137,26 @@ class ORBmatcher:
                                          len(kr), ptr(kr), ptr(dr), mb, mbf, ptr(u), ptr(d)))
         return u, d
 
+    def ExtractStereo(self, extractorLeft, extractorRight, imLeft, imRight, mb, mbf):
+        """The stereo Frame constructor's three steps as ONE call (cuorb_extract_stereo): ExtractORB on both eyes
+        (src/Frame.cc:202-205) + ComputeStereoMatches (:231).  Both extractors must have max_batch == 1.
+        Returns (monoIndexLeft, mvKeys, mDescriptors, mvKeysRight, mDescriptorsRight, mvuRight, mvDepth)."""
+        imL = np.ascontiguousarray(imLeft, np.uint8); imR = np.ascontiguousarray(imRight, np.uint8)
+        if imL.shape != imR.shape or imL.ndim != 2:
+            raise ValueError("imLeft / imRight must be two 8-bit single-channel images of one size")
+        h, w = imL.shape
+        cap = extractorLeft.capacity
+        kl = np.zeros(cap, KP_DTYPE); kr = np.zeros(cap, KP_DTYPE)
+        dl = np.zeros((cap, 32), np.uint8); dr = np.zeros((cap, 32), np.uint8)
+        u = np.zeros(cap, np.float32); d = np.zeros(cap, np.float32)
+        nl, nr = C.c_int(0), C.c_int(0)
+        mono = check(self._L.cuorb_extract_stereo(extractorLeft.handle, extractorRight.handle, ptr(imL), ptr(imR), w, h, w,
+                                                  mb, mbf, ptr(kl), ptr(dl), C.byref(nl), ptr(kr), ptr(dr), C.byref(nr), cap,
+                                                  ptr(u), ptr(d)))
+        extractorLeft._n_last = extractorRight._n_last = 1
+        return (mono, kl[:nl.value].copy(), dl[:nl.value].copy(), kr[:nr.value].copy(), dr[:nr.value].copy(),
+                u[:nl.value].copy(), d[:nl.value].copy())
+
     # int SearchByProjection(Frame&, const vector<MapPoint*>&, th, bFarPoints, thFarPoints)
     def SearchByProjection(self, F: Frame, mps: MapPointSoA, th=3.0, bFarPoints=False, thFarPoints=50.0):
         fv, keep = F.view()

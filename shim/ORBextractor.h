@@ -90,6 +90,7 @@ public:
   }
 
   cuorb_extractor* handle() const { return h_; }  // for ORBmatcher / Frame::ComputeStereoMatches
+  void InvalidateImagePyramid() { pyramid_stale_ = true; }   // after an extraction that bypassed operator()
 
 protected:
   int    nfeatures;

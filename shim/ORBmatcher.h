@@ -47,6 +47,37 @@ public:
                                       contiguous(F.mDescriptorsRight), F.mb, F.mbf, F.mvuRight.data(), F.mvDepth.data());
     if (rc < 0) throw std::runtime_error(std::string("ComputeStereoMatches (libcuorb): ") + cuorb_last_error());
   }
+  // The stereo Frame constructor's three steps in ONE library call (optional, for latency): what
+  //   thread threadLeft(&Frame::ExtractORB, this, 0, imLeft, 0, 0); thread threadRight(&Frame::ExtractORB, this, 1,
+  //   imRight, 0, 0); ... join ...; ComputeStereoMatches();            (src/Frame.cc:202-205, 231)
+  // leaves in mvKeys, mDescriptors, mvKeysRight, mDescriptorsRight, mvuRight, mvDepth - bit-identical - without
+  // sending the keypoints and descriptors back to the device for the association.  Returns the left monoIndex.
+  template <class FrameT>
+  static int ExtractStereo(FrameT& F, ORBextractor& left, ORBextractor& right, const cv::Mat& imLeft, const cv::Mat& imRight) {
+    if (imLeft.empty() || imRight.empty() || imLeft.rows != imRight.rows || imLeft.cols != imRight.cols || imLeft.step != imRight.step)
+      throw std::invalid_argument("ExtractStereo: two CV_8UC1 images of one size and row step needed");
+    const int cap = cuorb_extractor_capacity(left.handle());
+    std::vector<cv::KeyPoint> kl(cap), kr(cap);
+    cv::Mat dl(cap, 32, CV_8U), dr(cap, 32, CV_8U);
+    std::vector<float> u(cap), d(cap);
+    int nl = 0, nr = 0;
+    const int mono = cuorb_extract_stereo(left.handle(), right.handle(), imLeft.data, imRight.data, imLeft.cols, imLeft.rows,
+                                          imLeft.step, F.mb, F.mbf, (cuorb_keypoint*)kl.data(), dl.data, &nl,
+                                          (cuorb_keypoint*)kr.data(), dr.data, &nr, cap, u.data(), d.data());
+    if (mono < 0) throw std::runtime_error(std::string("ExtractStereo (libcuorb): ") + cuorb_last_error());
+    kl.resize(nl); kr.resize(nr);
+    F.mvKeys.swap(kl); F.mvKeysRight.swap(kr);
+    auto rows = [](const cv::Mat& src, int n, cv::Mat& dst) {
+      if (n == 0) { dst.release(); return; }
+      dst.create(n, 32, CV_8U);
+      for (int i = 0; i < n; i++) std::memcpy(dst.ptr<unsigned char>(i), src.ptr<unsigned char>(i), 32);
+    };
+    rows(dl, nl, F.mDescriptors); rows(dr, nr, F.mDescriptorsRight);
+    F.mvuRight.assign(u.begin(), u.begin() + nl);
+    F.mvDepth.assign(d.begin(), d.begin() + nl);
+    left.InvalidateImagePyramid(); right.InvalidateImagePyramid();
+    return mono;
+  }
   // the name BASELINE.json uses for the same operation
   template <class FrameT>
   static void SearchStereo(FrameT& F, ORBextractor& left, ORBextractor& right) { ComputeStereoMatches(F, left, right); }

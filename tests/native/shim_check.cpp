@@ -4,6 +4,7 @@
 // oracle.  usage: shim_check left.raw right.raw w h nfeatures mb mbf out.bin
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 
 #include "../../shim/ORBextractor.h"
@@ -42,6 +43,20 @@ int main(int argc, char** argv) {
   std::vector<cv::KeyPoint> again; cv::Mat dagain;
   if (exL(imL, cv::Mat(), again, dagain, lap) != monoL || again.size() != F.mvKeys.size()) return 4;
   ORB_SLAM3::ORBmatcher::ComputeStereoMatches(F, exL, exR);
+  {  // the fused call leaves exactly what the three steps left
+    MiniFrame G;
+    G.mb = F.mb; G.mbf = F.mbf;
+    const int monoG = ORB_SLAM3::ORBmatcher::ExtractStereo(G, exL, exR, imL, imR);
+    bool same = monoG == monoL && G.mvKeys.size() == F.mvKeys.size() && G.mvKeysRight.size() == F.mvKeysRight.size() &&
+                G.mvuRight.size() == F.mvuRight.size();
+    same = same && memcmp(G.mvKeys.data(), F.mvKeys.data(), sizeof(cv::KeyPoint) * F.mvKeys.size()) == 0;
+    same = same && memcmp(G.mvKeysRight.data(), F.mvKeysRight.data(), sizeof(cv::KeyPoint) * F.mvKeysRight.size()) == 0;
+    for (size_t i = 0; same && i < F.mvKeys.size(); i++) same = memcmp(G.mDescriptors.ptr<unsigned char>((int)i), F.mDescriptors.ptr<unsigned char>((int)i), 32) == 0;
+    for (size_t i = 0; same && i < F.mvKeysRight.size(); i++) same = memcmp(G.mDescriptorsRight.ptr<unsigned char>((int)i), F.mDescriptorsRight.ptr<unsigned char>((int)i), 32) == 0;
+    same = same && memcmp(G.mvuRight.data(), F.mvuRight.data(), 4 * F.mvuRight.size()) == 0 &&
+           memcmp(G.mvDepth.data(), F.mvDepth.data(), 4 * F.mvDepth.size()) == 0;
+    if (!same) { fprintf(stderr, "ExtractStereo differs from ExtractORB x2 + ComputeStereoMatches\n"); return 6; }
+  }
   exL.SyncImagePyramid();
   int selfdist = ORB_SLAM3::ORBmatcher::DescriptorDistance(F.mDescriptors.row(0), F.mDescriptors.row(0));
   int d01 = F.mvKeys.size() > 1 ? ORB_SLAM3::ORBmatcher::DescriptorDistance(F.mDescriptors.row(0), F.mDescriptors.row(1)) : 0;

@@ -275,3 +275,55 @@ def test_kernel_variants_subprocess(cu, env_over):
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "variant ok" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.parametrize("w,h,nf,seed,fx,mbf", [(752, 480, 1000, 11, 458.654, 47.906), (1241, 376, 2000, 12, 718.856, 386.1448)])
+def test_fused_stereo_frame(cu, w, h, nf, seed, fx, mbf):
+    """cuorb_extract_stereo (one call = ExtractORB x 2 + ComputeStereoMatches) against the oracle, twice in a
+    row on one handle pair (the packed result buffer is reused), then a black right image (no right keypoints)."""
+    L, R = synth.synth_stereo_pair(w, h, seed)
+    eL = cu.ORBextractor(nf, max_width=w, max_height=h, max_batch=1)
+    eR = cu.ORBextractor(nf, max_width=w, max_height=h, max_batch=1)
+    mb = mbf / fx
+    oL, oR = op.OracleExtractor(nf), op.OracleExtractor(nf)
+    m = cu.ORBmatcher()
+    for rep, (a, b) in enumerate(((L, R), (R, L), (L, R))):
+        mono, kl, dl, kr, dr, u, d = m.ExtractStereo(eL, eR, a, b, mb, mbf)
+        m0, k0, d0 = oL.extract(a); m1, k1, d1 = oR.extract(b)
+        assert mono == m0
+        assert_extract_equal(kl, dl, k0, d0)
+        assert_extract_equal(kr, dr, k1, d1)
+        so = op.stereo(oL, oR, k0, d0, k1, d1, mb, mbf)
+        assert u.tobytes() == so["u_right"].tobytes() and d.tobytes() == so["depth"].tobytes(), rep
+    assert (u >= 0).sum() > 100
+    mono, kl, dl, kr, dr, u, d = m.ExtractStereo(eL, eR, L, np.zeros_like(L), mb, mbf)
+    assert len(kr) == 0 and len(kl) == len(k0) and (u == -1).all() and (d == -1).all()
+    # handles made for batches cannot use the fused call
+    eB = cu.ORBextractor(nf, max_width=w, max_height=h, max_batch=2)
+    with pytest.raises(cu.CuorbError):
+        m.ExtractStereo(eB, eR, L, R, mb, mbf)
+
+
+def test_single_image_handle_packed_fetch(cu):
+    """cuorb_extract on a max_batch == 1 handle fetches through one packed copy: same results as a batch handle,
+    counts still written and CUORB_E_CAPACITY returned when the caller's arrays are too small, empty frame -> n = 0."""
+    import ctypes as C
+    from orbslam3_cpp_fork_b200 import _lib
+    w, h = 640, 480
+    img = synth.synth_image(w, h, 51)
+    e1 = cu.ORBextractor(1000, max_width=w, max_height=h, max_batch=1)
+    e4 = cu.ORBextractor(1000, max_width=w, max_height=h, max_batch=4)
+    a = e1(img, None, (100, 300)); b = e4(img, None, (100, 300))
+    assert a[0] == b[0] and a[1].tobytes() == b[1].tobytes() and (a[2] == b[2]).all()
+    mo, ko, do = op.OracleExtractor(1000).extract(img, (100, 300))
+    assert a[0] == mo
+    assert_extract_equal(a[1], a[2], ko, do)
+    L_ = cu.load()
+    small = 100
+    kps = np.zeros(small, _lib.KP_DTYPE); desc = np.zeros((small, 32), np.uint8); n = C.c_int(0)
+    rc = L_.cuorb_extract(e1.handle, _lib.ptr(img), w, h, w, 0, 0, _lib.ptr(kps), _lib.ptr(desc), small, C.byref(n))
+    assert rc == _lib.E_CAPACITY and n.value == len(ko)
+    mono, k, d = e1(np.zeros((h, w), np.uint8))
+    assert mono == 0 and len(k) == 0 and d.shape == (0, 32)
+    a2 = e1(img, None, (100, 300))
+    assert a2[1].tobytes() == a[1].tobytes() and (a2[2] == a[2]).all()
