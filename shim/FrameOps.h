@@ -27,7 +27,7 @@ void UndistortKeyPoints(FrameT& F, int device = 0) {
   for (int i = 0; i < 5 && i < nd; i++) d5[i] = F.mDistCoef.rows > 1 ? F.mDistCoef.template at<float>(i, 0) : F.mDistCoef.template at<float>(0, i);
   const int rc = cuorb_undistort_keypoints(device, (int)F.mvKeys.size(), (const cuorb_keypoint*)F.mvKeys.data(), K4, d5,
                                            (cuorb_keypoint*)F.mvKeysUn.data());
-  if (rc < 0) throw std::runtime_error(std::string("UndistortKeyPoints (libcuorb): ") + cuorb_last_error());
+  if (rc < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("UndistortKeyPoints (libcuorb): ") + cuorb_last_error());
 }
 
 // reads F.mvKeys, F.mvKeysUn, F.mbf and imDepth (CV_32F); writes F.mvuRight, F.mvDepth
@@ -37,11 +37,11 @@ void ComputeStereoFromRGBD(FrameT& F, const cv::Mat& imDepth, int device = 0) {
   F.mvuRight.assign(n, -1.0f);
   F.mvDepth.assign(n, -1.0f);
   if (n == 0) return;
-  if (imDepth.type() != CV_32F) throw std::invalid_argument("ComputeStereoFromRGBD: imDepth must be CV_32F");
+  if (imDepth.type() != CV_32F) CUORB_SHIM_FAIL(std::invalid_argument, "ComputeStereoFromRGBD: imDepth must be CV_32F");
   const int rc = cuorb_stereo_from_rgbd(device, n, (const cuorb_keypoint*)F.mvKeys.data(), (const cuorb_keypoint*)F.mvKeysUn.data(),
                                         imDepth.template ptr<float>(0), imDepth.cols, imDepth.rows, imDepth.step, CUORB_MEM_HOST,
                                         F.mbf, F.mvuRight.data(), F.mvDepth.data());
-  if (rc < 0) throw std::runtime_error(std::string("ComputeStereoFromRGBD (libcuorb): ") + cuorb_last_error());
+  if (rc < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("ComputeStereoFromRGBD (libcuorb): ") + cuorb_last_error());
 }
 
 }  // namespace ORB_SLAM3
@@ -58,12 +58,12 @@ inline void FisheyeStereoCandidates(const cv::Mat& stereoDescLeft, const cv::Mat
   accepted.assign(stereoDescLeft.rows, -1);
   if (stereoDescLeft.rows == 0 || stereoDescRight.rows == 0) return;
   if ((stereoDescLeft.rows > 1 && stereoDescLeft.step != 32) || (stereoDescRight.rows > 1 && stereoDescRight.step != 32))
-    throw std::invalid_argument("FisheyeStereoCandidates: descriptor matrices must be n x 32 contiguous");
+    CUORB_SHIM_FAIL(std::invalid_argument, "FisheyeStereoCandidates: descriptor matrices must be n x 32 contiguous");
   const int32_t qo[2] = {0, stereoDescLeft.rows}, to[2] = {0, stereoDescRight.rows};
   std::vector<int32_t> idx(2 * (size_t)stereoDescLeft.rows), dist(idx.size());
   const int rc = cuorb_knn_match2(device, 1, qo, stereoDescLeft.ptr<unsigned char>(0), to, stereoDescRight.ptr<unsigned char>(0),
                                   idx.data(), dist.data(), accepted.data());
-  if (rc < 0) throw std::runtime_error(std::string("FisheyeStereoCandidates (libcuorb): ") + cuorb_last_error());
+  if (rc < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("FisheyeStereoCandidates (libcuorb): ") + cuorb_last_error());
 }
 
 // void MapPoint::ComputeDistinctiveDescriptors() (src/MapPoint.cc:376-450) for a batch of MapPoints
@@ -79,7 +79,7 @@ inline std::vector<int> DistinctiveDescriptorIndices(const std::vector<std::vect
   std::vector<int> best(vDescriptors.size(), -1);
   if (vDescriptors.empty()) return best;
   const int rc = cuorb_distinctive_descriptors(device, (int)vDescriptors.size(), off.data(), flat.data(), best.data());
-  if (rc < 0) throw std::runtime_error(std::string("DistinctiveDescriptorIndices (libcuorb): ") + cuorb_last_error());
+  if (rc < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("DistinctiveDescriptorIndices (libcuorb): ") + cuorb_last_error(), std::vector<int>());
   return best;
 }
 

@@ -49,14 +49,14 @@ public:
                  cv::OutputArray _descriptors, std::vector<int>& vLappingArea) {
     if (_image.empty()) return -1;
     cv::Mat image = _image.getMat();
-    if (image.type() != CV_8UC1) throw std::invalid_argument("ORBextractor: image must be CV_8UC1");
+    if (image.type() != CV_8UC1) CUORB_SHIM_FAIL(std::invalid_argument, "ORBextractor: image must be CV_8UC1", -1);
     const int lap0 = vLappingArea.size() > 0 ? vLappingArea[0] : 0;
     const int lap1 = vLappingArea.size() > 1 ? vLappingArea[1] : 0;
     desc_buf_.create(capacity_, 32, CV_8U);
     int n = 0;
     const int mono = cuorb_extract(h_, image.data, image.cols, image.rows, image.step, lap0, lap1,
                                    kp_buf_.data(), desc_buf_.data, capacity_, &n);
-    if (mono < 0) throw std::runtime_error(std::string("ORBextractor (libcuorb): ") + cuorb_last_error());
+    if (mono < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("ORBextractor (libcuorb): ") + cuorb_last_error(), -1);
     pyramid_stale_ = true;
     static_assert(sizeof(cv::KeyPoint) == sizeof(cuorb_keypoint), "cv::KeyPoint must be 7 x 4 bytes");
     _keypoints.resize(n);

@@ -45,7 +45,7 @@ public:
     const int rc = cuorb_stereo_match(left.handle(), right.handle(), N, (const cuorb_keypoint*)F.mvKeys.data(),
                                       contiguous(F.mDescriptors), Nr, (const cuorb_keypoint*)F.mvKeysRight.data(),
                                       contiguous(F.mDescriptorsRight), F.mb, F.mbf, F.mvuRight.data(), F.mvDepth.data());
-    if (rc < 0) throw std::runtime_error(std::string("ComputeStereoMatches (libcuorb): ") + cuorb_last_error());
+    if (rc < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("ComputeStereoMatches (libcuorb): ") + cuorb_last_error());
   }
   // The stereo Frame constructor's three steps in ONE library call (optional, for latency): what
   //   thread threadLeft(&Frame::ExtractORB, this, 0, imLeft, 0, 0); thread threadRight(&Frame::ExtractORB, this, 1,
@@ -55,7 +55,7 @@ public:
   template <class FrameT>
   static int ExtractStereo(FrameT& F, ORBextractor& left, ORBextractor& right, const cv::Mat& imLeft, const cv::Mat& imRight) {
     if (imLeft.empty() || imRight.empty() || imLeft.rows != imRight.rows || imLeft.cols != imRight.cols || imLeft.step != imRight.step)
-      throw std::invalid_argument("ExtractStereo: two CV_8UC1 images of one size and row step needed");
+      CUORB_SHIM_FAIL(std::invalid_argument, "ExtractStereo: two CV_8UC1 images of one size and row step needed", -1);
     const int cap = cuorb_extractor_capacity(left.handle());
     std::vector<cv::KeyPoint> kl(cap), kr(cap);
     cv::Mat dl(cap, 32, CV_8U), dr(cap, 32, CV_8U);
@@ -64,7 +64,7 @@ public:
     const int mono = cuorb_extract_stereo(left.handle(), right.handle(), imLeft.data, imRight.data, imLeft.cols, imLeft.rows,
                                           imLeft.step, F.mb, F.mbf, (cuorb_keypoint*)kl.data(), dl.data, &nl,
                                           (cuorb_keypoint*)kr.data(), dr.data, &nr, cap, u.data(), d.data());
-    if (mono < 0) throw std::runtime_error(std::string("ExtractStereo (libcuorb): ") + cuorb_last_error());
+    if (mono < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("ExtractStereo (libcuorb): ") + cuorb_last_error(), -1);
     kl.resize(nl); kr.resize(nr);
     F.mvKeys.swap(kl); F.mvKeysRight.swap(kr);
     auto rows = [](const cv::Mat& src, int n, cv::Mat& dst) {
@@ -87,7 +87,7 @@ public:
   template <class FrameT, class MapPointT>
   int SearchByProjection(FrameT& F, const std::vector<MapPointT*>& vpMapPoints, const float th = 3,
                          const bool bFarPoints = false, const float thFarPoints = 50.0f) {
-    if (F.Nleft != -1) throw std::runtime_error("ORBmatcher shim: fisheye (Nleft != -1) branch is not built");
+    if (F.Nleft != -1) CUORB_SHIM_FAIL(std::runtime_error, "ORBmatcher shim: fisheye (Nleft != -1) branch is not built", 0);
     const int M = (int)vpMapPoints.size();
     if (M == 0 || F.N == 0) return 0;
     std::vector<uint8_t> desc((size_t)M * 32), flags(M);
@@ -107,7 +107,7 @@ public:
     const int n = cuorb_search_by_projection(device_, &fv, M, desc.data(), px.data(), py.data(), pxr.data(), lvl.data(),
                                              vc.data(), dep.data(), flags.data(), th, bFarPoints ? 1 : 0, thFarPoints,
                                              mfNNratio, best.data());
-    if (n < 0) throw std::runtime_error(std::string("SearchByProjection (libcuorb): ") + cuorb_last_error());
+    if (n < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("SearchByProjection (libcuorb): ") + cuorb_last_error(), 0);
     for (int i = 0; i < M; i++)
       if (best[i] >= 0) F.mvpMapPoints[best[i]] = vpMapPoints[i];  // :138, in MapPoint order
     return n;
@@ -123,7 +123,7 @@ public:
   template <class FrameT>
   int SearchByProjection(FrameT& CurrentFrame, const FrameT& LastFrame, const float th, const bool bMono) {
     if (CurrentFrame.Nleft != -1 || LastFrame.Nleft != -1)
-      throw std::runtime_error("ORBmatcher shim: fisheye (Nleft != -1) branch is not built");
+      CUORB_SHIM_FAIL(std::runtime_error, "ORBmatcher shim: fisheye (Nleft != -1) branch is not built", 0);
     const int NL = LastFrame.N;
     if (NL == 0 || CurrentFrame.N == 0) return 0;
     const auto Tcw = CurrentFrame.GetPose();                         // :1696
@@ -156,7 +156,7 @@ public:
     const int n = cuorb_search_by_projection_frame(device_, &fv, NL, desc.data(), u.data(), v.data(), invz.data(), oct.data(),
                                                    ang.data(), flags.data(), th, bForward ? 1 : 0, bBackward ? 1 : 0,
                                                    mbCheckOrientation ? 1 : 0, best.data(), bin.data(), keep);
-    if (n < 0) throw std::runtime_error(std::string("SearchByProjection(Cur, Last) (libcuorb): ") + cuorb_last_error());
+    if (n < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("SearchByProjection(Cur, Last) (libcuorb): ") + cuorb_last_error(), 0);
     for (int i = 0; i < NL; i++)                                     // :1786, in last-frame order
       if (best[i] >= 0) CurrentFrame.mvpMapPoints[best[i]] = LastFrame.mvpMapPoints[i];
     if (mbCheckOrientation)                                          // :1889-1905
@@ -171,7 +171,7 @@ public:
   // pKF->mFeatVec, pKF->mDescriptors, pKF->mvKeysUn, F.mFeatVec, F.mDescriptors, F.mvKeys, F.N.
   template <class KeyFrameT, class FrameT, class MapPointT>
   int SearchByBoW(KeyFrameT* pKF, FrameT& F, std::vector<MapPointT*>& vpMapPointMatches) {
-    if (F.Nleft != -1) throw std::runtime_error("ORBmatcher shim: fisheye (Nleft != -1) branch is not built");
+    if (F.Nleft != -1) CUORB_SHIM_FAIL(std::runtime_error, "ORBmatcher shim: fisheye (Nleft != -1) branch is not built", 0);
     const std::vector<MapPointT*> vpMapPointsKF = pKF->GetMapPointMatches();
     vpMapPointMatches.assign(F.N, static_cast<MapPointT*>(nullptr));
     const int n1 = (int)vpMapPointsKF.size(), n2 = F.N;
@@ -234,7 +234,7 @@ public:
   template <class FrameT, class MapPointT>
   int SearchByProjection(FrameT& CurrentFrame, const std::vector<MapPointT*>& vpMPs, const ProjectedPoints& P,
                          const float th, const int ORBdist) {
-    if (CurrentFrame.Nleft != -1) throw std::runtime_error("ORBmatcher shim: fisheye (Nleft != -1) branch is not built");
+    if (CurrentFrame.Nleft != -1) CUORB_SHIM_FAIL(std::runtime_error, "ORBmatcher shim: fisheye (Nleft != -1) branch is not built", 0);
     const int n = P.size();
     if (n == 0 || CurrentFrame.N == 0) return 0;
     std::vector<uint8_t> bound(CurrentFrame.N);
@@ -245,7 +245,7 @@ public:
     const int r = cuorb_search_by_projection_reloc(device_, &fv, n, P.desc.data(), P.u.data(), P.v.data(), P.level.data(),
                                                    P.angle.data(), P.active.data(), th, ORBdist, mbCheckOrientation ? 1 : 0,
                                                    best.data(), rot.data(), keep);
-    if (r < 0) throw std::runtime_error(std::string("SearchByProjection (libcuorb): ") + cuorb_last_error());
+    if (r < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("SearchByProjection (libcuorb): ") + cuorb_last_error(), 0);
     for (int i = 0; i < n; i++) {
       if (best[i] < 0) continue;
       const bool kept = !mbCheckOrientation || rot[i] == keep[0] || rot[i] == keep[1] || rot[i] == keep[2];
@@ -269,7 +269,7 @@ public:
     std::vector<int32_t> best(n);
     const int r = cuorb_search_by_projection_sim3(device_, &fv, n, P.desc.data(), P.u.data(), P.v.data(), P.level.data(),
                                                   P.active.data(), th, ratioHamming, best.data());
-    if (r < 0) throw std::runtime_error(std::string("SearchByProjection (libcuorb): ") + cuorb_last_error());
+    if (r < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("SearchByProjection (libcuorb): ") + cuorb_last_error(), 0);
     for (int i = 0; i < n; i++)
       if (best[i] >= 0) {
         vpMatched[best[i]] = vpPoints[i];                                                          // :531
@@ -293,7 +293,7 @@ public:
     const cuorb_frame_view fv = view_of(*pKF, bound);
     const int r = cuorb_fuse(device_, &fv, pKF->mvInvLevelSigma2.data(), n, P.desc.data(), P.u.data(), P.v.data(), P.ur.data(),
                              P.level.data(), P.active.data(), th, checkReprojection ? 1 : 0, bestIdx.data());
-    if (r < 0) throw std::runtime_error(std::string("Fuse (libcuorb): ") + cuorb_last_error());
+    if (r < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("Fuse (libcuorb): ") + cuorb_last_error(), 0);
     return r;
   }
 
@@ -303,7 +303,7 @@ public:
   template <class KeyFrameT, class MapPointT>
   int SearchBySim3(KeyFrameT* pKF1, KeyFrameT* pKF2, const ProjectedPoints& P12, const ProjectedPoints& P21,
                    std::vector<MapPointT*>& vpMatches12, const float th) {
-    if (P12.size() != pKF1->N || P21.size() != pKF2->N) throw std::runtime_error("SearchBySim3 shim: one entry per feature");
+    if (P12.size() != pKF1->N || P21.size() != pKF2->N) CUORB_SHIM_FAIL(std::runtime_error, "SearchBySim3 shim: one entry per feature", 0);
     if (pKF1->N == 0 || pKF2->N == 0) return 0;
     std::vector<uint8_t> b1(pKF1->N, 0), b2(pKF2->N, 0);
     const cuorb_frame_view fv1 = view_of(*pKF1, b1), fv2 = view_of(*pKF2, b2);
@@ -311,7 +311,7 @@ public:
     const int r = cuorb_search_by_sim3(device_, &fv1, &fv2, P12.desc.data(), P12.u.data(), P12.v.data(), P12.level.data(),
                                        P12.active.data(), P21.desc.data(), P21.u.data(), P21.v.data(), P21.level.data(),
                                        P21.active.data(), th, m12.data());
-    if (r < 0) throw std::runtime_error(std::string("SearchBySim3 (libcuorb): ") + cuorb_last_error());
+    if (r < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("SearchBySim3 (libcuorb): ") + cuorb_last_error(), 0);
     const std::vector<MapPointT*> vpMapPoints2 = pKF2->GetMapPointMatches();
     for (int i = 0; i < pKF1->N; i++)
       if (m12[i] >= 0) vpMatches12[i] = vpMapPoints2[m12[i]];                                      // :1674
@@ -330,7 +330,7 @@ public:
     const cuorb_frame_view fv1 = view_of(F1, b1), fv2 = view_of(F2, b2);
     const int r = cuorb_search_for_initialization(device_, &fv1, &fv2, reinterpret_cast<float*>(vbPrevMatched.data()),
                                                   windowSize, mfNNratio, mbCheckOrientation ? 1 : 0, vnMatches12.data());
-    if (r < 0) throw std::runtime_error(std::string("SearchForInitialization (libcuorb): ") + cuorb_last_error());
+    if (r < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("SearchForInitialization (libcuorb): ") + cuorb_last_error(), 0);
     return r;
   }
 
@@ -354,7 +354,7 @@ public:
     const int r = cuorb_search_for_triangulation(device_, &fv1, &fv2, (int)off1.size() - 1, off1.data(), idx1.data(), off2.data(),
                                                  idx2.data(), F12, ep, pKF2->mvLevelSigma2.data(), bOnlyStereo ? 1 : 0,
                                                  bCoarse ? 1 : 0, mbCheckOrientation ? 1 : 0, m12.data());
-    if (r < 0) throw std::runtime_error(std::string("SearchForTriangulation (libcuorb): ") + cuorb_last_error());
+    if (r < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("SearchForTriangulation (libcuorb): ") + cuorb_last_error(), 0);
     vMatchedPairs.reserve(r);
     for (int i = 0; i < pKF1->N; i++)                                                              // :1133-1144
       if (m12[i] >= 0) vMatchedPairs.push_back(std::make_pair((std::size_t)i, (std::size_t)m12[i]));
@@ -382,7 +382,7 @@ private:
     const int n = cuorb_search_by_bow(device_, n1, d1, valid1.data(), a1.data(), n2, d2, elig2.data(), a2.data(),
                                       (int)off1.size() - 1, off1.data(), idx1.data(), off2.data(), idx2.data(), mode, mfNNratio,
                                       mbCheckOrientation ? 1 : 0, match.data());
-    if (n < 0) throw std::runtime_error(std::string("SearchByBoW (libcuorb): ") + cuorb_last_error());
+    if (n < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("SearchByBoW (libcuorb): ") + cuorb_last_error(), 0);
     return n;
   }
 
@@ -421,7 +421,7 @@ private:
   }
 
   static const uint8_t* contiguous(const cv::Mat& m) {
-    if (m.rows > 1 && m.step != 32) throw std::runtime_error("descriptor matrix must be n x 32 contiguous");
+    if (m.rows > 1 && m.step != 32) CUORB_SHIM_FAIL(std::runtime_error, "descriptor matrix must be n x 32 contiguous", nullptr);
     return m.ptr<unsigned char>(0);
   }
 

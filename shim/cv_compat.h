@@ -5,6 +5,26 @@
 // real types (cuorb_keypoint is layout-identical to cv::KeyPoint, so the shim memcpy's).
 #pragma once
 
+// ---- error convention of the shim ----------------------------------------------------------------------------
+// The reference's path uses no C++ exceptions: failure is -1 / empty outputs / an early return in Frame
+// (src/ORBextractor.cc:1060-1062, src/Frame.cc:216-218).  The drop-in classes follow it: a libcuorb error
+// is reported once on stderr (with cuorb_last_error()'s text) and the method returns its neutral value - operator()
+// -1 with the outputs untouched, a search 0 matches, ComputeStereoMatches all -1.  Constructors are the exception
+// (they cannot return a status): they throw std::runtime_error when no CUDA device / arena is available.
+// Define CUORB_SHIM_THROW to get exceptions from every method instead.
+#include <cstdio>
+#include <stdexcept>
+#include <string>
+#ifdef CUORB_SHIM_THROW
+#define CUORB_SHIM_FAIL(ExcType, msg, ...) throw ExcType(msg)
+#else
+#define CUORB_SHIM_FAIL(ExcType, msg, ...)                                         \
+  do {                                                                             \
+    std::fprintf(stderr, "[cuorb shim] %s\n", std::string(msg).c_str());           \
+    return __VA_ARGS__;                                                            \
+  } while (0)
+#endif
+
 #ifdef CUORB_SHIM_USE_OPENCV
 #include <opencv2/core.hpp>
 #else
