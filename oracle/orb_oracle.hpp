@@ -10,9 +10,11 @@
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
 // load this.  libcuorb never links or calls it.
 //
-// Parity status: the reference's own tests hold no golden vectors for this path;
-// the reference itself cannot be compiled here (needs OpenCV C++/Eigen/Sophus headers that are
-// absent), so the oracle is pinned to outputs of the real OpenCV primitives through cv2 instead.
+// Parity status: pinned.  The reference's own tests hold no golden vectors for this path, so
+// (1) the OpenCV primitives are pinned to outputs of the real OpenCV 4.13.0 through cv2 (tests/golden/), and
+// (2) everything above them is pinned to the reference's OWN code: src/ORBextractor.cc and src/ORBmatcher.cc
+// compiled unmodified, plus bodies lifted verbatim from src/Frame.cc, src/KeyFrame.cc, src/MapPoint.cc and
+// Pinhole.cpp, over the stand-in headers of oracle/ref_compat (oracle/_ref; tests/test_oracle_vs_ref*.py).
 // Behaviour is defined as: OpenCV 4.13.0, GCC 13 libstdc++ (std::list / std::sort tie order in
 // DistributeOctTree), glibc cosf/sinf, compiled -O2 -ffp-contract=off (no FMA contraction).
 #pragma once

@@ -1,7 +1,7 @@
 // TEST INFRASTRUCTURE — NOT PRODUCT CODE.  Stub of include/CameraModels/GeometricCamera.h and
 // Pinhole.h: the virtual interface src/ORBmatcher.cc and the lifted Frame functions call.
-// Pinhole::project is the reference's own body (lifted from src/CameraModels/Pinhole.cpp:55-76
-// at build time); epipolarConstrain is delegated to the harness.
+// Pinhole::project and Pinhole::epipolarConstrain are the reference's own bodies (lifted from
+// src/CameraModels/Pinhole.cpp:55-76 and :143-172 at build time).
 #pragma once
 #include <vector>
 #include <Eigen/Core>
@@ -22,6 +22,7 @@ public:
                                  const cv::KeyPoint& kp2, const Eigen::Matrix3f& R12,
                                  const Eigen::Vector3f& t12, const float sigmaLevel,
                                  const float unc) = 0;
+  virtual Eigen::Matrix3f toK_() { return Eigen::Matrix3f::Identity(); }
   float getParameter(const int i) { return mvParameters[i]; }
 protected:
   std::vector<float> mvParameters;  // [fx, fy, cx, cy]
@@ -33,17 +34,19 @@ public:
   cv::Point2f     project(const cv::Point3f& p3D);
   Eigen::Vector2d project(const Eigen::Vector3d& v3D);
   Eigen::Vector2f project(const Eigen::Vector3f& v3D);
-  // harness hook: the epipolar test needs K^-T [t]x R K^-1 (matrix inverse, SO3::hat) which the
-  // Eigen stand-in does not carry; a harness that exercises SearchForTriangulation installs one
-  bool (*epipolar_hook)(const cv::KeyPoint&, const cv::KeyPoint&, const Eigen::Matrix3f&,
-                        const Eigen::Vector3f&, float, float, void*) = nullptr;
-  void* epipolar_ctx = nullptr;
-  bool epipolarConstrain(GeometricCamera*, const cv::KeyPoint& kp1, const cv::KeyPoint& kp2,
-                         const Eigen::Matrix3f& R12, const Eigen::Vector3f& t12,
-                         const float sigmaLevel, const float unc) {
-    if (!epipolar_hook) REF_COMPAT_UNSUPPORTED("Pinhole::epipolarConstrain without a harness hook");
-    return epipolar_hook(kp1, kp2, R12, t12, sigmaLevel, unc, epipolar_ctx);
+  // K as an Eigen matrix (Pinhole.cpp:137-141 fills it with the comma initialiser, absent from the stand-in)
+  Eigen::Matrix3f toK_() {
+    Eigen::Matrix3f K;
+    K(0, 0) = mvParameters[0]; K(0, 2) = mvParameters[2]; K(1, 1) = mvParameters[1]; K(1, 2) = mvParameters[3];
+    K(2, 2) = 1.f;
+    return K;
   }
+  // the reference's own body (Pinhole.cpp:143-172, lifted); its F12 = K1^-T [t12]x R12 K2^-1 runs on the
+  // Eigen / Sophus stand-ins (deterministic, not Eigen-bit-identical), the point-to-line test after it is
+  // the reference's arithmetic
+  bool epipolarConstrain(GeometricCamera* pCamera2, const cv::KeyPoint& kp1, const cv::KeyPoint& kp2,
+                         const Eigen::Matrix3f& R12, const Eigen::Vector3f& t12, const float sigmaLevel,
+                         const float unc);
 };
 
 }  // namespace ORB_SLAM3

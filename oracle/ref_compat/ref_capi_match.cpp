@@ -27,59 +27,12 @@
 #include "MapPoint.h"
 #include "ORBextractor.h"
 #include "ORBmatcher.h"
+#include "ref_harness.h"
 
 using namespace ORB_SLAM3;
+using namespace ref_harness;
 static_assert(sizeof(cv::KeyPoint) == sizeof(cuorb_keypoint), "KeyPoint ABI");
 
-namespace {
-
-struct PassThroughCamera : GeometricCamera {
-  cv::Point2f     project(const cv::Point3f& p) override { return cv::Point2f(p.x, p.y); }
-  Eigen::Vector2d project(const Eigen::Vector3d& v) override { return Eigen::Vector2d(v[0], v[1]); }
-  Eigen::Vector2f project(const Eigen::Vector3f& v) override { return Eigen::Vector2f(v[0], v[1]); }
-  bool epipolarConstrain(GeometricCamera*, const cv::KeyPoint&, const cv::KeyPoint&,
-                         const Eigen::Matrix3f&, const Eigen::Vector3f&, const float,
-                         const float) override {
-    REF_COMPAT_UNSUPPORTED("epipolarConstrain on the pass-through camera");
-    return false;
-  }
-};
-
-cv::Mat desc_mat(const uint8_t* d, int n) {
-  return n > 0 ? cv::Mat(n, 32, CV_8UC1, (void*)d, 32) : cv::Mat();
-}
-
-// Fill a stub Frame from a cuorb_frame_view the way the Frame constructors do (src/Frame.cc:
-// 240-257 sets the statics; AssignFeaturesToGrid is the reference's own, called as at :262).
-struct FrameFromView {
-  Frame                 F;
-  PassThroughCamera     cam;
-  std::unique_ptr<MapPoint[]> bound;  // MapPoints standing for "already bound, Observations() > 0"
-  FrameFromView(const cuorb_frame_view* f) {
-    F.N = f->n;
-    const cv::KeyPoint* k = (const cv::KeyPoint*)f->keys_un;
-    F.mvKeysUn.assign(k, k + f->n);
-    F.mvKeys = F.mvKeysUn;
-    F.mDescriptors = desc_mat(f->descriptors, f->n);
-    F.mvuRight.assign(f->n, -1.f);
-    if (f->u_right) F.mvuRight.assign(f->u_right, f->u_right + f->n);
-    F.mvpMapPoints.assign(f->n, nullptr);
-    F.mvbOutlier.assign(f->n, false);
-    bound.reset(new MapPoint[f->n > 0 ? f->n : 1]);
-    for (int i = 0; i < f->n; i++)
-      if (f->bound_with_obs && f->bound_with_obs[i]) { bound[i].nObs = 1; F.mvpMapPoints[i] = &bound[i]; }
-    Frame::mnMinX = f->min_x; Frame::mnMinY = f->min_y; Frame::mnMaxX = f->max_x; Frame::mnMaxY = f->max_y;
-    Frame::mfGridElementWidthInv = f->grid_w_inv; Frame::mfGridElementHeightInv = f->grid_h_inv;
-    F.mb = f->mb; F.mbf = f->mbf;
-    F.mvScaleFactors.assign(f->scale_factors, f->scale_factors + f->nlevels);
-    F.mnScaleLevels = f->nlevels;
-    F.Nleft = -1; F.Nright = -1;
-    F.mpCamera = &cam;
-    F.AssignFeaturesToGrid();
-  }
-};
-
-}  // namespace
 
 extern "C" {
 

@@ -8,6 +8,17 @@
 
 namespace Sophus {
 
+template <typename T> class SO3 {
+public:
+  // the cross-product matrix [w]x
+  static Eigen::Matrix<T, 3, 3> hat(const Eigen::Matrix<T, 3, 1>& w) {
+    Eigen::Matrix<T, 3, 3> m;
+    m(0, 1) = -w(2); m(0, 2) = w(1); m(1, 0) = w(2); m(1, 2) = -w(0); m(2, 0) = -w(1); m(2, 1) = w(0);
+    return m;
+  }
+};
+typedef SO3<float> SO3f;
+
 template <typename T> class SE3 {
 public:
   typedef Eigen::Matrix<T, 3, 3> Mat3;

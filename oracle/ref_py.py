@@ -84,6 +84,14 @@ def lib() -> C.CDLL:
         L.ref_bench_stereo.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                        C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int,
                                        C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        V = C.c_void_p
+        L.ref_search_by_bow.argtypes = ([C.c_int] + [FV, V, C.c_int, V, V, V] * 2 + [C.c_float, C.c_int, V])
+        L.ref_search_for_initialization.argtypes = [FV, FV, V, C.c_int, C.c_float, C.c_int, V]
+        L.ref_search_by_projection_reloc.argtypes = [FV, C.c_int] + [V] * 7 + [C.c_float, C.c_int, C.c_int, V]
+        L.ref_search_by_projection_sim3.argtypes = [FV, C.c_int] + [V] * 5 + [C.c_int, C.c_float, C.c_int, V]
+        L.ref_fuse.argtypes = [FV, C.c_int] + [V] * 6 + [C.c_float, C.c_int, V, V, V, V]
+        L.ref_search_by_sim3.argtypes = [FV, FV] + [V] * 10 + [C.c_float, V, V]
+        L.ref_search_for_triangulation.argtypes = ([FV, V, C.c_int, V, V, V] * 2 + [V, C.c_int, C.c_int, C.c_int, V, V, V])
         _lib = L
     return _lib
 
@@ -247,3 +255,89 @@ def search_by_projection_frame_pose(fv, pose_cur, pose_last, K4, last_desc, worl
     n = lib().ref_search_by_projection_frame_pose(C.byref(fv), *[_p(a) for a in arrs], len(last_octave),
                                                   *[_p(a) for a in per], th, int(mono), int(check_ori), _p(final))
     return n, final
+
+
+# ---- the ORBmatcher searches outside the tracking path (ref_compat/ref_capi_search.cpp) ----
+def _u8(a): return None if a is None else np.ascontiguousarray(a, np.uint8)
+def _f32(a): return None if a is None else np.ascontiguousarray(a, np.float32)
+def _i32(a): return None if a is None else np.ascontiguousarray(a, np.int32)
+
+
+def flatten_feature_vector(fv: dict):
+    """{node: [feature, ...]} -> (node ids ascending, offsets, features in insertion order), int32."""
+    nodes = sorted(fv)
+    off = np.zeros(len(nodes) + 1, np.int32)
+    for k, nd in enumerate(nodes):
+        off[k + 1] = off[k] + len(fv[nd])
+    idx = np.asarray([i for nd in nodes for i in fv[nd]], np.int32)
+    return len(nodes), np.asarray(nodes, np.int32), off, idx
+
+
+def search_by_bow(mode, fv1, has_mp1, featvec1, fv2, has_mp2, featvec2, nnratio, check_ori=True):
+    """ORBmatcher::SearchByBoW, mode 0 = (KeyFrame, Frame), 1 = (KeyFrame, KeyFrame); has_mp: 0 none, 1 good, 2 bad.
+    Returns (nmatches, match12[n1])."""
+    n1, nd1, o1, i1 = flatten_feature_vector(featvec1)
+    n2, nd2, o2, i2 = flatten_feature_vector(featvec2)
+    h1 = _u8(has_mp1); h2 = _u8(has_mp2)
+    m = np.empty(max(fv1.n, 1), np.int32)
+    r = lib().ref_search_by_bow(int(mode), C.byref(fv1), _p(h1), n1, _p(nd1), _p(o1), _p(i1), C.byref(fv2),
+                                _p(h2) if h2 is not None else None, n2, _p(nd2), _p(o2), _p(i2), nnratio,
+                                int(check_ori), _p(m))
+    return r, m[:fv1.n]
+
+
+def search_for_initialization(fv1, fv2, prev_matched, window, nnratio, check_ori=True):
+    pm = np.ascontiguousarray(prev_matched, np.float32).copy()
+    m = np.empty(max(fv1.n, 1), np.int32)
+    r = lib().ref_search_for_initialization(C.byref(fv1), C.byref(fv2), _p(pm), int(window), nnratio, int(check_ori), _p(m))
+    return r, m[:fv1.n], pm
+
+
+def search_by_projection_reloc(fv, mp_desc, u, v, level, kf_angle, active, found, th, orb_dist, check_ori=True):
+    """Returns (nmatches, binding[N]): binding[i2] = query bound to current feature i2 (-1 none, -2 pre-existing)."""
+    arrs = [_u8(mp_desc), _f32(u), _f32(v), _i32(level), _f32(kf_angle), _u8(active), _u8(found)]
+    out = np.empty(max(fv.n, 1), np.int32)
+    r = lib().ref_search_by_projection_reloc(C.byref(fv), len(arrs[1]), *[None if a is None else _p(a) for a in arrs],
+                                             th, int(orb_dist), int(check_ori), _p(out))
+    return r, out[:fv.n]
+
+
+def search_by_projection_sim3(fv, mp_desc, u, v, level, active, th, ratio_hamming, with_kfs=False):
+    """Returns (nmatches, matched[N]): matched[idx] = query matched to KeyFrame feature idx (-1 none, -2 pre-existing)."""
+    arrs = [_u8(mp_desc), _f32(u), _f32(v), _i32(level), _u8(active)]
+    out = np.empty(max(fv.n, 1), np.int32)
+    r = lib().ref_search_by_projection_sim3(C.byref(fv), len(arrs[1]), *[_p(a) for a in arrs], int(th), ratio_hamming,
+                                            int(with_kfs), _p(out))
+    return r, out[:fv.n]
+
+
+def fuse(fv, mp_desc, u, v, z, level, active, th, sim3, n_obs_kf=None, n_obs_q=None):
+    """Returns (nFused of one call over all queries, best_idx[n], outcome[n])."""
+    arrs = [_u8(mp_desc), _f32(u), _f32(v), _f32(z), _i32(level), _u8(active)]
+    n = len(arrs[1])
+    best = np.empty(max(n, 1), np.int32); outc = np.empty(max(n, 1), np.int32)
+    ok, oq = _i32(n_obs_kf), _i32(n_obs_q)
+    r = lib().ref_fuse(C.byref(fv), n, *[_p(a) for a in arrs], th, int(sim3), None if ok is None else _p(ok),
+                       None if oq is None else _p(oq), _p(best), _p(outc))
+    return r, best[:n], outc[:n]
+
+
+def search_by_sim3(fv1, fv2, d1, u12, v12, l12, a1, d2, u21, v21, l21, a2, th, pre12=None):
+    arrs = [_u8(d1), _f32(u12), _f32(v12), _i32(l12), _u8(a1), _u8(d2), _f32(u21), _f32(v21), _i32(l21), _u8(a2)]
+    m = np.empty(max(fv1.n, 1), np.int32)
+    pre = _i32(pre12)
+    r = lib().ref_search_by_sim3(C.byref(fv1), C.byref(fv2), *[_p(a) for a in arrs], th, None if pre is None else _p(pre), _p(m))
+    return r, m[:fv1.n]
+
+
+def search_for_triangulation(fv1, has_mp1, featvec1, fv2, has_mp2, featvec2, pose1, only_stereo, coarse, check_ori=True):
+    """pose1 = T1w (12 floats: R row-major, t); KF2 at the identity.  Returns (nmatches, match12[n1], ep[2], F12[9])
+    where ep and F12 are what the reference's prologue / Pinhole::epipolarConstrain computed from the pose."""
+    n1, nd1, o1, i1 = flatten_feature_vector(featvec1)
+    n2, nd2, o2, i2 = flatten_feature_vector(featvec2)
+    h1 = _u8(has_mp1); h2 = _u8(has_mp2); pose = _f32(pose1)
+    m = np.empty(max(fv1.n, 1), np.int32); ep = np.empty(2, np.float32); F = np.empty(9, np.float32)
+    r = lib().ref_search_for_triangulation(C.byref(fv1), _p(h1), n1, _p(nd1), _p(o1), _p(i1), C.byref(fv2), _p(h2), n2,
+                                           _p(nd2), _p(o2), _p(i2), _p(pose), int(only_stereo), int(coarse),
+                                           int(check_ori), _p(ep), _p(F), _p(m))
+    return r, m[:fv1.n], ep, F

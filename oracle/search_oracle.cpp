@@ -20,7 +20,8 @@
 // KeyFrame::GetFeaturesInArea (src/KeyFrame.cc:780-834) is Frame::GetFeaturesInArea without the
 // level filter and on the same 64x48 grid (the KeyFrame copies the Frame's grid), so
 // FrameView::features_in_area(x, y, r, -1, -1) stands for it.
-// Parity status: restatement only (the reference holds no test vectors for these functions).
+// Parity status: pinned to the reference's own functions (the unmodified src/ORBmatcher.cc in oracle/_ref, driven
+// by oracle/ref_compat/ref_capi_search.cpp; tests/test_oracle_vs_ref_search.py), bit for bit.
 #include <climits>
 #include <cmath>
 #include <vector>
