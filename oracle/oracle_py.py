@@ -153,6 +153,9 @@ def lib() -> C.CDLL:
         L.oo_search_by_sim3.argtypes = [FV, FV] + [C.c_void_p] * 10 + [C.c_float, C.c_void_p]
         L.oo_search_for_initialization.argtypes = [FV, FV, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p]
         L.oo_search_for_triangulation.argtypes = [FV, FV, C.c_int] + [C.c_void_p] * 7 + [C.c_int, C.c_int, C.c_int, C.c_void_p]
+        V = C.c_void_p
+        L.oo_search_by_projection_rig.argtypes = ([FV, FV, V, V, C.c_int] + [V] * 11 + [C.c_float, C.c_int, C.c_float, C.c_float, V, V])
+        L.oo_search_by_projection_frame_rig.argtypes = ([FV, FV, C.c_int] + [V] * 9 + [C.c_float, C.c_int, C.c_int, C.c_int] + [V] * 5)
         _lib = L
     return _lib
 
@@ -521,3 +524,31 @@ def search_for_triangulation(fv1, fv2, off1, idx1, off2, idx2, F12, ep, sigma2_2
     r = lib().oo_search_for_triangulation(C.byref(fv1), C.byref(fv2), len(off1) - 1, *[_p(a) for a in arrs],
                                           int(only_stereo), int(coarse), int(check_ori), _p(m12))
     return r, m12[:fv1.n]
+
+
+# ---- two-camera (Frame::Nleft != -1) branches of the tracking-time searches (rig_oracle.cpp) ----
+MP_IN_VIEW_R = 8
+
+
+def search_by_projection_rig(fvl, fvr, l2r, r2l, mp_desc, px, py, level, view_cos, pxr, pyr, level_r, view_cos_r, depth, flags,
+                             th, far_points, th_far, nn_ratio):
+    """Returns (nmatches incl. the cross-bound stereo partners, best_l[M], best_r[M])."""
+    arrs = [_u8(mp_desc), _f32(px), _f32(py), _i32(level), _f32(view_cos), _f32(pxr), _f32(pyr), _i32(level_r),
+            _f32(view_cos_r), _f32(depth), _u8(flags)]
+    a, b = _i32(l2r), _i32(r2l)
+    M = len(arrs[1])
+    bl = np.empty(max(M, 1), np.int32); br = np.empty(max(M, 1), np.int32)
+    n = lib().oo_search_by_projection_rig(C.byref(fvl), C.byref(fvr), _p(a), _p(b), M, *[_p(x) for x in arrs], th, int(far_points),
+                                          th_far, nn_ratio, _p(bl), _p(br))
+    return n, bl[:M], br[:M]
+
+
+def search_by_projection_frame_rig(fvl, fvr, last_desc, u, v, inv_z, ur, vr, last_octave, last_angle, flags, th, forward, backward,
+                                   check_ori=True):
+    """Returns (nmatches, best_l, best_r, rot_bin_l, rot_bin_r, keep_bins)."""
+    arrs = [_u8(last_desc), _f32(u), _f32(v), _f32(inv_z), _f32(ur), _f32(vr), _i32(last_octave), _f32(last_angle), _u8(flags)]
+    n_last = len(arrs[1])
+    outs = [np.empty(max(n_last, 1), np.int32) for _ in range(4)] + [np.empty(3, np.int32)]
+    n = lib().oo_search_by_projection_frame_rig(C.byref(fvl), C.byref(fvr), n_last, *[_p(x) for x in arrs], th, int(forward),
+                                                int(backward), int(check_ori), *[_p(o) for o in outs])
+    return (n,) + tuple(o[:n_last] for o in outs[:4]) + (outs[4],)

@@ -151,7 +151,9 @@ int oo_stereo(void* hl, void* hr, int nL, const KeyPoint* kl, const uint8_t* dl,
 }
 
 // ---- projection searches ----
-static FrameView make_view(const cuorb_frame_view* f) {
+extern "C++" { namespace orb_oracle { FrameView make_frame_view(const cuorb_frame_view* f); } }
+static FrameView make_view(const cuorb_frame_view* f) { return orb_oracle::make_frame_view(f); }
+extern "C++" FrameView orb_oracle::make_frame_view(const cuorb_frame_view* f) {
   FrameView F;
   F.N = f->n; F.keysUn = (const KeyPoint*)f->keys_un; F.desc = f->descriptors; F.uRight = f->u_right;
   F.bound_with_obs.assign(f->n, 0);

@@ -1,0 +1,145 @@
+// TEST INFRASTRUCTURE — NOT PRODUCT CODE.
+// Flat C entry points (ctypes) that drive the reference's OWN code for the two-camera (Frame::Nleft != -1)
+// branches of the tracking-time searches — the unmodified src/ORBmatcher.cc:
+//   SearchByProjection(Frame&, const vector<MapPoint*>&, th, bFarPoints, thFarPoints)   :38-227
+//   SearchByProjection(Frame& Cur, const Frame& Last, th, bMono)                         :1684-1908
+// over Frame::AssignFeaturesToGrid / GetFeaturesInArea / GetRelativePoseTrl lifted verbatim from src/Frame.cc.
+// A rig Frame is assembled from two cuorb_frame_views: the left camera's features become indices [0, Nleft)
+// (mvKeys, mGrid), the right camera's [Nleft, N) (mvKeysRight, mGridRight, descriptor rows idx + Nleft).
+#include <vector>
+
+#include "ORBmatcher.h"
+#include "ref_harness.h"
+
+using namespace ORB_SLAM3;
+using namespace ref_harness;
+
+namespace {
+
+struct RigFrame {
+  Frame                       F;
+  PassThroughCamera           cam;
+  std::unique_ptr<MapPoint[]> bound;
+  std::vector<uint8_t>        desc;
+  RigFrame(const cuorb_frame_view* l, const cuorb_frame_view* r, const int32_t* l2r, const int32_t* r2l) {
+    const int nl = l->n, nr = r->n, n = nl + nr;
+    F.N = n; F.Nleft = nl; F.Nright = nr;
+    const cv::KeyPoint* kl = (const cv::KeyPoint*)l->keys_un;
+    const cv::KeyPoint* kr = (const cv::KeyPoint*)r->keys_un;
+    F.mvKeys.assign(kl, kl + nl);
+    F.mvKeysRight.assign(kr, kr + nr);
+    F.mvKeysUn = F.mvKeys;
+    desc.resize((size_t)(n > 0 ? n : 1) * 32);
+    if (nl) memcpy(desc.data(), l->descriptors, (size_t)nl * 32);
+    if (nr) memcpy(desc.data() + (size_t)nl * 32, r->descriptors, (size_t)nr * 32);
+    F.mDescriptors = desc_mat(desc.data(), n);
+    F.mvuRight.assign(nl, -1.f);                                   // src/Frame.cc:1313
+    F.mvpMapPoints.assign(n, nullptr);
+    F.mvbOutlier.assign(n, false);
+    bound.reset(new MapPoint[n > 0 ? n : 1]);
+    for (int i = 0; i < nl; i++)
+      if (l->bound_with_obs && l->bound_with_obs[i]) { bound[i].nObs = 1; F.mvpMapPoints[i] = &bound[i]; }
+    for (int i = 0; i < nr; i++)
+      if (r->bound_with_obs && r->bound_with_obs[i]) { bound[nl + i].nObs = 1; F.mvpMapPoints[nl + i] = &bound[nl + i]; }
+    Frame::mnMinX = l->min_x; Frame::mnMinY = l->min_y; Frame::mnMaxX = l->max_x; Frame::mnMaxY = l->max_y;
+    Frame::mfGridElementWidthInv = l->grid_w_inv; Frame::mfGridElementHeightInv = l->grid_h_inv;
+    F.mb = l->mb; F.mbf = l->mbf;
+    F.mvScaleFactors.assign(l->scale_factors, l->scale_factors + l->nlevels);
+    F.mnScaleLevels = l->nlevels;
+    F.mvLeftToRightMatch.assign(nl, -1);
+    F.mvRightToLeftMatch.assign(nr, -1);
+    if (l2r) F.mvLeftToRightMatch.assign(l2r, l2r + nl);
+    if (r2l) F.mvRightToLeftMatch.assign(r2l, r2l + nr);
+    F.mpCamera = &cam; F.mpCamera2 = &cam;
+    F.AssignFeaturesToGrid();
+  }
+};
+
+}  // namespace
+
+extern "C" {
+
+// flags: bit0 mbTrackInView, bit1 isBad(), bit2 Observations() > 0, bit3 mbTrackInViewR.
+// binding_out[k], k in [0, Nleft + Nright): MapPoint bound to rig feature k on return (-1 none, -2 pre-existing).
+int ref_search_by_projection_rig(const cuorb_frame_view* left, const cuorb_frame_view* right, const int32_t* l2r,
+                                 const int32_t* r2l, int M, const uint8_t* mp_desc, const float* px, const float* py,
+                                 const int32_t* level, const float* view_cos, const float* pxr, const float* pyr,
+                                 const int32_t* level_r, const float* view_cos_r, const float* depth,
+                                 const uint8_t* flags, float th, int far_points, float th_far, float nn_ratio,
+                                 int32_t* binding_out, int32_t* per_mp_out) {
+  std::unique_ptr<MapPoint[]> mps(new MapPoint[M > 0 ? M : 1]);
+  std::vector<MapPoint*> ptrs(M);
+  for (int i = 0; i < M; i++) {
+    MapPoint& p = mps[i];
+    p.mbTrackInView = (flags[i] & 1) != 0; p.mbTrackInViewR = (flags[i] & 8) != 0;
+    p.mbBad = (flags[i] & 2) != 0;
+    p.nObs = (flags[i] & 4) ? 1 : 0;
+    p.mTrackProjX = px[i]; p.mTrackProjY = py[i]; p.mnTrackScaleLevel = level[i]; p.mTrackViewCos = view_cos[i];
+    p.mTrackProjXR = pxr[i]; p.mTrackProjYR = pyr[i]; p.mnTrackScaleLevelR = level_r[i]; p.mTrackViewCosR = view_cos_r[i];
+    p.mTrackDepth = depth ? depth[i] : 0.f;
+    p.mDescriptor = desc_mat(mp_desc + (size_t)i * 32, 1);
+    ptrs[i] = &p;
+  }
+  RigFrame rf(left, right, l2r, r2l);
+  ORBmatcher matcher(nn_ratio, true);
+  const int n = matcher.SearchByProjection(rf.F, ptrs, th, far_points != 0, th_far);
+  for (int k = 0; k < rf.F.N; k++) {
+    MapPoint* b = rf.F.mvpMapPoints[k];
+    binding_out[k] = !b ? -1 : (M && b >= &mps[0] && b < &mps[0] + M) ? (int32_t)(b - &mps[0]) : -2;
+  }
+  // per_mp_out[4 * i ..]: the rig features (ascending, -1 padded) that point at MapPoint i right after IT was
+  // processed, obtained by feeding the MapPoints one call at a time to a second Frame (the loop body only
+  // communicates through F.mvpMapPoints, so this is the same computation)
+  if (per_mp_out) {
+    RigFrame one(left, right, l2r, r2l);
+    int total = 0;
+    for (int i = 0; i < M; i++) {
+      std::vector<MapPoint*> v(1, ptrs[i]);
+      total += matcher.SearchByProjection(one.F, v, th, far_points != 0, th_far);
+      int c = 0;
+      for (int q = 0; q < 4; q++) per_mp_out[4 * i + q] = -1;
+      for (int k = 0; k < one.F.N; k++)
+        if (one.F.mvpMapPoints[k] == ptrs[i]) { if (c >= 4) return -1005; per_mp_out[4 * i + c++] = k; }
+    }
+    if (total != n) return -1000 - total;
+  }
+  return n;
+}
+
+// Last-frame feature i has world position (u, v, z) seen from the identity pose through the pass-through camera,
+// so the left projection is (u, v) and the right one project(Trl * x3Dc) = (u + trl_x, v + trl_y) for the pure
+// translation Trl given.  binding_out as above, indexed by current rig feature, holding last-frame feature ids.
+int ref_search_by_projection_frame_rig(const cuorb_frame_view* left, const cuorb_frame_view* right, int n_last,
+                                       const uint8_t* last_desc, const float* u, const float* v, const float* z,
+                                       float trl_x, float trl_y, const int32_t* last_octave,
+                                       const float* last_angle, const uint8_t* flags, float th, int forward,
+                                       int backward, int check_ori, int32_t* binding_out) {
+  RigFrame rf(left, right, nullptr, nullptr);
+  rf.F.mTrl = Sophus::SE3f(Eigen::Matrix3f::Identity(), Eigen::Vector3f(trl_x, trl_y, 0.f));
+  Frame last;
+  std::unique_ptr<MapPoint[]> mps(new MapPoint[n_last > 0 ? n_last : 1]);
+  last.N = n_last; last.Nleft = -1;
+  last.mvKeys.resize(n_last); last.mvKeysUn.resize(n_last);
+  last.mvpMapPoints.assign(n_last, nullptr);
+  last.mvbOutlier.assign(n_last, false);
+  for (int i = 0; i < n_last; i++) {
+    last.mvKeys[i].octave = last_octave[i]; last.mvKeys[i].angle = last_angle[i];
+    last.mvKeysUn[i] = last.mvKeys[i];
+    if (!(flags[i] & 1)) continue;
+    mps[i].mWorldPos = Eigen::Vector3f(u[i], v[i], z[i]);
+    mps[i].nObs = (flags[i] & 4) ? 1 : 0;
+    mps[i].mDescriptor = desc_mat(last_desc + (size_t)i * 32, 1);
+    last.mvpMapPoints[i] = &mps[i];
+  }
+  const float tz = forward ? rf.F.mb + 1.f : backward ? -(rf.F.mb + 1.f) : 0.f;
+  last.mTcw = Sophus::SE3f(Eigen::Matrix3f::Identity(), Eigen::Vector3f(0.f, 0.f, tz));
+  ORBmatcher matcher(0.9f, check_ori != 0);
+  const int n = matcher.SearchByProjection(rf.F, last, th, false);
+  for (int k = 0; k < rf.F.N; k++) {
+    MapPoint* b = rf.F.mvpMapPoints[k];
+    binding_out[k] = !b ? -1 : (n_last && b >= &mps[0] && b < &mps[0] + n_last) ? (int32_t)(b - &mps[0]) : -2;
+  }
+  return n;
+}
+
+}  // extern "C"

@@ -92,6 +92,9 @@ def lib() -> C.CDLL:
         L.ref_fuse.argtypes = [FV, C.c_int] + [V] * 6 + [C.c_float, C.c_int, V, V, V, V]
         L.ref_search_by_sim3.argtypes = [FV, FV] + [V] * 10 + [C.c_float, V, V]
         L.ref_search_for_triangulation.argtypes = ([FV, V, C.c_int, V, V, V] * 2 + [V, C.c_int, C.c_int, C.c_int, V, V, V])
+        L.ref_search_by_projection_rig.argtypes = ([FV, FV, V, V, C.c_int] + [V] * 11 + [C.c_float, C.c_int, C.c_float, C.c_float, V, V])
+        L.ref_search_by_projection_frame_rig.argtypes = ([FV, FV, C.c_int] + [V] * 4 + [C.c_float, C.c_float] + [V] * 3 +
+                                                         [C.c_float, C.c_int, C.c_int, C.c_int, V])
         _lib = L
     return _lib
 
@@ -341,3 +344,28 @@ def search_for_triangulation(fv1, has_mp1, featvec1, fv2, has_mp2, featvec2, pos
                                            _p(nd2), _p(o2), _p(i2), _p(pose), int(only_stereo), int(coarse),
                                            int(check_ori), _p(ep), _p(F), _p(m))
     return r, m[:fv1.n], ep, F
+
+
+# ---- two-camera (Frame::Nleft != -1) branches (ref_compat/ref_capi_rig.cpp) ----
+def search_by_projection_rig(fvl, fvr, l2r, r2l, mp_desc, px, py, level, view_cos, pxr, pyr, level_r, view_cos_r, depth, flags,
+                             th, far_points, th_far, nn_ratio):
+    """Returns (nmatches, binding[Nleft + Nright], per_mp[M, 4]): MapPoint bound to each rig feature on return (-1 none,
+    -2 pre-existing); the rig features pointing at MapPoint i right after it was processed (ascending, -1 padded)."""
+    arrs = [_u8(mp_desc), _f32(px), _f32(py), _i32(level), _f32(view_cos), _f32(pxr), _f32(pyr), _i32(level_r),
+            _f32(view_cos_r), _f32(depth), _u8(flags)]
+    a, b = _i32(l2r), _i32(r2l)
+    out = np.empty(max(fvl.n + fvr.n, 1), np.int32)
+    per = np.empty((max(len(arrs[1]), 1), 4), np.int32)
+    n = lib().ref_search_by_projection_rig(C.byref(fvl), C.byref(fvr), _p(a), _p(b), len(arrs[1]), *[_p(x) for x in arrs], th,
+                                           int(far_points), th_far, nn_ratio, _p(out), _p(per))
+    return n, out[:fvl.n + fvr.n], per[:len(arrs[1])]
+
+
+def search_by_projection_frame_rig(fvl, fvr, last_desc, u, v, z, trl_x, trl_y, last_octave, last_angle, flags, th, forward,
+                                   backward, check_ori=True):
+    arrs = [_u8(last_desc), _f32(u), _f32(v), _f32(z)]
+    tail = [_i32(last_octave), _f32(last_angle), _u8(flags)]
+    out = np.empty(max(fvl.n + fvr.n, 1), np.int32)
+    n = lib().ref_search_by_projection_frame_rig(C.byref(fvl), C.byref(fvr), len(arrs[1]), *[_p(x) for x in arrs], trl_x, trl_y,
+                                                 *[_p(x) for x in tail], th, int(forward), int(backward), int(check_ori), _p(out))
+    return n, out[:fvl.n + fvr.n]
