@@ -241,6 +241,51 @@ int cuorb_search_by_projection_frame(int device, const cuorb_frame_view* cur, in
                                      int32_t* best_idx_out, int32_t* rot_bin_out,
                                      int32_t* keep_bins_out);
 
+/* ---- the same two searches on a two-camera rig (Frame::Nleft != -1, the "fisheye" branches) ----
+ * A rig Frame keeps the left camera's features at indices [0, Nleft) (mvKeys, mGrid) and the right camera's at
+ * [Nleft, N) (mvKeysRight, mGridRight, descriptor rows idx + Nleft).  It is passed as two cuorb_frame_views:
+ * `left`  = {Nleft,  mvKeys,      mDescriptors rows [0, Nleft), bound_with_obs of mvpMapPoints[idx]},
+ * `right` = {Nright, mvKeysRight, mDescriptors rows [Nleft, N), bound_with_obs of mvpMapPoints[idx + Nleft]};
+ * both carry the Frame's image bounds, grid cell sizes and scale factors; u_right is ignored (the mvuRight gate is
+ * pinhole-only, src/ORBmatcher.cc:103, :1770).  Results are indices local to each camera. */
+
+/* int ORBmatcher::SearchByProjection(Frame&, const std::vector<MapPoint*>&, th, bFarPoints, thFarPoints) with
+ * F.Nleft != -1 (src/ORBmatcher.cc:38-227: left part :63-150, right part :152-224).  left_to_right / right_to_left =
+ * mvLeftToRightMatch [Nleft] / mvRightToLeftMatch [Nright] (-1: no stereo partner).  Per MapPoint: proj_x / proj_y /
+ * level / view_cos = mTrackProjX / Y, mnTrackScaleLevel, mTrackViewCos; proj_xr / proj_yr / level_r / view_cos_r =
+ * mTrackProjXR / YR, mnTrackScaleLevelR (-1 skips the right part, :154), mTrackViewCosR; flags as above plus
+ * CUORB_MP_IN_VIEW_R = mbTrackInViewR.  Reference behaviour kept: a match on one side also writes the MapPoint into
+ * the stereo partner's slot on the other side, unconditionally (:138-142, :212-216), so a slot's state is what its
+ * LAST writer left (a MapPoint without observations un-blocks it); a ratio-test rejection on the left skips the
+ * right part (:130-132); the right window has no `th` factor (:156-163).
+ * best_l_out[i] / best_r_out[i] = left / right feature MapPoint i matched directly, or -1; the caller replays, in
+ * MapPoint order, F.mvpMapPoints[bl] = pMP, F.mvpMapPoints[Nleft + l2r[bl]] = pMP, then F.mvpMapPoints[r2l[br]] = pMP,
+ * F.mvpMapPoints[Nleft + br] = pMP.  Returns nmatches (one per slot written, as the reference counts). */
+#define CUORB_MP_IN_VIEW_R 8u
+int cuorb_search_by_projection_rig(int device, const cuorb_frame_view* left, const cuorb_frame_view* right,
+                                   const int32_t* left_to_right, const int32_t* right_to_left, int n_mappoints,
+                                   const uint8_t* mp_desc, const float* proj_x, const float* proj_y,
+                                   const int32_t* level, const float* view_cos, const float* proj_xr,
+                                   const float* proj_yr, const int32_t* level_r, const float* view_cos_r,
+                                   const float* depth, const uint8_t* flags, float th, int far_points,
+                                   float th_far_points, float nn_ratio, int32_t* best_l_out, int32_t* best_r_out);
+
+/* int ORBmatcher::SearchByProjection(Frame& Cur, const Frame& Last, th, bMono) with CurrentFrame.Nleft != -1
+ * (src/ORBmatcher.cc:1684-1908, right part :1812-1886).  u / v / inv_z as for cuorb_search_by_projection_frame;
+ * ur / vr = project(CurrentFrame.GetRelativePoseTrl() * x3Dc) (:1813-1814).  Reference behaviour kept: the right part
+ * only runs for points that passed the left part's depth and bounds tests AND whose left window was not empty
+ * (the `continue` at :1750-1752), has no bounds test of its own, makes no cross-writes, and shares the rotation
+ * histogram with the left part.  best_l_out / best_r_out before the rotation check, rot_bin_l_out / rot_bin_r_out
+ * the bins, keep_bins_out[3] the kept ones; the caller replays the writes in last-frame order and then NULLs every
+ * (point, feature) entry whose bin was not kept (:1889-1905).  Returns nmatches after that removal. */
+int cuorb_search_by_projection_frame_rig(int device, const cuorb_frame_view* left, const cuorb_frame_view* right,
+                                         int n_last, const uint8_t* last_desc, const float* u, const float* v,
+                                         const float* inv_z, const float* ur, const float* vr,
+                                         const int32_t* last_octave, const float* last_angle, const uint8_t* flags,
+                                         float th, int forward, int backward, int check_orientation,
+                                         int32_t* best_l_out, int32_t* best_r_out, int32_t* rot_bin_l_out,
+                                         int32_t* rot_bin_r_out, int32_t* keep_bins_out);
+
 /* ---- benchmark input side ("cfg5") ----
  * Synthetic stereo pairs generated ON THE DEVICE: frames first_frame_id .. first_frame_id + n_pairs - 1 of
  * the counter-based generator defined by orbslam3_cpp_fork_b200/synth_cb.py (integer arithmetic only; the

@@ -22,7 +22,7 @@ assert KP_DTYPE.itemsize == 28  # cv::KeyPoint
 E_EMPTY, E_BADARG, E_CAPACITY, E_CUDA, E_UNSUPPORTED, E_STATE = -1, -2, -3, -4, -5, -6
 MEM_HOST, MEM_DEVICE = 0, 1
 STAGES = ("h2d", "pyramid", "fast", "octree", "blur", "describe", "stereo")
-MP_IN_VIEW, MP_BAD, MP_HAS_OBS = 1, 2, 4
+MP_IN_VIEW, MP_BAD, MP_HAS_OBS, MP_IN_VIEW_R = 1, 2, 4, 8
 
 
 class CuorbError(RuntimeError):
@@ -97,6 +97,10 @@ SIGNATURES = {
                                    [C.c_float, C.c_int, C.c_float, C.c_float, C.c_void_p]),
     "cuorb_search_by_projection_frame": (C.c_int, [C.c_int, C.POINTER(FrameView), C.c_int] + [C.c_void_p] * 7 +
                                          [C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "cuorb_search_by_projection_rig": (C.c_int, [C.c_int, C.POINTER(FrameView), C.POINTER(FrameView), C.c_void_p, C.c_void_p, C.c_int] +
+                                       [C.c_void_p] * 11 + [C.c_float, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p]),
+    "cuorb_search_by_projection_frame_rig": (C.c_int, [C.c_int, C.POINTER(FrameView), C.POINTER(FrameView), C.c_int] + [C.c_void_p] * 9 +
+                                             [C.c_float, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 5),
     "cuorb_preproc_create": (C.c_void_p, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                           C.c_void_p, C.c_int]),
     "cuorb_preproc_destroy": (None, [C.c_void_p]),

@@ -14,7 +14,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 OUT = os.path.join(PKG, "libcuorb.so")
 OBJ = os.path.join(PKG, "csrc", "_obj")
-SOURCES = ["pyramid.cu", "blur.cu", "fast.cu", "octree.cu", "describe.cu", "stereo.cu", "project.cu",
+SOURCES = ["pyramid.cu", "blur.cu", "fast.cu", "octree.cu", "describe.cu", "stereo.cu", "project.cu", "rig.cu",
            "preproc.cu", "frameglue.cu", "bfmatch.cu", "bow.cu", "search.cu", "synth.cu", "cuorb_api.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC,-ffp-contract=off"]

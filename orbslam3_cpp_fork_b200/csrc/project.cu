@@ -29,7 +29,9 @@ struct ProjQuery {
   const int* level;            // predicted level (mode 0) or last octave (mode 1)
   const float *viewcos, *depth;
   const uint8_t* flags;
-  int mode;                    // 0: local-map points, 1: last-frame points
+  int mode;                    // 0: local-map points, 1: last-frame points, 2: last-frame points into the right camera of a rig
+  int* gate_out;               // optional: 1 where GetFeaturesInArea returned a non-empty window (binding independent)
+  const int* gate_in;          // mode 2: the left pass's gate_out (the right part sits behind the left part's `continue`s)
   float th, thFar, nnratio;
   int far_points, forward, backward;
 };
@@ -58,8 +60,10 @@ __global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, ProjQuery Q,
       rad = __fmul_rn(r, F.scale[lvl]);
       minLevel = lvl - 1; maxLevel = lvl;
     } else {
-      if (Q.aux[i] < 0.f) active = false;                        // invzc < 0 (:1717)
-      if (x < F.minX || x > F.maxX || y < F.minY || y > F.maxY) active = false;
+      if (Q.mode == 1) {
+        if (Q.aux[i] < 0.f) active = false;                      // invzc < 0 (:1717)
+        if (x < F.minX || x > F.maxX || y < F.minY || y > F.maxY) active = false;
+      } else if (!Q.gate_in[i]) active = false;                  // :1812-1886: no tests of its own
       rad = __fmul_rn(Q.th, F.scale[lvl]);
       if (Q.forward) { minLevel = lvl; maxLevel = -1; }
       else if (Q.backward) { minLevel = 0; maxLevel = lvl; }
@@ -101,6 +105,7 @@ __global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, ProjQuery Q,
     const uint4 q0 = qd[0], q1 = qd[1];
     const float aux = Q.aux ? Q.aux[i] : 0.f;
     unsigned long long b1 = ~0ull, b2 = ~0ull;  // (dist << 32 | visiting position), two smallest
+    bool any_cand = false;
     // GetFeaturesInArea: only the features of the window's cells are visited (cell-sorted CSR); the reference's
     // visiting order is carried by the key, so the iteration order here is free
     for (int cy = cy0; cy <= cy1; cy++) {
@@ -114,6 +119,7 @@ __global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, ProjQuery Q,
         if (maxLevel >= 0 && oct > maxLevel) continue;
       }
       if (!(fabsf(__fsub_rn(F.x[f], x)) < rad && fabsf(__fsub_rn(F.y[f], y)) < rad)) continue;
+      any_cand = true;
       if (F.blocked0[f] || binder_prev[f] < i) continue;
       if (F.uright) {
         const float ur = F.uright[f];
@@ -127,6 +133,10 @@ __global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, ProjQuery Q,
       if (key < b1) { b2 = b1; b1 = key; }
       else if (key < b2) b2 = key;
      }
+    }
+    if (Q.gate_out) {
+      const bool any = __any_sync(0xffffffffu, any_cand);
+      if (lane == 0) Q.gate_out[i] = any ? 1 : 0;
     }
     unsigned long long B1 = b1;
 #pragma unroll
@@ -178,18 +188,23 @@ thread_local Arena t_arena;
 static int run_projection(int device, const cuorb_frame_view* fv, ProjQuery Q, const uint8_t* qdesc,
                           const float* px, const float* py, const float* aux, const int32_t* level,
                           const float* viewcos, const float* depth, const uint8_t* flags,
-                          int32_t* result_out) {
+                          int32_t* result_out, int32_t* gate_out_host = nullptr, const int32_t* gate_in_host = nullptr,
+                          bool ignore_uright = false) {
   const int n = fv->n, m = Q.n;
   if (n > 65535 || fv->nlevels > MAX_LEVELS) { set_error("frame too large for projection search"); return CUORB_E_UNSUPPORTED; }
   for (int i = 0; i < m; i++) result_out[i] = -1;
   if (n <= 0 || m <= 0) return 0;
   CUORB_CUDA_TRY(cudaSetDevice(device));
-  const size_t bytes = frame_bytes(n) + (size_t)m * (32 + 6 * 4 + 1 + 4) + 64 * 1024;
+  const size_t bytes = frame_bytes(n) + (size_t)m * (32 + 6 * 4 + 1 + 4 + 8) + 64 * 1024;
   if (t_arena.reserve(device, bytes) != 0) { set_error("cudaMalloc failed (projection workspace)"); return CUORB_E_CUDA; }
   Arena& A = t_arena;
   cudaStream_t st = cudaStreamPerThread;
   ProjFrame F;
   upload_frame(A, fv, st, F);
+  if (ignore_uright) F.uright = nullptr;                 // rig frames: the mvuRight gate is pinhole-only (:103, :1770)
+  Q.gate_out = gate_out_host ? A.take<int>(m) : nullptr;
+  Q.gate_in = gate_in_host ? up(A, gate_in_host, m, st) : nullptr;
+  if (Q.gate_out) CUORB_CUDA_TRY(cudaMemsetAsync(Q.gate_out, 0, sizeof(int) * m, st));
   Q.desc = up(A, qdesc, (size_t)m * 32, st);
   Q.px = up(A, px, m, st); Q.py = up(A, py, m, st);
   Q.aux = aux ? up(A, aux, m, st) : nullptr;
@@ -235,6 +250,7 @@ static int run_projection(int device, const cuorb_frame_view* fv, ProjQuery Q, c
       if (!h_flag[k]) { converged = true; rounds -= ROUND_BATCH - 1 - k; break; }   // rounds to the first quiet one, inclusive
   }
   CUORB_CUDA_TRY(cudaMemcpyAsync(result_out, result, sizeof(int) * m, cudaMemcpyDeviceToHost, st));
+  if (gate_out_host) CUORB_CUDA_TRY(cudaMemcpyAsync(gate_out_host, Q.gate_out, sizeof(int) * m, cudaMemcpyDeviceToHost, st));
   CUORB_CUDA_TRY(cudaStreamSynchronize(st));
   return rounds;
 }
@@ -296,6 +312,71 @@ int cuorb_search_by_projection_frame(int device, const cuorb_frame_view* cur, in
       if (bin < 0 || bin >= HISTO_LENGTH) { set_error("keypoint angle outside [0,360)"); return CUORB_E_BADARG; }
       hist[bin]++;
       rot_bin_out[i] = bin;
+    }
+  }
+  keep_bins_out[0] = keep_bins_out[1] = keep_bins_out[2] = -1;
+  if (check_orientation) {
+    int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+    for (int i = 0; i < HISTO_LENGTH; i++) {
+      const int s = hist[i];
+      if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+      else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+      else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+    keep_bins_out[0] = ind1; keep_bins_out[1] = ind2; keep_bins_out[2] = ind3;
+    for (int i = 0; i < HISTO_LENGTH; i++)
+      if (i != ind1 && i != ind2 && i != ind3) nmatches -= hist[i];
+  }
+  return nmatches;
+}
+
+int cuorb_search_by_projection_frame_rig(int device, const cuorb_frame_view* left, const cuorb_frame_view* right,
+                                         int n_last, const uint8_t* last_desc, const float* u, const float* v,
+                                         const float* inv_z, const float* ur, const float* vr,
+                                         const int32_t* last_octave, const float* last_angle, const uint8_t* flags,
+                                         float th, int forward, int backward, int check_orientation,
+                                         int32_t* best_l_out, int32_t* best_r_out, int32_t* rot_bin_l_out,
+                                         int32_t* rot_bin_r_out, int32_t* keep_bins_out) {
+  if (!left || !right || !left->keys_un || !right->keys_un || !left->descriptors || !right->descriptors ||
+      !left->scale_factors || !right->scale_factors || n_last < 0 || !keep_bins_out ||
+      (n_last && (!last_desc || !u || !v || !inv_z || !ur || !vr || !last_octave || !last_angle || !flags || !best_l_out ||
+                  !best_r_out || !rot_bin_l_out || !rot_bin_r_out))) {
+    set_error("cuorb_search_by_projection_frame_rig: null argument");
+    return CUORB_E_BADARG;
+  }
+  // The two cameras' features live in disjoint index ranges and this overload makes no cross-writes, so the two
+  // parts are two independent searches; the right one only runs for points whose left window was not empty
+  // (src/ORBmatcher.cc:1750-1752 `continue`s past it) and that passed the left part's depth / bounds tests.
+  std::vector<int32_t> gate((size_t)std::max(n_last, 1), 0);
+  ProjQuery Q{};
+  Q.n = n_last; Q.mode = 1; Q.th = th; Q.forward = forward; Q.backward = backward;
+  int rc = run_projection(device, left, Q, last_desc, u, v, inv_z, last_octave, nullptr, nullptr, flags, best_l_out,
+                          gate.data(), nullptr, true);
+  if (rc < 0) return rc;
+  Q.mode = 2;
+  rc = run_projection(device, right, Q, last_desc, ur, vr, nullptr, last_octave, nullptr, nullptr, flags, best_r_out,
+                      nullptr, gate.data(), true);
+  if (rc < 0) return rc;
+  const int HISTO_LENGTH = 30;
+  const float factor = 1.0f / HISTO_LENGTH;
+  int hist[HISTO_LENGTH] = {0};
+  int nmatches = 0;
+  for (int i = 0; i < n_last; i++) {
+    rot_bin_l_out[i] = rot_bin_r_out[i] = -1;
+    for (int side = 0; side < 2; side++) {
+      const int best = side ? best_r_out[i] : best_l_out[i];
+      if (best < 0) continue;
+      nmatches++;
+      if (!check_orientation) continue;
+      float rot = last_angle[i] - (side ? right : left)->keys_un[best].angle;    // :1793-1806, :1866-1884
+      if (rot < 0.0) rot += 360.0f;
+      int bin = (int)std::round(rot * factor);
+      if (bin == HISTO_LENGTH) bin = 0;
+      if (bin < 0 || bin >= HISTO_LENGTH) { set_error("keypoint angle outside [0,360)"); return CUORB_E_BADARG; }
+      hist[bin]++;
+      (side ? rot_bin_r_out : rot_bin_l_out)[i] = bin;
     }
   }
   keep_bins_out[0] = keep_bins_out[1] = keep_bins_out[2] = -1;

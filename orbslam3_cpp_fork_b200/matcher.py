@@ -197,6 +197,86 @@ class ORBmatcher:
         return n, best, rot, keepb
 
 
+@dataclass
+class RigFrame:
+    """A two-camera Frame (Nleft != -1): the left camera's features are indices [0, Nleft) of the reference's arrays
+    (mvKeys, mGrid), the right camera's [Nleft, N) (mvKeysRight, mGridRight, descriptor rows idx + Nleft).  Held as two
+    Frame mirrors that share bounds / scale factors; mvpMapPoints of the reference = left.mvpMapPoints followed by
+    right.mvpMapPoints."""
+    left: Frame
+    right: Frame
+    mvLeftToRightMatch: np.ndarray      # i32 [Nleft],  -1 = no stereo partner
+    mvRightToLeftMatch: np.ndarray      # i32 [Nright]
+
+    def __post_init__(self):
+        self.mvLeftToRightMatch = np.ascontiguousarray(self.mvLeftToRightMatch, np.int32)
+        self.mvRightToLeftMatch = np.ascontiguousarray(self.mvRightToLeftMatch, np.int32)
+        self.Nleft, self.Nright = self.left.N, self.right.N
+
+    def _write(self, side, idx, who, has_obs):
+        f = self.right if side else self.left
+        f.mvpMapPoints[idx] = who
+        f.mvpHasObs[idx] = 1 if has_obs else 0
+
+
+def SearchByProjectionRig(self, F: RigFrame, mp_desc, px, py, level, view_cos, pxr, pyr, level_r, view_cos_r, depth, flags,
+                          th=3.0, bFarPoints=False, thFarPoints=50.0):
+    """int SearchByProjection(Frame&, vpMapPoints, th, bFarPoints, thFarPoints) with F.Nleft != -1
+    (src/ORBmatcher.cc:38-227).  Returns (nmatches, best_l, best_r) and replays the reference's writes into
+    F.left / F.right mvpMapPoints in MapPoint order, stereo partners included (:138-142, :212-216)."""
+    fvl, keep_l = F.left.view(); fvr, keep_r = F.right.view()
+    flags = _c(flags, np.uint8)
+    arrs = [_c(mp_desc, np.uint8), _c(px, np.float32), _c(py, np.float32), _c(level, np.int32), _c(view_cos, np.float32),
+            _c(pxr, np.float32), _c(pyr, np.float32), _c(level_r, np.int32), _c(view_cos_r, np.float32), _c(depth, np.float32), flags]
+    M = len(arrs[1])
+    bl = np.full(max(M, 1), -1, np.int32); br = np.full(max(M, 1), -1, np.int32)
+    n = check(self._L.cuorb_search_by_projection_rig(self.device, C.byref(fvl), C.byref(fvr), ptr(F.mvLeftToRightMatch),
+                                                     ptr(F.mvRightToLeftMatch), M, *[ptr(a) for a in arrs], th, int(bFarPoints),
+                                                     thFarPoints, self.mfNNratio, ptr(bl), ptr(br)))
+    bl, br = bl[:M], br[:M]
+    for i in np.nonzero((bl >= 0) | (br >= 0))[0]:
+        obs = bool(flags[i] & _lib.MP_HAS_OBS)
+        if bl[i] >= 0:
+            F._write(0, bl[i], i, obs)
+            if F.mvLeftToRightMatch[bl[i]] != -1:
+                F._write(1, F.mvLeftToRightMatch[bl[i]], i, obs)
+        if br[i] >= 0:
+            if F.mvRightToLeftMatch[br[i]] != -1:
+                F._write(0, F.mvRightToLeftMatch[br[i]], i, obs)
+            F._write(1, br[i], i, obs)
+    return n, bl, br
+
+
+def SearchByProjectionLastFrameRig(self, Cur: RigFrame, last_desc, u, v, inv_z, ur, vr, last_octave, last_angle, flags, th,
+                                   bForward=False, bBackward=False):
+    """int SearchByProjection(Frame& Cur, const Frame& Last, th, bMono) with CurrentFrame.Nleft != -1
+    (src/ORBmatcher.cc:1684-1908); (ur, vr) = project(Trl * x3Dc).  Returns (nmatches, best_l, best_r, rot_l, rot_r, keep)."""
+    fvl, keep_l = Cur.left.view(); fvr, keep_r = Cur.right.view()
+    flags = _c(flags, np.uint8)
+    arrs = [_c(last_desc, np.uint8), _c(u, np.float32), _c(v, np.float32), _c(inv_z, np.float32), _c(ur, np.float32),
+            _c(vr, np.float32), _c(last_octave, np.int32), _c(last_angle, np.float32), flags]
+    n_last = len(arrs[1])
+    outs = [np.full(max(n_last, 1), -1, np.int32) for _ in range(4)] + [np.full(3, -1, np.int32)]
+    n = check(self._L.cuorb_search_by_projection_frame_rig(self.device, C.byref(fvl), C.byref(fvr), n_last, *[ptr(a) for a in arrs],
+                                                           th, int(bForward), int(bBackward), int(self.mbCheckOrientation),
+                                                           *[ptr(o) for o in outs]))
+    bl, br, rl, rr = (o[:n_last] for o in outs[:4])
+    keepb = outs[4]
+    for i in range(n_last):
+        obs = bool(flags[i] & _lib.MP_HAS_OBS)
+        if bl[i] >= 0: Cur._write(0, bl[i], i, obs)
+        if br[i] >= 0: Cur._write(1, br[i], i, obs)
+    if self.mbCheckOrientation:
+        for i in range(n_last):
+            if bl[i] >= 0 and rl[i] not in keepb: Cur.left.mvpMapPoints[bl[i]] = -1
+            if br[i] >= 0 and rr[i] not in keepb: Cur.right.mvpMapPoints[br[i]] = -1
+    return n, bl, br, rl, rr, keepb
+
+
+ORBmatcher.SearchByProjectionRig = SearchByProjectionRig
+ORBmatcher.SearchByProjectionLastFrameRig = SearchByProjectionLastFrameRig
+
+
 def join_feature_vectors(mFeatVec1, mFeatVec2):
     """The merge-join SearchByBoW does over two DBoW2::FeatureVectors (std::map<NodeId, std::vector<unsigned>>,
     src/ORBmatcher.cc:252-259, 395-399): common nodes in ascending NodeId order.

@@ -4,7 +4,8 @@
 // Frame / MapPoint types so the very same header compiles against the reference's real classes
 // (member names below are the reference's) and against the small structs of tests/native.
 // The pointer graph is flattened to SoA on the host, matched by libcuorb, and the bindings
-// F.mvpMapPoints[idx] = pMP are replayed in the reference's order.  Pinhole (Nleft == -1) only.
+// F.mvpMapPoints[idx] = pMP are replayed in the reference's order.  The two tracking-time SearchByProjection
+// overloads also take two-camera rig Frames (Nleft != -1); the other searches are pinhole (Nleft == -1) only.
 #pragma once
 #include <cmath>
 #include <cstring>
@@ -87,7 +88,7 @@ public:
   template <class FrameT, class MapPointT>
   int SearchByProjection(FrameT& F, const std::vector<MapPointT*>& vpMapPoints, const float th = 3,
                          const bool bFarPoints = false, const float thFarPoints = 50.0f) {
-    if (F.Nleft != -1) CUORB_SHIM_FAIL(std::runtime_error, "ORBmatcher shim: fisheye (Nleft != -1) branch is not built", 0);
+    if (F.Nleft != -1) return SearchByProjectionRig(F, vpMapPoints, th, bFarPoints, thFarPoints);
     const int M = (int)vpMapPoints.size();
     if (M == 0 || F.N == 0) return 0;
     std::vector<uint8_t> desc((size_t)M * 32), flags(M);
@@ -113,8 +114,50 @@ public:
     return n;
   }
 
+  // The same call on a two-camera rig Frame (F.Nleft != -1; src/ORBmatcher.cc:63-150 with the rig conditions and
+  // the right part :152-224).  The writes are replayed as the reference makes them, in MapPoint order: the matched
+  // slot and the stereo partner's slot on the other camera (:138-142, :212-216).
+  template <class FrameT, class MapPointT>
+  int SearchByProjectionRig(FrameT& F, const std::vector<MapPointT*>& vpMapPoints, const float th, const bool bFarPoints,
+                            const float thFarPoints) {
+    const int M = (int)vpMapPoints.size();
+    if (M == 0 || F.N == 0) return 0;
+    std::vector<uint8_t> desc((size_t)M * 32), flags(M);
+    std::vector<float> px(M), py(M), pxr(M), pyr(M), vc(M), vcr(M), dep(M);
+    std::vector<int32_t> lvl(M), lvlr(M), bl(M, -1), br(M, -1);
+    for (int i = 0; i < M; i++) {
+      MapPointT* p = vpMapPoints[i];
+      flags[i] = (p->mbTrackInView ? CUORB_MP_IN_VIEW : 0) | (p->mbTrackInViewR ? CUORB_MP_IN_VIEW_R : 0) |
+                 (p->isBad() ? CUORB_MP_BAD : 0) | (p->Observations() > 0 ? CUORB_MP_HAS_OBS : 0);
+      px[i] = p->mTrackProjX; py[i] = p->mTrackProjY; lvl[i] = p->mnTrackScaleLevel; vc[i] = p->mTrackViewCos;
+      pxr[i] = p->mTrackProjXR; pyr[i] = p->mTrackProjYR; lvlr[i] = p->mnTrackScaleLevelR; vcr[i] = p->mTrackViewCosR;
+      dep[i] = p->mTrackDepth;
+      const cv::Mat d = p->GetDescriptor();
+      std::memcpy(&desc[(size_t)i * 32], d.template ptr<unsigned char>(0), 32);
+    }
+    std::vector<uint8_t> boundL, boundR;
+    cuorb_frame_view vl, vr;
+    rig_views(F, boundL, boundR, vl, vr);
+    const int n = cuorb_search_by_projection_rig(device_, &vl, &vr, F.mvLeftToRightMatch.data(), F.mvRightToLeftMatch.data(), M,
+                                                 desc.data(), px.data(), py.data(), lvl.data(), vc.data(), pxr.data(), pyr.data(),
+                                                 lvlr.data(), vcr.data(), dep.data(), flags.data(), th, bFarPoints ? 1 : 0,
+                                                 thFarPoints, mfNNratio, bl.data(), br.data());
+    if (n < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("SearchByProjection (rig, libcuorb): ") + cuorb_last_error(), 0);
+    for (int i = 0; i < M; i++) {
+      if (bl[i] >= 0) {
+        F.mvpMapPoints[bl[i]] = vpMapPoints[i];                                                   // :136
+        if (F.mvLeftToRightMatch[bl[i]] != -1) F.mvpMapPoints[F.mvLeftToRightMatch[bl[i]] + F.Nleft] = vpMapPoints[i];
+      }
+      if (br[i] >= 0) {
+        if (F.mvRightToLeftMatch[br[i]] != -1) F.mvpMapPoints[F.mvRightToLeftMatch[br[i]]] = vpMapPoints[i];   // :212-216
+        F.mvpMapPoints[br[i] + F.Nleft] = vpMapPoints[i];
+      }
+    }
+    return n;
+  }
+
   // int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono)
-  // (include/ORBmatcher.h:54-56, src/ORBmatcher.cc:1684-1908; pinhole branch) - Tracking::TrackWithMotionModel.
+  // (include/ORBmatcher.h:54-56, src/ORBmatcher.cc:1684-1908) - Tracking::TrackWithMotionModel.
   // The geometric prologue (:1696-1721) runs here on the caller's own Sophus / Eigen types, in the reference's
   // expression order; the window search, the "already bound" skip, the uRight gate, the rotation histogram and
   // ComputeThreeMaxima run in libcuorb; the bindings are then replayed exactly as the reference makes them:
@@ -122,8 +165,7 @@ public:
   // has no observations), and afterwards the features of every non-kept histogram bin are set to NULL (:1889-1905).
   template <class FrameT>
   int SearchByProjection(FrameT& CurrentFrame, const FrameT& LastFrame, const float th, const bool bMono) {
-    if (CurrentFrame.Nleft != -1 || LastFrame.Nleft != -1)
-      CUORB_SHIM_FAIL(std::runtime_error, "ORBmatcher shim: fisheye (Nleft != -1) branch is not built", 0);
+    const bool rig = CurrentFrame.Nleft != -1;
     const int NL = LastFrame.N;
     if (NL == 0 || CurrentFrame.N == 0) return 0;
     const auto Tcw = CurrentFrame.GetPose();                         // :1696
@@ -133,8 +175,9 @@ public:
     const bool bForward  = tlc(2) > CurrentFrame.mb && !bMono;       // :1702
     const bool bBackward = -tlc(2) > CurrentFrame.mb && !bMono;      // :1703
     std::vector<uint8_t> desc((size_t)NL * 32, 0), flags(NL, 0);
-    std::vector<float> u(NL, 0.f), v(NL, 0.f), invz(NL, 0.f), ang(NL, 0.f);
+    std::vector<float> u(NL, 0.f), v(NL, 0.f), invz(NL, 0.f), ang(NL, 0.f), ur, vr;
     std::vector<int32_t> oct(NL, 0), best(NL, -1), bin(NL, -1);
+    if (rig) { ur.assign(NL, 0.f); vr.assign(NL, 0.f); }
     for (int i = 0; i < NL; i++) {
       auto* pMP = LastFrame.mvpMapPoints[i];
       if (!pMP || LastFrame.mvbOutlier[i]) continue;                 // :1706-1708
@@ -144,15 +187,45 @@ public:
       if (invzc < 0) continue;                                       // :1717
       const auto uv = CurrentFrame.mpCamera->project(x3Dc);          // :1721; the image-bounds test (:1723-1728) is libcuorb's
       u[i] = uv(0); v[i] = uv(1); invz[i] = invzc;
-      oct[i] = LastFrame.mvKeys[i].octave;                           // :1730-1732
-      ang[i] = LastFrame.mvKeysUn[i].angle;                          // :1793 (kpLF, Nleft == -1)
+      const bool lastRight = LastFrame.Nleft != -1 && i >= LastFrame.Nleft;
+      oct[i] = lastRight ? LastFrame.mvKeysRight[i - LastFrame.Nleft].octave : LastFrame.mvKeys[i].octave;   // :1730-1732
+      ang[i] = LastFrame.Nleft == -1 ? LastFrame.mvKeysUn[i].angle                                            // :1793-1795
+               : lastRight ? LastFrame.mvKeysRight[i - LastFrame.Nleft].angle : LastFrame.mvKeys[i].angle;
+      if (rig) {                                                     // :1813-1814 (through mpCamera, as the reference does)
+        const auto x3Dr = CurrentFrame.GetRelativePoseTrl() * x3Dc;
+        const auto uvr = CurrentFrame.mpCamera->project(x3Dr);
+        ur[i] = uvr(0); vr[i] = uvr(1);
+      }
       flags[i] = (uint8_t)(CUORB_MP_IN_VIEW | (pMP->Observations() > 0 ? CUORB_MP_HAS_OBS : 0));   // :1763-1767
       const cv::Mat d = pMP->GetDescriptor();
       std::memcpy(&desc[(size_t)i * 32], d.template ptr<unsigned char>(0), 32);
     }
+    int32_t keep[3] = {-1, -1, -1};
+    if (rig) {
+      std::vector<uint8_t> boundL, boundR;
+      cuorb_frame_view vl, vrv;
+      rig_views(CurrentFrame, boundL, boundR, vl, vrv);
+      std::vector<int32_t> bestR(NL, -1), binR(NL, -1);
+      const int n = cuorb_search_by_projection_frame_rig(device_, &vl, &vrv, NL, desc.data(), u.data(), v.data(), invz.data(),
+                                                         ur.data(), vr.data(), oct.data(), ang.data(), flags.data(), th,
+                                                         bForward ? 1 : 0, bBackward ? 1 : 0, mbCheckOrientation ? 1 : 0,
+                                                         best.data(), bestR.data(), bin.data(), binR.data(), keep);
+      if (n < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("SearchByProjection(Cur, Last) (rig, libcuorb): ") + cuorb_last_error(), 0);
+      const int nl = CurrentFrame.Nleft;
+      for (int i = 0; i < NL; i++) {                                 // :1786, :1863, in last-frame order
+        if (best[i] >= 0) CurrentFrame.mvpMapPoints[best[i]] = LastFrame.mvpMapPoints[i];
+        if (bestR[i] >= 0) CurrentFrame.mvpMapPoints[bestR[i] + nl] = LastFrame.mvpMapPoints[i];
+      }
+      if (mbCheckOrientation)                                        // :1889-1905
+        for (int i = 0; i < NL; i++) {
+          if (best[i] >= 0 && bin[i] != keep[0] && bin[i] != keep[1] && bin[i] != keep[2]) CurrentFrame.mvpMapPoints[best[i]] = nullptr;
+          if (bestR[i] >= 0 && binR[i] != keep[0] && binR[i] != keep[1] && binR[i] != keep[2])
+            CurrentFrame.mvpMapPoints[bestR[i] + nl] = nullptr;
+        }
+      return n;
+    }
     std::vector<uint8_t> bound;
     const cuorb_frame_view fv = view(CurrentFrame, bound);
-    int32_t keep[3] = {-1, -1, -1};
     const int n = cuorb_search_by_projection_frame(device_, &fv, NL, desc.data(), u.data(), v.data(), invz.data(), oct.data(),
                                                    ang.data(), flags.data(), th, bForward ? 1 : 0, bBackward ? 1 : 0,
                                                    mbCheckOrientation ? 1 : 0, best.data(), bin.data(), keep);
@@ -423,6 +496,29 @@ private:
   static const uint8_t* contiguous(const cv::Mat& m) {
     if (m.rows > 1 && m.step != 32) CUORB_SHIM_FAIL(std::runtime_error, "descriptor matrix must be n x 32 contiguous", nullptr);
     return m.ptr<unsigned char>(0);
+  }
+
+  // a two-camera rig Frame as the two views libcuorb takes: left = features [0, Nleft) (mvKeys), right = features
+  // [Nleft, N) (mvKeysRight, descriptor rows idx + Nleft)
+  template <class FrameT>
+  static void rig_views(FrameT& F, std::vector<uint8_t>& boundL, std::vector<uint8_t>& boundR, cuorb_frame_view& vl,
+                        cuorb_frame_view& vr) {
+    const int nl = F.Nleft, nr = F.N - F.Nleft;
+    const unsigned char* d = contiguous(F.mDescriptors);
+    boundL.assign(nl > 0 ? nl : 1, 0); boundR.assign(nr > 0 ? nr : 1, 0);
+    for (int i = 0; i < F.N; i++) {
+      const uint8_t b = (F.mvpMapPoints[i] && F.mvpMapPoints[i]->Observations() > 0) ? 1 : 0;
+      if (i < nl) boundL[i] = b; else boundR[i - nl] = b;
+    }
+    vl.n = nl; vl.keys_un = (const cuorb_keypoint*)F.mvKeys.data(); vl.descriptors = d; vl.u_right = nullptr;
+    vl.bound_with_obs = boundL.data();
+    vl.min_x = F.mnMinX; vl.min_y = F.mnMinY; vl.max_x = F.mnMaxX; vl.max_y = F.mnMaxY;
+    vl.grid_w_inv = F.mfGridElementWidthInv; vl.grid_h_inv = F.mfGridElementHeightInv;
+    vl.mb = F.mb; vl.mbf = F.mbf;
+    vl.nlevels = (int)F.mvScaleFactors.size(); vl.scale_factors = F.mvScaleFactors.data();
+    vr = vl;
+    vr.n = nr; vr.keys_un = (const cuorb_keypoint*)F.mvKeysRight.data(); vr.descriptors = d + (size_t)nl * 32;
+    vr.bound_with_obs = boundR.data();
   }
 
   // the Frame members the matchers read (src/ORBmatcher.cc:73-111; src/Frame.cc:788-877)

@@ -20,6 +20,7 @@ namespace ORB_SLAM3 {
 float Frame::fx = 0, Frame::fy = 0, Frame::cx = 0, Frame::cy = 0, Frame::invfx = 0, Frame::invfy = 0;
 float Frame::mnMinX = 0, Frame::mnMinY = 0, Frame::mnMaxX = 0, Frame::mnMaxY = 0;
 float Frame::mfGridElementWidthInv = 0, Frame::mfGridElementHeightInv = 0;
+Sophus::SE3f Frame::GetRelativePoseTrl() { return mTrl; }   // src/Frame.cc:628-630 (only called for rig Frames)
 }  // namespace ORB_SLAM3
 
 using namespace ORB_SLAM3;

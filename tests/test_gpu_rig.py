@@ -1,0 +1,87 @@
+"""GPU (-m gpu): the two-camera (Frame::Nleft != -1) branches of the tracking-time searches through the C ABI against
+the reference's OWN functions (oracle/_ref, oracle/ref_compat/ref_capi_rig.cpp) and against the oracle's restatement
+(oracle/rig_oracle.cpp).  Bit-exact: per-MapPoint matches on both cameras, the match count with its cross-bound stereo
+partners, the final F.mvpMapPoints over both cameras, rotation bins and kept bins."""
+import numpy as np
+import pytest
+
+from oracle import oracle_py as op
+from oracle import ref_py as rp
+from tests.rig_cases import H, W, frame_views, rig_lastframe, rig_mappoints, rig_replay, rig_replay_lastframe, rig_views
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def rv():
+    return rig_views(9, nf=1200)
+
+
+def _rig(rv):
+    from orbslam3_cpp_fork_b200.matcher import Frame, RigFrame
+    L = Frame(rv["k1"], rv["d1"], rv["sf"], W, H, mb=0.1, mbf=40.0)
+    R = Frame(rv["k2"], rv["d2"], rv["sf"], W, H, mb=0.1, mbf=40.0)
+    for f, b in ((L, rv["bound_l"]), (R, rv["bound_r"])):
+        f.mvpMapPoints[b > 0] = 10 ** 6; f.mvpHasObs[b > 0] = 1
+    return RigFrame(L, R, rv["l2r"], rv["r2l"])
+
+
+def _final(F):
+    out = np.concatenate([F.left.mvpMapPoints, F.right.mvpMapPoints]).astype(np.int64)
+    out[out == 10 ** 6] = -2
+    return out.astype(np.int32)
+
+
+@pytest.mark.parametrize("seed,M,th,far,no_obs,ratio", [(1, 20000, 1.0, False, 0.1, 0.8), (2, 8000, 3.0, True, 0.0, 0.8),
+                                                      (3, 5000, 3.0, False, 0.5, 0.9), (4, 50000, 1.0, False, 0.02, 0.6)])
+def test_mappoints_rig(rv, seed, M, th, far, no_obs, ratio):
+    from orbslam3_cpp_fork_b200 import ORBmatcher
+    q = rig_mappoints(rv, M, seed, no_obs_frac=no_obs)
+    args = [q[k] for k in ("desc", "px", "py", "level", "view_cos", "pxr", "pyr", "level_r", "view_cos_r", "depth", "flags")]
+    F = _rig(rv)
+    n, bl, br = ORBmatcher(ratio, True).SearchByProjectionRig(F, *args, th, far, 40.0)
+    fvl, fvr, keep = frame_views(rv)
+    on, obl, obr = op.search_by_projection_rig(fvl, fvr, rv["l2r"], rv["r2l"], *args, th, far, 40.0, ratio)
+    assert n == on and (bl == obl).all() and (br == obr).all()
+    assert (bl >= 0).sum() > 300 and (br >= 0).sum() > 300 and n - (bl >= 0).sum() - (br >= 0).sum() > 200
+    bind, cnt, per = rig_replay(bl, br, rv)
+    assert cnt == n and (_final(F) == bind).all()                 # the mirror's replay == the documented rule
+    if rp.available() and M <= 20000:
+        fvl, fvr, keep = frame_views(rv)
+        rn, rbind, rper = rp.search_by_projection_rig(fvl, fvr, rv["l2r"], rv["r2l"], *args, th, far, 40.0, ratio)
+        assert rn == n and (rbind == bind).all() and (rper == per).all()
+
+
+@pytest.mark.parametrize("seed,fwd,bwd,th,ori", [(1, False, False, 7.0, True), (2, True, False, 15.0, True),
+                                                (3, False, True, 7.0, True), (4, False, False, 15.0, False)])
+def test_lastframe_rig(rv, seed, fwd, bwd, th, ori):
+    from orbslam3_cpp_fork_b200 import ORBmatcher
+    q = rig_lastframe(rv, seed)
+    F = _rig(rv)
+    n, bl, br, rl, rr, kb = ORBmatcher(0.9, ori).SearchByProjectionLastFrameRig(F, q["desc"], q["u"], q["v"], q["inv_z"], q["ur"],
+                                                                                q["vr"], q["octave"], q["angle"], q["flags"], th, fwd, bwd)
+    fvl, fvr, keep = frame_views(rv)
+    o = op.search_by_projection_frame_rig(fvl, fvr, q["desc"], q["u"], q["v"], q["inv_z"], q["ur"], q["vr"], q["octave"], q["angle"],
+                                          q["flags"], th, fwd, bwd, ori)
+    assert n == o[0] and (bl == o[1]).all() and (br == o[2]).all() and (kb == o[5]).all()
+    if ori:
+        assert (rl == o[3]).all() and (rr == o[4]).all()
+    assert (bl >= 0).sum() > 100 and (br >= 0).sum() > 100
+    bind, cnt = rig_replay_lastframe(bl, br, rl, rr, kb, rv, ori)
+    assert cnt == n and (_final(F) == bind).all()
+    if rp.available():
+        fvl, fvr, keep = frame_views(rv)
+        rn, rbind = rp.search_by_projection_frame_rig(fvl, fvr, q["desc"], q["u"], q["v"], q["z"], q["trl"][0], q["trl"][1],
+                                                      q["octave"], q["angle"], q["flags"], th, fwd, bwd, ori)
+        assert rn == n and (rbind == bind).all()
+
+
+def test_rig_degenerate(rv):
+    from orbslam3_cpp_fork_b200 import ORBmatcher
+    q = rig_mappoints(rv, 64, 1)
+    args = [q[k] for k in ("desc", "px", "py", "level", "view_cos", "pxr", "pyr", "level_r", "view_cos_r", "depth")]
+    F = _rig(rv)
+    n, bl, br = ORBmatcher().SearchByProjectionRig(F, *args, np.zeros(64, np.uint8), 3.0)          # nothing in view
+    assert n == 0 and (bl == -1).all() and (br == -1).all()
+    n, bl, br = ORBmatcher().SearchByProjectionRig(F, *[a[:0] for a in args], np.zeros(0, np.uint8), 3.0)
+    assert n == 0 and len(bl) == 0

@@ -181,3 +181,55 @@ def test_cpp_shim_search_by_projection_lastframe(tmp_path, motion, th, mono):
     assert (final_s == final_r).all()
     # the order-dependent situation really occurred: fewer bound features than accepted matches + removed ones
     assert (final_r >= 0).sum() <= n_r
+
+
+@pytest.mark.parametrize("which,seed", [("mappoints", 1), ("mappoints", 3), ("lastframe", 1), ("lastframe", 2)])
+def test_cpp_shim_rig_branches(tmp_path, which, seed):
+    """shim/ORBmatcher.h on two-camera rig Frames (Nleft != -1): SearchByProjection(F, vpMapPoints, ...) and
+    SearchByProjection(Cur, Last, ...) leave the same F.mvpMapPoints (both cameras' slots, cross-bound stereo partners,
+    rotation NULLing) and return the same count as the reference's own functions (src/ORBmatcher.cc:38-227, :1684-1908)."""
+    from oracle import ref_py as rp
+    from tests.rig_cases import H, W, frame_views, rig_lastframe, rig_mappoints, rig_views
+    if not rp.available():
+        pytest.skip("oracle/_ref/liborb_ref.so did not travel to this box")
+    build.build_libcuorb()
+    exe = str(tmp_path / "rig_check")
+    pkg = os.path.join(ROOT, "orbslam3_cpp_fork_b200")
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-DCUORB_SHIM_USE_OPENCV",
+                           "-I" + os.path.join(ROOT, "oracle", "ref_compat"),
+                           os.path.join(ROOT, "tests", "native", "rig_check.cpp"), "-o", exe,
+                           "-L" + pkg, "-l:libcuorb.so", "-Wl,-rpath," + pkg])
+    rv = rig_views(9, nf=1200)
+    fvl, fvr, keep = frame_views(rv)
+    th, thfar, ratio, mb, mbf = (1.0 if seed == 1 else 3.0), 40.0, 0.8, 0.1, 40.0
+    case = str(tmp_path / "case.bin"); out = str(tmp_path / "out.bin")
+    if which == "mappoints":
+        q = rig_mappoints(rv, 6000, seed, no_obs_frac=0.1 if seed == 1 else 0.5)
+        n_r, final_r, _ = rp.search_by_projection_rig(fvl, fvr, rv["l2r"], rv["r2l"], q["desc"], q["px"], q["py"], q["level"],
+                                                      q["view_cos"], q["pxr"], q["pyr"], q["level_r"], q["view_cos_r"], q["depth"],
+                                                      q["flags"], th, seed == 3, thfar, ratio)
+        hi = [len(rv["k1"]), len(rv["k2"]), len(rv["sf"]), 6000, int(seed == 3), 0, 1]
+        hf = [th, thfar, ratio, mb, mbf, W, H, 0, 0]
+        tail = [q["desc"], q["px"], q["py"], q["view_cos"], q["pxr"], q["pyr"], q["view_cos_r"], q["depth"], q["level"], q["level_r"],
+                q["flags"]]
+    else:
+        q = rig_lastframe(rv, seed)
+        fwd, th = (seed == 2), (15.0 if seed == 2 else 7.0)
+        n_r, final_r = rp.search_by_projection_frame_rig(fvl, fvr, q["desc"], q["u"], q["v"], q["z"], q["trl"][0], q["trl"][1],
+                                                         q["octave"], q["angle"], q["flags"], th, fwd, False, True)
+        hi = [len(rv["k1"]), len(rv["k2"]), len(rv["sf"]), len(q["u"]), int(fwd), 0, 1]
+        hf = [th, thfar, ratio, mb, mbf, W, H, q["trl"][0], q["trl"][1]]
+        tail = [q["desc"], q["u"], q["v"], q["z"], q["angle"], q["octave"], q["flags"]]
+    with open(case, "wb") as f:
+        np.array(hi, np.int32).tofile(f); np.array(hf, np.float32).tofile(f)
+        np.ascontiguousarray(rv["k1"]).tofile(f); np.ascontiguousarray(rv["k2"]).tofile(f)
+        np.ascontiguousarray(rv["d1"]).tofile(f); np.ascontiguousarray(rv["d2"]).tofile(f)
+        np.concatenate([rv["bound_l"], rv["bound_r"]]).astype(np.uint8).tofile(f)
+        rv["l2r"].tofile(f); rv["r2l"].tofile(f); np.ascontiguousarray(rv["sf"], np.float32).tofile(f)
+        for a in tail:
+            np.ascontiguousarray(a).tofile(f)
+    subprocess.check_call([exe, which, case, out])
+    res = np.fromfile(out, np.int32)
+    assert n_r > 300
+    assert int(res[0]) == n_r
+    assert (res[1:] == final_r).all()
