@@ -11,6 +11,7 @@
 #include <Eigen/Core>
 #include <Thirdparty/DBoW2/DBoW2/FeatureVector.h>
 #include <opencv2/core.hpp>
+#include <opencv2/features2d.hpp>
 #include <sophus/se3.hpp>
 
 namespace ORB_SLAM3 {
@@ -40,6 +41,7 @@ public:
   void SetPose(const Sophus::SE3<float>& Tcw);                      // :568-574
   void UpdatePoseMatrices();                                        // :608-614
   Sophus::SE3f GetRelativePoseTrl();                                // :628-630
+  void ComputeStereoFishEyeMatches();                               // :1303-1355
 
   inline Sophus::SE3<float> GetPose() const { return mTcw; }        // Frame.h:183-186
   inline Eigen::Vector3f    GetCameraCenter() { return mOw; }
@@ -80,6 +82,13 @@ public:
   int              Nleft = -1, Nright = -1;
   std::vector<int> mvLeftToRightMatch, mvRightToLeftMatch;
   std::vector<std::size_t> mGridRight[FRAME_GRID_COLS][FRAME_GRID_ROWS];
+  // two-camera rigs (Frame.h:219-220, 284, 368-378)
+  Eigen::Matrix<float, 3, 3>   mRlr;
+  Eigen::Vector3f              mtlr;
+  int                          mnCloseMPs = 0;
+  int                          monoLeft = 0, monoRight = 0;
+  static cv::BFMatcher         BFmatcher;
+  std::vector<Eigen::Vector3f> mvStereo3Dpoints;
 };
 
 }  // namespace ORB_SLAM3

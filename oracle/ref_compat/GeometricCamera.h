@@ -49,4 +49,22 @@ public:
                          const float unc);
 };
 
+// Stub of include/CameraModels/KannalaBrandt8.h: Frame::ComputeStereoFishEyeMatches static_casts mpCamera to this
+// class and calls TriangulateMatches (src/Frame.cc:1335-1344).  The camera model itself is out of scope (SURVEY.md
+// §2); a harness installs a deterministic stand-in for the triangulation and checks everything around it.
+class KannalaBrandt8 : public GeometricCamera {
+public:
+  KannalaBrandt8() {}
+  cv::Point2f     project(const cv::Point3f& p) override { return cv::Point2f(p.x, p.y); }
+  Eigen::Vector2d project(const Eigen::Vector3d& v) override { return Eigen::Vector2d(v[0], v[1]); }
+  Eigen::Vector2f project(const Eigen::Vector3f& v) override { return Eigen::Vector2f(v[0], v[1]); }
+  bool epipolarConstrain(GeometricCamera*, const cv::KeyPoint&, const cv::KeyPoint&, const Eigen::Matrix3f&,
+                         const Eigen::Vector3f&, const float, const float) override { return false; }
+  float (*triangulate_hook)(const cv::KeyPoint&, const cv::KeyPoint&, float, float, Eigen::Vector3f&) = nullptr;
+  float TriangulateMatches(GeometricCamera*, const cv::KeyPoint& kp1, const cv::KeyPoint& kp2, const Eigen::Matrix3f&,
+                           const Eigen::Vector3f&, const float sigmaLevel, const float unc, Eigen::Vector3f& p3D) {
+    return triangulate_hook(kp1, kp2, sigmaLevel, unc, p3D);
+  }
+};
+
 }  // namespace ORB_SLAM3

@@ -114,3 +114,24 @@ void KeyPointsFilter::retainBest(std::vector<KeyPoint>& keypoints, int npoints) 
 }
 
 }  // namespace cv
+
+// cv::BFMatcher::knnMatch(query, train, matches, 2): rows in (distance, trainIdx) order, fewer when the train set is small
+namespace orb_oracle { void knn_match2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx, int32_t* dist); }
+void cv::BFMatcher::knnMatch(const Mat& q, const Mat& t, std::vector<std::vector<DMatch>>& matches, int k) const {
+  if (k != 2) REF_COMPAT_UNSUPPORTED("BFMatcher::knnMatch with k != 2");
+  if (q.type() != CV_8UC1 || (q.rows && q.cols != 32) || (t.rows && t.cols != 32)) REF_COMPAT_UNSUPPORTED("knnMatch: not n x 32 CV_8U");
+  const int nq = q.rows, nt = t.rows;
+  std::vector<uint8_t> qb((size_t)std::max(nq, 1) * 32), tb((size_t)std::max(nt, 1) * 32);
+  for (int i = 0; i < nq; i++) memcpy(&qb[(size_t)i * 32], q.ptr<uint8_t>(i), 32);
+  for (int i = 0; i < nt; i++) memcpy(&tb[(size_t)i * 32], t.ptr<uint8_t>(i), 32);
+  std::vector<int32_t> idx((size_t)std::max(nq, 1) * 2, -1), dist((size_t)std::max(nq, 1) * 2, -1);
+  if (nq && nt) orb_oracle::knn_match2(qb.data(), nq, tb.data(), nt, idx.data(), dist.data());
+  matches.assign(nq, {});
+  for (int i = 0; i < nq; i++)
+    for (int j = 0; j < 2; j++)
+      if (idx[2 * i + j] >= 0) {
+        DMatch m;
+        m.queryIdx = i; m.trainIdx = idx[2 * i + j]; m.imgIdx = 0; m.distance = (float)dist[2 * i + j];
+        matches[i].push_back(m);
+      }
+}

@@ -9,6 +9,7 @@
 #include <vector>
 
 #include "ORBmatcher.h"
+#include "fake_triangulate.h"
 #include "ref_harness.h"
 
 using namespace ORB_SLAM3;
@@ -139,6 +140,33 @@ int ref_search_by_projection_frame_rig(const cuorb_frame_view* left, const cuorb
     MapPoint* b = rf.F.mvpMapPoints[k];
     binding_out[k] = !b ? -1 : (n_last && b >= &mps[0] && b < &mps[0] + n_last) ? (int32_t)(b - &mps[0]) : -2;
   }
+  return n;
+}
+
+// ---- void Frame::ComputeStereoFishEyeMatches() (src/Frame.cc:1303-1355), the reference's own body, with
+// BFMatcher::knnMatch forwarded to the cv2-pinned 2-NN and KannalaBrandt8::TriangulateMatches replaced by
+// fake_triangulate.h.  Outputs: mvLeftToRightMatch [nl], mvRightToLeftMatch [nr], mvDepth [nl], mvStereo3Dpoints [nl x 3]. ----
+int ref_fisheye_stereo(int nl, const cv::KeyPoint* kl, const uint8_t* dl, int mono_left, int nr, const cv::KeyPoint* kr,
+                       const uint8_t* dr, int mono_right, int nlevels, const float* level_sigma2, int32_t* l2r, int32_t* r2l,
+                       float* depth, float* p3d) {
+  Frame F;
+  KannalaBrandt8 cam, cam2;
+  cam.triangulate_hook = fake_triangulate;
+  F.mpCamera = &cam; F.mpCamera2 = &cam2;
+  F.Nleft = nl; F.Nright = nr; F.N = nl + nr;
+  F.mvKeys.assign(kl, kl + nl); F.mvKeysRight.assign(kr, kr + nr);
+  F.mDescriptors = desc_mat(dl, nl); F.mDescriptorsRight = desc_mat(dr, nr);
+  F.monoLeft = mono_left; F.monoRight = mono_right;
+  F.mvLevelSigma2.assign(level_sigma2, level_sigma2 + nlevels);
+  F.mRlr = Eigen::Matrix3f::Identity();
+  F.ComputeStereoFishEyeMatches();
+  int n = 0;
+  for (int i = 0; i < nl; i++) {
+    l2r[i] = F.mvLeftToRightMatch[i]; depth[i] = F.mvDepth[i];
+    for (int c = 0; c < 3; c++) p3d[3 * i + c] = F.mvStereo3Dpoints[i](c);
+    n += l2r[i] >= 0;
+  }
+  for (int i = 0; i < nr; i++) r2l[i] = F.mvRightToLeftMatch[i];
   return n;
 }
 

@@ -22,6 +22,7 @@ namespace ORB_SLAM3 {
 float Frame::fx = 0, Frame::fy = 0, Frame::cx = 0, Frame::cy = 0, Frame::invfx = 0, Frame::invfy = 0;
 float Frame::mnMinX = 0, Frame::mnMinY = 0, Frame::mnMaxX = 0, Frame::mnMaxY = 0;
 float Frame::mfGridElementWidthInv = 0, Frame::mfGridElementHeightInv = 0;
+cv::BFMatcher Frame::BFmatcher = cv::BFMatcher(cv::NORM_HAMMING);   // src/Frame.cc:53
 
 #include "gen/frame_lifted.inc"
 #include "gen/keyframe_lifted.inc"

@@ -95,6 +95,7 @@ def lib() -> C.CDLL:
         L.ref_search_by_projection_rig.argtypes = ([FV, FV, V, V, C.c_int] + [V] * 11 + [C.c_float, C.c_int, C.c_float, C.c_float, V, V])
         L.ref_search_by_projection_frame_rig.argtypes = ([FV, FV, C.c_int] + [V] * 4 + [C.c_float, C.c_float] + [V] * 3 +
                                                          [C.c_float, C.c_int, C.c_int, C.c_int, V])
+        L.ref_fisheye_stereo.argtypes = [C.c_int, V, V, C.c_int, C.c_int, V, V, C.c_int, C.c_int, V, V, V, V, V]
         _lib = L
     return _lib
 
@@ -369,3 +370,16 @@ def search_by_projection_frame_rig(fvl, fvr, last_desc, u, v, z, trl_x, trl_y, l
     n = lib().ref_search_by_projection_frame_rig(C.byref(fvl), C.byref(fvr), len(arrs[1]), *[_p(x) for x in arrs], trl_x, trl_y,
                                                  *[_p(x) for x in tail], th, int(forward), int(backward), int(check_ori), _p(out))
     return n, out[:fvl.n + fvr.n]
+
+
+def fisheye_stereo(kps_l, desc_l, mono_left, kps_r, desc_r, mono_right, level_sigma2):
+    """Frame::ComputeStereoFishEyeMatches (the reference's own body; triangulation = oracle/ref_compat/fake_triangulate.h).
+    Returns (mvLeftToRightMatch, mvRightToLeftMatch, mvDepth, mvStereo3Dpoints)."""
+    kl = np.ascontiguousarray(kps_l, KP_DTYPE); kr = np.ascontiguousarray(kps_r, KP_DTYPE)
+    dl = _u8(desc_l); dr = _u8(desc_r); s2 = _f32(level_sigma2)
+    nl, nr = len(kl), len(kr)
+    l2r = np.empty(max(nl, 1), np.int32); r2l = np.empty(max(nr, 1), np.int32)
+    depth = np.empty(max(nl, 1), np.float32); p3d = np.zeros((max(nl, 1), 3), np.float32)
+    lib().ref_fisheye_stereo(nl, _p(kl), _p(dl), int(mono_left), nr, _p(kr), _p(dr), int(mono_right), len(s2), _p(s2), _p(l2r),
+                             _p(r2l), _p(depth), _p(p3d))
+    return l2r[:nl], r2l[:nr], depth[:nl], p3d[:nl]

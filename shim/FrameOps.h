@@ -7,6 +7,7 @@
 #pragma once
 #include <stdexcept>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "../include/cuorb.h"
@@ -64,6 +65,42 @@ inline void FisheyeStereoCandidates(const cv::Mat& stereoDescLeft, const cv::Mat
   const int rc = cuorb_knn_match2(device, 1, qo, stereoDescLeft.ptr<unsigned char>(0), to, stereoDescRight.ptr<unsigned char>(0),
                                   idx.data(), dist.data(), accepted.data());
   if (rc < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("FisheyeStereoCandidates (libcuorb): ") + cuorb_last_error());
+}
+
+// void Frame::ComputeStereoFishEyeMatches() (src/Frame.cc:1303-1355), whole: the lapping-area split (:1305-1309), the
+// 2-NN + 0.7 ratio test on the device (FisheyeStereoCandidates), then - on the accepted rows, in left-row order as the
+// reference walks `matches` - the caller's own camera model triangulates (CameraT = KannalaBrandt8, out of scope here)
+// and the stereo tables are filled exactly as at :1345-1351 (a right feature claimed by several left rows keeps the
+// last one in mvRightToLeftMatch while every left row keeps its own entry, as in the reference).
+template <class CameraT, class FrameT>
+inline void ComputeStereoFishEyeMatches(FrameT& F, int device = 0) {
+  F.mvLeftToRightMatch.assign(F.Nleft, -1);
+  F.mvRightToLeftMatch.assign(F.Nright, -1);
+  F.mvDepth.assign(F.Nleft, -1.0f);
+  F.mvuRight.assign(F.Nleft, -1);
+  typedef typename std::decay<decltype(F.mvStereo3Dpoints[0])>::type Vec3;
+  F.mvStereo3Dpoints = std::vector<Vec3>(F.Nleft);
+  F.mnCloseMPs = 0;
+  const int nq = F.mDescriptors.rows - F.monoLeft, nt = F.mDescriptorsRight.rows - F.monoRight;
+  if (nq <= 0 || nt <= 0) return;
+  const cv::Mat stereoDescLeft  = F.mDescriptors.rowRange(F.monoLeft, F.mDescriptors.rows);
+  const cv::Mat stereoDescRight = F.mDescriptorsRight.rowRange(F.monoRight, F.mDescriptorsRight.rows);
+  std::vector<int> accepted;
+  FisheyeStereoCandidates(stereoDescLeft, stereoDescRight, accepted, device);
+  for (int q = 0; q < nq; q++) {
+    if (accepted[q] < 0) continue;                                 // :1329
+    const int iL = q + F.monoLeft, iR = accepted[q] + F.monoRight;
+    const float sigma1 = F.mvLevelSigma2[F.mvKeys[iL].octave], sigma2 = F.mvLevelSigma2[F.mvKeysRight[iR].octave];
+    Vec3 p3D;
+    const float depth = static_cast<CameraT*>(F.mpCamera)->TriangulateMatches(F.mpCamera2, F.mvKeys[iL], F.mvKeysRight[iR], F.mRlr,
+                                                                              F.mtlr, sigma1, sigma2, p3D);   // :1335-1344
+    if (depth > 0.0001f) {                                         // :1345-1351
+      F.mvLeftToRightMatch[iL] = iR;
+      F.mvRightToLeftMatch[iR] = iL;
+      F.mvStereo3Dpoints[iL]   = p3D;
+      F.mvDepth[iL]            = depth;
+    }
+  }
 }
 
 // void MapPoint::ComputeDistinctiveDescriptors() (src/MapPoint.cc:376-450) for a batch of MapPoints

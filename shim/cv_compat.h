@@ -79,6 +79,7 @@ public:
   int  type() const { return type_; }
   int  channels() const { return (type_ >> 3) + 1; }
   Mat  row(int y) const { Mat m; m.rows = 1; m.cols = cols; m.step = step; m.data = data + (size_t)y * step; m.type_ = type_; m.own_ = own_; return m; }
+  Mat  rowRange(int a, int b) const { Mat m = row(a); m.rows = b - a; return m; }
   Mat  clone() const { Mat m(rows, cols, type_); for (int y = 0; y < rows; y++) std::memcpy(m.data + y * m.step, data + y * step, (size_t)cols * esz(type_)); return m; }
   template <typename T> T* ptr(int y = 0) { return (T*)(data + (size_t)y * step); }
   template <typename T> const T* ptr(int y = 0) const { return (const T*)(data + (size_t)y * step); }

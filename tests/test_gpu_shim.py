@@ -233,3 +233,45 @@ def test_cpp_shim_rig_branches(tmp_path, which, seed):
     assert n_r > 300
     assert int(res[0]) == n_r
     assert (res[1:] == final_r).all()
+
+
+@pytest.mark.parametrize("seed,mono_l,mono_r", [(1, 0, 0), (2, 300, 250), (3, 1195, 0)])
+def test_cpp_shim_fisheye_stereo(tmp_path, seed, mono_l, mono_r):
+    """shim/FrameOps.h ComputeStereoFishEyeMatches (lapping split, 2-NN + ratio test on the device, triangulation
+    hand-off, stereo tables) against the reference's own function lifted into oracle/_ref (src/Frame.cc:1303-1355); both
+    sides triangulate with the deterministic stand-in of oracle/ref_compat/fake_triangulate.h."""
+    from oracle import ref_py as rp
+    from tests.rig_cases import rig_views
+    if not rp.available():
+        pytest.skip("oracle/_ref/liborb_ref.so did not travel to this box")
+    build.build_libcuorb()
+    exe = str(tmp_path / "fisheye_check")
+    pkg = os.path.join(ROOT, "orbslam3_cpp_fork_b200")
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-DCUORB_SHIM_USE_OPENCV",
+                           "-I" + os.path.join(ROOT, "oracle", "ref_compat"),
+                           os.path.join(ROOT, "tests", "native", "fisheye_check.cpp"), "-o", exe,
+                           "-L" + pkg, "-l:libcuorb.so", "-Wl,-rpath," + pkg])
+    rv = rig_views(9 + seed, nf=1200)
+    k1, d1, k2, d2 = rv["k1"], rv["d1"], rv["k2"], rv["d2"]
+    mono_l = min(mono_l, len(k1)); mono_r = min(mono_r, len(k2))
+    sigma2 = (rv["sf"] * rv["sf"]).astype(np.float32)
+    l2r, r2l, depth, p3d = rp.fisheye_stereo(k1, d1, mono_l, k2, d2, mono_r, sigma2)
+    case = str(tmp_path / "case.bin"); out = str(tmp_path / "out.bin")
+    with open(case, "wb") as f:
+        np.array([len(k1), len(k2), mono_l, mono_r, len(sigma2)], np.int32).tofile(f)
+        np.ascontiguousarray(k1).tofile(f); np.ascontiguousarray(k2).tofile(f)
+        np.ascontiguousarray(d1).tofile(f); np.ascontiguousarray(d2).tofile(f); sigma2.tofile(f)
+    subprocess.check_call([exe, case, out])
+    raw = np.fromfile(out, np.uint8)
+    nl, nr = len(k1), len(k2)
+    s_l2r = raw[:4 * nl].view(np.int32); s_r2l = raw[4 * nl:4 * (nl + nr)].view(np.int32)
+    s_depth = raw[4 * (nl + nr):4 * (2 * nl + nr)].view(np.float32)
+    s_p3d = raw[4 * (2 * nl + nr):].view(np.float32).reshape(nl, 3)
+    assert (s_l2r == l2r).all() and (s_r2l == r2l).all()
+    assert s_depth.tobytes() == depth.tobytes()
+    hit = l2r >= 0
+    assert s_p3d[hit].tobytes() == p3d[hit].tobytes()
+    if mono_l < len(k1) - 100:
+        assert hit.sum() > 20 and (l2r[:mono_l] == -1).all() and (l2r[hit] >= mono_r).all()
+    else:
+        assert hit.sum() <= len(k1) - mono_l
