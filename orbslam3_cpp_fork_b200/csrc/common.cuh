@@ -88,6 +88,32 @@ inline void count_launch(int n = 1) { g_launch_count.fetch_add((unsigned long lo
     }                                                                                         \
   } while (0)
 
+// ---- programmatic dependent launch (single-frame latency) ----
+// A one-image extraction is a chain of ~13 kernels of 5-15 us each on one stream, so the gaps between them are a
+// visible part of the call.  Every kernel of the chain starts with pdl_enter(): wait until the previous grid has
+// completed and its writes are visible (a no-op when the kernel was not launched as a dependent), then let the NEXT
+// kernel of the stream be scheduled already, so its CTAs sit at their own pdl_enter() when this grid drains.  The
+// trigger comes after the wait, so at most one successor is resident at a time.  launch_k() adds the launch
+// attribute when t_pdl is set (cuorb_api.cu sets it for batches of at most two images; for large batches resident,
+// blocked successor CTAs would only take SM resources from the running kernel).
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_enter() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+#endif
+extern thread_local bool t_pdl;
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = t_pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 // device flags written by kernels (per handle)
 enum { FLAG_CAND_OVERFLOW = 1, FLAG_NODE_OVERFLOW = 2, FLAG_KEY_OVERFLOW = 4 };
 

@@ -55,6 +55,7 @@ __global__ void __launch_bounds__(256) k_finalize(const ExtractorGeom* __restric
                                                   const int* __restrict__ key_count, int lap0, int lap1,
                                                   int* __restrict__ slot_map, int* __restrict__ out_n,
                                                   int* __restrict__ out_mono) {
+  pdl_enter();
   __shared__ int s_off[MAX_LEVELS + 1];
   __shared__ int s_warp[8];
   __shared__ int s_run;
@@ -117,6 +118,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_describe(const ExtractorGeo
                                                               const int* __restrict__ slot_map,
                                                               cuorb_keypoint* __restrict__ out_kps,
                                                               uint8_t* __restrict__ out_desc) {
+  pdl_enter();
   extern __shared__ __align__(128) unsigned char smem[];     // DESC_WARPS x (IC_SLOT + BR_SLOT)
   __shared__ uint64_t s_bar[DESC_WARPS];
   __shared__ float s_angle[DESC_WARPS], s_cos[DESC_WARPS], s_sin[DESC_WARPS];
@@ -254,9 +256,9 @@ void launch_describe(const ExtractorGeom& g, const ExtractorGeom* dg, const TmaM
   (void)pyr; (void)blur;  // read through the TMA tensor maps
   const int smem = DESC_WARPS * (IC_SLOT + BR_SLOT) + 128;
   if (smem > 48 * 1024) cudaFuncSetAttribute(k_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);   // per device
-  k_finalize<<<n_img, 256, 0, st>>>(dg, keys, key_count, lap0, lap1, slot_map, out_n, out_mono);
-  k_describe<<<dim3((g.kp_cap + DESC_WARPS - 1) / DESC_WARPS, n_img), DESC_WARPS * 32, smem, st>>>(
-      dg, tmaps, keys, key_count, slot_map, out_kps, out_desc);
+  launch_k(k_finalize, dim3(n_img), dim3(256), 0, st, dg, keys, key_count, lap0, lap1, slot_map, out_n, out_mono);
+  launch_k(k_describe, dim3((g.kp_cap + DESC_WARPS - 1) / DESC_WARPS, n_img), dim3(DESC_WARPS * 32), (size_t)smem, st, dg, tmaps, keys,
+           key_count, slot_map, out_kps, out_desc);
   count_launch(2);
 }
 

@@ -106,6 +106,7 @@ __global__ void __launch_bounds__(128) k_fast_cells(const ExtractorGeom* __restr
                                                     int* __restrict__ cand_count,
                                                     int* __restrict__ flags, int tile_bytes, int tile8_bytes,
                                                     int score_bytes, int pcap, int ccap) {
+  pdl_enter();
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ int s_pcnt[4], s_ccnt[4], s_nlist, s_nout, s_base;
 
@@ -329,6 +330,7 @@ __device__ __forceinline__ void split_work(int w, int n_cells, float inv, int& i
 
 template <int NW>
 __global__ void __launch_bounds__(32 * NW) k_fast_persist(const __grid_constant__ FastMaps maps, const FastParams P) {
+  pdl_enter();
   extern __shared__ unsigned char smem_raw[];
   __shared__ uint64_t s_bar[2];
   __shared__ int s_next[2], s_img[2], s_cell[2];
@@ -572,8 +574,8 @@ static void launch_fast_tp(const ExtractorGeom& g, const ExtractorGeom* dg, cons
   const int smem        = tile_bytes + tile8_bytes + score_bytes + 2 * 4 * (pcap + ccap) + list_bytes;
   // the attribute is per device, not per process: set on every launch that needs it
   if (smem > 48 * 1024) cudaFuncSetAttribute(k_fast_cells<TP, TPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  k_fast_cells<TP, TPB><<<dim3(g.total_cells, n_img), 128, smem, st>>>(dg, cells, pyr, cand, cand_count, flags, tile_bytes,
-                                                                       tile8_bytes, score_bytes, pcap, ccap);
+  launch_k(k_fast_cells<TP, TPB>, dim3(g.total_cells, n_img), dim3(128), (size_t)smem, st, dg, cells, pyr, cand, cand_count, flags,
+           tile_bytes, tile8_bytes, score_bytes, pcap, ccap);
 }
 
 void launch_fast(const ExtractorGeom& g, const ExtractorGeom* dg, const int4* cells, int n_img, const uint8_t* pyr,
@@ -632,7 +634,7 @@ void launch_fast_persist(const ExtractorGeom& g, const FastMaps& maps, const int
   static const int cap = []() { const char* e = getenv("CUORB_FAST_CTAS"); return e ? atoi(e) : 12; }();
   const int use_per_sm = cap > 0 ? std::min(cap, std::max(per_sm, 1)) : std::max(per_sm, 1);
   const int grid = std::max(1, std::min(P.total_work, n_sm * use_per_sm));
-  kern<<<grid, 32 * NW, smem, st>>>(maps, P);
+  launch_k(kern, dim3(grid), dim3(32 * NW), (size_t)smem, st, maps, P);
   count_launch();
 }
 

@@ -231,6 +231,7 @@ __global__ void __launch_bounds__(OT_THREADS) k_octree(const ExtractorGeom* __re
                                                        LevelKey* __restrict__ keys_out,
                                                        int* __restrict__ key_count,
                                                        int* __restrict__ flags, int pool_cap) {
+  pdl_enter();
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ u64 s_warp[OT_THREADS / 32];
   __shared__ int s_cnt_ok;
@@ -499,8 +500,7 @@ void launch_octree(const ExtractorGeom& g, const ExtractorGeom* dg, int n_img, c
   for (int l = 0; l < g.nlevels; l++) cap = max(cap, g.lv[l].node_cap);
   const size_t smem = octree_node_bytes(cap) + (size_t)OT_KEYCAP * 6;
   if (smem > 48 * 1024) cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   // per device
-  k_octree<<<dim3(g.nlevels, n_img), OT_THREADS, smem, st>>>(dg, cand, cand_scratch, cand_count, keys,
-                                                             key_count, flags, cap);
+  launch_k(k_octree, dim3(g.nlevels, n_img), dim3(OT_THREADS), smem, st, dg, cand, cand_scratch, cand_count, keys, key_count, flags, cap);
   count_launch();
 }
 

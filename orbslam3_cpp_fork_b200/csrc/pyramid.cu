@@ -35,6 +35,7 @@ __global__ void __launch_bounds__(256) k_pyr_level0(const ExtractorGeom* __restr
                                                     const uint8_t* __restrict__ imgs, size_t stride,
                                                     size_t image_stride, uint8_t* __restrict__ pyr,
                                                     int aligned) {
+  pdl_enter();
   const LevelGeom& L = dg->lv[0];
   const int word = blockIdx.x * blockDim.x + threadIdx.x;
   if (word * 4 >= L.pitch) return;
@@ -119,6 +120,7 @@ __global__ void __launch_bounds__(PYR_TX) k_pyr_resize(const ExtractorGeom* __re
                                                        uint8_t* __restrict__ pyr,
                                                        const ResizeTap* __restrict__ xtab,
                                                        const ResizeTap* __restrict__ ytab) {
+  pdl_enter();
   const LevelGeom& L = dg->lv[level];
   const LevelGeom& S = dg->lv[level - 1];
   const int word = blockIdx.x * PYR_TX + threadIdx.x;
@@ -240,6 +242,7 @@ __global__ void __launch_bounds__(PYR_TAB_TX, 1536 / PYR_TAB_TX) k_pyr_resize_st
                                                            const uint4* __restrict__ wtab,
                                                            const ResizeTap* __restrict__ ytab, int rs,
                                                            const PyrCols pc) {
+  pdl_enter();
   extern __shared__ __align__(128) unsigned char s_tile[];
   __shared__ uint4 s_rec[PYR_RS];   // per output row {source row offsets, advance, vertical weights}, relative to the staged tile
   __shared__ uint64_t s_bar;
@@ -428,7 +431,7 @@ void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8
       // CTA width = the padded row's word count split evenly over whole warps (208 words -> one CTA of 224)
       const int words = L.pitch / 4, nb = (words + 255) / 256;
       const int tx = (((words + nb - 1) / nb) + 31) / 32 * 32;
-      k_pyr_level0<<<dim3((words + tx - 1) / tx, grid.y, n_img), tx, 0, st>>>(dg, imgs, stride, image_stride, pyr, aligned);
+      launch_k(k_pyr_level0, dim3((words + tx - 1) / tx, grid.y, n_img), dim3(tx), 0, st, dg, imgs, stride, image_stride, pyr, aligned);
     } else {
       // four adjacent output columns span 3*scale + 2 source bytes (+3 for alignment): 12 bytes up to scale 2
       const double sx = (double)g.lv[l - 1].w / L.w;
@@ -439,10 +442,10 @@ void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8
         // above the 48 KB default only for very wide levels; the attribute is per device, so it is set on every
         // such launch rather than cached per process
         if (p.smem > 48 * 1024) cudaFuncSetAttribute(k_pyr_resize_stage, cudaFuncAttributeMaxDynamicSharedMemorySize, p.smem);
-        k_pyr_resize_stage<<<dim3(p.nb, (L.h + PYR_RS - 1) / PYR_RS, n_img), p.tx, p.smem, st>>>(dg, l, pyr, wtab + wtab_off[l], ytab, PYR_RS, pc);
+        launch_k(k_pyr_resize_stage, dim3(p.nb, (L.h + PYR_RS - 1) / PYR_RS, n_img), dim3(p.tx), (size_t)p.smem, st, dg, l, pyr, wtab + wtab_off[l], ytab, PYR_RS, pc);
       }
-      else if (3.0 * sx + 5.0 < 11.5) k_pyr_resize<false><<<grid, PYR_TX, 0, st>>>(dg, l, pyr, xtab, ytab);
-      else k_pyr_resize<true><<<grid, PYR_TX, 0, st>>>(dg, l, pyr, xtab, ytab);
+      else if (3.0 * sx + 5.0 < 11.5) launch_k(k_pyr_resize<false>, grid, dim3(PYR_TX), 0, st, dg, l, pyr, xtab, ytab);
+      else launch_k(k_pyr_resize<true>, grid, dim3(PYR_TX), 0, st, dg, l, pyr, xtab, ytab);
     }
     count_launch();
   }
