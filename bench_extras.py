@@ -384,4 +384,51 @@ def cfg4_projection(local, with_cpu=True, M=50000):
                                                   c["depth"], c["flags"], 3.0, False, 60.0, 0.8)
         out["cpu_port_ms_per_call_1core"] = 1e3 * (time.perf_counter() - t0) / 3
         out["equal_to_cpu"] = bool(n_o == n and (best_o == best).all())
+    out["resident_local_map"] = localmap_track(local, with_cpu, M, (e, k, d))
+    return out
+
+
+def localmap_track(local, with_cpu=True, M=50000, frame=None):
+    """Tracking::SearchLocalPoints' two loops (isInFrustum over the local map, then SearchByProjection) on a local map that
+    stays in HBM (cuorb_localmap_*): per call only the pose, the frame's features and the skip list go up."""
+    import orbslam3_cpp_fork_b200 as cu
+    from orbslam3_cpp_fork_b200 import _lib
+    from oracle import oracle_py as op
+    from tests.matching_cases import extracted_frame, localmap_case, localmap_expected
+    e, k, d = frame if frame is not None else extracted_frame()
+    sf = np.asarray(e.tables()[0], np.float32)
+    c = localmap_case(k, d, sf, M, 11)
+    cam = _lib.FrustumCamera.from_buffer_copy(bytes(c["cam"]))
+    m = cu.LocalMap(M, device=local)
+    t0 = time.perf_counter()
+    m.update(0, c["P"], c["N"], c["min_d"], c["max_d"], c["desc"], c["bad"], c["has_obs"])
+    t_upload = time.perf_counter() - t0
+    L_ = _lib.load()
+    F = cu.Frame(k, d, sf, 752, 480, mvuRight=c["u_right"], mb=0.1, mbf=c["mbf"])
+    F.mvpMapPoints[c["bound"] > 0] = 10 ** 9; F.mvpHasObs[c["bound"] > 0] = 1
+    fvv, keep_alive = F.view()
+    skip = np.ascontiguousarray(c["skip_idx"], np.int32)
+    cap = 4096
+    mp = np.zeros(cap, np.int32); ft = np.zeros(cap, np.int32); nin = C.c_int32(0)
+
+    def call():
+        return _lib.check(L_.cuorb_localmap_search(m._h, C.byref(cam), C.byref(fvv), len(skip), _lib.ptr(skip), 0.5, 1.0, 0, 50.0,
+                                                   0.8, None, cap, _lib.ptr(mp), _lib.ptr(ft), C.byref(nin)))
+    n = call()
+    for _ in range(5):
+        call()
+    ts = []
+    for _ in range(60):
+        t0 = time.perf_counter(); call(); ts.append(time.perf_counter() - t0)
+    st = _stats(ts)
+    out = {"workload": f"isInFrustum + SearchByProjection over a resident local map of {M} MapPoints, frame 752x480 / {len(k)} "
+                       "keypoints, th 1, nnratio 0.8; wall clock around cuorb_localmap_search, (point, feature) pairs out",
+           "points_in_view": int(nin.value), "matches": int(n), "ms_per_call": st,
+           "mappoints_per_s": M / (st["median_ms"] * 1e-3), "one_time_map_upload_ms": 1e3 * t_upload}
+    if with_cpu:
+        t0 = time.perf_counter()
+        o_in, o_n, o_best = localmap_expected(c, k, d, sf, op.is_in_frustum, op.search_by_projection, 1.0, False, 50.0, 0.8)
+        out["cpu_port_ms_per_call_1core"] = 1e3 * (time.perf_counter() - t0)
+        hit = np.nonzero(o_best >= 0)[0]
+        out["equal_to_cpu"] = bool(o_n == n and o_in == nin.value and (mp[:n] == hit).all() and (ft[:n] == o_best[hit]).all())
     return out

@@ -383,6 +383,38 @@ int cuorb_is_in_frustum_noalloc(int device, const cuorb_frustum_camera* camera, 
                                 float viewing_cos_limit, uint8_t* in_view, float* proj_x, float* proj_y,
                                 float* proj_xr, int32_t* scale_level, float* view_cos, float* depth);
 
+/* ---- resident local map: Tracking::SearchLocalPoints' two hot loops in one call ----
+ * What Tracking::SearchLocalPoints (src/Tracking.cc) does per frame with the local map: for every MapPoint that is
+ * not already matched in this frame (mnLastFrameSeen == mCurrentFrame.mnId) and not bad, Frame::isInFrustum(pMP, 0.5)
+ * (src/Frame.cc:644-721) fills the tracking fields; then ORBmatcher::SearchByProjection(F, mvpLocalMapPoints, th,
+ * bFarPoints, thFarPoints) (src/ORBmatcher.cc:38-150) consumes them.  The local map changes by a few per cent per
+ * frame while its world positions, normals, distance ranges and descriptors are what both loops read, so the handle
+ * keeps them in HBM: per frame only the camera pose and the frame's own features go up and the matches come back.
+ * Results are those of cuorb_is_in_frustum followed by cuorb_search_by_projection on the same data, bit for bit.
+ * One handle serves one tracking thread; calls on one handle must not overlap. */
+typedef struct cuorb_localmap cuorb_localmap;
+cuorb_localmap* cuorb_localmap_create(int device, int capacity);   /* NULL + cuorb_last_error() on failure */
+void cuorb_localmap_destroy(cuorb_localmap* map);
+/* Write points [first, first + n) and set the number of points in use to new_count (<= capacity).  world_pos /
+ * normal: n x 3 floats (GetWorldPos / GetNormal), min_distance / max_distance: mfMinDistance / mfMaxDistance (the
+ * 0.8 / 1.2 invariance factors are applied inside), descriptors: n x 32 (GetDescriptor), flags: CUORB_MP_BAD |
+ * CUORB_MP_HAS_OBS per point.  Slots never written count as bad points.  Host arrays; synchronous. */
+int cuorb_localmap_update(cuorb_localmap* map, int first, int n, int new_count, const float* world_pos,
+                          const float* normal, const float* min_distance, const float* max_distance,
+                          const uint8_t* descriptors, const uint8_t* flags);
+int cuorb_localmap_count(const cuorb_localmap* map);
+/* One frame.  cam: the Frame's pose / intrinsics as for cuorb_is_in_frustum; frame: as for
+ * cuorb_search_by_projection; skip_idx[n_skip]: points to leave out (already matched in this frame).  Outputs (host):
+ * best_idx_out[count] (optional, may be NULL) = feature bound to each point or -1; match_point_out /
+ * match_feature_out[match_capacity] = the matches as (point, feature) pairs in point order, the order in which the
+ * caller replays F.mvpMapPoints[feature] = pMP (CUORB_E_CAPACITY if there are more than match_capacity);
+ * n_in_view_out = number of points isInFrustum accepted (the reference's nToMatch).  Returns nmatches. */
+int cuorb_localmap_search(cuorb_localmap* map, const cuorb_frustum_camera* cam, const cuorb_frame_view* frame, int n_skip,
+                          const int32_t* skip_idx, float viewing_cos_limit, float th, int far_points,
+                          float th_far_points, float nn_ratio, int32_t* best_idx_out, int match_capacity,
+                          int32_t* match_point_out, int32_t* match_feature_out, int32_t* n_in_view_out);
+
+
 /* void Frame::ComputeStereoFromRGBD(const cv::Mat& imDepth) (src/Frame.cc:1115-1133): depth = CV_32F
  * image (row pitch stride_bytes) in host or device memory; d = imDepth(v, u) at the truncated
  * keypoint position; if d > 0: depth_out = d, u_right = kps_un.x - mbf / d, else both -1. */

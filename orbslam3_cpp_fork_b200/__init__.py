@@ -5,7 +5,7 @@ include/cuorb.h), the ctypes binding, and the host-side mirrors of ORBextractor 
 """
 from ._lib import KP_DTYPE, CuorbError, load  # noqa: F401
 from .extractor import ORBextractor  # noqa: F401
-from .matcher import Frame, MapPointSoA, ORBmatcher  # noqa: F401
+from .matcher import Frame, MapPointSoA, ORBmatcher, RigFrame  # noqa: F401
 from .preproc import FramePreprocessor  # noqa: F401
-from .frame_ops import ComputeStereoFromRGBD, UndistortKeyPoints, isInFrustum  # noqa: F401
+from .frame_ops import ComputeStereoFromRGBD, LocalMap, UndistortKeyPoints, isInFrustum  # noqa: F401
 from .bfmatch import ComputeDistinctiveDescriptors, knnMatch2  # noqa: F401

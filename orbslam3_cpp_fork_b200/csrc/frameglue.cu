@@ -10,6 +10,7 @@
 #include <string>
 
 #include "common.cuh"
+#include "frustum.cuh"
 
 namespace cuorb {
 void set_error(const std::string& msg);
@@ -70,14 +71,7 @@ __global__ void k_stereo_from_rgbd(const cuorb_keypoint* __restrict__ kps, const
   u_right[i] = ur; depth_out[i] = dz;
 }
 
-// Frame::isInFrustum (src/Frame.cc:644-707, Nleft == -1) + MapPoint::PredictScale (src/MapPoint.cc:574-589) +
-// Pinhole::project (Pinhole.cpp:70-76): one thread per MapPoint, SoA in / SoA out.  Every float operation is an
-// explicit round-to-nearest intrinsic in the reference's expression order (size-3 sums associate as Eigen's
-// unrolled reduction does: x0 + (x1 + x2)), so nvcc cannot contract anything into an FMA.
-__device__ __forceinline__ float dot3(float a0, float a1, float a2, float b0, float b1, float b2) {
-  return __fadd_rn(__fmul_rn(a0, b0), __fadd_rn(__fmul_rn(a1, b1), __fmul_rn(a2, b2)));
-}
-
+// Frame::isInFrustum: one thread per MapPoint, SoA in / SoA out (the arithmetic is frustum_point, frustum.cuh)
 __global__ void k_is_in_frustum(const cuorb_frustum_camera c, int n, const float* __restrict__ P3, const float* __restrict__ N3,
                                 const float* __restrict__ minD, const float* __restrict__ maxD, float limit,
                                 uint8_t* __restrict__ in_view, float* __restrict__ projX, float* __restrict__ projY,
@@ -86,39 +80,9 @@ __global__ void k_is_in_frustum(const cuorb_frustum_camera c, int n, const float
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   bool ok = false;
   if (i < n) {
-    float px = -1.f, py = -1.f, pxr = -1.f, vc = 0.f, dz = 0.f;
-    int lv = -1;
-    const float P0 = P3[3 * i], P1 = P3[3 * i + 1], P2 = P3[3 * i + 2];
-    const float Pc0 = __fadd_rn(dot3(c.rcw[0], c.rcw[1], c.rcw[2], P0, P1, P2), c.tcw[0]);
-    const float Pc1 = __fadd_rn(dot3(c.rcw[3], c.rcw[4], c.rcw[5], P0, P1, P2), c.tcw[1]);
-    const float Pc2 = __fadd_rn(dot3(c.rcw[6], c.rcw[7], c.rcw[8], P0, P1, P2), c.tcw[2]);
-    const float Pc_dist = __fsqrt_rn(dot3(Pc0, Pc1, Pc2, Pc0, Pc1, Pc2));
-    const float invz = __fdiv_rn(1.0f, Pc2);
-    if (!(Pc2 < 0.0f)) {
-      const float u = __fadd_rn(__fdiv_rn(__fmul_rn(c.fx, Pc0), Pc2), c.cx);
-      const float v = __fadd_rn(__fdiv_rn(__fmul_rn(c.fy, Pc1), Pc2), c.cy);
-      if (!(u < c.min_x || u > c.max_x) && !(v < c.min_y || v > c.max_y)) {
-        px = u; py = v;
-        const float mx = maxD[i];
-        const float maxDistance = __fmul_rn(1.2f, mx), minDistance = __fmul_rn(0.8f, minD[i]);
-        const float O0 = __fsub_rn(P0, c.ow[0]), O1 = __fsub_rn(P1, c.ow[1]), O2 = __fsub_rn(P2, c.ow[2]);
-        const float dist = __fsqrt_rn(dot3(O0, O1, O2, O0, O1, O2));
-        if (!(dist < minDistance || dist > maxDistance)) {
-          const float viewCos = __fdiv_rn(dot3(O0, O1, O2, N3[3 * i], N3[3 * i + 1], N3[3 * i + 2]), dist);
-          if (!(viewCos < limit)) {
-            const float ratio = __fdiv_rn(mx, dist);
-            // std::log(float) = glibc logf (correctly rounded in practice): double log, rounded once
-            const float lg = (float)log((double)ratio);
-            int nScale = (int)ceilf(__fdiv_rn(lg, c.log_scale_factor));
-            nScale = nScale < 0 ? 0 : (nScale >= c.n_levels ? c.n_levels - 1 : nScale);
-            ok = true;
-            pxr = __fsub_rn(u, __fmul_rn(c.mbf, invz));
-            dz = Pc_dist; lv = nScale; vc = viewCos;
-          }
-        }
-      }
-    }
-    in_view[i] = ok ? 1 : 0; projX[i] = px; projY[i] = py; projXR[i] = pxr; level[i] = lv; viewCosOut[i] = vc; depth[i] = dz;
+    FrustumOut o;
+    ok = frustum_point(c, P3[3 * i], P3[3 * i + 1], P3[3 * i + 2], N3[3 * i], N3[3 * i + 1], N3[3 * i + 2], minD[i], maxD[i], limit, o);
+    in_view[i] = ok ? 1 : 0; projX[i] = o.px; projY[i] = o.py; projXR[i] = o.pxr; level[i] = o.lv; viewCosOut[i] = o.vc; depth[i] = o.dz;
   }
   const unsigned b = __ballot_sync(0xffffffffu, ok);
   if ((threadIdx.x & 31) == 0 && b) atomicAdd(count, __popc(b));

@@ -18,6 +18,7 @@
 #include <cmath>
 #include <mutex>
 
+#include "frustum.cuh"
 #include "project.cuh"
 
 namespace cuorb {
@@ -185,35 +186,11 @@ __global__ void k_hamming_pairs(const uint8_t* a, const uint8_t* b, const int* i
 // ---- host side ----
 thread_local Arena t_arena;
 
-static int run_projection(int device, const cuorb_frame_view* fv, ProjQuery Q, const uint8_t* qdesc,
-                          const float* px, const float* py, const float* aux, const int32_t* level,
-                          const float* viewcos, const float* depth, const uint8_t* flags,
-                          int32_t* result_out, int32_t* gate_out_host = nullptr, const int32_t* gate_in_host = nullptr,
-                          bool ignore_uright = false) {
-  const int n = fv->n, m = Q.n;
-  if (n > 65535 || fv->nlevels > MAX_LEVELS) { set_error("frame too large for projection search"); return CUORB_E_UNSUPPORTED; }
-  for (int i = 0; i < m; i++) result_out[i] = -1;
-  if (n <= 0 || m <= 0) return 0;
-  CUORB_CUDA_TRY(cudaSetDevice(device));
-  const size_t bytes = frame_bytes(n) + (size_t)m * (32 + 6 * 4 + 1 + 4 + 8) + 64 * 1024;
-  if (t_arena.reserve(device, bytes) != 0) { set_error("cudaMalloc failed (projection workspace)"); return CUORB_E_CUDA; }
-  Arena& A = t_arena;
-  cudaStream_t st = cudaStreamPerThread;
-  ProjFrame F;
-  upload_frame(A, fv, st, F);
-  if (ignore_uright) F.uright = nullptr;                 // rig frames: the mvuRight gate is pinhole-only (:103, :1770)
-  Q.gate_out = gate_out_host ? A.take<int>(m) : nullptr;
-  Q.gate_in = gate_in_host ? up(A, gate_in_host, m, st) : nullptr;
-  if (Q.gate_out) CUORB_CUDA_TRY(cudaMemsetAsync(Q.gate_out, 0, sizeof(int) * m, st));
-  Q.desc = up(A, qdesc, (size_t)m * 32, st);
-  Q.px = up(A, px, m, st); Q.py = up(A, py, m, st);
-  Q.aux = aux ? up(A, aux, m, st) : nullptr;
-  Q.level = up(A, level, m, st);
-  Q.viewcos = viewcos ? up(A, viewcos, m, st) : nullptr;
-  Q.depth = depth ? up(A, depth, m, st) : nullptr;
-  Q.flags = up(A, flags, m, st);
+// Binding rounds to the sequential fixed point on device-resident queries; result: device, m ints.  Returns the
+// number of rounds (>= 1) or a negative error code; the stream is synchronised on return.
+static int projection_rounds(Arena& A, cudaStream_t st, const ProjFrame& F, const ProjQuery& Q, int* result) {
+  const int n = F.n, m = Q.n;
   int* binder[2] = {A.take<int>(n), A.take<int>(n)};
-  int* result = A.take<int>(m);
   // Binding rounds to the sequential fixed point, enqueued ROUND_BATCH at a time with no host round trip in
   // between; round k of a batch sets flag[k] when a result changed and the host reads the batch's flags once.
   // Rounds past the fixed point are idempotent (equal results -> equal binder tables -> no dirty cell -> every
@@ -249,10 +226,91 @@ static int run_projection(int device, const cuorb_frame_view* fv, ProjQuery Q, c
     for (int k = 0; k < ROUND_BATCH; k++)
       if (!h_flag[k]) { converged = true; rounds -= ROUND_BATCH - 1 - k; break; }   // rounds to the first quiet one, inclusive
   }
+  return rounds;
+}
+
+static int run_projection(int device, const cuorb_frame_view* fv, ProjQuery Q, const uint8_t* qdesc,
+                          const float* px, const float* py, const float* aux, const int32_t* level,
+                          const float* viewcos, const float* depth, const uint8_t* flags,
+                          int32_t* result_out, int32_t* gate_out_host = nullptr, const int32_t* gate_in_host = nullptr,
+                          bool ignore_uright = false) {
+  const int n = fv->n, m = Q.n;
+  if (n > 65535 || fv->nlevels > MAX_LEVELS) { set_error("frame too large for projection search"); return CUORB_E_UNSUPPORTED; }
+  for (int i = 0; i < m; i++) result_out[i] = -1;
+  if (n <= 0 || m <= 0) return 0;
+  CUORB_CUDA_TRY(cudaSetDevice(device));
+  const size_t bytes = frame_bytes(n) + (size_t)m * (32 + 6 * 4 + 1 + 4 + 8) + 64 * 1024;
+  if (t_arena.reserve(device, bytes) != 0) { set_error("cudaMalloc failed (projection workspace)"); return CUORB_E_CUDA; }
+  Arena& A = t_arena;
+  cudaStream_t st = cudaStreamPerThread;
+  ProjFrame F;
+  upload_frame(A, fv, st, F);
+  if (ignore_uright) F.uright = nullptr;                 // rig frames: the mvuRight gate is pinhole-only (:103, :1770)
+  Q.gate_out = gate_out_host ? A.take<int>(m) : nullptr;
+  Q.gate_in = gate_in_host ? up(A, gate_in_host, m, st) : nullptr;
+  if (Q.gate_out) CUORB_CUDA_TRY(cudaMemsetAsync(Q.gate_out, 0, sizeof(int) * m, st));
+  Q.desc = up(A, qdesc, (size_t)m * 32, st);
+  Q.px = up(A, px, m, st); Q.py = up(A, py, m, st);
+  Q.aux = aux ? up(A, aux, m, st) : nullptr;
+  Q.level = up(A, level, m, st);
+  Q.viewcos = viewcos ? up(A, viewcos, m, st) : nullptr;
+  Q.depth = depth ? up(A, depth, m, st) : nullptr;
+  Q.flags = up(A, flags, m, st);
+  int* result = A.take<int>(m);
+  const int rounds = projection_rounds(A, st, F, Q, result);
+  if (rounds < 0) return rounds;
   CUORB_CUDA_TRY(cudaMemcpyAsync(result_out, result, sizeof(int) * m, cudaMemcpyDeviceToHost, st));
   if (gate_out_host) CUORB_CUDA_TRY(cudaMemcpyAsync(gate_out_host, Q.gate_out, sizeof(int) * m, cudaMemcpyDeviceToHost, st));
   CUORB_CUDA_TRY(cudaStreamSynchronize(st));
   return rounds;
+}
+
+// ---- resident local map (Tracking::SearchLocalPoints, src/Tracking.cc: the isInFrustum loop over mvpLocalMapPoints
+// followed by SearchByProjection) ----
+// grid: ceil(n/128).  Per MapPoint: skipped (mnLastFrameSeen == this frame) or bad points are not in view; the
+// rest go through Frame::isInFrustum (frustum.cuh) and leave their tracking fields in the map's resident SoA.
+__global__ void k_localmap_frustum(const cuorb_frustum_camera c, int n, const float* __restrict__ P3, const float* __restrict__ N3,
+                                   const float* __restrict__ minD, const float* __restrict__ maxD, const uint8_t* __restrict__ pflags,
+                                   const uint8_t* __restrict__ skip, float limit, float* __restrict__ projX,
+                                   float* __restrict__ projY, float* __restrict__ projXR, int* __restrict__ level,
+                                   float* __restrict__ viewCos, float* __restrict__ depth, uint8_t* __restrict__ qflags,
+                                   int* __restrict__ count) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  bool ok = false;
+  if (i < n) {
+    const unsigned pf = pflags[i];
+    FrustumOut o;
+    o.px = -1.f; o.py = -1.f; o.pxr = -1.f; o.vc = 0.f; o.dz = 0.f; o.lv = 0;
+    if (!skip[i] && !(pf & CUORB_MP_BAD))
+      ok = frustum_point(c, P3[3 * i], P3[3 * i + 1], P3[3 * i + 2], N3[3 * i], N3[3 * i + 1], N3[3 * i + 2], minD[i], maxD[i], limit, o);
+    projX[i] = o.px; projY[i] = o.py; projXR[i] = o.pxr; level[i] = ok ? o.lv : 0; viewCos[i] = o.vc; depth[i] = o.dz;
+    qflags[i] = (uint8_t)((ok ? CUORB_MP_IN_VIEW : 0u) | (pf & (CUORB_MP_BAD | CUORB_MP_HAS_OBS)));
+  }
+  const unsigned b = __ballot_sync(0xffffffffu, ok);
+  if ((threadIdx.x & 31) == 0 && b) atomicAdd(count, __popc(b));
+}
+
+// grid: ceil(n/256)
+__global__ void k_mark_skip(int n_skip, const int* __restrict__ idx, int n, uint8_t* __restrict__ skip) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n_skip && idx[k] >= 0 && idx[k] < n) skip[idx[k]] = 1;
+}
+
+// grid: ceil(m/256): (MapPoint, feature) pairs of the matches, in no particular order
+__global__ void k_compact_matches(int m, const int* __restrict__ result, int cap, int* __restrict__ out_mp,
+                                  int* __restrict__ out_feat, int* __restrict__ count) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool hit = i < m && result[i] >= 0;
+  const unsigned b = __ballot_sync(0xffffffffu, hit);
+  if (!b) return;
+  const int lane = threadIdx.x & 31;
+  int base = 0;
+  if (lane == 0) base = atomicAdd(count, __popc(b));
+  base = __shfl_sync(0xffffffffu, base, 0);
+  if (hit) {
+    const int pos = base + __popc(b & ((1u << lane) - 1u));
+    if (pos < cap) { out_mp[pos] = i; out_feat[pos] = result[i]; }
+  }
 }
 
 }  // namespace cuorb
@@ -416,6 +474,137 @@ int cuorb_hamming_batch(int device, const uint8_t* a, int n_a, const uint8_t* b,
   CUORB_CUDA_TRY(cudaMemcpyAsync(out, dout, sizeof(int) * n_pairs, cudaMemcpyDeviceToHost, st));
   CUORB_CUDA_TRY(cudaStreamSynchronize(st));
   return n_pairs;
+}
+
+// ---- resident local map ----
+struct cuorb_localmap {
+  int device = 0, capacity = 0, count = 0;
+  float *P = nullptr, *N = nullptr, *minD = nullptr, *maxD = nullptr;
+  uint8_t *desc = nullptr, *pflags = nullptr, *skip = nullptr, *qflags = nullptr;
+  float *px = nullptr, *py = nullptr, *pxr = nullptr, *vc = nullptr, *dz = nullptr;
+  int *lv = nullptr, *result = nullptr, *match_mp = nullptr, *match_feat = nullptr, *counters = nullptr;
+  int *h_counters = nullptr;    // pinned: [0] in view, [1] matches
+  cudaStream_t stream = nullptr;
+};
+
+cuorb_localmap* cuorb_localmap_create(int device, int capacity) {
+  if (capacity <= 0) { set_error("cuorb_localmap_create: capacity must be positive"); return nullptr; }
+  if (cudaSetDevice(device) != cudaSuccess) { set_error("cuorb_localmap_create: no such CUDA device"); return nullptr; }
+  cuorb_localmap* m = new cuorb_localmap();
+  m->device = device; m->capacity = capacity;
+  const size_t c = (size_t)capacity;
+  bool ok = true;
+  auto al = [&](auto** p, size_t bytes) { if (ok && cudaMalloc((void**)p, bytes) != cudaSuccess) ok = false; };
+  al(&m->P, 12 * c); al(&m->N, 12 * c); al(&m->minD, 4 * c); al(&m->maxD, 4 * c); al(&m->desc, 32 * c); al(&m->pflags, c);
+  al(&m->skip, c); al(&m->qflags, c); al(&m->px, 4 * c); al(&m->py, 4 * c); al(&m->pxr, 4 * c); al(&m->vc, 4 * c);
+  al(&m->dz, 4 * c); al(&m->lv, 4 * c); al(&m->result, 4 * c); al(&m->match_mp, 4 * c); al(&m->match_feat, 4 * c);
+  al(&m->counters, 2 * sizeof(int));
+  if (ok && cudaHostAlloc((void**)&m->h_counters, 2 * sizeof(int), cudaHostAllocDefault) != cudaSuccess) ok = false;
+  if (ok && cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess) ok = false;
+  if (ok && cudaMemset(m->pflags, CUORB_MP_BAD, c) != cudaSuccess) ok = false;   // slots never written are bad points
+  if (!ok) { set_error("cuorb_localmap_create: device allocation failed"); cuorb_localmap_destroy(m); return nullptr; }
+  return m;
+}
+
+void cuorb_localmap_destroy(cuorb_localmap* m) {
+  if (!m) return;
+  cudaSetDevice(m->device);
+  if (m->stream) { cudaStreamSynchronize(m->stream); cudaStreamDestroy(m->stream); }
+  void* ptrs[] = {m->P, m->N, m->minD, m->maxD, m->desc, m->pflags, m->skip, m->qflags, m->px, m->py, m->pxr, m->vc, m->dz,
+                  m->lv, m->result, m->match_mp, m->match_feat, m->counters};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  if (m->h_counters) cudaFreeHost(m->h_counters);
+  delete m;
+}
+
+int cuorb_localmap_update(cuorb_localmap* m, int first, int n, int new_count, const float* world_pos, const float* normal,
+                          const float* min_distance, const float* max_distance, const uint8_t* descriptors,
+                          const uint8_t* flags) {
+  if (!m || first < 0 || n < 0 || first + n > m->capacity || new_count < 0 || new_count > m->capacity ||
+      (n > 0 && (!world_pos || !normal || !min_distance || !max_distance || !descriptors || !flags))) {
+    set_error("cuorb_localmap_update: bad argument or range beyond the map's capacity");
+    return CUORB_E_BADARG;
+  }
+  CUORB_CUDA_TRY(cudaSetDevice(m->device));
+  cudaStream_t st = m->stream;
+  if (n > 0) {
+    const size_t f = (size_t)first, c = (size_t)n;
+    CUORB_CUDA_TRY(cudaMemcpyAsync(m->P + 3 * f, world_pos, 12 * c, cudaMemcpyHostToDevice, st));
+    CUORB_CUDA_TRY(cudaMemcpyAsync(m->N + 3 * f, normal, 12 * c, cudaMemcpyHostToDevice, st));
+    CUORB_CUDA_TRY(cudaMemcpyAsync(m->minD + f, min_distance, 4 * c, cudaMemcpyHostToDevice, st));
+    CUORB_CUDA_TRY(cudaMemcpyAsync(m->maxD + f, max_distance, 4 * c, cudaMemcpyHostToDevice, st));
+    CUORB_CUDA_TRY(cudaMemcpyAsync(m->desc + 32 * f, descriptors, 32 * c, cudaMemcpyHostToDevice, st));
+    CUORB_CUDA_TRY(cudaMemcpyAsync(m->pflags + f, flags, c, cudaMemcpyHostToDevice, st));
+    CUORB_CUDA_TRY(cudaStreamSynchronize(st));   // the caller's buffers may be pageable and reused
+  }
+  m->count = new_count;
+  return CUORB_OK;
+}
+
+int cuorb_localmap_count(const cuorb_localmap* m) { return m ? m->count : CUORB_E_BADARG; }
+
+int cuorb_localmap_search(cuorb_localmap* m, const cuorb_frustum_camera* cam, const cuorb_frame_view* frame, int n_skip,
+                          const int32_t* skip_idx, float viewing_cos_limit, float th, int far_points, float th_far_points,
+                          float nn_ratio, int32_t* best_idx_out, int match_capacity, int32_t* match_point_out,
+                          int32_t* match_feature_out, int32_t* n_in_view_out) {
+  if (!m || !cam || !frame || !frame->keys_un || !frame->descriptors || !frame->scale_factors || n_skip < 0 ||
+      (n_skip && !skip_idx) || match_capacity < 0 || (match_capacity && (!match_point_out || !match_feature_out))) {
+    set_error("cuorb_localmap_search: bad argument");
+    return CUORB_E_BADARG;
+  }
+  const int n = frame->n, M = m->count;
+  if (n > 65535 || frame->nlevels > MAX_LEVELS) { set_error("frame too large for projection search"); return CUORB_E_UNSUPPORTED; }
+  if (n_in_view_out) *n_in_view_out = 0;
+  if (best_idx_out) for (int i = 0; i < M; i++) best_idx_out[i] = -1;
+  if (M == 0) return 0;
+  CUORB_CUDA_TRY(cudaSetDevice(m->device));
+  cudaStream_t st = m->stream;
+  const size_t bytes = frame_bytes(std::max(n, 1)) + (size_t)std::max(n, 1) * 8 + (size_t)n_skip * 4 + 64 * 1024;
+  if (t_arena.reserve(m->device, bytes) != 0) { set_error("cudaMalloc failed (local map search workspace)"); return CUORB_E_CUDA; }
+  Arena& A = t_arena;
+  CUORB_CUDA_TRY(cudaMemsetAsync(m->skip, 0, (size_t)M, st));
+  CUORB_CUDA_TRY(cudaMemsetAsync(m->counters, 0, 2 * sizeof(int), st));
+  if (n_skip) {
+    const int* d_idx = up(A, skip_idx, n_skip, st);
+    k_mark_skip<<<(n_skip + 255) / 256, 256, 0, st>>>(n_skip, d_idx, M, m->skip);
+    count_launch();
+  }
+  k_localmap_frustum<<<(M + 127) / 128, 128, 0, st>>>(*cam, M, m->P, m->N, m->minD, m->maxD, m->pflags, m->skip, viewing_cos_limit,
+                                                      m->px, m->py, m->pxr, m->lv, m->vc, m->dz, m->qflags, m->counters);
+  count_launch();
+  int nmatches = 0;
+  if (n > 0) {
+    ProjFrame F;
+    upload_frame(A, frame, st, F);
+    ProjQuery Q{};
+    Q.n = M; Q.mode = 0; Q.th = th; Q.thFar = th_far_points; Q.nnratio = nn_ratio; Q.far_points = far_points;
+    Q.desc = m->desc; Q.px = m->px; Q.py = m->py; Q.aux = m->pxr; Q.level = m->lv; Q.viewcos = m->vc; Q.depth = m->dz;
+    Q.flags = m->qflags;
+    const int rounds = projection_rounds(A, st, F, Q, m->result);
+    if (rounds < 0) return rounds;
+    k_compact_matches<<<(M + 255) / 256, 256, 0, st>>>(M, m->result, match_capacity, m->match_mp, m->match_feat, m->counters + 1);
+    count_launch();
+  }
+  CUORB_CUDA_TRY(cudaMemcpyAsync(m->h_counters, m->counters, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+  if (best_idx_out && n > 0) CUORB_CUDA_TRY(cudaMemcpyAsync(best_idx_out, m->result, sizeof(int) * (size_t)M, cudaMemcpyDeviceToHost, st));
+  // the pairs come back with the counters in one round trip: the first match_capacity slots, whatever they hold
+  const int fetch = n > 0 ? std::min(match_capacity, M) : 0;
+  if (fetch > 0) {
+    CUORB_CUDA_TRY(cudaMemcpyAsync(match_point_out, m->match_mp, sizeof(int) * (size_t)fetch, cudaMemcpyDeviceToHost, st));
+    CUORB_CUDA_TRY(cudaMemcpyAsync(match_feature_out, m->match_feat, sizeof(int) * (size_t)fetch, cudaMemcpyDeviceToHost, st));
+  }
+  CUORB_CUDA_TRY(cudaStreamSynchronize(st));
+  if (n_in_view_out) *n_in_view_out = m->h_counters[0];
+  nmatches = m->h_counters[1];
+  if (match_capacity) {
+    if (nmatches > match_capacity) { set_error("cuorb_localmap_search: more matches than match_capacity"); return CUORB_E_CAPACITY; }
+    // MapPoint order = the order in which the caller replays F.mvpMapPoints[feature] = pMP
+    std::vector<std::pair<int32_t, int32_t>> pairs((size_t)nmatches);
+    for (int k = 0; k < nmatches; k++) pairs[k] = {match_point_out[k], match_feature_out[k]};
+    std::sort(pairs.begin(), pairs.end());
+    for (int k = 0; k < nmatches; k++) { match_point_out[k] = pairs[k].first; match_feature_out[k] = pairs[k].second; }
+  }
+  return nmatches;
 }
 
 }  // extern "C"

@@ -68,3 +68,54 @@ def isInFrustum(camera, world_pos, normal, mfMinDistance, mfMaxDistance, viewing
                                                ("mbTrackInView", "mTrackProjX", "mTrackProjY", "mTrackProjXR",
                                                 "mnTrackScaleLevel", "mTrackViewCos", "mTrackDepth")]))
     return out
+
+
+class LocalMap:
+    """A local map resident on the device (include/cuorb.h, cuorb_localmap_*): Tracking::SearchLocalPoints' isInFrustum
+    loop and ORBmatcher::SearchByProjection(F, mvpLocalMapPoints, ...) in one call per frame."""
+
+    def __init__(self, capacity, device=0):
+        self._L = _lib.load()
+        self.capacity = int(capacity)
+        self._h = self._L.cuorb_localmap_create(int(device), int(capacity))
+        if not self._h:
+            raise RuntimeError("cuorb_localmap_create: " + _lib.last_error())
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._L.cuorb_localmap_destroy(self._h)
+            self._h = None
+
+    def update(self, first, world_pos, normal, mfMinDistance, mfMaxDistance, descriptors, isBad, hasObservations,
+               new_count=None):
+        P = np.ascontiguousarray(world_pos, np.float32).reshape(-1, 3); N = np.ascontiguousarray(normal, np.float32).reshape(-1, 3)
+        mn = np.ascontiguousarray(mfMinDistance, np.float32); mx = np.ascontiguousarray(mfMaxDistance, np.float32)
+        d = np.ascontiguousarray(descriptors, np.uint8).reshape(-1, 32)
+        fl = (np.asarray(isBad, np.uint8) * _lib.MP_BAD | np.asarray(hasObservations, np.uint8) * _lib.MP_HAS_OBS).astype(np.uint8)
+        n = len(P)
+        cnt = max(self.count, first + n) if new_count is None else int(new_count)
+        check(self._L.cuorb_localmap_update(self._h, int(first), n, cnt, ptr(P), ptr(N), ptr(mn), ptr(mx), ptr(d), ptr(fl)))
+
+    @property
+    def count(self):
+        return check(self._L.cuorb_localmap_count(self._h))
+
+    def search(self, camera, frame, skip_idx=(), viewingCosLimit=0.5, th=1.0, bFarPoints=False, thFarPoints=50.0, nnratio=0.8,
+               match_capacity=None, want_best=True):
+        """frame: matcher.Frame.  Returns (nmatches, n_in_view, match_point, match_feature, best_idx or None) and
+        replays F.mvpMapPoints[feature] = point in point order."""
+        import ctypes as C
+        fv, keep = frame.view()
+        skip = np.ascontiguousarray(np.asarray(skip_idx, np.int32))
+        M = self.count
+        cap = int(match_capacity) if match_capacity is not None else max(M, 1)
+        mp = np.full(max(cap, 1), -1, np.int32); ft = np.full(max(cap, 1), -1, np.int32)
+        best = np.full(max(M, 1), -1, np.int32) if want_best else None
+        nin = C.c_int32(0)
+        n = check(self._L.cuorb_localmap_search(self._h, C.byref(camera), C.byref(fv), len(skip), ptr(skip) if len(skip) else None,
+                                                float(viewingCosLimit), float(th), int(bFarPoints), float(thFarPoints),
+                                                float(nnratio), ptr(best) if want_best else None, cap, ptr(mp), ptr(ft),
+                                                C.byref(nin)))
+        for p, f in zip(mp[:n], ft[:n]):
+            frame.mvpMapPoints[f] = p
+        return n, nin.value, mp[:n].copy(), ft[:n].copy(), (best[:M] if want_best else None)

@@ -150,3 +150,76 @@ def lastframe_pose_case(k, d, seed, motion, w=752, h=480):
     bound = (rng.random(N) < 0.05).astype(np.uint8)
     return dict(K4=K4, pose_cur=pose_cur, pose_last=pose_last, world=world, desc=desc, octave=octave, angle=angle,
                 has_mp=has_mp, outlier=outlier, n_obs=n_obs, u_right=u_right, bound=bound)
+
+
+def localmap_case(k, d, scale_factors, M, seed, w=752, h=480):
+    """Tracking::SearchLocalPoints inputs with the geometry live: a camera pose and M world points; ~25 % are
+    back-projections of frame features (bit-flipped descriptors, distance range chosen so that PredictScale lands on
+    or next to the feature's octave, normals near the viewing ray), several points per feature, the rest are
+    distractors all around the frustum; some points are bad, some have no observations, some are already matched."""
+    rng = np.random.default_rng(seed)
+    N = len(k)
+    a = rng.uniform(-0.3, 0.3, 3)
+    Rx = np.array([[1, 0, 0], [0, np.cos(a[0]), -np.sin(a[0])], [0, np.sin(a[0]), np.cos(a[0])]])
+    Ry = np.array([[np.cos(a[1]), 0, np.sin(a[1])], [0, 1, 0], [-np.sin(a[1]), 0, np.cos(a[1])]])
+    Rz = np.array([[np.cos(a[2]), -np.sin(a[2]), 0], [np.sin(a[2]), np.cos(a[2]), 0], [0, 0, 1]])
+    R = (Rz @ Ry @ Rx).astype(np.float32)
+    t = rng.uniform(-2, 2, 3).astype(np.float32)
+    K4 = (458.654, 457.296, 367.215, 248.375)
+    mbf = 47.906
+    cam = op.make_frustum_camera(R, t, K4, mbf, w, h)
+    n_true = int(0.25 * M)
+    tgt = rng.integers(0, N, n_true)
+    tgt[:n_true // 10] = tgt[n_true // 10:2 * (n_true // 10)]          # several MapPoints chase the same feature
+    sel = rng.permutation(M)[:n_true]
+    u = rng.uniform(-100, w + 100, M); v = rng.uniform(-100, h + 100, M)
+    z = rng.uniform(-2, 40, M)
+    u[sel] = k["x"][tgt] + rng.uniform(-1.5, 1.5, n_true); v[sel] = k["y"][tgt] + rng.uniform(-1.5, 1.5, n_true)
+    z[sel] = rng.uniform(1.0, 30.0, n_true)
+    pc = np.stack([(u - K4[2]) / K4[0] * z, (v - K4[3]) / K4[1] * z, z], 1)
+    P = ((pc - t.astype(np.float64)) @ R.astype(np.float64)).astype(np.float32)
+    ow = np.array(cam.ow[:], np.float64)
+    po = P.astype(np.float64) - ow
+    dist = np.linalg.norm(po, axis=1) + 1e-9
+    nrm = po / dist[:, None] + rng.normal(0, 0.5, (M, 3))
+    nrm[sel] = po[sel] / dist[sel, None] + rng.normal(0, 0.15, (n_true, 3))
+    nrm /= np.linalg.norm(nrm, axis=1)[:, None] + 1e-12
+    max_d = (dist * rng.uniform(0.6, 3.0, M)).astype(np.float32)
+    lvl = np.minimum(k["octave"][tgt] + rng.integers(0, 2, n_true), 7)
+    max_d[sel] = (dist[sel] * 1.2 ** (lvl - 0.5)).astype(np.float32)    # PredictScale -> lvl
+    min_d = (max_d / np.float32(1.2 ** 7) * rng.uniform(0.3, 1.0, M)).astype(np.float32)
+    desc = rng.integers(0, 256, (M, 32), dtype=np.uint8)
+    desc[sel] = flip_bits(d[tgt], rng)
+    bad = (rng.random(M) < 0.03).astype(np.uint8)
+    has_obs = (rng.random(M) < 0.92).astype(np.uint8)
+    skip_idx = rng.permutation(M)[:M // 40].astype(np.int32)            # mnLastFrameSeen == this frame
+    u_right = np.where(rng.random(N) < 0.6, k["x"] - rng.uniform(1, 60, N), -1).astype(np.float32)
+    ok = u_right[tgt] > 0
+    # depth consistent with the feature's right coordinate for most stereo targets: z = mbf / disparity
+    zz = np.where(ok & (rng.random(n_true) < 0.8), mbf / np.maximum(k["x"][tgt] - u_right[tgt], 1e-3), z[sel])
+    pc[sel] = np.stack([(u[sel] - K4[2]) / K4[0] * zz, (v[sel] - K4[3]) / K4[1] * zz, zz], 1)
+    P[sel] = ((pc[sel] - t.astype(np.float64)) @ R.astype(np.float64)).astype(np.float32)
+    po = P.astype(np.float64) - ow
+    dist2 = np.linalg.norm(po, axis=1) + 1e-9
+    max_d[sel] = (dist2[sel] * 1.2 ** (lvl - 0.5)).astype(np.float32)
+    min_d[sel] = (max_d[sel] / np.float32(1.2 ** 7) * 0.5).astype(np.float32)
+    nrm[sel] = po[sel] / dist2[sel, None] + rng.normal(0, 0.15, (n_true, 3))
+    nrm /= np.linalg.norm(nrm, axis=1)[:, None] + 1e-12
+    bound = (rng.random(N) < 0.1).astype(np.uint8)
+    return dict(cam=cam, P=P, N=nrm.astype(np.float32), min_d=min_d, max_d=max_d, desc=desc, bad=bad, has_obs=has_obs,
+                skip_idx=skip_idx, u_right=u_right, bound=bound, mbf=mbf)
+
+
+def localmap_expected(c, k, d, sf, frustum_fn, search_fn, th, far, th_far, ratio, limit=0.5, w=752, h=480):
+    """The same computation from its two parts: isInFrustum for the points that are neither skipped nor bad, then
+    SearchByProjection over all points with the resulting tracking fields.  frustum_fn / search_fn: the oracle's or the
+    reference's (oracle_py / ref_py)."""
+    M = len(c["P"])
+    f = frustum_fn(c["cam"], c["P"], c["N"], c["min_d"], c["max_d"], limit)
+    skip = np.zeros(M, bool); skip[c["skip_idx"]] = True
+    in_view = (f["in_view"] > 0) & ~skip & (c["bad"] == 0)
+    flags = (in_view * 1 + c["bad"] * 2 + c["has_obs"] * 4).astype(np.uint8)
+    fv, keep = op.make_frame_view(k, d, c["u_right"], c["bound"], w, h, sf, mb=0.1, mbf=c["mbf"])
+    res = search_fn(fv, c["desc"], f["proj_x"], f["proj_y"], f["proj_xr"], np.maximum(f["level"], 0), f["view_cos"], f["depth"],
+                    flags, th, far, th_far, ratio)
+    return int(in_view.sum()), res[0], res[1]
