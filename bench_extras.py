@@ -412,8 +412,8 @@ def localmap_track(local, with_cpu=True, M=50000, frame=None):
     mp = np.zeros(cap, np.int32); ft = np.zeros(cap, np.int32); nin = C.c_int32(0)
 
     def call():
-        return _lib.check(L_.cuorb_localmap_search(m._h, C.byref(cam), C.byref(fvv), len(skip), _lib.ptr(skip), 0.5, 1.0, 0, 50.0,
-                                                   0.8, None, cap, _lib.ptr(mp), _lib.ptr(ft), C.byref(nin)))
+        return _lib.check(L_.cuorb_localmap_search(m._h, C.byref(cam), C.byref(fvv), 0, None, len(skip), _lib.ptr(skip), 0.5, 1.0,
+                                                   0, 50.0, 0.8, None, None, cap, _lib.ptr(mp), _lib.ptr(ft), C.byref(nin)))
     n = call()
     for _ in range(5):
         call()

@@ -404,15 +404,21 @@ int cuorb_localmap_update(cuorb_localmap* map, int first, int n, int new_count, 
                           const uint8_t* descriptors, const uint8_t* flags);
 int cuorb_localmap_count(const cuorb_localmap* map);
 /* One frame.  cam: the Frame's pose / intrinsics as for cuorb_is_in_frustum; frame: as for
- * cuorb_search_by_projection; skip_idx[n_skip]: points to leave out (already matched in this frame).  Outputs (host):
- * best_idx_out[count] (optional, may be NULL) = feature bound to each point or -1; match_point_out /
- * match_feature_out[match_capacity] = the matches as (point, feature) pairs in point order, the order in which the
- * caller replays F.mvpMapPoints[feature] = pMP (CUORB_E_CAPACITY if there are more than match_capacity);
- * n_in_view_out = number of points isInFrustum accepted (the reference's nToMatch).  Returns nmatches. */
-int cuorb_localmap_search(cuorb_localmap* map, const cuorb_frustum_camera* cam, const cuorb_frame_view* frame, int n_skip,
-                          const int32_t* skip_idx, float viewing_cos_limit, float th, int far_points,
-                          float th_far_points, float nn_ratio, int32_t* best_idx_out, int match_capacity,
-                          int32_t* match_point_out, int32_t* match_feature_out, int32_t* n_in_view_out);
+ * cuorb_search_by_projection.  order[n_order] (may be NULL = slots 0 .. count-1 in storage order): the storage slots
+ * of mvpLocalMapPoints in the order Tracking holds them this frame - the reference's loops run in that order and the
+ * order decides who gets a contested feature, so storage can stay put while the vector is rebuilt every frame
+ * (n_order <= capacity; a slot outside [0, count) counts as a bad point).  Everything below is indexed by POSITION in
+ * that sequence.  skip_pos[n_skip]: positions to leave out (mnLastFrameSeen == this frame).  Outputs (host):
+ * best_idx_out[n] (optional) = feature bound to each position or -1; in_view_out[n] (optional) = mbTrackInView as
+ * isInFrustum leaves it (the caller's IncreaseVisible loop); match_pos_out / match_feature_out[match_capacity] = the
+ * matches as (position, feature) pairs in sequence order, the order in which the caller replays
+ * F.mvpMapPoints[feature] = pMP (CUORB_E_CAPACITY if there are more than match_capacity); n_in_view_out = number of
+ * points isInFrustum accepted (the reference's nToMatch).  Returns nmatches. */
+int cuorb_localmap_search(cuorb_localmap* map, const cuorb_frustum_camera* cam, const cuorb_frame_view* frame, int n_order,
+                          const int32_t* order, int n_skip, const int32_t* skip_pos, float viewing_cos_limit, float th,
+                          int far_points, float th_far_points, float nn_ratio, int32_t* best_idx_out,
+                          uint8_t* in_view_out, int match_capacity, int32_t* match_pos_out, int32_t* match_feature_out,
+                          int32_t* n_in_view_out);
 
 
 /* void Frame::ComputeStereoFromRGBD(const cv::Mat& imDepth) (src/Frame.cc:1115-1133): depth = CV_32F

@@ -105,8 +105,9 @@ SIGNATURES = {
     "cuorb_localmap_destroy": (None, [C.c_void_p]),
     "cuorb_localmap_update": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 6),
     "cuorb_localmap_count": (C.c_int, [C.c_void_p]),
-    "cuorb_localmap_search": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(FrameView), C.c_int, C.c_void_p, C.c_float, C.c_float,
-                                        C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "cuorb_localmap_search": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(FrameView), C.c_int, C.c_void_p, C.c_int, C.c_void_p,
+                                        C.c_float, C.c_float, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_int,
+                                        C.c_void_p, C.c_void_p, C.c_void_p]),
     "cuorb_preproc_create": (C.c_void_p, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                           C.c_void_p, C.c_int]),
     "cuorb_preproc_destroy": (None, [C.c_void_p]),

@@ -32,6 +32,7 @@ struct ProjQuery {
   const uint8_t* flags;
   int mode;                    // 0: local-map points, 1: last-frame points, 2: last-frame points into the right camera of a rig
   int* gate_out;               // optional: 1 where GetFeaturesInArea returned a non-empty window (binding independent)
+  const int* slot;             // optional: descriptor row of query i (resident local map: storage slot of sequence position i)
   const int* gate_in;          // mode 2: the left pass's gate_out (the right part sits behind the left part's `continue`s)
   float th, thFar, nnratio;
   int far_points, forward, backward;
@@ -102,7 +103,7 @@ __global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, ProjQuery Q,
   }
   if (active) {
     const bool checkLevels = (minLevel > 0) || (maxLevel >= 0);
-    const uint4* qd = reinterpret_cast<const uint4*>(Q.desc + (size_t)i * 32);
+    const uint4* qd = reinterpret_cast<const uint4*>(Q.desc + (size_t)(Q.slot ? Q.slot[i] : i) * 32);
     const uint4 q0 = qd[0], q1 = qd[1];
     const float aux = Q.aux ? Q.aux[i] : 0.f;
     unsigned long long b1 = ~0ull, b2 = ~0ull;  // (dist << 32 | visiting position), two smallest
@@ -185,6 +186,7 @@ __global__ void k_hamming_pairs(const uint8_t* a, const uint8_t* b, const int* i
 
 // ---- host side ----
 thread_local Arena t_arena;
+thread_local HostStage t_stage;
 
 // Binding rounds to the sequential fixed point on device-resident queries; result: device, m ints.  Returns the
 // number of rounds (>= 1) or a negative error code; the stream is synchronised on return.
@@ -269,7 +271,8 @@ static int run_projection(int device, const cuorb_frame_view* fv, ProjQuery Q, c
 // followed by SearchByProjection) ----
 // grid: ceil(n/128).  Per MapPoint: skipped (mnLastFrameSeen == this frame) or bad points are not in view; the
 // rest go through Frame::isInFrustum (frustum.cuh) and leave their tracking fields in the map's resident SoA.
-__global__ void k_localmap_frustum(const cuorb_frustum_camera c, int n, const float* __restrict__ P3, const float* __restrict__ N3,
+__global__ void k_localmap_frustum(const cuorb_frustum_camera c, int n, const int* __restrict__ order, int n_slots,
+                                   const float* __restrict__ P3, const float* __restrict__ N3,
                                    const float* __restrict__ minD, const float* __restrict__ maxD, const uint8_t* __restrict__ pflags,
                                    const uint8_t* __restrict__ skip, float limit, float* __restrict__ projX,
                                    float* __restrict__ projY, float* __restrict__ projXR, int* __restrict__ level,
@@ -278,11 +281,12 @@ __global__ void k_localmap_frustum(const cuorb_frustum_camera c, int n, const fl
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   bool ok = false;
   if (i < n) {
-    const unsigned pf = pflags[i];
+    const int s = order ? order[i] : i;                           // storage slot of sequence position i
+    const unsigned pf = (s >= 0 && s < n_slots) ? pflags[s] : CUORB_MP_BAD;
     FrustumOut o;
     o.px = -1.f; o.py = -1.f; o.pxr = -1.f; o.vc = 0.f; o.dz = 0.f; o.lv = 0;
     if (!skip[i] && !(pf & CUORB_MP_BAD))
-      ok = frustum_point(c, P3[3 * i], P3[3 * i + 1], P3[3 * i + 2], N3[3 * i], N3[3 * i + 1], N3[3 * i + 2], minD[i], maxD[i], limit, o);
+      ok = frustum_point(c, P3[3 * s], P3[3 * s + 1], P3[3 * s + 2], N3[3 * s], N3[3 * s + 1], N3[3 * s + 2], minD[s], maxD[s], limit, o);
     projX[i] = o.px; projY[i] = o.py; projXR[i] = o.pxr; level[i] = ok ? o.lv : 0; viewCos[i] = o.vc; depth[i] = o.dz;
     qflags[i] = (uint8_t)((ok ? CUORB_MP_IN_VIEW : 0u) | (pf & (CUORB_MP_BAD | CUORB_MP_HAS_OBS)));
   }
@@ -482,7 +486,7 @@ struct cuorb_localmap {
   float *P = nullptr, *N = nullptr, *minD = nullptr, *maxD = nullptr;
   uint8_t *desc = nullptr, *pflags = nullptr, *skip = nullptr, *qflags = nullptr;
   float *px = nullptr, *py = nullptr, *pxr = nullptr, *vc = nullptr, *dz = nullptr;
-  int *lv = nullptr, *result = nullptr, *match_mp = nullptr, *match_feat = nullptr, *counters = nullptr;
+  int *lv = nullptr, *result = nullptr, *match_mp = nullptr, *match_feat = nullptr, *counters = nullptr, *order = nullptr;
   int *h_counters = nullptr;    // pinned: [0] in view, [1] matches
   cudaStream_t stream = nullptr;
 };
@@ -497,7 +501,7 @@ cuorb_localmap* cuorb_localmap_create(int device, int capacity) {
   auto al = [&](auto** p, size_t bytes) { if (ok && cudaMalloc((void**)p, bytes) != cudaSuccess) ok = false; };
   al(&m->P, 12 * c); al(&m->N, 12 * c); al(&m->minD, 4 * c); al(&m->maxD, 4 * c); al(&m->desc, 32 * c); al(&m->pflags, c);
   al(&m->skip, c); al(&m->qflags, c); al(&m->px, 4 * c); al(&m->py, 4 * c); al(&m->pxr, 4 * c); al(&m->vc, 4 * c);
-  al(&m->dz, 4 * c); al(&m->lv, 4 * c); al(&m->result, 4 * c); al(&m->match_mp, 4 * c); al(&m->match_feat, 4 * c);
+  al(&m->dz, 4 * c); al(&m->lv, 4 * c); al(&m->result, 4 * c); al(&m->match_mp, 4 * c); al(&m->match_feat, 4 * c); al(&m->order, 4 * c);
   al(&m->counters, 2 * sizeof(int));
   if (ok && cudaHostAlloc((void**)&m->h_counters, 2 * sizeof(int), cudaHostAllocDefault) != cudaSuccess) ok = false;
   if (ok && cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess) ok = false;
@@ -511,7 +515,7 @@ void cuorb_localmap_destroy(cuorb_localmap* m) {
   cudaSetDevice(m->device);
   if (m->stream) { cudaStreamSynchronize(m->stream); cudaStreamDestroy(m->stream); }
   void* ptrs[] = {m->P, m->N, m->minD, m->maxD, m->desc, m->pflags, m->skip, m->qflags, m->px, m->py, m->pxr, m->vc, m->dz,
-                  m->lv, m->result, m->match_mp, m->match_feat, m->counters};
+                  m->lv, m->result, m->match_mp, m->match_feat, m->counters, m->order};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (m->h_counters) cudaFreeHost(m->h_counters);
   delete m;
@@ -543,19 +547,21 @@ int cuorb_localmap_update(cuorb_localmap* m, int first, int n, int new_count, co
 
 int cuorb_localmap_count(const cuorb_localmap* m) { return m ? m->count : CUORB_E_BADARG; }
 
-int cuorb_localmap_search(cuorb_localmap* m, const cuorb_frustum_camera* cam, const cuorb_frame_view* frame, int n_skip,
-                          const int32_t* skip_idx, float viewing_cos_limit, float th, int far_points, float th_far_points,
-                          float nn_ratio, int32_t* best_idx_out, int match_capacity, int32_t* match_point_out,
-                          int32_t* match_feature_out, int32_t* n_in_view_out) {
+int cuorb_localmap_search(cuorb_localmap* m, const cuorb_frustum_camera* cam, const cuorb_frame_view* frame, int n_order,
+                          const int32_t* order, int n_skip, const int32_t* skip_pos, float viewing_cos_limit, float th,
+                          int far_points, float th_far_points, float nn_ratio, int32_t* best_idx_out, uint8_t* in_view_out,
+                          int match_capacity, int32_t* match_pos_out, int32_t* match_feature_out, int32_t* n_in_view_out) {
   if (!m || !cam || !frame || !frame->keys_un || !frame->descriptors || !frame->scale_factors || n_skip < 0 ||
-      (n_skip && !skip_idx) || match_capacity < 0 || (match_capacity && (!match_point_out || !match_feature_out))) {
+      (n_skip && !skip_pos) || match_capacity < 0 || (match_capacity && (!match_pos_out || !match_feature_out)) ||
+      n_order < 0 || (order && n_order > m->capacity)) {
     set_error("cuorb_localmap_search: bad argument");
     return CUORB_E_BADARG;
   }
-  const int n = frame->n, M = m->count;
+  const int n = frame->n, M = order ? n_order : m->count;      // sequence length: the order the points are processed in
   if (n > 65535 || frame->nlevels > MAX_LEVELS) { set_error("frame too large for projection search"); return CUORB_E_UNSUPPORTED; }
   if (n_in_view_out) *n_in_view_out = 0;
   if (best_idx_out) for (int i = 0; i < M; i++) best_idx_out[i] = -1;
+  if (in_view_out) for (int i = 0; i < M; i++) in_view_out[i] = 0;
   if (M == 0) return 0;
   CUORB_CUDA_TRY(cudaSetDevice(m->device));
   cudaStream_t st = m->stream;
@@ -564,13 +570,15 @@ int cuorb_localmap_search(cuorb_localmap* m, const cuorb_frustum_camera* cam, co
   Arena& A = t_arena;
   CUORB_CUDA_TRY(cudaMemsetAsync(m->skip, 0, (size_t)M, st));
   CUORB_CUDA_TRY(cudaMemsetAsync(m->counters, 0, 2 * sizeof(int), st));
+  if (order) CUORB_CUDA_TRY(cudaMemcpyAsync(m->order, order, sizeof(int) * (size_t)M, cudaMemcpyHostToDevice, st));
   if (n_skip) {
-    const int* d_idx = up(A, skip_idx, n_skip, st);
+    const int* d_idx = up(A, skip_pos, n_skip, st);
     k_mark_skip<<<(n_skip + 255) / 256, 256, 0, st>>>(n_skip, d_idx, M, m->skip);
     count_launch();
   }
-  k_localmap_frustum<<<(M + 127) / 128, 128, 0, st>>>(*cam, M, m->P, m->N, m->minD, m->maxD, m->pflags, m->skip, viewing_cos_limit,
-                                                      m->px, m->py, m->pxr, m->lv, m->vc, m->dz, m->qflags, m->counters);
+  k_localmap_frustum<<<(M + 127) / 128, 128, 0, st>>>(*cam, M, order ? m->order : nullptr, m->count, m->P, m->N, m->minD, m->maxD,
+                                                      m->pflags, m->skip, viewing_cos_limit, m->px, m->py, m->pxr, m->lv,
+                                                      m->vc, m->dz, m->qflags, m->counters);
   count_launch();
   int nmatches = 0;
   if (n > 0) {
@@ -579,30 +587,32 @@ int cuorb_localmap_search(cuorb_localmap* m, const cuorb_frustum_camera* cam, co
     ProjQuery Q{};
     Q.n = M; Q.mode = 0; Q.th = th; Q.thFar = th_far_points; Q.nnratio = nn_ratio; Q.far_points = far_points;
     Q.desc = m->desc; Q.px = m->px; Q.py = m->py; Q.aux = m->pxr; Q.level = m->lv; Q.viewcos = m->vc; Q.depth = m->dz;
-    Q.flags = m->qflags;
+    Q.flags = m->qflags; Q.slot = order ? m->order : nullptr;
     const int rounds = projection_rounds(A, st, F, Q, m->result);
     if (rounds < 0) return rounds;
     k_compact_matches<<<(M + 255) / 256, 256, 0, st>>>(M, m->result, match_capacity, m->match_mp, m->match_feat, m->counters + 1);
     count_launch();
   }
+  if (in_view_out) CUORB_CUDA_TRY(cudaMemcpyAsync(in_view_out, m->qflags, (size_t)M, cudaMemcpyDeviceToHost, st));
   CUORB_CUDA_TRY(cudaMemcpyAsync(m->h_counters, m->counters, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
   if (best_idx_out && n > 0) CUORB_CUDA_TRY(cudaMemcpyAsync(best_idx_out, m->result, sizeof(int) * (size_t)M, cudaMemcpyDeviceToHost, st));
   // the pairs come back with the counters in one round trip: the first match_capacity slots, whatever they hold
   const int fetch = n > 0 ? std::min(match_capacity, M) : 0;
   if (fetch > 0) {
-    CUORB_CUDA_TRY(cudaMemcpyAsync(match_point_out, m->match_mp, sizeof(int) * (size_t)fetch, cudaMemcpyDeviceToHost, st));
+    CUORB_CUDA_TRY(cudaMemcpyAsync(match_pos_out, m->match_mp, sizeof(int) * (size_t)fetch, cudaMemcpyDeviceToHost, st));
     CUORB_CUDA_TRY(cudaMemcpyAsync(match_feature_out, m->match_feat, sizeof(int) * (size_t)fetch, cudaMemcpyDeviceToHost, st));
   }
   CUORB_CUDA_TRY(cudaStreamSynchronize(st));
   if (n_in_view_out) *n_in_view_out = m->h_counters[0];
+  if (in_view_out) for (int i = 0; i < M; i++) in_view_out[i] &= CUORB_MP_IN_VIEW;
   nmatches = m->h_counters[1];
   if (match_capacity) {
     if (nmatches > match_capacity) { set_error("cuorb_localmap_search: more matches than match_capacity"); return CUORB_E_CAPACITY; }
     // MapPoint order = the order in which the caller replays F.mvpMapPoints[feature] = pMP
     std::vector<std::pair<int32_t, int32_t>> pairs((size_t)nmatches);
-    for (int k = 0; k < nmatches; k++) pairs[k] = {match_point_out[k], match_feature_out[k]};
+    for (int k = 0; k < nmatches; k++) pairs[k] = {match_pos_out[k], match_feature_out[k]};
     std::sort(pairs.begin(), pairs.end());
-    for (int k = 0; k < nmatches; k++) { match_point_out[k] = pairs[k].first; match_feature_out[k] = pairs[k].second; }
+    for (int k = 0; k < nmatches; k++) { match_pos_out[k] = pairs[k].first; match_feature_out[k] = pairs[k].second; }
   }
   return nmatches;
 }

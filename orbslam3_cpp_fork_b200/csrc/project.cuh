@@ -3,6 +3,7 @@
 #pragma once
 #include <algorithm>
 #include <cmath>
+#include <cstring>
 #include <vector>
 
 #include "common.cuh"
@@ -70,14 +71,40 @@ inline T* up(Arena& A, const T* host, size_t count, cudaStream_t st) {
 
 inline size_t frame_bytes(int n) { return (size_t)n * (4 * 4 + 2 * 2 + 32 + 1 + 8 + 2) + (FRAME_GRID_ROWS * FRAME_GRID_COLS + 1) * 4 + 20 * 256; }
 
-// host-side flattening of the Frame: SoA + PosInGrid (src/Frame.cc:867-877, std::round); the arena must
-// already hold frame_bytes(n) more bytes
+struct HostStage {  // grow-only pinned staging per host thread: a Frame's SoA goes up as ONE copy
+  void* p = nullptr; size_t cap = 0;
+  void* get(size_t bytes) {
+    if (bytes > cap) {
+      if (p) { cudaFreeHost(p); p = nullptr; cap = 0; }
+      if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) { p = nullptr; return nullptr; }
+      cap = bytes;
+    }
+    return p;
+  }
+};
+extern thread_local HostStage t_stage;
+
+// host-side flattening of the Frame: SoA + PosInGrid (src/Frame.cc:867-877, std::round) + the cell-sorted CSR, laid
+// out in one pinned staging block and sent with one copy (ten small pageable copies before: ~35 us of a 0.3-0.5 ms
+// call); the arena must already hold frame_bytes(n) more bytes.  Synchronises the stream: the staging block is reused.
 inline void upload_frame(Arena& A, const cuorb_frame_view* fv, cudaStream_t st, ProjFrame& F) {
-  const int n = fv->n;
-  std::vector<float> fx(n), fy(n);
-  std::vector<int> foct(n);
-  std::vector<short> cxv(n), cyv(n);
-  std::vector<uint8_t> blk(n, 0);
+  const int n = fv->n, nn = std::max(n, 1);
+  const int ncell = FRAME_GRID_ROWS * FRAME_GRID_COLS + 1;
+  size_t off = 0;
+  auto slot = [&](size_t bytes) { const size_t o = off; off = (off + bytes + 255) & ~(size_t)255; return o; };
+  const size_t o_cstart = slot(sizeof(int) * ncell), o_order = slot(2 * (size_t)nn), o_x = slot(4 * (size_t)nn), o_y = slot(4 * (size_t)nn),
+               o_ur = slot(fv->u_right ? 4 * (size_t)nn : 0), o_oct = slot(4 * (size_t)nn), o_cx = slot(2 * (size_t)nn),
+               o_cy = slot(2 * (size_t)nn), o_desc = slot(32 * (size_t)nn), o_blk = slot((size_t)nn);
+  const size_t total = off;
+  unsigned char* h = (unsigned char*)t_stage.get(total);
+  std::vector<unsigned char> fallback;
+  if (!h) { fallback.resize(total); h = fallback.data(); }   // pinned allocation failed: a pageable block still works
+  int* cstart = (int*)(h + o_cstart); unsigned short* order = (unsigned short*)(h + o_order);
+  float *fx = (float*)(h + o_x), *fy = (float*)(h + o_y);
+  int* foct = (int*)(h + o_oct);
+  short *cxv = (short*)(h + o_cx), *cyv = (short*)(h + o_cy);
+  uint8_t* blk = h + o_blk;
+  for (int c = 0; c < ncell; c++) cstart[c] = 0;
   for (int i = 0; i < n; i++) {
     const cuorb_keypoint& k = fv->keys_un[i];
     fx[i] = k.x; fy[i] = k.y; foct[i] = k.octave;
@@ -85,30 +112,30 @@ inline void upload_frame(Arena& A, const cuorb_frame_view* fv, cudaStream_t st, 
     const int posY = (int)std::round((k.y - fv->min_y) * fv->grid_h_inv);
     const bool in = !(posX < 0 || posX >= FRAME_GRID_COLS || posY < 0 || posY >= FRAME_GRID_ROWS);
     cxv[i] = in ? (short)posX : (short)-1; cyv[i] = in ? (short)posY : (short)-1;
-    if (fv->bound_with_obs) blk[i] = fv->bound_with_obs[i];
+    blk[i] = fv->bound_with_obs ? fv->bound_with_obs[i] : 0;
+    if (in) cstart[posY * FRAME_GRID_COLS + posX + 1]++;          // counting sort of the in-grid features by cell
   }
-  // counting sort of the in-grid features by cell
-  std::vector<int> cstart(FRAME_GRID_ROWS * FRAME_GRID_COLS + 1, 0);
-  for (int i = 0; i < n; i++) if (cxv[i] >= 0) cstart[cyv[i] * FRAME_GRID_COLS + cxv[i] + 1]++;
-  for (size_t c = 1; c < cstart.size(); c++) cstart[c] += cstart[c - 1];
-  std::vector<unsigned short> order((size_t)std::max(n, 1));
+  for (int c = 1; c < ncell; c++) cstart[c] += cstart[c - 1];
   {
-    std::vector<int> fill(cstart.begin(), cstart.end() - 1);
+    std::vector<int> fill(cstart, cstart + ncell - 1);
     for (int i = 0; i < n; i++) if (cxv[i] >= 0) order[fill[cyv[i] * FRAME_GRID_COLS + cxv[i]]++] = (unsigned short)i;
   }
+  if (n) memcpy(h + o_desc, fv->descriptors, 32 * (size_t)n);
+  if (fv->u_right && n) memcpy(h + o_ur, fv->u_right, 4 * (size_t)n);
+  unsigned char* d = A.take<unsigned char>(total);
+  cudaMemcpyAsync(d, h, total, cudaMemcpyHostToDevice, st);
   F.n = n;
-  F.cstart = up(A, cstart.data(), cstart.size(), st);
-  F.order = up(A, order.data(), order.size(), st);
-  F.x = up(A, fx.data(), n, st); F.y = up(A, fy.data(), n, st);
-  F.uright = fv->u_right ? up(A, fv->u_right, n, st) : nullptr;
-  F.octave = up(A, foct.data(), n, st);
-  F.cellx = up(A, cxv.data(), n, st); F.celly = up(A, cyv.data(), n, st);
-  F.desc = up(A, fv->descriptors, (size_t)n * 32, st);
-  F.blocked0 = up(A, blk.data(), n, st);
+  F.cstart = (const int*)(d + o_cstart); F.order = (const unsigned short*)(d + o_order);
+  F.x = (const float*)(d + o_x); F.y = (const float*)(d + o_y);
+  F.uright = fv->u_right ? (const float*)(d + o_ur) : nullptr;
+  F.octave = (const int*)(d + o_oct);
+  F.cellx = (const short*)(d + o_cx); F.celly = (const short*)(d + o_cy);
+  F.desc = d + o_desc;
+  F.blocked0 = d + o_blk;
   F.minX = fv->min_x; F.minY = fv->min_y; F.maxX = fv->max_x; F.maxY = fv->max_y;
   F.gwinv = fv->grid_w_inv; F.ghinv = fv->grid_h_inv; F.mbf = fv->mbf;
   for (int l = 0; l < MAX_LEVELS; l++) F.scale[l] = l < fv->nlevels ? fv->scale_factors[l] : 0.f;
-  cudaStreamSynchronize(st);  // the staging vectors above die with this scope
+  cudaStreamSynchronize(st);  // the staging block is reused by the next upload
 }
 
 }  // namespace cuorb

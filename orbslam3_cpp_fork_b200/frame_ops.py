@@ -101,21 +101,26 @@ class LocalMap:
         return check(self._L.cuorb_localmap_count(self._h))
 
     def search(self, camera, frame, skip_idx=(), viewingCosLimit=0.5, th=1.0, bFarPoints=False, thFarPoints=50.0, nnratio=0.8,
-               match_capacity=None, want_best=True):
-        """frame: matcher.Frame.  Returns (nmatches, n_in_view, match_point, match_feature, best_idx or None) and
-        replays F.mvpMapPoints[feature] = point in point order."""
+               match_capacity=None, want_best=True, order=None, want_in_view=False):
+        """frame: matcher.Frame.  order: storage slots in the order mvpLocalMapPoints holds the points this frame (None =
+        storage order); skip_idx and all results are positions in that sequence.  Returns (nmatches, n_in_view,
+        match_pos, match_feature, best_idx or None[, in_view]) and replays F.mvpMapPoints[feature] = position in order."""
         import ctypes as C
         fv, keep = frame.view()
         skip = np.ascontiguousarray(np.asarray(skip_idx, np.int32))
-        M = self.count
+        ordr = None if order is None else np.ascontiguousarray(np.asarray(order, np.int32))
+        M = self.count if ordr is None else len(ordr)
         cap = int(match_capacity) if match_capacity is not None else max(M, 1)
         mp = np.full(max(cap, 1), -1, np.int32); ft = np.full(max(cap, 1), -1, np.int32)
         best = np.full(max(M, 1), -1, np.int32) if want_best else None
+        inv = np.zeros(max(M, 1), np.uint8) if want_in_view else None
         nin = C.c_int32(0)
-        n = check(self._L.cuorb_localmap_search(self._h, C.byref(camera), C.byref(fv), len(skip), ptr(skip) if len(skip) else None,
+        n = check(self._L.cuorb_localmap_search(self._h, C.byref(camera), C.byref(fv), 0 if ordr is None else len(ordr),
+                                                None if ordr is None else ptr(ordr), len(skip), ptr(skip) if len(skip) else None,
                                                 float(viewingCosLimit), float(th), int(bFarPoints), float(thFarPoints),
-                                                float(nnratio), ptr(best) if want_best else None, cap, ptr(mp), ptr(ft),
-                                                C.byref(nin)))
+                                                float(nnratio), ptr(best) if want_best else None,
+                                                ptr(inv) if want_in_view else None, cap, ptr(mp), ptr(ft), C.byref(nin)))
         for p, f in zip(mp[:n], ft[:n]):
             frame.mvpMapPoints[f] = p
-        return n, nin.value, mp[:n].copy(), ft[:n].copy(), (best[:M] if want_best else None)
+        out = (n, nin.value, mp[:n].copy(), ft[:n].copy(), (best[:M] if want_best else None))
+        return out + (inv[:M],) if want_in_view else out

@@ -102,3 +102,33 @@ def test_localmap_limits(fr):
     assert n == 0 and n_in == 0
     n, n_in, mp, ft, best = m.search(_cam(c), _frame(k, d, sf, c), [], 0.5, 1.0, False, 30.0, 0.8, want_best=False)
     assert best is None and n > 100 and len(mp) == n
+
+
+def test_localmap_processing_order_and_in_view(fr):
+    """Storage stays put while Tracking rebuilds mvpLocalMapPoints in another order every frame: `order` lists the
+    storage slots in this frame's processing order (which decides contested features); all results are positions."""
+    from orbslam3_cpp_fork_b200 import LocalMap
+    k, d, sf = fr
+    M = 15000
+    c = localmap_case(k, d, sf, M, 8)
+    m = LocalMap(M + 7)
+    _fill(m, c)
+    rng = np.random.default_rng(3)
+    order = rng.permutation(M)[:M - 500].astype(np.int32)          # a permuted subset: 500 points left the local map
+    skip_pos = rng.permutation(len(order))[:300].astype(np.int32)
+    n, n_in, mp, ft, best, inv = m.search(_cam(c), _frame(k, d, sf, c), skip_pos, 0.5, 1.0, False, 30.0, 0.8, order=order,
+                                          want_in_view=True)
+    cp = {key: (c[key][order] if key in ("P", "N", "min_d", "max_d", "desc", "bad", "has_obs") else c[key]) for key in c}
+    cp["skip_idx"] = skip_pos
+    o_in, o_n, o_best = localmap_expected(cp, k, d, sf, op.is_in_frustum, op.search_by_projection, 1.0, False, 30.0, 0.8)
+    assert n_in == o_in and n == o_n and (best == o_best).all() and n > 300
+    assert inv.sum() == n_in and (inv[best >= 0] == 1).all() and (inv[skip_pos] == 0).all()
+    # the order matters: the identity order over the same subset gives another assignment of contested features
+    srt = np.sort(order)
+    n2, _, _, _, best2 = m.search(_cam(c), _frame(k, d, sf, c), [], 0.5, 1.0, False, 30.0, 0.8, order=srt)
+    by_slot = np.full(M, -1, np.int32); by_slot[order] = best
+    by_slot2 = np.full(M, -1, np.int32); by_slot2[srt] = best2
+    assert (by_slot != by_slot2).any()
+    if rp.available():
+        r_in, r_n, r_best = localmap_expected(cp, k, d, sf, rp.is_in_frustum, rp.search_by_projection, 1.0, False, 30.0, 0.8)
+        assert n_in == r_in and n == r_n and (best == r_best).all()
