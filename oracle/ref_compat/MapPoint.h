@@ -22,6 +22,9 @@ public:
   cv::Mat         GetDescriptor() { return mDescriptor.clone(); }
   float           GetMinDistanceInvariance() { return 0.8f * mfMinDistance; }
   float           GetMaxDistanceInvariance() { return 1.2f * mfMaxDistance; }
+  float           GetMinDistance() { return mfMinDistance; }   // the two getters INTEGRATION.md asks a maintainer to add
+  float           GetMaxDistance() { return mfMaxDistance; }
+  void            IncreaseVisible(int n = 1) { mnVisible += n; }
   int             PredictScale(const float& currentDist, KeyFrame* pKF);
   int             PredictScale(const float& currentDist, Frame* pF);
   std::tuple<int, int> GetIndexInKeyFrame(KeyFrame* pKF) {
@@ -51,7 +54,7 @@ public:
   // plain state
   Eigen::Vector3f mWorldPos, mNormalVector;
   cv::Mat         mDescriptor;
-  int             nObs = 0;
+  int             nObs = 0, mnVisible = 1;
   bool            mbBad = false;
   float           mfMinDistance = 0, mfMaxDistance = 0;
   MapPoint*       mpReplaced = nullptr;

@@ -498,6 +498,7 @@ private:
     return m.ptr<unsigned char>(0);
   }
 
+public:
   // a two-camera rig Frame as the two views libcuorb takes: left = features [0, Nleft) (mvKeys), right = features
   // [Nleft, N) (mvKeysRight, descriptor rows idx + Nleft)
   template <class FrameT>

@@ -126,7 +126,8 @@ def test_localmap_processing_order_and_in_view(fr):
     # the order matters: the identity order over the same subset gives another assignment of contested features
     srt = np.sort(order)
     n2, _, _, _, best2 = m.search(_cam(c), _frame(k, d, sf, c), [], 0.5, 1.0, False, 30.0, 0.8, order=srt)
-    by_slot = np.full(M, -1, np.int32); by_slot[order] = best
+    n3, _, _, _, best3 = m.search(_cam(c), _frame(k, d, sf, c), [], 0.5, 1.0, False, 30.0, 0.8, order=order)
+    by_slot = np.full(M, -1, np.int32); by_slot[order] = best3
     by_slot2 = np.full(M, -1, np.int32); by_slot2[srt] = best2
     assert (by_slot != by_slot2).any()
     if rp.available():

@@ -275,3 +275,70 @@ def test_cpp_shim_fisheye_stereo(tmp_path, seed, mono_l, mono_r):
         assert hit.sum() > 20 and (l2r[:mono_l] == -1).all() and (l2r[hit] >= mono_r).all()
     else:
         assert hit.sum() <= len(k1) - mono_l
+
+
+def test_cpp_shim_local_map_two_frames(tmp_path):
+    """shim/LocalMap.h (LocalMapMirror::Sync + SearchLocalPoints over cuorb_localmap_*) for two consecutive frames - the
+    second with another subset of the map in another order, some points changed in between, another pose - against the
+    reference's own Frame::isInFrustum (lifted) followed by the unmodified ORBmatcher::SearchByProjection on the same
+    vectors: return value, nToMatch and the final F.mvpMapPoints."""
+    from oracle import ref_py as rp
+    from tests.matching_cases import extracted_frame, localmap_case
+    if not rp.available():
+        pytest.skip("oracle/_ref/liborb_ref.so did not travel to this box")
+    build.build_libcuorb()
+    exe = str(tmp_path / "localmap_check")
+    pkg = os.path.join(ROOT, "orbslam3_cpp_fork_b200")
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-DCUORB_SHIM_USE_OPENCV",
+                           "-I" + os.path.join(ROOT, "oracle", "ref_compat"),
+                           os.path.join(ROOT, "tests", "native", "localmap_check.cpp"), "-o", exe,
+                           "-L" + pkg, "-l:libcuorb.so", "-Wl,-rpath," + pkg])
+    e, k, d = extracted_frame(seed=33)
+    sf = np.asarray(e.tables()[0], np.float32)
+    w, h, M = 752, 480, 12000
+    c1 = localmap_case(k, d, sf, M, 21); c2 = localmap_case(k, d, sf, M, 22)
+    rng = np.random.default_rng(4)
+    order1 = rng.permutation(M)[:M - 800].astype(np.int32)
+    skip1 = rng.permutation(len(order1))[:250].astype(np.int32)
+    order2 = rng.permutation(M)[:M - 600].astype(np.int32)
+    changed = rng.permutation(M)[:1500].astype(np.int32)
+    th, thfar, ratio, mb = 1.0, 30.0, 0.8, 0.1
+    keys = ("P", "N", "min_d", "max_d", "desc", "bad", "has_obs")
+    v2 = {key: c1[key].copy() for key in keys}
+    for key in keys:
+        v2[key][changed] = c2[key][changed]
+
+    def expected(data, cam, order, skip_pos):
+        f = rp.is_in_frustum(cam, data["P"][order], data["N"][order], data["min_d"][order], data["max_d"][order], 0.5)
+        skip = np.zeros(len(order), bool); skip[skip_pos] = True
+        in_view = (f["in_view"] > 0) & ~skip & (data["bad"][order] == 0)
+        flags = (in_view * 1 + data["bad"][order] * 2 + data["has_obs"][order] * 4).astype(np.uint8)
+        fv, keep = op.make_frame_view(k, d, c1["u_right"], c1["bound"], w, h, sf, mb=mb, mbf=c1["mbf"])
+        n, best, final = rp.search_by_projection(fv, data["desc"][order], f["proj_x"], f["proj_y"], f["proj_xr"],
+                                                 np.maximum(f["level"], 0), f["view_cos"], f["depth"], flags, th, False, thfar, ratio)
+        final = np.where(final >= 0, order[np.maximum(final, 0)], final).astype(np.int32)
+        return n, int(in_view.sum()), final
+
+    e1 = expected(c1, c1["cam"], order1, skip1)
+    e2 = expected(v2, c2["cam"], order2, np.zeros(0, np.int32))
+    case = str(tmp_path / "case.bin"); out = str(tmp_path / "out.bin")
+    with open(case, "wb") as f:
+        np.array([len(k), len(sf), M, len(order1), len(skip1), len(order2), len(changed)], np.int32).tofile(f)
+        np.array([th, thfar, ratio, mb, c1["mbf"], w, h], np.float32).tofile(f)
+        f.write(bytes(c1["cam"])); f.write(bytes(c2["cam"]))
+        np.ascontiguousarray(k).tofile(f); np.ascontiguousarray(d).tofile(f)
+        c1["u_right"].tofile(f); c1["bound"].tofile(f); sf.tofile(f)
+        for data in (c1, v2):
+            for key in keys:
+                np.ascontiguousarray(data[key]).tofile(f)
+        order1.tofile(f); skip1.tofile(f); order2.tofile(f); changed.tofile(f)
+    subprocess.check_call([exe, case, out])
+    res = np.fromfile(out, np.int32).reshape(2, 3 + len(k))
+    for r, ex in zip(res, (e1, e2)):
+        assert int(r[0]) == ex[0] and int(r[1]) == ex[1]
+        assert (r[3:] == ex[2]).all()
+    assert e1[0] > 300 and e2[0] > 300
+    in1 = np.zeros(M, bool); in1[order1] = True
+    ch = np.zeros(M, bool); ch[changed] = True
+    assert int(res[0][2]) == len(order1)
+    assert int(res[1][2]) == int((~in1[order2]).sum() + (in1[order2] & ch[order2]).sum())   # only new or changed points were sent
