@@ -337,7 +337,7 @@ def test_cpp_shim_local_map_two_frames(tmp_path):
     for r, ex in zip(res, (e1, e2)):
         assert int(r[0]) == ex[0] and int(r[1]) == ex[1]
         assert (r[3:] == ex[2]).all()
-    assert e1[0] > 300 and e2[0] > 300
+    assert e1[0] > 300 and e2[0] > 100      # frame 2 looks at mostly frame-1 points from another pose
     in1 = np.zeros(M, bool); in1[order1] = True
     ch = np.zeros(M, bool); ch[changed] = True
     assert int(res[0][2]) == len(order1)
