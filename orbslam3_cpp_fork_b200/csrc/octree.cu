@@ -25,6 +25,7 @@
 //     (cell-row-major, then row-major inside a FAST cell) is a pure function of (x, y).
 // Keys and node ids are staged in shared memory when they fit, else read from the L2-resident
 // candidate list / scratch arena.  No roofline claim: latency/occupancy-bound bookkeeping.
+#include <cstdlib>
 #include "common.cuh"
 #include "introsort.cuh"
 
@@ -32,7 +33,8 @@ namespace cuorb {
 
 namespace {
 
-constexpr int OT_THREADS = 128;
+constexpr int OT_THREADS = 128;       // large batches: many CTAs per SM, 4 warps each
+constexpr int OT_THREADS_WIDE = 512;  // a handful of images: one CTA per (image, level) is all there is, so it gets 16 warps
 constexpr int OT_KEYCAP  = 4096;  // keys staged in shared memory (6 bytes each)
 
 struct SortEnt { int size; short ulx; short node; };
@@ -55,9 +57,10 @@ __host__ __device__ inline size_t octree_node_bytes(int cap) {
 }
 
 // exclusive prefix sum over a[0..n) (packed 3 x 20-bit fields), returns the total
+template <int NT>
 __device__ u64 block_scan(u64* a, int n, u64* s_warp) {
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  const int K = (n + OT_THREADS - 1) / OT_THREADS;
+  const int K = (n + NT - 1) / NT;
   const int b = min(tid * K, n), e = min(b + K, n);
   u64 s = 0;
   for (int i = b; i < e; i++) s += a[i];
@@ -72,7 +75,7 @@ __device__ u64 block_scan(u64* a, int n, u64* s_warp) {
   __syncthreads();
   u64 woff = 0, total = 0;
 #pragma unroll
-  for (int w = 0; w < OT_THREADS / 32; w++) {
+  for (int w = 0; w < NT / 32; w++) {
     const u64 v = s_warp[w];
     if (w < wid) woff += v;
     total += v;
@@ -166,6 +169,7 @@ __device__ int warp_partition(SortEnt* a, int first, int last, u16* Lpos, u16* R
 }
 
 // sorts a[0..n) (n <= cap); work arrays: seg (3*cap u16), pos (4*cap u16), tmp (cap entries)
+template <int NT>
 __device__ bool block_std_sort(SortEnt* a, int n, u16* seg, u16* pos, SortEnt* tmp, int cap) {
   __shared__ int s_nseg, s_more, s_fb;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -182,7 +186,7 @@ __device__ bool block_std_sort(SortEnt* a, int n, u16* seg, u16* pos, SortEnt* t
       __syncthreads();
       if (tid == 0) s_more = 0;
       __syncthreads();
-      for (int si = wid; si < nseg; si += OT_THREADS / 32) {
+      for (int si = wid; si < nseg; si += NT / 32) {
         const int f = segF[si], l = segL[si], d = segD[si];
         if (l - f <= 16) continue;
         if (d == 0) { if (lane == 0) s_fb = 1; continue; }
@@ -200,12 +204,12 @@ __device__ bool block_std_sort(SortEnt* a, int n, u16* seg, u16* pos, SortEnt* t
     if (s_fb) return false;
   }
   const int nseg = s_nseg;
-  for (int si = tid; si < nseg; si += OT_THREADS) {
+  for (int si = tid; si < nseg; si += NT) {
     const int f = segF[si], l = segL[si];
     for (int q = f; q < l; q++) { lo[q] = (u16)f; hi[q] = (u16)l; }
   }
   __syncthreads();
-  for (int q = tid; q < n; q += OT_THREADS) {
+  for (int q = tid; q < n; q += NT) {
     const int f = lo[q], l = hi[q];
     const u64 mk = sort_key(a, q);
     int r = f;
@@ -216,7 +220,7 @@ __device__ bool block_std_sort(SortEnt* a, int n, u16* seg, u16* pos, SortEnt* t
     tmp[r] = a[q];
   }
   __syncthreads();
-  for (int q = tid; q < n; q += OT_THREADS) a[q] = tmp[q];
+  for (int q = tid; q < n; q += NT) a[q] = tmp[q];
   __syncthreads();
   return true;
 }
@@ -224,7 +228,8 @@ __device__ bool block_std_sort(SortEnt* a, int n, u16* seg, u16* pos, SortEnt* t
 }  // namespace
 
 // grid: (nlevels, n_img), block OT_THREADS
-__global__ void __launch_bounds__(OT_THREADS) k_octree(const ExtractorGeom* __restrict__ dg,
+template <int NT>
+__global__ void __launch_bounds__(NT) k_octree(const ExtractorGeom* __restrict__ dg,
                                                        const unsigned* __restrict__ cand,
                                                        unsigned* __restrict__ scratch,
                                                        const int* __restrict__ cand_count,
@@ -233,7 +238,7 @@ __global__ void __launch_bounds__(OT_THREADS) k_octree(const ExtractorGeom* __re
                                                        int* __restrict__ flags, int pool_cap) {
   pdl_enter();
   extern __shared__ __align__(16) unsigned char smem[];
-  __shared__ u64 s_warp[OT_THREADS / 32];
+  __shared__ u64 s_warp[NT / 32];
   __shared__ int s_cnt_ok;
 
   const int level = blockIdx.x, img = blockIdx.y, tid = threadIdx.x;
@@ -265,7 +270,7 @@ __global__ void __launch_bounds__(OT_THREADS) k_octree(const ExtractorGeom* __re
   const unsigned* keys;
   unsigned short* nid;
   if (M <= OT_KEYCAP) {
-    for (int i = tid; i < M; i += OT_THREADS) s_keys[i] = gkeys[i];
+    for (int i = tid; i < M; i += NT) s_keys[i] = gkeys[i];
     keys = s_keys; nid = s_nid;
   } else {
     keys = gkeys;
@@ -282,9 +287,9 @@ __global__ void __launch_bounds__(OT_THREADS) k_octree(const ExtractorGeom* __re
     const int   nIni = L.nIni;
     const float hX   = L.hX;
     const int   H    = L.maxBorderY - FAST_BORDER;
-    for (int r = tid; r < nIni; r += OT_THREADS) cc[r] = 0;
+    for (int r = tid; r < nIni; r += NT) cc[r] = 0;
     __syncthreads();
-    for (int i = tid; i < M; i += OT_THREADS) {
+    for (int i = tid; i < M; i += NT) {
       const int r = (int)((float)cand_x(keys[i]) / hX);
       nid[i] = (unsigned short)r;
       atomicAdd(&cc[r], 1);
@@ -304,7 +309,7 @@ __global__ void __launch_bounds__(OT_THREADS) k_octree(const ExtractorGeom* __re
     }
     __syncthreads();
     size = s_cnt_ok;
-    for (int i = tid; i < M; i += OT_THREADS) nid[i] = remap[nid[i]];
+    for (int i = tid; i < M; i += NT) nid[i] = remap[nid[i]];
     __syncthreads();
   }
 
@@ -314,20 +319,20 @@ __global__ void __launch_bounds__(OT_THREADS) k_octree(const ExtractorGeom* __re
     const int prevSize = size;
     // ---- (final phase only) sort the expandable nodes (:686-689) ----
     if (final_phase) {
-      for (int i = tid; i < vcount; i += OT_THREADS) Vs[i] = V[i];
+      for (int i = tid; i < vcount; i += NT) Vs[i] = V[i];
       __syncthreads();
-      if (vcount > 1 && !block_std_sort(Vs, vcount, remap, reinterpret_cast<u16*>(cc), reinterpret_cast<SortEnt*>(scanA), cap)) {
+      if (vcount > 1 && !block_std_sort<NT>(Vs, vcount, remap, reinterpret_cast<u16*>(cc), reinterpret_cast<SortEnt*>(scanA), cap)) {
         // depth limit reached somewhere (heapsort branch): run the serial port on a fresh copy
-        for (int i = tid; i < vcount; i += OT_THREADS) Vs[i] = V[i];
+        for (int i = tid; i < vcount; i += NT) Vs[i] = V[i];
         __syncthreads();
         if (tid == 0) cuorb_sort::Introsort<SortEnt, SortLess>::sort(Vs, Vs + vcount, SortLess());
         __syncthreads();
       }
     }
     // ---- child counts of every node with more than one key ----
-    for (int i = tid; i < size * 4; i += OT_THREADS) cc[i] = 0;
+    for (int i = tid; i < size * 4; i += NT) cc[i] = 0;
     __syncthreads();
-    for (int i = tid; i < M; i += OT_THREADS) {
+    for (int i = tid; i < M; i += NT) {
       const int pos = nid[i];
       if (cnt[pos] > 1) {
         const int q = quadrant(keys[i], box[pos]);
@@ -340,7 +345,7 @@ __global__ void __launch_bounds__(OT_THREADS) k_octree(const ExtractorGeom* __re
     int newSize, newV;
     if (!final_phase) {
       // ---- one full pass of the main loop (:613-675) ----
-      for (int pos = tid; pos < size; pos += OT_THREADS) {
+      for (int pos = tid; pos < size; pos += NT) {
         u64 v = 1ull << 40;  // unsplit
         if (cnt[pos] > 1) {
           const int* c = cc + pos * 4;
@@ -351,11 +356,11 @@ __global__ void __launch_bounds__(OT_THREADS) k_octree(const ExtractorGeom* __re
         scanA[pos] = v;
       }
       __syncthreads();
-      const u64 tot = block_scan(scanA, size, s_warp);
+      const u64 tot = block_scan<NT>(scanA, size, s_warp);
       const int totCh = (int)(tot & F20), totEx = (int)((tot >> 20) & F20), nUn = (int)(tot >> 40);
       newSize = totCh + nUn; newV = totEx;
       if (newSize > cap) { fail = true; break; }
-      for (int pos = tid; pos < size; pos += OT_THREADS) {
+      for (int pos = tid; pos < size; pos += NT) {
         const u64 ex = scanA[pos];
         if (cnt[pos] > 1) {
           const int* c = cc + pos * 4;
@@ -386,36 +391,36 @@ __global__ void __launch_bounds__(OT_THREADS) k_octree(const ExtractorGeom* __re
       }
     } else {
       // ---- one round of the final phase (:677-725) ----
-      for (int j = tid; j < vcount; j += OT_THREADS) {
+      for (int j = tid; j < vcount; j += NT) {
         const int* c = cc + (int)Vs[j].node * 4;
         const int nch = (c[0] > 0) + (c[1] > 0) + (c[2] > 0) + (c[3] > 0);
         const int nex = (c[0] > 1) + (c[1] > 1) + (c[2] > 1) + (c[3] > 1);
         scanA[j] = (u64)(nch - 1) | ((u64)nch << 20) | ((u64)nex << 40);
       }
-      for (int pos = tid; pos < size; pos += OT_THREADS) jrank[pos] = 0xFFFF;
+      for (int pos = tid; pos < size; pos += NT) jrank[pos] = 0xFFFF;
       if (tid == 0) s_cnt_ok = 0;
       __syncthreads();
-      const u64 tot = block_scan(scanA, vcount, s_warp);
+      const u64 tot = block_scan<NT>(scanA, vcount, s_warp);
       const int totGain = (int)(tot & F20);
       // splitting goes from the back and stops as soon as size >= N (:721): j* = largest j with
       // size + sum_{j' >= j} gain >= N; the sums are non-increasing in j, so count them
       int ok = 0;
-      for (int j = tid; j < vcount; j += OT_THREADS) ok += (size + totGain - (int)(scanA[j] & F20)) >= N;
+      for (int j = tid; j < vcount; j += NT) ok += (size + totGain - (int)(scanA[j] & F20)) >= N;
       if (ok) atomicAdd(&s_cnt_ok, ok);
       __syncthreads();
       const int jstar = s_cnt_ok > 0 ? s_cnt_ok - 1 : 0;
       const u64 exStar = vcount > 0 ? scanA[jstar] : 0;
-      for (int j = tid + jstar; j < vcount; j += OT_THREADS) jrank[Vs[j].node] = (unsigned short)j;
+      for (int j = tid + jstar; j < vcount; j += NT) jrank[Vs[j].node] = (unsigned short)j;
       __syncthreads();
-      for (int pos = tid; pos < size; pos += OT_THREADS) scanB[pos] = jrank[pos] == 0xFFFF ? 1 : 0;
+      for (int pos = tid; pos < size; pos += NT) scanB[pos] = jrank[pos] == 0xFFFF ? 1 : 0;
       __syncthreads();
-      const int nKeep = (int)block_scan(scanB, size, s_warp);
+      const int nKeep = (int)block_scan<NT>(scanB, size, s_warp);
       const int newCh = (int)((tot >> 20) & F20) - (int)((exStar >> 20) & F20);
       const int totEx = (int)(tot >> 40);
       newSize = nKeep + newCh;
       newV = totEx - (int)(exStar >> 40);
       if (newSize > cap) { fail = true; break; }
-      for (int j = tid + jstar; j < vcount; j += OT_THREADS) {
+      for (int j = tid + jstar; j < vcount; j += NT) {
         const int pos = Vs[j].node;
         const int* c = cc + pos * 4;
         const Box b = box[pos];
@@ -438,7 +443,7 @@ __global__ void __launch_bounds__(OT_THREADS) k_octree(const ExtractorGeom* __re
         for (int q = 0; q < 4; q++)
           if (c[q] > 1) { V[vi] = SortEnt{c[q], (q & 1) ? (short)(b.x0 + ((b.x1 - b.x0 + 1) >> 1)) : b.x0, (short)npos[q]}; vi++; }
       }
-      for (int pos = tid; pos < size; pos += OT_THREADS) {
+      for (int pos = tid; pos < size; pos += NT) {
         if (jrank[pos] != 0xFFFF) continue;
         const unsigned short np = (unsigned short)(newCh + (int)scanB[pos]);
         nbox[np] = box[pos]; ncnt[np] = cnt[pos];
@@ -447,7 +452,7 @@ __global__ void __launch_bounds__(OT_THREADS) k_octree(const ExtractorGeom* __re
     }
     __syncthreads();
     // ---- move every key to its node's new list position ----
-    for (int i = tid; i < M; i += OT_THREADS) {
+    for (int i = tid; i < M; i += NT) {
       const int v = nid[i];
       nid[i] = remap[(v & 0x3FFF) * 4 + (v >> 14)];
     }
@@ -465,12 +470,12 @@ __global__ void __launch_bounds__(OT_THREADS) k_octree(const ExtractorGeom* __re
 
   // ---- per node keep the max-response key, first in reference order wins (:735-750) ----
   u64* best = scanA;
-  for (int pos = tid; pos < size; pos += OT_THREADS) best[pos] = 0;
+  for (int pos = tid; pos < size; pos += NT) best[pos] = 0;
   __syncthreads();
   {
     const int hCell = L.hCell, wCell = L.wCell, nCols = L.nCols;
     constexpr u64 ORD = (1ull << 38) - 1;
-    for (int i = tid; i < M; i += OT_THREADS) {
+    for (int i = tid; i < M; i += NT) {
       const unsigned k = keys[i];
       const int x = cand_x(k), y = cand_y(k);
       const u64 cell = (u64)(((y - 3) / hCell) * nCols + (x - 3) / wCell);
@@ -480,7 +485,7 @@ __global__ void __launch_bounds__(OT_THREADS) k_octree(const ExtractorGeom* __re
   }
   __syncthreads();
   LevelKey* out = keys_out + (size_t)img * dg->key_img_stride + L.key_off;
-  for (int pos = tid; pos < size; pos += OT_THREADS) {
+  for (int pos = tid; pos < size; pos += NT) {
     const u64 b = best[pos];
     const u64 ord = ((1ull << 38) - 1) - (b & ((1ull << 38) - 1));
     LevelKey kq;
@@ -499,8 +504,17 @@ void launch_octree(const ExtractorGeom& g, const ExtractorGeom* dg, int n_img, c
   int cap = 0;
   for (int l = 0; l < g.nlevels; l++) cap = max(cap, g.lv[l].node_cap);
   const size_t smem = octree_node_bytes(cap) + (size_t)OT_KEYCAP * 6;
-  if (smem > 48 * 1024) cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   // per device
-  launch_k(k_octree, dim3(g.nlevels, n_img), dim3(OT_THREADS), smem, st, dg, cand, cand_scratch, cand_count, keys, key_count, flags, cap);
+  // The per-candidate passes of a level are spread over the CTA's threads; with a few images the grid cannot fill
+  // the GPU anyway and the level-0 CTA is the critical path of the call, so it runs 512 threads wide
+  // (single-frame call on a B200: quadtree stage 46 us at 128 threads, 35 us at 256 or 512, 41 us at 1024;
+  // profiles/r02_s19_cfg1_ot*.json); results do not depend on the width.
+  const bool wide = g.nlevels * n_img <= 64;
+  auto go = [&](auto kern, int nt) {
+    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   // per device
+    launch_k(kern, dim3(g.nlevels, n_img), dim3(nt), smem, st, dg, cand, cand_scratch, cand_count, keys, key_count, flags, cap);
+  };
+  if (wide) go(k_octree<OT_THREADS_WIDE>, OT_THREADS_WIDE);
+  else go(k_octree<OT_THREADS>, OT_THREADS);
   count_launch();
 }
 
