@@ -200,7 +200,7 @@ static int projection_rounds(Arena& A, cudaStream_t st, const ProjFrame& F, cons
   // round was quiet" test at the top of k_proj_round cost 0.07-0.15 ms per call in every form tried (per thread,
   // per block), more than the rounds it saves.  Measured at cfg4 (50k MapPoints, 5 rounds to converge): one sync
   // per round 0.556 ms per call, batches of 6 0.510 ms (scripts/ab_projection.py, profiles/r02_s9_abproj.txt).
-  constexpr int ROUND_BATCH = 6;
+  constexpr int ROUND_BATCH = 6;   // 2 / 3 / 4 per sync: cfg4 0.558 / 0.561 / 0.581 ms against 0.525, local map 0.339 / 0.324 / 0.365 against 0.302
   int* flag = A.take<int>(ROUND_BATCH);
   unsigned* dirty = A.take<unsigned>(2 * FRAME_GRID_ROWS);
   k_fill<<<(n + 255) / 256, 256, 0, st>>>(binder[0], n, NO_BINDER);

@@ -205,7 +205,7 @@ extern "C" int cuorb_search_by_projection_rig(int device, const cuorb_frame_view
   const int nev = 4 * m;
   size_t sort_bytes = 0;
   CUORB_CUDA_TRY(cub::DeviceRadixSort::SortKeys(nullptr, sort_bytes, (const unsigned long long*)nullptr,
-                                                (unsigned long long*)nullptr, nev, 0, 64, cudaStreamPerThread));
+                                                (unsigned long long*)nullptr, nev, 0, 51, cudaStreamPerThread));
   const size_t bytes = frame_bytes(nl) + frame_bytes(nr) + (size_t)m * (32 + 9 * 4 + 1 + 8 + 2 * 4 * 8) + (size_t)nf * 12 +
                        sort_bytes + 128 * 1024;
   if (t_arena.reserve(device, bytes) != 0) { set_error("cudaMalloc failed (rig projection workspace)"); return CUORB_E_CUDA; }
@@ -243,7 +243,7 @@ extern "C" int cuorb_search_by_projection_rig(int device, const cuorb_frame_view
     for (int k = 0; k < ROUND_BATCH; k++, rounds++) {
       k_rig_round<<<(m + 7) / 8, 256, 0, st>>>(FL, FR, Q, G, resL, resR, flag + k);
       k_rig_events<<<(m + 255) / 256, 256, 0, st>>>(m, nl, resL, resR, Q.flags, d_l2r, d_r2l, ev_raw);
-      CUORB_CUDA_TRY(cub::DeviceRadixSort::SortKeys(sort_tmp, sort_bytes, (const unsigned long long*)ev_raw, ev_sorted, nev, 0, 64, st));
+      CUORB_CUDA_TRY(cub::DeviceRadixSort::SortKeys(sort_tmp, sort_bytes, (const unsigned long long*)ev_raw, ev_sorted, nev, 0, 51, st));
       k_rig_index<<<(nf + 255) / 256, 256, 0, st>>>(nf, ev_sorted, nev, fstart);
       count_launch(3 + 8);
       G.nev = nev;
