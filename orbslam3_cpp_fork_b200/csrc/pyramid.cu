@@ -22,6 +22,7 @@ namespace cuorb {
 
 constexpr int PYR_RS = 16;  // interior rows per thread strip
 constexpr int PYR_TX = 64;  // threads (output words) per CTA
+constexpr int PYR_MIN_CTAS = 2 * 148;  // below this many CTAs a pyramid launch switches to shorter strips
 constexpr int PYR_TAB_TX = 192;  // k_pyr_resize_stage: upper bound of its per-level CTA width
 
 __device__ __forceinline__ int reflect101(int i, int n) {
@@ -31,6 +32,7 @@ __device__ __forceinline__ int reflect101(int i, int n) {
 }
 
 // grid: (ceil(pitch/4/128), ceil(h/PYR_RS), n_img)
+template <int RS>
 __global__ void __launch_bounds__(256) k_pyr_level0(const ExtractorGeom* __restrict__ dg,
                                                     const uint8_t* __restrict__ imgs, size_t stride,
                                                     size_t image_stride, uint8_t* __restrict__ pyr,
@@ -48,24 +50,24 @@ __global__ void __launch_bounds__(256) k_pyr_level0(const ExtractorGeom* __restr
 #pragma unroll
   for (int b = 0; b < 4; b++)
     xs[b] = reflect101(min(max(xw + b, -EDGE_THRESHOLD), L.w + EDGE_THRESHOLD - 1), L.w);  // pad bytes: clamp
-  const int y0 = blockIdx.y * PYR_RS, y1 = min(y0 + PYR_RS, L.h);
+  const int y0 = blockIdx.y * RS, y1 = min(y0 + RS, L.h);
   const int dp4 = L.pitch >> 2;
   unsigned* drow = reinterpret_cast<unsigned*>(dst) + word;
   // common case (aligned interior word, full strip away from the mirrored rows): pointer-increment copy,
   // all loads of the strip issued before the stores
-  if (inner && y0 > EDGE_THRESHOLD && y0 + PYR_RS < L.h - 1 - EDGE_THRESHOLD) {
+  if (inner && y0 > EDGE_THRESHOLD && y0 + RS < L.h - 1 - EDGE_THRESHOLD) {
     const uint8_t* sp = src + (size_t)y0 * stride + xw;
-    unsigned v[PYR_RS];
+    unsigned v[RS];
 #pragma unroll
-    for (int r = 0; r < PYR_RS; r++, sp += stride) v[r] = __ldg(reinterpret_cast<const unsigned*>(sp));
+    for (int r = 0; r < RS; r++, sp += stride) v[r] = __ldg(reinterpret_cast<const unsigned*>(sp));
     unsigned* dpz = drow + (size_t)(y0 + EDGE_THRESHOLD) * dp4;
 #pragma unroll
-    for (int r = 0; r < PYR_RS; r++, dpz += dp4) *dpz = v[r];
+    for (int r = 0; r < RS; r++, dpz += dp4) *dpz = v[r];
     return;
   }
-  unsigned v[PYR_RS];
+  unsigned v[RS];
 #pragma unroll
-  for (int r = 0; r < PYR_RS; r++) {
+  for (int r = 0; r < RS; r++) {
     const uint8_t* srow = src + (size_t)min(y0 + r, y1 - 1) * stride;
     if (inner) {
       v[r] = __ldg(reinterpret_cast<const unsigned*>(srow + xw));
@@ -75,7 +77,7 @@ __global__ void __launch_bounds__(256) k_pyr_level0(const ExtractorGeom* __restr
     }
   }
 #pragma unroll
-  for (int r = 0; r < PYR_RS; r++) {
+  for (int r = 0; r < RS; r++) {
     const int y = y0 + r;
     if (y >= y1) break;
     const unsigned out = v[r];
@@ -431,7 +433,13 @@ void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8
       // CTA width = the padded row's word count split evenly over whole warps (208 words -> one CTA of 224)
       const int words = L.pitch / 4, nb = (words + 255) / 256;
       const int tx = (((words + nb - 1) / nb) + 31) / 32 * 32;
-      launch_k(k_pyr_level0, dim3((words + tx - 1) / tx, grid.y, n_img), dim3(tx), 0, st, dg, imgs, stride, image_stride, pyr, aligned);
+      // 16-row strips for large batches; when that would leave most of the 148 SMs without a CTA (a handful of
+      // images) the strips are 4 rows and the kernel's critical path - one thread's row loop - is a quarter as long
+      const int nbx = (words + tx - 1) / tx;
+      if ((int)grid.y * nbx * n_img < PYR_MIN_CTAS)
+        launch_k(k_pyr_level0<4>, dim3(nbx, (L.h + 3) / 4, n_img), dim3(tx), 0, st, dg, imgs, stride, image_stride, pyr, aligned);
+      else
+        launch_k(k_pyr_level0<PYR_RS>, dim3(nbx, grid.y, n_img), dim3(tx), 0, st, dg, imgs, stride, image_stride, pyr, aligned);
     } else {
       // four adjacent output columns span 3*scale + 2 source bytes (+3 for alignment): 12 bytes up to scale 2
       const double sx = (double)g.lv[l - 1].w / L.w;
@@ -442,7 +450,13 @@ void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8
         // above the 48 KB default only for very wide levels; the attribute is per device, so it is set on every
         // such launch rather than cached per process
         if (p.smem > 48 * 1024) cudaFuncSetAttribute(k_pyr_resize_stage, cudaFuncAttributeMaxDynamicSharedMemorySize, p.smem);
-        launch_k(k_pyr_resize_stage, dim3(p.nb, (L.h + PYR_RS - 1) / PYR_RS, n_img), dim3(p.tx), (size_t)p.smem, st, dg, l, pyr, wtab + wtab_off[l], ytab, PYR_RS, pc);
+        // strips of PYR_RS output rows amortise the staging for large batches; with a handful of images a level is
+        // only 10-30 such strips on 148 SMs and the row loop is the kernel's critical path, so the strips get shorter
+        // until the grid fills the GPU (single 752x480 frame: pyramid stage 68 -> 36 us, the call 0.160 -> 0.133 ms;
+        // strips of 1, 2, 3 or 4 rows within 1 us of each other)
+        int rs = PYR_RS;
+        while (rs > 2 && ((L.h + rs - 1) / rs) * p.nb * n_img < PYR_MIN_CTAS) rs >>= 1;
+        launch_k(k_pyr_resize_stage, dim3(p.nb, (L.h + rs - 1) / rs, n_img), dim3(p.tx), (size_t)p.smem, st, dg, l, pyr, wtab + wtab_off[l], ytab, rs, pc);
       }
       else if (3.0 * sx + 5.0 < 11.5) launch_k(k_pyr_resize<false>, grid, dim3(PYR_TX), 0, st, dg, l, pyr, xtab, ytab);
       else launch_k(k_pyr_resize<true>, grid, dim3(PYR_TX), 0, st, dg, l, pyr, xtab, ytab);
