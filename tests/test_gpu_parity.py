@@ -245,14 +245,14 @@ def test_other_geometries(cu, w, h, nf, scale, nlevels, ini, mn, seed):
     assert_extract_equal(k, d, ko, do)
 
 
-VARIANTS = [{"CUORB_FAST_LEGACY": "1"}, {"CUORB_SIDE_BLUR": "0"}, {"CUORB_FAST_CTAS": "0"}, {"CUORB_FAST_CTAS": "3"}]
+VARIANTS = [{"CUORB_FAST_LEGACY": "1"}, {"CUORB_SIDE_BLUR": "0"}, {"CUORB_FAST_CTAS": "0"}, {"CUORB_FAST_CTAS": "3"}, {"CUORB_PDL": "0"}]
 
 
 @pytest.mark.parametrize("env_over", VARIANTS, ids=lambda d: ",".join(f"{k[6:]}={v}" for k, v in d.items()))
 def test_kernel_variants_subprocess(cu, env_over):
-    """The three test / tuning hooks of DESIGN.md section 6 select launch shapes or the wide-cell kernel, which must
+    """The four test / tuning hooks of DESIGN.md section 6 select launch shapes or the wide-cell kernel, which must
     stay bit-identical to the oracle (one-CTA-per-cell FAST on ordinary geometry, serial blur, other persistent-grid
-    sizes).  The hooks are read once per process, hence the subprocess."""
+    sizes, plain stream order instead of dependent launches for this two-image batch).  The hooks are read once per process, hence the subprocess."""
     import subprocess, sys, textwrap
     code = textwrap.dedent("""
         import numpy as np
