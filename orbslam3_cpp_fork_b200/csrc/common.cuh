@@ -103,6 +103,9 @@ __device__ __forceinline__ void pdl_enter() {
 }
 #endif
 extern thread_local bool t_pdl;
+// A kernel whose predecessor in the stream is not a kernel of the chain (a copy, a memset, a cross-stream event wait)
+// is launched with plain stream ordering: the attribute is only meant for kernel-after-kernel edges.
+struct PdlPause { bool saved; PdlPause() : saved(t_pdl) { t_pdl = false; } ~PdlPause() { t_pdl = saved; } };
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
   cudaLaunchConfig_t cfg = {};

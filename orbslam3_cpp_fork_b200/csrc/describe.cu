@@ -256,7 +256,10 @@ void launch_describe(const ExtractorGeom& g, const ExtractorGeom* dg, const TmaM
   (void)pyr; (void)blur;  // read through the TMA tensor maps
   const int smem = DESC_WARPS * (IC_SLOT + BR_SLOT) + 128;
   if (smem > 48 * 1024) cudaFuncSetAttribute(k_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);   // per device
-  launch_k(k_finalize, dim3(n_img), dim3(256), 0, st, dg, keys, key_count, lap0, lap1, slot_map, out_n, out_mono);
+  {
+    PdlPause after_event_wait;   // the stream has just waited for the side stream's blur: a full dependency
+    launch_k(k_finalize, dim3(n_img), dim3(256), 0, st, dg, keys, key_count, lap0, lap1, slot_map, out_n, out_mono);
+  }
   launch_k(k_describe, dim3((g.kp_cap + DESC_WARPS - 1) / DESC_WARPS, n_img), dim3(DESC_WARPS * 32), (size_t)smem, st, dg, tmaps, keys,
            key_count, slot_map, out_kps, out_desc);
   count_launch(2);

@@ -436,6 +436,7 @@ void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8
       // 16-row strips for large batches; when that would leave most of the 148 SMs without a CTA (a handful of
       // images) the strips are 4 rows and the kernel's critical path - one thread's row loop - is a quarter as long
       const int nbx = (words + tx - 1) / tx;
+      PdlPause first_of_chain;   // follows the frame upload and two memsets
       if ((int)grid.y * nbx * n_img < PYR_MIN_CTAS)
         launch_k(k_pyr_level0<4>, dim3(nbx, (L.h + 3) / 4, n_img), dim3(tx), 0, st, dg, imgs, stride, image_stride, pyr, aligned);
       else
