@@ -118,9 +118,8 @@ struct QueryPoints {
   std::vector<MapPoint*>      ptr;
   int                         n;
   QueryPoints(int n_, const uint8_t* desc, const float* u, const float* v, const float* z, const int32_t* level,
-              const uint8_t* active, float scale_factor, bool norm_of_camera_point = true)
+              const uint8_t* active, float scale_factor)
       : mp(new MapPoint[n_ > 0 ? n_ : 1]), ptr(n_), n(n_) {
-    (void)norm_of_camera_point;
     for (int i = 0; i < n; i++) {
       MapPoint& p = mp[i];
       const float zi = z ? z[i] : 1.f;
