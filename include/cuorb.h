@@ -447,6 +447,18 @@ int cuorb_search_by_bow(int device, int n1, const uint8_t* desc1, const uint8_t*
                         const int32_t* node_idx1, const int32_t* node_off2, const int32_t* node_idx2,
                         int mode, float nnratio, int check_orientation, int32_t* match12_out);
 
+/* The same (KeyFrame, Frame) search when F is a two-camera rig Frame (F.Nleft != -1; src/ORBmatcher.cc:306-331,
+ * :371-396).  Side-2 arrays cover F's features [0, nleft2) (left camera) and [nleft2, n2) (right camera); the node lists
+ * index that combined range.  A KeyFrame feature may bind one feature per camera: the left one under the ratio test,
+ * the right one inside the left one's `bestDist1 <= TH_LOW` block with its ratio test disabled (`|| true`, :373), as the
+ * reference does.  match_left_out[i1] / match_right_out[i1] = F feature or -1, after the rotation cut; the caller sets
+ * vpMapPointMatches[match] = pKF's MapPoint i1.  angle1 = kp.angle of the KeyFrame feature (:340-343), angle2 = the F
+ * keypoint's (mvKeys for the left range, mvKeysRight for the right one).  Returns nmatches (both cameras). */
+int cuorb_search_by_bow_rig(int device, int n1, const uint8_t* desc1, const uint8_t* valid1, const float* angle1, int n2,
+                            int nleft2, const uint8_t* desc2, const float* angle2, int n_nodes, const int32_t* node_off1,
+                            const int32_t* node_idx1, const int32_t* node_off2, const int32_t* node_idx2, float nnratio,
+                            int check_orientation, int32_t* match_left_out, int32_t* match_right_out);
+
 /* ---- the remaining ORBmatcher searches, pinhole / NLeft == -1 branches ----
  * The caller keeps what needs Sophus / Eigen / MapPoint state (pose transform, camera projection,
  * distance-invariance range, viewing-angle test, MapPoint::PredictScale) and passes one SoA entry per

@@ -156,6 +156,7 @@ def lib() -> C.CDLL:
         V = C.c_void_p
         L.oo_search_by_projection_rig.argtypes = ([FV, FV, V, V, C.c_int] + [V] * 11 + [C.c_float, C.c_int, C.c_float, C.c_float, V, V])
         L.oo_search_by_projection_frame_rig.argtypes = ([FV, FV, C.c_int] + [V] * 9 + [C.c_float, C.c_int, C.c_int, C.c_int] + [V] * 5)
+        L.oo_search_by_bow_rig.argtypes = [C.c_int, V, V, V, C.c_int, C.c_int, V, V, C.c_int, V, V, V, V, C.c_float, C.c_int, V, V]
         _lib = L
     return _lib
 
@@ -552,3 +553,15 @@ def search_by_projection_frame_rig(fvl, fvr, last_desc, u, v, inv_z, ur, vr, las
     n = lib().oo_search_by_projection_frame_rig(C.byref(fvl), C.byref(fvr), n_last, *[_p(x) for x in arrs], th, int(forward),
                                                 int(backward), int(check_ori), *[_p(o) for o in outs])
     return (n,) + tuple(o[:n_last] for o in outs[:4]) + (outs[4],)
+
+
+def search_by_bow_rig(desc1, valid1, angle1, desc2, nleft2, angle2, off1, idx1, off2, idx2, nnratio=0.7, check_orientation=True):
+    """SearchByBoW(KeyFrame, Frame) with F.Nleft != -1; side-2 arrays cover F's left-then-right features.
+    Returns (nmatches, match_l[n1], match_r[n1])."""
+    desc1 = _u8(desc1).reshape(-1, 32); desc2 = _u8(desc2).reshape(-1, 32)
+    v1 = _u8(np.asarray(valid1).astype(np.uint8)); a1 = _f32(angle1); a2 = _f32(angle2)
+    o1, i1, o2, i2 = _i32(off1), _i32(idx1), _i32(off2), _i32(idx2)
+    ml = np.empty(max(len(desc1), 1), np.int32); mr = np.empty(max(len(desc1), 1), np.int32)
+    n = lib().oo_search_by_bow_rig(len(desc1), _p(desc1), _p(v1), _p(a1), len(desc2), int(nleft2), _p(desc2), _p(a2), len(o1) - 1,
+                                   _p(o1), _p(i1), _p(o2), _p(i2), np.float32(nnratio), int(bool(check_orientation)), _p(ml), _p(mr))
+    return n, ml[:len(desc1)], mr[:len(desc1)]

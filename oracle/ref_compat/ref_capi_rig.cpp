@@ -8,6 +8,7 @@
 // (mvKeys, mGrid), the right camera's [Nleft, N) (mvKeysRight, mGridRight, descriptor rows idx + Nleft).
 #include <vector>
 
+#include "KeyFrame.h"
 #include "ORBmatcher.h"
 #include "fake_triangulate.h"
 #include "ref_harness.h"
@@ -167,6 +168,51 @@ int ref_fisheye_stereo(int nl, const cv::KeyPoint* kl, const uint8_t* dl, int mo
     n += l2r[i] >= 0;
   }
   for (int i = 0; i < nr; i++) r2l[i] = F.mvRightToLeftMatch[i];
+  return n;
+}
+
+// ---- int ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame& F, vpMapPointMatches) with BOTH a rig KeyFrame and a rig
+// Frame (src/ORBmatcher.cc:237-420, the F.Nleft != -1 branch :306-331, :371-396).  The KeyFrame's features are
+// [0, NLeft) = kl (mvKeys) and [NLeft, N1) = kr (mvKeysRight), has_mp1 over all N1 (1 good MapPoint, 2 bad one);
+// F likewise from fl / fr.  FeatureVectors index the combined ranges.  match_l[i1] / match_r[i1] = F feature (combined
+// index) holding KeyFrame feature i1's MapPoint on return, split by camera; -1 none. ----
+int ref_search_by_bow_rig(const cuorb_frame_view* kl, const cuorb_frame_view* kr, const uint8_t* has_mp1, int nn1,
+                          const int32_t* node1, const int32_t* off1, const int32_t* idx1, const cuorb_frame_view* fl,
+                          const cuorb_frame_view* fr, int nn2, const int32_t* node2, const int32_t* off2,
+                          const int32_t* idx2, float nnratio, int check_ori, int32_t* match_l, int32_t* match_r) {
+  RigFrame rf(fl, fr, nullptr, nullptr);
+  rf.F.mvpMapPoints.assign(rf.F.N, nullptr);
+  for (int k = 0; k < nn2; k++)
+    for (int a = off2[k]; a < off2[k + 1]; a++) rf.F.mFeatVec.addFeature((DBoW2::NodeId)node2[k], (unsigned)idx2[a]);
+  const int n1l = kl->n, n1r = kr->n, n1 = n1l + n1r;
+  KeyFrame K;
+  PassThroughCamera cam;
+  K.N = n1; K.NLeft = n1l; K.NRight = n1r;
+  const cv::KeyPoint* a = (const cv::KeyPoint*)kl->keys_un;
+  const cv::KeyPoint* b = (const cv::KeyPoint*)kr->keys_un;
+  K.mvKeys.assign(a, a + n1l); K.mvKeysRight.assign(b, b + n1r); K.mvKeysUn = K.mvKeys;
+  std::vector<uint8_t> desc((size_t)(n1 > 0 ? n1 : 1) * 32);
+  if (n1l) memcpy(desc.data(), kl->descriptors, (size_t)n1l * 32);
+  if (n1r) memcpy(desc.data() + (size_t)n1l * 32, kr->descriptors, (size_t)n1r * 32);
+  K.mDescriptors = desc_mat(desc.data(), n1);
+  K.mpCamera = &cam; K.mpCamera2 = &cam;
+  std::unique_ptr<MapPoint[]> mps(new MapPoint[n1 > 0 ? n1 : 1]);
+  K.mvpMapPoints.assign(n1, nullptr);
+  for (int i = 0; i < n1; i++) if (has_mp1[i]) { mps[i].mbBad = has_mp1[i] == 2; K.mvpMapPoints[i] = &mps[i]; }
+  for (int k = 0; k < nn1; k++)
+    for (int q = off1[k]; q < off1[k + 1]; q++) K.mFeatVec.addFeature((DBoW2::NodeId)node1[k], (unsigned)idx1[q]);
+  std::vector<MapPoint*> matches;
+  ORBmatcher matcher(nnratio, check_ori != 0);
+  const int n = matcher.SearchByBoW(&K, rf.F, matches);
+  for (int i = 0; i < n1; i++) match_l[i] = match_r[i] = -1;
+  for (int i2 = 0; i2 < (int)matches.size(); i2++) {
+    if (!matches[i2]) continue;
+    const int i1 = (int)(matches[i2] - &mps[0]);
+    if (i1 < 0 || i1 >= n1) return -1001;
+    int32_t* dst = i2 < rf.F.Nleft ? match_l : match_r;
+    if (dst[i1] != -1) return -1002;
+    dst[i1] = i2;
+  }
   return n;
 }
 

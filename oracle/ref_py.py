@@ -96,6 +96,7 @@ def lib() -> C.CDLL:
         L.ref_search_by_projection_frame_rig.argtypes = ([FV, FV, C.c_int] + [V] * 4 + [C.c_float, C.c_float] + [V] * 3 +
                                                          [C.c_float, C.c_int, C.c_int, C.c_int, V])
         L.ref_fisheye_stereo.argtypes = [C.c_int, V, V, C.c_int, C.c_int, V, V, C.c_int, C.c_int, V, V, V, V, V]
+        L.ref_search_by_bow_rig.argtypes = [FV, FV, V, C.c_int, V, V, V, FV, FV, C.c_int, V, V, V, C.c_float, C.c_int, V, V]
         _lib = L
     return _lib
 
@@ -383,3 +384,16 @@ def fisheye_stereo(kps_l, desc_l, mono_left, kps_r, desc_r, mono_right, level_si
     lib().ref_fisheye_stereo(nl, _p(kl), _p(dl), int(mono_left), nr, _p(kr), _p(dr), int(mono_right), len(s2), _p(s2), _p(l2r),
                              _p(r2l), _p(depth), _p(p3d))
     return l2r[:nl], r2l[:nr], depth[:nl], p3d[:nl]
+
+
+def search_by_bow_rig(kl, kr, has_mp1, featvec1, fl, fr, featvec2, nnratio, check_ori=True):
+    """ORBmatcher::SearchByBoW(KeyFrame, Frame) with a rig KeyFrame (views kl, kr) and a rig Frame (views fl, fr); the
+    FeatureVectors index the combined left-then-right ranges.  Returns (nmatches, match_l[n1], match_r[n1])."""
+    n1, nd1, o1, i1 = flatten_feature_vector(featvec1)
+    n2, nd2, o2, i2 = flatten_feature_vector(featvec2)
+    h1 = _u8(has_mp1)
+    N1 = kl.n + kr.n
+    ml = np.empty(max(N1, 1), np.int32); mr = np.empty(max(N1, 1), np.int32)
+    r = lib().ref_search_by_bow_rig(C.byref(kl), C.byref(kr), _p(h1), n1, _p(nd1), _p(o1), _p(i1), C.byref(fl), C.byref(fr), n2,
+                                    _p(nd2), _p(o2), _p(i2), nnratio, int(check_ori), _p(ml), _p(mr))
+    return r, ml[:N1], mr[:N1]

@@ -101,6 +101,9 @@ SIGNATURES = {
                                        [C.c_void_p] * 11 + [C.c_float, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p]),
     "cuorb_search_by_projection_frame_rig": (C.c_int, [C.c_int, C.POINTER(FrameView), C.POINTER(FrameView), C.c_int] + [C.c_void_p] * 9 +
                                              [C.c_float, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 5),
+    "cuorb_search_by_bow_rig": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                          C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_void_p,
+                                          C.c_void_p]),
     "cuorb_localmap_create": (C.c_void_p, [C.c_int, C.c_int]),
     "cuorb_localmap_destroy": (None, [C.c_void_p]),
     "cuorb_localmap_update": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 6),

@@ -319,7 +319,22 @@ def SearchByBoW_KF_KF(self, desc1, has_mp1, angle1, featvec1, desc2, has_mp2, an
     return _search_by_bow(self, desc1, has_mp1, angle1, featvec1, desc2, has_mp2, angle2, featvec2, 1)
 
 
+def SearchByBoW_KF_RigF(self, kf_desc, kf_has_mappoint, kf_angle, kf_featvec, f_desc, f_nleft, f_angle, f_featvec):
+    """int SearchByBoW(KeyFrame* pKF, Frame& F, vpMapPointMatches) with F.Nleft != -1 (src/ORBmatcher.cc:306-331, :371-396).
+    f_desc / f_angle cover F's left-then-right features, f_nleft = F.Nleft.  Returns (nmatches, match_left, match_right)."""
+    desc1 = _c(kf_desc, np.uint8).reshape(-1, 32); desc2 = _c(f_desc, np.uint8).reshape(-1, 32)
+    valid1 = _c(np.asarray(kf_has_mappoint).astype(np.uint8), np.uint8)
+    angle1 = _c(kf_angle, np.float32); angle2 = _c(f_angle, np.float32)
+    off1, idx1, off2, idx2 = join_feature_vectors(kf_featvec, f_featvec)
+    ml = np.full(max(len(desc1), 1), -1, np.int32); mr = np.full(max(len(desc1), 1), -1, np.int32)
+    n = check(self._L.cuorb_search_by_bow_rig(self.device, len(desc1), ptr(desc1), ptr(valid1), ptr(angle1), len(desc2), int(f_nleft),
+                                              ptr(desc2), ptr(angle2), len(off1) - 1, ptr(off1), ptr(idx1), ptr(off2), ptr(idx2),
+                                              self.mfNNratio, int(self.mbCheckOrientation), ptr(ml), ptr(mr)))
+    return n, ml[:len(desc1)], mr[:len(desc1)]
+
+
 ORBmatcher.SearchByBoW_KF_F = SearchByBoW_KF_F
+ORBmatcher.SearchByBoW_KF_RigF = SearchByBoW_KF_RigF
 ORBmatcher.SearchByBoW_KF_KF = SearchByBoW_KF_KF
 
 

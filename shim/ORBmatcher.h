@@ -5,7 +5,8 @@
 // (member names below are the reference's) and against the small structs of tests/native.
 // The pointer graph is flattened to SoA on the host, matched by libcuorb, and the bindings
 // F.mvpMapPoints[idx] = pMP are replayed in the reference's order.  The two tracking-time SearchByProjection
-// overloads also take two-camera rig Frames (Nleft != -1); the other searches are pinhole (Nleft == -1) only.
+// overloads and SearchByBoW(KeyFrame, Frame) also take two-camera rig Frames (Nleft != -1); the other searches are
+// pinhole (Nleft == -1) only.
 #pragma once
 #include <cmath>
 #include <cstring>
@@ -240,17 +241,36 @@ public:
   }
 
   // int SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches)
-  // (include/ORBmatcher.h:66, src/ORBmatcher.cc:237-420), mono branch.  Reads pKF->GetMapPointMatches(),
+  // (include/ORBmatcher.h:66, src/ORBmatcher.cc:237-420), pinhole and two-camera rig Frames.  Reads pKF->GetMapPointMatches(),
   // pKF->mFeatVec, pKF->mDescriptors, pKF->mvKeysUn, F.mFeatVec, F.mDescriptors, F.mvKeys, F.N.
   template <class KeyFrameT, class FrameT, class MapPointT>
   int SearchByBoW(KeyFrameT* pKF, FrameT& F, std::vector<MapPointT*>& vpMapPointMatches) {
-    if (F.Nleft != -1) CUORB_SHIM_FAIL(std::runtime_error, "ORBmatcher shim: fisheye (Nleft != -1) branch is not built", 0);
     const std::vector<MapPointT*> vpMapPointsKF = pKF->GetMapPointMatches();
     vpMapPointMatches.assign(F.N, static_cast<MapPointT*>(nullptr));
     const int n1 = (int)vpMapPointsKF.size(), n2 = F.N;
     if (n1 == 0 || n2 == 0) return 0;
     std::vector<uint8_t> valid1(n1), elig2(n2, 1);
     std::vector<float> a1(n1), a2(n2);
+    if (F.Nleft != -1) {
+      // two-camera rig Frame (:306-331, :371-396): one best / runner-up pair per camera, both may bind
+      for (int i = 0; i < n1; i++) {
+        valid1[i] = vpMapPointsKF[i] && !vpMapPointsKF[i]->isBad();
+        a1[i] = !pKF->mpCamera2 ? pKF->mvKeysUn[i].angle                                       // :340-343
+                : i >= pKF->NLeft ? pKF->mvKeysRight[i - pKF->NLeft].angle : pKF->mvKeys[i].angle;
+      }
+      for (int j = 0; j < n2; j++) a2[j] = j >= F.Nleft ? F.mvKeysRight[j - F.Nleft].angle : F.mvKeys[j].angle;   // :346-348, :384-386
+      std::vector<int32_t> off1, idx1, off2, idx2, ml(n1, -1), mr(n1, -1);
+      join(pKF->mFeatVec, F.mFeatVec, off1, idx1, off2, idx2);
+      const int n = cuorb_search_by_bow_rig(device_, n1, contiguous(pKF->mDescriptors), valid1.data(), a1.data(), n2, F.Nleft,
+                                            contiguous(F.mDescriptors), a2.data(), (int)off1.size() - 1, off1.data(), idx1.data(),
+                                            off2.data(), idx2.data(), mfNNratio, mbCheckOrientation ? 1 : 0, ml.data(), mr.data());
+      if (n < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("SearchByBoW (rig, libcuorb): ") + cuorb_last_error(), 0);
+      for (int i = 0; i < n1; i++) {
+        if (ml[i] >= 0) vpMapPointMatches[ml[i]] = vpMapPointsKF[i];     // :335
+        if (mr[i] >= 0) vpMapPointMatches[mr[i]] = vpMapPointsKF[i];     // :374
+      }
+      return n;
+    }
     for (int i = 0; i < n1; i++) { valid1[i] = vpMapPointsKF[i] && !vpMapPointsKF[i]->isBad(); a1[i] = pKF->mvKeysUn[i].angle; }
     for (int j = 0; j < n2; j++) a2[j] = F.mvKeys[j].angle;
     std::vector<int32_t> match(n1, -1);

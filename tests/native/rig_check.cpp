@@ -2,7 +2,7 @@
 // src/ORBmatcher.cc:38-227 and :1684-1908) over Frame / MapPoint / Sophus / camera classes with the reference's
 // member names (the stand-ins of oracle/ref_compat, headers only; nothing of the reference is linked), and writes the
 // final F.mvpMapPoints to a file the pytest compares with the reference's own functions.
-// usage: rig_check mappoints|lastframe case.bin out.bin
+// usage: rig_check mappoints|lastframe|bow case.bin out.bin
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -11,6 +11,7 @@
 
 #include "Frame.h"
 #include "GeometricCamera.h"
+#include "KeyFrame.h"
 #include "MapPoint.h"
 
 #include "../../shim/ORBmatcher.h"
@@ -38,8 +39,53 @@ template <class T> static std::vector<T> rd(FILE* f, size_t n) {
   return v;
 }
 
+// SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) with a rig KeyFrame and a rig Frame (src/ORBmatcher.cc:237-420)
+static int bow_main(const char* in, const char* outp) {
+  FILE* f = fopen(in, "rb");
+  if (!f) return 2;
+  // ints: n1l, n1r, n2l, n2r, nn1, m1, nn2, m2, check_ori | floats: ratio
+  const std::vector<int32_t> hi = rd<int32_t>(f, 9);
+  const std::vector<float> hf = rd<float>(f, 1);
+  const int n1l = hi[0], n1r = hi[1], n2l = hi[2], n2r = hi[3], n1 = n1l + n1r, n2 = n2l + n2r;
+  PassThrough cam;
+  KeyFrame K;
+  K.N = n1; K.NLeft = n1l; K.NRight = n1r; K.mpCamera = &cam; K.mpCamera2 = &cam;
+  K.mvKeys = rd<cv::KeyPoint>(f, n1l); K.mvKeysRight = rd<cv::KeyPoint>(f, n1r); K.mvKeysUn = K.mvKeys;
+  std::vector<uint8_t> d1 = rd<uint8_t>(f, (size_t)n1 * 32);
+  K.mDescriptors = cv::Mat(n1, 32, CV_8UC1, d1.data(), 32);
+  const std::vector<uint8_t> has = rd<uint8_t>(f, n1);
+  Frame F;
+  F.N = n2; F.Nleft = n2l; F.Nright = n2r; F.mpCamera = &cam; F.mpCamera2 = &cam;
+  F.mvKeys = rd<cv::KeyPoint>(f, n2l); F.mvKeysRight = rd<cv::KeyPoint>(f, n2r);
+  std::vector<uint8_t> d2 = rd<uint8_t>(f, (size_t)n2 * 32);
+  F.mDescriptors = cv::Mat(n2, 32, CV_8UC1, d2.data(), 32);
+  auto featvec = [&](DBoW2::FeatureVector& fv, int nn, int m) {
+    const std::vector<int32_t> node = rd<int32_t>(f, nn), off = rd<int32_t>(f, nn + 1), idx = rd<int32_t>(f, m);
+    for (int k = 0; k < nn; k++) for (int a = off[k]; a < off[k + 1]; a++) fv.addFeature((DBoW2::NodeId)node[k], (unsigned)idx[a]);
+  };
+  featvec(K.mFeatVec, hi[4], hi[5]);
+  featvec(F.mFeatVec, hi[6], hi[7]);
+  fclose(f);
+  std::unique_ptr<MapPoint[]> mps(new MapPoint[n1 + 1]);
+  K.mvpMapPoints.assign(n1, nullptr);
+  for (int i = 0; i < n1; i++) if (has[i]) { mps[i].mbBad = has[i] == 2; K.mvpMapPoints[i] = &mps[i]; }
+  std::vector<MapPoint*> matches;
+  ORBmatcher matcher(hf[0], hi[8] != 0);
+  const int n = matcher.SearchByBoW(&K, F, matches);
+  std::vector<int32_t> out(1 + 2 * (size_t)n1, -1);
+  out[0] = n;
+  for (int i2 = 0; i2 < (int)matches.size(); i2++)
+    if (matches[i2]) out[1 + (i2 < n2l ? 0 : n1) + (matches[i2] - &mps[0])] = i2;
+  f = fopen(outp, "wb");
+  fwrite(out.data(), 4, out.size(), f);
+  fclose(f);
+  printf("rig bow ok: %d matches\n", n);
+  return 0;
+}
+
 int main(int argc, char** argv) {
-  if (argc != 4) { fprintf(stderr, "usage: rig_check mappoints|lastframe case.bin out.bin\n"); return 2; }
+  if (argc != 4) { fprintf(stderr, "usage: rig_check mappoints|lastframe|bow case.bin out.bin\n"); return 2; }
+  if (!strcmp(argv[1], "bow")) return bow_main(argv[2], argv[3]);
   const bool last = !strcmp(argv[1], "lastframe");
   FILE* f = fopen(argv[2], "rb");
   if (!f) return 2;

@@ -115,3 +115,19 @@ def fuse_bookkeeping(best, bound, nobs_kf, nobs_q, sim3):
         elif best[i] >= 0 and replaced_by.get(("kf", int(best[i]))) == me:
             out[i] = 2
     return out
+
+
+def bow_rig_views(c, nleft1, nleft2, sf=None):
+    """Four frame views for a tests/bow_cases.py pair read as a rig KeyFrame (features [0, nleft1) left camera, the
+    rest right camera) and a rig Frame (split at nleft2): arbitrary in-image positions, octave 0, the case's angles."""
+    sf = np.asarray([1.2 ** i for i in range(8)], np.float32) if sf is None else sf
+    out, keep = [], []
+    for desc, angle, seed, cut in ((c["desc1"], c["angle1"], 1, nleft1), (c["desc2"], c["angle2"], 2, nleft2)):
+        rng = np.random.default_rng(seed)
+        k = np.zeros(len(desc), op.KP_DTYPE)
+        k["x"] = rng.uniform(1, W - 1, len(desc)).astype(np.float32); k["y"] = rng.uniform(1, H - 1, len(desc)).astype(np.float32)
+        k["size"] = 31; k["angle"] = angle; k["octave"] = 0; k["class_id"] = -1
+        for lo, hi in ((0, cut), (cut, len(desc))):
+            fv, ka = op.make_frame_view(k[lo:hi], desc[lo:hi], None, None, W, H, sf)
+            out.append(fv); keep.append(ka)
+    return out, keep

@@ -85,3 +85,27 @@ def test_rig_degenerate(rv):
     assert n == 0 and (bl == -1).all() and (br == -1).all()
     n, bl, br = ORBmatcher().SearchByProjectionRig(F, *[a[:0] for a in args], np.zeros(0, np.uint8), 3.0)
     assert n == 0 and len(bl) == 0
+
+
+@pytest.mark.parametrize("seed,tie_heavy,ratio,ori", [(1, False, 0.7, True), (2, True, 0.9, True), (3, False, 0.6, False)])
+def test_search_by_bow_rig(seed, tie_heavy, ratio, ori):
+    """SearchByBoW(KeyFrame, Frame) with F.Nleft != -1 (src/ORBmatcher.cc:306-331, :371-396) through the C ABI against
+    the oracle and the reference's own function."""
+    from orbslam3_cpp_fork_b200 import ORBmatcher
+    from orbslam3_cpp_fork_b200.matcher import join_feature_vectors
+    from tests.bow_cases import make_pair
+    from tests.ref_search_cases import bow_rig_views, has_mp_codes
+    c = make_pair(seed, tie_heavy=tie_heavy)
+    nleft1, nleft2 = 650, 560
+    h1 = has_mp_codes(c["valid1"], seed)
+    n, ml, mr = ORBmatcher(ratio, ori).SearchByBoW_KF_RigF(c["desc1"], h1 == 1, c["angle1"], c["fv1"], c["desc2"], nleft2, c["angle2"],
+                                                           c["fv2"])
+    off1, idx1, off2, idx2 = join_feature_vectors(c["fv1"], c["fv2"])
+    on, oml, omr = op.search_by_bow_rig(c["desc1"], h1 == 1, c["angle1"], c["desc2"], nleft2, c["angle2"], off1, idx1, off2, idx2,
+                                        ratio, ori)
+    assert n == on and (ml == oml).all() and (mr == omr).all()
+    assert (ml >= 0).sum() > 40 and (mr >= 0).sum() > 40
+    if rp.available():
+        (kl, kr, fl, fr), keep = bow_rig_views(c, nleft1, nleft2)
+        rn, rml, rmr = rp.search_by_bow_rig(kl, kr, h1, c["fv1"], fl, fr, c["fv2"], ratio, ori)
+        assert rn == n and (rml == ml).all() and (rmr == mr).all()

@@ -342,3 +342,43 @@ def test_cpp_shim_local_map_two_frames(tmp_path):
     ch = np.zeros(M, bool); ch[changed] = True
     assert int(res[0][2]) == len(order1)
     assert int(res[1][2]) == int((~in1[order2]).sum() + (in1[order2] & ch[order2]).sum())   # only new or changed points were sent
+
+
+@pytest.mark.parametrize("seed,ori", [(1, True), (2, False)])
+def test_cpp_shim_rig_bow(tmp_path, seed, ori):
+    """shim/ORBmatcher.h SearchByBoW(KeyFrame*, Frame&, ...) with a rig KeyFrame and a rig Frame against the reference's
+    own function (src/ORBmatcher.cc:237-420 with F.Nleft != -1)."""
+    from oracle import ref_py as rp
+    from tests.bow_cases import make_pair
+    from tests.ref_search_cases import bow_rig_views, has_mp_codes
+    if not rp.available():
+        pytest.skip("oracle/_ref/liborb_ref.so did not travel to this box")
+    build.build_libcuorb()
+    exe = str(tmp_path / "rig_check")
+    pkg = os.path.join(ROOT, "orbslam3_cpp_fork_b200")
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-DCUORB_SHIM_USE_OPENCV",
+                           "-I" + os.path.join(ROOT, "oracle", "ref_compat"),
+                           os.path.join(ROOT, "tests", "native", "rig_check.cpp"), "-o", exe,
+                           "-L" + pkg, "-l:libcuorb.so", "-Wl,-rpath," + pkg])
+    c = make_pair(seed, tie_heavy=(seed == 2))
+    nleft1, nleft2, ratio = 650, 560, 0.75
+    h1 = has_mp_codes(c["valid1"], seed)
+    (kl, kr, fl, fr), keep = bow_rig_views(c, nleft1, nleft2)
+    rn, rml, rmr = rp.search_by_bow_rig(kl, kr, h1, c["fv1"], fl, fr, c["fv2"], ratio, ori)
+    n1, n2 = len(c["desc1"]), len(c["desc2"])
+    a1, b1, c1_, d1_ = rp.flatten_feature_vector(c["fv1"]); a2, b2, c2_, d2_ = rp.flatten_feature_vector(c["fv2"])
+    case = str(tmp_path / "case.bin"); out = str(tmp_path / "out.bin")
+    with open(case, "wb") as f:
+        np.array([nleft1, n1 - nleft1, nleft2, n2 - nleft2, a1, len(d1_), a2, len(d2_), int(ori)], np.int32).tofile(f)
+        np.array([ratio], np.float32).tofile(f)
+        for k in keep[0:2]:
+            np.ascontiguousarray(k[0]).tofile(f)               # KeyFrame keys: left, right
+        np.ascontiguousarray(c["desc1"]).tofile(f); h1.astype(np.uint8).tofile(f)
+        for k in keep[2:4]:
+            np.ascontiguousarray(k[0]).tofile(f)               # Frame keys: left, right
+        np.ascontiguousarray(c["desc2"]).tofile(f)
+        b1.tofile(f); c1_.tofile(f); d1_.tofile(f); b2.tofile(f); c2_.tofile(f); d2_.tofile(f)
+    subprocess.check_call([exe, "bow", case, out])
+    res = np.fromfile(out, np.int32)
+    assert int(res[0]) == rn and rn > 80
+    assert (res[1:1 + n1] == rml).all() and (res[1 + n1:] == rmr).all()

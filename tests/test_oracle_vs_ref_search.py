@@ -133,3 +133,22 @@ def test_search_for_triangulation_equals_reference(tv, pose_kind, only_stereo, c
         assert n > 8
     if pose_kind == "epipole_in_image":
         assert 0 < ep[0] < W and 0 < ep[1] < H
+
+
+@pytest.mark.parametrize("seed,tie_heavy,ratio,ori", [(1, False, 0.75, True), (2, True, 0.75, True), (5, True, 0.6, False),
+                                                      (7, False, 0.9, True)])
+def test_search_by_bow_rig_equals_reference(seed, tie_heavy, ratio, ori):
+    """SearchByBoW(KeyFrame, Frame) with F.Nleft != -1 (src/ORBmatcher.cc:306-331, :371-396): a best / second-best pair
+    per camera, the right match nested in the left one's threshold test with its ratio test disabled."""
+    from tests.ref_search_cases import bow_rig_views
+    c = make_pair(seed, n1=700, n2=640, n_nodes=60, tie_heavy=tie_heavy)
+    nleft1, nleft2 = 420, 350
+    (kl, kr, fl, fr), keep = bow_rig_views(c, nleft1, nleft2)
+    h1 = has_mp_codes(c["valid1"], seed)
+    off1, idx1, off2, idx2 = join_feature_vectors(c["fv1"], c["fv2"])
+    n, ml, mr = op.search_by_bow_rig(c["desc1"], h1 == 1, c["angle1"], c["desc2"], nleft2, c["angle2"], off1, idx1, off2, idx2,
+                                     ratio, ori)
+    rn, rml, rmr = rp.search_by_bow_rig(kl, kr, h1, c["fv1"], fl, fr, c["fv2"], ratio, ori)
+    assert rn == n and (rml == ml).all() and (rmr == mr).all()
+    assert (ml >= 0).sum() > 10 and (mr >= 0).sum() > 10 and ((ml >= 0) & (mr >= 0)).sum() > 0
+    assert (ml[ml >= 0] < nleft2).all() and (mr[mr >= 0] >= nleft2).all()
