@@ -216,4 +216,57 @@ int ref_search_by_bow_rig(const cuorb_frame_view* kl, const cuorb_frame_view* kr
   return n;
 }
 
+// ---- int ORBmatcher::Fuse(KeyFrame* pKF, vpMapPoints, th, bRight) on a rig KeyFrame, either camera
+// (src/ORBmatcher.cc:1149-1328: bRight selects GetRightPose / mpCamera2 / mGridRight / mvKeysRight and adds NLeft to
+// the chosen index, :1156-1164, :1236, :1270-1272).  Queries as in ref_fuse (identity poses, pass-through cameras,
+// world position (u, v, z)); best_idx_out[i] = KeyFrame feature (combined index) query i fuses into, recovered one
+// query at a time on a KeyFrame without MapPoints.  A rig KeyFrame's mvuRight is all -1 (src/Frame.cc:1313), so only
+// the monocular 5.99 gate applies. ----
+int ref_fuse_rig(const cuorb_frame_view* kl, const cuorb_frame_view* kr, int right, int n, const uint8_t* mp_desc,
+                 const float* u, const float* v, const float* z, const int32_t* level, const uint8_t* active, float th,
+                 int32_t* best_idx_out) {
+  RigFrame rf(kl, kr, nullptr, nullptr);
+  const Frame& F = rf.F;
+  KeyFrame K;
+  K.N = F.N; K.NLeft = F.Nleft; K.NRight = F.Nright;
+  K.mnGridCols = FRAME_GRID_COLS; K.mnGridRows = FRAME_GRID_ROWS;
+  K.mfGridElementWidthInv = Frame::mfGridElementWidthInv; K.mfGridElementHeightInv = Frame::mfGridElementHeightInv;
+  K.fx = 1.f; K.fy = 1.f; K.cx = 0.f; K.cy = 0.f; K.mbf = F.mbf; K.mb = F.mb;
+  K.mvKeys = F.mvKeys; K.mvKeysRight = F.mvKeysRight; K.mvKeysUn = F.mvKeys;
+  K.mvuRight.assign(std::max(F.Nleft, F.Nright), -1.f);   // the reference indexes it with the right camera's local idx (:1248)
+  K.mDescriptors = F.mDescriptors;
+  K.mnScaleLevels = F.mnScaleLevels; K.mfScaleFactor = kl->nlevels > 1 ? kl->scale_factors[1] : 1.2f;
+  K.mfLogScaleFactor = std::log(K.mfScaleFactor);
+  K.mvScaleFactors = F.mvScaleFactors;
+  K.mvLevelSigma2.resize(F.mnScaleLevels); K.mvInvLevelSigma2.resize(F.mnScaleLevels);
+  for (int l = 0; l < F.mnScaleLevels; l++) {
+    K.mvLevelSigma2[l] = F.mvScaleFactors[l] * F.mvScaleFactors[l];
+    K.mvInvLevelSigma2[l] = 1.0f / K.mvLevelSigma2[l];
+  }
+  K.mnMinX = Frame::mnMinX; K.mnMinY = Frame::mnMinY; K.mnMaxX = Frame::mnMaxX; K.mnMaxY = Frame::mnMaxY;
+  K.mGrid.resize(K.mnGridCols); K.mGridRight.resize(K.mnGridCols);
+  for (int i = 0; i < K.mnGridCols; i++) {
+    K.mGrid[i].resize(K.mnGridRows); K.mGridRight[i].resize(K.mnGridRows);
+    for (int j = 0; j < K.mnGridRows; j++) { K.mGrid[i][j] = F.mGrid[i][j]; K.mGridRight[i][j] = F.mGridRight[i][j]; }
+  }
+  PassThroughCamera cam, cam2;
+  K.mpCamera = &cam; K.mpCamera2 = &cam2;
+  K.mvpMapPoints.assign(K.N, nullptr);
+  QueryPoints q(n, mp_desc, u, v, z, level, active, K.mfScaleFactor);
+  ORBmatcher matcher(0.9f, true);
+  int total = 0;
+  for (int i = 0; i < n; i++) {
+    std::vector<MapPoint*> one(1, q.ptr[i]);
+    const int r = matcher.Fuse(&K, one, th, right != 0);
+    best_idx_out[i] = -1;
+    if (r) {
+      if (!q.mp[i].IsInKeyFrame(&K)) return -1004;
+      best_idx_out[i] = std::get<0>(q.mp[i].GetIndexInKeyFrame(&K));
+      K.mvpMapPoints[best_idx_out[i]] = nullptr;
+    }
+    total += r;
+  }
+  return total;
+}
+
 }  // extern "C"

@@ -97,6 +97,7 @@ def lib() -> C.CDLL:
                                                          [C.c_float, C.c_int, C.c_int, C.c_int, V])
         L.ref_fisheye_stereo.argtypes = [C.c_int, V, V, C.c_int, C.c_int, V, V, C.c_int, C.c_int, V, V, V, V, V]
         L.ref_search_by_bow_rig.argtypes = [FV, FV, V, C.c_int, V, V, V, FV, FV, C.c_int, V, V, V, C.c_float, C.c_int, V, V]
+        L.ref_fuse_rig.argtypes = [FV, FV, C.c_int, C.c_int] + [V] * 6 + [C.c_float, V]
         _lib = L
     return _lib
 
@@ -397,3 +398,13 @@ def search_by_bow_rig(kl, kr, has_mp1, featvec1, fl, fr, featvec2, nnratio, chec
     r = lib().ref_search_by_bow_rig(C.byref(kl), C.byref(kr), _p(h1), n1, _p(nd1), _p(o1), _p(i1), C.byref(fl), C.byref(fr), n2,
                                     _p(nd2), _p(o2), _p(i2), nnratio, int(check_ori), _p(ml), _p(mr))
     return r, ml[:N1], mr[:N1]
+
+
+def fuse_rig(kl, kr, right, mp_desc, u, v, z, level, active, th):
+    """ORBmatcher::Fuse(pKF, vpMapPoints, th, bRight) on a rig KeyFrame (views kl, kr).  Returns (nFused, best_idx[n]) with
+    best_idx in the KeyFrame's combined left-then-right index range."""
+    arrs = [_u8(mp_desc), _f32(u), _f32(v), _f32(z), _i32(level), _u8(active)]
+    n = len(arrs[1])
+    best = np.empty(max(n, 1), np.int32)
+    r = lib().ref_fuse_rig(C.byref(kl), C.byref(kr), int(right), n, *[_p(a) for a in arrs], th, _p(best))
+    return r, best[:n]

@@ -381,6 +381,22 @@ def Fuse(self, KF: Frame, mvInvLevelSigma2, mp_desc, u, v, ur, level, active, th
     return r, best
 
 
+def FuseRig(self, KF: "RigFrame", bRight, mvInvLevelSigma2, mp_desc, u, v, ur, level, active, th=3.0, check_reprojection=True):
+    """Fuse on a two-camera rig KeyFrame (NLeft != -1; src/ORBmatcher.cc:1156-1164, :1236, :1270-1272): the search runs on
+    the left camera's features or, with bRight, on the right camera's; best indices come back in the KeyFrame's combined
+    left-then-right range, as the reference leaves them."""
+    side = KF.right if bRight else KF.left
+    saved = side.mvuRight
+    side.mvuRight = None                                           # a rig KeyFrame's mvuRight is all -1
+    try:
+        r, best = Fuse(self, side, mvInvLevelSigma2, mp_desc, u, v, ur, level, active, th, check_reprojection)
+    finally:
+        side.mvuRight = saved
+    if bRight:
+        best = np.where(best >= 0, best + KF.Nleft, -1).astype(np.int32)
+    return r, best
+
+
 def SearchBySim3(self, KF1: Frame, KF2: Frame, mp_desc1, u12, v12, level12, active1, mp_desc2, u21, v21, level21,
                  active2, th):
     """int SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, vpMatches12, S12, th) (src/ORBmatcher.cc:1454-1682)."""
@@ -423,6 +439,7 @@ def SearchForTriangulation(self, KF1: Frame, KF2: Frame, has_mp1, has_mp2, featv
 ORBmatcher.SearchByProjectionReloc = SearchByProjectionReloc
 ORBmatcher.SearchByProjectionSim3 = SearchByProjectionSim3
 ORBmatcher.Fuse = Fuse
+ORBmatcher.FuseRig = FuseRig
 ORBmatcher.SearchBySim3 = SearchBySim3
 ORBmatcher.SearchForInitialization = SearchForInitialization
 ORBmatcher.SearchForTriangulation = SearchForTriangulation

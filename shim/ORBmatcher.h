@@ -377,11 +377,35 @@ public:
   // (include/ORBmatcher.h:137-143, src/ORBmatcher.cc:1330-1452; checkReprojection = false).
   // bestIdx[i] = pKF feature MapPoint i fuses into, or -1; the Replace / AddObservation / AddMapPoint
   // bookkeeping (:1301-1318, :1436-1447) stays in the caller's loop over bestIdx.
+  // On a two-camera rig KeyFrame (NLeft != -1) the search runs on ONE camera's features: the left one's (mvKeys) or,
+  // with bRight, the right one's (mvKeysRight, descriptor rows idx + NLeft; P projected with GetRightPose /
+  // mpCamera2, :1156-1164), and bestIdx is the KeyFrame's combined index as the reference leaves it (:1270-1272).
   template <class KeyFrameT>
-  int Fuse(KeyFrameT* pKF, const ProjectedPoints& P, const float th, bool checkReprojection, std::vector<int>& bestIdx) {
+  int Fuse(KeyFrameT* pKF, const ProjectedPoints& P, const float th, bool checkReprojection, std::vector<int>& bestIdx,
+           const bool bRight = false) {
     const int n = P.size();
     bestIdx.assign(n, -1);
     if (n == 0 || pKF->N == 0) return 0;
+    if (pKF->NLeft != -1) {
+      const int nl = pKF->NLeft, nr = pKF->N - pKF->NLeft, nn = bRight ? nr : nl;
+      if (nn == 0) return 0;
+      std::vector<uint8_t> bound(nn, 0);
+      cuorb_frame_view fv;
+      fv.n = nn;
+      fv.keys_un = (const cuorb_keypoint*)(bRight ? pKF->mvKeysRight.data() : pKF->mvKeys.data());
+      fv.descriptors = contiguous(pKF->mDescriptors) + (bRight ? (size_t)nl * 32 : 0);
+      fv.u_right = nullptr;                                        // a rig KeyFrame's mvuRight is all -1 (src/Frame.cc:1313)
+      fv.bound_with_obs = bound.data();
+      fv.min_x = pKF->mnMinX; fv.min_y = pKF->mnMinY; fv.max_x = pKF->mnMaxX; fv.max_y = pKF->mnMaxY;
+      fv.grid_w_inv = pKF->mfGridElementWidthInv; fv.grid_h_inv = pKF->mfGridElementHeightInv;
+      fv.mb = pKF->mb; fv.mbf = pKF->mbf;
+      fv.nlevels = (int)pKF->mvScaleFactors.size(); fv.scale_factors = pKF->mvScaleFactors.data();
+      const int r = cuorb_fuse(device_, &fv, pKF->mvInvLevelSigma2.data(), n, P.desc.data(), P.u.data(), P.v.data(), P.ur.data(),
+                               P.level.data(), P.active.data(), th, checkReprojection ? 1 : 0, bestIdx.data());
+      if (r < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("Fuse (rig, libcuorb): ") + cuorb_last_error(), 0);
+      if (bRight) for (int i = 0; i < n; i++) if (bestIdx[i] >= 0) bestIdx[i] += nl;
+      return r;
+    }
     std::vector<uint8_t> bound(pKF->N, 0);
     const cuorb_frame_view fv = view_of(*pKF, bound);
     const int r = cuorb_fuse(device_, &fv, pKF->mvInvLevelSigma2.data(), n, P.desc.data(), P.u.data(), P.v.data(), P.ur.data(),

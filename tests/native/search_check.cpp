@@ -16,7 +16,7 @@ struct MiniPoint { int id; };
 
 struct MiniKF {  // members of Frame / KeyFrame the searches read (include/Frame.h, include/KeyFrame.h)
   int N = 0, Nleft = -1, NLeft = -1;
-  std::vector<cv::KeyPoint> mvKeysUn;
+  std::vector<cv::KeyPoint> mvKeysUn, mvKeys, mvKeysRight;   // mvKeys / mvKeysRight: only read for rig frames (NLeft != -1)
   cv::Mat mDescriptors;
   std::vector<float> mvuRight, mvScaleFactors, mvLevelSigma2, mvInvLevelSigma2;
   float mnMinX = 0, mnMinY = 0, mnMaxX = 0, mnMaxY = 0, mfGridElementWidthInv = 0, mfGridElementHeightInv = 0, mb = 0.1f, mbf = 40.f;

@@ -109,3 +109,25 @@ def test_search_by_bow_rig(seed, tie_heavy, ratio, ori):
         (kl, kr, fl, fr), keep = bow_rig_views(c, nleft1, nleft2)
         rn, rml, rmr = rp.search_by_bow_rig(kl, kr, h1, c["fv1"], fl, fr, c["fv2"], ratio, ori)
         assert rn == n and (rml == ml).all() and (rmr == mr).all()
+
+
+@pytest.mark.parametrize("right,seed,th", [(0, 3, 3.0), (1, 4, 3.0)])
+def test_fuse_on_rig_keyframe(rv, right, seed, th):
+    """Fuse(pKF, vpMapPoints, th, bRight) on a rig KeyFrame through the mirror (cuorb_fuse on the chosen camera's view,
+    NLeft added to the index) against the reference's own function."""
+    from orbslam3_cpp_fork_b200 import ORBmatcher
+    from tests.ref_search_cases import fuse_depths, in_image
+    from tests.search_cases import point_queries
+    sf = rv["sf"]
+    inv_sigma2 = (np.float32(1.0) / (sf * sf)).astype(np.float32)
+    k, d = (rv["k2"], rv["d2"]) if right else (rv["k1"], rv["d1"])
+    q = point_queries(k, d, sf, 3000, seed, jitter=3.0)
+    z, ur = fuse_depths(q, 40.0, seed)
+    n, best = ORBmatcher().FuseRig(_rig(rv), bool(right), inv_sigma2, q["desc"], q["u"], q["v"], ur, q["level"],
+                                   q["active"] & in_image(q["u"], q["v"]), th, True)
+    hit = best[best >= 0]
+    assert n > 300 and ((hit >= len(rv["k1"])).all() if right else (hit < len(rv["k1"])).all())
+    if rp.available():
+        fvl, fvr, keep = frame_views(rv)
+        rn, rbest = rp.fuse_rig(fvl, fvr, right, q["desc"], q["u"], q["v"], z, q["level"], q["active"], th)
+        assert rn == n and (rbest == best).all()

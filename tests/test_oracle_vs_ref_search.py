@@ -152,3 +152,22 @@ def test_search_by_bow_rig_equals_reference(seed, tie_heavy, ratio, ori):
     assert rn == n and (rml == ml).all() and (rmr == mr).all()
     assert (ml >= 0).sum() > 10 and (mr >= 0).sum() > 10 and ((ml >= 0) & (mr >= 0)).sum() > 0
     assert (ml[ml >= 0] < nleft2).all() and (mr[mr >= 0] >= nleft2).all()
+
+
+@pytest.mark.parametrize("right,seed,th", [(0, 3, 3.0), (1, 4, 3.0), (1, 5, 4.0)])
+def test_fuse_on_rig_keyframe_equals_reference(right, seed, th):
+    """Fuse(pKF, vpMapPoints, th, bRight) on a two-camera rig KeyFrame (src/ORBmatcher.cc:1156-1164, :1236, :1270-1272) is
+    the flat search on the chosen camera's features (no mvuRight: only the 5.99 gate) plus NLeft on the index."""
+    from tests.rig_cases import W as RW, H as RH, frame_views, rig_views
+    rv = rig_views(7)
+    sf = rv["sf"]
+    inv_sigma2 = (np.float32(1.0) / (sf * sf)).astype(np.float32)
+    k, d = (rv["k2"], rv["d2"]) if right else (rv["k1"], rv["d1"])
+    q = point_queries(k, d, sf, 600, seed)
+    z, ur = fuse_depths(q, 40.0, seed)
+    fv, keep = op.make_frame_view(k, d, None, None, RW, RH, sf, mb=0.1, mbf=40.0)
+    n, best = op.fuse(fv, inv_sigma2, q["desc"], q["u"], q["v"], ur, q["level"], q["active"] & in_image(q["u"], q["v"]), th, True)
+    fvl, fvr, kk = frame_views(rv)
+    rn, rbest = rp.fuse_rig(fvl, fvr, right, q["desc"], q["u"], q["v"], z, q["level"], q["active"], th)
+    off = len(rv["k1"]) if right else 0
+    assert rn == n and (rbest == np.where(best >= 0, best + off, -1)).all() and n > 100
