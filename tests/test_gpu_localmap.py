@@ -133,3 +133,22 @@ def test_localmap_processing_order_and_in_view(fr):
     if rp.available():
         r_in, r_n, r_best = localmap_expected(cp, k, d, sf, rp.is_in_frustum, rp.search_by_projection, 1.0, False, 30.0, 0.8)
         assert n_in == r_in and n == r_n and (best == r_best).all()
+
+
+def test_localmap_empty_frame_and_inactive_slots(fr):
+    from orbslam3_cpp_fork_b200 import LocalMap
+    from orbslam3_cpp_fork_b200.matcher import Frame
+    k, d, sf = fr
+    c = localmap_case(k, d, sf, 3000, 9)
+    m = LocalMap(5000)
+    _fill(m, c)
+    empty = Frame(k[:0], d[:0], sf, W, H, mb=0.1, mbf=c["mbf"])
+    n, n_in, mp, ft, best, inv = m.search(_cam(c), empty, [], 0.5, 1.0, False, 30.0, 0.8, want_in_view=True)
+    f = op.is_in_frustum(c["cam"], c["P"], c["N"], c["min_d"], c["max_d"], 0.5)
+    want = (f["in_view"] > 0) & (c["bad"] == 0)
+    assert n == 0 and n_in == want.sum() and (inv == want).all() and (best == -1).all()     # isInFrustum still runs
+    # slots beyond the written range and out-of-range slots in `order` count as bad points
+    order = np.array([0, 1, 4999, 2, -7, 3, 6000], np.int32)
+    n, n_in, mp, ft, best, inv = m.search(_cam(c), _frame(k, d, sf, c), [], 0.5, 1.0, False, 30.0, 0.8, order=order, want_in_view=True)
+    assert (inv[[2, 4, 6]] == 0).all() and (best[[2, 4, 6]] == -1).all()
+    assert (inv[[0, 1, 3, 5]] == want[[0, 1, 2, 3]]).all()

@@ -131,3 +131,24 @@ def test_fuse_on_rig_keyframe(rv, right, seed, th):
         fvl, fvr, keep = frame_views(rv)
         rn, rbest = rp.fuse_rig(fvl, fvr, right, q["desc"], q["u"], q["v"], z, q["level"], q["active"], th)
         assert rn == n and (rbest == best).all()
+
+
+def test_rig_one_camera_empty(rv):
+    """A rig frame whose right camera found no features: the left part still runs, nothing is cross-bound."""
+    from orbslam3_cpp_fork_b200 import ORBmatcher
+    from orbslam3_cpp_fork_b200.matcher import Frame, RigFrame
+    L = Frame(rv["k1"], rv["d1"], rv["sf"], W, H, mb=0.1, mbf=40.0)
+    R = Frame(rv["k2"][:0], rv["d2"][:0], rv["sf"], W, H, mb=0.1, mbf=40.0)
+    F = RigFrame(L, R, np.full(len(rv["k1"]), -1, np.int32), np.zeros(0, np.int32))
+    q = rig_mappoints(rv, 4000, 2)
+    args = [q[k] for k in ("desc", "px", "py", "level", "view_cos", "pxr", "pyr", "level_r", "view_cos_r", "depth", "flags")]
+    n, bl, br = ORBmatcher(0.8, True).SearchByProjectionRig(F, *args, 1.0, False, 40.0)
+    assert (br == -1).all() and n == (bl >= 0).sum() and n > 100
+    # the pinhole search on the same left features, without the mvuRight gate, gives the same left matches as long as no
+    # MapPoint's left part is skipped... which only the rig's right part could cause: compare directly
+    fl = (q["flags"] & ~np.uint8(8)).astype(np.uint8)
+    from orbslam3_cpp_fork_b200 import MapPointSoA
+    mps = MapPointSoA(q["desc"], q["px"], q["py"], q["pxr"], q["level"], q["view_cos"], q["depth"], (fl & 1) > 0, (fl & 2) > 0, (fl & 4) > 0)
+    L2 = Frame(rv["k1"], rv["d1"], rv["sf"], W, H, mb=0.1, mbf=40.0)
+    n2, best = ORBmatcher(0.8, True).SearchByProjection(L2, mps, 1.0, False, 40.0)
+    assert n2 == n and (best == bl).all()
