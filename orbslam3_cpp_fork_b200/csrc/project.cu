@@ -401,8 +401,8 @@ int cuorb_search_by_projection_frame_rig(int device, const cuorb_frame_view* lef
                                          float th, int forward, int backward, int check_orientation,
                                          int32_t* best_l_out, int32_t* best_r_out, int32_t* rot_bin_l_out,
                                          int32_t* rot_bin_r_out, int32_t* keep_bins_out) {
-  if (!left || !right || !left->keys_un || !right->keys_un || !left->descriptors || !right->descriptors ||
-      !left->scale_factors || !right->scale_factors || n_last < 0 || !keep_bins_out ||
+  if (!left || !right || (left->n > 0 && (!left->keys_un || !left->descriptors)) || (right->n > 0 && (!right->keys_un || !right->descriptors)) ||
+      left->n < 0 || right->n < 0 || !left->scale_factors || !right->scale_factors || n_last < 0 || !keep_bins_out ||
       (n_last && (!last_desc || !u || !v || !inv_z || !ur || !vr || !last_octave || !last_angle || !flags || !best_l_out ||
                   !best_r_out || !rot_bin_l_out || !rot_bin_r_out))) {
     set_error("cuorb_search_by_projection_frame_rig: null argument");
@@ -551,7 +551,7 @@ int cuorb_localmap_search(cuorb_localmap* m, const cuorb_frustum_camera* cam, co
                           const int32_t* order, int n_skip, const int32_t* skip_pos, float viewing_cos_limit, float th,
                           int far_points, float th_far_points, float nn_ratio, int32_t* best_idx_out, uint8_t* in_view_out,
                           int match_capacity, int32_t* match_pos_out, int32_t* match_feature_out, int32_t* n_in_view_out) {
-  if (!m || !cam || !frame || !frame->keys_un || !frame->descriptors || !frame->scale_factors || n_skip < 0 ||
+  if (!m || !cam || !frame || frame->n < 0 || (frame->n > 0 && (!frame->keys_un || !frame->descriptors)) || !frame->scale_factors || n_skip < 0 ||
       (n_skip && !skip_pos) || match_capacity < 0 || (match_capacity && (!match_pos_out || !match_feature_out)) ||
       n_order < 0 || (order && n_order > m->capacity)) {
     set_error("cuorb_localmap_search: bad argument");

@@ -183,8 +183,8 @@ extern "C" int cuorb_search_by_projection_rig(int device, const cuorb_frame_view
                                               float th_far_points, float nn_ratio, int32_t* best_l_out,
                                               int32_t* best_r_out) {
   const int m = n_mappoints;
-  if (!left || !right || !left->keys_un || !right->keys_un || !left->descriptors || !right->descriptors ||
-      !left->scale_factors || !right->scale_factors || m < 0 || (left->n && !left_to_right) || (right->n && !right_to_left) ||
+  if (!left || !right || (left->n > 0 && (!left->keys_un || !left->descriptors)) || (right->n > 0 && (!right->keys_un || !right->descriptors)) ||
+      left->n < 0 || right->n < 0 || !left->scale_factors || !right->scale_factors || m < 0 || (left->n && !left_to_right) || (right->n && !right_to_left) ||
       (m && (!mp_desc || !proj_x || !proj_y || !level || !view_cos || !proj_xr || !proj_yr || !level_r || !view_cos_r ||
              !depth || !flags || !best_l_out || !best_r_out))) {
     set_error("cuorb_search_by_projection_rig: null argument");
