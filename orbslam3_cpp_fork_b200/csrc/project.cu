@@ -44,6 +44,7 @@ __global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, ProjQuery Q,
                                                     int* __restrict__ binder_next,
                                                     int* __restrict__ result, int* __restrict__ changed,
                                                     const unsigned* __restrict__ dirty) {
+  pdl_enter();
   const int i = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (i >= Q.n) return;
   int res = -1;
@@ -167,10 +168,15 @@ __global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, ProjQuery Q,
 }
 
 // grid: ceil(n/256): one bit per grid cell (row-major, 64 columns = 2 words per row) that holds a feature whose
-// binder differs between two consecutive rounds
-__global__ void k_dirty_cells(ProjFrame F, const int* __restrict__ a, const int* __restrict__ b, unsigned* __restrict__ dirty) {
+// binder differs between two consecutive rounds (a = last round's table, b = the one before); b is then reset for
+// the coming round to fill (one launch instead of a compare and a fill)
+__global__ void k_dirty_cells(ProjFrame F, const int* __restrict__ a, int* __restrict__ b, unsigned* __restrict__ dirty) {
+  pdl_enter();
   const int f = blockIdx.x * blockDim.x + threadIdx.x;
-  if (f >= F.n || a[f] == b[f]) return;
+  if (f >= F.n) return;
+  const bool changed = a[f] != b[f];
+  b[f] = NO_BINDER;
+  if (!changed) return;
   const int cx = F.cellx[f], cy = F.celly[f];
   if (cx >= 0) atomicOr(&dirty[2 * cy + (cx >> 5)], 1u << (cx & 31));
 }
@@ -201,25 +207,36 @@ static int projection_rounds(Arena& A, cudaStream_t st, const ProjFrame& F, cons
   // per block), more than the rounds it saves.  Measured at cfg4 (50k MapPoints, 5 rounds to converge): one sync
   // per round 0.556 ms per call, batches of 6 0.510 ms (scripts/ab_projection.py, profiles/r02_s9_abproj.txt).
   constexpr int ROUND_BATCH = 6;   // 2 / 3 / 4 per sync: cfg4 0.558 / 0.561 / 0.581 ms against 0.525, local map 0.339 / 0.324 / 0.365 against 0.302
+  constexpr int DIRTY_WORDS = 2 * FRAME_GRID_ROWS;
   int* flag = A.take<int>(ROUND_BATCH);
-  unsigned* dirty = A.take<unsigned>(2 * FRAME_GRID_ROWS);
-  k_fill<<<(n + 255) / 256, 256, 0, st>>>(binder[0], n, NO_BINDER);
-  k_fill<<<(m + 255) / 256, 256, 0, st>>>(result, m, -2);
-  count_launch(2);
+  unsigned* dirty = A.take<unsigned>(ROUND_BATCH * DIRTY_WORDS);   // one bitmap per round of a batch: cleared with one memset
+  {
+    PdlPause plain;
+    k_fill<<<(n + 255) / 256, 256, 0, st>>>(binder[0], n, NO_BINDER);
+    k_fill<<<(m + 255) / 256, 256, 0, st>>>(result, m, -2);
+    count_launch(2);
+  }
+  // The rounds are chains of kernels of a few microseconds each (a table pass over the frame's features, then the
+  // warp-per-point round), so they are launched as programmatic dependents (common.cuh): every kernel starts with
+  // pdl_enter() and nothing but kernels sits between them inside a batch.
+  struct Chain { bool saved; Chain() : saved(t_pdl) { t_pdl = true; } ~Chain() { t_pdl = saved; } } chain;
   int rounds = 0;
   for (bool converged = false; !converged;) {
     if (rounds > m + 2) { set_error("projection search did not converge"); return CUORB_E_CUDA; }
     CUORB_CUDA_TRY(cudaMemsetAsync(flag, 0, ROUND_BATCH * sizeof(int), st));
+    CUORB_CUDA_TRY(cudaMemsetAsync(dirty, 0, ROUND_BATCH * DIRTY_WORDS * sizeof(unsigned), st));
     for (int k = 0; k < ROUND_BATCH; k++, rounds++) {
       int* prev = binder[rounds & 1];
       int* next = binder[(rounds + 1) & 1];
-      if (rounds > 0) {   // cells whose features changed binder between the last two rounds (next still holds round-2's table)
-        CUORB_CUDA_TRY(cudaMemsetAsync(dirty, 0, 2 * FRAME_GRID_ROWS * sizeof(unsigned), st));
-        k_dirty_cells<<<(n + 255) / 256, 256, 0, st>>>(F, prev, next, dirty);
-        count_launch();
-      }
-      k_fill<<<(n + 255) / 256, 256, 0, st>>>(next, n, NO_BINDER);
-      k_proj_round<<<(m + 7) / 8, 256, 0, st>>>(F, Q, prev, next, result, flag + k, rounds > 0 ? dirty : nullptr);
+      unsigned* dk = dirty + k * DIRTY_WORDS;
+      t_pdl = k != 0;   // the batch's first kernel follows two memsets: plain stream order
+      if (rounds > 0)   // cells whose features changed binder between the last two rounds (next still holds round-2's table)
+        launch_k(k_dirty_cells, dim3((n + 255) / 256), dim3(256), 0, st, F, (const int*)prev, next, dk);
+      else
+        launch_k(k_fill, dim3((n + 255) / 256), dim3(256), 0, st, next, n, NO_BINDER);
+      t_pdl = true;
+      launch_k(k_proj_round, dim3((m + 7) / 8), dim3(256), 0, st, F, Q, (const int*)prev, next, result, flag + k,
+               rounds > 0 ? (const unsigned*)dk : (const unsigned*)nullptr);
       count_launch(2);
     }
     int h_flag[ROUND_BATCH];

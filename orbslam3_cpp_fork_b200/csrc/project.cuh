@@ -36,6 +36,7 @@ __device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, cons
 }
 
 static __global__ void k_fill(int* p, int n, int v) {
+  pdl_enter();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) p[i] = v;
 }
