@@ -4,6 +4,7 @@
 #include <stdint.h>
 
 #include <atomic>
+#include <cstdlib>
 #include <string>
 #include <vector>
 
@@ -103,6 +104,8 @@ __device__ __forceinline__ void pdl_enter() {
 }
 #endif
 extern thread_local bool t_pdl;
+// CUORB_PDL=0 turns every dependent-launch chain of the library into plain stream order (A/B and test hook)
+inline bool pdl_allowed() { static const bool on = []() { const char* v = getenv("CUORB_PDL"); return !v || atoi(v) != 0; }(); return on; }
 // A kernel whose predecessor in the stream is not a kernel of the chain (a copy, a memset, a cross-stream event wait)
 // is launched with plain stream ordering: the attribute is only meant for kernel-after-kernel edges.
 struct PdlPause { bool saved; PdlPause() : saved(t_pdl) { t_pdl = false; } ~PdlPause() { t_pdl = saved; } };

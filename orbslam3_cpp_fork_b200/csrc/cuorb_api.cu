@@ -497,15 +497,13 @@ static int check_flags(cuorb_extractor* e) {
 
 extern "C" {
 
-static bool pdl_enabled() { static const bool on = []() { const char* v = getenv("CUORB_PDL"); return !v || atoi(v) != 0; }(); return on; }
-
 // enqueue pyramid .. describe on device-resident gray planes (the H2D stage event is the caller's)
 static int enqueue_pipeline(cuorb_extractor* e, int n_images, const uint8_t* dimgs, int width, int height,
                             size_t dstride, size_t dimg_stride, int lap0, int lap1) {
   cudaStream_t st = e->stream;
   const bool prof = e->profiling;
   // one or two images: the kernels are a few microseconds each, launch them as programmatic dependents (common.cuh)
-  struct PdlScope { PdlScope(bool on) { ::cuorb::t_pdl = on; } ~PdlScope() { ::cuorb::t_pdl = false; } } pdl_scope(n_images <= 2 && !prof && pdl_enabled());
+  struct PdlScope { PdlScope(bool on) { ::cuorb::t_pdl = on; } ~PdlScope() { ::cuorb::t_pdl = false; } } pdl_scope(n_images <= 2 && !prof && pdl_allowed());
   CUORB_CUDA_TRY(cudaMemsetAsync(e->d_cand_count, 0, sizeof(int) * (size_t)n_images * e->g.nlevels, st));
   CUORB_CUDA_TRY(cudaMemsetAsync(e->d_flags, 0, 2 * sizeof(int), st));  // [0] overflow flags, [1] FAST work counter
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_PYRAMID], st);

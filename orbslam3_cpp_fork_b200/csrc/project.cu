@@ -219,7 +219,8 @@ static int projection_rounds(Arena& A, cudaStream_t st, const ProjFrame& F, cons
   // The rounds are chains of kernels of a few microseconds each (a table pass over the frame's features, then the
   // warp-per-point round), so they are launched as programmatic dependents (common.cuh): every kernel starts with
   // pdl_enter() and nothing but kernels sits between them inside a batch.
-  struct Chain { bool saved; Chain() : saved(t_pdl) { t_pdl = true; } ~Chain() { t_pdl = saved; } } chain;
+  const bool pdl = pdl_allowed();
+  struct Chain { bool saved; Chain(bool on) : saved(t_pdl) { t_pdl = on; } ~Chain() { t_pdl = saved; } } chain(pdl);
   int rounds = 0;
   for (bool converged = false; !converged;) {
     if (rounds > m + 2) { set_error("projection search did not converge"); return CUORB_E_CUDA; }
@@ -229,12 +230,12 @@ static int projection_rounds(Arena& A, cudaStream_t st, const ProjFrame& F, cons
       int* prev = binder[rounds & 1];
       int* next = binder[(rounds + 1) & 1];
       unsigned* dk = dirty + k * DIRTY_WORDS;
-      t_pdl = k != 0;   // the batch's first kernel follows two memsets: plain stream order
+      t_pdl = pdl && k != 0;   // the batch's first kernel follows two memsets: plain stream order
       if (rounds > 0)   // cells whose features changed binder between the last two rounds (next still holds round-2's table)
         launch_k(k_dirty_cells, dim3((n + 255) / 256), dim3(256), 0, st, F, (const int*)prev, next, dk);
       else
         launch_k(k_fill, dim3((n + 255) / 256), dim3(256), 0, st, next, n, NO_BINDER);
-      t_pdl = true;
+      t_pdl = pdl;
       launch_k(k_proj_round, dim3((m + 7) / 8), dim3(256), 0, st, F, Q, (const int*)prev, next, result, flag + k,
                rounds > 0 ? (const unsigned*)dk : (const unsigned*)nullptr);
       count_launch(2);

@@ -30,6 +30,7 @@ __device__ __forceinline__ int row_bucket(float y, int nb) {
 
 // grid: n_img, block 256
 __global__ void __launch_bounds__(256) k_stereo_rows(StereoArgs A) {
+  pdl_enter();
   __shared__ int s_cnt[STEREO_MAX_BUCKETS + 1];
   __shared__ int s_warp[8];
   const ExtractorGeom* dg = A.dgL;
@@ -76,6 +77,7 @@ __global__ void __launch_bounds__(256) k_stereo_rows(StereoArgs A) {
 
 // grid: (ceil(kp_cap/8), n_img), block 256
 __global__ void __launch_bounds__(256, 6) k_stereo_match(StereoArgs A, int band) {
+  pdl_enter();
   const ExtractorGeom* dg = A.dgL;
   const int img = blockIdx.y, lane = threadIdx.x & 31;
   const int iL = blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -208,6 +210,7 @@ __global__ void __launch_bounds__(256, 6) k_stereo_match(StereoArgs A, int band)
 
 // grid: n_img, block 256
 __global__ void __launch_bounds__(256) k_stereo_outliers(StereoArgs A) {
+  pdl_enter();
   __shared__ int h1[256], h2[128];
   __shared__ int s_cnt, s_b1, s_rem, s_med;
   const int img = blockIdx.x, tid = threadIdx.x;
@@ -254,9 +257,15 @@ __global__ void __launch_bounds__(256) k_stereo_outliers(StereoArgs A) {
 void launch_stereo(const ExtractorGeom& g, const StereoArgs& a, cudaStream_t st) {
   // a right keypoint can register in rows up to ceil(2*scale_max)+1 away from its own
   const int band = (int)ceilf(2.0f * g.lv[g.nlevels - 1].scale) + 2;
-  k_stereo_rows<<<a.n_img, 256, 0, st>>>(a);
-  k_stereo_match<<<dim3((g.kp_cap + 7) / 8, a.n_img), 256, 0, st>>>(a, band);
-  k_stereo_outliers<<<a.n_img, 256, 0, st>>>(a);
+  // a one- or two-pair call is three kernels of a few microseconds each: dependent launches (common.cuh); the first
+  // one follows a cross-stream event wait and keeps plain stream order
+  struct Chain { bool saved; Chain(bool on) : saved(t_pdl) { t_pdl = on; } ~Chain() { t_pdl = saved; } } chain(a.n_img <= 2 && pdl_allowed());
+  {
+    PdlPause first;
+    launch_k(k_stereo_rows, dim3(a.n_img), dim3(256), 0, st, a);
+  }
+  launch_k(k_stereo_match, dim3((g.kp_cap + 7) / 8, a.n_img), dim3(256), 0, st, a, band);
+  launch_k(k_stereo_outliers, dim3(a.n_img), dim3(256), 0, st, a);
   count_launch(3);
 }
 
