@@ -137,7 +137,8 @@ void build_pyr_plan(const ExtractorGeom& g, const std::vector<uint4>& wt, const 
                     const std::vector<ResizeTap>& ytab, PyrPlan* plan);
 void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8_t* imgs, int w, int h,
                     size_t stride, size_t image_stride, int n_img, uint8_t* pyr, const ResizeTap* xtab,
-                    const ResizeTap* ytab, const uint4* wtab, const int* wtab_off, const PyrPlan* plan, cudaStream_t st);
+                    const ResizeTap* ytab, const uint4* wtab, const int* wtab_off, const PyrPlan* plan, cudaStream_t st,
+                    int* zero_counts = nullptr, int* zero_flags = nullptr);   // non-null: level 0 clears them (small batches)
 void build_blur_tiles(const ExtractorGeom& g, std::vector<int4>& tiles);
 void launch_blur(const ExtractorGeom* g, const ExtractorGeom* dg, int n_img, const int4* tiles,
                  int n_tiles, const uint8_t* pyr, uint8_t* blur, cudaStream_t st);

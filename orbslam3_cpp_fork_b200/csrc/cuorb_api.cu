@@ -504,11 +504,17 @@ static int enqueue_pipeline(cuorb_extractor* e, int n_images, const uint8_t* dim
   const bool prof = e->profiling;
   // one or two images: the kernels are a few microseconds each, launch them as programmatic dependents (common.cuh)
   struct PdlScope { PdlScope(bool on) { ::cuorb::t_pdl = on; } ~PdlScope() { ::cuorb::t_pdl = false; } } pdl_scope(n_images <= 2 && !prof && pdl_allowed());
-  CUORB_CUDA_TRY(cudaMemsetAsync(e->d_cand_count, 0, sizeof(int) * (size_t)n_images * e->g.nlevels, st));
-  CUORB_CUDA_TRY(cudaMemsetAsync(e->d_flags, 0, 2 * sizeof(int), st));  // [0] overflow flags, [1] FAST work counter
+  // [0] overflow flags, [1] FAST work counter; per-level candidate counters.  One or two images: cleared by the
+  // pyramid's first kernel (two memsets in front of the chain cost 8 us of a 130 us call)
+  const bool clear_in_kernel = n_images <= 2;
+  if (!clear_in_kernel) {
+    CUORB_CUDA_TRY(cudaMemsetAsync(e->d_cand_count, 0, sizeof(int) * (size_t)n_images * e->g.nlevels, st));
+    CUORB_CUDA_TRY(cudaMemsetAsync(e->d_flags, 0, 2 * sizeof(int), st));
+  }
   if (prof) cudaEventRecord(e->ev_stage[CUORB_STAGE_PYRAMID], st);
   launch_pyramid(e->g, e->d_geom, dimgs, width, height, dstride, dimg_stride, n_images, e->d_pyr, e->d_xtab, e->d_ytab,
-                 e->d_wtab, e->wtab_off, e->pyr_plan, st);
+                 e->d_wtab, e->wtab_off, e->pyr_plan, st, clear_in_kernel ? e->d_cand_count : nullptr,
+                 clear_in_kernel ? e->d_flags : nullptr);
   // FAST (integer-ALU bound, 20 warps per SM) and the blur (FMA pipe + loads) both depend only on the
   // pyramid: outside profiling runs the blur goes to the side stream, after FAST in launch order so
   // FAST's CTAs get their shared memory first and blur CTAs fill the remaining warp slots of each SM

@@ -36,8 +36,15 @@ template <int RS>
 __global__ void __launch_bounds__(256) k_pyr_level0(const ExtractorGeom* __restrict__ dg,
                                                     const uint8_t* __restrict__ imgs, size_t stride,
                                                     size_t image_stride, uint8_t* __restrict__ pyr,
-                                                    int aligned) {
+                                                    int aligned, int* __restrict__ zero_counts, int n_counts,
+                                                    int* __restrict__ zero_flags) {
   pdl_enter();
+  // single-frame calls: the per-level candidate counters, the overflow flags and FAST's work counter are cleared
+  // here, by the first kernel of the chain, instead of by two memsets in front of it (8 us of a 130 us call)
+  if (zero_counts && blockIdx.x == 0 && blockIdx.y == 0) {
+    if ((int)threadIdx.x < n_counts) zero_counts[blockIdx.z * n_counts + threadIdx.x] = 0;
+    if (blockIdx.z == 0 && threadIdx.x < 2) zero_flags[threadIdx.x] = 0;
+  }
   const LevelGeom& L = dg->lv[0];
   const int word = blockIdx.x * blockDim.x + threadIdx.x;
   if (word * 4 >= L.pitch) return;
@@ -424,7 +431,7 @@ void build_resize_words(const ExtractorGeom& g, const std::vector<ResizeTap>& xt
 void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8_t* imgs, int, int,
                     size_t stride, size_t image_stride, int n_img, uint8_t* pyr,
                     const ResizeTap* xtab, const ResizeTap* ytab, const uint4* wtab, const int* wtab_off,
-                    const PyrPlan* plan, cudaStream_t st) {
+                    const PyrPlan* plan, cudaStream_t st, int* zero_counts, int* zero_flags) {
   const int aligned = (((uintptr_t)imgs | stride | image_stride) & 3) == 0;
   for (int l = 0; l < g.nlevels; l++) {
     const LevelGeom& L = g.lv[l];
@@ -436,11 +443,13 @@ void launch_pyramid(const ExtractorGeom& g, const ExtractorGeom* dg, const uint8
       // 16-row strips for large batches; when that would leave most of the 148 SMs without a CTA (a handful of
       // images) the strips are 4 rows and the kernel's critical path - one thread's row loop - is a quarter as long
       const int nbx = (words + tx - 1) / tx;
-      PdlPause first_of_chain;   // follows the frame upload and two memsets
+      PdlPause first_of_chain;   // follows the frame upload (and, for large batches, two memsets)
       if ((int)grid.y * nbx * n_img < PYR_MIN_CTAS)
-        launch_k(k_pyr_level0<4>, dim3(nbx, (L.h + 3) / 4, n_img), dim3(tx), 0, st, dg, imgs, stride, image_stride, pyr, aligned);
+        launch_k(k_pyr_level0<4>, dim3(nbx, (L.h + 3) / 4, n_img), dim3(tx), 0, st, dg, imgs, stride, image_stride, pyr, aligned, zero_counts,
+                 g.nlevels, zero_flags);
       else
-        launch_k(k_pyr_level0<PYR_RS>, dim3(nbx, grid.y, n_img), dim3(tx), 0, st, dg, imgs, stride, image_stride, pyr, aligned);
+        launch_k(k_pyr_level0<PYR_RS>, dim3(nbx, grid.y, n_img), dim3(tx), 0, st, dg, imgs, stride, image_stride, pyr, aligned, zero_counts,
+                 g.nlevels, zero_flags);
     } else {
       // four adjacent output columns span 3*scale + 2 source bytes (+3 for alignment): 12 bytes up to scale 2
       const double sx = (double)g.lv[l - 1].w / L.w;
