@@ -436,10 +436,35 @@ def localmap_track(local, with_cpu=True, M=50000, frame=None):
     for _ in range(60):
         t0 = time.perf_counter(); call(); ts.append(time.perf_counter() - t0)
     st = _stats(ts)
+    # the same call with the Frame's features left on the device (cuorb_localmap_search_resident): grid and SoA built there
+    import torch
+    dev = torch.device("cuda", local)
+    dk = torch.from_numpy(np.ascontiguousarray(k).view(np.uint8).copy()).to(dev); dd = torch.from_numpy(np.ascontiguousarray(d)).to(dev)
+    du = torch.from_numpy(np.ascontiguousarray(c["u_right"], np.float32)).to(dev)
+    torch.cuda.synchronize(dev)
+    fvr = _lib.FrameView.from_buffer_copy(bytes(fvv))
+    fvr.keys_un = dk.data_ptr(); fvr.descriptors = dd.data_ptr(); fvr.u_right = du.data_ptr()
+    mp_r = np.zeros(cap, np.int32); ft_r = np.zeros(cap, np.int32); nin_r = C.c_int32(0)
+
+    def call_resident():
+        return _lib.check(L_.cuorb_localmap_search_resident(m._h, C.byref(cam), C.byref(fvr), None, None, None, None, 0, None,
+                                                            len(skip), _lib.ptr(skip), 0.5, 1.0, 0, 50.0, 0.8, None, None, cap,
+                                                            _lib.ptr(mp_r), _lib.ptr(ft_r), C.byref(nin_r)))
+    n_r = call_resident()
+    for _ in range(5):
+        call_resident()
+    ts_r = []
+    for _ in range(60):
+        t0 = time.perf_counter(); call_resident(); ts_r.append(time.perf_counter() - t0)
     out = {"workload": f"isInFrustum + SearchByProjection over a resident local map of {M} MapPoints, frame 752x480 / {len(k)} "
                        "keypoints, th 1, nnratio 0.8; wall clock around cuorb_localmap_search, (point, feature) pairs out",
            "points_in_view": int(nin.value), "matches": int(n), "ms_per_call": st,
-           "mappoints_per_s": M / (st["median_ms"] * 1e-3), "one_time_map_upload_ms": 1e3 * t_upload}
+           "mappoints_per_s": M / (st["median_ms"] * 1e-3), "one_time_map_upload_ms": 1e3 * t_upload,
+           "frame_left_on_device": {"ms_per_call": _stats(ts_r),
+                                    "equal_to_host_frame_call": bool(n_r == n and nin_r.value == nin.value and
+                                                                     (mp_r[:n] == mp[:n]).all() and (ft_r[:n] == ft[:n]).all()),
+                                    "note": "cuorb_localmap_search_resident: keypoints / descriptors / uRight read in place, "
+                                            "PosInGrid + cell CSR built by one kernel; only pose, skip list and bound flags go up"}}
     if with_cpu:
         t0 = time.perf_counter()
         o_in, o_n, o_best = localmap_expected(c, k, d, sf, op.is_in_frustum, op.search_by_projection, 1.0, False, 50.0, 0.8)

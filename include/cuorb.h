@@ -134,6 +134,14 @@ void* cuorb_extractor_stream(cuorb_extractor* ext);
 int cuorb_extractor_pyramid(const cuorb_extractor* ext, int image_index, int level,
                             const uint8_t** dev_ptr, int* width, int* height, size_t* stride);
 
+/* The device arrays behind mvKeys / mDescriptors (and, once cuorb_stereo_match has run on this handle, mvuRight /
+ * mvDepth) of image `image_index` of the last batch, where the extractor left them: what
+ * cuorb_localmap_search_resident reads in place instead of a host round trip.  Work that reads them must be ordered
+ * after cuorb_extractor_stream(ext); they are valid until the next extract call on the handle.  The counts are the
+ * ones cuorb_extract_fetch returns.  Returns the per-image capacity of the arrays, or a negative cuorb_status. */
+int cuorb_extractor_device_features(const cuorb_extractor* ext, int image_index, const cuorb_keypoint** d_keys,
+                                    const uint8_t** d_descriptors, const float** d_u_right, const float** d_depth);
+
 /* Parity/debug downloads (synchronous).  plane: 0 = pyramid level incl. 19-px border
  * ((w+38)*(h+38) bytes, tightly packed), 1 = pyramid level without border (w*h),
  * 2 = 7x7 sigma-2 blurred level (w*h) (src/ORBextractor.cc:1103-1104).  Returns bytes written. */
@@ -419,6 +427,22 @@ int cuorb_localmap_search(cuorb_localmap* map, const cuorb_frustum_camera* cam, 
                           int far_points, float th_far_points, float nn_ratio, int32_t* best_idx_out,
                           uint8_t* in_view_out, int match_capacity, int32_t* match_pos_out, int32_t* match_feature_out,
                           int32_t* n_in_view_out);
+/* The same search on a Frame whose arrays never left the device: frame->keys_un, frame->descriptors and (optional)
+ * frame->u_right are DEVICE pointers on the map's device (cuorb_extractor_device_features), the remaining members
+ * of the view are host data as before.  Replaces, on the device, the three steps the reference runs between
+ * ORBextractor::operator() and SearchLocalPoints: Frame::UndistortKeyPoints (src/Frame.cc:886-913; K4 / dist5 as for
+ * cuorb_undistort_keypoints, both NULL when keys_un already holds undistorted keypoints - a rectified stereo rig),
+ * Frame::AssignFeaturesToGrid (src/Frame.cc:524-553) and the flattening of the Frame for the search.
+ * producer_stream: the cudaStream_t that wrote the device arrays (cuorb_extractor_stream(ext)); the search is ordered
+ * after it.  NULL = the arrays are already complete.  keys_un_out[frame->n] (host, optional): mvKeysUn as the search
+ * used it.  Everything else as cuorb_localmap_search; results are identical to those of that call on the same Frame. */
+int cuorb_localmap_search_resident(cuorb_localmap* map, const cuorb_frustum_camera* cam, const cuorb_frame_view* frame,
+                                   void* producer_stream, const float* K4, const float* dist5,
+                                   cuorb_keypoint* keys_un_out, int n_order, const int32_t* order, int n_skip,
+                                   const int32_t* skip_pos, float viewing_cos_limit, float th, int far_points,
+                                   float th_far_points, float nn_ratio, int32_t* best_idx_out, uint8_t* in_view_out,
+                                   int match_capacity, int32_t* match_pos_out, int32_t* match_feature_out,
+                                   int32_t* n_in_view_out);
 
 
 /* void Frame::ComputeStereoFromRGBD(const cv::Mat& imDepth) (src/Frame.cc:1115-1133): depth = CV_32F

@@ -78,6 +78,7 @@ SIGNATURES = {
     "cuorb_extractor_stream": (C.c_void_p, [C.c_void_p]),
     "cuorb_extractor_pyramid": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p),
                                           C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_size_t)]),
+    "cuorb_extractor_device_features": (C.c_int, [C.c_void_p, C.c_int] + [C.POINTER(C.c_void_p)] * 4),
     "cuorb_extractor_download_plane": (C.c_int64, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                                    C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "cuorb_extractor_download_candidates": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
@@ -111,6 +112,10 @@ SIGNATURES = {
     "cuorb_localmap_search": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(FrameView), C.c_int, C.c_void_p, C.c_int, C.c_void_p,
                                         C.c_float, C.c_float, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_int,
                                         C.c_void_p, C.c_void_p, C.c_void_p]),
+    "cuorb_localmap_search_resident": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(FrameView), C.c_void_p, C.c_void_p, C.c_void_p,
+                                                 C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_float, C.c_float,
+                                                 C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                                 C.c_void_p, C.c_void_p]),
     "cuorb_preproc_create": (C.c_void_p, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                           C.c_void_p, C.c_int]),
     "cuorb_preproc_destroy": (None, [C.c_void_p]),

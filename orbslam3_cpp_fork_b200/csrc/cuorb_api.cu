@@ -828,6 +828,20 @@ int cuorb_extractor_pyramid(const cuorb_extractor* e, int image_index, int level
   return CUORB_OK;
 }
 
+int cuorb_extractor_device_features(const cuorb_extractor* e, int image_index, const cuorb_keypoint** d_keys,
+                                    const uint8_t** d_descriptors, const float** d_u_right, const float** d_depth) {
+  if (!e || !e->have_batch || image_index < 0 || image_index >= e->n_img) {
+    set_error("cuorb_extractor_device_features: bad handle / index, or no batch extracted yet");
+    return CUORB_E_BADARG;
+  }
+  const size_t off = (size_t)image_index * e->g.kp_cap;
+  if (d_keys) *d_keys = e->d_out_kps + off;
+  if (d_descriptors) *d_descriptors = e->d_out_desc + off * 32;
+  if (d_u_right) *d_u_right = e->have_stereo ? e->d_uright + off : nullptr;
+  if (d_depth) *d_depth = e->have_stereo ? e->d_depth + off : nullptr;
+  return e->g.kp_cap;
+}
+
 int64_t cuorb_extractor_download_plane(cuorb_extractor* e, int image_index, int level, int plane,
                                        uint8_t* out, size_t out_bytes, int* width, int* height) {
   if (!e || !e->have_batch || image_index < 0 || image_index >= e->n_img || level < 0 ||

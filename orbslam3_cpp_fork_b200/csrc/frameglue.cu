@@ -11,49 +11,18 @@
 
 #include "common.cuh"
 #include "frustum.cuh"
+#include "undistort.cuh"
 
 namespace cuorb {
 void set_error(const std::string& msg);
 
 namespace {
 
-struct UndistortArgs {
-  double fx, fy, cx, cy, ifx, ify;
-  double k[12];
-};
-
 __global__ void k_undistort(const cuorb_keypoint* __restrict__ in, cuorb_keypoint* __restrict__ out, int n, const UndistortArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   cuorb_keypoint kp = in[i];
-  double x = (double)kp.x, y = (double)kp.y;
-  const double u = x, v = y;
-  x = __dmul_rn(__dsub_rn(x, a.cx), a.ifx); y = __dmul_rn(__dsub_rn(y, a.cy), a.ify);
-  const double x0 = x, y0 = y;
-  const double* k = a.k;
-  for (int j = 0; j < 5; j++) {
-    const double r2 = __dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y));
-    const double num = __dadd_rn(1.0, __dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn(__dmul_rn(k[7], r2), k[6]), r2), k[5]), r2));
-    const double den = __dadd_rn(1.0, __dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn(__dmul_rn(k[4], r2), k[1]), r2), k[0]), r2));
-    const double icdist = __ddiv_rn(num, den);
-    if (icdist < 0) { x = __dmul_rn(__dsub_rn(u, a.cx), a.ifx); y = __dmul_rn(__dsub_rn(v, a.cy), a.ify); break; }
-    // deltaX = 2*k2*x*y + k3*(r2 + 2*x*x) + k8*r2 + k9*r2*r2   (left to right)
-    double dX = __dmul_rn(__dmul_rn(__dmul_rn(2.0, k[2]), x), y);
-    dX = __dadd_rn(dX, __dmul_rn(k[3], __dadd_rn(r2, __dmul_rn(__dmul_rn(2.0, x), x))));
-    dX = __dadd_rn(dX, __dmul_rn(k[8], r2));
-    dX = __dadd_rn(dX, __dmul_rn(__dmul_rn(k[9], r2), r2));
-    // deltaY = k2*(r2 + 2*y*y) + 2*k3*x*y + k10*r2 + k11*r2*r2
-    double dY = __dmul_rn(k[2], __dadd_rn(r2, __dmul_rn(__dmul_rn(2.0, y), y)));
-    dY = __dadd_rn(dY, __dmul_rn(__dmul_rn(__dmul_rn(2.0, k[3]), x), y));
-    dY = __dadd_rn(dY, __dmul_rn(k[10], r2));
-    dY = __dadd_rn(dY, __dmul_rn(__dmul_rn(k[11], r2), r2));
-    x = __dmul_rn(__dsub_rn(x0, dX), icdist);
-    y = __dmul_rn(__dsub_rn(y0, dY), icdist);
-  }
-  const double xx = __dadd_rn(__dadd_rn(__dmul_rn(a.fx, x), __dmul_rn(0.0, y)), a.cx);
-  const double yy = __dadd_rn(__dadd_rn(__dmul_rn(0.0, x), __dmul_rn(a.fy, y)), a.cy);
-  kp.x = (float)xx;   // ww = 1 / (0*x + 0*y + 1) = 1
-  kp.y = (float)yy;
+  undistort_point(a, kp.x, kp.y);
   out[i] = kp;
 }
 
@@ -129,9 +98,7 @@ int cuorb_undistort_keypoints(int device, int n, const cuorb_keypoint* kps, cons
   if (!d) { set_error("cudaMalloc failed (undistort workspace)"); return CUORB_E_CUDA; }
   cuorb_keypoint* din = (cuorb_keypoint*)d;
   cuorb_keypoint* dout = (cuorb_keypoint*)(d + ((bytes + 255) & ~(size_t)255));
-  UndistortArgs a;
-  a.fx = K4[0]; a.fy = K4[1]; a.cx = K4[2]; a.cy = K4[3]; a.ifx = 1. / a.fx; a.ify = 1. / a.fy;
-  for (int i = 0; i < 12; i++) a.k[i] = i < 5 ? (double)dist5[i] : 0.0;
+  const UndistortArgs a = undistort_args(K4, dist5);
   cudaStream_t st = cudaStreamPerThread;
   GLUE_TRY(cudaMemcpyAsync(din, kps, bytes, cudaMemcpyHostToDevice, st));
   k_undistort<<<(n + 127) / 128, 128, 0, st>>>(din, dout, n, a);

@@ -20,6 +20,7 @@
 
 #include "frustum.cuh"
 #include "project.cuh"
+#include "undistort.cuh"
 
 namespace cuorb {
 
@@ -38,108 +39,174 @@ struct ProjQuery {
   int far_points, forward, backward;
 };
 
-// grid: ceil(n/8), block 256 (warp per query point)
-__global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, ProjQuery Q,
-                                                    const int* __restrict__ binder_prev,
-                                                    int* __restrict__ binder_next,
-                                                    int* __restrict__ result, int* __restrict__ changed,
-                                                    const unsigned* __restrict__ dirty) {
+// One in-play query point, as k_proj_begin leaves it for every later round: everything the rounds need that does not
+// change between rounds (window, radius, level range) in two 16-byte loads.
+struct __align__(16) ProjItem {
+  int      i;        // query index
+  unsigned win;      // cx0 | cx1 << 6 | cy0 << 12 | cy1 << 18 | HAS_OBS << 24 (GetFeaturesInArea cell window)
+  float    x, y;
+  float    rad;
+  float    pr;       // predicted right coordinate compared with mvuRight (mode 0: projXR, else x - mbf * invz)
+  int      min_level, max_level;
+};
+
+// Control block of one batch of rounds (device ints): dirty[k] = one bit per grid cell holding a feature whose
+// binder differs between the two rounds before round k (slot ROUND_BATCH carries over to the next batch's slot 0).
+constexpr int ROUND_BATCH = 6;   // rounds per host sync; 2 / 3 / 4: cfg4 0.558 / 0.561 / 0.581 ms against 0.525 (r02_s9)
+constexpr int DIRTY_WORDS = 2 * FRAME_GRID_ROWS;
+struct RoundCtl {
+  unsigned dirty[ROUND_BATCH + 1][DIRTY_WORDS];
+  int flag[ROUND_BATCH];     // a result changed in round k
+  int count[ROUND_BATCH];    // length of round k's work list
+  int ticket[ROUND_BATCH];   // CTAs of round k that are through (the last one makes dirty[k + 1])
+};
+
+// The per-point prologue of the three projection searches, once per call.  grid: ceil(max(m, n)/256).
+//   mode 0  SearchByProjection(F, vpMapPoints, th, bFarPoints, thFarPoints)   src/ORBmatcher.cc:38-227
+//   mode 1  SearchByProjection(CurrentFrame, LastFrame, th, bMono)            src/ORBmatcher.cc:1684-1908
+//   mode 2  its right-camera half on a rig
+// Points that can bind go to `items` (any order); every result starts at -1; both binder tables start empty.
+__global__ void k_proj_begin(ProjFrame F, ProjQuery Q, int* __restrict__ binder0, int* __restrict__ binder1,
+                             int* __restrict__ result, ProjItem* __restrict__ items, int* __restrict__ n_items) {
   pdl_enter();
-  const int i = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-  if (i >= Q.n) return;
-  int res = -1;
-  const unsigned fl = Q.flags[i];
-  bool active = (fl & CUORB_MP_IN_VIEW) != 0;
-  float x = 0, y = 0, rad = 0;
-  int minLevel = -1, maxLevel = -1;
-  if (active) {
-    x = Q.px[i]; y = Q.py[i];
-    const int lvl = Q.level[i];
-    if (Q.mode == 0) {
-      if (Q.far_points && Q.depth[i] > Q.thFar) active = false;
-      if (fl & CUORB_MP_BAD) active = false;
-      float r = ((double)Q.viewcos[i] > 0.998) ? 2.5f : 4.0f;   // RadiusByViewingCos (:229-235)
-      if ((double)Q.th != 1.0) r = __fmul_rn(r, Q.th);
-      rad = __fmul_rn(r, F.scale[lvl]);
-      minLevel = lvl - 1; maxLevel = lvl;
-    } else {
-      if (Q.mode == 1) {
-        if (Q.aux[i] < 0.f) active = false;                      // invzc < 0 (:1717)
-        if (x < F.minX || x > F.maxX || y < F.minY || y > F.maxY) active = false;
-      } else if (!Q.gate_in[i]) active = false;                  // :1812-1886: no tests of its own
-      rad = __fmul_rn(Q.th, F.scale[lvl]);
-      if (Q.forward) { minLevel = lvl; maxLevel = -1; }
-      else if (Q.backward) { minLevel = 0; maxLevel = lvl; }
-      else { minLevel = lvl - 1; maxLevel = lvl + 1; }
-    }
-  }
-  int cx0 = 0, cx1 = -1, cy0 = 0, cy1 = -1;
-  if (active) {  // GetFeaturesInArea cell window (src/Frame.cc:802-828)
-    cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, F.minX), rad), F.gwinv)));
-    cx1 = min(FRAME_GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, F.minX), rad), F.gwinv)));
-    cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, F.minY), rad), F.ghinv)));
-    cy1 = min(FRAME_GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, F.minY), rad), F.ghinv)));
-    if (cx0 >= FRAME_GRID_COLS || cx1 < 0 || cy0 >= FRAME_GRID_ROWS || cy1 < 0) active = false;
-  }
-  // Rounds after the first: a MapPoint's outcome is a function of "binder_prev[f] < i" over the features of its
-  // window, so it can only differ from the previous round's if a feature of one of the window's cells changed its
-  // binder in between.  `dirty` has one bit per grid cell holding such a feature (k_dirty_cells); a clean window
-  // keeps result[i] and only re-asserts its claim in this round's binder table.
-  if (dirty) {
-    bool hit = false;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31;
+  if (i < F.n) { binder0[i] = NO_BINDER; binder1[i] = NO_BINDER; }
+  bool active = false;
+  ProjItem it{};
+  if (i < Q.n) {
+    result[i] = -1;
+    const unsigned fl = Q.flags[i];
+    active = (fl & CUORB_MP_IN_VIEW) != 0;
     if (active) {
-      const unsigned long long cols = (cx1 >= 63 ? ~0ull : ((2ull << cx1) - 1ull)) & ~((1ull << cx0) - 1ull);
-      for (int cy = cy0 + lane; cy <= cy1; cy += 32) {
-        const unsigned long long row = ((unsigned long long)dirty[2 * cy + 1] << 32) | dirty[2 * cy];
-        hit |= (row & cols) != 0;
+      const float x = Q.px[i], y = Q.py[i];
+      const int lvl = Q.level[i];
+      const float aux = Q.aux ? Q.aux[i] : 0.f;
+      float rad;
+      int minLevel, maxLevel;
+      if (Q.mode == 0) {
+        if (Q.far_points && Q.depth[i] > Q.thFar) active = false;
+        if (fl & CUORB_MP_BAD) active = false;
+        float r = ((double)Q.viewcos[i] > 0.998) ? 2.5f : 4.0f;   // RadiusByViewingCos (:229-235)
+        if ((double)Q.th != 1.0) r = __fmul_rn(r, Q.th);
+        rad = __fmul_rn(r, F.scale[lvl]);
+        minLevel = lvl - 1; maxLevel = lvl;
+        it.pr = aux;
+      } else {
+        if (Q.mode == 1) {
+          if (aux < 0.f) active = false;                           // invzc < 0 (:1717)
+          if (x < F.minX || x > F.maxX || y < F.minY || y > F.maxY) active = false;
+        } else if (!Q.gate_in[i]) active = false;                  // :1812-1886: no tests of its own
+        rad = __fmul_rn(Q.th, F.scale[lvl]);
+        if (Q.forward) { minLevel = lvl; maxLevel = -1; }
+        else if (Q.backward) { minLevel = 0; maxLevel = lvl; }
+        else { minLevel = lvl - 1; maxLevel = lvl + 1; }
+        it.pr = __fsub_rn(x, __fmul_rn(F.mbf, aux));
       }
-    }
-    if (!__any_sync(0xffffffffu, hit)) {
-      if (lane == 0) {
-        const int r0 = result[i];
-        if (r0 >= 0 && (fl & CUORB_MP_HAS_OBS)) atomicMin(&binder_next[r0], i);
+      if (active) {  // GetFeaturesInArea cell window (src/Frame.cc:802-828)
+        const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, F.minX), rad), F.gwinv)));
+        const int cx1 = min(FRAME_GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, F.minX), rad), F.gwinv)));
+        const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, F.minY), rad), F.ghinv)));
+        const int cy1 = min(FRAME_GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, F.minY), rad), F.ghinv)));
+        if (cx0 >= FRAME_GRID_COLS || cx1 < 0 || cy0 >= FRAME_GRID_ROWS || cy1 < 0) active = false;
+        // an empty range (x or y far outside the grid) visits no cell: nothing to bind, gate_out stays 0
+        if (cx0 > cx1 || cy0 > cy1) active = false;
+        it.i = i; it.x = x; it.y = y; it.rad = rad; it.min_level = minLevel; it.max_level = maxLevel;
+        it.win = (unsigned)cx0 | ((unsigned)cx1 << 6) | ((unsigned)cy0 << 12) | ((unsigned)cy1 << 18) |
+                 ((fl & CUORB_MP_HAS_OBS) ? 1u << 24 : 0u);
       }
-      return;
     }
   }
-  if (active) {
+  const unsigned b = __ballot_sync(0xffffffffu, active);
+  if (!b) return;
+  int base = 0;
+  if (lane == __ffs(b) - 1) base = atomicAdd(n_items, __popc(b));
+  base = __shfl_sync(0xffffffffu, base, __ffs(b) - 1);
+  if (active) items[base + __popc(b & ((1u << lane) - 1u))] = it;
+}
+
+// Rounds after the first.  A point's outcome is a function of "binder_prev[f] < i" over the features of its window, so
+// it can only differ from the previous round's if a feature of one of the window's cells changed its binder in
+// between: `dirty` has one bit per such cell.  A point with a clean window keeps its result and only re-asserts its
+// claim in this round's binder table; the others form this round's work list.  grid: ceil(m/256), thread per item.
+__global__ void k_proj_select(const ProjItem* __restrict__ items, const int* __restrict__ n_items,
+                              const unsigned* __restrict__ dirty, const int* __restrict__ result,
+                              int* __restrict__ binder_next, int* __restrict__ work, int* __restrict__ count) {
+  pdl_enter();
+  const int t = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31;
+  bool hit = false;
+  if (t < *n_items) {
+    const uint2 hd = *reinterpret_cast<const uint2*>(&items[t]);   // i, win
+    const int cx0 = hd.y & 63, cx1 = (hd.y >> 6) & 63, cy0 = (hd.y >> 12) & 63, cy1 = (hd.y >> 18) & 63;
+    const unsigned long long cols = (cx1 >= 63 ? ~0ull : ((2ull << cx1) - 1ull)) & ~((1ull << cx0) - 1ull);
+    for (int cy = cy0; cy <= cy1; cy++) {
+      const unsigned long long row = ((unsigned long long)dirty[2 * cy + 1] << 32) | dirty[2 * cy];
+      hit |= (row & cols) != 0;
+    }
+    if (!hit && (hd.y >> 24)) {
+      const int r0 = result[hd.x];
+      if (r0 >= 0) atomicMin(&binder_next[r0], (int)hd.x);
+    }
+  }
+  const unsigned b = __ballot_sync(0xffffffffu, hit);
+  if (!b) return;
+  int base = 0;
+  if (lane == __ffs(b) - 1) base = atomicAdd(count, __popc(b));
+  base = __shfl_sync(0xffffffffu, base, __ffs(b) - 1);
+  if (hit) work[base + __popc(b & ((1u << lane) - 1u))] = t;
+}
+
+// One binding round over a work list (work == null: every item).  Persistent warps, one item at a time per warp: the
+// window's rows go to four groups of eight lanes, so a typical window (2-4 rows of a few features) is one pass of
+// cstart -> record -> descriptor + binder.  The last CTA through turns this round's binder table into the next
+// round's dirty-cell bitmap and empties the older table for the next round to fill.
+__global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, const uint8_t* __restrict__ qdesc, const int* __restrict__ qslot,
+                                                    int* __restrict__ gate_out, int mode0, float nnratio,
+                                                    const ProjItem* __restrict__ items, const int* __restrict__ work,
+                                                    const int* __restrict__ count, int* binder_prev, int* binder_next,
+                                                    int* __restrict__ result, int* __restrict__ changed,
+                                                    unsigned* __restrict__ dirty_next, int* __restrict__ ticket) {
+  pdl_enter();
+  const int lane = threadIdx.x & 31, grp = lane >> 3, sub = lane & 7;
+  const int n_work = *count;
+  for (int w = blockIdx.x * 8 + (threadIdx.x >> 5); w < n_work; w += gridDim.x * 8) {
+    const uint4* ip = reinterpret_cast<const uint4*>(&items[work ? work[w] : w]);
+    const uint4 h0 = ip[0], h1 = ip[1];
+    const int i = (int)h0.x;
+    const int cx0 = h0.y & 63, cx1 = (h0.y >> 6) & 63, cy0 = (h0.y >> 12) & 63, cy1 = (h0.y >> 18) & 63;
+    const bool has_obs = (h0.y >> 24) != 0;
+    const float x = __uint_as_float(h0.z), y = __uint_as_float(h0.w), rad = __uint_as_float(h1.x), pr = __uint_as_float(h1.y);
+    const int minLevel = (int)h1.z, maxLevel = (int)h1.w;
     const bool checkLevels = (minLevel > 0) || (maxLevel >= 0);
-    const uint4* qd = reinterpret_cast<const uint4*>(Q.desc + (size_t)(Q.slot ? Q.slot[i] : i) * 32);
+    const uint4* qd = reinterpret_cast<const uint4*>(qdesc + (size_t)(qslot ? qslot[i] : i) * 32);
     const uint4 q0 = qd[0], q1 = qd[1];
-    const float aux = Q.aux ? Q.aux[i] : 0.f;
     unsigned long long b1 = ~0ull, b2 = ~0ull;  // (dist << 32 | visiting position), two smallest
     bool any_cand = false;
     // GetFeaturesInArea: only the features of the window's cells are visited (cell-sorted CSR); the reference's
     // visiting order is carried by the key, so the iteration order here is free
-    for (int cy = cy0; cy <= cy1; cy++) {
-     const int js = F.cstart[cy * FRAME_GRID_COLS + cx0], je = F.cstart[cy * FRAME_GRID_COLS + cx1 + 1];
-     for (int j = js + lane; j < je; j += 32) {
-      const int f = F.order[j];
-      const int cx = F.cellx[f];
-      const int oct = F.octave[f];
-      if (checkLevels) {
-        if (oct < minLevel) continue;
-        if (maxLevel >= 0 && oct > maxLevel) continue;
-      }
-      if (!(fabsf(__fsub_rn(F.x[f], x)) < rad && fabsf(__fsub_rn(F.y[f], y)) < rad)) continue;
-      any_cand = true;
-      if (F.blocked0[f] || binder_prev[f] < i) continue;
-      if (F.uright) {
-        const float ur = F.uright[f];
-        if (ur > 0.f) {
-          const float pr = Q.mode == 0 ? aux : __fsub_rn(x, __fmul_rn(F.mbf, aux));
-          if (fabsf(__fsub_rn(pr, ur)) > rad) continue;
+    for (int cy = cy0 + grp; cy <= cy1; cy += 4) {
+      const int js = F.cstart[cy * FRAME_GRID_COLS + cx0], je = F.cstart[cy * FRAME_GRID_COLS + cx1 + 1];
+      for (int j = js + sub; j < je; j += 8) {
+        const float4 r = F.rec[j];
+        const unsigned bits = __float_as_uint(r.w);
+        const int f = bits & 0xFFFF, oct = (bits >> 16) & 31, cx = (bits >> 21) & 63;
+        if (checkLevels) {
+          if (oct < minLevel) continue;
+          if (maxLevel >= 0 && oct > maxLevel) continue;
         }
+        if (!(fabsf(__fsub_rn(r.x, x)) < rad && fabsf(__fsub_rn(r.y, y)) < rad)) continue;
+        any_cand = true;
+        if ((bits >> 27) & 1u) continue;                                     // blocked0
+        if (F.uright && r.z > 0.f && fabsf(__fsub_rn(pr, r.z)) > rad) continue;
+        if (binder_prev[f] < i) continue;
+        const int dist = hamming256(q0, q1, reinterpret_cast<const uint4*>(F.desc + (size_t)f * 32));
+        const unsigned long long key = ((unsigned long long)dist << 32) | ((unsigned)cx << 22) | ((unsigned)cy << 16) | (unsigned)f;
+        if (key < b1) { b2 = b1; b1 = key; }
+        else if (key < b2) b2 = key;
       }
-      const int dist = hamming256(q0, q1, reinterpret_cast<const uint4*>(F.desc + (size_t)f * 32));
-      const unsigned long long key = ((unsigned long long)dist << 32) | ((unsigned)cx << 22) | ((unsigned)cy << 16) | (unsigned)f;
-      if (key < b1) { b2 = b1; b1 = key; }
-      else if (key < b2) b2 = key;
-     }
     }
-    if (Q.gate_out) {
+    if (gate_out) {
       const bool any = __any_sync(0xffffffffu, any_cand);
-      if (lane == 0) Q.gate_out[i] = any ? 1 : 0;
+      if (lane == 0) gate_out[i] = any ? 1 : 0;
     }
     unsigned long long B1 = b1;
 #pragma unroll
@@ -147,38 +214,43 @@ __global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, ProjQuery Q,
     unsigned long long B2 = (b1 == B1) ? b2 : b1;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) B2 = min(B2, __shfl_xor_sync(0xffffffffu, B2, o));
+    int res = -1;
     if (B1 != ~0ull) {
       const int bestDist = (int)(B1 >> 32), bestIdx = (int)(B1 & 0xFFFF);
       if (bestDist <= TH_HIGH_P) {
         bool ok = true;
-        if (Q.mode == 0) {
+        if (mode0) {
           int bestDist2 = 256, bestLevel2 = -1;
           if (B2 != ~0ull) { bestDist2 = (int)(B2 >> 32); bestLevel2 = F.octave[(int)(B2 & 0xFFFF)]; }
           const int bestLevel = F.octave[bestIdx];
-          if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(Q.nnratio, (float)bestDist2)) ok = false;
+          if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(nnratio, (float)bestDist2)) ok = false;
         }
         if (ok) res = bestIdx;
       }
     }
+    if (lane == 0) {
+      if (result[i] != res) { result[i] = res; *changed = 1; }
+      if (res >= 0 && has_obs) atomicMin(&binder_next[res], i);
+    }
   }
-  if (lane == 0) {
-    if (result[i] != res) { result[i] = res; *changed = 1; }
-    if (res >= 0 && (fl & CUORB_MP_HAS_OBS)) atomicMin(&binder_next[res], i);
+  // ---- last CTA through: dirty cells for the next round (binder_next = this round's table against binder_prev =
+  // the round before), and binder_prev emptied: it is the next round's table to fill
+  __shared__ bool s_last;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    s_last = atomicAdd(ticket, 1) == (int)gridDim.x - 1;
   }
-}
-
-// grid: ceil(n/256): one bit per grid cell (row-major, 64 columns = 2 words per row) that holds a feature whose
-// binder differs between two consecutive rounds (a = last round's table, b = the one before); b is then reset for
-// the coming round to fill (one launch instead of a compare and a fill)
-__global__ void k_dirty_cells(ProjFrame F, const int* __restrict__ a, int* __restrict__ b, unsigned* __restrict__ dirty) {
-  pdl_enter();
-  const int f = blockIdx.x * blockDim.x + threadIdx.x;
-  if (f >= F.n) return;
-  const bool changed = a[f] != b[f];
-  b[f] = NO_BINDER;
-  if (!changed) return;
-  const int cx = F.cellx[f], cy = F.celly[f];
-  if (cx >= 0) atomicOr(&dirty[2 * cy + (cx >> 5)], 1u << (cx & 31));
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  for (int f = threadIdx.x; f < F.n; f += blockDim.x) {
+    const bool diff = __ldcg(&binder_next[f]) != __ldcg(&binder_prev[f]);
+    binder_prev[f] = NO_BINDER;
+    if (!diff) continue;
+    const int cx = F.cellx[f], cy = F.celly[f];
+    if (cx >= 0) atomicOr(&dirty_next[2 * cy + (cx >> 5)], 1u << (cx & 31));
+  }
 }
 
 // grid: ceil(n/256)
@@ -196,52 +268,57 @@ thread_local HostStage t_stage;
 
 // Binding rounds to the sequential fixed point on device-resident queries; result: device, m ints.  Returns the
 // number of rounds (>= 1) or a negative error code; the stream is synchronised on return.
+// arena bytes projection_rounds takes for m query points (on top of frame_bytes(n), which covers the binder tables)
+inline size_t rounds_bytes(int m) { return (size_t)std::max(m, 1) * (sizeof(ProjItem) + 4) + sizeof(RoundCtl) + 4 * 256; }
+
 static int projection_rounds(Arena& A, cudaStream_t st, const ProjFrame& F, const ProjQuery& Q, int* result) {
   const int n = F.n, m = Q.n;
   int* binder[2] = {A.take<int>(n), A.take<int>(n)};
   // Binding rounds to the sequential fixed point, enqueued ROUND_BATCH at a time with no host round trip in
   // between; round k of a batch sets flag[k] when a result changed and the host reads the batch's flags once.
   // Rounds past the fixed point are idempotent (equal results -> equal binder tables -> no dirty cell -> every
-  // window keeps its result) and cheap (17 us at cfg4), so they simply run: a device-side "skip if the previous
-  // round was quiet" test at the top of k_proj_round cost 0.07-0.15 ms per call in every form tried (per thread,
-  // per block), more than the rounds it saves.  Measured at cfg4 (50k MapPoints, 5 rounds to converge): one sync
-  // per round 0.556 ms per call, batches of 6 0.510 ms (scripts/ab_projection.py, profiles/r02_s9_abproj.txt).
-  constexpr int ROUND_BATCH = 6;   // 2 / 3 / 4 per sync: cfg4 0.558 / 0.561 / 0.581 ms against 0.525, local map 0.339 / 0.324 / 0.365 against 0.302
-  constexpr int DIRTY_WORDS = 2 * FRAME_GRID_ROWS;
-  int* flag = A.take<int>(ROUND_BATCH);
-  unsigned* dirty = A.take<unsigned>(ROUND_BATCH * DIRTY_WORDS);   // one bitmap per round of a batch: cleared with one memset
-  {
-    PdlPause plain;
-    k_fill<<<(n + 255) / 256, 256, 0, st>>>(binder[0], n, NO_BINDER);
-    k_fill<<<(m + 255) / 256, 256, 0, st>>>(result, m, -2);
-    count_launch(2);
-  }
-  // The rounds are chains of kernels of a few microseconds each (a table pass over the frame's features, then the
-  // warp-per-point round), so they are launched as programmatic dependents (common.cuh): every kernel starts with
-  // pdl_enter() and nothing but kernels sits between them inside a batch.
+  // window keeps its result) and cheap, so they simply run: a device-side "skip if the previous round was quiet"
+  // test cost 0.07-0.15 ms per call in every form tried, more than the rounds it saves (profiles/r02_s9_abproj.txt).
+  ProjItem* items = A.take<ProjItem>(std::max(m, 1));
+  int* work = A.take<int>(std::max(m, 1));
+  RoundCtl* ctl = A.take<RoundCtl>(1);
+  int* n_items = A.take<int>(1);
+  // A chain of kernels of a few microseconds each, launched as programmatic dependents (common.cuh): every kernel
+  // starts with pdl_enter() and nothing but kernels sits between them inside a batch.
   const bool pdl = pdl_allowed();
   struct Chain { bool saved; Chain(bool on) : saved(t_pdl) { t_pdl = on; } ~Chain() { t_pdl = saved; } } chain(pdl);
+  int device = 0, sms = 148;
+  cudaGetDevice(&device);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  const int round_grid = std::max(1, std::min((m + 7) / 8, sms * 6));   // 40 registers: 6 CTAs of 256 threads per SM
   int rounds = 0;
   for (bool converged = false; !converged;) {
     if (rounds > m + 2) { set_error("projection search did not converge"); return CUORB_E_CUDA; }
-    CUORB_CUDA_TRY(cudaMemsetAsync(flag, 0, ROUND_BATCH * sizeof(int), st));
-    CUORB_CUDA_TRY(cudaMemsetAsync(dirty, 0, ROUND_BATCH * DIRTY_WORDS * sizeof(unsigned), st));
+    if (rounds == 0) {
+      CUORB_CUDA_TRY(cudaMemsetAsync(n_items, 0, sizeof(int), st));
+      CUORB_CUDA_TRY(cudaMemsetAsync(ctl, 0, sizeof(RoundCtl), st));
+    } else {   // the last round's dirty cells are the next batch's first; everything else starts from zero
+      CUORB_CUDA_TRY(cudaMemcpyAsync(ctl->dirty[0], ctl->dirty[ROUND_BATCH], sizeof(ctl->dirty[0]), cudaMemcpyDeviceToDevice, st));
+      CUORB_CUDA_TRY(cudaMemsetAsync(ctl->dirty[1], 0, sizeof(RoundCtl) - sizeof(ctl->dirty[0]), st));
+    }
     for (int k = 0; k < ROUND_BATCH; k++, rounds++) {
       int* prev = binder[rounds & 1];
       int* next = binder[(rounds + 1) & 1];
-      unsigned* dk = dirty + k * DIRTY_WORDS;
-      t_pdl = pdl && k != 0;   // the batch's first kernel follows two memsets: plain stream order
-      if (rounds > 0)   // cells whose features changed binder between the last two rounds (next still holds round-2's table)
-        launch_k(k_dirty_cells, dim3((n + 255) / 256), dim3(256), 0, st, F, (const int*)prev, next, dk);
+      t_pdl = pdl && k != 0;   // the batch's first kernel follows memsets: plain stream order
+      if (rounds == 0)
+        launch_k(k_proj_begin, dim3((std::max(m, n) + 255) / 256), dim3(256), 0, st, F, Q, binder[0], binder[1], result, items, n_items);
       else
-        launch_k(k_fill, dim3((n + 255) / 256), dim3(256), 0, st, next, n, NO_BINDER);
+        launch_k(k_proj_select, dim3((m + 255) / 256), dim3(256), 0, st, (const ProjItem*)items, (const int*)n_items,
+                 (const unsigned*)ctl->dirty[k], (const int*)result, next, work, ctl->count + k);
       t_pdl = pdl;
-      launch_k(k_proj_round, dim3((m + 7) / 8), dim3(256), 0, st, F, Q, (const int*)prev, next, result, flag + k,
-               rounds > 0 ? (const unsigned*)dk : (const unsigned*)nullptr);
+      launch_k(k_proj_round, dim3(round_grid), dim3(256), 0, st, F, Q.desc, Q.slot, Q.gate_out, Q.mode == 0 ? 1 : 0, Q.nnratio,
+               (const ProjItem*)items, rounds == 0 ? (const int*)nullptr : (const int*)work,
+               rounds == 0 ? (const int*)n_items : (const int*)(ctl->count + k), prev, next, result, ctl->flag + k,
+               ctl->dirty[k + 1], ctl->ticket + k);
       count_launch(2);
     }
     int h_flag[ROUND_BATCH];
-    CUORB_CUDA_TRY(cudaMemcpyAsync(h_flag, flag, sizeof(h_flag), cudaMemcpyDeviceToHost, st));
+    CUORB_CUDA_TRY(cudaMemcpyAsync(h_flag, ctl->flag, sizeof(h_flag), cudaMemcpyDeviceToHost, st));
     CUORB_CUDA_TRY(cudaStreamSynchronize(st));
     for (int k = 0; k < ROUND_BATCH; k++)
       if (!h_flag[k]) { converged = true; rounds -= ROUND_BATCH - 1 - k; break; }   // rounds to the first quiet one, inclusive
@@ -259,7 +336,7 @@ static int run_projection(int device, const cuorb_frame_view* fv, ProjQuery Q, c
   for (int i = 0; i < m; i++) result_out[i] = -1;
   if (n <= 0 || m <= 0) return 0;
   CUORB_CUDA_TRY(cudaSetDevice(device));
-  const size_t bytes = frame_bytes(n) + (size_t)m * (32 + 6 * 4 + 1 + 4 + 8) + 64 * 1024;
+  const size_t bytes = frame_bytes(n) + rounds_bytes(m) + (size_t)m * (32 + 6 * 4 + 1 + 4 + 8) + 64 * 1024;
   if (t_arena.reserve(device, bytes) != 0) { set_error("cudaMalloc failed (projection workspace)"); return CUORB_E_CUDA; }
   Arena& A = t_arena;
   cudaStream_t st = cudaStreamPerThread;
@@ -333,6 +410,116 @@ __global__ void k_compact_matches(int m, const int* __restrict__ result, int cap
     const int pos = base + __popc(b & ((1u << lane) - 1u));
     if (pos < cap) { out_mp[pos] = i; out_feat[pos] = result[i]; }
   }
+}
+
+// ---- the searched Frame built where the extractor left it ------------------------------------------------------
+// Frame::UndistortKeyPoints (src/Frame.cc:886-913) + Frame::AssignFeaturesToGrid (src/Frame.cc:524-553, PosInGrid
+// :867-877) on device-resident keypoints: the SoA, the per-feature cell and the cell-sorted CSR that upload_frame
+// builds on the host.  One CTA (a frame has a few thousand features): count per cell in shared memory, exclusive scan,
+// scatter, then each cell's range is put in ascending feature order -- the order mGrid's vectors hold, which decides
+// ties between equally distant candidates.
+constexpr int FB_THREADS = 1024, FB_CELLS = FRAME_GRID_ROWS * FRAME_GRID_COLS, FB_PER_THREAD = FB_CELLS / FB_THREADS;
+static_assert(FB_PER_THREAD * FB_THREADS == FB_CELLS, "the scan gives each thread a whole number of cells");
+
+__global__ void __launch_bounds__(FB_THREADS)
+k_frame_build(const cuorb_keypoint* __restrict__ keys, int n, int undistort, const UndistortArgs ua, float minX, float minY,
+              float gwinv, float ghinv, float* __restrict__ fx, float* __restrict__ fy, int* __restrict__ foct,
+              short* __restrict__ cellx, short* __restrict__ celly, int* __restrict__ cstart,
+              unsigned short* __restrict__ order, cuorb_keypoint* __restrict__ keys_un, const uint8_t* __restrict__ blocked0,
+              const float* __restrict__ uright, float4* __restrict__ rec) {
+  __shared__ int s_cell[FB_CELLS];   // per-cell count, then the running fill cursor
+  __shared__ int s_warp[FB_THREADS / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int c = tid; c < FB_CELLS; c += FB_THREADS) s_cell[c] = 0;
+  __syncthreads();
+  for (int i = tid; i < n; i += FB_THREADS) {
+    cuorb_keypoint kp = keys[i];
+    if (undistort) undistort_point(ua, kp.x, kp.y);
+    fx[i] = kp.x; fy[i] = kp.y; foct[i] = kp.octave;
+    if (keys_un) keys_un[i] = kp;
+    const int posX = (int)roundf(__fmul_rn(__fsub_rn(kp.x, minX), gwinv));
+    const int posY = (int)roundf(__fmul_rn(__fsub_rn(kp.y, minY), ghinv));
+    const bool in = !(posX < 0 || posX >= FRAME_GRID_COLS || posY < 0 || posY >= FRAME_GRID_ROWS);
+    cellx[i] = in ? (short)posX : (short)-1; celly[i] = in ? (short)posY : (short)-1;
+    if (in) atomicAdd(&s_cell[posY * FRAME_GRID_COLS + posX], 1);
+  }
+  __syncthreads();
+  int cnt[FB_PER_THREAD], sum = 0;
+#pragma unroll
+  for (int k = 0; k < FB_PER_THREAD; k++) { cnt[k] = s_cell[tid * FB_PER_THREAD + k]; sum += cnt[k]; }
+  int incl = sum;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += v; }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    int w = s_warp[lane];
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(0xffffffffu, w, d); if (lane >= d) w += v; }
+    s_warp[lane] = w;
+  }
+  __syncthreads();
+  int start = incl - sum + (warp ? s_warp[warp - 1] : 0);
+#pragma unroll
+  for (int k = 0; k < FB_PER_THREAD; k++) {
+    cstart[tid * FB_PER_THREAD + k] = start; s_cell[tid * FB_PER_THREAD + k] = start;
+    start += cnt[k];
+  }
+  if (tid == FB_THREADS - 1) cstart[FB_CELLS] = start;
+  __syncthreads();
+  for (int i = tid; i < n; i += FB_THREADS) {
+    const int cx = cellx[i];
+    if (cx >= 0) order[atomicAdd(&s_cell[celly[i] * FRAME_GRID_COLS + cx], 1)] = (unsigned short)i;
+  }
+  __syncthreads();
+  for (int c = tid; c < FB_CELLS; c += FB_THREADS) {       // s_cell[c] is now the end of cell c
+    const int b = cstart[c], e = s_cell[c];
+    for (int a = b + 1; a < e; a++) {
+      const unsigned short v = order[a];
+      int j = a - 1;
+      while (j >= b && order[j] > v) { order[j + 1] = order[j]; j--; }
+      order[j + 1] = v;
+    }
+  }
+  __syncthreads();
+  const int total = cstart[FB_CELLS];
+  for (int j = tid; j < total; j += FB_THREADS) {           // the 16-byte record per CSR position (pack_feature_bits)
+    const int f = order[j];
+    rec[j] = make_float4(fx[f], fy[f], uright ? uright[f] : -1.0f,
+                         __uint_as_float(pack_feature_bits(f, foct[f], cellx[f], blocked0[f])));
+  }
+}
+
+// ProjFrame over a cuorb_frame_view whose keys_un / descriptors / u_right are device pointers: descriptors and uRight
+// are read in place, everything else is made by k_frame_build.  Returns the device array of undistorted keypoints
+// when want_keys_un, else null.
+static const cuorb_keypoint* build_frame_on_device(Arena& A, const cuorb_frame_view* fv, const float* K4, const float* dist5,
+                                                   bool want_keys_un, cudaStream_t st, ProjFrame& F) {
+  const int n = fv->n, nn = std::max(n, 1);
+  int* cstart = A.take<int>(FB_CELLS + 1);
+  unsigned short* order = A.take<unsigned short>(nn);
+  float *x = A.take<float>(nn), *y = A.take<float>(nn);
+  int* oct = A.take<int>(nn);
+  short *cx = A.take<short>(nn), *cy = A.take<short>(nn);
+  uint8_t* blk = A.take<uint8_t>(nn);
+  cuorb_keypoint* keys_un = want_keys_un ? A.take<cuorb_keypoint>(nn) : nullptr;
+  float4* rec = A.take<float4>(nn);
+  if (fv->bound_with_obs) cudaMemcpyAsync(blk, fv->bound_with_obs, (size_t)n, cudaMemcpyHostToDevice, st);
+  else cudaMemsetAsync(blk, 0, (size_t)nn, st);
+  // src/Frame.cc:888-892: mDistCoef.at<float>(0) == 0.0 -> mvKeysUn = mvKeys
+  const bool undistort = K4 && dist5 && dist5[0] != 0.0f;
+  const float identK[4] = {1.f, 1.f, 0.f, 0.f}, zeroD[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+  const UndistortArgs ua = undistort ? undistort_args(K4, dist5) : undistort_args(identK, zeroD);
+  k_frame_build<<<1, FB_THREADS, 0, st>>>(fv->keys_un, n, undistort ? 1 : 0, ua, fv->min_x, fv->min_y, fv->grid_w_inv,
+                                          fv->grid_h_inv, x, y, oct, cx, cy, cstart, order, keys_un, blk, fv->u_right, rec);
+  count_launch();
+  F.n = n;
+  F.cstart = cstart; F.order = order; F.rec = rec; F.x = x; F.y = y; F.uright = fv->u_right; F.octave = oct; F.cellx = cx; F.celly = cy;
+  F.desc = fv->descriptors; F.blocked0 = blk;
+  F.minX = fv->min_x; F.minY = fv->min_y; F.maxX = fv->max_x; F.maxY = fv->max_y;
+  F.gwinv = fv->grid_w_inv; F.ghinv = fv->grid_h_inv; F.mbf = fv->mbf;
+  for (int l = 0; l < MAX_LEVELS; l++) F.scale[l] = l < fv->nlevels ? fv->scale_factors[l] : 0.f;
+  return keys_un;
 }
 
 }  // namespace cuorb
@@ -507,6 +694,7 @@ struct cuorb_localmap {
   int *lv = nullptr, *result = nullptr, *match_mp = nullptr, *match_feat = nullptr, *counters = nullptr, *order = nullptr;
   int *h_counters = nullptr;    // pinned: [0] in view, [1] matches
   cudaStream_t stream = nullptr;
+  cudaEvent_t producer_done = nullptr;   // orders a device-resident frame's producer stream before this map's stream
 };
 
 cuorb_localmap* cuorb_localmap_create(int device, int capacity) {
@@ -523,6 +711,7 @@ cuorb_localmap* cuorb_localmap_create(int device, int capacity) {
   al(&m->counters, 2 * sizeof(int));
   if (ok && cudaHostAlloc((void**)&m->h_counters, 2 * sizeof(int), cudaHostAllocDefault) != cudaSuccess) ok = false;
   if (ok && cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess) ok = false;
+  if (ok && cudaEventCreateWithFlags(&m->producer_done, cudaEventDisableTiming) != cudaSuccess) ok = false;
   if (ok && cudaMemset(m->pflags, CUORB_MP_BAD, c) != cudaSuccess) ok = false;   // slots never written are bad points
   if (!ok) { set_error("cuorb_localmap_create: device allocation failed"); cuorb_localmap_destroy(m); return nullptr; }
   return m;
@@ -532,6 +721,7 @@ void cuorb_localmap_destroy(cuorb_localmap* m) {
   if (!m) return;
   cudaSetDevice(m->device);
   if (m->stream) { cudaStreamSynchronize(m->stream); cudaStreamDestroy(m->stream); }
+  if (m->producer_done) cudaEventDestroy(m->producer_done);
   void* ptrs[] = {m->P, m->N, m->minD, m->maxD, m->desc, m->pflags, m->skip, m->qflags, m->px, m->py, m->pxr, m->vc, m->dz,
                   m->lv, m->result, m->match_mp, m->match_feat, m->counters, m->order};
   for (void* p : ptrs) if (p) cudaFree(p);
@@ -565,13 +755,22 @@ int cuorb_localmap_update(cuorb_localmap* m, int first, int n, int new_count, co
 
 int cuorb_localmap_count(const cuorb_localmap* m) { return m ? m->count : CUORB_E_BADARG; }
 
-int cuorb_localmap_search(cuorb_localmap* m, const cuorb_frustum_camera* cam, const cuorb_frame_view* frame, int n_order,
-                          const int32_t* order, int n_skip, const int32_t* skip_pos, float viewing_cos_limit, float th,
-                          int far_points, float th_far_points, float nn_ratio, int32_t* best_idx_out, uint8_t* in_view_out,
-                          int match_capacity, int32_t* match_pos_out, int32_t* match_feature_out, int32_t* n_in_view_out) {
+// where the searched Frame's arrays live
+struct FrameSource {
+  bool on_device = false;               // keys_un / descriptors / u_right of the view are device pointers
+  cudaStream_t producer = nullptr;      // stream that wrote them (ordered before the search); null = already complete
+  const float *K4 = nullptr, *dist5 = nullptr;   // non-null: the keys are mvKeys and are undistorted on the device first
+  cuorb_keypoint* keys_un_out = nullptr;          // host, optional: mvKeysUn as the search saw it
+};
+
+static int localmap_search_impl(cuorb_localmap* m, const cuorb_frustum_camera* cam, const cuorb_frame_view* frame,
+                                const FrameSource& src, int n_order, const int32_t* order, int n_skip, const int32_t* skip_pos,
+                                float viewing_cos_limit, float th, int far_points, float th_far_points, float nn_ratio,
+                                int32_t* best_idx_out, uint8_t* in_view_out, int match_capacity, int32_t* match_pos_out,
+                                int32_t* match_feature_out, int32_t* n_in_view_out) {
   if (!m || !cam || !frame || frame->n < 0 || (frame->n > 0 && (!frame->keys_un || !frame->descriptors)) || !frame->scale_factors || n_skip < 0 ||
       (n_skip && !skip_pos) || match_capacity < 0 || (match_capacity && (!match_pos_out || !match_feature_out)) ||
-      n_order < 0 || (order && n_order > m->capacity)) {
+      n_order < 0 || (order && n_order > m->capacity) || ((src.K4 == nullptr) != (src.dist5 == nullptr))) {
     set_error("cuorb_localmap_search: bad argument");
     return CUORB_E_BADARG;
   }
@@ -583,7 +782,7 @@ int cuorb_localmap_search(cuorb_localmap* m, const cuorb_frustum_camera* cam, co
   if (M == 0) return 0;
   CUORB_CUDA_TRY(cudaSetDevice(m->device));
   cudaStream_t st = m->stream;
-  const size_t bytes = frame_bytes(std::max(n, 1)) + (size_t)std::max(n, 1) * 8 + (size_t)n_skip * 4 + 64 * 1024;
+  const size_t bytes = frame_bytes(std::max(n, 1)) + rounds_bytes(M) + (size_t)std::max(n, 1) * (8 + sizeof(cuorb_keypoint)) + (size_t)n_skip * 4 + 64 * 1024;
   if (t_arena.reserve(m->device, bytes) != 0) { set_error("cudaMalloc failed (local map search workspace)"); return CUORB_E_CUDA; }
   Arena& A = t_arena;
   CUORB_CUDA_TRY(cudaMemsetAsync(m->skip, 0, (size_t)M, st));
@@ -601,7 +800,18 @@ int cuorb_localmap_search(cuorb_localmap* m, const cuorb_frustum_camera* cam, co
   int nmatches = 0;
   if (n > 0) {
     ProjFrame F;
-    upload_frame(A, frame, st, F);
+    const cuorb_keypoint* d_keys_un = nullptr;
+    if (src.on_device) {
+      if (src.producer) {
+        CUORB_CUDA_TRY(cudaEventRecord(m->producer_done, src.producer));
+        CUORB_CUDA_TRY(cudaStreamWaitEvent(m->stream, m->producer_done, 0));
+      }
+      d_keys_un = build_frame_on_device(A, frame, src.K4, src.dist5, src.keys_un_out != nullptr, st, F);
+    } else {
+      upload_frame(A, frame, st, F);
+    }
+    if (src.keys_un_out && d_keys_un)
+      CUORB_CUDA_TRY(cudaMemcpyAsync(src.keys_un_out, d_keys_un, sizeof(cuorb_keypoint) * (size_t)n, cudaMemcpyDeviceToHost, st));
     ProjQuery Q{};
     Q.n = M; Q.mode = 0; Q.th = th; Q.thFar = th_far_points; Q.nnratio = nn_ratio; Q.far_points = far_points;
     Q.desc = m->desc; Q.px = m->px; Q.py = m->py; Q.aux = m->pxr; Q.level = m->lv; Q.viewcos = m->vc; Q.depth = m->dz;
@@ -633,6 +843,39 @@ int cuorb_localmap_search(cuorb_localmap* m, const cuorb_frustum_camera* cam, co
     for (int k = 0; k < nmatches; k++) { match_pos_out[k] = pairs[k].first; match_feature_out[k] = pairs[k].second; }
   }
   return nmatches;
+}
+
+int cuorb_localmap_search(cuorb_localmap* m, const cuorb_frustum_camera* cam, const cuorb_frame_view* frame, int n_order,
+                          const int32_t* order, int n_skip, const int32_t* skip_pos, float viewing_cos_limit, float th,
+                          int far_points, float th_far_points, float nn_ratio, int32_t* best_idx_out, uint8_t* in_view_out,
+                          int match_capacity, int32_t* match_pos_out, int32_t* match_feature_out, int32_t* n_in_view_out) {
+  return localmap_search_impl(m, cam, frame, FrameSource{}, n_order, order, n_skip, skip_pos, viewing_cos_limit, th, far_points,
+                              th_far_points, nn_ratio, best_idx_out, in_view_out, match_capacity, match_pos_out,
+                              match_feature_out, n_in_view_out);
+}
+
+int cuorb_localmap_search_resident(cuorb_localmap* m, const cuorb_frustum_camera* cam, const cuorb_frame_view* frame,
+                                   void* producer_stream, const float* K4, const float* dist5, cuorb_keypoint* keys_un_out,
+                                   int n_order, const int32_t* order, int n_skip, const int32_t* skip_pos,
+                                   float viewing_cos_limit, float th, int far_points, float th_far_points, float nn_ratio,
+                                   int32_t* best_idx_out, uint8_t* in_view_out, int match_capacity, int32_t* match_pos_out,
+                                   int32_t* match_feature_out, int32_t* n_in_view_out) {
+  FrameSource src;
+  src.on_device = true; src.producer = (cudaStream_t)producer_stream; src.K4 = K4; src.dist5 = dist5; src.keys_un_out = keys_un_out;
+  if (frame && frame->n > 0 && frame->keys_un && frame->descriptors) {
+    cudaPointerAttributes pa{}, pd{};
+    const bool dev_k = cudaPointerGetAttributes(&pa, frame->keys_un) == cudaSuccess && pa.type == cudaMemoryTypeDevice;
+    const bool dev_d = cudaPointerGetAttributes(&pd, frame->descriptors) == cudaSuccess && pd.type == cudaMemoryTypeDevice;
+    if (!dev_k || !dev_d || (m && (pa.device != m->device || pd.device != m->device)) || ((uintptr_t)frame->descriptors & 15) ||
+        ((uintptr_t)frame->keys_un & 3)) {
+      cudaGetLastError();
+      set_error("cuorb_localmap_search_resident: keys_un / descriptors must be device pointers on the map's device");
+      return CUORB_E_BADARG;
+    }
+  }
+  return localmap_search_impl(m, cam, frame, src, n_order, order, n_skip, skip_pos, viewing_cos_limit, th, far_points,
+                              th_far_points, nn_ratio, best_idx_out, in_view_out, match_capacity, match_pos_out,
+                              match_feature_out, n_in_view_out);
 }
 
 }  // extern "C"

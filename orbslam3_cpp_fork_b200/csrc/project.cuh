@@ -20,6 +20,9 @@ struct ProjFrame {  // device SoA of the frame members the searches read
   // row are one contiguous range
   const int* cstart;
   const unsigned short* order;
+  // the same features as one 16-byte record per CSR position (pack_feature): what the projection rounds read, so a
+  // window row is one coalesced load instead of an index and six gathers
+  const float4* rec;
   const uint8_t* desc;
   const uint8_t* blocked0;     // mvpMapPoints[i] && Observations() > 0 on entry
   float minX, minY, maxX, maxY, gwinv, ghinv, mbf;
@@ -28,6 +31,12 @@ struct ProjFrame {  // device SoA of the frame members the searches read
 
 constexpr int FRAME_GRID_ROWS = 48, FRAME_GRID_COLS = 64, TH_HIGH_P = 100;
 constexpr int NO_BINDER = 0x7fffffff;
+
+// CSR record of feature f: x, y, uRight (-1 when the frame has none), and f | octave << 16 | cellx << 21 | blocked0 << 27
+__host__ __device__ __forceinline__ unsigned pack_feature_bits(int f, int octave, int cellx, int blocked) {
+  return (unsigned)f | ((unsigned)octave << 16) | ((unsigned)cellx << 21) | ((unsigned)(blocked != 0) << 27);
+}
+static_assert(MAX_LEVELS <= 32, "octave field of the CSR record is 5 bits");
 
 __device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, const uint4* b) {
   const uint4 b0 = b[0], b1 = b[1];
@@ -70,7 +79,7 @@ inline T* up(Arena& A, const T* host, size_t count, cudaStream_t st) {
 }
 
 
-inline size_t frame_bytes(int n) { return (size_t)n * (4 * 4 + 2 * 2 + 32 + 1 + 8 + 2) + (FRAME_GRID_ROWS * FRAME_GRID_COLS + 1) * 4 + 20 * 256; }
+inline size_t frame_bytes(int n) { return (size_t)n * (4 * 4 + 2 * 2 + 32 + 1 + 8 + 2 + 16) + (FRAME_GRID_ROWS * FRAME_GRID_COLS + 1) * 4 + 20 * 256; }
 
 struct HostStage {  // grow-only pinned staging per host thread: a Frame's SoA goes up as ONE copy
   void* p = nullptr; size_t cap = 0;
@@ -95,7 +104,7 @@ inline void upload_frame(Arena& A, const cuorb_frame_view* fv, cudaStream_t st, 
   auto slot = [&](size_t bytes) { const size_t o = off; off = (off + bytes + 255) & ~(size_t)255; return o; };
   const size_t o_cstart = slot(sizeof(int) * ncell), o_order = slot(2 * (size_t)nn), o_x = slot(4 * (size_t)nn), o_y = slot(4 * (size_t)nn),
                o_ur = slot(fv->u_right ? 4 * (size_t)nn : 0), o_oct = slot(4 * (size_t)nn), o_cx = slot(2 * (size_t)nn),
-               o_cy = slot(2 * (size_t)nn), o_desc = slot(32 * (size_t)nn), o_blk = slot((size_t)nn);
+               o_cy = slot(2 * (size_t)nn), o_desc = slot(32 * (size_t)nn), o_blk = slot((size_t)nn), o_rec = slot(16 * (size_t)nn);
   const size_t total = off;
   unsigned char* h = (unsigned char*)t_stage.get(total);
   std::vector<unsigned char> fallback;
@@ -121,12 +130,21 @@ inline void upload_frame(Arena& A, const cuorb_frame_view* fv, cudaStream_t st, 
     std::vector<int> fill(cstart, cstart + ncell - 1);
     for (int i = 0; i < n; i++) if (cxv[i] >= 0) order[fill[cyv[i] * FRAME_GRID_COLS + cxv[i]]++] = (unsigned short)i;
   }
+  {
+    struct Rec { float x, y, ur; unsigned bits; };
+    Rec* rec = (Rec*)(h + o_rec);
+    for (int j = 0; j < cstart[ncell - 1]; j++) {
+      const int f = order[j];
+      rec[j] = Rec{fx[f], fy[f], fv->u_right ? fv->u_right[f] : -1.0f, pack_feature_bits(f, foct[f], cxv[f], blk[f])};
+    }
+  }
   if (n) memcpy(h + o_desc, fv->descriptors, 32 * (size_t)n);
   if (fv->u_right && n) memcpy(h + o_ur, fv->u_right, 4 * (size_t)n);
   unsigned char* d = A.take<unsigned char>(total);
   cudaMemcpyAsync(d, h, total, cudaMemcpyHostToDevice, st);
   F.n = n;
   F.cstart = (const int*)(d + o_cstart); F.order = (const unsigned short*)(d + o_order);
+  F.rec = (const float4*)(d + o_rec);
   F.x = (const float*)(d + o_x); F.y = (const float*)(d + o_y);
   F.uright = fv->u_right ? (const float*)(d + o_ur) : nullptr;
   F.octave = (const int*)(d + o_oct);

@@ -124,3 +124,50 @@ class LocalMap:
             frame.mvpMapPoints[f] = p
         out = (n, nin.value, mp[:n].copy(), ft[:n].copy(), (best[:M] if want_best else None))
         return out + (inv[:M],) if want_in_view else out
+
+    def search_extracted(self, camera, frame, extractor, image_index=0, **kw):
+        """search() on the Frame the extractor just produced, read where the extractor left it on the device:
+        keypoints, descriptors and (when frame.mvuRight is not None, i.e. after SearchStereo on this handle) uRight of
+        image `image_index` of extractor's last batch.  `frame` supplies N, the grid constants, the scale factors and
+        the bound flags; its mvKeysUn / mDescriptors / mvuRight arrays are NOT read.  Keywords as search_resident."""
+        import ctypes as C
+        dk, dd, du, dz = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
+        check(self._L.cuorb_extractor_device_features(extractor.handle, int(image_index), C.byref(dk), C.byref(dd), C.byref(du), C.byref(dz)))
+        if frame.mvuRight is not None and not du.value:
+            raise RuntimeError("frame has mvuRight but no stereo match has run on this extractor handle")
+        return self.search_resident(camera, frame, dk.value, dd.value, du.value if frame.mvuRight is not None else None,
+                                    producer_stream=extractor.stream, **kw)
+
+    def search_resident(self, camera, frame, d_keys, d_descriptors, d_u_right=None, producer_stream=None, K4=None, dist5=None,
+                        want_keys_un=False, skip_idx=(), viewingCosLimit=0.5, th=1.0, bFarPoints=False, thFarPoints=50.0,
+                        nnratio=0.8, match_capacity=None, want_best=True, order=None, want_in_view=False):
+        """cuorb_localmap_search_resident: d_keys / d_descriptors / d_u_right are device addresses (ints) of the Frame's
+        mvKeys (or mvKeysUn when K4 / dist5 are None), mDescriptors and mvuRight; producer_stream the cudaStream_t
+        (int) that wrote them or None.  K4 / dist5: Frame::UndistortKeyPoints runs on the device first.  Returns
+        search()'s tuple, plus mvKeysUn as the search used it when want_keys_un."""
+        import ctypes as C
+        fv, keep = frame.view()
+        fv.keys_un = d_keys; fv.descriptors = d_descriptors; fv.u_right = d_u_right
+        k4 = None if K4 is None else np.ascontiguousarray(K4, np.float32)
+        d5 = None if dist5 is None else np.ascontiguousarray(dist5, np.float32)
+        kun = np.zeros(max(frame.N, 1), _lib.KP_DTYPE) if want_keys_un else None
+        skip = np.ascontiguousarray(np.asarray(skip_idx, np.int32))
+        ordr = None if order is None else np.ascontiguousarray(np.asarray(order, np.int32))
+        M = self.count if ordr is None else len(ordr)
+        cap = int(match_capacity) if match_capacity is not None else max(M, 1)
+        mp = np.full(max(cap, 1), -1, np.int32); ft = np.full(max(cap, 1), -1, np.int32)
+        best = np.full(max(M, 1), -1, np.int32) if want_best else None
+        inv = np.zeros(max(M, 1), np.uint8) if want_in_view else None
+        nin = C.c_int32(0)
+        n = check(self._L.cuorb_localmap_search_resident(
+            self._h, C.byref(camera), C.byref(fv), producer_stream or None,
+            None if k4 is None else ptr(k4), None if d5 is None else ptr(d5), ptr(kun) if want_keys_un else None,
+            0 if ordr is None else len(ordr), None if ordr is None else ptr(ordr), len(skip), ptr(skip) if len(skip) else None,
+            float(viewingCosLimit), float(th), int(bFarPoints), float(thFarPoints), float(nnratio),
+            ptr(best) if want_best else None, ptr(inv) if want_in_view else None, cap, ptr(mp), ptr(ft), C.byref(nin)))
+        for p, f in zip(mp[:n], ft[:n]):
+            frame.mvpMapPoints[f] = p
+        out = (n, nin.value, mp[:n].copy(), ft[:n].copy(), (best[:M] if want_best else None))
+        if want_in_view: out = out + (inv[:M],)
+        if want_keys_un: out = out + (kun[:frame.N],)
+        return out

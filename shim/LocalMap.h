@@ -106,25 +106,35 @@ public:
   template <class FrameT>
   int SearchLocalPoints(FrameT& F, const cuorb_frustum_camera& cam, const cuorb_frame_view& fv, unsigned long frame_id, float th,
                         bool bFarPoints, float thFarPoints, float nnratio, int* nToMatch) {
-    const int M = (int)points_.size();
-    if (nToMatch) *nToMatch = 0;
-    if (M == 0) return 0;
-    std::vector<int32_t> skip;
-    for (int i = 0; i < M; i++) if (points_[i]->mnLastFrameSeen == frame_id) skip.push_back(i);   // :3214-3216
-    std::vector<uint8_t> in_view(M);
-    const int cap = F.N > 0 ? 4 * F.N + 64 : 64;
-    std::vector<int32_t> mp(cap), ft(cap);
-    int32_t n_in = 0;
-    const int n = cuorb_localmap_search(h_, &cam, &fv, M, order_.data(), (int)skip.size(), skip.data(), 0.5f, th, bFarPoints ? 1 : 0,
-                                        thFarPoints, nnratio, nullptr, in_view.data(), cap, mp.data(), ft.data(), &n_in);
-    if (n < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string("SearchLocalPoints (libcuorb): ") + cuorb_last_error(), 0);
-    for (int i = 0; i < M; i++) {
-      points_[i]->mbTrackInView = in_view[i] != 0;
-      if (in_view[i]) points_[i]->IncreaseVisible();                                              // :3222-3225
-    }
-    for (int k = 0; k < n; k++) F.mvpMapPoints[ft[k]] = points_[mp[k]];                           // src/ORBmatcher.cc:136
-    if (nToMatch) *nToMatch = n_in;
-    return n;
+    return Run(F, frame_id, nToMatch, "SearchLocalPoints", [&](int M, const std::vector<int32_t>& skip, uint8_t* in_view, int cap,
+                                                                 int32_t* mp, int32_t* ft, int32_t* n_in) {
+      return cuorb_localmap_search(h_, &cam, &fv, M, order_.data(), (int)skip.size(), skip.data(), 0.5f, th, bFarPoints ? 1 : 0,
+                                   thFarPoints, nnratio, nullptr, in_view, cap, mp, ft, n_in);
+    });
+  }
+
+  // The same, on the Frame's arrays where the extractor left them on the device (cuorb_localmap_search_resident):
+  // ext = the handle behind the Frame's left ORBextractor (shim/ORBextractor.h handle()), image_index = the Frame's
+  // position in that handle's last batch.  fv as above - its keys_un / descriptors / u_right host pointers are replaced
+  // by the device arrays (u_right only if fv.u_right is set, i.e. a stereo Frame whose ComputeStereoMatches ran on the
+  // handle).  K4 / dist5 (fx fy cx cy / k1 k2 p1 p2 k3, or both null for a rectified camera): the device keypoints are
+  // mvKeys and Frame::UndistortKeyPoints is applied to them on the device.  Nothing of the Frame's feature arrays is
+  // uploaded.
+  template <class FrameT>
+  int SearchLocalPointsResident(FrameT& F, const cuorb_frustum_camera& cam, cuorb_frame_view fv, cuorb_extractor* ext,
+                                int image_index, const float* K4, const float* dist5, unsigned long frame_id, float th,
+                                bool bFarPoints, float thFarPoints, float nnratio, int* nToMatch) {
+    const cuorb_keypoint* dk = nullptr; const uint8_t* dd = nullptr; const float* du = nullptr;
+    if (cuorb_extractor_device_features(ext, image_index, &dk, &dd, &du, nullptr) < 0 || (fv.u_right && !du))
+      CUORB_SHIM_FAIL(std::runtime_error, std::string("SearchLocalPointsResident (libcuorb): ") +
+                      (fv.u_right && dk ? "no stereo match has run on the handle" : cuorb_last_error()), 0);
+    fv.keys_un = dk; fv.descriptors = dd; fv.u_right = fv.u_right ? du : nullptr;
+    return Run(F, frame_id, nToMatch, "SearchLocalPointsResident", [&](int M, const std::vector<int32_t>& skip, uint8_t* in_view,
+                                                                         int cap, int32_t* mp, int32_t* ft, int32_t* n_in) {
+      return cuorb_localmap_search_resident(h_, &cam, &fv, cuorb_extractor_stream(ext), K4, dist5, nullptr, M, order_.data(),
+                                            (int)skip.size(), skip.data(), 0.5f, th, bFarPoints ? 1 : 0, thFarPoints, nnratio,
+                                            nullptr, in_view, cap, mp, ft, n_in);
+    });
   }
 
   // cuorb_frustum_camera from the reference's Frame members (mRcw, mtcw, mOw, fx, fy, cx, cy, mbf, image bounds,
@@ -146,6 +156,29 @@ public:
   cuorb_localmap* handle() const { return h_; }
 
 private:
+  // skip list (:3214-3216) -> one library call -> what the reference's loops leave in the MapPoints and the Frame
+  template <class FrameT, class CallFn>
+  int Run(FrameT& F, unsigned long frame_id, int* nToMatch, const char* who, CallFn call) {
+    const int M = (int)points_.size();
+    if (nToMatch) *nToMatch = 0;
+    if (M == 0) return 0;
+    std::vector<int32_t> skip;
+    for (int i = 0; i < M; i++) if (points_[i]->mnLastFrameSeen == frame_id) skip.push_back(i);
+    std::vector<uint8_t> in_view(M);
+    const int cap = F.N > 0 ? 4 * F.N + 64 : 64;
+    std::vector<int32_t> mp(cap), ft(cap);
+    int32_t n_in = 0;
+    const int n = call(M, skip, in_view.data(), cap, mp.data(), ft.data(), &n_in);
+    if (n < 0) CUORB_SHIM_FAIL(std::runtime_error, std::string(who) + " (libcuorb): " + cuorb_last_error(), 0);
+    for (int i = 0; i < M; i++) {
+      points_[i]->mbTrackInView = in_view[i] != 0;
+      if (in_view[i]) points_[i]->IncreaseVisible();                                              // :3222-3225
+    }
+    for (int k = 0; k < n; k++) F.mvpMapPoints[ft[k]] = points_[mp[k]];                           // src/ORBmatcher.cc:136
+    if (nToMatch) *nToMatch = n_in;
+    return n;
+  }
+
   cuorb_localmap* h_ = nullptr;
   int capacity_ = 0, used_ = 0;
   std::unordered_map<MapPointT*, int> slot_;

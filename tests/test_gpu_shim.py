@@ -382,3 +382,64 @@ def test_cpp_shim_rig_bow(tmp_path, seed, ori):
     res = np.fromfile(out, np.int32)
     assert int(res[0]) == rn and rn > 80
     assert (res[1:1 + n1] == rml).all() and (res[1 + n1:] == rmr).all()
+
+
+def test_cpp_shim_local_map_resident_frame(tmp_path):
+    """One frame end to end in C++: cuorb_extract leaves the features on the device, then Tracking::SearchLocalPoints
+    through shim/LocalMap.h twice - Frame flattened on the host, and SearchLocalPointsResident (keypoints and
+    descriptors read in place, Frame::UndistortKeyPoints on the device).  Both against the reference's own
+    Frame::isInFrustum (lifted) + unmodified ORBmatcher::SearchByProjection on the host-side undistorted keypoints."""
+    from oracle import ref_py as rp
+    from orbslam3_cpp_fork_b200 import UndistortKeyPoints, synth
+    from tests.matching_cases import extracted_frame, localmap_case
+    if not rp.available():
+        pytest.skip("oracle/_ref/liborb_ref.so did not travel to this box")
+    build.build_libcuorb()
+    exe = str(tmp_path / "localmap_resident_check")
+    pkg = os.path.join(ROOT, "orbslam3_cpp_fork_b200")
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-DCUORB_SHIM_USE_OPENCV",
+                           "-I" + os.path.join(ROOT, "oracle", "ref_compat"),
+                           os.path.join(ROOT, "tests", "native", "localmap_resident_check.cpp"), "-o", exe,
+                           "-L" + pkg, "-l:libcuorb.so", "-Wl,-rpath," + pkg])
+    w, h, M, nf = 752, 480, 15000, 1000
+    e, k, d = extracted_frame(w, h, nf, seed=35)             # the oracle's extraction = what the device will hold
+    sf = np.asarray(e.tables()[0], np.float32)
+    K4 = np.array([458.654, 457.296, 367.215, 248.375], np.float32)
+    D5 = np.array([-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05, 0.0], np.float32)
+    kun = UndistortKeyPoints(k, K4, D5)
+    bounds = (-25.5, -14.0, w + 30.25, h + 18.0)
+    c = localmap_case(kun, d, sf, M, 23)
+    rng = np.random.default_rng(6)
+    order = rng.permutation(M)[:M - 700].astype(np.int32)
+    skip = rng.permutation(len(order))[:200].astype(np.int32)
+    th, thfar, ratio, mb = 1.0, 30.0, 0.8, 0.1
+    f = rp.is_in_frustum(c["cam"], c["P"][order], c["N"][order], c["min_d"][order], c["max_d"][order], 0.5)
+    sk = np.zeros(len(order), bool); sk[skip] = True
+    in_view = (f["in_view"] > 0) & ~sk & (c["bad"][order] == 0)
+    flags = (in_view * 1 + c["bad"][order] * 2 + c["has_obs"][order] * 4).astype(np.uint8)
+    fv, keep = op.make_frame_view(kun, d, np.full(len(k), -1, np.float32), c["bound"], w, h, sf, mb=mb, mbf=c["mbf"],
+                                  min_x=bounds[0], min_y=bounds[1], max_x=bounds[2], max_y=bounds[3])
+    n_ref, best, final = rp.search_by_projection(fv, c["desc"][order], f["proj_x"], f["proj_y"], f["proj_xr"],
+                                                 np.maximum(f["level"], 0), f["view_cos"], f["depth"], flags, th, False, thfar, ratio)
+    final = np.where(final >= 0, order[np.maximum(final, 0)], final).astype(np.int32)
+    img = str(tmp_path / "img.raw"); case = str(tmp_path / "case.bin"); out = str(tmp_path / "out.bin")
+    synth.synth_image(w, h, 35).tofile(img)
+    with open(case, "wb") as fh:
+        np.array([len(k), len(sf), M, len(order), len(skip), nf], np.int32).tofile(fh)
+        np.array([th, thfar, ratio, mb, c["mbf"], *bounds, *K4, *D5], np.float32).tofile(fh)
+        fh.write(bytes(c["cam"]))
+        c["bound"].tofile(fh); sf.tofile(fh)
+        for key in ("P", "N", "min_d", "max_d", "desc", "bad", "has_obs"):
+            np.ascontiguousarray(c[key]).tofile(fh)
+        order.tofile(fh); skip.tofile(fh)
+    subprocess.check_call([exe, img, str(w), str(h), case, out])
+    raw = np.fromfile(out, np.uint8)
+    N = len(k)
+    head = raw[:4 * (1 + 2 * (2 + N))].view(np.int32)
+    assert head[0] == N
+    assert raw[4 * (1 + 2 * (2 + N)):].tobytes() == kun.tobytes()
+    res = head[1:].reshape(2, 2 + N)
+    assert n_ref > 200
+    for r in res:                                            # host frame, then resident frame
+        assert int(r[0]) == n_ref and int(r[1]) == int(in_view.sum())
+        assert (r[2:] == final).all()
