@@ -50,15 +50,14 @@ struct __align__(16) ProjItem {
   int      min_level, max_level;
 };
 
-// Control block of one batch of rounds (device ints): dirty[k] = one bit per grid cell holding a feature whose
-// binder differs between the two rounds before round k (slot ROUND_BATCH carries over to the next batch's slot 0).
+// Control block of one batch of rounds (device ints): dirty[k] = one bit per grid cell holding a feature that a point
+// joined or left in the round before round k (slot ROUND_BATCH carries over to the next batch's slot 0).
 constexpr int ROUND_BATCH = 6;   // rounds per host sync; 2 / 3 / 4: cfg4 0.558 / 0.561 / 0.581 ms against 0.525 (r02_s9)
 constexpr int DIRTY_WORDS = 2 * FRAME_GRID_ROWS;
 struct RoundCtl {
   unsigned dirty[ROUND_BATCH + 1][DIRTY_WORDS];
   int flag[ROUND_BATCH];     // a result changed in round k
   int count[ROUND_BATCH];    // length of round k's work list
-  int ticket[ROUND_BATCH];   // CTAs of round k that are through (the last one makes dirty[k + 1])
 };
 
 // The per-point prologue of the three projection searches, once per call.  grid: ceil(max(m, n)/256).
@@ -155,20 +154,28 @@ __global__ void k_proj_select(const ProjItem* __restrict__ items, const int* __r
   if (hit) work[base + __popc(b & ((1u << lane) - 1u))] = t;
 }
 
-// One binding round over a work list (work == null: every item).  Persistent warps, one item at a time per warp: the
-// window's rows go to four groups of eight lanes, so a typical window (2-4 rows of a few features) is one pass of
-// cstart -> record -> descriptor + binder.  The last CTA through turns this round's binder table into the next
-// round's dirty-cell bitmap and empties the older table for the next round to fill.
+// One binding round over a work list (work == null: every item).  Persistent warps, eight lanes per item (four items
+// in flight per warp).  The candidates of the item's cell window - a few features spread over 2-4 grid rows - are
+// numbered across the rows (prefix sum over the lanes' row lengths) and dealt to the lanes, so a typical window is ONE
+// pass of item -> cstart -> record -> binder + descriptor with all loads of a stage in flight together: the round is
+// bound by the length of that chain, not by arithmetic.
+// A point whose result changes marks the grid cells of the old and of the new feature in dirty_next: a feature's
+// binder can only change between two rounds if a point joined or left it, so those cells cover every window that the
+// next round has to look at again (k_proj_select).  `spare` is the binder table of the round after this one (nobody
+// reads it now): emptied here, so the next round's claims find it clean.
 __global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, const uint8_t* __restrict__ qdesc, const int* __restrict__ qslot,
                                                     int* __restrict__ gate_out, int mode0, float nnratio,
                                                     const ProjItem* __restrict__ items, const int* __restrict__ work,
-                                                    const int* __restrict__ count, int* binder_prev, int* binder_next,
+                                                    const int* __restrict__ count, const int* __restrict__ binder_prev,
+                                                    int* __restrict__ binder_next, int* __restrict__ spare,
                                                     int* __restrict__ result, int* __restrict__ changed,
-                                                    unsigned* __restrict__ dirty_next, int* __restrict__ ticket) {
+                                                    unsigned* __restrict__ dirty_next) {
   pdl_enter();
-  const int lane = threadIdx.x & 31, grp = lane >> 3, sub = lane & 7;
+  for (int f = blockIdx.x * blockDim.x + threadIdx.x; f < F.n; f += gridDim.x * blockDim.x) spare[f] = NO_BINDER;
+  const int lane = threadIdx.x & 31, sub = lane & 7;
+  const unsigned mask = 0xFFu << (lane & 24);                 // this item's eight lanes
   const int n_work = *count;
-  for (int w = blockIdx.x * 8 + (threadIdx.x >> 5); w < n_work; w += gridDim.x * 8) {
+  for (int w = (blockIdx.x * 8 + (threadIdx.x >> 5)) * 4 + (lane >> 3); w < n_work; w += gridDim.x * 32) {
     const uint4* ip = reinterpret_cast<const uint4*>(&items[work ? work[w] : w]);
     const uint4 h0 = ip[0], h1 = ip[1];
     const int i = (int)h0.x;
@@ -177,15 +184,33 @@ __global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, const uint8_t* 
     const float x = __uint_as_float(h0.z), y = __uint_as_float(h0.w), rad = __uint_as_float(h1.x), pr = __uint_as_float(h1.y);
     const int minLevel = (int)h1.z, maxLevel = (int)h1.w;
     const bool checkLevels = (minLevel > 0) || (maxLevel >= 0);
+    const int r_old = sub == 0 ? result[i] : 0;               // needed at the very end: in flight with everything else
     const uint4* qd = reinterpret_cast<const uint4*>(qdesc + (size_t)(qslot ? qslot[i] : i) * 32);
     const uint4 q0 = qd[0], q1 = qd[1];
-    unsigned long long b1 = ~0ull, b2 = ~0ull;  // (dist << 32 | visiting position), two smallest
+    // key = dist << 32 | visiting position (cx, cy, f) << 4 | octave: smallest = the reference's best, second = its
+    // second best; the iteration order here is free
+    unsigned long long b1 = ~0ull, b2 = ~0ull;
     bool any_cand = false;
-    // GetFeaturesInArea: only the features of the window's cells are visited (cell-sorted CSR); the reference's
-    // visiting order is carried by the key, so the iteration order here is free
-    for (int cy = cy0 + grp; cy <= cy1; cy += 4) {
-      const int js = F.cstart[cy * FRAME_GRID_COLS + cx0], je = F.cstart[cy * FRAME_GRID_COLS + cx1 + 1];
-      for (int j = js + sub; j < je; j += 8) {
+    for (int cyb = cy0; cyb <= cy1; cyb += 8) {
+      // GetFeaturesInArea: lane r owns grid row cyb + r; the row's cells cx0..cx1 are one contiguous CSR range
+      int js = 0, cnt = 0;
+      if (cyb + sub <= cy1) {
+        js = F.cstart[(cyb + sub) * FRAME_GRID_COLS + cx0];
+        cnt = F.cstart[(cyb + sub) * FRAME_GRID_COLS + cx1 + 1] - js;
+      }
+      int incl = cnt;
+#pragma unroll
+      for (int d = 1; d < 8; d <<= 1) { const int v = __shfl_up_sync(mask, incl, d, 8); if (sub >= d) incl += v; }
+      const int total = __shfl_sync(mask, incl, 7, 8);
+      for (int t0 = 0; t0 < total; t0 += 8) {
+        const int t = t0 + sub;
+        int j = -1, cy = 0;
+#pragma unroll
+        for (int r = 0; r < 8; r++) {                          // which row holds candidate t
+          const int e = __shfl_sync(mask, incl, r, 8), c = __shfl_sync(mask, cnt, r, 8), j0 = __shfl_sync(mask, js, r, 8);
+          if (t < e && t >= e - c) { j = j0 + (t - (e - c)); cy = cyb + r; }
+        }
+        if (j < 0) continue;
         const float4 r = F.rec[j];
         const unsigned bits = __float_as_uint(r.w);
         const int f = bits & 0xFFFF, oct = (bits >> 16) & 31, cx = (bits >> 21) & 63;
@@ -197,59 +222,51 @@ __global__ void __launch_bounds__(256) k_proj_round(ProjFrame F, const uint8_t* 
         any_cand = true;
         if ((bits >> 27) & 1u) continue;                                     // blocked0
         if (F.uright && r.z > 0.f && fabsf(__fsub_rn(pr, r.z)) > rad) continue;
-        if (binder_prev[f] < i) continue;
-        const int dist = hamming256(q0, q1, reinterpret_cast<const uint4*>(F.desc + (size_t)f * 32));
-        const unsigned long long key = ((unsigned long long)dist << 32) | ((unsigned)cx << 22) | ((unsigned)cy << 16) | (unsigned)f;
+        const int bp = binder_prev[f];                                       // binder and descriptor: one round trip
+        const uint4* fd = reinterpret_cast<const uint4*>(F.desc + (size_t)f * 32);
+        const uint4 d0 = fd[0], d1 = fd[1];
+        if (bp < i) continue;
+        const int dist = __popc(q0.x ^ d0.x) + __popc(q0.y ^ d0.y) + __popc(q0.z ^ d0.z) + __popc(q0.w ^ d0.w) +
+                         __popc(q1.x ^ d1.x) + __popc(q1.y ^ d1.y) + __popc(q1.z ^ d1.z) + __popc(q1.w ^ d1.w);
+        const unsigned long long key = ((unsigned long long)dist << 32) | ((unsigned)cx << 26) | ((unsigned)cy << 20) |
+                                       ((unsigned)f << 4) | (unsigned)oct;
         if (key < b1) { b2 = b1; b1 = key; }
         else if (key < b2) b2 = key;
       }
     }
     if (gate_out) {
-      const bool any = __any_sync(0xffffffffu, any_cand);
-      if (lane == 0) gate_out[i] = any ? 1 : 0;
+      const bool any = (__ballot_sync(mask, any_cand) & mask) != 0;
+      if (sub == 0) gate_out[i] = any ? 1 : 0;
     }
     unsigned long long B1 = b1;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) B1 = min(B1, __shfl_xor_sync(0xffffffffu, B1, o));
+    for (int o = 4; o > 0; o >>= 1) B1 = min(B1, __shfl_xor_sync(mask, B1, o));
     unsigned long long B2 = (b1 == B1) ? b2 : b1;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) B2 = min(B2, __shfl_xor_sync(0xffffffffu, B2, o));
-    int res = -1;
-    if (B1 != ~0ull) {
-      const int bestDist = (int)(B1 >> 32), bestIdx = (int)(B1 & 0xFFFF);
-      if (bestDist <= TH_HIGH_P) {
-        bool ok = true;
-        if (mode0) {
-          int bestDist2 = 256, bestLevel2 = -1;
-          if (B2 != ~0ull) { bestDist2 = (int)(B2 >> 32); bestLevel2 = F.octave[(int)(B2 & 0xFFFF)]; }
-          const int bestLevel = F.octave[bestIdx];
-          if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(nnratio, (float)bestDist2)) ok = false;
+    for (int o = 4; o > 0; o >>= 1) B2 = min(B2, __shfl_xor_sync(mask, B2, o));
+    if (sub == 0) {
+      int res = -1;
+      if (B1 != ~0ull) {
+        const int bestDist = (int)(B1 >> 32), bestIdx = (int)((B1 >> 4) & 0xFFFF), bestLevel = (int)(B1 & 15);
+        if (bestDist <= TH_HIGH_P) {
+          bool ok = true;
+          if (mode0) {
+            int bestDist2 = 256, bestLevel2 = -1;
+            if (B2 != ~0ull) { bestDist2 = (int)(B2 >> 32); bestLevel2 = (int)(B2 & 15); }
+            if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(nnratio, (float)bestDist2)) ok = false;
+          }
+          if (ok) res = bestIdx;
         }
-        if (ok) res = bestIdx;
       }
-    }
-    if (lane == 0) {
-      if (result[i] != res) { result[i] = res; *changed = 1; }
+      if (r_old != res) {
+        result[i] = res; *changed = 1;
+        if (has_obs) {          // only points with observations bind a feature (src/ORBmatcher.cc:79-81)
+          if (r_old >= 0) { const int cx = F.cellx[r_old], cy = F.celly[r_old]; atomicOr(&dirty_next[2 * cy + (cx >> 5)], 1u << (cx & 31)); }
+          if (res >= 0) { const int cx = F.cellx[res], cy = F.celly[res]; atomicOr(&dirty_next[2 * cy + (cx >> 5)], 1u << (cx & 31)); }
+        }
+      }
       if (res >= 0 && has_obs) atomicMin(&binder_next[res], i);
     }
-  }
-  // ---- last CTA through: dirty cells for the next round (binder_next = this round's table against binder_prev =
-  // the round before), and binder_prev emptied: it is the next round's table to fill
-  __shared__ bool s_last;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence();
-    s_last = atomicAdd(ticket, 1) == (int)gridDim.x - 1;
-  }
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
-  for (int f = threadIdx.x; f < F.n; f += blockDim.x) {
-    const bool diff = __ldcg(&binder_next[f]) != __ldcg(&binder_prev[f]);
-    binder_prev[f] = NO_BINDER;
-    if (!diff) continue;
-    const int cx = F.cellx[f], cy = F.celly[f];
-    if (cx >= 0) atomicOr(&dirty_next[2 * cy + (cx >> 5)], 1u << (cx & 31));
   }
 }
 
@@ -270,10 +287,22 @@ thread_local HostStage t_stage;
 // number of rounds (>= 1) or a negative error code; the stream is synchronised on return.
 // arena bytes projection_rounds takes for m query points (on top of frame_bytes(n), which covers the binder tables)
 inline size_t rounds_bytes(int m) { return (size_t)std::max(m, 1) * (sizeof(ProjItem) + 4) + sizeof(RoundCtl) + 4 * 256; }
+static_assert(MAX_LEVELS <= 16, "the octave rides in the low four bits of the candidate key (k_proj_round)");
 
-static int projection_rounds(Arena& A, cudaStream_t st, const ProjFrame& F, const ProjQuery& Q, int* result) {
+struct PinnedFlags {  // per host thread: the batch's flags come back by DMA into pinned memory (a pageable target is staged)
+  int* p = nullptr;
+  int* get() { if (!p && cudaHostAlloc((void**)&p, 64, cudaHostAllocDefault) != cudaSuccess) p = nullptr; return p; }
+};
+static thread_local PinnedFlags t_flags;
+
+// after_batch (optional): enqueued behind every batch of rounds, before the flags are read back - what the caller wants
+// on the host together with the verdict (its copies ride the same synchronisation; a batch that did not converge
+// simply runs it again)
+template <class AfterBatch>
+static int projection_rounds(Arena& A, cudaStream_t st, const ProjFrame& F, const ProjQuery& Q, int* result, AfterBatch after_batch) {
   const int n = F.n, m = Q.n;
-  int* binder[2] = {A.take<int>(n), A.take<int>(n)};
+  // binder tables: round r reads [r % 3] (the claims of round r - 1), fills [(r + 1) % 3] and empties [(r + 2) % 3]
+  int* binder[3] = {A.take<int>(n), A.take<int>(n), A.take<int>(n)};
   // Binding rounds to the sequential fixed point, enqueued ROUND_BATCH at a time with no host round trip in
   // between; round k of a batch sets flag[k] when a result changed and the host reads the batch's flags once.
   // Rounds past the fixed point are idempotent (equal results -> equal binder tables -> no dirty cell -> every
@@ -290,7 +319,9 @@ static int projection_rounds(Arena& A, cudaStream_t st, const ProjFrame& F, cons
   int device = 0, sms = 148;
   cudaGetDevice(&device);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-  const int round_grid = std::max(1, std::min((m + 7) / 8, sms * 6));   // 40 registers: 6 CTAs of 256 threads per SM
+  int per_sm = 4;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_proj_round, 256, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
+  const int round_grid = std::max(1, std::min((m + 31) / 32, sms * per_sm));   // 32 items per CTA pass, every CTA resident
   int rounds = 0;
   for (bool converged = false; !converged;) {
     if (rounds > m + 2) { set_error("projection search did not converge"); return CUORB_E_CUDA; }
@@ -302,8 +333,9 @@ static int projection_rounds(Arena& A, cudaStream_t st, const ProjFrame& F, cons
       CUORB_CUDA_TRY(cudaMemsetAsync(ctl->dirty[1], 0, sizeof(RoundCtl) - sizeof(ctl->dirty[0]), st));
     }
     for (int k = 0; k < ROUND_BATCH; k++, rounds++) {
-      int* prev = binder[rounds & 1];
-      int* next = binder[(rounds + 1) & 1];
+      int* prev = binder[rounds % 3];
+      int* next = binder[(rounds + 1) % 3];
+      int* spare = binder[(rounds + 2) % 3];
       t_pdl = pdl && k != 0;   // the batch's first kernel follows memsets: plain stream order
       if (rounds == 0)
         launch_k(k_proj_begin, dim3((std::max(m, n) + 255) / 256), dim3(256), 0, st, F, Q, binder[0], binder[1], result, items, n_items);
@@ -313,17 +345,28 @@ static int projection_rounds(Arena& A, cudaStream_t st, const ProjFrame& F, cons
       t_pdl = pdl;
       launch_k(k_proj_round, dim3(round_grid), dim3(256), 0, st, F, Q.desc, Q.slot, Q.gate_out, Q.mode == 0 ? 1 : 0, Q.nnratio,
                (const ProjItem*)items, rounds == 0 ? (const int*)nullptr : (const int*)work,
-               rounds == 0 ? (const int*)n_items : (const int*)(ctl->count + k), prev, next, result, ctl->flag + k,
-               ctl->dirty[k + 1], ctl->ticket + k);
+               rounds == 0 ? (const int*)n_items : (const int*)(ctl->count + k), (const int*)prev, next, spare, result,
+               ctl->flag + k, ctl->dirty[k + 1]);
       count_launch(2);
     }
-    int h_flag[ROUND_BATCH];
-    CUORB_CUDA_TRY(cudaMemcpyAsync(h_flag, ctl->flag, sizeof(h_flag), cudaMemcpyDeviceToHost, st));
+    t_pdl = false;
+    {
+      const int rc = after_batch();
+      if (rc < 0) return rc;
+    }
+    int stack_flag[ROUND_BATCH];
+    int* h_flag = t_flags.get();
+    if (!h_flag) h_flag = stack_flag;
+    CUORB_CUDA_TRY(cudaMemcpyAsync(h_flag, ctl->flag, sizeof(stack_flag), cudaMemcpyDeviceToHost, st));
     CUORB_CUDA_TRY(cudaStreamSynchronize(st));
     for (int k = 0; k < ROUND_BATCH; k++)
       if (!h_flag[k]) { converged = true; rounds -= ROUND_BATCH - 1 - k; break; }   // rounds to the first quiet one, inclusive
   }
   return rounds;
+}
+
+static int projection_rounds(Arena& A, cudaStream_t st, const ProjFrame& F, const ProjQuery& Q, int* result) {
+  return projection_rounds(A, st, F, Q, result, [] { return 0; });
 }
 
 static int run_projection(int device, const cuorb_frame_view* fv, ProjQuery Q, const uint8_t* qdesc,
@@ -692,7 +735,13 @@ struct cuorb_localmap {
   uint8_t *desc = nullptr, *pflags = nullptr, *skip = nullptr, *qflags = nullptr;
   float *px = nullptr, *py = nullptr, *pxr = nullptr, *vc = nullptr, *dz = nullptr;
   int *lv = nullptr, *result = nullptr, *match_mp = nullptr, *match_feat = nullptr, *counters = nullptr, *order = nullptr;
-  int *h_counters = nullptr;    // pinned: [0] in view, [1] matches
+  // counters ([0] in view, [1] matches), match_mp and match_feat are views of ONE allocation (out_pack), so the pair
+  // list and the counters come back in one copy into h_out (pinned: out_pack's image, then qflags, then result)
+  int *out_pack = nullptr;
+  unsigned char* h_out = nullptr;
+  // skip[] and the counters are all zero: every search clears them behind itself (off the next call's critical path);
+  // false after a call that returned early
+  bool scratch_clean = false;
   cudaStream_t stream = nullptr;
   cudaEvent_t producer_done = nullptr;   // orders a device-resident frame's producer stream before this map's stream
 };
@@ -707,9 +756,10 @@ cuorb_localmap* cuorb_localmap_create(int device, int capacity) {
   auto al = [&](auto** p, size_t bytes) { if (ok && cudaMalloc((void**)p, bytes) != cudaSuccess) ok = false; };
   al(&m->P, 12 * c); al(&m->N, 12 * c); al(&m->minD, 4 * c); al(&m->maxD, 4 * c); al(&m->desc, 32 * c); al(&m->pflags, c);
   al(&m->skip, c); al(&m->qflags, c); al(&m->px, 4 * c); al(&m->py, 4 * c); al(&m->pxr, 4 * c); al(&m->vc, 4 * c);
-  al(&m->dz, 4 * c); al(&m->lv, 4 * c); al(&m->result, 4 * c); al(&m->match_mp, 4 * c); al(&m->match_feat, 4 * c); al(&m->order, 4 * c);
-  al(&m->counters, 2 * sizeof(int));
-  if (ok && cudaHostAlloc((void**)&m->h_counters, 2 * sizeof(int), cudaHostAllocDefault) != cudaSuccess) ok = false;
+  al(&m->dz, 4 * c); al(&m->lv, 4 * c); al(&m->result, 4 * c); al(&m->order, 4 * c);
+  al(&m->out_pack, (2 + 2 * c) * sizeof(int));
+  if (ok) { m->counters = m->out_pack; m->match_mp = m->out_pack + 2; }
+  if (ok && cudaHostAlloc((void**)&m->h_out, (2 + 2 * c) * sizeof(int) + c + 4 * c + 64, cudaHostAllocDefault) != cudaSuccess) ok = false;
   if (ok && cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess) ok = false;
   if (ok && cudaEventCreateWithFlags(&m->producer_done, cudaEventDisableTiming) != cudaSuccess) ok = false;
   if (ok && cudaMemset(m->pflags, CUORB_MP_BAD, c) != cudaSuccess) ok = false;   // slots never written are bad points
@@ -723,9 +773,9 @@ void cuorb_localmap_destroy(cuorb_localmap* m) {
   if (m->stream) { cudaStreamSynchronize(m->stream); cudaStreamDestroy(m->stream); }
   if (m->producer_done) cudaEventDestroy(m->producer_done);
   void* ptrs[] = {m->P, m->N, m->minD, m->maxD, m->desc, m->pflags, m->skip, m->qflags, m->px, m->py, m->pxr, m->vc, m->dz,
-                  m->lv, m->result, m->match_mp, m->match_feat, m->counters, m->order};
+                  m->lv, m->result, m->out_pack, m->order};
   for (void* p : ptrs) if (p) cudaFree(p);
-  if (m->h_counters) cudaFreeHost(m->h_counters);
+  if (m->h_out) cudaFreeHost(m->h_out);
   delete m;
 }
 
@@ -785,8 +835,11 @@ static int localmap_search_impl(cuorb_localmap* m, const cuorb_frustum_camera* c
   const size_t bytes = frame_bytes(std::max(n, 1)) + rounds_bytes(M) + (size_t)std::max(n, 1) * (8 + sizeof(cuorb_keypoint)) + (size_t)n_skip * 4 + 64 * 1024;
   if (t_arena.reserve(m->device, bytes) != 0) { set_error("cudaMalloc failed (local map search workspace)"); return CUORB_E_CUDA; }
   Arena& A = t_arena;
-  CUORB_CUDA_TRY(cudaMemsetAsync(m->skip, 0, (size_t)M, st));
-  CUORB_CUDA_TRY(cudaMemsetAsync(m->counters, 0, 2 * sizeof(int), st));
+  if (!m->scratch_clean) {
+    CUORB_CUDA_TRY(cudaMemsetAsync(m->skip, 0, (size_t)m->capacity, st));
+    CUORB_CUDA_TRY(cudaMemsetAsync(m->counters, 0, 2 * sizeof(int), st));
+  }
+  m->scratch_clean = false;
   if (order) CUORB_CUDA_TRY(cudaMemcpyAsync(m->order, order, sizeof(int) * (size_t)M, cudaMemcpyHostToDevice, st));
   if (n_skip) {
     const int* d_idx = up(A, skip_pos, n_skip, st);
@@ -797,7 +850,14 @@ static int localmap_search_impl(cuorb_localmap* m, const cuorb_frustum_camera* c
                                                       m->pflags, m->skip, viewing_cos_limit, m->px, m->py, m->pxr, m->lv,
                                                       m->vc, m->dz, m->qflags, m->counters);
   count_launch();
-  int nmatches = 0;
+  // Everything the caller gets back lands in h_out (pinned) behind ONE synchronisation: [counters | pairs] as one
+  // copy of out_pack's head, then mbTrackInView, then the per-point results.  The tracking flags do not change during
+  // the rounds, so their copy is enqueued right away; the rest follows each batch of rounds (projection_rounds).
+  const int fetch = n > 0 ? std::min(match_capacity, M) : 0;
+  int* h_pack = (int*)m->h_out;
+  uint8_t* h_view = m->h_out + (2 + 2 * (size_t)m->capacity) * sizeof(int);
+  int* h_best = (int*)(h_view + (((size_t)m->capacity + 63) & ~(size_t)63));
+  if (in_view_out) CUORB_CUDA_TRY(cudaMemcpyAsync(h_view, m->qflags, (size_t)M, cudaMemcpyDeviceToHost, st));
   if (n > 0) {
     ProjFrame F;
     const cuorb_keypoint* d_keys_un = nullptr;
@@ -816,29 +876,35 @@ static int localmap_search_impl(cuorb_localmap* m, const cuorb_frustum_camera* c
     Q.n = M; Q.mode = 0; Q.th = th; Q.thFar = th_far_points; Q.nnratio = nn_ratio; Q.far_points = far_points;
     Q.desc = m->desc; Q.px = m->px; Q.py = m->py; Q.aux = m->pxr; Q.level = m->lv; Q.viewcos = m->vc; Q.depth = m->dz;
     Q.flags = m->qflags; Q.slot = order ? m->order : nullptr;
-    const int rounds = projection_rounds(A, st, F, Q, m->result);
+    m->match_feat = m->match_mp + fetch;          // the pair list is contiguous behind the counters: one copy
+    bool first_batch = true;
+    const int rounds = projection_rounds(A, st, F, Q, m->result, [&]() -> int {
+      if (!first_batch) CUORB_CUDA_TRY(cudaMemsetAsync(m->counters + 1, 0, sizeof(int), st));
+      first_batch = false;
+      k_compact_matches<<<(M + 255) / 256, 256, 0, st>>>(M, m->result, fetch, m->match_mp, m->match_feat, m->counters + 1);
+      count_launch();
+      CUORB_CUDA_TRY(cudaMemcpyAsync(h_pack, m->out_pack, sizeof(int) * (2 + 2 * (size_t)fetch), cudaMemcpyDeviceToHost, st));
+      if (best_idx_out) CUORB_CUDA_TRY(cudaMemcpyAsync(h_best, m->result, sizeof(int) * (size_t)M, cudaMemcpyDeviceToHost, st));
+      return 0;
+    });
     if (rounds < 0) return rounds;
-    k_compact_matches<<<(M + 255) / 256, 256, 0, st>>>(M, m->result, match_capacity, m->match_mp, m->match_feat, m->counters + 1);
-    count_launch();
+  } else {
+    CUORB_CUDA_TRY(cudaMemcpyAsync(h_pack, m->out_pack, sizeof(int) * 2, cudaMemcpyDeviceToHost, st));
+    CUORB_CUDA_TRY(cudaStreamSynchronize(st));
   }
-  if (in_view_out) CUORB_CUDA_TRY(cudaMemcpyAsync(in_view_out, m->qflags, (size_t)M, cudaMemcpyDeviceToHost, st));
-  CUORB_CUDA_TRY(cudaMemcpyAsync(m->h_counters, m->counters, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
-  if (best_idx_out && n > 0) CUORB_CUDA_TRY(cudaMemcpyAsync(best_idx_out, m->result, sizeof(int) * (size_t)M, cudaMemcpyDeviceToHost, st));
-  // the pairs come back with the counters in one round trip: the first match_capacity slots, whatever they hold
-  const int fetch = n > 0 ? std::min(match_capacity, M) : 0;
-  if (fetch > 0) {
-    CUORB_CUDA_TRY(cudaMemcpyAsync(match_pos_out, m->match_mp, sizeof(int) * (size_t)fetch, cudaMemcpyDeviceToHost, st));
-    CUORB_CUDA_TRY(cudaMemcpyAsync(match_feature_out, m->match_feat, sizeof(int) * (size_t)fetch, cudaMemcpyDeviceToHost, st));
-  }
-  CUORB_CUDA_TRY(cudaStreamSynchronize(st));
-  if (n_in_view_out) *n_in_view_out = m->h_counters[0];
-  if (in_view_out) for (int i = 0; i < M; i++) in_view_out[i] &= CUORB_MP_IN_VIEW;
-  nmatches = m->h_counters[1];
+  // leave the scratch clean for the next frame (asynchronous: runs while the caller works on this frame's result)
+  if ((n_skip == 0 || cudaMemsetAsync(m->skip, 0, (size_t)M, st) == cudaSuccess) &&
+      cudaMemsetAsync(m->counters, 0, 2 * sizeof(int), st) == cudaSuccess)
+    m->scratch_clean = true;
+  if (n_in_view_out) *n_in_view_out = h_pack[0];
+  if (in_view_out) for (int i = 0; i < M; i++) in_view_out[i] = h_view[i] & CUORB_MP_IN_VIEW;
+  if (best_idx_out && n > 0) memcpy(best_idx_out, h_best, sizeof(int) * (size_t)M);
+  const int nmatches = n > 0 ? h_pack[1] : 0;
   if (match_capacity) {
     if (nmatches > match_capacity) { set_error("cuorb_localmap_search: more matches than match_capacity"); return CUORB_E_CAPACITY; }
     // MapPoint order = the order in which the caller replays F.mvpMapPoints[feature] = pMP
     std::vector<std::pair<int32_t, int32_t>> pairs((size_t)nmatches);
-    for (int k = 0; k < nmatches; k++) pairs[k] = {match_pos_out[k], match_feature_out[k]};
+    for (int k = 0; k < nmatches; k++) pairs[k] = {h_pack[2 + k], h_pack[2 + fetch + k]};
     std::sort(pairs.begin(), pairs.end());
     for (int k = 0; k < nmatches; k++) { match_pos_out[k] = pairs[k].first; match_feature_out[k] = pairs[k].second; }
   }

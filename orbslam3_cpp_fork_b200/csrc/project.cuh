@@ -79,11 +79,15 @@ inline T* up(Arena& A, const T* host, size_t count, cudaStream_t st) {
 }
 
 
-inline size_t frame_bytes(int n) { return (size_t)n * (4 * 4 + 2 * 2 + 32 + 1 + 8 + 2 + 16) + (FRAME_GRID_ROWS * FRAME_GRID_COLS + 1) * 4 + 20 * 256; }
+inline size_t frame_bytes(int n) { return (size_t)n * (4 * 4 + 2 * 2 + 32 + 1 + 12 + 2 + 16) + (FRAME_GRID_ROWS * FRAME_GRID_COLS + 1) * 4 + 20 * 256; }
 
 struct HostStage {  // grow-only pinned staging per host thread: a Frame's SoA goes up as ONE copy
   void* p = nullptr; size_t cap = 0;
+  cudaEvent_t sent = nullptr; int ev_device = -1; bool pending = false;   // the last copy out of the block
+  // the block, free for writing: waits for the copy enqueued by the previous user (normally long complete - every
+  // search synchronises its stream before it returns)
   void* get(size_t bytes) {
+    if (pending) { cudaEventSynchronize(sent); pending = false; }
     if (bytes > cap) {
       if (p) { cudaFreeHost(p); p = nullptr; cap = 0; }
       if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) { p = nullptr; return nullptr; }
@@ -91,12 +95,23 @@ struct HostStage {  // grow-only pinned staging per host thread: a Frame's SoA g
     }
     return p;
   }
+  // call right after enqueueing the copy out of the block on `st`; false = no event (the caller must synchronise)
+  bool mark_sent(cudaStream_t st) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (sent && dev != ev_device) { cudaEventDestroy(sent); sent = nullptr; }
+    if (!sent) { if (cudaEventCreateWithFlags(&sent, cudaEventDisableTiming) != cudaSuccess) { sent = nullptr; return false; } ev_device = dev; }
+    if (cudaEventRecord(sent, st) != cudaSuccess) return false;
+    pending = true;
+    return true;
+  }
 };
 extern thread_local HostStage t_stage;
 
 // host-side flattening of the Frame: SoA + PosInGrid (src/Frame.cc:867-877, std::round) + the cell-sorted CSR, laid
 // out in one pinned staging block and sent with one copy (ten small pageable copies before: ~35 us of a 0.3-0.5 ms
-// call); the arena must already hold frame_bytes(n) more bytes.  Synchronises the stream: the staging block is reused.
+// call); the arena must already hold frame_bytes(n) more bytes.  Does not wait for the copy: the staging block is
+// guarded by an event that the next upload on this thread waits for.
 inline void upload_frame(Arena& A, const cuorb_frame_view* fv, cudaStream_t st, ProjFrame& F) {
   const int n = fv->n, nn = std::max(n, 1);
   const int ncell = FRAME_GRID_ROWS * FRAME_GRID_COLS + 1;
@@ -142,6 +157,7 @@ inline void upload_frame(Arena& A, const cuorb_frame_view* fv, cudaStream_t st, 
   if (fv->u_right && n) memcpy(h + o_ur, fv->u_right, 4 * (size_t)n);
   unsigned char* d = A.take<unsigned char>(total);
   cudaMemcpyAsync(d, h, total, cudaMemcpyHostToDevice, st);
+  if (h != t_stage.p || !t_stage.mark_sent(st)) cudaStreamSynchronize(st);   // pageable fallback block / no event: drain now
   F.n = n;
   F.cstart = (const int*)(d + o_cstart); F.order = (const unsigned short*)(d + o_order);
   F.rec = (const float4*)(d + o_rec);
@@ -154,7 +170,6 @@ inline void upload_frame(Arena& A, const cuorb_frame_view* fv, cudaStream_t st, 
   F.minX = fv->min_x; F.minY = fv->min_y; F.maxX = fv->max_x; F.maxY = fv->max_y;
   F.gwinv = fv->grid_w_inv; F.ghinv = fv->grid_h_inv; F.mbf = fv->mbf;
   for (int l = 0; l < MAX_LEVELS; l++) F.scale[l] = l < fv->nlevels ? fv->scale_factors[l] : 0.f;
-  cudaStreamSynchronize(st);  // the staging block is reused by the next upload
 }
 
 }  // namespace cuorb
