@@ -32,9 +32,10 @@ def main():
     from tests.matching_cases import extracted_frame, localmap_case, mappoint_case
     e, k, d = extracted_frame()
     sf = np.asarray(e.tables()[0], np.float32)
-    c = localmap_case(k, d, sf, 50000, 11)
+    M_ = int(os.environ.get("LM_POINTS", "50000"))
+    c = localmap_case(k, d, sf, M_, 11)
     cam = _lib.FrustumCamera.from_buffer_copy(bytes(c["cam"]))
-    m = cu.LocalMap(50000)
+    m = cu.LocalMap(M_)
     m.update(0, c["P"], c["N"], c["min_d"], c["max_d"], c["desc"], c["bad"], c["has_obs"])
 
     def frame():
@@ -49,8 +50,8 @@ def main():
     dk = torch.from_numpy(np.ascontiguousarray(k).view(np.uint8).copy()).cuda(); dd = torch.from_numpy(np.ascontiguousarray(d)).cuda()
     du = torch.from_numpy(np.ascontiguousarray(c["u_right"], np.float32)).cuda()
     torch.cuda.synchronize()
-    for title, fn in (("cuorb_localmap_search_resident, 50k points", lambda: m.search_resident(cam, frame(), dk.data_ptr(), dd.data_ptr(), du.data_ptr(), skip_idx=c["skip_idx"], thFarPoints=50.0, want_best=False, match_capacity=4096)),
-                      ("cuorb_localmap_search, 50k points", lambda: m.search(cam, frame(), c["skip_idx"], 0.5, 1.0, False, 50.0, 0.8, want_best=False, match_capacity=4096)),
+    for title, fn in ((f"cuorb_localmap_search_resident, {M_} points", lambda: m.search_resident(cam, frame(), dk.data_ptr(), dd.data_ptr(), du.data_ptr(), skip_idx=c["skip_idx"], thFarPoints=50.0, want_best=False, match_capacity=4096)),
+                      (f"cuorb_localmap_search, {M_} points", lambda: m.search(cam, frame(), c["skip_idx"], 0.5, 1.0, False, 50.0, 0.8, want_best=False, match_capacity=4096)),
                       ("cuorb_search_by_projection, 50k MapPoints (cfg4)", lambda: M.SearchByProjection(frame(), mps, 3.0))):
         for _ in range(5):
             fn()
