@@ -15,6 +15,7 @@
 // (atomicMin of the binder index per feature).  MapPoint 0 is final after round 1, MapPoint i once
 // every j < i it depends on is final, and a round that changes nothing is the sequential result.
 #include <algorithm>
+#include <cstdlib>
 #include <cmath>
 #include <mutex>
 
@@ -52,7 +53,7 @@ struct __align__(16) ProjItem {
 
 // Control block of one batch of rounds (device ints): dirty[k] = one bit per grid cell holding a feature that a point
 // joined or left in the round before round k (slot ROUND_BATCH carries over to the next batch's slot 0).
-constexpr int ROUND_BATCH = 6;   // rounds per host sync; 2 / 3 / 4: cfg4 0.558 / 0.561 / 0.581 ms against 0.525 (r02_s9)
+constexpr int ROUND_BATCH = 6;   // most rounds per host sync (projection_rounds picks 4 or 6)
 constexpr int DIRTY_WORDS = 2 * FRAME_GRID_ROWS;
 struct RoundCtl {
   unsigned dirty[ROUND_BATCH + 1][DIRTY_WORDS];
@@ -322,6 +323,13 @@ static int projection_rounds(Arena& A, cudaStream_t st, const ProjFrame& F, cons
   int per_sm = 4;
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_proj_round, 256, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
   const int round_grid = std::max(1, std::min((m + 31) / 32, sms * per_sm));   // 32 items per CTA pass, every CTA resident
+  // Rounds per host sync.  How many rounds the fixed point takes grows with the number of points that chase one
+  // feature: 4 (3 + the quiet one) at 2 - 10 points per feature of the frame, 6 at 50 (the 50k-point benchmark map).
+  // A batch that stops short pays a second sync and a second batch; one that runs long pays ~4 us per idle round.
+  // Measured (profiles/r02_s45_round_batch.txt): 2k / 4k / 10k points 0.099 / 0.107 / 0.119 ms at 4 per batch against
+  // 0.110 / 0.117 / 0.130 at 6; 50k points 0.199 at 4 against 0.161 at 6.  CUORB_ROUND_BATCH overrides.
+  static const int batch_env = getenv("CUORB_ROUND_BATCH") ? atoi(getenv("CUORB_ROUND_BATCH")) : 0;
+  const int batch = batch_env >= 1 && batch_env <= ROUND_BATCH ? batch_env : ((long long)m <= 16LL * n ? 4 : ROUND_BATCH);
   int rounds = 0;
   for (bool converged = false; !converged;) {
     if (rounds > m + 2) { set_error("projection search did not converge"); return CUORB_E_CUDA; }
@@ -329,10 +337,10 @@ static int projection_rounds(Arena& A, cudaStream_t st, const ProjFrame& F, cons
       CUORB_CUDA_TRY(cudaMemsetAsync(n_items, 0, sizeof(int), st));
       CUORB_CUDA_TRY(cudaMemsetAsync(ctl, 0, sizeof(RoundCtl), st));
     } else {   // the last round's dirty cells are the next batch's first; everything else starts from zero
-      CUORB_CUDA_TRY(cudaMemcpyAsync(ctl->dirty[0], ctl->dirty[ROUND_BATCH], sizeof(ctl->dirty[0]), cudaMemcpyDeviceToDevice, st));
+      CUORB_CUDA_TRY(cudaMemcpyAsync(ctl->dirty[0], ctl->dirty[batch], sizeof(ctl->dirty[0]), cudaMemcpyDeviceToDevice, st));
       CUORB_CUDA_TRY(cudaMemsetAsync(ctl->dirty[1], 0, sizeof(RoundCtl) - sizeof(ctl->dirty[0]), st));
     }
-    for (int k = 0; k < ROUND_BATCH; k++, rounds++) {
+    for (int k = 0; k < batch; k++, rounds++) {
       int* prev = binder[rounds % 3];
       int* next = binder[(rounds + 1) % 3];
       int* spare = binder[(rounds + 2) % 3];
@@ -359,8 +367,8 @@ static int projection_rounds(Arena& A, cudaStream_t st, const ProjFrame& F, cons
     if (!h_flag) h_flag = stack_flag;
     CUORB_CUDA_TRY(cudaMemcpyAsync(h_flag, ctl->flag, sizeof(stack_flag), cudaMemcpyDeviceToHost, st));
     CUORB_CUDA_TRY(cudaStreamSynchronize(st));
-    for (int k = 0; k < ROUND_BATCH; k++)
-      if (!h_flag[k]) { converged = true; rounds -= ROUND_BATCH - 1 - k; break; }   // rounds to the first quiet one, inclusive
+    for (int k = 0; k < batch; k++)
+      if (!h_flag[k]) { converged = true; rounds -= batch - 1 - k; break; }   // rounds to the first quiet one, inclusive
   }
   return rounds;
 }
