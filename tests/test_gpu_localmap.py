@@ -152,3 +152,21 @@ def test_localmap_empty_frame_and_inactive_slots(fr):
     n, n_in, mp, ft, best, inv = m.search(_cam(c), _frame(k, d, sf, c), [], 0.5, 1.0, False, 30.0, 0.8, order=order, want_in_view=True)
     assert (inv[[2, 4, 6]] == 0).all() and (best[[2, 4, 6]] == -1).all()
     assert (inv[[0, 1, 3, 5]] == want[[0, 1, 2, 3]]).all()
+
+
+@pytest.mark.parametrize("env_over", [{"CUORB_ROUND_BATCH": "1"}, {"CUORB_ROUND_BATCH": "6"}, {"CUORB_PDL": "0"}],
+                         ids=lambda d: ",".join(f"{k[6:]}={v}" for k, v in d.items()))
+def test_round_scheduling_switches_subprocess(env_over):
+    """How the binding rounds are enqueued (rounds per host synchronisation, dependent launches or plain stream order)
+    must not show in the result: one round per sync walks the batch-to-batch carry-over of the dirty cells every
+    round.  The switches are read once per process, hence the subprocess, which re-runs tests of this file and the
+    crafted tie-heavy frame of test_gpu_localmap_resident.py."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, **env_over)
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-m", "gpu", "-x",
+                        "tests/test_gpu_localmap.py::test_localmap_search_equals_its_two_parts",
+                        "tests/test_gpu_localmap.py::test_localmap_processing_order_and_in_view",
+                        "tests/test_gpu_localmap_resident.py::test_resident_cell_order_decides_ties"],
+                       env=env, cwd=root, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0 and " passed" in r.stdout, r.stdout[-3000:] + r.stderr[-2000:]
