@@ -3,11 +3,12 @@
 // and SearchByProjection(Frame& Cur, const Frame& Last, th, bMono), :1684-1811, 1889-1908; pinhole
 // branches) plus Frame::GetFeaturesInArea / PosInGrid (src/Frame.cc:788-877).
 //
-// One warp per MapPoint; it visits the features of its GetFeaturesInArea cell window through a cell-sorted CSR
-// of the frame (built on the host while the frame is flattened: a counting sort of <= a few thousand features)
-// and applies the exact predicate (level window, |dx|,|dy| < r); the reference's candidate visiting order (cell
-// ix, then iy, then insertion = feature index) is part of the arg-min key, which reproduces its "first strict
-// minimum wins" and best/second-best bookkeeping whatever order the lanes see the candidates in.
+// Eight lanes per MapPoint; they visit the features of its GetFeaturesInArea cell window through a cell-sorted CSR
+// of the frame (a counting sort of <= a few thousand features, made on the host while the frame is flattened -
+// upload_frame - or on the device from the extractor's output - k_frame_build) and apply the exact predicate (level
+// window, |dx|,|dy| < r); the reference's candidate visiting order (cell ix, then iy, then insertion = feature index)
+// is part of the arg-min key, which reproduces its "first strict minimum wins" and best/second-best bookkeeping
+// whatever order the lanes see the candidates in.
 //
 // The reference loop is order dependent: a feature bound to a MapPoint with observations is
 // skipped by all later MapPoints (:96-100, :1763-1767).  That is resolved by fixed-point rounds:
